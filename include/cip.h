@@ -1,0 +1,167 @@
+/* cip.h -- C-ABI of the B200-native invert hot path (libcip_b200.so).
+ *
+ * Drop-in boundary for the step the reference delegates to native code:
+ *
+ *   reference interface                                           replaced by
+ *   ------------------------------------------------------------  -------------------------
+ *   ducc0.wgridder.ms2dirty(uvw, freq, ms, wgt, npix_x, npix_y,    cip_invert
+ *     pixsize_x, pixsize_y, epsilon=, do_wstacking=, nthreads=,    (cip_scan + cip_plan_make +
+ *     mask=)   call site src/ska_sdp_cip/invert.py:170-183          cip_grid_accumulate +
+ *                                                                   cip_correct_image when the
+ *                                                                   visibilities are sharded)
+ *   effective_weights.sum()         src/ska_sdp_cip/invert.py:184  cip_scan_result.sum_wgt
+ *   StokesIGridderInput.from_measurement_set_reader / effective_weights
+ *                                   src/ska_sdp_cip/invert.py:72-116   cip_stokes_i
+ *   create_uvw_tile_mapping(uvw, tile_size, channel_freqs)         cip_tile_bin
+ *     src/ska_sdp_cip/uvw_tiling/tiling_plan.py:84-134 (and :29-61, :150-181)
+ *   Tile._from_jagged_visibilities_slice                           cip_tile_gather
+ *     src/ska_sdp_cip/uvw_tiling/tile.py:83-115
+ *   integrate_weighted_images (sum of chunk images / sum of weights)
+ *     src/ska_sdp_cip/invert.py:200-209                            caller-side NCCL reduce of the
+ *                                                                   uncorrected images, then
+ *                                                                   cip_correct_image(scale=1/sum)
+ *
+ * Conventions: plain pointers and sizes only; the caller owns every input and
+ * output buffer; the library owns what hangs off cip_ctx (streams, cuFFT plans,
+ * device workspaces).  A cip_ctx is bound to one CUDA device and is not
+ * re-entrant (one context per process and GPU).  Every entry point returns a
+ * cip_status; cip_last_error() gives a thread-local message for the last
+ * failure.  There is no CPU fallback: without a CUDA device cip_ctx_create fails.
+ */
+#ifndef CIP_H
+#define CIP_H
+
+#include <stdint.h>
+
+#ifdef __cplusplus
+extern "C" {
+#endif
+
+typedef struct cip_ctx cip_ctx;
+
+typedef enum {
+  CIP_OK = 0,
+  CIP_EINVAL = 1, /* bad argument (Python shim raises ValueError)            */
+  CIP_ENOMEM = 2, /* device memory exhausted                                 */
+  CIP_ECUDA = 3,  /* CUDA runtime error, incl. "no device" (RuntimeError)    */
+  CIP_ECUFFT = 4  /* cuFFT error                                             */
+} cip_status;
+
+const char* cip_last_error(void);
+const char* cip_version(void);
+
+/* device < 0: use the current CUDA device */
+cip_status cip_ctx_create(int device, cip_ctx** out);
+cip_status cip_ctx_destroy(cip_ctx* ctx);
+/* The stream all work of this context is enqueued on (a cudaStream_t). */
+void* cip_ctx_stream(cip_ctx* ctx);
+cip_status cip_ctx_synchronize(cip_ctx* ctx);
+
+/* ---- ms2dirty arguments, 1:1 (invert.py:170-183) -------------------------------- */
+typedef struct {
+  const double* uvw;        /* (nrow,3) C order, metres                              */
+  int64_t nrow;
+  const double* freq;       /* (nchan,) Hz                                           */
+  int64_t nchan;
+  const void* vis;          /* (nrow,nchan) complex64                                */
+  const float* wgt;         /* (nrow,nchan) float32 or NULL (= all ones)             */
+  const uint8_t* mask;      /* (nrow,nchan) or NULL; 0 = skip sample                 */
+  int64_t vis_row_stride;   /* elements between rows of vis (>= nchan; 0 = nchan)    */
+  int64_t wgt_row_stride;   /* same for wgt and mask                                 */
+  int npix_x, npix_y;       /* even, >= 16                                           */
+  double pixsize_x, pixsize_y; /* radians (direction cosines per pixel)              */
+  double epsilon;
+  int do_wstacking;         /* 1 = improved w-stacking, 0 = ignore w                 */
+  int accumulate_fp64;      /* 0: complex64 grids; 1: complex128 grids + tighter kernel */
+  int memspace;             /* 0: all pointers are host memory; 1: device memory of the ctx device */
+} cip_invert_args;
+
+typedef struct {
+  double wmin, wmax;        /* range of |w| in wavelengths over active samples       */
+  int64_t nactive;          /* samples with wgt*mask != 0 and vis != 0               */
+  double sum_wgt;           /* sum of wgt*mask over ALL samples (invert.py:184)      */
+} cip_scan_result;
+
+typedef struct {
+  int npix_x, npix_y;
+  double pixsize_x, pixsize_y;
+  double sigma;             /* oversampling actually used                            */
+  int support;              /* kernel support W in cells                             */
+  double beta;              /* phi(x) = exp(beta*W*(sqrt(1-x^2)-1))                   */
+  int nu, nv;               /* oversampled grid                                      */
+  double nshift;            /* n-1 shift s                                           */
+  double dw, w0;            /* plane p sits at w0 + p*dw                              */
+  int nplanes;
+  int accumulate_fp64;
+  int do_wstacking;
+  int plane_block;          /* planes resident at once (filled by the library)       */
+} cip_plan;
+
+typedef struct {
+  double ms_total, ms_h2d, ms_scan, ms_bin, ms_grid, ms_fft, ms_wscreen, ms_correct, ms_d2h;
+  int64_t launches;         /* kernels of this library launched by the call          */
+  int64_t nactive;
+  int nblocks;              /* plane blocks processed                                */
+} cip_report;
+
+/* Host-only planning: choose (sigma, W) and the w-plane layout.  No GPU needed.
+ * sigma_override/support_override: 0 = automatic. */
+cip_status cip_plan_make(int npix_x, int npix_y, double pixsize_x, double pixsize_y, double epsilon,
+                         int do_wstacking, int accumulate_fp64, double wmin, double wmax, int64_t nactive,
+                         double sigma_override, int support_override, cip_plan* out);
+
+/* Kernel design table of the library: rms aliasing error and beta for (sigma, W). */
+cip_status cip_kernel_table(double sigma, int support, double* beta, double* rms_err);
+
+/* Gridding-kernel Fourier transform c(xi) used by the correction (host, float64). */
+cip_status cip_kernel_ft(const cip_plan* plan, const double* xi, int64_t n, double* out);
+
+/* G1 scan: w-range, active count and weight sum of one shard. */
+cip_status cip_scan(cip_ctx* ctx, const cip_invert_args* args, cip_scan_result* out);
+
+/* G1 binning + G2 gridding + G3 FFT + G4 w-screen: ADD the uncorrected dirty image of the
+ * samples in args to `image` (device memory, (npix_x,npix_y) float32, or float64 when
+ * plan->accumulate_fp64).  Linear in the samples, so shards may be reduced before
+ * cip_correct_image. */
+cip_status cip_grid_accumulate(cip_ctx* ctx, const cip_invert_args* args, cip_plan* plan, void* image_dev,
+                               cip_report* report /* may be NULL */);
+
+/* G4 final + P4: image[r,:] *= scale / (c_u c_v c_w n) for rows row_begin..row_end-1.
+ * `image_dev` points at row 0 of the full image. */
+cip_status cip_correct_image(cip_ctx* ctx, const cip_plan* plan, void* image_dev, int row_begin, int row_end,
+                             double scale);
+
+/* The whole of ms2dirty on one GPU.  dirty_out: (npix_x,npix_y) float32 (float64 when
+ * accumulate_fp64) in the memory space of args->memspace.  scan_out, plan_out, report may be NULL. */
+cip_status cip_invert(cip_ctx* ctx, const cip_invert_args* args, void* dirty_out, cip_scan_result* scan_out,
+                      cip_plan* plan_out, cip_report* report);
+
+/* ---- P1/P2: Stokes-I prologue (invert.py:72-116) -------------------------------- */
+/* vis4 (nrow,nchan,4) complex64, flags4 (nrow,nchan,4) uint8/bool, wgt4 (nrow,nchan,4) float32
+ * -> vis_I = 0.5 (v0+v3), eff_w = (!(f0|f3)) * 4/(1/w0+1/w3).  memspace as above. */
+cip_status cip_stokes_i(cip_ctx* ctx, const void* vis4, const uint8_t* flags4, const float* wgt4,
+                        int64_t nrow, int64_t nchan, void* vis_out, float* effw_out, int memspace);
+
+/* ---- T1-T3: uvw tile binning (tiling_plan.py:29-181), bit-exact ------------------ */
+typedef struct cip_tile_result cip_tile_result; /* device-resident result of one binning */
+
+/* idx = (int64) floor((freq/c) * (uvw/tile_size) + 0.5), run-length compressed per row,
+ * grouped by tile in first-appearance order, slices ascending (irow, chan_start). */
+cip_status cip_tile_bin(cip_ctx* ctx, const double* uvw, int64_t nrow, const double* freq, int64_t nchan,
+                        const double tile_size[3], int64_t row_offset, int memspace,
+                        cip_tile_result** result, int64_t* n_tiles, int64_t* n_slices);
+/* Copy the result out (host buffers; any pointer may be NULL). */
+cip_status cip_tile_fetch(cip_ctx* ctx, const cip_tile_result* result,
+                          int64_t* tile_coords /* (n_tiles,3) */, int64_t* tile_offsets /* (n_tiles+1,) */,
+                          int64_t* slice_irow, int32_t* slice_ch_start, int32_t* slice_ch_stop /* (n_slices,) */);
+/* T5 gather (tile.py:83-115): visibilities (nrow,nchan) complex64 reordered tile-contiguous.
+ * vis_out (nvis_total,) complex64, vis_offsets (n_slices+1,) int64, uvw_out (n_slices,3) float64. */
+cip_status cip_tile_gather(cip_ctx* ctx, const cip_tile_result* result, const void* vis, const double* uvw,
+                           int64_t nrow, int64_t nchan, int memspace, void* vis_out, int64_t* vis_offsets,
+                           double* uvw_out);
+cip_status cip_tile_free(cip_ctx* ctx, cip_tile_result* result);
+
+#ifdef __cplusplus
+}
+#endif
+#endif /* CIP_H */

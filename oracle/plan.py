@@ -34,8 +34,10 @@ ES_TABLE = {
 }
 
 # cost-model constants (seconds per unit); see DESIGN.md "planning"
-COST_CELL_UPDATE = 6.0e-13   # one complex cell update of one visibility on one plane
-COST_GRID_CELL = 1.2e-11     # zero + FFT + w-screen of one complex grid cell of one plane
+COST_VIS_FAST = 6.0e-11      # one visibility through the residue-owner gridder (W <= 8)
+COST_CELL_UPDATE = 2.0e-12   # one complex cell update in the wide-support gridder (W > 8)
+COST_GRID_CELL = 1.0e-11     # zero + FFT + w-screen of one complex grid cell of one plane
+FAST_SUPPORT = 8
 
 
 @dataclass
@@ -88,6 +90,8 @@ def make_plan(nx, ny, px, py, epsilon, wmin_d, wmax_d, nvis, *, fp64=False, do_w
     scale = 2.0 if fp64 else 1.0
     best = None
     for sg in (sigma,) if sigma else (1.25, 1.5, 1.75, 2.0):
+        if not sigma and not fp64 and sg < 1.4:
+            continue  # fp32 grids: keep the 1/c(xi) edge gain modest
         tab = ES_TABLE[sg]
         if W:
             w = W
@@ -104,7 +108,8 @@ def make_plan(nx, ny, px, py, epsilon, wmin_d, wmax_d, nvis, *, fp64=False, do_w
             dw = 1.0 / (2.0 * sg * half)
             npl = int(math.floor((wmax_d - wmin_d) / dw + w))
         wfac = w if do_wstacking else 1
-        cost = scale * (nvis * w * w * wfac * COST_CELL_UPDATE + npl * nu * nv * COST_GRID_CELL)
+        per_vis = COST_VIS_FAST if w <= FAST_SUPPORT else w * w * wfac * COST_CELL_UPDATE
+        cost = scale * (nvis * per_vis + npl * nu * nv * COST_GRID_CELL)
         if best is None or cost < best[0]:
             best = (cost, sg, w, nu, nv, dw, npl)
     if best is None:

@@ -1,0 +1,333 @@
+// Kernel 1 (gridder side): binning of (row, channel) visibilities into uv tiles and w-plane
+// windows -- stage G1 of SURVEY.md section 8a, the work ducc0.wgridder.ms2dirty does internally
+// before gridding (reference call site src/ska_sdp_cip/invert.py:170-183).
+//
+// Per row the channels are run-length encoded by their (window, tile_u, tile_v) key (one warp per
+// row, ballot on "key differs from the previous channel"); the runs are ordered by key with a
+// stable LSD radix sort, so inside a bin they stay in (row, channel) order and the accumulation
+// order of the gridder is reproducible; the sorted runs are then expanded into 24-byte
+// gridder-ready records (all float64 coordinate arithmetic happens here, once) and cut into work
+// items of at most kItemVis records.
+#include <algorithm>
+
+#include <cub/device/device_radix_sort.cuh>
+#include <cub/device/device_scan.cuh>
+
+#include "geom.cuh"
+
+namespace cip {
+
+namespace {
+
+struct MaxOp {
+  __device__ __forceinline__ int64_t operator()(int64_t a, int64_t b) const { return a > b ? a : b; }
+};
+
+// pass 0: count runs per row; pass 1: write them at row_off[row].
+template <int PASS>
+__global__ void __launch_bounds__(256) runs_kernel(DevInputs in, GridGeom g, int64_t* __restrict__ row_nruns,
+                                                   const int64_t* __restrict__ row_off, Run* __restrict__ runs,
+                                                   uint64_t* __restrict__ keys) {
+  const int lane = threadIdx.x & 31;
+  const int64_t row = ((int64_t)blockIdx.x * blockDim.x + threadIdx.x) >> 5;
+  if (row >= in.nrow) return;
+  const double um = in.uvw[3 * row], vm = in.uvw[3 * row + 1], wm = in.uvw[3 * row + 2];
+  uint64_t carry = ~0ull;
+  int64_t n = 0;
+  const int64_t base = PASS ? row_off[row] : 0;
+  for (int64_t c0 = 0; c0 < in.nchan; c0 += 32) {
+    int64_t c = c0 + lane;
+    uint64_t key = ~0ull;
+    if (c < in.nchan) {
+      SampleGeom s = sample_geom(g, um, vm, wm, in.freq[c] / kSpeedOfLight);
+      key = bin_key(g, s);
+    }
+    uint64_t prev = __shfl_up_sync(0xffffffffu, key, 1);
+    if (lane == 0) prev = carry;
+    bool start = c < in.nchan && key != prev;
+    unsigned m = __ballot_sync(0xffffffffu, start);
+    if (PASS && start) {
+      int64_t pos = base + n + __popc(m & ((1u << lane) - 1));
+      Run r;
+      r.key = key;
+      r.row = (int32_t)row;
+      r.ch0 = (int32_t)c;
+      runs[pos] = r;
+      keys[pos] = key;
+    }
+    n += __popc(m);
+    carry = __shfl_sync(0xffffffffu, key, 31);
+  }
+  if (!PASS && lane == 0) row_nruns[row] = n;
+}
+
+__global__ void run_len_kernel(const Run* __restrict__ runs, int64_t nruns, int32_t nchan, uint32_t* __restrict__ idx,
+                               int32_t* __restrict__ len) {
+  int64_t r = (int64_t)blockIdx.x * blockDim.x + threadIdx.x;
+  if (r >= nruns) return;
+  Run a = runs[r];
+  int32_t stop = nchan;
+  if (r + 1 < nruns) {
+    Run b = runs[r + 1];
+    if (b.row == a.row) stop = b.ch0;
+  }
+  len[r] = stop - a.ch0;
+  idx[r] = (uint32_t)r;
+}
+
+// sorted order: gather run + length, flag bin starts
+__global__ void gather_kernel(const Run* __restrict__ runs, const int32_t* __restrict__ len,
+                              const uint32_t* __restrict__ idx, const uint64_t* __restrict__ keys_sorted, int64_t nruns,
+                              Run* __restrict__ runs_sorted, int64_t* __restrict__ len_sorted,
+                              int64_t* __restrict__ start_flag) {
+  int64_t i = (int64_t)blockIdx.x * blockDim.x + threadIdx.x;
+  if (i >= nruns) return;
+  uint32_t r = idx[i];
+  runs_sorted[i] = runs[r];
+  len_sorted[i] = len[r];
+  start_flag[i] = (i == 0 || keys_sorted[i] != keys_sorted[i - 1]) ? 1 : 0;
+}
+
+// group g = g-th distinct key; first run of each group, number of items of each group
+__global__ void groups_kernel(const int64_t* __restrict__ start_flag, const int64_t* __restrict__ group_of /*inclusive scan*/,
+                              const int64_t* __restrict__ visoff, int64_t nruns, int64_t nrec,
+                              int64_t* __restrict__ group_first) {
+  int64_t i = (int64_t)blockIdx.x * blockDim.x + threadIdx.x;
+  if (i >= nruns) return;
+  if (start_flag[i]) group_first[group_of[i] - 1] = i;
+}
+
+__global__ void group_items_kernel(const int64_t* __restrict__ group_first, const int64_t* __restrict__ visoff,
+                                   int64_t ngroups, int64_t nruns, int64_t nrec, int64_t* __restrict__ group_nitems) {
+  int64_t gidx = (int64_t)blockIdx.x * blockDim.x + threadIdx.x;
+  if (gidx > ngroups) return;
+  if (gidx == ngroups) { group_nitems[gidx] = 0; return; }
+  int64_t b = visoff[group_first[gidx]];
+  int64_t e = gidx + 1 < ngroups ? visoff[group_first[gidx + 1]] : nrec;
+  group_nitems[gidx] = (e - b + kItemVis - 1) / kItemVis;
+}
+
+__global__ void items_kernel(const int64_t* __restrict__ group_first, const int64_t* __restrict__ group_item_off,
+                             const int64_t* __restrict__ visoff, const Run* __restrict__ runs_sorted, int64_t ngroups,
+                             int64_t nrec, GridGeom g, Item* __restrict__ items, int64_t* __restrict__ win_item_start) {
+  int64_t gidx = (int64_t)blockIdx.x * blockDim.x + threadIdx.x;
+  if (gidx >= ngroups) return;
+  int64_t fr = group_first[gidx];
+  int64_t b = visoff[fr];
+  int64_t e = gidx + 1 < ngroups ? visoff[group_first[gidx + 1]] : nrec;
+  uint64_t key = runs_sorted[fr].key;
+  int tv = (int)(key % g.ntv);
+  uint64_t q = key / g.ntv;
+  int tu = (int)(q % g.ntu);
+  int win = (int)(q / g.ntu);
+  int64_t it = group_item_off[gidx];
+  atomicMin((unsigned long long*)&win_item_start[win], (unsigned long long)it);
+  for (int64_t r = b; r < e; r += kItemVis, ++it) {
+    Item item;
+    item.rec_begin = r;
+    item.nrec = (int32_t)std::min<int64_t>(kItemVis, e - r);
+    item.tu = tu;
+    item.tv = tv;
+    item.win = win;
+    item.pad[0] = item.pad[1] = 0;
+    items[it] = item;
+  }
+}
+
+__global__ void fill_i64_kernel(int64_t* p, int64_t n, int64_t v) {
+  int64_t i = (int64_t)blockIdx.x * blockDim.x + threadIdx.x;
+  if (i < n) p[i] = v;
+}
+
+// One warp per sorted run: expand into gridder-ready records.
+template <typename REC>
+__global__ void __launch_bounds__(256) records_kernel(DevInputs in, GridGeom g, const Run* __restrict__ runs_sorted,
+                                                      const int64_t* __restrict__ len_sorted,
+                                                      const int64_t* __restrict__ visoff, int64_t nruns,
+                                                      REC* __restrict__ recs) {
+  const int lane = threadIdx.x & 31;
+  const int64_t i = ((int64_t)blockIdx.x * blockDim.x + threadIdx.x) >> 5;
+  if (i >= nruns) return;
+  const Run run = runs_sorted[i];
+  const int len = (int)len_sorted[i];
+  const int64_t out0 = visoff[i];
+  const int64_t row = run.row;
+  const double um = in.uvw[3 * row], vm = in.uvw[3 * row + 1], wm = in.uvw[3 * row + 2];
+  const int tv = (int)(run.key % g.ntv);
+  const uint64_t q = run.key / g.ntv;
+  const int tu = (int)(q % g.ntu);
+  const int win = (int)(q / g.ntu);
+  for (int k = lane; k < len; k += 32) {
+    int64_t c = run.ch0 + k;
+    SampleGeom s = sample_geom(g, um, vm, wm, in.freq[c] / kSpeedOfLight);
+    float2 v = in.vis[row * in.vstride + c];
+    float wgt;
+    bool act = sample_active(v, in.wgt, in.mask, row * in.wstride + c, &wgt);
+    double re = 0.0, im = 0.0;
+    if (act) {
+      re = (double)v.x * wgt;
+      im = (double)v.y * wgt;
+      if (s.flip) im = -im;
+      if (g.do_wstacking && g.nshift != 0.0) {  // V' = V exp(+2 pi i w s)
+        double ph = s.w * g.nshift;
+        ph -= rint(ph);
+        double sn, cs;
+        sincospi(2.0 * ph, &sn, &cs);
+        double t = re * cs - im * sn;
+        im = re * sn + im * cs;
+        re = t;
+      }
+    }
+    REC r;
+    uint32_t i0r = (uint32_t)(s.i0 + kHalo - tu * kTile);
+    uint32_t j0r = (uint32_t)(s.j0 + kHalo - tv * kTile);
+    uint32_t p0r = (uint32_t)(s.p0 - win * g.win_step);
+    r.cell = i0r | (j0r << 5) | (p0r << 10);
+    r.fu = s.fu;
+    r.fv = s.fv;
+    r.fw = s.fw;
+    r.re = re;
+    r.im = im;
+    recs[out0 + k] = r;
+  }
+}
+
+template <typename T>
+cip_status d2h_scalar(cip_ctx* ctx, const T* dev, T* out) {
+  CIP_CHECK_CUDA(cudaMemcpyAsync(ctx->scan_host, dev, sizeof(T), cudaMemcpyDeviceToHost, ctx->stream));
+  CIP_CHECK_CUDA(cudaStreamSynchronize(ctx->stream));
+  *out = *static_cast<T*>(ctx->scan_host);
+  return CIP_OK;
+}
+
+inline int nblk(int64_t n, int per) { return (int)((n + per - 1) / per); }
+
+}  // namespace
+
+cip_status run_binning(cip_ctx* ctx, const DevInputs& in, const GridGeom& g, int fp64, BinResult* out) {
+  cudaStream_t st = ctx->stream;
+  const int64_t nrow = in.nrow, nchan = in.nchan;
+  out->nruns = out->nrec = out->nitems = 0;
+  out->win_item_start.assign(g.nwin + 1, 0);
+  if (nrow == 0 || nchan == 0) return CIP_OK;
+  const int64_t nrec = nrow * nchan;
+
+  // --- runs per row, offsets -------------------------------------------------------
+  CIP_TRY(ctx->row_nruns.ensure(sizeof(int64_t) * (nrow + 1)));
+  CIP_TRY(ctx->row_off.ensure(sizeof(int64_t) * (nrow + 1)));
+  int64_t* row_nruns = ctx->row_nruns.as<int64_t>();
+  int64_t* row_off = ctx->row_off.as<int64_t>();
+  CIP_CHECK_CUDA(cudaMemsetAsync(row_nruns + nrow, 0, sizeof(int64_t), st));
+  const int rblocks = nblk(nrow * 32, 256);
+  runs_kernel<0><<<rblocks, 256, 0, st>>>(in, g, row_nruns, nullptr, nullptr, nullptr);
+  ctx->launches++;
+  size_t tmp_bytes = 0;
+  CIP_CHECK_CUDA(cub::DeviceScan::ExclusiveSum(nullptr, tmp_bytes, row_nruns, row_off, nrow + 1, st));
+  CIP_TRY(ctx->cub_tmp.ensure(tmp_bytes));
+  tmp_bytes = ctx->cub_tmp.cap;
+  CIP_CHECK_CUDA(cub::DeviceScan::ExclusiveSum(ctx->cub_tmp.p, tmp_bytes, row_nruns, row_off, nrow + 1, st));
+  ctx->launches++;
+  int64_t nruns = 0;
+  CIP_TRY(d2h_scalar(ctx, row_off + nrow, &nruns));
+  CIP_REQUIRE(nruns > 0 && nruns < ((int64_t)1 << 32), "unexpected number of runs %lld", (long long)nruns);
+
+  // --- write runs, lengths ---------------------------------------------------------
+  CIP_TRY(ctx->runs.ensure(sizeof(Run) * nruns));
+  CIP_TRY(ctx->run_keys.ensure(sizeof(uint64_t) * nruns));
+  CIP_TRY(ctx->run_keys_alt.ensure(sizeof(uint64_t) * nruns));
+  CIP_TRY(ctx->run_idx.ensure(sizeof(uint32_t) * nruns));
+  CIP_TRY(ctx->run_idx_alt.ensure(sizeof(uint32_t) * nruns));
+  CIP_TRY(ctx->run_len.ensure(sizeof(int32_t) * nruns));
+  Run* runs = ctx->runs.as<Run>();
+  runs_kernel<1><<<rblocks, 256, 0, st>>>(in, g, nullptr, row_off, runs, ctx->run_keys.as<uint64_t>());
+  run_len_kernel<<<nblk(nruns, 256), 256, 0, st>>>(runs, nruns, (int32_t)nchan, ctx->run_idx.as<uint32_t>(),
+                                                   ctx->run_len.as<int32_t>());
+  ctx->launches += 2;
+
+  // --- stable sort of the runs by key ----------------------------------------------
+  uint64_t nkeys = (uint64_t)g.nwin * g.ntu * g.ntv;
+  int bits = 1;
+  while (bits < 64 && (nkeys >> bits)) ++bits;
+  CIP_CHECK_CUDA(cub::DeviceRadixSort::SortPairs(nullptr, tmp_bytes, ctx->run_keys.as<uint64_t>(),
+                                                 ctx->run_keys_alt.as<uint64_t>(), ctx->run_idx.as<uint32_t>(),
+                                                 ctx->run_idx_alt.as<uint32_t>(), nruns, 0, bits, st));
+  CIP_TRY(ctx->cub_tmp.ensure(tmp_bytes));
+  tmp_bytes = ctx->cub_tmp.cap;
+  CIP_CHECK_CUDA(cub::DeviceRadixSort::SortPairs(ctx->cub_tmp.p, tmp_bytes, ctx->run_keys.as<uint64_t>(),
+                                                 ctx->run_keys_alt.as<uint64_t>(), ctx->run_idx.as<uint32_t>(),
+                                                 ctx->run_idx_alt.as<uint32_t>(), nruns, 0, bits, st));
+  ctx->launches += 2 + (bits + 7) / 8;
+
+  // --- sorted runs, record offsets, bins -------------------------------------------
+  CIP_TRY(ctx->runs_sorted.ensure(sizeof(Run) * nruns));
+  CIP_TRY(ctx->run_visoff.ensure(sizeof(int64_t) * (nruns + 1) * 2));  // lengths + offsets
+  CIP_TRY(ctx->flags.ensure(sizeof(int64_t) * nruns * 2));              // start flags + group index
+  Run* runs_sorted = ctx->runs_sorted.as<Run>();
+  int64_t* len_sorted = ctx->run_visoff.as<int64_t>();
+  int64_t* visoff = len_sorted + (nruns + 1);
+  int64_t* start_flag = ctx->flags.as<int64_t>();
+  int64_t* group_of = start_flag + nruns;
+  gather_kernel<<<nblk(nruns, 256), 256, 0, st>>>(runs, ctx->run_len.as<int32_t>(), ctx->run_idx_alt.as<uint32_t>(),
+                                                  ctx->run_keys_alt.as<uint64_t>(), nruns, runs_sorted, len_sorted,
+                                                  start_flag);
+  ctx->launches++;
+  CIP_CHECK_CUDA(cub::DeviceScan::ExclusiveSum(nullptr, tmp_bytes, len_sorted, visoff, nruns, st));
+  CIP_TRY(ctx->cub_tmp.ensure(tmp_bytes));
+  tmp_bytes = ctx->cub_tmp.cap;
+  CIP_CHECK_CUDA(cub::DeviceScan::ExclusiveSum(ctx->cub_tmp.p, tmp_bytes, len_sorted, visoff, nruns, st));
+  CIP_CHECK_CUDA(cub::DeviceScan::InclusiveSum(nullptr, tmp_bytes, start_flag, group_of, nruns, st));
+  CIP_TRY(ctx->cub_tmp.ensure(tmp_bytes));
+  tmp_bytes = ctx->cub_tmp.cap;
+  CIP_CHECK_CUDA(cub::DeviceScan::InclusiveSum(ctx->cub_tmp.p, tmp_bytes, start_flag, group_of, nruns, st));
+  ctx->launches += 2;
+  int64_t ngroups = 0;
+  CIP_TRY(d2h_scalar(ctx, group_of + nruns - 1, &ngroups));
+
+  CIP_TRY(ctx->group_start.ensure(sizeof(int64_t) * (ngroups + 1) * 3));
+  int64_t* group_first = ctx->group_start.as<int64_t>();
+  int64_t* group_nitems = group_first + (ngroups + 1);
+  int64_t* group_item_off = group_nitems + (ngroups + 1);
+  groups_kernel<<<nblk(nruns, 256), 256, 0, st>>>(start_flag, group_of, visoff, nruns, nrec, group_first);
+  group_items_kernel<<<nblk(ngroups + 1, 256), 256, 0, st>>>(group_first, visoff, ngroups, nruns, nrec, group_nitems);
+  ctx->launches += 2;
+  CIP_CHECK_CUDA(cub::DeviceScan::ExclusiveSum(nullptr, tmp_bytes, group_nitems, group_item_off, ngroups + 1, st));
+  CIP_TRY(ctx->cub_tmp.ensure(tmp_bytes));
+  tmp_bytes = ctx->cub_tmp.cap;
+  CIP_CHECK_CUDA(cub::DeviceScan::ExclusiveSum(ctx->cub_tmp.p, tmp_bytes, group_nitems, group_item_off, ngroups + 1, st));
+  ctx->launches++;
+  int64_t nitems = 0;
+  CIP_TRY(d2h_scalar(ctx, group_item_off + ngroups, &nitems));
+
+  CIP_TRY(ctx->items.ensure(sizeof(Item) * std::max<int64_t>(nitems, 1)));
+  CIP_TRY(ctx->win_item_start.ensure(sizeof(int64_t) * (g.nwin + 1)));
+  int64_t* wis = ctx->win_item_start.as<int64_t>();
+  fill_i64_kernel<<<nblk(g.nwin + 1, 256), 256, 0, st>>>(wis, g.nwin + 1, nitems);
+  items_kernel<<<nblk(ngroups, 256), 256, 0, st>>>(group_first, group_item_off, visoff, runs_sorted, ngroups, nrec, g,
+                                                   ctx->items.as<Item>(), wis);
+  ctx->launches += 2;
+
+  // --- records ---------------------------------------------------------------------
+  const size_t rec_size = fp64 ? sizeof(VisRec64) : sizeof(VisRec);
+  CIP_TRY(ctx->recs.ensure(rec_size * nrec));
+  if (fp64)
+    records_kernel<VisRec64><<<nblk(nruns * 32, 256), 256, 0, st>>>(in, g, runs_sorted, len_sorted, visoff, nruns,
+                                                                   ctx->recs.as<VisRec64>());
+  else
+    records_kernel<VisRec><<<nblk(nruns * 32, 256), 256, 0, st>>>(in, g, runs_sorted, len_sorted, visoff, nruns,
+                                                                 ctx->recs.as<VisRec>());
+  ctx->launches++;
+  CIP_CHECK_CUDA(cudaGetLastError());
+
+  std::vector<int64_t> h(g.nwin + 1);
+  CIP_CHECK_CUDA(cudaMemcpyAsync(h.data(), wis, sizeof(int64_t) * (g.nwin + 1), cudaMemcpyDeviceToHost, st));
+  CIP_CHECK_CUDA(cudaStreamSynchronize(st));
+  h[g.nwin] = nitems;
+  for (int w = g.nwin - 1; w >= 0; --w) h[w] = std::min(h[w], h[w + 1]);  // empty windows start where the next does
+  out->win_item_start = h;
+  out->nruns = nruns;
+  out->nrec = nrec;
+  out->nitems = nitems;
+  return CIP_OK;
+}
+
+}  // namespace cip

@@ -1,0 +1,192 @@
+// Internal declarations shared by the translation units of libcip_b200.so.
+#pragma once
+
+#include <cstdarg>
+#include <cstdint>
+#include <cstdio>
+#include <map>
+#include <string>
+#include <tuple>
+#include <vector>
+
+#include <cuda_runtime.h>
+#include <cufft.h>
+
+#include "cip.h"
+
+namespace cip {
+
+constexpr double kSpeedOfLight = 299792458.0;
+constexpr int kMaxSupport = 16;   // widest kernel in the design table
+constexpr int kFastSupport = 8;   // widest kernel of the residue-owner gridder (= residue modulus)
+constexpr int kMinSupport = 4;
+constexpr int kTile = 16;         // uv tile edge of the gridder, in grid cells
+constexpr int kHalo = 8;          // shift that keeps window origins non-negative (>= kMaxSupport/2)
+constexpr int kSub = kTile + kFastSupport - 1;  // sub-grid edge held in shared memory (23, odd on purpose)
+constexpr int kWin = 8;           // w planes of one gridding window (= planes per consumer thread)
+constexpr int kBatch = 32;        // visibilities per producer/consumer hand-over
+constexpr int kItemVis = 4096;    // visibilities per gridding work item (one CTA)
+
+void set_error(const char* fmt, ...);
+
+#define CIP_CHECK_CUDA(expr)                                                                       \
+  do {                                                                                             \
+    cudaError_t _e = (expr);                                                                       \
+    if (_e != cudaSuccess) {                                                                       \
+      ::cip::set_error("%s failed: %s (%s:%d)", #expr, cudaGetErrorString(_e), __FILE__, __LINE__); \
+      return _e == cudaErrorMemoryAllocation ? CIP_ENOMEM : CIP_ECUDA;                             \
+    }                                                                                              \
+  } while (0)
+
+#define CIP_CHECK_CUFFT(expr)                                                              \
+  do {                                                                                     \
+    cufftResult _r = (expr);                                                               \
+    if (_r != CUFFT_SUCCESS) {                                                             \
+      ::cip::set_error("%s failed: cufft error %d (%s:%d)", #expr, (int)_r, __FILE__, __LINE__); \
+      return _r == CUFFT_ALLOC_FAILED ? CIP_ENOMEM : CIP_ECUFFT;                           \
+    }                                                                                      \
+  } while (0)
+
+#define CIP_TRY(expr)                  \
+  do {                                 \
+    cip_status _s = (expr);            \
+    if (_s != CIP_OK) return _s;       \
+  } while (0)
+
+#define CIP_REQUIRE(cond, ...)         \
+  do {                                 \
+    if (!(cond)) {                     \
+      ::cip::set_error(__VA_ARGS__);   \
+      return CIP_EINVAL;               \
+    }                                  \
+  } while (0)
+
+// Grow-only device buffer owned by the context.
+struct DevBuf {
+  void* p = nullptr;
+  size_t cap = 0;
+  cip_status ensure(size_t bytes);
+  void release();
+  template <typename T> T* as() const { return static_cast<T*>(p); }
+};
+
+struct FftPlan {
+  cufftHandle handle = 0;
+  size_t work = 0;
+};
+
+// One visibility, ready for the gridder: written by the record kernel in (window, tile) order.
+// 24 bytes; `cell` packs the tile-relative origin of the support and flags:
+//   bits 0-4 i0 (u cell, 0..kTile-1), 5-9 j0, 10-13 first plane relative to the window start.
+struct __align__(8) VisRec {
+  uint32_t cell;
+  float fu, fv, fw;  // distance of the first cell / plane from the left edge of the support, in [0,1)
+  float re, im;      // weighted, conjugated-if-flipped, n-shift-rotated visibility
+};
+
+struct __align__(16) VisRec64 {  // accumulate_fp64 variant (32 bytes)
+  uint32_t cell;
+  float fu, fv, fw;
+  double re, im;
+};
+
+// A run of channels of one row that fall into the same (window, tile) bin.
+struct __align__(16) Run {
+  uint64_t key;   // (window * ntu + tu) * ntv + tv
+  int32_t row;
+  int32_t ch0;
+};
+
+// One gridding work item = one CTA: a slice of the sorted records of one (window, tile) bin.
+struct __align__(16) Item {
+  int64_t rec_begin;
+  int32_t nrec;
+  int32_t tu, tv;  // tile coordinates
+  int32_t win;     // window index: planes [win*win_step, win*win_step + kWin)
+  int32_t pad[2];
+};
+
+// Geometry shared by the scan / binning / record / gridding kernels.
+struct GridGeom {
+  double px, py;          // pixel sizes (direction cosines)
+  double w0, inv_dw;      // plane p sits at w0 + p*dw
+  double nshift;          // n-1 shift s
+  int nu, nv;             // oversampled grid
+  int W;                  // kernel support
+  int nplanes;
+  int win_step;           // first-plane stride between windows = kWin - W + 1
+  int nwin;               // number of windows
+  int ntu, ntv;           // tiles per axis
+  int do_wstacking;
+  float beta_w;           // beta * W
+};
+
+}  // namespace cip
+
+struct cip_ctx {
+  int device = 0;
+  int sm_count = 148;
+  size_t smem_optin = 0;
+  cudaStream_t stream = nullptr;
+  cudaEvent_t ev[16] = {};
+  int64_t launches = 0;
+  // inputs staged on the device when the caller passes host memory
+  cip::DevBuf in_uvw, in_freq, in_vis, in_wgt, in_mask;
+  cip::DevBuf out_img;
+  // scan
+  cip::DevBuf scan_out;
+  void* scan_host = nullptr;  // pinned
+  // binning
+  cip::DevBuf row_nruns, row_off, runs, run_keys, run_keys_alt, run_idx, run_idx_alt, runs_sorted, run_len,
+      run_visoff, flags, group_start, item_idx, items, win_item_start, cub_tmp, recs;
+  // grids, fft, image
+  cip::DevBuf grid, image, tables;
+  std::map<std::tuple<int, int, int, int>, cip::FftPlan> fft_plans;  // (nu, nv, batch, fp64)
+  // tiling
+  cip::DevBuf t_uvw, t_freq, t_vis;
+};
+
+namespace cip {
+
+// ---- planning (plan.cpp) ----------------------------------------------------------
+int good_size(int n);
+struct KernelEntry { double beta, err; };
+bool kernel_lookup(double sigma, int W, KernelEntry* out);
+void gauss_legendre(int n, std::vector<double>& x, std::vector<double>& w);
+// c(xi) = int_{-W/2}^{W/2} phi(2t/W) cos(2 pi t xi) dt
+double kernel_ft_one(double xi, int W, double beta, const std::vector<double>& glx, const std::vector<double>& glw);
+int correction_quadrature_size(int W);
+GridGeom make_geom(const cip_plan& p);
+
+// ---- staged inputs (ctx.cu) -------------------------------------------------------
+struct DevInputs {
+  const double* uvw;
+  const double* freq;
+  const float2* vis;
+  const float* wgt;
+  const uint8_t* mask;
+  int64_t nrow, nchan, vstride, wstride;
+};
+cip_status validate_args(const cip_invert_args* a);
+cip_status stage_inputs(cip_ctx* ctx, const cip_invert_args* a, DevInputs* d, double* ms_h2d);
+float elapsed_ms(cip_ctx* ctx, int e0, int e1);
+
+// ---- stages -----------------------------------------------------------------------
+cip_status run_scan(cip_ctx* ctx, const DevInputs& in, int do_wstacking, cip_scan_result* out);
+
+struct BinResult {
+  int64_t nruns = 0;
+  int64_t nrec = 0;
+  int64_t nitems = 0;
+  std::vector<int64_t> win_item_start;  // (nwin+1,) first item of each window
+};
+cip_status run_binning(cip_ctx* ctx, const DevInputs& in, const GridGeom& g, int fp64, BinResult* out);
+
+// Grid the items [item_begin, item_end) into `grid` (planes slot = plane - plane_base).
+cip_status run_gridder(cip_ctx* ctx, const GridGeom& g, int fp64, int64_t item_begin, int64_t item_end,
+                       void* grid, int plane_base, int nslots);
+cip_status run_fft(cip_ctx* ctx, void* grid, int nu, int nv, int batch, int fp64);
+cip_status run_wscreen(cip_ctx* ctx, const cip_plan& p, const void* grid, int plane_base, int nslots, void* image);
+cip_status run_correct(cip_ctx* ctx, const cip_plan& p, void* image, int row_begin, int row_end, double scale);
+
+}  // namespace cip

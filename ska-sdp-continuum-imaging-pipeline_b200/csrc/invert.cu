@@ -1,0 +1,193 @@
+// The ms2dirty replacement: scan -> plan -> binning -> per block of w planes { grid, FFT,
+// w-screen } -> correction.  Replaces the single native call of the reference,
+// ducc0.wgridder.ms2dirty at src/ska_sdp_cip/invert.py:170-183, and the weight sum of :184.
+#include <algorithm>
+#include <cstdlib>
+#include <cstring>
+
+#include "common.h"
+
+using namespace cip;
+
+namespace {
+
+struct StageTimer {
+  cip_ctx* ctx;
+  bool on;
+  StageTimer(cip_ctx* c, bool enabled) : ctx(c), on(enabled) {}
+  void start() { if (on) cudaEventRecord(ctx->ev[0], ctx->stream); }
+  void stop(double* acc) {
+    if (!on) return;
+    cudaEventRecord(ctx->ev[1], ctx->stream);
+    cudaEventSynchronize(ctx->ev[1]);
+    *acc += elapsed_ms(ctx, 0, 1);
+  }
+};
+
+cip_status fft_prepare(cip_ctx* ctx, int nu, int nv, int fp64) {
+  return run_fft(ctx, nullptr, nu, nv, 0, fp64);  // batch 0: only creates and caches the plan
+}
+
+}  // namespace
+
+extern "C" cip_status cip_scan(cip_ctx* ctx, const cip_invert_args* args, cip_scan_result* out) {
+  CIP_REQUIRE(ctx && out, "NULL argument");
+  CIP_TRY(validate_args(args));
+  CIP_CHECK_CUDA(cudaSetDevice(ctx->device));
+  DevInputs in;
+  CIP_TRY(stage_inputs(ctx, args, &in, nullptr));
+  return run_scan(ctx, in, args->do_wstacking, out);
+}
+
+static cip_status grid_accumulate_staged(cip_ctx* ctx, const DevInputs& in, cip_plan* plan, void* image_dev,
+                                         cip_report* rep) {
+  const int fp64 = plan->accumulate_fp64;
+  CIP_REQUIRE(plan->support >= kMinSupport && plan->support <= kMaxSupport, "bad support %d", plan->support);
+  CIP_REQUIRE(plan->nu >= plan->npix_x && plan->nv >= plan->npix_y && plan->nu % 2 == 0 && plan->nv % 2 == 0,
+              "bad grid size %d x %d", plan->nu, plan->nv);
+  CIP_REQUIRE(plan->nplanes >= 1 && plan->dw > 0, "bad w-plane layout");
+  CIP_REQUIRE(plan->nu >= 2 * kFastSupport + kTile && plan->nv >= 2 * kFastSupport + kTile, "grid too small");
+  const GridGeom g = make_geom(*plan);
+  StageTimer tm(ctx, rep != nullptr);
+  double dummy = 0;
+
+  tm.start();
+  BinResult bins;
+  CIP_TRY(run_binning(ctx, in, g, fp64, &bins));
+  tm.stop(rep ? &rep->ms_bin : &dummy);
+  if (bins.nitems == 0) return CIP_OK;
+
+  // how many planes fit
+  CIP_TRY(fft_prepare(ctx, plan->nu, plan->nv, fp64));
+  const size_t plane_bytes = (size_t)plan->nu * plan->nv * (fp64 ? 16 : 8);
+  size_t free_b = 0, total_b = 0;
+  CIP_CHECK_CUDA(cudaMemGetInfo(&free_b, &total_b));
+  const size_t reserve = (size_t)768 << 20;
+  size_t avail = free_b + ctx->grid.cap;
+  avail = avail > reserve ? avail - reserve : 0;
+  int64_t max_slots = (int64_t)(avail / plane_bytes);
+  if (const char* e = getenv("CIP_MAX_PLANE_SLOTS")) max_slots = std::min<int64_t>(max_slots, atoll(e));
+  int nslots_alloc;
+  if (max_slots >= plan->nplanes) {
+    nslots_alloc = plan->nplanes;
+  } else {
+    CIP_REQUIRE(g.W <= kFastSupport, "the wide-support gridder needs all %d planes resident (%lld fit)",
+                plan->nplanes, (long long)max_slots);
+    if (max_slots < kWin) {
+      set_error("not enough device memory for one window of %d planes of %zu bytes", kWin, plane_bytes);
+      return CIP_ENOMEM;
+    }
+    nslots_alloc = (int)max_slots;
+  }
+  plan->plane_block = nslots_alloc;
+  CIP_TRY(ctx->grid.ensure(plane_bytes * nslots_alloc));
+
+  int w = 0;
+  while (w < g.nwin) {
+    int pb, wl, used;
+    if (nslots_alloc >= plan->nplanes) {
+      pb = 0;
+      wl = g.nwin - 1;
+      used = plan->nplanes;
+    } else {
+      pb = w * g.win_step;
+      wl = std::min(g.nwin - 1, w + (nslots_alloc - kWin) / g.win_step);
+      used = std::min(plan->nplanes, wl * g.win_step + kWin) - pb;
+    }
+    const int64_t it0 = bins.win_item_start[w], it1 = bins.win_item_start[wl + 1];
+    if (it1 > it0) {
+      tm.start();
+      CIP_CHECK_CUDA(cudaMemsetAsync(ctx->grid.p, 0, plane_bytes * used, ctx->stream));
+      CIP_TRY(run_gridder(ctx, g, fp64, it0, it1, ctx->grid.p, pb, used));
+      tm.stop(rep ? &rep->ms_grid : &dummy);
+      tm.start();
+      CIP_TRY(run_fft(ctx, ctx->grid.p, plan->nu, plan->nv, used, fp64));
+      tm.stop(rep ? &rep->ms_fft : &dummy);
+      tm.start();
+      CIP_TRY(run_wscreen(ctx, *plan, ctx->grid.p, pb, used, image_dev));
+      tm.stop(rep ? &rep->ms_wscreen : &dummy);
+      if (rep) rep->nblocks++;
+    }
+    w = wl + 1;
+  }
+  return CIP_OK;
+}
+
+extern "C" cip_status cip_grid_accumulate(cip_ctx* ctx, const cip_invert_args* args, cip_plan* plan, void* image_dev,
+                                          cip_report* report) {
+  CIP_REQUIRE(ctx && plan && image_dev, "NULL argument");
+  CIP_TRY(validate_args(args));
+  CIP_REQUIRE(plan->npix_x == args->npix_x && plan->npix_y == args->npix_y, "plan and args disagree on the image size");
+  CIP_CHECK_CUDA(cudaSetDevice(ctx->device));
+  if (report) memset(report, 0, sizeof(*report));
+  const int64_t l0 = ctx->launches;
+  DevInputs in;
+  CIP_TRY(stage_inputs(ctx, args, &in, report ? &report->ms_h2d : nullptr));
+  CIP_TRY(grid_accumulate_staged(ctx, in, plan, image_dev, report));
+  CIP_CHECK_CUDA(cudaStreamSynchronize(ctx->stream));
+  if (report) report->launches += ctx->launches - l0;
+  return CIP_OK;
+}
+
+extern "C" cip_status cip_correct_image(cip_ctx* ctx, const cip_plan* plan, void* image_dev, int row_begin,
+                                        int row_end, double scale) {
+  CIP_REQUIRE(ctx && plan && image_dev, "NULL argument");
+  CIP_CHECK_CUDA(cudaSetDevice(ctx->device));
+  CIP_TRY(run_correct(ctx, *plan, image_dev, row_begin, row_end, scale));
+  CIP_CHECK_CUDA(cudaStreamSynchronize(ctx->stream));
+  return CIP_OK;
+}
+
+extern "C" cip_status cip_invert(cip_ctx* ctx, const cip_invert_args* args, void* dirty_out, cip_scan_result* scan_out,
+                                 cip_plan* plan_out, cip_report* report) {
+  CIP_REQUIRE(ctx && dirty_out, "NULL argument");
+  CIP_TRY(validate_args(args));
+  CIP_CHECK_CUDA(cudaSetDevice(ctx->device));
+  if (report) memset(report, 0, sizeof(*report));
+  const int64_t l0 = ctx->launches;
+  cudaStream_t st = ctx->stream;
+  CIP_CHECK_CUDA(cudaEventRecord(ctx->ev[2], st));
+  const int fp64 = args->accumulate_fp64 != 0;
+  const size_t img_bytes = (size_t)args->npix_x * args->npix_y * (fp64 ? 8 : 4);
+  void* image = dirty_out;
+  if (args->memspace == 0) {
+    CIP_TRY(ctx->image.ensure(img_bytes));
+    image = ctx->image.p;
+  }
+  CIP_CHECK_CUDA(cudaMemsetAsync(image, 0, img_bytes, st));
+
+  DevInputs in;
+  CIP_TRY(stage_inputs(ctx, args, &in, report ? &report->ms_h2d : nullptr));
+  StageTimer tm(ctx, report != nullptr);
+  double dummy = 0;
+  tm.start();
+  cip_scan_result scan{};
+  CIP_TRY(run_scan(ctx, in, args->do_wstacking, &scan));
+  tm.stop(report ? &report->ms_scan : &dummy);
+  if (scan_out) *scan_out = scan;
+  cip_plan plan{};
+  CIP_TRY(cip_plan_make(args->npix_x, args->npix_y, args->pixsize_x, args->pixsize_y, args->epsilon,
+                        args->do_wstacking, fp64, scan.wmin, scan.wmax, scan.nactive,
+                        getenv("CIP_SIGMA") ? atof(getenv("CIP_SIGMA")) : 0.0,
+                        getenv("CIP_SUPPORT") ? atoi(getenv("CIP_SUPPORT")) : 0, &plan));
+  if (scan.nactive > 0) {
+    CIP_TRY(grid_accumulate_staged(ctx, in, &plan, image, report));
+    tm.start();
+    CIP_TRY(run_correct(ctx, plan, image, 0, args->npix_x, 1.0));
+    tm.stop(report ? &report->ms_correct : &dummy);
+  }
+  if (plan_out) *plan_out = plan;
+  if (args->memspace == 0) {
+    tm.start();
+    CIP_CHECK_CUDA(cudaMemcpyAsync(dirty_out, image, img_bytes, cudaMemcpyDeviceToHost, st));
+    tm.stop(report ? &report->ms_d2h : &dummy);
+  }
+  CIP_CHECK_CUDA(cudaEventRecord(ctx->ev[3], st));
+  CIP_CHECK_CUDA(cudaStreamSynchronize(st));
+  if (report) {
+    report->ms_total = elapsed_ms(ctx, 2, 3);
+    report->launches += ctx->launches - l0;
+    report->nactive = scan.nactive;
+  }
+  return CIP_OK;
+}

@@ -1,0 +1,179 @@
+"""ctypes binding of libcip_b200.so (the C-ABI declared in include/cip.h).
+
+This is the only place the package crosses into native code.  There is no CPU
+fallback: if the shared library is missing or no CUDA device is present the
+calls raise.  PyTorch tensors (or numpy arrays) are used purely as buffers;
+only raw pointers and sizes cross the boundary.
+"""
+from __future__ import annotations
+
+import ctypes as C
+import os
+import threading
+from pathlib import Path
+
+import numpy as np
+
+_LIB_PATH = Path(__file__).resolve().parent / "_lib" / "libcip_b200.so"
+_lib = None
+_lock = threading.Lock()
+
+
+class CipError(RuntimeError):
+    """Raised for CUDA / cuFFT / memory failures (ducc0 raises RuntimeError too)."""
+
+
+class InvertArgs(C.Structure):
+    _fields_ = [("uvw", C.c_void_p), ("nrow", C.c_int64), ("freq", C.c_void_p), ("nchan", C.c_int64),
+                ("vis", C.c_void_p), ("wgt", C.c_void_p), ("mask", C.c_void_p),
+                ("vis_row_stride", C.c_int64), ("wgt_row_stride", C.c_int64),
+                ("npix_x", C.c_int), ("npix_y", C.c_int), ("pixsize_x", C.c_double), ("pixsize_y", C.c_double),
+                ("epsilon", C.c_double), ("do_wstacking", C.c_int), ("accumulate_fp64", C.c_int),
+                ("memspace", C.c_int)]
+
+
+class ScanResult(C.Structure):
+    _fields_ = [("wmin", C.c_double), ("wmax", C.c_double), ("nactive", C.c_int64), ("sum_wgt", C.c_double)]
+
+
+class Plan(C.Structure):
+    _fields_ = [("npix_x", C.c_int), ("npix_y", C.c_int), ("pixsize_x", C.c_double), ("pixsize_y", C.c_double),
+                ("sigma", C.c_double), ("support", C.c_int), ("beta", C.c_double), ("nu", C.c_int), ("nv", C.c_int),
+                ("nshift", C.c_double), ("dw", C.c_double), ("w0", C.c_double), ("nplanes", C.c_int),
+                ("accumulate_fp64", C.c_int), ("do_wstacking", C.c_int), ("plane_block", C.c_int)]
+
+    def as_dict(self):
+        return {n: getattr(self, n) for n, _ in self._fields_}
+
+
+class Report(C.Structure):
+    _fields_ = [("ms_total", C.c_double), ("ms_h2d", C.c_double), ("ms_scan", C.c_double), ("ms_bin", C.c_double),
+                ("ms_grid", C.c_double), ("ms_fft", C.c_double), ("ms_wscreen", C.c_double),
+                ("ms_correct", C.c_double), ("ms_d2h", C.c_double), ("launches", C.c_int64),
+                ("nactive", C.c_int64), ("nblocks", C.c_int)]
+
+    def as_dict(self):
+        return {n: getattr(self, n) for n, _ in self._fields_}
+
+
+def lib_path() -> Path:
+    return Path(os.environ.get("CIP_B200_LIB", _LIB_PATH))
+
+
+def lib():
+    """Load libcip_b200.so; raises ImportError with build instructions if it is missing."""
+    global _lib
+    with _lock:
+        if _lib is None:
+            path = lib_path()
+            if not path.exists():
+                raise ImportError(
+                    f"{path} not found: build it with `python -c 'import __graft_entry__ as g; g.build()'` "
+                    "(or `make -C ska-sdp-continuum-imaging-pipeline_b200`); there is no CPU fallback")
+            L = C.CDLL(str(path))
+            L.cip_last_error.restype = C.c_char_p
+            L.cip_version.restype = C.c_char_p
+            L.cip_ctx_stream.restype = C.c_void_p
+            L.cip_ctx_stream.argtypes = [C.c_void_p]
+            L.cip_ctx_create.argtypes = [C.c_int, C.POINTER(C.c_void_p)]
+            L.cip_ctx_destroy.argtypes = [C.c_void_p]
+            L.cip_ctx_synchronize.argtypes = [C.c_void_p]
+            L.cip_plan_make.argtypes = [C.c_int, C.c_int, C.c_double, C.c_double, C.c_double, C.c_int, C.c_int,
+                                        C.c_double, C.c_double, C.c_int64, C.c_double, C.c_int, C.POINTER(Plan)]
+            L.cip_kernel_table.argtypes = [C.c_double, C.c_int, C.POINTER(C.c_double), C.POINTER(C.c_double)]
+            L.cip_kernel_ft.argtypes = [C.POINTER(Plan), C.c_void_p, C.c_int64, C.c_void_p]
+            L.cip_scan.argtypes = [C.c_void_p, C.POINTER(InvertArgs), C.POINTER(ScanResult)]
+            L.cip_grid_accumulate.argtypes = [C.c_void_p, C.POINTER(InvertArgs), C.POINTER(Plan), C.c_void_p,
+                                              C.POINTER(Report)]
+            L.cip_correct_image.argtypes = [C.c_void_p, C.POINTER(Plan), C.c_void_p, C.c_int, C.c_int, C.c_double]
+            L.cip_invert.argtypes = [C.c_void_p, C.POINTER(InvertArgs), C.c_void_p, C.POINTER(ScanResult),
+                                     C.POINTER(Plan), C.POINTER(Report)]
+            L.cip_stokes_i.argtypes = [C.c_void_p, C.c_void_p, C.c_void_p, C.c_void_p, C.c_int64, C.c_int64,
+                                       C.c_void_p, C.c_void_p, C.c_int]
+            L.cip_tile_bin.argtypes = [C.c_void_p, C.c_void_p, C.c_int64, C.c_void_p, C.c_int64,
+                                       C.POINTER(C.c_double * 3), C.c_int64, C.c_int, C.POINTER(C.c_void_p),
+                                       C.POINTER(C.c_int64), C.POINTER(C.c_int64)]
+            L.cip_tile_fetch.argtypes = [C.c_void_p] * 7
+            L.cip_tile_gather.argtypes = [C.c_void_p, C.c_void_p, C.c_void_p, C.c_void_p, C.c_int64, C.c_int64,
+                                          C.c_int, C.c_void_p, C.c_void_p, C.c_void_p]
+            L.cip_tile_free.argtypes = [C.c_void_p, C.c_void_p]
+            _lib = L
+    return _lib
+
+
+EXPORTS = ["cip_last_error", "cip_version", "cip_ctx_create", "cip_ctx_destroy", "cip_ctx_stream",
+           "cip_ctx_synchronize", "cip_plan_make", "cip_kernel_table", "cip_kernel_ft", "cip_scan",
+           "cip_grid_accumulate", "cip_correct_image", "cip_invert", "cip_stokes_i", "cip_tile_bin",
+           "cip_tile_fetch", "cip_tile_gather", "cip_tile_free"]
+
+
+def check(status: int) -> None:
+    """CIP_EINVAL -> ValueError, everything else -> CipError (a RuntimeError), as SURVEY 8(b) specifies."""
+    if status == 0:
+        return
+    msg = lib().cip_last_error().decode(errors="replace")
+    if status == 1:
+        raise ValueError(msg)
+    if status == 2:
+        raise MemoryError(msg)
+    raise CipError(f"libcip_b200 status {status}: {msg}")
+
+
+class Context:
+    """One context per process and GPU (cip_ctx is not re-entrant; calls are serialised by a lock)."""
+
+    _instances: dict[int, "Context"] = {}
+
+    def __init__(self, device: int = -1):
+        self._h = C.c_void_p()
+        check(lib().cip_ctx_create(device, C.byref(self._h)))
+        self.lock = threading.Lock()
+
+    @classmethod
+    def get(cls, device: int = -1) -> "Context":
+        with _lock:
+            inst = cls._instances.get(device)
+        if inst is None:
+            inst = cls(device)
+            with _lock:
+                cls._instances[device] = inst
+        return inst
+
+    @property
+    def handle(self):
+        return self._h
+
+    def close(self):
+        if self._h:
+            lib().cip_ctx_destroy(self._h)
+            self._h = C.c_void_p()
+
+    def __del__(self):  # pragma: no cover
+        try:
+            self.close()
+        except Exception:
+            pass
+
+
+def _ptr(a):
+    """Raw pointer of a numpy array or torch tensor (None -> NULL)."""
+    if a is None:
+        return None
+    if isinstance(a, np.ndarray):
+        return a.ctypes.data
+    return a.data_ptr()  # torch tensor
+
+
+def plan_make(nx, ny, px, py, epsilon, wmin, wmax, nactive, *, do_wstacking=True, fp64=False, sigma=0.0,
+              support=0) -> Plan:
+    p = Plan()
+    check(lib().cip_plan_make(nx, ny, px, py, epsilon, int(do_wstacking), int(fp64), wmin, wmax, int(nactive),
+                              float(sigma or 0.0), int(support or 0), C.byref(p)))
+    return p
+
+
+def kernel_ft(plan: Plan, xi) -> np.ndarray:
+    xi = np.ascontiguousarray(xi, dtype=np.float64)
+    out = np.empty_like(xi)
+    check(lib().cip_kernel_ft(C.byref(plan), xi.ctypes.data, xi.size, out.ctypes.data))
+    return out

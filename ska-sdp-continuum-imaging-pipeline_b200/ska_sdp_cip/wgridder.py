@@ -1,0 +1,106 @@
+"""B200 replacement of ``ducc0.wgridder.ms2dirty`` -- the one native call of the reference
+(src/ska_sdp_cip/invert.py:13, :170-183).
+
+Same positional arguments and keywords as the ducc0 function the reference calls, so
+``ducc_invert`` below reads like the reference's.  Inputs may be numpy arrays (host memory;
+copied to the GPU inside the call) or CUDA torch tensors (used in place, result returned as a
+CUDA tensor).  All arithmetic happens in libcip_b200.so; nothing here computes.
+"""
+from __future__ import annotations
+
+import ctypes as C
+from typing import Optional
+
+import numpy as np
+
+from . import _cabi
+from ._cabi import Context, InvertArgs, Plan, Report, ScanResult, check, lib
+
+
+def _is_torch_cuda(a) -> bool:
+    return a is not None and not isinstance(a, np.ndarray) and hasattr(a, "is_cuda") and a.is_cuda
+
+
+def _prep_host(uvw, freq, ms, wgt, mask):
+    uvw = np.ascontiguousarray(uvw, dtype=np.float64)
+    freq = np.ascontiguousarray(freq, dtype=np.float64)
+    if uvw.ndim != 2 or uvw.shape[1] != 3:
+        raise ValueError(f"uvw must have shape (nrow, 3), got {uvw.shape}")
+    ms = np.asarray(ms)
+    if ms.ndim != 2 or ms.shape != (uvw.shape[0], freq.shape[0]):
+        raise ValueError(f"ms must have shape (nrow, nchan) = {(uvw.shape[0], freq.shape[0])}, got {ms.shape}")
+    fp64_in = ms.dtype == np.complex128
+    ms = np.ascontiguousarray(ms, dtype=np.complex64)
+    if wgt is not None:
+        wgt = np.ascontiguousarray(wgt, dtype=np.float32)
+        if wgt.shape != ms.shape:
+            raise ValueError("wgt must have the shape of ms")
+    if mask is not None:
+        mask = np.ascontiguousarray(mask, dtype=np.uint8)
+        if mask.shape != ms.shape:
+            raise ValueError("mask must have the shape of ms")
+    return uvw, freq, ms, wgt, mask, fp64_in
+
+
+def make_args(uvw, freq, ms, wgt, mask, npix_x, npix_y, pixsize_x, pixsize_y, epsilon, do_wstacking, fp64,
+              memspace) -> InvertArgs:
+    a = InvertArgs()
+    a.uvw = _cabi._ptr(uvw)
+    a.nrow = int(uvw.shape[0])
+    a.freq = _cabi._ptr(freq)
+    a.nchan = int(freq.shape[0])
+    a.vis = _cabi._ptr(ms)
+    a.wgt = _cabi._ptr(wgt)
+    a.mask = _cabi._ptr(mask)
+    a.vis_row_stride = 0
+    a.wgt_row_stride = 0
+    a.npix_x, a.npix_y = int(npix_x), int(npix_y)
+    a.pixsize_x, a.pixsize_y = float(pixsize_x), float(pixsize_y)
+    a.epsilon = float(epsilon)
+    a.do_wstacking = int(bool(do_wstacking))
+    a.accumulate_fp64 = int(bool(fp64))
+    a.memspace = memspace
+    return a
+
+
+def ms2dirty(uvw, freq, ms, wgt=None, npix_x=0, npix_y=0, pixsize_x=0.0, pixsize_y=0.0, nu=0, nv=0,
+             epsilon=1e-4, do_wstacking=False, nthreads=1, verbosity=0, mask=None,
+             double_precision_accumulation=False, *, device: int = -1, return_info: bool = False):
+    """Dirty image (npix_x, npix_y) of the given visibilities; see the module docstring.
+
+    ``nthreads``, ``nu``, ``nv`` and ``verbosity`` are accepted for signature compatibility and ignored.
+    complex128 ``ms`` or ``double_precision_accumulation=True`` selects float64 grids and a float64 result.
+    """
+    del nthreads, nu, nv, verbosity
+    dev_in = _is_torch_cuda(ms)
+    if dev_in:
+        import torch
+        for t in (uvw, freq, ms):
+            if not (_is_torch_cuda(t) and t.is_contiguous()):
+                raise ValueError("with CUDA inputs, uvw, freq and ms must all be contiguous CUDA tensors")
+        if uvw.dtype != torch.float64 or freq.dtype != torch.float64 or ms.dtype != torch.complex64:
+            raise ValueError("CUDA inputs must be float64 uvw/freq and complex64 ms")
+        if wgt is not None and (not _is_torch_cuda(wgt) or wgt.dtype != torch.float32 or not wgt.is_contiguous()):
+            raise ValueError("wgt must be a contiguous float32 CUDA tensor")
+        if mask is not None and (not _is_torch_cuda(mask) or mask.dtype != torch.uint8 or not mask.is_contiguous()):
+            raise ValueError("mask must be a contiguous uint8 CUDA tensor")
+        fp64 = bool(double_precision_accumulation)
+        device = ms.device.index
+        out = torch.empty((npix_x, npix_y), dtype=torch.float64 if fp64 else torch.float32, device=ms.device)
+        torch.cuda.current_stream(ms.device).synchronize()
+        memspace = 1
+    else:
+        uvw, freq, ms, wgt, mask, fp64_in = _prep_host(uvw, freq, ms, wgt, mask)
+        fp64 = bool(double_precision_accumulation) or fp64_in
+        out = np.empty((npix_x, npix_y), dtype=np.float64 if fp64 else np.float32)
+        memspace = 0
+    args = make_args(uvw, freq, ms, wgt, mask, npix_x, npix_y, pixsize_x, pixsize_y, epsilon, do_wstacking, fp64,
+                     memspace)
+    ctx = Context.get(device)
+    scan, plan, rep = ScanResult(), Plan(), Report()
+    with ctx.lock:
+        check(lib().cip_invert(ctx.handle, C.byref(args), _cabi._ptr(out), C.byref(scan), C.byref(plan), C.byref(rep)))
+    if return_info:
+        return out, {"scan": {n: getattr(scan, n) for n, _ in scan._fields_}, "plan": plan.as_dict(),
+                     "report": rep.as_dict()}
+    return out
