@@ -1,0 +1,321 @@
+#!/usr/bin/env python
+"""Headline benchmark: invert throughput (Mvis/s) of the B200 hot path.
+
+    python bench.py [--gpus N] [--steps K] [--warmup W] [--impl reference] [--times T]
+
+A "step" is one complete invert (scan, binning, gridding, FFTs, w-screen, correction) of one batch
+of synthetic SKA-Mid AA* visibilities (BASELINE.json configs[1]: 144 dishes = 10,296 baselines x 256
+times x 64 channels = 168.7 M visibilities, 4096^2 image, epsilon 1e-4, w-stacking).  With N > 1
+(launched under torchrun, one rank per GPU) every rank grids its own 256-time shard of a longer
+observation and the partial images are combined by one NCCL reduce-scatter / all-gather around the
+correction: weak scaling, no other collective.
+
+Printed JSON (one line, rank 0): `value` = device-resident inputs, timed with CUDA events on the
+library's stream; `e2e` = the same step through the reference-facing call
+(`ska_sdp_cip.wgridder.ms2dirty` with HOST arrays: pinned host -> device copies and the image read-back
+inside the timed region); `roofline` = the gridding kernel against measured HBM bandwidth;
+`cpu_baseline` = the oracle's C/OpenMP w-stacking port on a bounded sample, on this box's host cores.
+`--impl reference` times that CPU port alone (the reference's own gridder, ducc0, is a third-party
+wheel that is not installable here -- see DESIGN.md).
+"""
+from __future__ import annotations
+
+import argparse
+import ctypes as C
+import json
+import os
+import subprocess
+import sys
+import tempfile
+import time
+from pathlib import Path
+
+import numpy as np
+
+ROOT = Path(__file__).resolve().parent
+sys.path.insert(0, str(ROOT))
+sys.path.insert(0, str(ROOT / "ska-sdp-continuum-imaging-pipeline_b200"))
+
+METRIC = "invert_throughput"
+UNIT = "Mvis/s"
+
+
+def measured_peaks():
+    p = ROOT / "MEASURED_PEAKS.json"
+    if p.exists():
+        try:
+            return float(json.loads(p.read_text())["hbm_gbs"]), "measured"
+        except Exception:  # noqa: BLE001
+            pass
+    return 6650.0, "fallback"
+
+
+class ClockSampler:
+    """nvidia-smi clocks / throttle reasons sampled DURING the timed region."""
+
+    Q = ("index,clocks.sm,clocks.max.sm,power.draw,clocks_event_reasons.hw_slowdown,"
+         "clocks_event_reasons.hw_thermal_slowdown,clocks_event_reasons.sw_thermal_slowdown,"
+         "clocks_event_reasons.sw_power_cap")
+
+    def __init__(self, index: int):
+        self.index = index
+        self.f = tempfile.NamedTemporaryFile("w+", suffix=".csv", delete=False)
+        self.p = None
+
+    def start(self):
+        try:
+            self.p = subprocess.Popen(["nvidia-smi", "-i", str(self.index), f"--query-gpu={self.Q}",
+                                       "--format=csv,noheader,nounits", "-lms", "100"], stdout=self.f,
+                                      stderr=subprocess.DEVNULL)
+        except OSError:
+            self.p = None
+
+    def stop(self):
+        out = {"sm_mhz": None, "sm_max_mhz": None, "reasons": []}
+        if self.p is None:
+            return out
+        self.p.terminate()
+        try:
+            self.p.wait(timeout=5)
+        except subprocess.TimeoutExpired:
+            self.p.kill()
+        self.f.flush()
+        rows = [l.split(",") for l in Path(self.f.name).read_text().strip().splitlines() if l.count(",") >= 7]
+        os.unlink(self.f.name)
+        if not rows:
+            return out
+        sm = [float(r[1]) for r in rows if r[1].strip().replace(".", "").isdigit()]
+        mx = [float(r[2]) for r in rows if r[2].strip().replace(".", "").isdigit()]
+        names = ["hw_slowdown", "hw_thermal_slowdown", "sw_thermal_slowdown", "sw_power_cap"]
+        reasons = sorted({n for r in rows for n, v in zip(names, r[4:8]) if v.strip().lower().startswith("active")})
+        out.update(sm_mhz=float(np.median(sm)) if sm else None, sm_max_mhz=max(mx) if mx else None,
+                   reasons=reasons, samples=len(rows))
+        return out
+
+
+def workload(times: int):
+    from ska_sdp_cip import synthetic as S
+    cfg = S.ska_mid(n_times=times)
+    full = S.ska_mid()  # the pixel size is that of the full 256-time configuration
+    px = S.pixel_size_lm(full, S.make_uvw(full, (0, full.n_times)))
+    return cfg, px
+
+
+def cpu_port_rate(cfg, px, sample_times: int, repeats: int = 1):
+    """The oracle's C/OpenMP w-stacking port on the first `sample_times` time steps of the workload."""
+    from oracle import wstack
+    from ska_sdp_cip import synthetic as S
+    sub = S.ska_mid(n_times=sample_times)
+    sub.seed = cfg.seed
+    uvw = S.make_uvw(cfg, (0, sample_times))
+    freq = cfg.frequencies()
+    vis, wgt = S.make_vis_numpy(sub, uvw, freq, px)
+    wstack.lib()
+    best = None
+    for _ in range(repeats):
+        t = time.perf_counter()
+        wstack.ms2dirty(uvw, freq, vis, wgt, cfg.num_pixels, cfg.num_pixels, px, px, cfg.epsilon)
+        dt = time.perf_counter() - t
+        best = dt if best is None else min(best, dt)
+    nvis = uvw.shape[0] * freq.shape[0]
+    return nvis / best / 1e6, best, nvis, wstack.lib().oracle_num_threads()
+
+
+def run_reference(args):
+    rank = int(os.environ.get("RANK", "0"))
+    if rank != 0:
+        return
+    cfg, px = workload(args.times)
+    sample_times = 4
+    rates = []
+    for _ in range(args.warmup):
+        cpu_port_rate(cfg, px, 1)
+    t_total = 0.0
+    for _ in range(args.steps):
+        r, dt, nvis, cores = cpu_port_rate(cfg, px, sample_times)
+        rates.append(r)
+        t_total += dt
+    value = float(np.mean(rates))
+    sample = (f"first {sample_times} of {cfg.n_times} time steps ({nvis} visibilities) of the same workload, "
+              f"full {cfg.num_pixels}^2 image, per step")
+    line = {"impl": "reference", "metric": METRIC, "value": value, "unit": UNIT, "n_gpus": args.gpus,
+            "steps": args.steps, "warmup": args.warmup, "ms_per_step": 1e3 * t_total / max(args.steps, 1),
+            "higher_is_better": True, "scaling": "weak", "vs_baseline": None, "dtype": "f32", "data": "synthetic",
+            "config": {"workload": f"{cfg.name}: {cfg.n_baselines} baselines x {cfg.n_times} times x {cfg.n_chan} "
+                                   f"channels, {cfg.num_pixels}^2 image, epsilon {cfg.epsilon}, w-stacking",
+                       "note": "ducc0 (the reference's gridder) is not installable here; this is the oracle's "
+                               "C/OpenMP port of the same algorithm"},
+            "cpu_baseline": {"value": value, "unit": UNIT, "cores": cores, "kind": "port", "sample": sample},
+            "e2e": {"value": value, "unit": UNIT, "h2d_bytes_per_step": 0, "d2h_bytes_per_step": 0},
+            "gpu_launches": 0}
+    print(json.dumps(line), flush=True)
+
+
+def run_b200(args):
+    import torch
+    import torch.distributed as dist
+    from ska_sdp_cip import _cabi, synthetic as S, wgridder
+    from ska_sdp_cip.invert import StokesIGridderInput, accumulate_shards, reduce_and_correct
+
+    world = int(os.environ.get("WORLD_SIZE", "1"))
+    rank = int(os.environ.get("RANK", "0"))
+    local = int(os.environ.get("LOCAL_RANK", "0"))
+    torch.cuda.set_device(local)
+    dev = torch.device("cuda", local)
+    if world > 1:
+        dist.init_process_group("nccl", device_id=dev)
+    cfg, px = workload(args.times)
+    N = cfg.num_pixels
+    # rank r observes times [r*T, (r+1)*T) of a world*T-step observation (weak scaling)
+    long_cfg = S.ska_mid(n_times=cfg.n_times * world)
+    uvw = S.make_uvw(long_cfg, (rank * cfg.n_times, (rank + 1) * cfg.n_times))
+    freq = cfg.frequencies()
+    d_vis, d_wgt = S.make_vis_torch(cfg, uvw, freq, px, dev, seed=1234 + rank)
+    d_uvw, d_freq = torch.from_numpy(uvw).to(dev), torch.from_numpy(freq).to(dev)
+    nvis = cfg.n_vis
+    ctx = _cabi.Context.get(local)
+    stream = torch.cuda.ExternalStream(_cabi.lib().cip_ctx_stream(ctx.handle), device=dev)
+    flush_buf = torch.empty(256 << 20, dtype=torch.uint8, device=dev)  # > 126 MB L2
+
+    reports = []
+
+    def step_device():
+        """One invert with inputs resident in HBM; multi-rank: + NCCL reduction of the partial images."""
+        if world == 1:
+            img, info = wgridder.ms2dirty(d_uvw, d_freq, d_vis, d_wgt, N, N, px, px, epsilon=cfg.epsilon,
+                                          do_wstacking=True, return_info=True)
+            reports.append(info["report"])
+            return img, info["plan"]
+        shard = StokesIGridderInput(d_freq, None, d_uvw, d_vis, d_wgt)
+        reps = []
+        img, plan, sumw = accumulate_shards([shard], N, px, epsilon=cfg.epsilon, reports=reps)
+        reports.extend(reps)
+        img = reduce_and_correct(img, plan, sumw, normalise=False)
+        return img, plan.as_dict()
+
+    def barrier():
+        if world > 1:
+            dist.barrier()
+        torch.cuda.synchronize()
+
+    def timed(fn, steps):
+        barrier()
+        e0, e1 = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
+        e0.record(stream)
+        for _ in range(steps):
+            flush_buf.zero_()          # flush L2 between iterations (inputs are also >> L2)
+            torch.cuda.synchronize()
+            fn()
+        e1.record(stream)
+        barrier()
+        ms = e0.elapsed_time(e1)
+        if world > 1:
+            t = torch.tensor([ms], dtype=torch.float64, device=dev)
+            dist.all_reduce(t, op=dist.ReduceOp.MAX)
+            ms = float(t.item())
+        return ms
+
+    for _ in range(args.warmup):
+        step_device()
+    reports.clear()
+    sampler = ClockSampler(local)
+    if rank == 0:
+        sampler.start()
+    l0 = ctx_launches(ctx)
+    ms_dev = timed(step_device, args.steps)
+    launches = ctx_launches(ctx) - l0
+    clocks = sampler.stop() if rank == 0 else {}
+    timed_reports = list(reports)
+    _, plan = step_device()
+
+    # ---- e2e: host buffers through the public call ------------------------------------------
+    h_vis = torch.empty(d_vis.shape, dtype=d_vis.dtype, pin_memory=True)
+    h_wgt = torch.empty(d_wgt.shape, dtype=d_wgt.dtype, pin_memory=True)
+    h_vis.copy_(d_vis)
+    h_wgt.copy_(d_wgt)
+    n_vis_np, n_wgt_np = h_vis.numpy(), h_wgt.numpy()
+    torch.cuda.synchronize()
+
+    def step_host():
+        if world == 1:
+            return wgridder.ms2dirty(uvw, freq, n_vis_np, n_wgt_np, N, N, px, px, epsilon=cfg.epsilon,
+                                     do_wstacking=True)
+        shard = StokesIGridderInput(freq, None, uvw, n_vis_np, n_wgt_np)
+        img, plan_, sumw = accumulate_shards([shard], N, px, epsilon=cfg.epsilon)
+        return reduce_and_correct(img, plan_, sumw, normalise=False).cpu().numpy()
+
+    e2e_steps = max(1, min(args.steps, 3))
+    step_host()
+    ms_e2e = timed(step_host, e2e_steps)
+    h2d = int(n_vis_np.nbytes + n_wgt_np.nbytes + uvw.nbytes + freq.nbytes)
+    d2h = int(N * N * 4)
+
+    if rank != 0:
+        if world > 1:
+            dist.destroy_process_group()
+        return
+    # ---- roofline of the dominant kernel (gridding) ------------------------------------------
+    peak, peak_kind = measured_peaks()
+    n_grid_launch = sum(r["nblocks"] for r in timed_reports)
+    ms_grid = sum(r["ms_grid"] for r in timed_reports) / max(n_grid_launch, 1)
+    # algorithmic bytes of one gridding launch: every input read once (12 B + 24 B/row + 8 B/chan) and the
+    # plane stack written once (DESIGN.md "kernel 2")
+    alg_bytes = nvis * 12 + uvw.shape[0] * 24 + freq.shape[0] * 8 + plan["nplanes"] * plan["nu"] * plan["nv"] * 8
+    achieved = alg_bytes / (ms_grid * 1e-3) / 1e9
+    stage = {k: float(np.mean([r[k] for r in timed_reports])) for k in
+             ("ms_scan", "ms_bin", "ms_zero", "ms_grid", "ms_fft", "ms_wscreen", "ms_correct", "ms_total")}
+    # ---- CPU baseline on a bounded sample -----------------------------------------------------
+    cpu = None
+    if not args.no_cpu:
+        r, dt, nv_s, cores = cpu_port_rate(cfg, px, 4)
+        cpu = {"value": r, "unit": UNIT, "cores": cores, "kind": "port",
+               "sample": f"first 4 of {cfg.n_times} time steps ({nv_s} visibilities), full {N}^2 image, {dt:.1f} s"}
+    total_vis = nvis * world
+    line = {
+        "metric": METRIC, "value": total_vis * args.steps / ms_dev / 1e3, "unit": UNIT, "n_gpus": world,
+        "steps": args.steps, "warmup": args.warmup, "ms_per_step": ms_dev / args.steps, "higher_is_better": True,
+        "scaling": "weak", "vs_baseline": None, "dtype": "f32", "data": "synthetic",
+        "config": {"workload": f"{cfg.name}: {cfg.n_baselines} baselines x {cfg.n_times} times x {cfg.n_chan} channels "
+                               f"per GPU ({nvis} visibilities), {N}^2 image, epsilon {cfg.epsilon}, w-stacking",
+                   "sigma": plan["sigma"], "support": plan["support"], "nu": plan["nu"], "nv": plan["nv"],
+                   "nplanes": plan["nplanes"], "l2": "256 MB buffer written between iterations; inputs 2 GB >> L2",
+                   "sharding": "time ranges per rank, NCCL reduce-scatter + all-gather of the dirty image" if world > 1
+                   else "single GPU"},
+        "e2e": {"value": total_vis * e2e_steps / ms_e2e / 1e3, "unit": UNIT, "h2d_bytes_per_step": h2d,
+                "d2h_bytes_per_step": d2h, "steps": e2e_steps},
+        "gpu_launches": int(launches),
+        "roofline": {"bound": "hbm", "kernel": "grid_kernel<float>", "achieved": achieved, "peak": peak,
+                     "unit": "GB/s", "frac": achieved / peak, "traffic": None, "peak_source": peak_kind,
+                     "ms_per_launch": ms_grid, "algorithmic_bytes": int(alg_bytes)},
+        "stage_ms": stage,
+        "cpu_baseline": cpu,
+        "clocks": clocks,
+    }
+    print(json.dumps(line), flush=True)
+    if world > 1:
+        dist.destroy_process_group()
+
+
+def ctx_launches(ctx) -> int:
+    """Kernel launches counted by the library (cip_ctx.launches is read through a report delta)."""
+    from ska_sdp_cip import _cabi
+    return int(_cabi.lib().cip_ctx_launches(ctx.handle))
+
+
+def main():
+    ap = argparse.ArgumentParser()
+    ap.add_argument("--gpus", type=int, default=1)
+    ap.add_argument("--steps", type=int, default=5)
+    ap.add_argument("--warmup", type=int, default=3)
+    ap.add_argument("--impl", default="b200", choices=["b200", "reference"])
+    ap.add_argument("--times", type=int, default=256, help="time steps per GPU (256 = BASELINE.json configs[1])")
+    ap.add_argument("--no-cpu", action="store_true", help="skip the CPU baseline leg")
+    args = ap.parse_args()
+    if args.impl == "reference":
+        run_reference(args)
+    else:
+        run_b200(args)
+
+
+if __name__ == "__main__":
+    main()

@@ -56,6 +56,8 @@ cip_status cip_ctx_destroy(cip_ctx* ctx);
 /* The stream all work of this context is enqueued on (a cudaStream_t). */
 void* cip_ctx_stream(cip_ctx* ctx);
 cip_status cip_ctx_synchronize(cip_ctx* ctx);
+/* Number of kernels this library has launched on the context so far (own kernels, CUB passes, cuFFT execs). */
+int64_t cip_ctx_launches(cip_ctx* ctx);
 
 /* ---- ms2dirty arguments, 1:1 (invert.py:170-183) -------------------------------- */
 typedef struct {
@@ -98,10 +100,11 @@ typedef struct {
 } cip_plan;
 
 typedef struct {
-  double ms_total, ms_h2d, ms_scan, ms_bin, ms_grid, ms_fft, ms_wscreen, ms_correct, ms_d2h;
+  double ms_total, ms_h2d, ms_scan, ms_bin, ms_grid /* gridding kernel only */, ms_fft, ms_wscreen, ms_correct, ms_d2h;
   int64_t launches;         /* kernels of this library launched by the call          */
   int64_t nactive;
-  int nblocks;              /* plane blocks processed                                */
+  int nblocks;              /* plane blocks processed = launches of the gridding kernel */
+  double ms_zero;           /* clearing the plane stack before gridding                 */
 } cip_report;
 
 /* Host-only planning: choose (sigma, W) and the w-plane layout.  No GPU needed.

@@ -176,6 +176,8 @@ extern "C" cip_status cip_ctx_destroy(cip_ctx* ctx) {
 
 extern "C" void* cip_ctx_stream(cip_ctx* ctx) { return ctx ? (void*)ctx->stream : nullptr; }
 
+extern "C" int64_t cip_ctx_launches(cip_ctx* ctx) { return ctx ? ctx->launches : 0; }
+
 extern "C" cip_status cip_ctx_synchronize(cip_ctx* ctx) {
   CIP_REQUIRE(ctx != nullptr, "ctx is NULL");
   CIP_CHECK_CUDA(cudaStreamSynchronize(ctx->stream));

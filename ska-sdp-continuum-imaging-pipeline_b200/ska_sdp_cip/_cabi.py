@@ -50,7 +50,7 @@ class Report(C.Structure):
     _fields_ = [("ms_total", C.c_double), ("ms_h2d", C.c_double), ("ms_scan", C.c_double), ("ms_bin", C.c_double),
                 ("ms_grid", C.c_double), ("ms_fft", C.c_double), ("ms_wscreen", C.c_double),
                 ("ms_correct", C.c_double), ("ms_d2h", C.c_double), ("launches", C.c_int64),
-                ("nactive", C.c_int64), ("nblocks", C.c_int)]
+                ("nactive", C.c_int64), ("nblocks", C.c_int), ("ms_zero", C.c_double)]
 
     def as_dict(self):
         return {n: getattr(self, n) for n, _ in self._fields_}
@@ -78,6 +78,8 @@ def lib():
             L.cip_ctx_create.argtypes = [C.c_int, C.POINTER(C.c_void_p)]
             L.cip_ctx_destroy.argtypes = [C.c_void_p]
             L.cip_ctx_synchronize.argtypes = [C.c_void_p]
+            L.cip_ctx_launches.argtypes = [C.c_void_p]
+            L.cip_ctx_launches.restype = C.c_int64
             L.cip_plan_make.argtypes = [C.c_int, C.c_int, C.c_double, C.c_double, C.c_double, C.c_int, C.c_int,
                                         C.c_double, C.c_double, C.c_int64, C.c_double, C.c_int, C.POINTER(Plan)]
             L.cip_kernel_table.argtypes = [C.c_double, C.c_int, C.POINTER(C.c_double), C.POINTER(C.c_double)]
@@ -102,7 +104,7 @@ def lib():
 
 
 EXPORTS = ["cip_last_error", "cip_version", "cip_ctx_create", "cip_ctx_destroy", "cip_ctx_stream",
-           "cip_ctx_synchronize", "cip_plan_make", "cip_kernel_table", "cip_kernel_ft", "cip_scan",
+           "cip_ctx_synchronize", "cip_ctx_launches", "cip_plan_make", "cip_kernel_table", "cip_kernel_ft", "cip_scan",
            "cip_grid_accumulate", "cip_correct_image", "cip_invert", "cip_stokes_i", "cip_tile_bin",
            "cip_tile_fetch", "cip_tile_gather", "cip_tile_free"]
 
