@@ -140,11 +140,10 @@ __global__ void fill_i64_kernel(int64_t* p, int64_t n, int64_t v) {
 }
 
 // One warp per sorted run: expand into gridder-ready records.
-template <typename REC>
+template <typename R>
 __global__ void __launch_bounds__(256) records_kernel(DevInputs in, GridGeom g, const Run* __restrict__ runs_sorted,
                                                       const int64_t* __restrict__ len_sorted,
-                                                      const int64_t* __restrict__ visoff, int64_t nruns,
-                                                      REC* __restrict__ recs) {
+                                                      const int64_t* __restrict__ visoff, int64_t nruns, Recs<R> recs) {
   const int lane = threadIdx.x & 31;
   const int64_t i = ((int64_t)blockIdx.x * blockDim.x + threadIdx.x) >> 5;
   if (i >= nruns) return;
@@ -178,17 +177,16 @@ __global__ void __launch_bounds__(256) records_kernel(DevInputs in, GridGeom g, 
         re = t;
       }
     }
-    REC r;
     uint32_t i0r = (uint32_t)(s.i0 + kHalo - tu * kTile);
     uint32_t j0r = (uint32_t)(s.j0 + kHalo - tv * kTile);
     uint32_t p0r = (uint32_t)(s.p0 - win * g.win_step);
-    r.cell = i0r | (j0r << 5) | (p0r << 10);
-    r.fu = s.fu;
-    r.fv = s.fv;
-    r.fw = s.fw;
-    r.re = re;
-    r.im = im;
-    recs[out0 + k] = r;
+    const int64_t o = out0 + k;
+    recs.cell[o] = i0r | (j0r << 5) | (p0r << 10);
+    recs.fu[o] = s.fu;
+    recs.fv[o] = s.fv;
+    recs.fw[o] = s.fw;
+    recs.re[o] = (R)re;
+    recs.im[o] = (R)im;
   }
 }
 
@@ -307,14 +305,13 @@ cip_status run_binning(cip_ctx* ctx, const DevInputs& in, const GridGeom& g, int
   ctx->launches += 2;
 
   // --- records ---------------------------------------------------------------------
-  const size_t rec_size = fp64 ? sizeof(VisRec64) : sizeof(VisRec);
-  CIP_TRY(ctx->recs.ensure(rec_size * nrec));
+  CIP_TRY(ctx->recs.ensure(recs_bytes(nrec, fp64)));
   if (fp64)
-    records_kernel<VisRec64><<<nblk(nruns * 32, 256), 256, 0, st>>>(in, g, runs_sorted, len_sorted, visoff, nruns,
-                                                                   ctx->recs.as<VisRec64>());
+    records_kernel<double><<<nblk(nruns * 32, 256), 256, 0, st>>>(in, g, runs_sorted, len_sorted, visoff, nruns,
+                                                                 recs_view<double>(ctx->recs.p, nrec));
   else
-    records_kernel<VisRec><<<nblk(nruns * 32, 256), 256, 0, st>>>(in, g, runs_sorted, len_sorted, visoff, nruns,
-                                                                 ctx->recs.as<VisRec>());
+    records_kernel<float><<<nblk(nruns * 32, 256), 256, 0, st>>>(in, g, runs_sorted, len_sorted, visoff, nruns,
+                                                                recs_view<float>(ctx->recs.p, nrec));
   ctx->launches++;
   CIP_CHECK_CUDA(cudaGetLastError());
 

@@ -75,20 +75,33 @@ struct FftPlan {
   size_t work = 0;
 };
 
-// One visibility, ready for the gridder: written by the record kernel in (window, tile) order.
-// 24 bytes; `cell` packs the tile-relative origin of the support and flags:
-//   bits 0-4 i0 (u cell, 0..kTile-1), 5-9 j0, 10-13 first plane relative to the window start.
-struct __align__(8) VisRec {
-  uint32_t cell;
-  float fu, fv, fw;  // distance of the first cell / plane from the left edge of the support, in [0,1)
-  float re, im;      // weighted, conjugated-if-flipped, n-shift-rotated visibility
+// Gridder-ready visibilities, written by the record kernel in (window, tile) order as a structure of
+// arrays so that both the writer and the gridder's producer warp move whole 128-byte lines:
+//   cell  bits 0-4 i0 (u cell of the support origin inside the tile, 0..kTile-1), 5-9 j0,
+//         10-13 first plane relative to the window start
+//   fu, fv, fw  distance of the first cell / plane from the left edge of the support, in [0,1)
+//   re, im      weighted, conjugated-if-flipped, n-shift-rotated visibility (R = float or double)
+template <typename R>
+struct Recs {
+  uint32_t* cell;
+  float *fu, *fv, *fw;
+  R *re, *im;
 };
-
-struct __align__(16) VisRec64 {  // accumulate_fp64 variant (32 bytes)
-  uint32_t cell;
-  float fu, fv, fw;
-  double re, im;
-};
+inline size_t recs_pad(int64_t nrec) { return ((size_t)nrec + 31) & ~(size_t)31; }
+inline size_t recs_bytes(int64_t nrec, int fp64) { return recs_pad(nrec) * (16 + 2 * (fp64 ? 8 : 4)); }
+template <typename R>
+inline Recs<R> recs_view(void* base, int64_t nrec) {
+  const size_t n = recs_pad(nrec);
+  Recs<R> r;
+  char* p = static_cast<char*>(base);
+  r.re = reinterpret_cast<R*>(p); p += n * sizeof(R);
+  r.im = reinterpret_cast<R*>(p); p += n * sizeof(R);
+  r.cell = reinterpret_cast<uint32_t*>(p); p += n * 4;
+  r.fu = reinterpret_cast<float*>(p); p += n * 4;
+  r.fv = reinterpret_cast<float*>(p); p += n * 4;
+  r.fw = reinterpret_cast<float*>(p);
+  return r;
+}
 
 // A run of channels of one row that fall into the same (window, tile) bin.
 struct __align__(16) Run {
@@ -141,6 +154,8 @@ struct cip_ctx {
       run_visoff, flags, group_start, item_idx, items, win_item_start, cub_tmp, recs;
   // grids, fft, image
   cip::DevBuf grid, image, tables;
+  std::vector<double> tables_key;  // plan parameters the correction tables were built for
+  int tables_ncheb = 0;
   std::map<std::tuple<int, int, int, int>, cip::FftPlan> fft_plans;  // (nu, nv, batch, fp64)
   // tiling
   cip::DevBuf t_uvw, t_freq, t_vis;
@@ -183,8 +198,8 @@ struct BinResult {
 cip_status run_binning(cip_ctx* ctx, const DevInputs& in, const GridGeom& g, int fp64, BinResult* out);
 
 // Grid the items [item_begin, item_end) into `grid` (planes slot = plane - plane_base).
-cip_status run_gridder(cip_ctx* ctx, const GridGeom& g, int fp64, int64_t item_begin, int64_t item_end,
-                       void* grid, int plane_base, int nslots);
+cip_status run_gridder(cip_ctx* ctx, const GridGeom& g, int fp64, int64_t nrec_total, int64_t item_begin,
+                       int64_t item_end, void* grid, int plane_base, int nslots);
 cip_status run_fft(cip_ctx* ctx, void* grid, int nu, int nv, int batch, int fp64);
 cip_status run_wscreen(cip_ctx* ctx, const cip_plan& p, const void* grid, int plane_base, int nslots, void* image);
 cip_status run_correct(cip_ctx* ctx, const cip_plan& p, void* image, int row_begin, int row_end, double scale);

@@ -5,18 +5,19 @@
 // Design ("residue owner"): one CTA per work item = a slice of the records of one uv tile
 // (kTile x kTile support origins) and one window of kWin w planes.  The tile's sub-grid
 // (kSub x kSub cells x kWin planes) lives in shared memory.  Warp 0 (producer) streams the
-// 24-byte records with coalesced loads, evaluates the ES kernel separably (8 u-, 8 v-, 8 w-
-// weights per visibility) and hands batches of 32 visibilities to warp 1 (consumer) through a
-// two-stage shared-memory ring guarded by named barriers.  In the consumer, lane (a, b) owns the
-// grid cells with u index = a (mod 8) and v index = b or b+4 (mod 8): the support of ANY
-// visibility (W <= 8) holds exactly one cell of each residue class, so every lane always has
-// exactly one cell per class to update, no two lanes ever touch the same cell, and no atomics
-// or shuffles are needed.  The lane keeps its 2 cells x 8 planes in registers (packed f32x2
-// FMAs: FFMA2) while consecutive visibilities fall on the same cells -- along a run of channels
-// they move by a fraction of a cell -- and folds them into the shared sub-grid (plain,
-// conflict-free 128-bit read-modify-write; the row pitch kSub is odd) only when the support
-// origin moves.  The finished sub-grid is added to the global plane stack with vector
-// reductions (red.global.add.v4.f32), skipping empty cells.
+// structure-of-arrays records with coalesced loads, evaluates the ES kernel separably (8 u-, 8 v-,
+// 8 w-weights per visibility, one visibility per lane) and hands batches of 32 visibilities to
+// warp 1 (consumer) through a two-stage shared-memory ring guarded by mbarriers.  In the consumer,
+// lane (a, b) owns the grid cells with u index = a (mod 8) and v index = b or b+4 (mod 8): an
+// 8 x 8-cell register window that contains the support of the visibility (W <= 8) holds exactly one
+// cell of each residue class, so no two lanes ever touch the same cell and no atomics or shuffles are
+// needed.  The lane keeps its 2 cells x 8 planes in registers as packed pairs (FFMA2: fma.rn.f32x2)
+// while consecutive visibilities fall into the same register window -- the window origin is snapped
+// to a lattice of 9-W cells, and along a run of channels the support moves by a fraction of a cell
+// -- and folds them into the shared sub-grid (plain, conflict-free 128-bit read-modify-write; the
+// row pitch kSub is odd) only when the window moves.  The operands of visibility k+1 are loaded
+// while visibility k is accumulated.  The finished sub-grid is added to the global plane stack with
+// vector reductions (red.global.add.v4.f32), skipping empty cells.
 #include "geom.cuh"
 
 namespace cip {
@@ -26,38 +27,42 @@ namespace {
 constexpr int kStages = 2;
 constexpr int kGridThreads = 64;
 
-template <typename R> struct Cplx;
-template <> struct Cplx<float> { using type = float2; using cell4 = float4; };
-template <> struct Cplx<double> { using type = double2; };
+using u64 = unsigned long long;
 
-template <typename R>
-struct alignas(16) Stage {
-  float ku[kBatch][8];    // weight of u residue class r for visibility k (0 outside the support)
-  float kv[kBatch][8];    // v classes, stored as pairs: [2*b + s] = class b + 4*s
-  float kw[kBatch][16];   // the 8 plane weights, each duplicated (operand of the packed FMA)
-  typename Cplx<R>::type val[kBatch];
-  uint32_t info[kBatch];  // bits 0-4 i0, 5-9 j0, bit 31: support origin differs from the previous visibility
-};
+// ---- small PTX helpers ----------------------------------------------------------------
+__device__ __forceinline__ uint32_t smem_u32(const void* p) { return (uint32_t)__cvta_generic_to_shared(p); }
+__device__ __forceinline__ void mbar_init(uint64_t* bar, int count) {
+  asm volatile("mbarrier.init.shared::cta.b64 [%0], %1;" ::"r"(smem_u32(bar)), "r"(count) : "memory");
+}
+__device__ __forceinline__ void mbar_arrive(uint64_t* bar) {
+  asm volatile("mbarrier.arrive.shared::cta.b64 _, [%0];" ::"r"(smem_u32(bar)) : "memory");
+}
+__device__ __forceinline__ void mbar_wait(uint64_t* bar, uint32_t parity) {
+  uint32_t done;
+  const uint32_t a = smem_u32(bar);
+  do {
+    asm volatile(
+        "{\n .reg .pred p;\n mbarrier.try_wait.parity.shared::cta.b64 p, [%1], %2;\n selp.u32 %0, 1, 0, p;\n}"
+        : "=r"(done)
+        : "r"(a), "r"(parity)
+        : "memory");
+  } while (!done);
+}
 
-__device__ __forceinline__ void bar_sync(int id, int n) { asm volatile("bar.sync %0, %1;" ::"r"(id), "r"(n) : "memory"); }
-__device__ __forceinline__ void bar_arrive(int id, int n) { asm volatile("bar.arrive %0, %1;" ::"r"(id), "r"(n) : "memory"); }
-
-__device__ __forceinline__ unsigned long long pack2(float lo, float hi) {
-  unsigned long long r;
+__device__ __forceinline__ u64 pack2(float lo, float hi) {
+  u64 r;
   asm("mov.b64 %0, {%1, %2};" : "=l"(r) : "f"(lo), "f"(hi));
   return r;
 }
-__device__ __forceinline__ float2 unpack2(unsigned long long v) {
+__device__ __forceinline__ float2 unpack2(u64 v) {
   float2 r;
   asm("mov.b64 {%0, %1}, %2;" : "=f"(r.x), "=f"(r.y) : "l"(v));
   return r;
 }
 // d = a * b + d on two packed floats (FFMA2 on sm_100a)
-__device__ __forceinline__ void ffma2(unsigned long long& d, unsigned long long a, unsigned long long b) {
-  asm("fma.rn.f32x2 %0, %1, %2, %0;" : "+l"(d) : "l"(a), "l"(b));
-}
-__device__ __forceinline__ unsigned long long fmul2(unsigned long long a, unsigned long long b) {
-  unsigned long long d;
+__device__ __forceinline__ void ffma2(u64& d, u64 a, u64 b) { asm("fma.rn.f32x2 %0, %1, %2, %0;" : "+l"(d) : "l"(a), "l"(b)); }
+__device__ __forceinline__ u64 fmul2(u64 a, u64 b) {
+  u64 d;
   asm("mul.rn.f32x2 %0, %1, %2;" : "=l"(d) : "l"(a), "l"(b));
   return d;
 }
@@ -76,16 +81,53 @@ __device__ __forceinline__ void red_add_v4(float* addr, float a, float b, float 
   asm volatile("red.global.add.v4.f32 [%0], {%1, %2, %3, %4};" ::"l"(addr), "f"(a), "f"(b), "f"(c), "f"(d) : "memory");
 }
 
-// ---- producer -------------------------------------------------------------------------
-template <typename R, typename REC>
-__device__ __forceinline__ void produce(Stage<R>& st, const REC& rec, bool valid, int lane, uint32_t& carry,
-                                        const GridGeom& g, float bw2, float two_over_w) {
+// ---- producer -> consumer hand-over ------------------------------------------------------
+template <typename R> struct StageVal;
+template <> struct StageVal<float> { using type = float4; };    // (re, re, im, im)
+template <> struct StageVal<double> { using type = double2; };  // (re, im)
+
+template <typename R>
+struct alignas(16) Stage {
+  float2 ku[kBatch][8];   // (k, k): weight of u residue class r for visibility k (0 outside the support)
+  float2 kv[kBatch][4];   // (class b, class b + 4)
+  float2 kw[kBatch][8];   // (k, k): the 8 plane weights of the window
+  typename StageVal<R>::type val[kBatch];
+  uint32_t org[kBatch];   // register-window origin: bits 0-4 u cell, 5-9 v cell (sub-grid coordinates)
+  uint32_t moved;         // bit k: the window of visibility k differs from that of visibility k-1
+  uint32_t pad[3];
+};
+
+template <typename R>
+struct RecRegs {
+  uint32_t cell;
+  float fu, fv, fw;
+  R re, im;
+};
+
+template <typename R>
+__device__ __forceinline__ RecRegs<R> load_rec(const Recs<R>& recs, int64_t k, bool valid) {
+  RecRegs<R> r;
+  r.cell = valid ? __ldg(recs.cell + k) : 0u;
+  r.fu = valid ? __ldg(recs.fu + k) : 0.f;
+  r.fv = valid ? __ldg(recs.fv + k) : 0.f;
+  r.fw = valid ? __ldg(recs.fw + k) : 0.f;
+  r.re = valid ? __ldg(recs.re + k) : (R)0;
+  r.im = valid ? __ldg(recs.im + k) : (R)0;
+  return r;
+}
+
+template <typename R>
+__device__ __forceinline__ void produce(Stage<R>& st, const RecRegs<R>& rec, bool valid, int lane, uint32_t& carry,
+                                        const GridGeom& g, float bw2, float two_over_w, int snap) {
   const int W = g.W;
-  uint32_t cxy = valid ? (rec.cell & 0x3ffu) : carry;
+  const int i0 = rec.cell & 31, j0 = (rec.cell >> 5) & 31, p0 = (rec.cell >> 10) & 15;
+  // register window: origin snapped to a lattice of `snap` cells, so that nearby supports share it
+  const uint32_t wxy = (uint32_t)(i0 - i0 % snap) | ((uint32_t)(j0 - j0 % snap) << 5);
+  const uint32_t cxy = valid ? wxy : carry;
   uint32_t prev = __shfl_up_sync(0xffffffffu, cxy, 1);
   if (lane == 0) prev = carry;
   carry = __shfl_sync(0xffffffffu, cxy, 31);
-  const int i0 = cxy & 31, j0 = (cxy >> 5) & 31, p0 = (rec.cell >> 10) & 15;
+  const uint32_t moved = __ballot_sync(0xffffffffu, cxy != prev);
   float ku[8], kv[8], kw[8];
 #pragma unroll
   for (int r = 0; r < 8; ++r) {
@@ -102,72 +144,90 @@ __device__ __forceinline__ void produce(Stage<R>& st, const REC& rec, bool valid
     for (int r = 0; r < 8; ++r) kw[r] = r == 0 ? 1.0f : 0.0f;
   }
   float4* pu = reinterpret_cast<float4*>(st.ku[lane]);
-  pu[0] = make_float4(ku[0], ku[1], ku[2], ku[3]);
-  pu[1] = make_float4(ku[4], ku[5], ku[6], ku[7]);
+  float4* pw = reinterpret_cast<float4*>(st.kw[lane]);
+#pragma unroll
+  for (int q = 0; q < 4; ++q) {
+    pu[q] = make_float4(ku[2 * q], ku[2 * q], ku[2 * q + 1], ku[2 * q + 1]);
+    pw[q] = make_float4(kw[2 * q], kw[2 * q], kw[2 * q + 1], kw[2 * q + 1]);
+  }
   float4* pv = reinterpret_cast<float4*>(st.kv[lane]);
   pv[0] = make_float4(kv[0], kv[4], kv[1], kv[5]);
   pv[1] = make_float4(kv[2], kv[6], kv[3], kv[7]);
-  float4* pw = reinterpret_cast<float4*>(st.kw[lane]);
-  pw[0] = make_float4(kw[0], kw[0], kw[1], kw[1]);
-  pw[1] = make_float4(kw[2], kw[2], kw[3], kw[3]);
-  pw[2] = make_float4(kw[4], kw[4], kw[5], kw[5]);
-  pw[3] = make_float4(kw[6], kw[6], kw[7], kw[7]);
-  typename Cplx<R>::type v;
-  v.x = valid ? (R)rec.re : (R)0;
-  v.y = valid ? (R)rec.im : (R)0;
-  st.val[lane] = v;
-  st.info[lane] = cxy | (cxy != prev ? 0x80000000u : 0u);
+  const R re = valid ? rec.re : (R)0, im = valid ? rec.im : (R)0;
+  if constexpr (sizeof(R) == 4) st.val[lane] = make_float4(re, re, im, im);
+  else st.val[lane] = make_double2(re, im);
+  st.org[lane] = cxy;
+  if (lane == 0) st.moved = moved;
 }
 
 // ---- consumer -------------------------------------------------------------------------
+template <typename R> struct SubGrid;
+template <> struct SubGrid<float> { using cell = float4; static constexpr int ncell = 4 * kSub * kSub; };
+template <> struct SubGrid<double> { using cell = double2; static constexpr int ncell = 8 * kSub * kSub; };
+
 template <typename R> struct Acc;
 
+// float: accumulators are packed pairs over the lane's two cells: re[p] = (cell0, cell1), im[p] likewise
 template <>
 struct Acc<float> {
-  unsigned long long a[2][8];
+  struct Ops {
+    u64 ku, kv, rr, ii;
+    ulonglong2 kw[4];
+  };
+  u64 re[8], im[8];
   __device__ __forceinline__ void clear() {
 #pragma unroll
-    for (int s = 0; s < 2; ++s)
-#pragma unroll
-      for (int c = 0; c < 8; ++c) a[s][c] = 0ull;
+    for (int c = 0; c < 8; ++c) re[c] = im[c] = 0ull;
   }
-  // sub-grid cell = float4 {re(c), im(c), re(c+1), im(c+1)} for plane pair pp = c/2
-  __device__ __forceinline__ void fold(float4* sg, int i, int j0s, int j1s) {
-#pragma unroll
-    for (int s = 0; s < 2; ++s) {
-      int j = s ? j1s : j0s;
-#pragma unroll
-      for (int pp = 0; pp < 4; ++pp) {
-        float4* p = sg + ((pp * kSub + i) * kSub + j);
-        float4 v = *p;
-        float2 lo = unpack2(a[s][2 * pp]), hi = unpack2(a[s][2 * pp + 1]);
-        v.x += lo.x; v.y += lo.y; v.z += hi.x; v.w += hi.y;
-        *p = v;
-        a[s][2 * pp] = 0ull;
-        a[s][2 * pp + 1] = 0ull;
-      }
-    }
-  }
-  __device__ __forceinline__ void update(const Stage<float>& st, int k, int a8, int b4) {
-    float ku = st.ku[k][a8];
-    float2 kv = *reinterpret_cast<const float2*>(&st.kv[k][2 * b4]);
-    float2 val = st.val[k];
-    float w0 = ku * kv.x, w1 = ku * kv.y;
-    unsigned long long t0 = pack2(val.x * w0, val.y * w0), t1 = pack2(val.x * w1, val.y * w1);
+  static __device__ __forceinline__ Ops load(const Stage<float>& st, int k, int a8, int b4) {
+    Ops o;
+    o.ku = *reinterpret_cast<const u64*>(&st.ku[k][a8]);
+    o.kv = *reinterpret_cast<const u64*>(&st.kv[k][b4]);
+    const ulonglong2 v = *reinterpret_cast<const ulonglong2*>(&st.val[k]);
+    o.rr = v.x;
+    o.ii = v.y;
     const ulonglong2* kw = reinterpret_cast<const ulonglong2*>(st.kw[k]);
 #pragma unroll
+    for (int q = 0; q < 4; ++q) o.kw[q] = kw[q];
+    return o;
+  }
+  __device__ __forceinline__ void update(const Ops& o) {
+    const u64 w = fmul2(o.ku, o.kv);  // (ku kv0, ku kv1)
+    const u64 tr = fmul2(o.rr, w), ti = fmul2(o.ii, w);
+#pragma unroll
     for (int q = 0; q < 4; ++q) {
-      ulonglong2 w = kw[q];
-      ffma2(a[0][2 * q], t0, w.x);
-      ffma2(a[0][2 * q + 1], t0, w.y);
-      ffma2(a[1][2 * q], t1, w.x);
-      ffma2(a[1][2 * q + 1], t1, w.y);
+      ffma2(re[2 * q], tr, o.kw[q].x);
+      ffma2(im[2 * q], ti, o.kw[q].x);
+      ffma2(re[2 * q + 1], tr, o.kw[q].y);
+      ffma2(im[2 * q + 1], ti, o.kw[q].y);
     }
+  }
+  // sub-grid cell = float4 {re(2pp), im(2pp), re(2pp+1), im(2pp+1)} for plane pair pp
+  __device__ __forceinline__ void fold(float4* sg, int i, int j0s, int j1s) {
+#pragma unroll
+    for (int pp = 0; pp < 4; ++pp) {
+      const float2 r0 = unpack2(re[2 * pp]), i0 = unpack2(im[2 * pp]);
+      const float2 r1 = unpack2(re[2 * pp + 1]), i1 = unpack2(im[2 * pp + 1]);
+      float4* p0 = sg + ((pp * kSub + i) * kSub + j0s);
+      float4* p1 = sg + ((pp * kSub + i) * kSub + j1s);
+      float4 v0 = *p0, v1 = *p1;
+      v0.x += r0.x; v0.y += i0.x; v0.z += r1.x; v0.w += i1.x;
+      v1.x += r0.y; v1.y += i0.y; v1.z += r1.y; v1.w += i1.y;
+      *p0 = v0;
+      *p1 = v1;
+    }
+    clear();
   }
 };
 
 template <>
 struct Acc<double> {
+  struct Ops {
+    float ku;
+    float2 kv;
+    double2 val;
+    float kw[8];
+  };
   double2 a[2][8];
   __device__ __forceinline__ void clear() {
 #pragma unroll
@@ -175,11 +235,32 @@ struct Acc<double> {
 #pragma unroll
       for (int c = 0; c < 8; ++c) a[s][c] = make_double2(0.0, 0.0);
   }
+  static __device__ __forceinline__ Ops load(const Stage<double>& st, int k, int a8, int b4) {
+    Ops o;
+    o.ku = st.ku[k][a8].x;
+    o.kv = st.kv[k][b4];
+    o.val = st.val[k];
+#pragma unroll
+    for (int c = 0; c < 8; ++c) o.kw[c] = st.kw[k][c].x;
+    return o;
+  }
+  __device__ __forceinline__ void update(const Ops& o) {
+    const double w0 = (double)o.ku * (double)o.kv.x, w1 = (double)o.ku * (double)o.kv.y;
+    const double tr0 = o.val.x * w0, ti0 = o.val.y * w0, tr1 = o.val.x * w1, ti1 = o.val.y * w1;
+#pragma unroll
+    for (int c = 0; c < 8; ++c) {
+      const double w = (double)o.kw[c];
+      a[0][c].x = fma(tr0, w, a[0][c].x);
+      a[0][c].y = fma(ti0, w, a[0][c].y);
+      a[1][c].x = fma(tr1, w, a[1][c].x);
+      a[1][c].y = fma(ti1, w, a[1][c].y);
+    }
+  }
   // sub-grid cell = double2 per plane: layout [plane][i][j]
   __device__ __forceinline__ void fold(double2* sg, int i, int j0s, int j1s) {
 #pragma unroll
     for (int s = 0; s < 2; ++s) {
-      int j = s ? j1s : j0s;
+      const int j = s ? j1s : j0s;
 #pragma unroll
       for (int c = 0; c < 8; ++c) {
         double2* p = sg + ((c * kSub + i) * kSub + j);
@@ -187,46 +268,42 @@ struct Acc<double> {
         v.x += a[s][c].x;
         v.y += a[s][c].y;
         *p = v;
-        a[s][c] = make_double2(0.0, 0.0);
       }
     }
-  }
-  __device__ __forceinline__ void update(const Stage<double>& st, int k, int a8, int b4) {
-    float ku = st.ku[k][a8];
-    float2 kv = *reinterpret_cast<const float2*>(&st.kv[k][2 * b4]);
-    double2 val = st.val[k];
-    double w0 = (double)ku * (double)kv.x, w1 = (double)ku * (double)kv.y;
-    double tr0 = val.x * w0, ti0 = val.y * w0, tr1 = val.x * w1, ti1 = val.y * w1;
-#pragma unroll
-    for (int c = 0; c < 8; ++c) {
-      double w = (double)st.kw[k][2 * c];
-      a[0][c].x = fma(tr0, w, a[0][c].x);
-      a[0][c].y = fma(ti0, w, a[0][c].y);
-      a[1][c].x = fma(tr1, w, a[1][c].x);
-      a[1][c].y = fma(ti1, w, a[1][c].y);
-    }
+    clear();
   }
 };
 
-template <typename R> struct SubGrid;
-template <> struct SubGrid<float> { using cell = float4; static constexpr int ncell = 4 * kSub * kSub; };
-template <> struct SubGrid<double> { using cell = double2; static constexpr int ncell = 8 * kSub * kSub; };
+template <typename R>
+constexpr size_t grid_smem_bytes() {
+  return sizeof(typename SubGrid<R>::cell) * SubGrid<R>::ncell + sizeof(Stage<R>) * kStages + 2 * kStages * sizeof(uint64_t);
+}
 
 // ---- the kernel -----------------------------------------------------------------------
-template <typename R, typename REC>
+template <typename R>
 __global__ void __launch_bounds__(kGridThreads) grid_kernel(const Item* __restrict__ items, int64_t item_base,
-                                                            const REC* __restrict__ recs, GridGeom g,
-                                                            R* __restrict__ grid, int plane_base, int nslots) {
+                                                            Recs<R> recs, GridGeom g, R* __restrict__ grid,
+                                                            int plane_base, int nslots) {
   using Cell = typename SubGrid<R>::cell;
   extern __shared__ __align__(16) unsigned char smem_raw[];
   Cell* sg = reinterpret_cast<Cell*>(smem_raw);
   Stage<R>* stages = reinterpret_cast<Stage<R>*>(smem_raw + sizeof(Cell) * SubGrid<R>::ncell);
+  uint64_t* full = reinterpret_cast<uint64_t*>(stages + kStages);  // [kStages] producer -> consumer
+  uint64_t* empty = full + kStages;                                 // [kStages] consumer -> producer
 
   const Item item = items[item_base + blockIdx.x];
   const int tid = threadIdx.x, lane = tid & 31, warp = tid >> 5;
   const int nrec = item.nrec;
   const int nb = (nrec + kBatch - 1) / kBatch;
 
+  if (tid == 0) {
+#pragma unroll
+    for (int s = 0; s < kStages; ++s) {
+      mbar_init(&full[s], 32);
+      mbar_init(&empty[s], 32);
+    }
+    asm volatile("fence.mbarrier_init.release.cluster;" ::: "memory");
+  }
   {  // zero the sub-grid
     Cell z;
     memset(&z, 0, sizeof(z));
@@ -238,21 +315,19 @@ __global__ void __launch_bounds__(kGridThreads) grid_kernel(const Item* __restri
     // ---------------- producer ----------------
     const float bw2 = g.beta_w * 1.4426950408889634f;
     const float two_over_w = 2.0f / (float)g.W;
-    const REC* src = recs + item.rec_begin;
+    const int snap = 9 - g.W;  // windows of 8 cells hold the supports of `snap` consecutive origins
+    const int64_t base = item.rec_begin;
     uint32_t carry = 0xffffffffu;
-    REC cur;
     bool cur_valid = lane < nrec;
-    if (cur_valid) cur = src[lane]; else memset(&cur, 0, sizeof(cur));
+    RecRegs<R> cur = load_rec(recs, base + lane, cur_valid);
     for (int b = 0; b < nb; ++b) {
-      const int s = b & 1;
-      REC nxt;
-      int kn = (b + 1) * kBatch + lane;
-      bool nxt_valid = kn < nrec;
-      if (nxt_valid) nxt = src[kn]; else memset(&nxt, 0, sizeof(nxt));
-      if (b >= kStages) bar_sync(3 + s, kGridThreads);  // wait until the consumer released stage s
-      produce<R, REC>(stages[s], cur, cur_valid, lane, carry, g, bw2, two_over_w);
-      __threadfence_block();
-      bar_arrive(1 + s, kGridThreads);
+      const int s = b % kStages;
+      const int kn = (b + 1) * kBatch + lane;
+      const bool nxt_valid = kn < nrec;
+      RecRegs<R> nxt = load_rec(recs, base + kn, nxt_valid);
+      if (b >= kStages) mbar_wait(&empty[s], ((b / kStages) - 1) & 1);  // the consumer released stage s
+      produce<R>(stages[s], cur, cur_valid, lane, carry, g, bw2, two_over_w, snap);
+      mbar_arrive(&full[s]);
       cur = nxt;
       cur_valid = nxt_valid;
     }
@@ -263,23 +338,27 @@ __global__ void __launch_bounds__(kGridThreads) grid_kernel(const Item* __restri
     acc.clear();
     int ci = a8, cj0 = b4, cj1 = b4 + 4;  // current cells of this lane (sub-grid coordinates)
     for (int b = 0; b < nb; ++b) {
-      const int s = b & 1;
-      bar_sync(1 + s, kGridThreads);
+      const int s = b % kStages;
+      mbar_wait(&full[s], (b / kStages) & 1);
       const Stage<R>& st = stages[s];
       const int n = min(kBatch, nrec - b * kBatch);
+      const uint32_t moved = st.moved;
+      typename Acc<R>::Ops cur = Acc<R>::load(st, 0, a8, b4);
 #pragma unroll 4
       for (int k = 0; k < n; ++k) {
-        const uint32_t info = st.info[k];
-        if (info & 0x80000000u) {  // warp-uniform: the support origin moved
+        const typename Acc<R>::Ops nxt = Acc<R>::load(st, min(k + 1, kBatch - 1), a8, b4);
+        if ((moved >> k) & 1u) {  // warp-uniform: the register window moved
           acc.fold(sg, ci, cj0, cj1);
-          const int i0 = info & 31, j0 = (info >> 5) & 31;
-          ci = i0 + ((a8 - i0) & 7);
-          cj0 = j0 + ((b4 - j0) & 7);
-          cj1 = j0 + ((b4 + 4 - j0) & 7);
+          const uint32_t o = st.org[k];
+          const int wi = o & 31, wj = (o >> 5) & 31;
+          ci = wi + ((a8 - wi) & 7);
+          cj0 = wj + ((b4 - wj) & 7);
+          cj1 = wj + ((b4 + 4 - wj) & 7);
         }
-        acc.update(st, k, a8, b4);
+        acc.update(cur);
+        cur = nxt;
       }
-      if (b + kStages < nb) bar_arrive(3 + s, kGridThreads);
+      mbar_arrive(&empty[s]);
     }
     acc.fold(sg, ci, cj0, cj1);
   }
@@ -343,15 +422,15 @@ __global__ void __launch_bounds__(kGridThreads) grid_kernel(const Item* __restri
 }
 
 // Wide supports (W > 8, only reached for very small epsilon): plain scatter with global atomics.
-template <typename R, typename REC>
+template <typename R>
 __global__ void __launch_bounds__(128) grid_wide_kernel(const Item* __restrict__ items, int64_t item_base,
-                                                        const REC* __restrict__ recs, GridGeom g, R* __restrict__ grid,
+                                                        Recs<R> recs, GridGeom g, R* __restrict__ grid,
                                                         int plane_base, int nslots) {
   const Item item = items[item_base + blockIdx.x];
   const int W = g.W;
   const int su0 = item.tu * kTile - kHalo + g.nu / 2, sv0 = item.tv * kTile - kHalo + g.nv / 2;
   for (int k = threadIdx.x; k < item.nrec; k += blockDim.x) {
-    const REC rec = recs[item.rec_begin + k];
+    const RecRegs<R> rec = load_rec(recs, item.rec_begin + k, true);
     if (rec.re == 0 && rec.im == 0) continue;
     const int i0 = rec.cell & 31, j0 = (rec.cell >> 5) & 31, p0 = rec.cell >> 10;
     float kv[kMaxSupport];
@@ -377,23 +456,25 @@ __global__ void __launch_bounds__(128) grid_wide_kernel(const Item* __restrict__
   }
 }
 
-template <typename R, typename REC>
-cip_status launch(cip_ctx* ctx, const GridGeom& g, int64_t item_begin, int64_t item_end, void* grid, int plane_base,
-                  int nslots) {
+template <typename R>
+cip_status launch(cip_ctx* ctx, const GridGeom& g, int64_t nrec_total, int64_t item_begin, int64_t item_end,
+                  void* grid, int plane_base, int nslots) {
   const Item* items = ctx->items.as<Item>();
-  const REC* recs = ctx->recs.as<REC>();
+  const Recs<R> recs = recs_view<R>(ctx->recs.p, nrec_total);
   const int64_t n = item_end - item_begin;
   if (n <= 0) return CIP_OK;
   CIP_REQUIRE(n < ((int64_t)1 << 31), "too many work items");
   if (g.W <= kFastSupport) {
-    size_t smem = sizeof(typename SubGrid<R>::cell) * SubGrid<R>::ncell + sizeof(Stage<R>) * kStages;
-    auto kern = grid_kernel<R, REC>;
+    constexpr size_t smem = grid_smem_bytes<R>();
+    auto kern = grid_kernel<R>;
     CIP_CHECK_CUDA(cudaFuncSetAttribute(kern, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem));
+    CIP_CHECK_CUDA(cudaFuncSetAttribute(kern, cudaFuncAttributePreferredSharedMemoryCarveout,
+                                        (int)cudaSharedmemCarveoutMaxShared));
     kern<<<(unsigned)n, kGridThreads, smem, ctx->stream>>>(items, item_begin, recs, g, static_cast<R*>(grid), plane_base,
                                                           nslots);
   } else {
-    grid_wide_kernel<R, REC><<<(unsigned)n, 128, 0, ctx->stream>>>(items, item_begin, recs, g, static_cast<R*>(grid),
-                                                                   plane_base, nslots);
+    grid_wide_kernel<R><<<(unsigned)n, 128, 0, ctx->stream>>>(items, item_begin, recs, g, static_cast<R*>(grid),
+                                                              plane_base, nslots);
   }
   ctx->launches++;
   CIP_CHECK_CUDA(cudaGetLastError());
@@ -402,10 +483,10 @@ cip_status launch(cip_ctx* ctx, const GridGeom& g, int64_t item_begin, int64_t i
 
 }  // namespace
 
-cip_status run_gridder(cip_ctx* ctx, const GridGeom& g, int fp64, int64_t item_begin, int64_t item_end, void* grid,
-                       int plane_base, int nslots) {
-  if (fp64) return launch<double, VisRec64>(ctx, g, item_begin, item_end, grid, plane_base, nslots);
-  return launch<float, VisRec>(ctx, g, item_begin, item_end, grid, plane_base, nslots);
+cip_status run_gridder(cip_ctx* ctx, const GridGeom& g, int fp64, int64_t nrec_total, int64_t item_begin,
+                       int64_t item_end, void* grid, int plane_base, int nslots) {
+  if (fp64) return launch<double>(ctx, g, nrec_total, item_begin, item_end, grid, plane_base, nslots);
+  return launch<float>(ctx, g, nrec_total, item_begin, item_end, grid, plane_base, nslots);
 }
 
 }  // namespace cip

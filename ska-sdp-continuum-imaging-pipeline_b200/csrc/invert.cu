@@ -100,7 +100,7 @@ static cip_status grid_accumulate_staged(cip_ctx* ctx, const DevInputs& in, cip_
       CIP_CHECK_CUDA(cudaMemsetAsync(ctx->grid.p, 0, plane_bytes * used, ctx->stream));
       tm.stop(rep ? &rep->ms_zero : &dummy);
       tm.start();
-      CIP_TRY(run_gridder(ctx, g, fp64, it0, it1, ctx->grid.p, pb, used));
+      CIP_TRY(run_gridder(ctx, g, fp64, bins.nrec, it0, it1, ctx->grid.p, pb, used));
       tm.stop(rep ? &rep->ms_grid : &dummy);
       tm.start();
       CIP_TRY(run_fft(ctx, ctx->grid.p, plan->nu, plan->nv, used, fp64));

@@ -1,0 +1,116 @@
+"""The CPU oracle against the golden vectors produced by the reference's own code
+(tools/make_golden.py) and against itself (w-stacking restatement vs float64 DFT)."""
+import numpy as np
+import pytest
+
+from oracle import dft, partition, plan as oplan, stokes, tiling, wstack
+
+from conftest import random_problem
+
+TILING_CASES = ["meerkat_l", "small_tiles", "one_channel", "descending_freq", "half_integers"]
+
+
+@pytest.mark.parametrize("case", TILING_CASES)
+def test_tiling_oracle_matches_reference_golden(golden, case):
+    g = golden(f"tiling_{case}")
+    got = tiling.tile_mapping_arrays(g["uvw"], tuple(g["tile_size"]), g["freq"], row_offset=int(g["row_offset"]))
+    for name, a in zip(("coords", "offsets", "irow", "chan_start", "chan_stop"), got):
+        assert np.array_equal(a, g[name]), name
+
+
+@pytest.mark.parametrize("case", TILING_CASES)
+def test_tiling_oracle_gather_matches_reference_golden(golden, case):
+    g = golden(f"tiling_{case}")
+    off = int(g["row_offset"])
+    uvw, freq = g["uvw"], g["freq"]
+    rng = np.random.default_rng(int(g["vis_seed"]))
+    vis = (rng.normal(size=(len(uvw), len(freq))) + 1j * rng.normal(size=(len(uvw), len(freq)))).astype(np.complex64)
+    mapping = tiling.tile_mapping(uvw, tuple(g["tile_size"]), freq, row_offset=off)
+    for t, key in enumerate(list(mapping)[: int(g["n_gather_tiles"])]):
+        slices = [(r - off, a, b) for r, a, b in mapping[key]]
+        t_uvw, t_vis, t_a, t_b = tiling.gather_tile(vis, uvw, slices)
+        assert np.array_equal(t_uvw, g[f"tile{t}_uvw"])
+        assert np.array_equal(t_vis, g[f"tile{t}_vis"])
+        assert np.array_equal(t_a, g[f"tile{t}_start"]) and np.array_equal(t_b, g[f"tile{t}_stop"])
+
+
+def test_tiling_every_sample_covered_exactly_once():
+    # the property the reference tests (tests/uvw_tiling/test_uvw_tiling_plan.py:7-32)
+    rng = np.random.default_rng(0)
+    uvw = rng.normal(size=(500, 3)) * np.array([4000, 4000, 300.0])
+    freq = 856e6 + np.arange(256) * 214e6 / 256
+    mapping = tiling.tile_mapping(uvw, (3000.0, 3000.0, 6000.0), freq)
+    cover = np.zeros((500, 256), dtype=int)
+    for slices in mapping.values():
+        for r, a, b in slices:
+            cover[r, a:b] += 1
+    assert np.all(cover == 1)
+
+
+def test_stokes_oracle_matches_reference_golden(golden):
+    g = golden("stokes_small")
+    v, f, w = stokes.stokes_i(g["vis4"], g["flags4"], g["weights4"])
+    assert v.dtype == g["vis_i"].dtype and np.array_equal(v, g["vis_i"])
+    assert np.array_equal(f, g["flags_i"])
+    assert w.dtype == g["weights_i"].dtype and np.array_equal(w, g["weights_i"])
+    e = stokes.effective_weights(f, w)
+    assert np.array_equal(e, g["effw"]) and e.sum() == g["effw_sum"]
+    integ = stokes.integrate_weighted_images(list(zip(g["images"], g["image_weights"])))
+    assert np.array_equal(integ, g["integrated"])
+
+
+def test_partition_oracle_matches_reference_golden(golden):
+    g = golden("partition")
+    for key, want in g.items():
+        _, a, b, k = key.split("_")
+        assert np.array_equal(np.array(partition.chunk_bounds(int(a), int(b), int(k))), want), key
+    # the reference's own golden numbers (tests/test_measurement_set_partition_indices.py:51-61)
+    assert partition.chunk_bounds(0, 74214, 5) == [(0, 14843), (14843, 29686), (29686, 44529), (44529, 59372),
+                                                    (59372, 74214)]
+    with pytest.raises(ValueError):
+        partition.chunk_bounds(0, 4, 5)
+
+
+@pytest.mark.parametrize("fp64,sigma,W,tol", [(True, 2.0, 8, 1e-6), (False, 1.5, 7, 5e-5), (True, 1.5, 10, 1e-6)])
+def test_wstack_oracle_reproduces_dft(fp64, sigma, W, tol):
+    uvw, freq, vis, wgt, nx, px = random_problem(nrow=600, nchan=4, nx=64)
+    ref = dft.dft_dirty(uvw, freq, vis, wgt, nx, nx, px, px)
+    img = wstack.ms2dirty(uvw, freq, vis, wgt, nx, nx, px, px, 1e-4, fp64=fp64, sigma=sigma, W=W)
+    assert dft.rel_rms(img, ref) < tol
+
+
+def test_wstack_oracle_default_plan_meets_epsilon():
+    uvw, freq, vis, wgt, nx, px = random_problem(nrow=800, nchan=4, nx=96, wscale=300.0, uvscale=40.0)
+    ref = dft.dft_dirty(uvw, freq, vis, wgt, nx, nx, px, px)
+    for eps in (1e-3, 1e-4):
+        img = wstack.ms2dirty(uvw, freq, vis, wgt, nx, nx, px, px, eps)
+        assert dft.rel_rms(img, ref) < eps
+
+
+def test_dft_oracle_point_source_and_sampled_pixels():
+    # a unit point source at pixel (40, 20) gives D = sum of weights there (times 1/n)
+    nx, px = 64, 1e-4
+    rng = np.random.default_rng(3)
+    uvw = rng.normal(size=(300, 3)) * np.array([500.0, 500.0, 50.0])
+    freq = np.array([1.0e9, 1.1e9])
+    l, m = (40 - 32) * px, (20 - 32) * px
+    nm1 = -(l * l + m * m) / (np.sqrt(1 - l * l - m * m) + 1)
+    ph = (uvw[:, 0] * l + uvw[:, 1] * m - uvw[:, 2] * nm1)[:, None] * freq[None, :] / 299792458.0
+    vis = np.exp(-2j * np.pi * ph).astype(np.complex64)
+    wgt = np.ones(vis.shape, dtype=np.float32)
+    img = dft.dft_dirty(uvw, freq, vis, wgt, nx, nx, px, px)
+    assert abs(img[40, 20] * (1 + nm1) - vis.size) < 1e-2
+    assert img[40, 20] == img.max()
+    pix = np.array([40 * nx + 20, 5, 777])
+    sub = dft.dft_dirty(uvw, freq, vis, wgt, nx, nx, px, px, pixels=pix)
+    assert np.allclose(sub, img.reshape(-1)[pix], rtol=1e-12, atol=1e-9)
+
+
+def test_plan_oracle_basic_properties():
+    p = oplan.make_plan(1024, 1024, 1e-5, 1e-5, 1e-4, 0.0, 1000.0, 10 ** 6)
+    assert p.nu >= 1024 * p.sigma - 1 and p.nu % 2 == 0
+    assert oplan.good_size(p.nu) == p.nu
+    assert p.nplanes == int(np.floor(1000.0 / p.dw + p.W))
+    assert oplan.ES_TABLE[p.sigma][p.W][1] <= 1e-4 / 3
+    # planes are centred on the data range
+    assert abs((p.w0 + 0.5 * (p.nplanes - 1) * p.dw) - 500.0) < 1e-9
