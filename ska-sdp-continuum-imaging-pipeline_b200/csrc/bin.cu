@@ -23,42 +23,97 @@ struct MaxOp {
   __device__ __forceinline__ int64_t operator()(int64_t a, int64_t b) const { return a > b ? a : b; }
 };
 
-// pass 0: count runs per row; pass 1: write them at row_off[row].
-template <int PASS>
+// One warp per row, lanes stride the channels; a run is a maximal stretch of channels of one row with
+// the same (window, tile) bin AND the same register-window lattice position inside the tile, so that
+// after the sort all records that share a register window of the gridder's consumer are contiguous.
+//   PASS 0: count the runs of each row.
+//   PASS 1: write the runs (input order) at row_off[row] and their sort keys.
+//   PASS 2: after the sort, expand the samples into gridder-ready records at their sorted positions
+//           (outpos[r] = first record of input-order run r); all float64 coordinate arithmetic of the
+//           gridder happens here.  Reads are row-contiguous, writes contiguous per run.
+template <int PASS, typename R>
 __global__ void __launch_bounds__(256) runs_kernel(DevInputs in, GridGeom g, int64_t* __restrict__ row_nruns,
                                                    const int64_t* __restrict__ row_off, Run* __restrict__ runs,
-                                                   uint64_t* __restrict__ keys) {
+                                                   uint64_t* __restrict__ keys, const int64_t* __restrict__ outpos,
+                                                   Rec<R>* __restrict__ recs) {
   const int lane = threadIdx.x & 31;
   const int64_t row = ((int64_t)blockIdx.x * blockDim.x + threadIdx.x) >> 5;
   if (row >= in.nrow) return;
   const double um = in.uvw[3 * row], vm = in.uvw[3 * row + 1], wm = in.uvw[3 * row + 2];
   uint64_t carry = ~0ull;
   int64_t n = 0;
+  int carry_ch0 = 0;
   const int64_t base = PASS ? row_off[row] : 0;
   for (int64_t c0 = 0; c0 < in.nchan; c0 += 32) {
-    int64_t c = c0 + lane;
+    const int64_t c = c0 + lane;
+    const bool valid = c < in.nchan;
     uint64_t key = ~0ull;
-    if (c < in.nchan) {
-      SampleGeom s = sample_geom(g, um, vm, wm, in.freq[c] / kSpeedOfLight);
-      key = bin_key(g, s);
+    SampleGeom s;
+    if (valid) {
+      s = sample_geom(g, um, vm, wm, in.freq[c] / kSpeedOfLight);
+      key = (bin_key(g, s) << kSubKeyBits) | window_lattice(g, s);
     }
     uint64_t prev = __shfl_up_sync(0xffffffffu, key, 1);
     if (lane == 0) prev = carry;
-    bool start = c < in.nchan && key != prev;
-    unsigned m = __ballot_sync(0xffffffffu, start);
-    if (PASS && start) {
-      int64_t pos = base + n + __popc(m & ((1u << lane) - 1));
+    const bool start = valid && key != prev;
+    const unsigned m = __ballot_sync(0xffffffffu, start);
+    if (PASS == 1 && start) {
+      const int64_t pos = base + n + __popc(m & ((1u << lane) - 1));
       Run r;
-      r.key = key;
+      r.key = key >> kSubKeyBits;
       r.row = (int32_t)row;
       r.ch0 = (int32_t)c;
       runs[pos] = r;
       keys[pos] = key;
     }
+    if (PASS == 2) {
+      const unsigned upto = m & (0xffffffffu >> (31 - lane));  // starts at or before this lane
+      const int64_t r = base + n + __popc(upto) - 1;           // input-order index of this sample's run
+      const int ch0 = upto ? (int)c0 + (31 - __clz(upto)) : carry_ch0;
+      if (valid) {
+        const float2 v = in.vis[row * in.vstride + c];
+        float wgt;
+        const bool act = sample_active(v, in.wgt, in.mask, row * in.wstride + c, &wgt);
+        R re = 0, im = 0;
+        if (act) {
+          re = (R)v.x * (R)wgt;
+          im = (R)v.y * (R)wgt;
+          if (s.flip) im = -im;
+          if (g.do_wstacking && g.nshift != 0.0) {  // V' = V exp(+2 pi i w s); phase reduced in float64
+            double ph = s.w * g.nshift;
+            ph -= rint(ph);
+            R sn, cs;
+            if constexpr (sizeof(R) == 4) sincospif(2.0f * (float)ph, &sn, &cs);
+            else sincospi(2.0 * ph, &sn, &cs);
+            const R t = re * cs - im * sn;
+            im = re * sn + im * cs;
+            re = t;
+          }
+        }
+        const int tu = (s.i0 + kHalo) / kTile, tv = (s.j0 + kHalo) / kTile;
+        const int win = g.W <= kFastSupport ? s.p0 / g.win_step : 0;
+        const uint32_t i0r = (uint32_t)(s.i0 + kHalo - tu * kTile);
+        const uint32_t j0r = (uint32_t)(s.j0 + kHalo - tv * kTile);
+        const uint32_t p0r = (uint32_t)(s.p0 - win * g.win_step);
+        Rec<R> rec;
+        rec.cell = i0r | (j0r << 5) | (p0r << 10);
+        rec.fu = s.fu;
+        rec.fv = s.fv;
+        rec.fw = s.fw;
+        rec.re = re;
+        rec.im = im;
+        if constexpr (sizeof(R) == 4) rec.pad[0] = rec.pad[1] = 0.f;
+        float4* dst = reinterpret_cast<float4*>(recs + outpos[r] + ((int)c - ch0));
+        const float4* src = reinterpret_cast<const float4*>(&rec);
+        dst[0] = src[0];
+        dst[1] = src[1];
+      }
+      if (m) carry_ch0 = (int)c0 + (31 - __clz(m));
+    }
     n += __popc(m);
     carry = __shfl_sync(0xffffffffu, key, 31);
   }
-  if (!PASS && lane == 0) row_nruns[row] = n;
+  if (PASS == 0 && lane == 0) row_nruns[row] = n;
 }
 
 __global__ void run_len_kernel(const Run* __restrict__ runs, int64_t nruns, int32_t nchan, uint32_t* __restrict__ idx,
@@ -85,15 +140,16 @@ __global__ void gather_kernel(const Run* __restrict__ runs, const int32_t* __res
   uint32_t r = idx[i];
   runs_sorted[i] = runs[r];
   len_sorted[i] = len[r];
-  start_flag[i] = (i == 0 || keys_sorted[i] != keys_sorted[i - 1]) ? 1 : 0;
+  start_flag[i] = (i == 0 || (keys_sorted[i] >> kSubKeyBits) != (keys_sorted[i - 1] >> kSubKeyBits)) ? 1 : 0;
 }
 
 // group g = g-th distinct key; first run of each group, number of items of each group
 __global__ void groups_kernel(const int64_t* __restrict__ start_flag, const int64_t* __restrict__ group_of /*inclusive scan*/,
-                              const int64_t* __restrict__ visoff, int64_t nruns, int64_t nrec,
-                              int64_t* __restrict__ group_first) {
+                              const int64_t* __restrict__ visoff, const uint32_t* __restrict__ idx, int64_t nruns,
+                              int64_t nrec, int64_t* __restrict__ group_first, int64_t* __restrict__ outpos) {
   int64_t i = (int64_t)blockIdx.x * blockDim.x + threadIdx.x;
   if (i >= nruns) return;
+  outpos[idx[i]] = visoff[i];  // first record of input-order run idx[i]
   if (start_flag[i]) group_first[group_of[i] - 1] = i;
 }
 
@@ -139,57 +195,6 @@ __global__ void fill_i64_kernel(int64_t* p, int64_t n, int64_t v) {
   if (i < n) p[i] = v;
 }
 
-// One warp per sorted run: expand into gridder-ready records.
-template <typename R>
-__global__ void __launch_bounds__(256) records_kernel(DevInputs in, GridGeom g, const Run* __restrict__ runs_sorted,
-                                                      const int64_t* __restrict__ len_sorted,
-                                                      const int64_t* __restrict__ visoff, int64_t nruns, Recs<R> recs) {
-  const int lane = threadIdx.x & 31;
-  const int64_t i = ((int64_t)blockIdx.x * blockDim.x + threadIdx.x) >> 5;
-  if (i >= nruns) return;
-  const Run run = runs_sorted[i];
-  const int len = (int)len_sorted[i];
-  const int64_t out0 = visoff[i];
-  const int64_t row = run.row;
-  const double um = in.uvw[3 * row], vm = in.uvw[3 * row + 1], wm = in.uvw[3 * row + 2];
-  const int tv = (int)(run.key % g.ntv);
-  const uint64_t q = run.key / g.ntv;
-  const int tu = (int)(q % g.ntu);
-  const int win = (int)(q / g.ntu);
-  for (int k = lane; k < len; k += 32) {
-    int64_t c = run.ch0 + k;
-    SampleGeom s = sample_geom(g, um, vm, wm, in.freq[c] / kSpeedOfLight);
-    float2 v = in.vis[row * in.vstride + c];
-    float wgt;
-    bool act = sample_active(v, in.wgt, in.mask, row * in.wstride + c, &wgt);
-    double re = 0.0, im = 0.0;
-    if (act) {
-      re = (double)v.x * wgt;
-      im = (double)v.y * wgt;
-      if (s.flip) im = -im;
-      if (g.do_wstacking && g.nshift != 0.0) {  // V' = V exp(+2 pi i w s)
-        double ph = s.w * g.nshift;
-        ph -= rint(ph);
-        double sn, cs;
-        sincospi(2.0 * ph, &sn, &cs);
-        double t = re * cs - im * sn;
-        im = re * sn + im * cs;
-        re = t;
-      }
-    }
-    uint32_t i0r = (uint32_t)(s.i0 + kHalo - tu * kTile);
-    uint32_t j0r = (uint32_t)(s.j0 + kHalo - tv * kTile);
-    uint32_t p0r = (uint32_t)(s.p0 - win * g.win_step);
-    const int64_t o = out0 + k;
-    recs.cell[o] = i0r | (j0r << 5) | (p0r << 10);
-    recs.fu[o] = s.fu;
-    recs.fv[o] = s.fv;
-    recs.fw[o] = s.fw;
-    recs.re[o] = (R)re;
-    recs.im[o] = (R)im;
-  }
-}
-
 template <typename T>
 cip_status d2h_scalar(cip_ctx* ctx, const T* dev, T* out) {
   CIP_CHECK_CUDA(cudaMemcpyAsync(ctx->scan_host, dev, sizeof(T), cudaMemcpyDeviceToHost, ctx->stream));
@@ -217,7 +222,7 @@ cip_status run_binning(cip_ctx* ctx, const DevInputs& in, const GridGeom& g, int
   int64_t* row_off = ctx->row_off.as<int64_t>();
   CIP_CHECK_CUDA(cudaMemsetAsync(row_nruns + nrow, 0, sizeof(int64_t), st));
   const int rblocks = nblk(nrow * 32, 256);
-  runs_kernel<0><<<rblocks, 256, 0, st>>>(in, g, row_nruns, nullptr, nullptr, nullptr);
+  runs_kernel<0, float><<<rblocks, 256, 0, st>>>(in, g, row_nruns, nullptr, nullptr, nullptr, nullptr, (Rec<float>*)nullptr);
   ctx->launches++;
   size_t tmp_bytes = 0;
   CIP_CHECK_CUDA(cub::DeviceScan::ExclusiveSum(nullptr, tmp_bytes, row_nruns, row_off, nrow + 1, st));
@@ -237,7 +242,8 @@ cip_status run_binning(cip_ctx* ctx, const DevInputs& in, const GridGeom& g, int
   CIP_TRY(ctx->run_idx_alt.ensure(sizeof(uint32_t) * nruns));
   CIP_TRY(ctx->run_len.ensure(sizeof(int32_t) * nruns));
   Run* runs = ctx->runs.as<Run>();
-  runs_kernel<1><<<rblocks, 256, 0, st>>>(in, g, nullptr, row_off, runs, ctx->run_keys.as<uint64_t>());
+  runs_kernel<1, float><<<rblocks, 256, 0, st>>>(in, g, nullptr, row_off, runs, ctx->run_keys.as<uint64_t>(), nullptr,
+                                                 (Rec<float>*)nullptr);
   run_len_kernel<<<nblk(nruns, 256), 256, 0, st>>>(runs, nruns, (int32_t)nchan, ctx->run_idx.as<uint32_t>(),
                                                    ctx->run_len.as<int32_t>());
   ctx->launches += 2;
@@ -246,6 +252,8 @@ cip_status run_binning(cip_ctx* ctx, const DevInputs& in, const GridGeom& g, int
   uint64_t nkeys = (uint64_t)g.nwin * g.ntu * g.ntv;
   int bits = 1;
   while (bits < 64 && (nkeys >> bits)) ++bits;
+  bits += kSubKeyBits;
+  CIP_REQUIRE(bits <= 64, "bin key too wide (%d bits)", bits);
   CIP_CHECK_CUDA(cub::DeviceRadixSort::SortPairs(nullptr, tmp_bytes, ctx->run_keys.as<uint64_t>(),
                                                  ctx->run_keys_alt.as<uint64_t>(), ctx->run_idx.as<uint32_t>(),
                                                  ctx->run_idx_alt.as<uint32_t>(), nruns, 0, bits, st));
@@ -285,7 +293,10 @@ cip_status run_binning(cip_ctx* ctx, const DevInputs& in, const GridGeom& g, int
   int64_t* group_first = ctx->group_start.as<int64_t>();
   int64_t* group_nitems = group_first + (ngroups + 1);
   int64_t* group_item_off = group_nitems + (ngroups + 1);
-  groups_kernel<<<nblk(nruns, 256), 256, 0, st>>>(start_flag, group_of, visoff, nruns, nrec, group_first);
+  CIP_TRY(ctx->item_idx.ensure(sizeof(int64_t) * nruns));
+  int64_t* outpos = ctx->item_idx.as<int64_t>();
+  groups_kernel<<<nblk(nruns, 256), 256, 0, st>>>(start_flag, group_of, visoff, ctx->run_idx_alt.as<uint32_t>(), nruns,
+                                                  nrec, group_first, outpos);
   group_items_kernel<<<nblk(ngroups + 1, 256), 256, 0, st>>>(group_first, visoff, ngroups, nruns, nrec, group_nitems);
   ctx->launches += 2;
   CIP_CHECK_CUDA(cub::DeviceScan::ExclusiveSum(nullptr, tmp_bytes, group_nitems, group_item_off, ngroups + 1, st));
@@ -305,13 +316,13 @@ cip_status run_binning(cip_ctx* ctx, const DevInputs& in, const GridGeom& g, int
   ctx->launches += 2;
 
   // --- records ---------------------------------------------------------------------
-  CIP_TRY(ctx->recs.ensure(recs_bytes(nrec, fp64)));
+  CIP_TRY(ctx->recs.ensure(recs_bytes(nrec)));
   if (fp64)
-    records_kernel<double><<<nblk(nruns * 32, 256), 256, 0, st>>>(in, g, runs_sorted, len_sorted, visoff, nruns,
-                                                                 recs_view<double>(ctx->recs.p, nrec));
+    runs_kernel<2, double><<<rblocks, 256, 0, st>>>(in, g, nullptr, row_off, nullptr, nullptr, outpos,
+                                                    ctx->recs.as<Rec<double>>());
   else
-    records_kernel<float><<<nblk(nruns * 32, 256), 256, 0, st>>>(in, g, runs_sorted, len_sorted, visoff, nruns,
-                                                                recs_view<float>(ctx->recs.p, nrec));
+    runs_kernel<2, float><<<rblocks, 256, 0, st>>>(in, g, nullptr, row_off, nullptr, nullptr, outpos,
+                                                   ctx->recs.as<Rec<float>>());
   ctx->launches++;
   CIP_CHECK_CUDA(cudaGetLastError());
 

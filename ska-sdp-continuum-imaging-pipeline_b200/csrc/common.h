@@ -75,33 +75,29 @@ struct FftPlan {
   size_t work = 0;
 };
 
-// Gridder-ready visibilities, written by the record kernel in (window, tile) order as a structure of
-// arrays so that both the writer and the gridder's producer warp move whole 128-byte lines:
+// One gridder-ready visibility: exactly one 32-byte sector, so that the scattered writes of the
+// record pass never touch a partial sector and the gridder's producer reads two 128-bit words.
 //   cell  bits 0-4 i0 (u cell of the support origin inside the tile, 0..kTile-1), 5-9 j0,
 //         10-13 first plane relative to the window start
 //   fu, fv, fw  distance of the first cell / plane from the left edge of the support, in [0,1)
 //   re, im      weighted, conjugated-if-flipped, n-shift-rotated visibility (R = float or double)
 template <typename R>
-struct Recs {
-  uint32_t* cell;
-  float *fu, *fv, *fw;
-  R *re, *im;
+struct __align__(32) Rec;
+template <>
+struct __align__(32) Rec<float> {
+  uint32_t cell;
+  float fu, fv, fw;
+  float re, im;
+  float pad[2];
 };
-inline size_t recs_pad(int64_t nrec) { return ((size_t)nrec + 31) & ~(size_t)31; }
-inline size_t recs_bytes(int64_t nrec, int fp64) { return recs_pad(nrec) * (16 + 2 * (fp64 ? 8 : 4)); }
-template <typename R>
-inline Recs<R> recs_view(void* base, int64_t nrec) {
-  const size_t n = recs_pad(nrec);
-  Recs<R> r;
-  char* p = static_cast<char*>(base);
-  r.re = reinterpret_cast<R*>(p); p += n * sizeof(R);
-  r.im = reinterpret_cast<R*>(p); p += n * sizeof(R);
-  r.cell = reinterpret_cast<uint32_t*>(p); p += n * 4;
-  r.fu = reinterpret_cast<float*>(p); p += n * 4;
-  r.fv = reinterpret_cast<float*>(p); p += n * 4;
-  r.fw = reinterpret_cast<float*>(p);
-  return r;
-}
+template <>
+struct __align__(32) Rec<double> {
+  uint32_t cell;
+  float fu, fv, fw;
+  double re, im;
+};
+static_assert(sizeof(Rec<float>) == 32 && sizeof(Rec<double>) == 32, "records are one sector");
+inline size_t recs_bytes(int64_t nrec) { return (size_t)nrec * 32; }
 
 // A run of channels of one row that fall into the same (window, tile) bin.
 struct __align__(16) Run {

@@ -60,6 +60,16 @@ __device__ __forceinline__ uint64_t bin_key(const GridGeom& g, const SampleGeom&
   return ((uint64_t)win * g.ntu + tu) * g.ntv + tv;
 }
 
+// Position of the sample's register window (8 x 8 cells, origin snapped to multiples of 9-W cells,
+// see grid.cu) inside its tile: 4 bits per axis.
+constexpr int kSubKeyBits = 8;
+__device__ __forceinline__ uint32_t window_lattice(const GridGeom& g, const SampleGeom& s) {
+  if (g.W > kFastSupport) return 0;
+  const int snap = 9 - g.W;
+  const int iu = (s.i0 + kHalo) % kTile, iv = (s.j0 + kHalo) % kTile;
+  return (uint32_t)((iu / snap) << 4 | (iv / snap));
+}
+
 __device__ __forceinline__ bool sample_active(const float2 v, const float* wgt, const uint8_t* mask, int64_t k,
                                               float* wout) {
   float w = wgt ? wgt[k] : 1.0f;

@@ -5,9 +5,9 @@
 // Design ("residue owner"): one CTA per work item = a slice of the records of one uv tile
 // (kTile x kTile support origins) and one window of kWin w planes.  The tile's sub-grid
 // (kSub x kSub cells x kWin planes) lives in shared memory.  Warp 0 (producer) streams the
-// structure-of-arrays records with coalesced loads, evaluates the ES kernel separably (8 u-, 8 v-,
+// 32-byte records with 128-bit loads, evaluates the ES kernel separably (8 u-, 8 v-,
 // 8 w-weights per visibility, one visibility per lane) and hands batches of 32 visibilities to
-// warp 1 (consumer) through a two-stage shared-memory ring guarded by mbarriers.  In the consumer,
+// warp 1 (consumer) through a double buffer in shared memory (one named-barrier rendezvous per batch).  In the consumer,
 // lane (a, b) owns the grid cells with u index = a (mod 8) and v index = b or b+4 (mod 8): an
 // 8 x 8-cell register window that contains the support of the visibility (W <= 8) holds exactly one
 // cell of each residue class, so no two lanes ever touch the same cell and no atomics or shuffles are
@@ -31,23 +31,9 @@ using u64 = unsigned long long;
 
 // ---- small PTX helpers ----------------------------------------------------------------
 __device__ __forceinline__ uint32_t smem_u32(const void* p) { return (uint32_t)__cvta_generic_to_shared(p); }
-__device__ __forceinline__ void mbar_init(uint64_t* bar, int count) {
-  asm volatile("mbarrier.init.shared::cta.b64 [%0], %1;" ::"r"(smem_u32(bar)), "r"(count) : "memory");
-}
-__device__ __forceinline__ void mbar_arrive(uint64_t* bar) {
-  asm volatile("mbarrier.arrive.shared::cta.b64 _, [%0];" ::"r"(smem_u32(bar)) : "memory");
-}
-__device__ __forceinline__ void mbar_wait(uint64_t* bar, uint32_t parity) {
-  uint32_t done;
-  const uint32_t a = smem_u32(bar);
-  do {
-    asm volatile(
-        "{\n .reg .pred p;\n mbarrier.try_wait.parity.shared::cta.b64 p, [%1], %2;\n selp.u32 %0, 1, 0, p;\n}"
-        : "=r"(done)
-        : "r"(a), "r"(parity)
-        : "memory");
-  } while (!done);
-}
+// Rendezvous of the producer and the consumer warp (named barrier 1; barrier 0 is __syncthreads).
+// A blocked warp costs no issue slots, unlike a polling mbarrier wait.
+__device__ __forceinline__ void pair_sync() { asm volatile("bar.sync 1, 64;" ::: "memory"); }
 
 __device__ __forceinline__ u64 pack2(float lo, float hi) {
   u64 r;
@@ -98,26 +84,17 @@ struct alignas(16) Stage {
 };
 
 template <typename R>
-struct RecRegs {
-  uint32_t cell;
-  float fu, fv, fw;
-  R re, im;
-};
-
-template <typename R>
-__device__ __forceinline__ RecRegs<R> load_rec(const Recs<R>& recs, int64_t k, bool valid) {
-  RecRegs<R> r;
-  r.cell = valid ? __ldg(recs.cell + k) : 0u;
-  r.fu = valid ? __ldg(recs.fu + k) : 0.f;
-  r.fv = valid ? __ldg(recs.fv + k) : 0.f;
-  r.fw = valid ? __ldg(recs.fw + k) : 0.f;
-  r.re = valid ? __ldg(recs.re + k) : (R)0;
-  r.im = valid ? __ldg(recs.im + k) : (R)0;
+__device__ __forceinline__ Rec<R> load_rec(const Rec<R>* __restrict__ recs, int64_t k, bool valid) {
+  Rec<R> r;
+  float4* d = reinterpret_cast<float4*>(&r);
+  const float4* p = reinterpret_cast<const float4*>(recs + k);
+  d[0] = valid ? __ldg(p) : make_float4(0.f, 0.f, 0.f, 0.f);
+  d[1] = valid ? __ldg(p + 1) : make_float4(0.f, 0.f, 0.f, 0.f);
   return r;
 }
 
 template <typename R>
-__device__ __forceinline__ void produce(Stage<R>& st, const RecRegs<R>& rec, bool valid, int lane, uint32_t& carry,
+__device__ __forceinline__ void produce(Stage<R>& st, const Rec<R>& rec, bool valid, int lane, uint32_t& carry,
                                         const GridGeom& g, float bw2, float two_over_w, int snap) {
   const int W = g.W;
   const int i0 = rec.cell & 31, j0 = (rec.cell >> 5) & 31, p0 = (rec.cell >> 10) & 15;
@@ -143,16 +120,19 @@ __device__ __forceinline__ void produce(Stage<R>& st, const RecRegs<R>& rec, boo
 #pragma unroll
     for (int r = 0; r < 8; ++r) kw[r] = r == 0 ? 1.0f : 0.0f;
   }
+  // 16-byte chunks are XOR-swizzled with the visibility index so that the producer's 128-bit stores
+  // (row pitch 64 / 32 bytes) are bank-conflict free; the consumer applies the same permutation
+  const int sw = (lane >> 1) & 3, sv = (lane >> 2) & 1;
   float4* pu = reinterpret_cast<float4*>(st.ku[lane]);
   float4* pw = reinterpret_cast<float4*>(st.kw[lane]);
 #pragma unroll
   for (int q = 0; q < 4; ++q) {
-    pu[q] = make_float4(ku[2 * q], ku[2 * q], ku[2 * q + 1], ku[2 * q + 1]);
-    pw[q] = make_float4(kw[2 * q], kw[2 * q], kw[2 * q + 1], kw[2 * q + 1]);
+    pu[q ^ sw] = make_float4(ku[2 * q], ku[2 * q], ku[2 * q + 1], ku[2 * q + 1]);
+    pw[q ^ sw] = make_float4(kw[2 * q], kw[2 * q], kw[2 * q + 1], kw[2 * q + 1]);
   }
   float4* pv = reinterpret_cast<float4*>(st.kv[lane]);
-  pv[0] = make_float4(kv[0], kv[4], kv[1], kv[5]);
-  pv[1] = make_float4(kv[2], kv[6], kv[3], kv[7]);
+  pv[0 ^ sv] = make_float4(kv[0], kv[4], kv[1], kv[5]);
+  pv[1 ^ sv] = make_float4(kv[2], kv[6], kv[3], kv[7]);
   const R re = valid ? rec.re : (R)0, im = valid ? rec.im : (R)0;
   if constexpr (sizeof(R) == 4) st.val[lane] = make_float4(re, re, im, im);
   else st.val[lane] = make_double2(re, im);
@@ -179,16 +159,35 @@ struct Acc<float> {
 #pragma unroll
     for (int c = 0; c < 8; ++c) re[c] = im[c] = 0ull;
   }
-  static __device__ __forceinline__ Ops load(const Stage<float>& st, int k, int a8, int b4) {
+  // Per-lane pointers to the rows of visibility k0 (a multiple of 8) of a stage, one per swizzle
+  // state, so that every operand of visibilities k0 .. k0+8 is a load at [register + immediate].
+  struct Group {
+    const char *ku[4], *kv[2], *kw, *val;
+  };
+  static __device__ __forceinline__ Group group(const Stage<float>& st, int k0, int a8, int b4) {
+    Group gp;
+#pragma unroll
+    for (int s = 0; s < 4; ++s) gp.ku[s] = reinterpret_cast<const char*>(st.ku[k0]) + (a8 ^ (2 * s)) * 8;
+#pragma unroll
+    for (int t = 0; t < 2; ++t)
+      gp.kv[t] = reinterpret_cast<const char*>(st.kv[k0]) + (((b4 >> 1) ^ t) * 2 + (b4 & 1)) * 8;
+    gp.kw = reinterpret_cast<const char*>(st.kw[k0]);
+    gp.val = reinterpret_cast<const char*>(&st.val[k0]);
+    return gp;
+  }
+  // Operands of visibility k0 + U, U = 0..8 (U = 8 is the first one of the next group; past the end of
+  // a stage it reads the following array of the struct and is discarded).
+  template <int U>
+  static __device__ __forceinline__ Ops load(const Group& gp) {
+    constexpr int sw = (U >> 1) & 3, sv = (U >> 2) & 1;
     Ops o;
-    o.ku = *reinterpret_cast<const u64*>(&st.ku[k][a8]);
-    o.kv = *reinterpret_cast<const u64*>(&st.kv[k][b4]);
-    const ulonglong2 v = *reinterpret_cast<const ulonglong2*>(&st.val[k]);
+    o.ku = *reinterpret_cast<const u64*>(gp.ku[sw] + U * 64);
+    o.kv = *reinterpret_cast<const u64*>(gp.kv[sv] + U * 32);
+    const ulonglong2 v = *reinterpret_cast<const ulonglong2*>(gp.val + U * 16);
     o.rr = v.x;
     o.ii = v.y;
-    const ulonglong2* kw = reinterpret_cast<const ulonglong2*>(st.kw[k]);
 #pragma unroll
-    for (int q = 0; q < 4; ++q) o.kw[q] = kw[q];
+    for (int q = 0; q < 4; ++q) o.kw[q] = *reinterpret_cast<const ulonglong2*>(gp.kw + U * 64 + (q ^ sw) * 16);
     return o;
   }
   __device__ __forceinline__ void update(const Ops& o) {
@@ -235,13 +234,24 @@ struct Acc<double> {
 #pragma unroll
       for (int c = 0; c < 8; ++c) a[s][c] = make_double2(0.0, 0.0);
   }
-  static __device__ __forceinline__ Ops load(const Stage<double>& st, int k, int a8, int b4) {
+  struct Group {
+    const Stage<double>* st;
+    int k0, a8, b4;
+  };
+  static __device__ __forceinline__ Group group(const Stage<double>& st, int k0, int a8, int b4) {
+    return Group{&st, k0, a8, b4};
+  }
+  template <int U>
+  static __device__ __forceinline__ Ops load(const Group& gp) {
+    constexpr int sw = (U >> 1) & 3, sv = (U >> 2) & 1;
+    const Stage<double>& st = *gp.st;
+    const int k = min(gp.k0 + U, kBatch - 1);
     Ops o;
-    o.ku = st.ku[k][a8].x;
-    o.kv = st.kv[k][b4];
+    o.ku = st.ku[k][gp.a8 ^ (2 * sw)].x;
+    o.kv = st.kv[k][(((gp.b4 >> 1) ^ sv) << 1) | (gp.b4 & 1)];
     o.val = st.val[k];
 #pragma unroll
-    for (int c = 0; c < 8; ++c) o.kw[c] = st.kw[k][c].x;
+    for (int c = 0; c < 8; ++c) o.kw[c] = st.kw[k][c ^ (2 * sw)].x;
     return o;
   }
   __device__ __forceinline__ void update(const Ops& o) {
@@ -276,34 +286,59 @@ struct Acc<double> {
 
 template <typename R>
 constexpr size_t grid_smem_bytes() {
-  return sizeof(typename SubGrid<R>::cell) * SubGrid<R>::ncell + sizeof(Stage<R>) * kStages + 2 * kStages * sizeof(uint64_t);
+  return sizeof(typename SubGrid<R>::cell) * SubGrid<R>::ncell + sizeof(Stage<R>) * kStages;
+}
+
+// One visibility of a group of eight (compile-time position U): prefetch the operands of the next
+// visibility into `nxt`, fold if the register window moved (warp-uniform; only in CHECK groups),
+// accumulate `cur`.  Every stage always holds kBatch entries (the producer pads with zero
+// visibilities), so there is no bounds check and the two operand sets simply alternate roles.
+template <typename R, int U, bool CHECK>
+__device__ __forceinline__ void consume1(const Stage<R>& st, const typename Acc<R>::Group& gp, int k0, uint32_t moved,
+                                         const typename Acc<R>::Ops& cur, typename Acc<R>::Ops& nxt, Acc<R>& acc,
+                                         typename SubGrid<R>::cell* sg, int& ci, int& cj0, int& cj1, int a8, int b4) {
+  nxt = Acc<R>::template load<U + 1>(gp);
+  if (CHECK && ((moved >> (k0 + U)) & 1u)) {
+    acc.fold(sg, ci, cj0, cj1);
+    const uint32_t o = st.org[k0 + U];
+    const int wi = o & 31, wj = (o >> 5) & 31;
+    ci = wi + ((a8 - wi) & 7);
+    cj0 = wj + ((b4 - wj) & 7);
+    cj1 = wj + ((b4 + 4 - wj) & 7);
+  }
+  acc.update(cur);
+}
+
+template <typename R, bool CHECK>
+__device__ __forceinline__ void consume8(const Stage<R>& st, const typename Acc<R>::Group& gp, int k0, uint32_t moved,
+                                         typename Acc<R>::Ops& x, Acc<R>& acc, typename SubGrid<R>::cell* sg, int& ci,
+                                         int& cj0, int& cj1, int a8, int b4) {
+  typename Acc<R>::Ops y;
+  consume1<R, 0, CHECK>(st, gp, k0, moved, x, y, acc, sg, ci, cj0, cj1, a8, b4);
+  consume1<R, 1, CHECK>(st, gp, k0, moved, y, x, acc, sg, ci, cj0, cj1, a8, b4);
+  consume1<R, 2, CHECK>(st, gp, k0, moved, x, y, acc, sg, ci, cj0, cj1, a8, b4);
+  consume1<R, 3, CHECK>(st, gp, k0, moved, y, x, acc, sg, ci, cj0, cj1, a8, b4);
+  consume1<R, 4, CHECK>(st, gp, k0, moved, x, y, acc, sg, ci, cj0, cj1, a8, b4);
+  consume1<R, 5, CHECK>(st, gp, k0, moved, y, x, acc, sg, ci, cj0, cj1, a8, b4);
+  consume1<R, 6, CHECK>(st, gp, k0, moved, x, y, acc, sg, ci, cj0, cj1, a8, b4);
+  consume1<R, 7, CHECK>(st, gp, k0, moved, y, x, acc, sg, ci, cj0, cj1, a8, b4);
 }
 
 // ---- the kernel -----------------------------------------------------------------------
 template <typename R>
 __global__ void __launch_bounds__(kGridThreads) grid_kernel(const Item* __restrict__ items, int64_t item_base,
-                                                            Recs<R> recs, GridGeom g, R* __restrict__ grid,
+                                                            const Rec<R>* __restrict__ recs, GridGeom g, R* __restrict__ grid,
                                                             int plane_base, int nslots) {
   using Cell = typename SubGrid<R>::cell;
   extern __shared__ __align__(16) unsigned char smem_raw[];
   Cell* sg = reinterpret_cast<Cell*>(smem_raw);
   Stage<R>* stages = reinterpret_cast<Stage<R>*>(smem_raw + sizeof(Cell) * SubGrid<R>::ncell);
-  uint64_t* full = reinterpret_cast<uint64_t*>(stages + kStages);  // [kStages] producer -> consumer
-  uint64_t* empty = full + kStages;                                 // [kStages] consumer -> producer
 
   const Item item = items[item_base + blockIdx.x];
   const int tid = threadIdx.x, lane = tid & 31, warp = tid >> 5;
   const int nrec = item.nrec;
   const int nb = (nrec + kBatch - 1) / kBatch;
 
-  if (tid == 0) {
-#pragma unroll
-    for (int s = 0; s < kStages; ++s) {
-      mbar_init(&full[s], 32);
-      mbar_init(&empty[s], 32);
-    }
-    asm volatile("fence.mbarrier_init.release.cluster;" ::: "memory");
-  }
   {  // zero the sub-grid
     Cell z;
     memset(&z, 0, sizeof(z));
@@ -319,15 +354,14 @@ __global__ void __launch_bounds__(kGridThreads) grid_kernel(const Item* __restri
     const int64_t base = item.rec_begin;
     uint32_t carry = 0xffffffffu;
     bool cur_valid = lane < nrec;
-    RecRegs<R> cur = load_rec(recs, base + lane, cur_valid);
+    Rec<R> cur = load_rec(recs, base + lane, cur_valid);
     for (int b = 0; b < nb; ++b) {
       const int s = b % kStages;
       const int kn = (b + 1) * kBatch + lane;
       const bool nxt_valid = kn < nrec;
-      RecRegs<R> nxt = load_rec(recs, base + kn, nxt_valid);
-      if (b >= kStages) mbar_wait(&empty[s], ((b / kStages) - 1) & 1);  // the consumer released stage s
+      Rec<R> nxt = load_rec(recs, base + kn, nxt_valid);
       produce<R>(stages[s], cur, cur_valid, lane, carry, g, bw2, two_over_w, snap);
-      mbar_arrive(&full[s]);
+      pair_sync();  // rendezvous b: batch b is ready, and the consumer has finished batch b-1 (stage s^1 is free)
       cur = nxt;
       cur_valid = nxt_valid;
     }
@@ -339,26 +373,17 @@ __global__ void __launch_bounds__(kGridThreads) grid_kernel(const Item* __restri
     int ci = a8, cj0 = b4, cj1 = b4 + 4;  // current cells of this lane (sub-grid coordinates)
     for (int b = 0; b < nb; ++b) {
       const int s = b % kStages;
-      mbar_wait(&full[s], (b / kStages) & 1);
+      pair_sync();  // rendezvous b
       const Stage<R>& st = stages[s];
-      const int n = min(kBatch, nrec - b * kBatch);
       const uint32_t moved = st.moved;
-      typename Acc<R>::Ops cur = Acc<R>::load(st, 0, a8, b4);
-#pragma unroll 4
-      for (int k = 0; k < n; ++k) {
-        const typename Acc<R>::Ops nxt = Acc<R>::load(st, min(k + 1, kBatch - 1), a8, b4);
-        if ((moved >> k) & 1u) {  // warp-uniform: the register window moved
-          acc.fold(sg, ci, cj0, cj1);
-          const uint32_t o = st.org[k];
-          const int wi = o & 31, wj = (o >> 5) & 31;
-          ci = wi + ((a8 - wi) & 7);
-          cj0 = wj + ((b4 - wj) & 7);
-          cj1 = wj + ((b4 + 4 - wj) & 7);
-        }
-        acc.update(cur);
-        cur = nxt;
+      typename Acc<R>::Ops x = Acc<R>::template load<0>(Acc<R>::group(st, 0, a8, b4));
+#pragma unroll 1
+      for (int k0 = 0; k0 < kBatch; k0 += 8) {
+        const typename Acc<R>::Group gp = Acc<R>::group(st, k0, a8, b4);
+        // most groups stay inside one register window: branch-free fast path
+        if (((moved >> k0) & 0xffu) == 0) consume8<R, false>(st, gp, k0, moved, x, acc, sg, ci, cj0, cj1, a8, b4);
+        else consume8<R, true>(st, gp, k0, moved, x, acc, sg, ci, cj0, cj1, a8, b4);
       }
-      mbar_arrive(&empty[s]);
     }
     acc.fold(sg, ci, cj0, cj1);
   }
@@ -424,13 +449,13 @@ __global__ void __launch_bounds__(kGridThreads) grid_kernel(const Item* __restri
 // Wide supports (W > 8, only reached for very small epsilon): plain scatter with global atomics.
 template <typename R>
 __global__ void __launch_bounds__(128) grid_wide_kernel(const Item* __restrict__ items, int64_t item_base,
-                                                        Recs<R> recs, GridGeom g, R* __restrict__ grid,
+                                                        const Rec<R>* __restrict__ recs, GridGeom g, R* __restrict__ grid,
                                                         int plane_base, int nslots) {
   const Item item = items[item_base + blockIdx.x];
   const int W = g.W;
   const int su0 = item.tu * kTile - kHalo + g.nu / 2, sv0 = item.tv * kTile - kHalo + g.nv / 2;
   for (int k = threadIdx.x; k < item.nrec; k += blockDim.x) {
-    const RecRegs<R> rec = load_rec(recs, item.rec_begin + k, true);
+    const Rec<R> rec = load_rec(recs, item.rec_begin + k, true);
     if (rec.re == 0 && rec.im == 0) continue;
     const int i0 = rec.cell & 31, j0 = (rec.cell >> 5) & 31, p0 = rec.cell >> 10;
     float kv[kMaxSupport];
@@ -460,7 +485,8 @@ template <typename R>
 cip_status launch(cip_ctx* ctx, const GridGeom& g, int64_t nrec_total, int64_t item_begin, int64_t item_end,
                   void* grid, int plane_base, int nslots) {
   const Item* items = ctx->items.as<Item>();
-  const Recs<R> recs = recs_view<R>(ctx->recs.p, nrec_total);
+  const Rec<R>* recs = ctx->recs.as<Rec<R>>();
+  (void)nrec_total;
   const int64_t n = item_end - item_begin;
   if (n <= 0) return CIP_OK;
   CIP_REQUIRE(n < ((int64_t)1 << 31), "too many work items");
