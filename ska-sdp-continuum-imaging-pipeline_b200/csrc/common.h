@@ -20,7 +20,7 @@ constexpr double kSpeedOfLight = 299792458.0;
 constexpr int kMaxSupport = 16;   // widest kernel in the design table
 constexpr int kFastSupport = 8;   // widest kernel of the residue-owner gridder (= residue modulus)
 constexpr int kMinSupport = 4;
-constexpr int kTile = 16;         // uv tile edge of the gridder, in grid cells
+constexpr int kTile = 8;          // uv tile edge of the gridder, in grid cells
 constexpr int kHalo = 8;          // shift that keeps window origins non-negative (>= kMaxSupport/2)
 constexpr int kSub = kTile + kFastSupport - 1;  // sub-grid edge held in shared memory (23, odd on purpose)
 constexpr int kWin = 8;           // w planes of one gridding window (= planes per consumer thread)

@@ -339,6 +339,16 @@ __global__ void __launch_bounds__(kGridThreads) grid_kernel(const Item* __restri
   const int nrec = item.nrec;
   const int nb = (nrec + kBatch - 1) / kBatch;
 
+  // Which of the two warps consumes: the sub-partition (SMSP) of a warp is its hardware slot modulo 4
+  // and a two-warp CTA occupies an aligned pair of slots, so a fixed role would put every consumer of
+  // the SM on SMSPs 1 and 3.  Alternating the role with bit 2 of the slot spreads the (FMA-heavy)
+  // consumers of co-resident CTAs over all four SMSPs.  Only a heuristic: any choice is correct.
+  __shared__ int s_consumer_warp;
+  if (tid == 0) {
+    uint32_t hw;
+    asm volatile("mov.u32 %0, %%warpid;" : "=r"(hw));
+    s_consumer_warp = (hw >> 2) & 1;
+  }
   {  // zero the sub-grid
     Cell z;
     memset(&z, 0, sizeof(z));
@@ -346,7 +356,7 @@ __global__ void __launch_bounds__(kGridThreads) grid_kernel(const Item* __restri
   }
   __syncthreads();
 
-  if (warp == 0) {
+  if (warp != s_consumer_warp) {
     // ---------------- producer ----------------
     const float bw2 = g.beta_w * 1.4426950408889634f;
     const float two_over_w = 2.0f / (float)g.W;
