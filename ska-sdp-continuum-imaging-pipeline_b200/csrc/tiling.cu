@@ -16,6 +16,8 @@
 #include <cub/device/device_radix_sort.cuh>
 #include <cub/device/device_scan.cuh>
 
+#include <cmath>
+
 #include "common.h"
 
 struct cip_tile_result {
@@ -224,6 +226,8 @@ extern "C" cip_status cip_tile_bin(cip_ctx* ctx, const double* uvw, int64_t nrow
   CIP_REQUIRE(nchan > 0 || nrow == 0, "channel_freqs is empty (the reference raises IndexError here)");
   CIP_REQUIRE(nchan == 0 || freq != nullptr, "freq is NULL");
   CIP_REQUIRE(memspace == 0 || memspace == 1, "memspace must be 0 or 1");
+  for (int k = 0; k < 3; ++k)
+    CIP_REQUIRE(tile_size[k] > 0 && tile_size[k] < HUGE_VAL, "tile_size[%d] must be positive and finite", k);
   CIP_CHECK_CUDA(cudaSetDevice(ctx->device));
   *result = nullptr;
   cudaStream_t st = ctx->stream;

@@ -138,6 +138,60 @@ def integrate_weighted_images(weighted_images: Iterable[tuple[NDArray, float]]) 
     return sum(images) / sum(weights)
 
 
+def shard_of_rank(chunks: Sequence, rank: int, world: int) -> list:
+    """Chunks of the reference's partition (row-major, frequency-minor) owned by ``rank``: round-robin,
+    so that with freq_chunks = world each rank gets one frequency chunk of every row chunk."""
+    return list(chunks[rank::world])
+
+
+def agree_on_shard_statistics(wmin: float, wmax: float, nactive: int, sumw: float, *, group=None, device=None):
+    """All ranks must build their partial images with the same (sigma, W, dw, nshift, nplanes): combine
+    the per-rank |w| range (min/max), active count and weight sum (sums) over the process group.
+    Two small all-reduces; a no-op without an initialised process group."""
+    if not _dist_ready():
+        return wmin, wmax, nactive, sumw
+    torch = _torch()
+    dist = torch.distributed
+    if dist.get_world_size(group) == 1:
+        return wmin, wmax, nactive, sumw
+    t = torch.tensor([-wmin, wmax], dtype=torch.float64, device=device)
+    dist.all_reduce(t, op=dist.ReduceOp.MAX, group=group)
+    s = torch.tensor([float(nactive), sumw], dtype=torch.float64, device=device)
+    dist.all_reduce(s, op=dist.ReduceOp.SUM, group=group)
+    return -float(t[0]), float(t[1]), int(s[0].item()), float(s[1])
+
+
+def reduce_image_rows(image, *, group=None):
+    """Sum the partial images over the ranks, leaving each rank with a contiguous block of rows:
+    returns (rows tensor, row_begin, row_end).  NCCL: one reduce-scatter.  Images whose row count is
+    not divisible by the world size (and the gloo backend, which has no reduce-scatter) use an
+    all-reduce and every rank keeps all rows."""
+    torch = _torch()
+    n = image.shape[0]
+    if not _dist_ready() or torch.distributed.get_world_size(group) == 1:
+        return image, 0, n
+    dist = torch.distributed
+    world, rank = dist.get_world_size(group), dist.get_rank(group)
+    if n % world == 0 and dist.get_backend(group) == "nccl":
+        rows = n // world
+        mine = torch.empty((rows, image.shape[1]), dtype=image.dtype, device=image.device)
+        dist.reduce_scatter_tensor(mine, image, op=dist.ReduceOp.SUM, group=group)
+        return mine, rank * rows, (rank + 1) * rows
+    dist.all_reduce(image, op=dist.ReduceOp.SUM, group=group)
+    if n % world == 0:
+        rows = n // world
+        return image[rank * rows:(rank + 1) * rows], rank * rows, (rank + 1) * rows
+    return image, 0, n
+
+
+def gather_image_rows(image, mine, row_begin: int, row_end: int, *, group=None):
+    """Inverse of reduce_image_rows after the per-block correction: the full image on every rank."""
+    if row_begin == 0 and row_end == image.shape[0]:
+        return mine
+    _torch().distributed.all_gather_into_tensor(image, mine.contiguous(), group=group)
+    return image
+
+
 # ---- sharded invert: the B200 form of dask_invert_measurement_set ------------------------------
 
 def accumulate_shards(shards: Sequence[StokesIGridderInput], num_pixels: int, pixel_size_lm: float, *,
@@ -174,14 +228,7 @@ def accumulate_shards(shards: Sequence[StokesIGridderInput], num_pixels: int, pi
             wmin, wmax = min(wmin, scan.wmin), max(wmax, scan.wmax)
         nactive += scan.nactive
         sumw += scan.sum_wgt
-    if group is not None or (_dist_ready() and _torch().distributed.get_world_size() > 1):
-        dist = torch.distributed
-        t = torch.tensor([-wmin, wmax], dtype=torch.float64, device=dev)
-        dist.all_reduce(t, op=dist.ReduceOp.MAX, group=group)
-        s = torch.tensor([float(nactive), sumw], dtype=torch.float64, device=dev)
-        dist.all_reduce(s, op=dist.ReduceOp.SUM, group=group)
-        wmin, wmax = -float(t[0]), float(t[1])
-        nactive, sumw = int(s[0].item()), float(s[1])
+    wmin, wmax, nactive, sumw = agree_on_shard_statistics(wmin, wmax, nactive, sumw, group=group, device=dev)
     if nactive == 0:
         wmin = wmax = 0.0
     plan = _cabi.plan_make(num_pixels, num_pixels, pixel_size_lm, pixel_size_lm, epsilon, wmin, wmax, nactive,
@@ -209,38 +256,20 @@ def _dist_ready() -> bool:
 def reduce_and_correct(image, plan: Plan, total_weight: float, *, group=None, normalise: bool = True):
     """Sum the partial images of all ranks and apply the grid correction once (P5 + G4 final).
 
-    Multi-rank: reduce-scatter by image rows over NCCL, each rank corrects its row slice
+    Multi-rank: reduce-scatter by image rows over NCCL, each rank corrects its row block
     (cip_correct_image with the 1/sum(weights) scale folded in), all-gather.  Returns the full
     corrected image on every rank."""
     torch = _torch()
     ctx = Context.get(image.device.index)
-    L = lib()
     scale = (1.0 / total_weight) if normalise else 1.0
-    n = image.shape[0]
-    world = torch.distributed.get_world_size(group) if (_dist_ready()) else 1
     torch.cuda.current_stream(image.device).synchronize()
-    if world == 1:
-        with ctx.lock:
-            check(L.cip_correct_image(ctx.handle, C.byref(plan), image.data_ptr(), 0, n, scale))
-        return image
-    dist = torch.distributed
-    rank = dist.get_rank(group)
-    if n % world == 0:
-        rows = n // world
-        mine = torch.empty((rows, image.shape[1]), dtype=image.dtype, device=image.device)
-        dist.reduce_scatter_tensor(mine, image, op=dist.ReduceOp.SUM, group=group)
-        torch.cuda.current_stream(image.device).synchronize()
-        # cip_correct_image takes the pointer to row 0 of the full image: offset back by this rank's rows
-        base = mine.data_ptr() - rank * rows * image.shape[1] * image.element_size()
-        with ctx.lock:
-            check(L.cip_correct_image(ctx.handle, C.byref(plan), base, rank * rows, (rank + 1) * rows, scale))
-        dist.all_gather_into_tensor(image, mine, group=group)
-    else:
-        dist.all_reduce(image, op=dist.ReduceOp.SUM, group=group)
-        torch.cuda.current_stream(image.device).synchronize()
-        with ctx.lock:
-            check(L.cip_correct_image(ctx.handle, C.byref(plan), image.data_ptr(), 0, n, scale))
-    return image
+    mine, r0, r1 = reduce_image_rows(image, group=group)
+    torch.cuda.current_stream(image.device).synchronize()
+    # cip_correct_image takes the pointer to row 0 of the full image: offset back by this rank's first row
+    base = mine.data_ptr() - r0 * image.shape[1] * image.element_size()
+    with ctx.lock:
+        check(lib().cip_correct_image(ctx.handle, C.byref(plan), base, r0, r1, scale))
+    return gather_image_rows(image, mine, r0, r1, group=group)
 
 
 def dask_invert_measurement_set(ms_reader: MeasurementSetReader, client, num_pixels: int, pixel_size_asec: float,
@@ -274,7 +303,7 @@ def dask_invert_measurement_set(ms_reader: MeasurementSetReader, client, num_pix
 
     torch = _torch()
     rank, world = (torch.distributed.get_rank(), torch.distributed.get_world_size()) if _dist_ready() else (0, 1)
-    shards = [StokesIGridderInput.from_measurement_set_reader(c) for c in chunks[rank::world]]
+    shards = [StokesIGridderInput.from_measurement_set_reader(c) for c in shard_of_rank(chunks, rank, world)]
     image, plan, sumw = accumulate_shards(shards, num_pixels, _pixel_size_lm(pixel_size_asec), epsilon=epsilon,
                                           accumulate_fp64=accumulate_fp64)
     image = reduce_and_correct(image, plan, float(np.float32(sumw)))

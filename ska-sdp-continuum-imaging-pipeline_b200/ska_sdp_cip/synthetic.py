@@ -132,7 +132,7 @@ def make_vis_numpy(cfg, uvw, freq, pix_lm, seed=1234, noise=1.0, flag_fraction=0
     vis = np.zeros((nrow, nchan), dtype=np.complex128)
     for ls, ms_, fs in zip(l, m, flux):
         nm1 = -(ls * ls + ms_ * ms_) / (np.sqrt(1.0 - ls * ls - ms_ * ms_) + 1.0)
-        ph = (uvw[:, 0] * ls + uvw[:, 1] * ms_ + uvw[:, 2] * nm1)[:, None] * finv[None, :]
+        ph = (uvw[:, 0] * ls + uvw[:, 1] * ms_ - uvw[:, 2] * nm1)[:, None] * finv[None, :]  # ms2dirty's w sign
         vis += fs * np.exp(-2j * np.pi * ph)
     vis += noise * (rng.normal(size=vis.shape) + 1j * rng.normal(size=vis.shape))
     wgt = rng.uniform(0.5, 1.5, size=vis.shape).astype(np.float32)
@@ -156,7 +156,7 @@ def make_vis_torch(cfg, uvw, freq, pix_lm, device, seed=1234, noise=1.0, flag_fr
         blk = torch.zeros((r1 - r0, nchan), dtype=torch.complex128, device=device)
         for ls, ms_, fs in zip(l, m, flux):
             nm1 = -(ls * ls + ms_ * ms_) / (np.sqrt(1.0 - ls * ls - ms_ * ms_) + 1.0)
-            ph = (d_uvw[r0:r1, 0] * ls + d_uvw[r0:r1, 1] * ms_ + d_uvw[r0:r1, 2] * nm1)[:, None] * finv[None, :]
+            ph = (d_uvw[r0:r1, 0] * ls + d_uvw[r0:r1, 1] * ms_ - d_uvw[r0:r1, 2] * nm1)[:, None] * finv[None, :]
             ph = (ph - torch.round(ph)) * (-2.0 * np.pi)
             blk += fs * torch.complex(torch.cos(ph), torch.sin(ph))
         nz = torch.randn((r1 - r0, nchan, 2), generator=gen, device=device, dtype=torch.float32) * noise

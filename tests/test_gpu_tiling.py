@@ -1,0 +1,167 @@
+"""Bit-exact parity of the CUDA tile binning (cip_tile_bin / cip_tile_fetch / cip_tile_gather through
+the C-ABI) with the reference's own uvw_tiling results (golden fixtures made by importing the
+reference, tools/make_golden.py) and with the oracle on seeded inputs; at BASELINE.json configs[2]
+scale through size-independent properties."""
+import numpy as np
+import pytest
+
+from oracle import tiling
+
+pytestmark = pytest.mark.gpu
+
+CASES = ["meerkat_l", "small_tiles", "one_channel", "descending_freq", "half_integers"]
+NAMES = ("coords", "offsets", "irow", "chan_start", "chan_stop")
+
+
+@pytest.fixture(scope="module")
+def T(built_lib):
+    import torch
+    assert torch.cuda.is_available(), "gpu tests need a CUDA device"
+    from ska_sdp_cip import uvw_tiling
+    return uvw_tiling
+
+
+@pytest.mark.parametrize("case", CASES)
+def test_tile_binning_matches_reference_golden(T, golden, case):
+    g = golden(f"tiling_{case}")
+    dm = T.device_tile_mapping(g["uvw"], tuple(g["tile_size"]), g["freq"], row_offset=int(g["row_offset"]))
+    for name, got in zip(NAMES, dm.arrays()):
+        assert got.dtype == g[name].dtype or np.can_cast(got.dtype, g[name].dtype), name
+        assert np.array_equal(got, g[name]), name
+
+
+@pytest.mark.parametrize("case", CASES)
+def test_tile_gather_matches_reference_golden(T, golden, case):
+    g = golden(f"tiling_{case}")
+    off = int(g["row_offset"])
+    uvw, freq = g["uvw"], g["freq"]
+    rng = np.random.default_rng(int(g["vis_seed"]))
+    vis = (rng.normal(size=(len(uvw), len(freq))) + 1j * rng.normal(size=(len(uvw), len(freq)))).astype(np.complex64)
+    dm = T.device_tile_mapping(uvw, tuple(g["tile_size"]), freq, row_offset=off)
+    tiles = T.tiles_from_device_mapping(dm, vis, uvw)
+    assert len(tiles) == dm.n_tiles
+    for t in range(int(g["n_gather_tiles"])):
+        assert np.array_equal(tiles[t].uvw, g[f"tile{t}_uvw"])
+        assert np.array_equal(tiles[t].visibilities, g[f"tile{t}_vis"])
+        assert np.array_equal(tiles[t].channel_start_indices, g[f"tile{t}_start"])
+        assert np.array_equal(tiles[t].channel_stop_indices, g[f"tile{t}_stop"])
+    assert sum(t.num_visibilities for t in tiles) == vis.size
+
+
+def test_mapping_has_reference_types_and_order(T, golden):
+    g = golden("tiling_small_tiles")
+    m = T.create_uvw_tile_mapping(g["uvw"], tuple(g["tile_size"]), g["freq"])
+    want = tiling.tile_mapping(g["uvw"], tuple(g["tile_size"]), g["freq"])
+    assert list(m) == list(want)                      # first-appearance key order
+    for key, slices in m.items():
+        assert all(type(k) is int for k in key)       # python ints (tiling_plan.py:163-165)
+        assert all(isinstance(s, T.RowSliceId) and type(s.irow) is int for s in slices[:3])
+        assert [tuple(s) for s in slices] == [tuple(s) for s in want[key]]
+
+
+def test_every_sample_in_exactly_one_tile(T):
+    """The reference's own test (tests/uvw_tiling/test_uvw_tiling_plan.py:7-32) on a MeerKAT-L-shaped layout."""
+    rng = np.random.default_rng(0)
+    nrow, nchan = 5000, 256
+    uvw = rng.normal(size=(nrow, 3)) * np.array([4000, 4000, 300.0])
+    uvw[::50] = 0  # autocorrelations
+    freq = 856e6 + np.arange(nchan) * 214e6 / 256
+    m = T.create_uvw_tile_mapping(uvw, (3000.0, 3000.0, 6000.0), freq)
+    hit = np.zeros((nrow, nchan), dtype=int)
+    for slices in m.values():
+        for s in slices:
+            hit[s.irow, s.chan_start:s.chan_stop] += 1
+    assert (hit == 1).sum() == hit.size
+
+
+@pytest.mark.parametrize("nrow,nchan,ts,seed", [(3000, 64, (300.0, 300.0, 600.0), 0),
+                                                 (20000, 256, (50.0, 50.0, 100.0), 1),
+                                                 (1, 1, (3000.0, 3000.0, 6000.0), 2),
+                                                 (7, 1000, (10.0, 10.0, 10.0), 3),
+                                                 (200000, 64, (3000.0, 3000.0, 6000.0), 4),
+                                                 (5000, 33, (1e-2, 1e9, 1e9), 5)])
+def test_random_layouts_match_oracle(T, nrow, nchan, ts, seed):
+    rng = np.random.default_rng(seed)
+    uvw = rng.normal(size=(nrow, 3)) * np.array([4000, 4000, 300.0])
+    freq = 856e6 + np.arange(nchan) * 214e6 / 256
+    dm = T.device_tile_mapping(uvw, ts, freq, row_offset=5)
+    want = tiling.tile_mapping_arrays(uvw, ts, freq, row_offset=5)
+    for name, got, exp in zip(NAMES, dm.arrays(), want):
+        assert np.array_equal(got, exp), name
+
+
+def test_half_integer_boundaries_round_like_numpy(T):
+    """floor(x + 0.5) with x exactly on a boundary, negative zero, denormals and huge coordinates."""
+    freq = np.array([299792458.0, 2 * 299792458.0])  # freq/c = 1, 2 exactly
+    vals = np.array([0.5, -0.5, 1.5, -1.5, 2.5, 0.49999999999999994, -0.0, 5e-324, 1e15 + 0.5, -1e15 - 0.5, 4503599627370495.5])
+    uvw = np.stack([vals, vals[::-1], np.zeros_like(vals)], axis=1)
+    dm = T.device_tile_mapping(uvw, (1.0, 1.0, 1.0), freq)
+    want = tiling.tile_mapping_arrays(uvw, (1.0, 1.0, 1.0), freq)
+    for name, got, exp in zip(NAMES, dm.arrays(), want):
+        assert np.array_equal(got, exp), name
+
+
+def test_empty_and_degenerate_inputs(T):
+    freq = np.array([1e9, 1.1e9])
+    m = T.create_uvw_tile_mapping(np.zeros((0, 3)), (1.0, 1.0, 1.0), freq)
+    assert m == {}
+    m = T.create_uvw_tile_mapping(np.zeros((3, 3)), (1.0, 1.0, 1.0), freq)
+    assert m == {(0, 0, 0): [T.RowSliceId(0, 0, 2), T.RowSliceId(1, 0, 2), T.RowSliceId(2, 0, 2)]}
+    with pytest.raises(IndexError):  # the reference indexes channel 0 of an empty frequency axis
+        T.create_uvw_tile_mapping(np.zeros((3, 3)), (1.0, 1.0, 1.0), np.zeros(0))
+    with pytest.raises(ValueError):
+        T.create_uvw_tile_mapping(np.zeros((3, 2)), (1.0, 1.0, 1.0), freq)
+    with pytest.raises(ValueError):
+        T.create_uvw_tile_mapping(np.zeros((3, 3)), (0.0, 1.0, 1.0), freq)
+
+
+def test_row_blocks_merge_like_the_reference_pool(T):
+    """tiling_plan.py:114-147: binning row blocks with offsets and merging equals one pass."""
+    rng = np.random.default_rng(9)
+    uvw = rng.normal(size=(4001, 3)) * np.array([4000, 4000, 300.0])
+    freq = 856e6 + np.arange(64) * 214e6 / 256
+    ts = (500.0, 500.0, 1000.0)
+    whole = T.create_uvw_tile_mapping(uvw, ts, freq)
+    block = -(-len(uvw) // 3)
+    parts = [T.create_uvw_tile_mapping_sequential(uvw[a:a + block], ts, freq, row_offset=a)
+             for a in range(0, len(uvw), block)]
+    merged = T.merge_tile_mappings(parts)
+    assert list(merged) == list(whole) and merged == whole
+
+
+def test_full_size_ska_low_binning_properties(T):
+    """BASELINE.json configs[2] (130,816 baselines x 32 times x 128 channels = 5.36e8 samples): too big for
+    the oracle, so check what must hold at any size -- every sample covered exactly once, slices
+    sorted by (irow, chan_start) inside each tile, tile keys unique and in first-appearance order,
+    and the tile index of sampled slices recomputed on the host with the reference formula."""
+    from ska_sdp_cip import synthetic as S
+    cfg = S.ska_low()
+    uvw, freq = S.make_uvw(cfg), cfg.frequencies()
+    ts = (200.0, 200.0, 400.0)
+    dm = T.device_tile_mapping(uvw, ts, freq)
+    coords, offsets, irow, c0, c1 = dm.arrays()
+    assert offsets[0] == 0 and offsets[-1] == dm.n_slices == len(irow) and np.all(np.diff(offsets) > 0)
+    assert len(np.unique(coords, axis=0)) == dm.n_tiles
+    length = (c1 - c0).astype(np.int64)
+    assert length.min() > 0 and int(length.sum()) == cfg.n_vis
+    # per row: the slices tile [0, nchan) without gap or overlap (checksum of checksums)
+    per_row = np.bincount(irow, weights=length, minlength=cfg.n_rows)
+    assert np.all(per_row == cfg.n_chan)
+    sq = np.bincount(irow, weights=(c1.astype(np.float64) ** 2 - c0.astype(np.float64) ** 2), minlength=cfg.n_rows)
+    assert np.all(sq == cfg.n_chan ** 2)  # sum (b^2 - a^2) telescopes to nchan^2 only for a gap-free cover
+    tile_of_slice = np.repeat(np.arange(dm.n_tiles), np.diff(offsets))
+    key = irow * (cfg.n_chan + 1) + c0
+    same_tile = tile_of_slice[1:] == tile_of_slice[:-1]
+    assert np.all(key[1:][same_tile] > key[:-1][same_tile])
+    # first-appearance order: the first slice of each tile is ordered by (irow, chan_start)
+    first = key[offsets[:-1]]
+    assert np.all(np.diff(first) > 0)
+    # sampled slices: both end channels have the tile's index, the neighbours outside do not
+    rng = np.random.default_rng(1)
+    pick = rng.integers(0, dm.n_slices, 20000)
+    idx = lambda r, ch: np.floor((freq[ch] / 299792458.0)[:, None] * (uvw[r] / np.array(ts)) + 0.5).astype(np.int64)
+    want = coords[tile_of_slice[pick]]
+    assert np.array_equal(idx(irow[pick], c0[pick]), want)
+    assert np.array_equal(idx(irow[pick], c1[pick] - 1), want)
+    inner = pick[c0[pick] > 0]
+    assert np.all(np.any(idx(irow[inner], c0[inner] - 1) != coords[tile_of_slice[inner]], axis=1))

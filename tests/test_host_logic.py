@@ -1,0 +1,189 @@
+"""Host-side mirror of the reference interface (no GPU): partitioning, chunked reads, result types,
+Tile containers, synthetic generators.  The cases follow the reference's own tests
+(tests/test_measurement_set_partition_indices.py, tests/test_measurement_set_chunked_read.py)."""
+import numpy as np
+import pytest
+
+from oracle import partition as opart
+
+from ska_sdp_cip import measurement_set as MS
+from ska_sdp_cip import synthetic as S
+from ska_sdp_cip.uvw_tiling import RowSliceId, Tile, merge_tile_mappings
+
+
+def make_reader(nrow=74214, nchan=4, seed=0, dense=False):
+    rng = np.random.default_rng(seed)
+    uvw = rng.normal(size=(nrow, 3)) * 1000.0
+    freqs = 1.4e9 + 1e6 * np.arange(nchan)
+    if dense:
+        vis = (rng.normal(size=(nrow, nchan, 4)) + 1j * rng.normal(size=(nrow, nchan, 4))).astype(np.complex64)
+        flags = rng.random((nrow, nchan, 4)) < 0.05
+        wgt = rng.uniform(0.5, 1.5, (nrow, nchan, 4)).astype(np.float32)
+    else:  # broadcast views: shape without memory
+        vis = np.broadcast_to(np.complex64(1), (nrow, nchan, 4))
+        flags = np.broadcast_to(np.False_, (nrow, nchan, 4))
+        wgt = np.broadcast_to(np.float32(1), (nrow, nchan, 4))
+    return MS.ArrayMeasurementSetReader(uvw, freqs, vis, flags, wgt)
+
+
+# the reference's golden partition indices (tests/test_measurement_set_partition_indices.py:33-61)
+REFERENCE_PARTITIONS = [
+    (1, 1, [(0, 74214, 0, 4)]),
+    (2, 3, [(0, 37107, 0, 2), (0, 37107, 2, 3), (0, 37107, 3, 4),
+            (37107, 74214, 0, 2), (37107, 74214, 2, 3), (37107, 74214, 3, 4)]),
+    (5, 1, [(0, 14843, 0, 4), (14843, 29686, 0, 4), (29686, 44529, 0, 4), (44529, 59372, 0, 4),
+            (59372, 74214, 0, 4)]),
+]
+
+
+@pytest.mark.parametrize("row_chunks,freq_chunks,expected", REFERENCE_PARTITIONS)
+def test_partition_indices_match_reference_golden(row_chunks, freq_chunks, expected):
+    chunks = make_reader().partition(row_chunks, freq_chunks)
+    assert [(c.row_start, c.row_end, c.channel_start, c.channel_end) for c in chunks] == expected
+    assert opart.partition_bounds(74214, 4, row_chunks, freq_chunks) == expected
+
+
+def test_partition_raises_on_excessive_num_chunks():
+    r = make_reader()
+    with pytest.raises(ValueError):
+        r.partition(1_000_000, 1)
+    with pytest.raises(ValueError):
+        r.partition(1, 1_000_000)
+
+
+def test_balanced_chunks_match_golden_fixture(golden):
+    for key, want in golden("partition").items():
+        _, a, b, k = key.split("_")
+        assert np.array_equal(np.array(list(MS.balanced_chunk_bounds(int(a), int(b), int(k)))), want), key
+    with pytest.raises(ValueError):
+        list(MS.balanced_chunk_sizes(4, 5))
+    with pytest.raises(ValueError):
+        list(MS.balanced_chunk_sizes(0, 1))
+
+
+@pytest.mark.parametrize("method", ["visibilities", "flags", "weights", "uvw", "channel_frequencies"])
+@pytest.mark.parametrize("row_chunks,freq_chunks", [(1, 4), (2, 3), (7, 1)])
+def test_chunked_read_reassembles_full_read(method, row_chunks, freq_chunks):
+    # tests/test_measurement_set_chunked_read.py: concatenating chunk reads gives the full read
+    r = make_reader(nrow=301, nchan=4, dense=True)
+    full = getattr(r, method)()
+    chunks = r.partition(row_chunks, freq_chunks)
+    rows = []
+    for i in range(row_chunks):
+        parts = [getattr(c, method)() for c in chunks[i * freq_chunks:(i + 1) * freq_chunks]]
+        if method == "uvw":
+            rows.append(parts[0])
+            assert all(np.array_equal(p, parts[0]) for p in parts)
+        elif method == "channel_frequencies":
+            rows.append(np.concatenate(parts))
+        else:
+            rows.append(np.concatenate(parts, axis=1))
+    got = rows[0] if method == "channel_frequencies" else np.concatenate(rows, axis=0)
+    assert np.array_equal(got, full)
+
+
+def test_partition_of_a_chunk_stays_inside_it():
+    r = make_reader(nrow=100, nchan=8)
+    c = r.partition(3, 2)[3]
+    sub = c.partition(2, 2)
+    assert (sub[0].row_start, sub[-1].row_end) == (c.row_start, c.row_end)
+    assert (sub[0].channel_start, sub[-1].channel_end) == (c.channel_start, c.channel_end)
+
+
+def test_reader_validates_shapes():
+    with pytest.raises(ValueError):
+        MS.ArrayMeasurementSetReader(np.zeros((3, 3)), np.zeros(2), np.zeros((3, 2, 2), np.complex64),
+                                     np.zeros((3, 2, 2), bool), np.zeros((3, 2, 2), np.float32))
+    with pytest.raises(ValueError):
+        MS.ArrayMeasurementSetReader(np.zeros((4, 3)), np.zeros(2), np.zeros((3, 2, 4), np.complex64),
+                                     np.zeros((3, 2, 4), bool), np.zeros((3, 2, 4), np.float32))
+
+
+def test_casacore_reader_errors(tmp_path):
+    with pytest.raises(FileNotFoundError):
+        MS.MeasurementSetReader("/nonexistent.ms")
+    try:
+        import casacore  # noqa: F401
+        pytest.skip("casacore is installed")
+    except ImportError:
+        pass
+    with pytest.raises(ImportError):
+        MS.MeasurementSetReader(tmp_path)
+
+
+def test_merge_tile_mappings_keeps_first_appearance_order():
+    a = {(0, 0, 0): [RowSliceId(0, 0, 4)], (1, 0, 0): [RowSliceId(1, 0, 2)]}
+    b = {(1, 0, 0): [RowSliceId(5, 2, 4)], (2, 2, 2): [RowSliceId(6, 0, 4)]}
+    m = merge_tile_mappings([a, b])
+    assert list(m) == [(0, 0, 0), (1, 0, 0), (2, 2, 2)]
+    assert m[(1, 0, 0)] == [RowSliceId(1, 0, 2), RowSliceId(5, 2, 4)]
+    assert a[(1, 0, 0)] == [RowSliceId(1, 0, 2)]  # inputs untouched
+
+
+def test_tile_container_matches_reference_golden(golden, tmp_path):
+    g = golden("tiling_small_tiles")
+    from oracle import tiling
+    off = int(g["row_offset"])
+    uvw, freq = g["uvw"], g["freq"]
+    rng = np.random.default_rng(int(g["vis_seed"]))
+    vis = (rng.normal(size=(len(uvw), len(freq))) + 1j * rng.normal(size=(len(uvw), len(freq)))).astype(np.complex64)
+    mapping = tiling.tile_mapping(uvw, tuple(g["tile_size"]), freq, row_offset=off)
+    key = list(mapping)[0]
+    slices = [RowSliceId(r - off, a, b) for r, a, b in mapping[key]]
+    t = Tile._from_jagged_visibilities_slice(vis, uvw, key, slices)
+    assert np.array_equal(t.uvw, g["tile0_uvw"]) and np.array_equal(t.visibilities, g["tile0_vis"])
+    assert np.array_equal(t.channel_start_indices, g["tile0_start"])
+    assert np.array_equal(t.channel_stop_indices, g["tile0_stop"])
+    assert t.num_rows == len(slices) and t.num_visibilities == sum(b - a for _, a, b in slices)
+    p = tmp_path / "tile.npz"
+    t.save_npz(p)
+    with np.load(p) as z:
+        assert sorted(z.files) == ["channel_start_indices", "channel_stop_indices", "coords", "uvw", "visibilities"]
+    u = Tile.load_npz(p)
+    assert u.coords == key and np.array_equal(u.visibilities, t.visibilities) and np.array_equal(u.uvw, t.uvw)
+    z = Tile._zeros((1, 2, 3), 4, 9)
+    assert z.uvw.shape == (4, 3) and z.visibilities.dtype == np.complex64 and z.num_visibilities == 9
+
+
+def test_synthetic_configurations_have_the_baseline_shapes():
+    mid, low = S.ska_mid(), S.ska_low()
+    assert (mid.n_baselines, mid.n_rows, mid.n_vis) == (10296, 2635776, 168689664)
+    assert (low.n_baselines, low.n_rows, low.n_vis) == (130816, 4186112, 535822336)
+    cfg4 = S.ska_mid(n_times=512, n_chan=256, num_pixels=16384, dfreq_hz=0.5e6)
+    assert cfg4.n_vis == 1349517312
+    uvw = S.make_uvw(S.ska_mid(n_times=4))
+    assert uvw.shape == (4 * 10296, 3) and uvw.dtype == np.float64
+    # a time range of a longer observation is the same rows as the slice of the whole
+    whole = S.make_uvw(S.ska_mid(n_times=8))
+    part = S.make_uvw(S.ska_mid(n_times=8), (4, 8))
+    assert np.array_equal(whole[4 * 10296:], part)
+    px = S.pixel_size_lm(mid, uvw)
+    lam = 299792458.0 / mid.frequencies().max()
+    assert np.abs(uvw[:, :2]).max() / lam * px <= 0.4 + 1e-12
+
+
+def test_synthetic_visibilities_image_to_their_sources():
+    """One source, no noise: the dirty image at the source pixel is the flux (the generator uses
+    the sign convention of the gridder's measurement equation)."""
+    cfg = S.meerkat_like(num_pixels=128)
+    full = S.make_uvw(cfg)
+    uvw = full[:: len(full) // 3000][:3000]
+    freq = cfg.frequencies()
+    px = S.pixel_size_lm(cfg, full)
+    vis, wgt = S.make_vis_numpy(cfg, uvw, freq, px, noise=0.0, flag_fraction=0.0)
+    assert vis.dtype == np.complex64 and wgt.dtype == np.float32 and vis.shape == (3000, len(freq))
+    from oracle import dft
+    l, m, flux, pi, pj = S.source_list(cfg, px)
+    # rebuild the model from the documented formula and image each source separately
+    finv = freq / 299792458.0
+    model = np.zeros(vis.shape, dtype=np.complex128)
+    for k in range(len(flux)):
+        nm1 = -(l[k] ** 2 + m[k] ** 2) / (np.sqrt(1 - l[k] ** 2 - m[k] ** 2) + 1)
+        ph = (uvw[:, 0] * l[k] + uvw[:, 1] * m[k] - uvw[:, 2] * nm1)[:, None] * finv[None, :]
+        one = flux[k] * np.exp(-2j * np.pi * ph)
+        model += one
+        pix = np.array([pi[k] * cfg.num_pixels + pj[k]])
+        peak = dft.dft_dirty(uvw, freq, one.astype(np.complex64), wgt, cfg.num_pixels, cfg.num_pixels, px, px,
+                             pixels=pix)[0] / wgt.sum() * (1 + nm1)
+        assert peak == pytest.approx(flux[k], rel=1e-5)
+    assert np.allclose(vis, model.astype(np.complex64), atol=1e-5)
