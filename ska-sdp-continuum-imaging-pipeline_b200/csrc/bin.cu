@@ -97,9 +97,15 @@ __global__ void __launch_bounds__(256) runs_kernel(DevInputs in, GridGeom g, int
         const uint32_t p0r = (uint32_t)(s.p0 - win * g.win_step);
         Rec<R> rec;
         rec.cell = i0r | (j0r << 5) | (p0r << 10);
-        rec.fu = s.fu;
-        rec.fv = s.fv;
-        rec.fw = s.fw;
+        if constexpr (sizeof(R) == 4) {
+          rec.fu = s.fu;
+          rec.fv = s.fv;
+          rec.fw = s.fw;
+        } else {
+          rec.fu = to_fix32(s.dfu);
+          rec.fv = to_fix32(s.dfv);
+          rec.fw = to_fix32(s.dfw);
+        }
         rec.re = re;
         rec.im = im;
         if constexpr (sizeof(R) == 4) rec.pad[0] = rec.pad[1] = 0.f;

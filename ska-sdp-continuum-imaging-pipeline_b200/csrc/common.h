@@ -80,6 +80,7 @@ struct FftPlan {
 //   cell  bits 0-4 i0 (u cell of the support origin inside the tile, 0..kTile-1), 5-9 j0,
 //         10-13 first plane relative to the window start
 //   fu, fv, fw  distance of the first cell / plane from the left edge of the support, in [0,1)
+//               (float32 in Rec<float>, 0.32 fixed point in Rec<double>)
 //   re, im      weighted, conjugated-if-flipped, n-shift-rotated visibility (R = float or double)
 template <typename R>
 struct __align__(32) Rec;
@@ -93,9 +94,10 @@ struct __align__(32) Rec<float> {
 template <>
 struct __align__(32) Rec<double> {
   uint32_t cell;
-  float fu, fv, fw;
-  double re, im;
+  uint32_t fu, fv, fw;  // the same fractions as 0.32 fixed point (2.3e-10 of a cell): float32 would cap the
+  double re, im;        // accuracy of the float64 path near 1e-7
 };
+constexpr double kFix32 = 4294967296.0;
 static_assert(sizeof(Rec<float>) == 32 && sizeof(Rec<double>) == 32, "records are one sector");
 inline size_t recs_bytes(int64_t nrec) { return (size_t)nrec * 32; }
 
@@ -128,6 +130,7 @@ struct GridGeom {
   int ntu, ntv;           // tiles per axis
   int do_wstacking;
   float beta_w;           // beta * W
+  double beta_wd;         // the same in float64 (float64 path)
 };
 
 }  // namespace cip

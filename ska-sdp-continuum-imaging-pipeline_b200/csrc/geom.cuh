@@ -8,6 +8,7 @@ namespace cip {
 struct SampleGeom {
   int i0, j0, p0;     // first cell (shifted coordinates: zero frequency at nu/2) and first plane
   float fu, fv, fw;   // i0 - left edge of the support, in [0,1)
+  double dfu, dfv, dfw;  // the same in float64 (records of the float64 path)
   bool flip;          // w < 0: sample replaced by its Hermitian conjugate
   double w;           // |w| in wavelengths
 };
@@ -32,8 +33,10 @@ __device__ __forceinline__ SampleGeom sample_geom(const GridGeom& g, double um, 
   double ci = ceil(us), cj = ceil(vs);
   s.i0 = (int)ci;
   s.j0 = (int)cj;
-  s.fu = (float)(ci - us);
-  s.fv = (float)(cj - vs);
+  s.dfu = ci - us;
+  s.dfv = cj - vs;
+  s.fu = (float)s.dfu;
+  s.fv = (float)s.dfv;
   if (g.do_wstacking) {
     double ps = (w - g.w0) * g.inv_dw - 0.5 * g.W;
     double cp = ceil(ps);
@@ -45,11 +48,12 @@ __device__ __forceinline__ SampleGeom sample_geom(const GridGeom& g, double um, 
       cp = (double)p0;
     }
     s.p0 = p0;
-    float fw = (float)(cp - ps);
-    s.fw = fminf(fmaxf(fw, 0.0f), 1.0f);
+    s.dfw = fmin(fmax(cp - ps, 0.0), 1.0);
+    s.fw = (float)s.dfw;
   } else {
     s.p0 = 0;
     s.fw = 0.0f;
+    s.dfw = 0.0;
   }
   return s;
 }
@@ -83,5 +87,16 @@ __device__ __forceinline__ float es_kernel(float x, float beta_w) {
   float t = 1.0f - x * x;
   return t >= 0.0f ? expf(beta_w * (sqrtf(t) - 1.0f)) : 0.0f;
 }
+
+__device__ __forceinline__ double es_kernel(double x, double beta_w) {
+  double t = 1.0 - x * x;
+  return t >= 0.0 ? exp(beta_w * (sqrt(t) - 1.0)) : 0.0;
+}
+
+__device__ __forceinline__ uint32_t to_fix32(double f) {
+  double v = f * kFix32;
+  return v >= 4294967295.0 ? 0xffffffffu : (uint32_t)v;
+}
+__device__ __forceinline__ double from_fix32(uint32_t v) { return (double)v * (1.0 / kFix32); }
 
 }  // namespace cip

@@ -73,13 +73,30 @@ template <> struct StageVal<float> { using type = float4; };    // (re, re, im, 
 template <> struct StageVal<double> { using type = double2; };  // (re, im)
 
 template <typename R>
-struct alignas(16) Stage {
+struct Stage;
+
+template <>
+struct alignas(16) Stage<float> {
+  using R = float;
   float2 ku[kBatch][8];   // (k, k): weight of u residue class r for visibility k (0 outside the support)
   float2 kv[kBatch][4];   // (class b, class b + 4)
   float2 kw[kBatch][8];   // (k, k): the 8 plane weights of the window
   typename StageVal<R>::type val[kBatch];
   uint32_t org[kBatch];   // register-window origin: bits 0-4 u cell, 5-9 v cell (sub-grid coordinates)
   uint32_t moved;         // bit k: the window of visibility k differs from that of visibility k-1
+  uint32_t pad[3];
+};
+
+// float64 path: weights in float64 (the float32 hardware approximations of es_fast would cap the
+// accuracy near 1e-6), no pair duplication (the consumer uses scalar DFMA)
+template <>
+struct alignas(16) Stage<double> {
+  double ku[kBatch][8];   // weight of u residue class r
+  double kv[kBatch][8];   // weight of v residue class r
+  double kw[kBatch][8];   // the 8 plane weights of the window
+  double2 val[kBatch];    // (re, im)
+  uint32_t org[kBatch];
+  uint32_t moved;
   uint32_t pad[3];
 };
 
@@ -93,18 +110,49 @@ __device__ __forceinline__ Rec<R> load_rec(const Rec<R>* __restrict__ recs, int6
   return r;
 }
 
-template <typename R>
-__device__ __forceinline__ void produce(Stage<R>& st, const Rec<R>& rec, bool valid, int lane, uint32_t& carry,
-                                        const GridGeom& g, float bw2, float two_over_w, int snap) {
-  const int W = g.W;
-  const int i0 = rec.cell & 31, j0 = (rec.cell >> 5) & 31, p0 = (rec.cell >> 10) & 15;
+// Register-window origin of a record and the "window moved" mask of the batch (common to both precisions).
+__device__ __forceinline__ uint32_t window_origin(uint32_t cell, bool valid, int lane, uint32_t& carry, int snap,
+                                                  uint32_t* moved) {
+  const int i0 = cell & 31, j0 = (cell >> 5) & 31;
   // register window: origin snapped to a lattice of `snap` cells, so that nearby supports share it
   const uint32_t wxy = (uint32_t)(i0 - i0 % snap) | ((uint32_t)(j0 - j0 % snap) << 5);
   const uint32_t cxy = valid ? wxy : carry;
   uint32_t prev = __shfl_up_sync(0xffffffffu, cxy, 1);
   if (lane == 0) prev = carry;
   carry = __shfl_sync(0xffffffffu, cxy, 31);
-  const uint32_t moved = __ballot_sync(0xffffffffu, cxy != prev);
+  *moved = __ballot_sync(0xffffffffu, cxy != prev);
+  return cxy;
+}
+
+__device__ __forceinline__ void produce(Stage<double>& st, const Rec<double>& rec, bool valid, int lane, uint32_t& carry,
+                                        const GridGeom& g, float, float, int snap) {
+  const int W = g.W;
+  const int i0 = rec.cell & 31, j0 = (rec.cell >> 5) & 31, p0 = (rec.cell >> 10) & 15;
+  uint32_t moved;
+  const uint32_t cxy = window_origin(rec.cell, valid, lane, carry, snap, &moved);
+  const double fu = from_fix32(rec.fu), fv = from_fix32(rec.fv), fw = from_fix32(rec.fw);
+  const double two_over_w = 2.0 / (double)W, bw = g.beta_wd;
+#pragma unroll
+  for (int r = 0; r < 8; ++r) {
+    const int da = (r - i0) & 7, db = (r - j0) & 7, dc = r - p0;
+    st.ku[lane][r] = da < W ? es_kernel(fma(fu + (double)da, two_over_w, -1.0), bw) : 0.0;
+    st.kv[lane][r] = db < W ? es_kernel(fma(fv + (double)db, two_over_w, -1.0), bw) : 0.0;
+    double kw = (dc >= 0 && dc < W) ? es_kernel(fma(fw + (double)dc, two_over_w, -1.0), bw) : 0.0;
+    if (!g.do_wstacking) kw = r == 0 ? 1.0 : 0.0;
+    st.kw[lane][r] = kw;
+  }
+  st.val[lane] = valid ? make_double2(rec.re, rec.im) : make_double2(0.0, 0.0);
+  st.org[lane] = cxy;
+  if (lane == 0) st.moved = moved;
+}
+
+__device__ __forceinline__ void produce(Stage<float>& st, const Rec<float>& rec, bool valid, int lane, uint32_t& carry,
+                                        const GridGeom& g, float bw2, float two_over_w, int snap) {
+  using R = float;
+  const int W = g.W;
+  const int i0 = rec.cell & 31, j0 = (rec.cell >> 5) & 31, p0 = (rec.cell >> 10) & 15;
+  uint32_t moved;
+  const uint32_t cxy = window_origin(rec.cell, valid, lane, carry, snap, &moved);
   float ku[8], kv[8], kw[8];
 #pragma unroll
   for (int r = 0; r < 8; ++r) {
@@ -134,8 +182,7 @@ __device__ __forceinline__ void produce(Stage<R>& st, const Rec<R>& rec, bool va
   pv[0 ^ sv] = make_float4(kv[0], kv[4], kv[1], kv[5]);
   pv[1 ^ sv] = make_float4(kv[2], kv[6], kv[3], kv[7]);
   const R re = valid ? rec.re : (R)0, im = valid ? rec.im : (R)0;
-  if constexpr (sizeof(R) == 4) st.val[lane] = make_float4(re, re, im, im);
-  else st.val[lane] = make_double2(re, im);
+  st.val[lane] = make_float4(re, re, im, im);
   st.org[lane] = cxy;
   if (lane == 0) st.moved = moved;
 }
@@ -222,10 +269,9 @@ struct Acc<float> {
 template <>
 struct Acc<double> {
   struct Ops {
-    float ku;
-    float2 kv;
+    double ku, kv0, kv1;
     double2 val;
-    float kw[8];
+    double kw[8];
   };
   double2 a[2][8];
   __device__ __forceinline__ void clear() {
@@ -243,23 +289,23 @@ struct Acc<double> {
   }
   template <int U>
   static __device__ __forceinline__ Ops load(const Group& gp) {
-    constexpr int sw = (U >> 1) & 3, sv = (U >> 2) & 1;
     const Stage<double>& st = *gp.st;
     const int k = min(gp.k0 + U, kBatch - 1);
     Ops o;
-    o.ku = st.ku[k][gp.a8 ^ (2 * sw)].x;
-    o.kv = st.kv[k][(((gp.b4 >> 1) ^ sv) << 1) | (gp.b4 & 1)];
+    o.ku = st.ku[k][gp.a8];
+    o.kv0 = st.kv[k][gp.b4];
+    o.kv1 = st.kv[k][gp.b4 + 4];
     o.val = st.val[k];
 #pragma unroll
-    for (int c = 0; c < 8; ++c) o.kw[c] = st.kw[k][c ^ (2 * sw)].x;
+    for (int c = 0; c < 8; ++c) o.kw[c] = st.kw[k][c];
     return o;
   }
   __device__ __forceinline__ void update(const Ops& o) {
-    const double w0 = (double)o.ku * (double)o.kv.x, w1 = (double)o.ku * (double)o.kv.y;
+    const double w0 = o.ku * o.kv0, w1 = o.ku * o.kv1;
     const double tr0 = o.val.x * w0, ti0 = o.val.y * w0, tr1 = o.val.x * w1, ti1 = o.val.y * w1;
 #pragma unroll
     for (int c = 0; c < 8; ++c) {
-      const double w = (double)o.kw[c];
+      const double w = o.kw[c];
       a[0][c].x = fma(tr0, w, a[0][c].x);
       a[0][c].y = fma(ti0, w, a[0][c].y);
       a[1][c].x = fma(tr1, w, a[1][c].x);
@@ -370,7 +416,7 @@ __global__ void __launch_bounds__(kGridThreads) grid_kernel(const Item* __restri
       const int kn = (b + 1) * kBatch + lane;
       const bool nxt_valid = kn < nrec;
       Rec<R> nxt = load_rec(recs, base + kn, nxt_valid);
-      produce<R>(stages[s], cur, cur_valid, lane, carry, g, bw2, two_over_w, snap);
+      produce(stages[s], cur, cur_valid, lane, carry, g, bw2, two_over_w, snap);
       pair_sync();  // rendezvous b: batch b is ready, and the consumer has finished batch b-1 (stage s^1 is free)
       cur = nxt;
       cur_valid = nxt_valid;
@@ -468,23 +514,30 @@ __global__ void __launch_bounds__(128) grid_wide_kernel(const Item* __restrict__
     const Rec<R> rec = load_rec(recs, item.rec_begin + k, true);
     if (rec.re == 0 && rec.im == 0) continue;
     const int i0 = rec.cell & 31, j0 = (rec.cell >> 5) & 31, p0 = rec.cell >> 10;
-    float kv[kMaxSupport];
-    for (int b = 0; b < W; ++b) kv[b] = es_kernel((2.0f * (rec.fv + b) - W) / W, g.beta_w);
+    // kernel weights in the precision of the grids: float32 evaluation of a wide ES kernel loses ~1e-5
+    R fu, fv, fw, bw;
+    if constexpr (sizeof(R) == 4) {
+      fu = rec.fu; fv = rec.fv; fw = rec.fw; bw = g.beta_w;
+    } else {
+      fu = from_fix32(rec.fu); fv = from_fix32(rec.fv); fw = from_fix32(rec.fw); bw = g.beta_wd;
+    }
+    R kv[kMaxSupport];
+    for (int b = 0; b < W; ++b) kv[b] = es_kernel(((R)2 * (fv + b) - W) / W, bw);
     for (int c = 0; c < (g.do_wstacking ? W : 1); ++c) {
       int plane = p0 + c, slot = plane - plane_base;
       if (plane >= g.nplanes || slot < 0 || slot >= nslots) continue;
-      float kw = g.do_wstacking ? es_kernel((2.0f * (rec.fw + c) - W) / W, g.beta_w) : 1.0f;
+      R kw = g.do_wstacking ? es_kernel(((R)2 * (fw + c) - W) / W, bw) : (R)1;
       for (int a = 0; a < W; ++a) {
-        float ku = es_kernel((2.0f * (rec.fu + a) - W) / W, g.beta_w) * kw;
+        R ku = es_kernel(((R)2 * (fu + a) - W) / W, bw) * kw;
         int gi = (su0 + i0 + a) % g.nu;
         if (gi < 0) gi += g.nu;
-        R tr = (R)rec.re * (R)ku, ti = (R)rec.im * (R)ku;
+        R tr = rec.re * ku, ti = rec.im * ku;
         for (int b = 0; b < W; ++b) {
           int gj = (sv0 + j0 + b) % g.nv;
           if (gj < 0) gj += g.nv;
           R* dst = grid + 2 * (((int64_t)slot * g.nu + gi) * g.nv + gj);
-          atomicAdd(dst, tr * (R)kv[b]);
-          atomicAdd(dst + 1, ti * (R)kv[b]);
+          atomicAdd(dst, tr * kv[b]);
+          atomicAdd(dst + 1, ti * kv[b]);
         }
       }
     }

@@ -71,9 +71,7 @@ static cip_status grid_accumulate_staged(cip_ctx* ctx, const DevInputs& in, cip_
   if (max_slots >= plan->nplanes) {
     nslots_alloc = plan->nplanes;
   } else {
-    CIP_REQUIRE(g.W <= kFastSupport, "the wide-support gridder needs all %d planes resident (%lld fit)",
-                plan->nplanes, (long long)max_slots);
-    if (max_slots < kWin) {
+    if (max_slots < (g.W <= kFastSupport ? kWin : 1)) {
       set_error("not enough device memory for one window of %d planes of %zu bytes", kWin, plane_bytes);
       return CIP_ENOMEM;
     }
@@ -81,6 +79,28 @@ static cip_status grid_accumulate_staged(cip_ctx* ctx, const DevInputs& in, cip_
   }
   plan->plane_block = nslots_alloc;
   CIP_TRY(ctx->grid.ensure(plane_bytes * nslots_alloc));
+
+  if (g.W > kFastSupport && nslots_alloc < plan->nplanes) {
+    // Wide supports have a single window; blocks of resident planes each take a pass over all
+    // records (the kernel skips contributions to planes outside the block).
+    for (int pb = 0; pb < plan->nplanes; pb += nslots_alloc) {
+      const int used = std::min(nslots_alloc, plan->nplanes - pb);
+      tm.start();
+      CIP_CHECK_CUDA(cudaMemsetAsync(ctx->grid.p, 0, plane_bytes * used, ctx->stream));
+      tm.stop(rep ? &rep->ms_zero : &dummy);
+      tm.start();
+      CIP_TRY(run_gridder(ctx, g, fp64, bins.nrec, 0, bins.nitems, ctx->grid.p, pb, used));
+      tm.stop(rep ? &rep->ms_grid : &dummy);
+      tm.start();
+      CIP_TRY(run_fft(ctx, ctx->grid.p, plan->nu, plan->nv, used, fp64));
+      tm.stop(rep ? &rep->ms_fft : &dummy);
+      tm.start();
+      CIP_TRY(run_wscreen(ctx, *plan, ctx->grid.p, pb, used, image_dev));
+      tm.stop(rep ? &rep->ms_wscreen : &dummy);
+      if (rep) rep->nblocks++;
+    }
+    return CIP_OK;
+  }
 
   int w = 0;
   while (w < g.nwin) {

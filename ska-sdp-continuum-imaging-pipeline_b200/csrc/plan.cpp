@@ -120,6 +120,7 @@ GridGeom make_geom(const cip_plan& p) {
   g.nplanes = p.nplanes;
   g.do_wstacking = p.do_wstacking;
   g.beta_w = (float)(p.beta * p.support);
+  g.beta_wd = p.beta * p.support;
   if (p.support <= kFastSupport) {
     g.win_step = kWin - p.support + 1;
     int np0 = std::max(p.nplanes - p.support + 1, 1);  // number of distinct first planes

@@ -242,15 +242,21 @@ def test_device_inputs_match_host_inputs(wg, small):
     t = lambda a: torch.from_numpy(a).to(dev)
     out = wg.ms2dirty(t(uvw), t(freq), t(vis), t(wgt), nx, nx, px, px, epsilon=1e-4, do_wstacking=True)
     assert out.is_cuda and out.dtype == torch.float32
-    assert np.array_equal(out.cpu().numpy(), host)  # same kernels, same order: bit-identical
+    # same kernels on the same data; only the order of the sub-grid reductions into the plane stack differs
+    assert dft.rel_rms(out.cpu().numpy(), host) <= 2e-6
 
 
-def test_repeatable_bitwise(wg, small):
-    """No global atomics in the gridder: two runs give identical bits."""
+def test_repeatable_to_rounding(wg, small):
+    """Tiles are accumulated in shared memory in a fixed order; only the final reductions of the sub-grids
+    into the global plane stack (red.global.add) are unordered, so two runs agree to float32 rounding
+    in fp32 and to float64 rounding in fp64."""
     prob, _ = small
     a, _ = invert(wg, prob)
     b, _ = invert(wg, prob)
-    assert np.array_equal(a, b)
+    assert dft.rel_rms(a, b) <= 2e-6
+    a, _ = invert(wg, prob, double_precision_accumulation=True)
+    b, _ = invert(wg, prob, double_precision_accumulation=True)
+    assert dft.rel_rms(a, b) <= 1e-14
 
 
 def test_invalid_arguments_raise(wg, small):

@@ -93,12 +93,22 @@ def test_random_layouts_match_oracle(T, nrow, nchan, ts, seed):
 def test_half_integer_boundaries_round_like_numpy(T):
     """floor(x + 0.5) with x exactly on a boundary, negative zero, denormals and huge coordinates."""
     freq = np.array([299792458.0, 2 * 299792458.0])  # freq/c = 1, 2 exactly
-    vals = np.array([0.5, -0.5, 1.5, -1.5, 2.5, 0.49999999999999994, -0.0, 5e-324, 1e15 + 0.5, -1e15 - 0.5, 4503599627370495.5])
+    vals = np.array([0.5, -0.5, 1.5, -1.5, 2.5, 0.49999999999999994, -0.0, 5e-324, 2.0 ** 19 + 0.5, -2.0 ** 19 - 0.5,
+                     1048575.5, 0.25, -0.25, 0.75, -0.75])
     uvw = np.stack([vals, vals[::-1], np.zeros_like(vals)], axis=1)
     dm = T.device_tile_mapping(uvw, (1.0, 1.0, 1.0), freq)
     want = tiling.tile_mapping_arrays(uvw, (1.0, 1.0, 1.0), freq)
     for name, got, exp in zip(NAMES, dm.arrays(), want):
         assert np.array_equal(got, exp), name
+
+
+def test_tile_index_range_beyond_the_sort_key_is_refused(T):
+    """The three tile indices of all slices are packed into one 64-bit sort key; a layout whose index
+    extents need more bits is refused with ValueError (documented limit), never binned wrongly."""
+    freq = np.array([299792458.0])
+    uvw = np.array([[1e15, -1e15, 0.0], [-1e15, 1e15, 0.0]])
+    with pytest.raises(ValueError, match="too large"):
+        T.create_uvw_tile_mapping(uvw, (1.0, 1.0, 1.0), freq)
 
 
 def test_empty_and_degenerate_inputs(T):
