@@ -22,7 +22,7 @@ constexpr int kFastSupport = 8;   // widest kernel of the residue-owner gridder 
 constexpr int kMinSupport = 4;
 constexpr int kTile = 8;          // uv tile edge of the gridder, in grid cells
 constexpr int kHalo = 8;          // shift that keeps window origins non-negative (>= kMaxSupport/2)
-constexpr int kSub = kTile + kFastSupport - 1;  // sub-grid edge held in shared memory (23, odd on purpose)
+constexpr int kSub = kTile + kFastSupport - 1;  // sub-grid edge held in shared memory (15, odd on purpose)
 constexpr int kWin = 8;           // w planes of one gridding window (= planes per consumer thread)
 constexpr int kBatch = 32;        // visibilities per producer/consumer hand-over
 constexpr int kItemVis = 4096;    // visibilities per gridding work item (one CTA)
