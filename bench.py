@@ -53,7 +53,7 @@ def measured_peaks():
 class ClockSampler:
     """nvidia-smi clocks / throttle reasons sampled DURING the timed region."""
 
-    Q = ("index,clocks.sm,clocks.max.sm,power.draw,clocks_event_reasons.hw_slowdown,"
+    Q = ("timestamp,clocks.sm,clocks.max.sm,power.draw,clocks_event_reasons.hw_slowdown,"
          "clocks_event_reasons.hw_thermal_slowdown,clocks_event_reasons.sw_thermal_slowdown,"
          "clocks_event_reasons.sw_power_cap")
 
@@ -61,6 +61,11 @@ class ClockSampler:
         self.index = index
         self.f = tempfile.NamedTemporaryFile("w+", suffix=".csv", delete=False)
         self.p = None
+        self.window = None
+
+    def mark(self, t0: float, t1: float):
+        """Wall-clock window (time.time()) of the timed region: only samples inside it are reported."""
+        self.window = (t0, t1)
 
     def start(self):
         try:
@@ -82,6 +87,18 @@ class ClockSampler:
         self.f.flush()
         rows = [l.split(",") for l in Path(self.f.name).read_text().strip().splitlines() if l.count(",") >= 7]
         os.unlink(self.f.name)
+        if self.window and rows:
+            import datetime
+            inside = []
+            for r in rows:
+                try:
+                    ts = datetime.datetime.strptime(r[0].strip(), "%Y/%m/%d %H:%M:%S.%f").timestamp()
+                except ValueError:
+                    continue
+                if self.window[0] - 0.02 <= ts <= self.window[1] + 0.02:
+                    inside.append(r)
+            out["samples_total"] = len(rows)
+            rows = inside or rows[-3:]  # a region shorter than the sampling period: the samples right around it
         if not rows:
             return out
         sm = [float(r[1]) for r in rows if r[1].strip().replace(".", "").isdigit()]
@@ -202,10 +219,16 @@ def run_b200(args):
         barrier()
         e0, e1 = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
         e0.record(stream)
-        for _ in range(steps):
+        for i in range(steps):
             flush_buf.zero_()          # flush L2 between iterations (inputs are also >> L2)
             torch.cuda.synchronize()
+            t_host = time.perf_counter()
             fn()
+            if args.verbose:
+                torch.cuda.synchronize()
+                print(f"[rank {rank}] step {i}: {1e3 * (time.perf_counter() - t_host):.2f} ms (host clock)",
+                      file=sys.stderr, flush=True)
+        torch.cuda.current_stream(dev).synchronize()  # collectives run on torch's stream, the library on its own
         e1.record(stream)
         barrier()
         ms = e0.elapsed_time(e1)
@@ -215,14 +238,16 @@ def run_b200(args):
             ms = float(t.item())
         return ms
 
+    sampler = ClockSampler(local)
+    if rank == 0:
+        sampler.start()  # nvidia-smi takes a moment to start: launch it before the warm-up
     for _ in range(args.warmup):
         step_device()
     reports.clear()
-    sampler = ClockSampler(local)
-    if rank == 0:
-        sampler.start()
     l0 = ctx_launches(ctx)
+    w0 = time.time()
     ms_dev = timed(step_device, args.steps)
+    sampler.mark(w0, time.time())
     launches = ctx_launches(ctx) - l0
     clocks = sampler.stop() if rank == 0 else {}
     timed_reports = list(reports)
@@ -234,18 +259,25 @@ def run_b200(args):
     h_vis.copy_(d_vis)
     h_wgt.copy_(d_wgt)
     n_vis_np, n_wgt_np = h_vis.numpy(), h_wgt.numpy()
+    h_uvw, h_freq = torch.from_numpy(uvw).pin_memory(), torch.from_numpy(freq).pin_memory()
+    uvw_p, freq_p = h_uvw.numpy(), h_freq.numpy()  # every input of the e2e step sits in pinned host memory
     torch.cuda.synchronize()
+
+    host_reports = []
 
     def step_host():
         if world == 1:
-            return wgridder.ms2dirty(uvw, freq, n_vis_np, n_wgt_np, N, N, px, px, epsilon=cfg.epsilon,
-                                     do_wstacking=True)
-        shard = StokesIGridderInput(freq, None, uvw, n_vis_np, n_wgt_np)
+            img, info = wgridder.ms2dirty(uvw_p, freq_p, n_vis_np, n_wgt_np, N, N, px, px, epsilon=cfg.epsilon,
+                                          do_wstacking=True, return_info=True)
+            host_reports.append(info["report"])
+            return img
+        shard = StokesIGridderInput(freq_p, None, uvw_p, n_vis_np, n_wgt_np)
         img, plan_, sumw = accumulate_shards([shard], N, px, epsilon=cfg.epsilon)
         return reduce_and_correct(img, plan_, sumw, normalise=False).cpu().numpy()
 
     e2e_steps = max(1, min(args.steps, 3))
     step_host()
+    host_reports.clear()
     ms_e2e = timed(step_host, e2e_steps)
     h2d = int(n_vis_np.nbytes + n_wgt_np.nbytes + uvw.nbytes + freq.nbytes)
     d2h = int(N * N * 4)
@@ -266,7 +298,7 @@ def run_b200(args):
              ("ms_scan", "ms_bin", "ms_zero", "ms_grid", "ms_fft", "ms_wscreen", "ms_correct", "ms_total")}
     # ---- CPU baseline on a bounded sample -----------------------------------------------------
     cpu = None
-    if not args.no_cpu:
+    if not args.no_cpu and world == 1:  # rank 0 at N = 1 only
         r, dt, nv_s, cores = cpu_port_rate(cfg, px, 4)
         cpu = {"value": r, "unit": UNIT, "cores": cores, "kind": "port",
                "sample": f"first 4 of {cfg.n_times} time steps ({nv_s} visibilities), full {N}^2 image, {dt:.1f} s"}
@@ -282,7 +314,10 @@ def run_b200(args):
                    "sharding": "time ranges per rank, NCCL reduce-scatter + all-gather of the dirty image" if world > 1
                    else "single GPU"},
         "e2e": {"value": total_vis * e2e_steps / ms_e2e / 1e3, "unit": UNIT, "h2d_bytes_per_step": h2d,
-                "d2h_bytes_per_step": d2h, "steps": e2e_steps},
+                "d2h_bytes_per_step": d2h, "steps": e2e_steps,
+                "stage_ms": {k: float(np.mean([r[k] for r in host_reports])) for k in
+                             ("ms_h2d", "ms_scan", "ms_bin", "ms_grid", "ms_fft", "ms_d2h", "ms_total")}
+                if host_reports else None},
         "gpu_launches": int(launches),
         "roofline": {"bound": "hbm", "kernel": "grid_kernel<float>", "achieved": achieved, "peak": peak,
                      "unit": "GB/s", "frac": achieved / peak, "traffic": None, "peak_source": peak_kind,
@@ -310,6 +345,7 @@ def main():
     ap.add_argument("--impl", default="b200", choices=["b200", "reference"])
     ap.add_argument("--times", type=int, default=256, help="time steps per GPU (256 = BASELINE.json configs[1])")
     ap.add_argument("--no-cpu", action="store_true", help="skip the CPU baseline leg")
+    ap.add_argument("--verbose", action="store_true", help="per-step host timings on stderr")
     args = ap.parse_args()
     if args.impl == "reference":
         run_reference(args)

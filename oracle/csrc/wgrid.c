@@ -186,3 +186,14 @@ int oracle_num_threads(void)
   return 1;
 #endif
 }
+
+/* The timed CPU baseline uses every host core even when the launcher exported OMP_NUM_THREADS=1
+ * (torchrun does); n <= 0 leaves the setting alone. */
+void oracle_set_num_threads(int n)
+{
+#ifdef _OPENMP
+  if (n > 0) omp_set_num_threads(n);
+#else
+  (void)n;
+#endif
+}

@@ -38,6 +38,8 @@ def lib():
         _lib = C.CDLL(str(_build.build()))
         _lib.oracle_wg_bin.restype = C.c_int64
         _lib.oracle_num_threads.restype = C.c_int
+        _lib.oracle_set_num_threads.argtypes = [C.c_int]
+        _lib.oracle_set_num_threads(os.cpu_count() or 1)  # all host cores, whatever OMP_NUM_THREADS says
     return _lib
 
 

@@ -203,10 +203,7 @@ __global__ void fill_i64_kernel(int64_t* p, int64_t n, int64_t v) {
 
 template <typename T>
 cip_status d2h_scalar(cip_ctx* ctx, const T* dev, T* out) {
-  CIP_CHECK_CUDA(cudaMemcpyAsync(ctx->scan_host, dev, sizeof(T), cudaMemcpyDeviceToHost, ctx->stream));
-  CIP_CHECK_CUDA(cudaStreamSynchronize(ctx->stream));
-  *out = *static_cast<T*>(ctx->scan_host);
-  return CIP_OK;
+  return fetch_small(ctx, dev, sizeof(T), out);
 }
 
 inline int nblk(int64_t n, int per) { return (int)((n + per - 1) / per); }
@@ -333,8 +330,12 @@ cip_status run_binning(cip_ctx* ctx, const DevInputs& in, const GridGeom& g, int
   CIP_CHECK_CUDA(cudaGetLastError());
 
   std::vector<int64_t> h(g.nwin + 1);
-  CIP_CHECK_CUDA(cudaMemcpyAsync(h.data(), wis, sizeof(int64_t) * (g.nwin + 1), cudaMemcpyDeviceToHost, st));
-  CIP_CHECK_CUDA(cudaStreamSynchronize(st));
+  if (sizeof(int64_t) * (g.nwin + 1) <= kSmallHostBytes) {
+    CIP_TRY(fetch_small(ctx, wis, sizeof(int64_t) * (g.nwin + 1), h.data()));
+  } else {
+    CIP_CHECK_CUDA(cudaMemcpyAsync(h.data(), wis, sizeof(int64_t) * (g.nwin + 1), cudaMemcpyDeviceToHost, st));
+    CIP_CHECK_CUDA(cudaStreamSynchronize(st));
+  }
   h[g.nwin] = nitems;
   for (int w = g.nwin - 1; w >= 0; --w) h[w] = std::min(h[w], h[w + 1]);  // empty windows start where the next does
   out->win_item_start = h;

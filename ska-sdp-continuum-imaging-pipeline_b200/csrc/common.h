@@ -26,8 +26,12 @@ constexpr int kSub = kTile + kFastSupport - 1;  // sub-grid edge held in shared 
 constexpr int kWin = 8;           // w planes of one gridding window (= planes per consumer thread)
 constexpr int kBatch = 32;        // visibilities per producer/consumer hand-over
 constexpr int kItemVis = 4096;    // visibilities per gridding work item (one CTA)
+constexpr int kMaxChunks = 8;     // row chunks of the host -> device visibility stream
 
 void set_error(const char* fmt, ...);
+// CIP_TRACE=1: host wall-clock marks on stderr (development aid; no device synchronisation).
+void trace_mark(const char* label);
+double now_ms();  // host monotonic clock
 
 #define CIP_CHECK_CUDA(expr)                                                                       \
   do {                                                                                             \
@@ -140,14 +144,24 @@ struct cip_ctx {
   int sm_count = 148;
   size_t smem_optin = 0;
   cudaStream_t stream = nullptr;
+  cudaStream_t copy_stream = nullptr;          // host -> device visibility chunks, overlapped with compute
+  cudaEvent_t chunk_ev[cip::kMaxChunks] = {};  // chunk c of the visibilities has arrived
+  cudaEvent_t small_ev = nullptr;              // uvw, freq, weights and mask have arrived
+  cudaEvent_t sync_ev = nullptr;               // non-timing event for host-clock stage timing
+  double t_stage_begin = 0;                    // host clock (ms) when the staging of the current call began
   cudaEvent_t ev[16] = {};
+  // hand-over of staged host inputs from cip_scan to the cip_grid_accumulate that follows it
+  bool staged_valid = false;
+  const void* staged_key[4] = {};
+  int64_t staged_dims[4] = {};
   int64_t launches = 0;
   // inputs staged on the device when the caller passes host memory
   cip::DevBuf in_uvw, in_freq, in_vis, in_wgt, in_mask;
   cip::DevBuf out_img;
   // scan
   cip::DevBuf scan_out;
-  void* scan_host = nullptr;  // pinned
+  void* scan_host = nullptr;      // pinned + mapped (kSmallHostBytes): small results land here without a copy engine
+  void* scan_host_dev = nullptr;  // its device-side address
   // binning
   cip::DevBuf row_nruns, row_off, runs, run_keys, run_keys_alt, run_idx, run_idx_alt, runs_sorted, run_len,
       run_visoff, flags, group_start, item_idx, items, win_item_start, cub_tmp, recs;
@@ -182,8 +196,26 @@ struct DevInputs {
   int64_t nrow, nchan, vstride, wstride;
 };
 cip_status validate_args(const cip_invert_args* a);
-cip_status stage_inputs(cip_ctx* ctx, const cip_invert_args* a, DevInputs* d, double* ms_h2d);
+// Rows [row0[c], row0[c+1]) of the visibilities are on the device once ready[c] has fired.
+struct VisFeed {
+  int nchunks = 0;
+  int64_t row0[kMaxChunks + 1] = {};
+  cudaEvent_t ready[kMaxChunks] = {};
+};
+// Host inputs (memspace 0): uvw, freq, weights and mask are copied on the context stream (skipped when
+// `reuse_small` and the previous call was a cip_scan of the same arrays); when `feed` is given the
+// visibilities follow in row chunks on the copy stream, else they are not copied at all (cip_scan).
+// Device inputs (memspace 1) are used in place and the feed, if any, is a single chunk that is ready.
+cip_status stage_inputs(cip_ctx* ctx, const cip_invert_args* a, DevInputs* d, VisFeed* feed, bool reuse_small,
+                        double* ms_h2d);
+// Make the context stream wait for every chunk of the feed (for code that needs all visibilities).
+cip_status wait_feed(cip_ctx* ctx, const VisFeed& feed);
 float elapsed_ms(cip_ctx* ctx, int e0, int e1);
+// Bring `bytes` (a multiple of 4, <= kSmallHostBytes) of device memory to the host and wait for it.  A tiny
+// kernel writes them into mapped pinned memory: a cudaMemcpy here would queue on a copy engine
+// behind the visibility chunks that are streaming in and stall the compute stream until they are done.
+constexpr size_t kSmallHostBytes = 64 << 10;
+cip_status fetch_small(cip_ctx* ctx, const void* dev, size_t bytes, void* host_out);
 
 // ---- stages -----------------------------------------------------------------------
 cip_status run_scan(cip_ctx* ctx, const DevInputs& in, int do_wstacking, cip_scan_result* out);

@@ -1,5 +1,9 @@
 // Context, error reporting, device buffers and input staging of libcip_b200.so.
+#include <cstdlib>
 #include <cstring>
+#include <ctime>
+
+#include <algorithm>
 
 #include "common.h"
 
@@ -47,6 +51,21 @@ float elapsed_ms(cip_ctx* ctx, int e0, int e1) {
   return ms;
 }
 
+double now_ms() {
+  timespec ts;
+  clock_gettime(CLOCK_MONOTONIC, &ts);
+  return ts.tv_sec * 1e3 + ts.tv_nsec * 1e-6;
+}
+
+void trace_mark(const char* label) {
+  static const bool on = getenv("CIP_TRACE") != nullptr;
+  if (!on) return;
+  static double t0 = 0;
+  const double t = now_ms();
+  if (t0 == 0 || strcmp(label, "begin") == 0) t0 = t;
+  fprintf(stderr, "[cip trace] %8.3f ms  %s\n", t - t0, label);
+}
+
 cip_status validate_args(const cip_invert_args* a) {
   CIP_REQUIRE(a != nullptr, "args is NULL");
   CIP_REQUIRE(a->nrow >= 0 && a->nchan >= 0, "negative nrow/nchan");
@@ -62,15 +81,32 @@ cip_status validate_args(const cip_invert_args* a) {
   return CIP_OK;
 }
 
+// nrow rows of nchan elements, source row stride `stride` elements -> packed rows on the device.  Packed
+// sources go as ONE linear copy: a 2-D copy of millions of short rows is descriptor-bound.
+static cip_status copy_rows(void* dst, const void* src, size_t elem, int64_t nrow, int64_t nchan, int64_t stride,
+                            cudaStream_t st) {
+  if (stride == nchan) {
+    CIP_CHECK_CUDA(cudaMemcpyAsync(dst, src, elem * (size_t)nrow * nchan, cudaMemcpyHostToDevice, st));
+  } else {
+    CIP_CHECK_CUDA(cudaMemcpy2DAsync(dst, elem * nchan, src, elem * stride, elem * nchan, nrow, cudaMemcpyHostToDevice, st));
+  }
+  return CIP_OK;
+}
+
 // Host inputs are copied to context-owned device buffers (rows compacted to stride nchan);
-// device inputs are used in place.
-cip_status stage_inputs(cip_ctx* ctx, const cip_invert_args* a, DevInputs* d, double* ms_h2d) {
+// device inputs are used in place.  See common.h for the streaming contract.
+cip_status stage_inputs(cip_ctx* ctx, const cip_invert_args* a, DevInputs* d, VisFeed* feed, bool reuse_small,
+                        double* ms_h2d) {
   const int64_t nrow = a->nrow, nchan = a->nchan;
   const int64_t vs = a->vis_row_stride ? a->vis_row_stride : nchan;
   const int64_t ws = a->wgt_row_stride ? a->wgt_row_stride : nchan;
   d->nrow = nrow;
   d->nchan = nchan;
   if (ms_h2d) *ms_h2d = 0.0;
+  const bool reuse = reuse_small && ctx->staged_valid && a->memspace == 0 && ctx->staged_key[0] == a->uvw &&
+                     ctx->staged_key[1] == a->freq && ctx->staged_key[2] == a->wgt && ctx->staged_key[3] == a->mask &&
+                     ctx->staged_dims[0] == nrow && ctx->staged_dims[1] == nchan && ctx->staged_dims[2] == ws;
+  ctx->staged_valid = false;
   if (a->memspace == 1) {
     d->uvw = a->uvw;
     d->freq = a->freq;
@@ -79,44 +115,87 @@ cip_status stage_inputs(cip_ctx* ctx, const cip_invert_args* a, DevInputs* d, do
     d->mask = a->mask;
     d->vstride = vs;
     d->wstride = ws;
+    if (feed) {
+      feed->nchunks = 1;
+      feed->row0[0] = 0;
+      feed->row0[1] = nrow;
+      feed->ready[0] = nullptr;  // nothing to wait for
+    }
     return CIP_OK;
   }
   cudaStream_t st = ctx->stream;
-  CIP_CHECK_CUDA(cudaEventRecord(ctx->ev[14], st));
+  ctx->t_stage_begin = now_ms();
   CIP_TRY(ctx->in_uvw.ensure(sizeof(double) * 3 * (size_t)nrow + 8));
   CIP_TRY(ctx->in_freq.ensure(sizeof(double) * (size_t)nchan + 8));
-  CIP_TRY(ctx->in_vis.ensure(sizeof(float2) * (size_t)nrow * nchan + 8));
-  if (nrow && nchan) {
-    CIP_CHECK_CUDA(cudaMemcpyAsync(ctx->in_uvw.p, a->uvw, sizeof(double) * 3 * nrow, cudaMemcpyHostToDevice, st));
-    CIP_CHECK_CUDA(cudaMemcpyAsync(ctx->in_freq.p, a->freq, sizeof(double) * nchan, cudaMemcpyHostToDevice, st));
-    CIP_CHECK_CUDA(cudaMemcpy2DAsync(ctx->in_vis.p, sizeof(float2) * nchan, a->vis, sizeof(float2) * vs,
-                                     sizeof(float2) * nchan, nrow, cudaMemcpyHostToDevice, st));
-  }
+  if (a->wgt) CIP_TRY(ctx->in_wgt.ensure(sizeof(float) * (size_t)nrow * nchan + 8));
+  if (a->mask) CIP_TRY(ctx->in_mask.ensure((size_t)nrow * nchan + 8));
+  if (feed) CIP_TRY(ctx->in_vis.ensure(sizeof(float2) * (size_t)nrow * nchan + 8));
   d->uvw = ctx->in_uvw.as<double>();
   d->freq = ctx->in_freq.as<double>();
-  d->vis = ctx->in_vis.as<float2>();
+  d->vis = feed ? ctx->in_vis.as<float2>() : nullptr;
   d->vstride = nchan;
   d->wstride = nchan;
-  d->wgt = nullptr;
-  d->mask = nullptr;
-  if (a->wgt) {
-    CIP_TRY(ctx->in_wgt.ensure(sizeof(float) * (size_t)nrow * nchan + 8));
-    if (nrow && nchan)
-      CIP_CHECK_CUDA(cudaMemcpy2DAsync(ctx->in_wgt.p, sizeof(float) * nchan, a->wgt, sizeof(float) * ws,
-                                       sizeof(float) * nchan, nrow, cudaMemcpyHostToDevice, st));
-    d->wgt = ctx->in_wgt.as<float>();
+  d->wgt = a->wgt ? ctx->in_wgt.as<float>() : nullptr;
+  d->mask = a->mask ? ctx->in_mask.as<uint8_t>() : nullptr;
+  if (nrow && nchan && !reuse) {
+    CIP_CHECK_CUDA(cudaMemcpyAsync(ctx->in_uvw.p, a->uvw, sizeof(double) * 3 * nrow, cudaMemcpyHostToDevice, st));
+    CIP_CHECK_CUDA(cudaMemcpyAsync(ctx->in_freq.p, a->freq, sizeof(double) * nchan, cudaMemcpyHostToDevice, st));
+    if (a->wgt) CIP_TRY(copy_rows(ctx->in_wgt.p, a->wgt, sizeof(float), nrow, nchan, ws, st));
+    if (a->mask) CIP_TRY(copy_rows(ctx->in_mask.p, a->mask, 1, nrow, nchan, ws, st));
   }
-  if (a->mask) {
-    CIP_TRY(ctx->in_mask.ensure((size_t)nrow * nchan + 8));
-    if (nrow && nchan)
-      CIP_CHECK_CUDA(cudaMemcpy2DAsync(ctx->in_mask.p, nchan, a->mask, ws, nchan, nrow, cudaMemcpyHostToDevice, st));
-    d->mask = ctx->in_mask.as<uint8_t>();
+  CIP_CHECK_CUDA(cudaEventRecord(ctx->small_ev, st));
+  if (feed) {
+    // visibilities: row chunks of >= 64 MB on the copy stream, behind the small inputs so that the scan
+    // and the planning can start as early as possible
+    const size_t vis_bytes = sizeof(float2) * (size_t)nrow * nchan;
+    int nchunks = (int)std::min<size_t>(kMaxChunks, std::max<size_t>(1, vis_bytes >> 26));
+    if (const char* e = getenv("CIP_STREAM_CHUNKS")) nchunks = std::min(kMaxChunks, std::max(1, atoi(e)));  // tests
+    nchunks = (int)std::min<int64_t>(nchunks, std::max<int64_t>(nrow, 1));
+    feed->nchunks = nchunks;
+    CIP_CHECK_CUDA(cudaStreamWaitEvent(ctx->copy_stream, ctx->small_ev, 0));
+    for (int c = 0; c < nchunks; ++c) {
+      const int64_t r0 = nrow * c / nchunks, r1 = nrow * (c + 1) / nchunks;
+      feed->row0[c] = r0;
+      feed->row0[c + 1] = r1;
+      if (r1 > r0 && nchan)
+        CIP_TRY(copy_rows(ctx->in_vis.as<float2>() + r0 * nchan, static_cast<const float2*>(a->vis) + r0 * vs,
+                          sizeof(float2), r1 - r0, nchan, vs, ctx->copy_stream));
+      CIP_CHECK_CUDA(cudaEventRecord(ctx->chunk_ev[c], ctx->copy_stream));
+      feed->ready[c] = ctx->chunk_ev[c];
+    }
   }
-  CIP_CHECK_CUDA(cudaEventRecord(ctx->ev[15], st));
-  if (ms_h2d) {
-    CIP_CHECK_CUDA(cudaEventSynchronize(ctx->ev[15]));
-    *ms_h2d = elapsed_ms(ctx, 14, 15);
+  if (ms_h2d) {  // host clock: see StageTimer in invert.cu for why no timing event is recorded here
+    CIP_CHECK_CUDA(cudaEventSynchronize(ctx->small_ev));
+    *ms_h2d = now_ms() - ctx->t_stage_begin;
   }
+  ctx->staged_key[0] = a->uvw;
+  ctx->staged_key[1] = a->freq;
+  ctx->staged_key[2] = a->wgt;
+  ctx->staged_key[3] = a->mask;
+  ctx->staged_dims[0] = nrow;
+  ctx->staged_dims[1] = nchan;
+  ctx->staged_dims[2] = ws;
+  return CIP_OK;
+}
+
+__global__ void small_copy_kernel(const uint32_t* __restrict__ src, uint32_t* __restrict__ dst, int nwords) {
+  for (int i = threadIdx.x; i < nwords; i += blockDim.x) dst[i] = src[i];
+  __threadfence_system();
+}
+
+cip_status fetch_small(cip_ctx* ctx, const void* dev, size_t bytes, void* host_out) {
+  CIP_REQUIRE(bytes % 4 == 0 && bytes <= kSmallHostBytes, "fetch_small: bad size %zu", bytes);
+  small_copy_kernel<<<1, 256, 0, ctx->stream>>>(static_cast<const uint32_t*>(dev),
+                                               static_cast<uint32_t*>(ctx->scan_host_dev), (int)(bytes / 4));
+  CIP_CHECK_CUDA(cudaGetLastError());
+  CIP_CHECK_CUDA(cudaStreamSynchronize(ctx->stream));
+  memcpy(host_out, ctx->scan_host, bytes);
+  return CIP_OK;
+}
+
+cip_status wait_feed(cip_ctx* ctx, const VisFeed& feed) {
+  for (int c = 0; c < feed.nchunks; ++c)
+    if (feed.ready[c]) CIP_CHECK_CUDA(cudaStreamWaitEvent(ctx->stream, feed.ready[c], 0));
   return CIP_OK;
 }
 
@@ -148,8 +227,13 @@ extern "C" cip_status cip_ctx_create(int device, cip_ctx** out) {
   ctx->sm_count = prop.multiProcessorCount;
   ctx->smem_optin = prop.sharedMemPerBlockOptin;
   CIP_CHECK_CUDA(cudaStreamCreateWithFlags(&ctx->stream, cudaStreamNonBlocking));
+  CIP_CHECK_CUDA(cudaStreamCreateWithFlags(&ctx->copy_stream, cudaStreamNonBlocking));
   for (auto& ev : ctx->ev) CIP_CHECK_CUDA(cudaEventCreate(&ev));
-  CIP_CHECK_CUDA(cudaMallocHost(&ctx->scan_host, 256));
+  for (auto& ev : ctx->chunk_ev) CIP_CHECK_CUDA(cudaEventCreateWithFlags(&ev, cudaEventDisableTiming));
+  CIP_CHECK_CUDA(cudaEventCreateWithFlags(&ctx->sync_ev, cudaEventDisableTiming));
+  CIP_CHECK_CUDA(cudaEventCreateWithFlags(&ctx->small_ev, cudaEventDisableTiming));
+  CIP_CHECK_CUDA(cudaHostAlloc(&ctx->scan_host, kSmallHostBytes, cudaHostAllocMapped));
+  CIP_CHECK_CUDA(cudaHostGetDevicePointer(&ctx->scan_host_dev, ctx->scan_host, 0));
   *out = ctx;
   return CIP_OK;
 }
@@ -157,6 +241,7 @@ extern "C" cip_status cip_ctx_create(int device, cip_ctx** out) {
 extern "C" cip_status cip_ctx_destroy(cip_ctx* ctx) {
   if (!ctx) return CIP_OK;
   cudaSetDevice(ctx->device);
+  if (ctx->copy_stream) cudaStreamSynchronize(ctx->copy_stream);
   if (ctx->stream) cudaStreamSynchronize(ctx->stream);
   for (auto& kv : ctx->fft_plans) cufftDestroy(kv.second.handle);
   DevBuf* bufs[] = {&ctx->in_uvw, &ctx->in_freq, &ctx->in_vis, &ctx->in_wgt, &ctx->in_mask, &ctx->out_img,
@@ -169,6 +254,11 @@ extern "C" cip_status cip_ctx_destroy(cip_ctx* ctx) {
   if (ctx->scan_host) cudaFreeHost(ctx->scan_host);
   for (auto& ev : ctx->ev)
     if (ev) cudaEventDestroy(ev);
+  for (auto& ev : ctx->chunk_ev)
+    if (ev) cudaEventDestroy(ev);
+  if (ctx->small_ev) cudaEventDestroy(ctx->small_ev);
+  if (ctx->sync_ev) cudaEventDestroy(ctx->sync_ev);
+  if (ctx->copy_stream) cudaStreamDestroy(ctx->copy_stream);
   if (ctx->stream) cudaStreamDestroy(ctx->stream);
   delete ctx;
   return CIP_OK;

@@ -11,17 +11,42 @@ using namespace cip;
 
 namespace {
 
+// Stage timing for cip_report.  Device inputs: CUDA timing events on the context stream.  Host inputs:
+// while visibility chunks are in flight on the copy stream NO timing event may be recorded on the
+// compute stream -- a timing-enabled cudaEventRecord is ordered behind all copy-engine work already
+// submitted on other streams (measured on B200, driver 580: tools/experiments/overlap_probe.cu mode 9),
+// which would serialise the whole compute stream behind the upload.  So host inputs are timed with
+// the host clock around a non-timing event synchronisation (every stage ends with one anyway).
 struct StageTimer {
   cip_ctx* ctx;
-  bool on;
-  StageTimer(cip_ctx* c, bool enabled) : ctx(c), on(enabled) {}
-  void start() { if (on) cudaEventRecord(ctx->ev[0], ctx->stream); }
+  bool on, host;
+  double t0 = 0;
+  StageTimer(cip_ctx* c, bool enabled, bool host_clock) : ctx(c), on(enabled), host(host_clock) {}
+  void start() {
+    if (!on) return;
+    if (host) t0 = now_ms();
+    else cudaEventRecord(ctx->ev[0], ctx->stream);
+  }
   void stop(double* acc) {
     if (!on) return;
-    cudaEventRecord(ctx->ev[1], ctx->stream);
-    cudaEventSynchronize(ctx->ev[1]);
-    *acc += elapsed_ms(ctx, 0, 1);
+    if (host) {
+      cudaEventRecord(ctx->sync_ev, ctx->stream);
+      cudaEventSynchronize(ctx->sync_ev);
+      *acc += now_ms() - t0;
+    } else {
+      cudaEventRecord(ctx->ev[1], ctx->stream);
+      cudaEventSynchronize(ctx->ev[1]);
+      *acc += elapsed_ms(ctx, 0, 1);
+    }
   }
+};
+
+// Host -> device copies of the caller's arrays may still be in flight on the copy stream when an entry
+// point returns early (error, nothing active): never return before they have drained.
+struct CopyStreamGuard {
+  cip_ctx* ctx;
+  explicit CopyStreamGuard(cip_ctx* c) : ctx(c) {}
+  ~CopyStreamGuard() { cudaStreamSynchronize(ctx->copy_stream); }
 };
 
 cip_status fft_prepare(cip_ctx* ctx, int nu, int nv, int fp64) {
@@ -35,12 +60,25 @@ extern "C" cip_status cip_scan(cip_ctx* ctx, const cip_invert_args* args, cip_sc
   CIP_TRY(validate_args(args));
   CIP_CHECK_CUDA(cudaSetDevice(ctx->device));
   DevInputs in;
-  CIP_TRY(stage_inputs(ctx, args, &in, nullptr));
-  return run_scan(ctx, in, args->do_wstacking, out);
+  CIP_TRY(stage_inputs(ctx, args, &in, nullptr, false, nullptr));  // no visibilities: the scan reads weights only
+  CIP_TRY(run_scan(ctx, in, args->do_wstacking, out));
+  ctx->staged_valid = args->memspace == 0;  // a cip_grid_accumulate of the same arrays may reuse them
+  return CIP_OK;
 }
 
-static cip_status grid_accumulate_staged(cip_ctx* ctx, const DevInputs& in, cip_plan* plan, void* image_dev,
-                                         cip_report* rep) {
+// Rows [r0, r1) of the staged inputs as inputs of their own.
+static DevInputs row_slice(const DevInputs& in, int64_t r0, int64_t r1) {
+  DevInputs c = in;
+  c.nrow = r1 - r0;
+  c.uvw = in.uvw + 3 * r0;
+  c.vis = in.vis + r0 * in.vstride;
+  if (in.wgt) c.wgt = in.wgt + r0 * in.wstride;
+  if (in.mask) c.mask = in.mask + r0 * in.wstride;
+  return c;
+}
+
+static cip_status grid_accumulate_staged(cip_ctx* ctx, const DevInputs& in, const VisFeed& feed, cip_plan* plan,
+                                         void* image_dev, cip_report* rep) {
   const int fp64 = plan->accumulate_fp64;
   CIP_REQUIRE(plan->support >= kMinSupport && plan->support <= kMaxSupport, "bad support %d", plan->support);
   CIP_REQUIRE(plan->nu >= plan->npix_x && plan->nv >= plan->npix_y && plan->nu % 2 == 0 && plan->nv % 2 == 0,
@@ -48,24 +86,27 @@ static cip_status grid_accumulate_staged(cip_ctx* ctx, const DevInputs& in, cip_
   CIP_REQUIRE(plan->nplanes >= 1 && plan->dw > 0, "bad w-plane layout");
   CIP_REQUIRE(plan->nu >= 2 * kFastSupport + kTile && plan->nv >= 2 * kFastSupport + kTile, "grid too small");
   const GridGeom g = make_geom(*plan);
-  StageTimer tm(ctx, rep != nullptr);
+  StageTimer tm(ctx, rep != nullptr, feed.nchunks > 0 && feed.ready[0] != nullptr);
   double dummy = 0;
-
-  tm.start();
-  BinResult bins;
-  CIP_TRY(run_binning(ctx, in, g, fp64, &bins));
-  tm.stop(rep ? &rep->ms_bin : &dummy);
-  if (bins.nitems == 0) return CIP_OK;
 
   // how many planes fit
   CIP_TRY(fft_prepare(ctx, plan->nu, plan->nv, fp64));
   const size_t plane_bytes = (size_t)plan->nu * plan->nv * (fp64 ? 16 : 8);
-  size_t free_b = 0, total_b = 0;
-  CIP_CHECK_CUDA(cudaMemGetInfo(&free_b, &total_b));
-  const size_t reserve = (size_t)768 << 20;
-  size_t avail = free_b + ctx->grid.cap;
-  avail = avail > reserve ? avail - reserve : 0;
-  int64_t max_slots = (int64_t)(avail / plane_bytes);
+  // cudaMemGetInfo is a device-wide driver call (it can wait behind in-flight copies): only ask when the
+  // plane stack has to grow
+  int64_t max_slots = (int64_t)(ctx->grid.cap / plane_bytes);
+  if (max_slots < plan->nplanes) {
+    size_t free_b = 0, total_b = 0;
+    CIP_CHECK_CUDA(cudaMemGetInfo(&free_b, &total_b));
+    // keep room for the binning workspaces (records 32 B + runs/keys ~16 B per visibility) if they are
+    // not allocated yet
+    size_t reserve = (size_t)768 << 20;
+    const size_t nvis = (size_t)in.nrow * in.nchan;
+    if (ctx->recs.cap < recs_bytes(nvis) / std::max(feed.nchunks, 1)) reserve += 48 * nvis;
+    size_t avail = free_b + ctx->grid.cap;
+    avail = avail > reserve ? avail - reserve : 0;
+    max_slots = (int64_t)(avail / plane_bytes);
+  }
   if (const char* e = getenv("CIP_MAX_PLANE_SLOTS")) max_slots = std::min<int64_t>(max_slots, atoll(e));
   int nslots_alloc;
   if (max_slots >= plan->nplanes) {
@@ -79,6 +120,56 @@ static cip_status grid_accumulate_staged(cip_ctx* ctx, const DevInputs& in, cip_
   }
   plan->plane_block = nslots_alloc;
   CIP_TRY(ctx->grid.ensure(plane_bytes * nslots_alloc));
+  trace_mark("  grid ensured");
+
+  if (nslots_alloc >= plan->nplanes) {
+    // All planes resident: bin and grid each row chunk as soon as its visibilities have arrived (host
+    // inputs stream in on the copy stream; device inputs are one chunk), then transform once.
+    tm.start();
+    CIP_CHECK_CUDA(cudaMemsetAsync(ctx->grid.p, 0, plane_bytes * plan->nplanes, ctx->stream));
+    tm.stop(rep ? &rep->ms_zero : &dummy);
+    bool any = false;
+    for (int c = 0; c < feed.nchunks; ++c) {
+      if (feed.row0[c + 1] <= feed.row0[c]) continue;
+      if (feed.ready[c]) {
+        if (rep) {  // timed call: the host waits for the chunk so that the stage times exclude the upload
+          CIP_CHECK_CUDA(cudaEventSynchronize(feed.ready[c]));
+          if (c == feed.nchunks - 1) rep->ms_h2d = now_ms() - ctx->t_stage_begin;  // all inputs on the device
+        } else {
+          CIP_CHECK_CUDA(cudaStreamWaitEvent(ctx->stream, feed.ready[c], 0));
+        }
+      }
+      const DevInputs chunk = row_slice(in, feed.row0[c], feed.row0[c + 1]);
+      tm.start();
+      BinResult bins;
+      CIP_TRY(run_binning(ctx, chunk, g, fp64, &bins));
+      tm.stop(rep ? &rep->ms_bin : &dummy);
+      trace_mark("  chunk binned");
+      if (bins.nitems == 0) continue;
+      any = true;
+      tm.start();
+      CIP_TRY(run_gridder(ctx, g, fp64, bins.nrec, 0, bins.nitems, ctx->grid.p, 0, plan->nplanes));
+      tm.stop(rep ? &rep->ms_grid : &dummy);
+      trace_mark("  chunk gridded");
+    }
+    if (rep) rep->nblocks = feed.nchunks;
+    if (!any) return CIP_OK;
+    tm.start();
+    CIP_TRY(run_fft(ctx, ctx->grid.p, plan->nu, plan->nv, plan->nplanes, fp64));
+    tm.stop(rep ? &rep->ms_fft : &dummy);
+    tm.start();
+    CIP_TRY(run_wscreen(ctx, *plan, ctx->grid.p, 0, plan->nplanes, image_dev));
+    tm.stop(rep ? &rep->ms_wscreen : &dummy);
+    return CIP_OK;
+  }
+
+  // Blocks of planes: every block needs all visibilities, so bin them once, unchunked.
+  CIP_TRY(wait_feed(ctx, feed));
+  tm.start();
+  BinResult bins;
+  CIP_TRY(run_binning(ctx, in, g, fp64, &bins));
+  tm.stop(rep ? &rep->ms_bin : &dummy);
+  if (bins.nitems == 0) return CIP_OK;
 
   if (g.W > kFastSupport && nslots_alloc < plan->nplanes) {
     // Wide supports have a single window; blocks of resident planes each take a pass over all
@@ -144,8 +235,10 @@ extern "C" cip_status cip_grid_accumulate(cip_ctx* ctx, const cip_invert_args* a
   if (report) memset(report, 0, sizeof(*report));
   const int64_t l0 = ctx->launches;
   DevInputs in;
-  CIP_TRY(stage_inputs(ctx, args, &in, report ? &report->ms_h2d : nullptr));
-  CIP_TRY(grid_accumulate_staged(ctx, in, plan, image_dev, report));
+  VisFeed feed;
+  CopyStreamGuard guard(ctx);
+  CIP_TRY(stage_inputs(ctx, args, &in, &feed, true, report ? &report->ms_h2d : nullptr));
+  CIP_TRY(grid_accumulate_staged(ctx, in, feed, plan, image_dev, report));
   CIP_CHECK_CUDA(cudaStreamSynchronize(ctx->stream));
   if (report) report->launches += ctx->launches - l0;
   return CIP_OK;
@@ -168,6 +261,7 @@ extern "C" cip_status cip_invert(cip_ctx* ctx, const cip_invert_args* args, void
   if (report) memset(report, 0, sizeof(*report));
   const int64_t l0 = ctx->launches;
   cudaStream_t st = ctx->stream;
+  trace_mark("begin");
   CIP_CHECK_CUDA(cudaEventRecord(ctx->ev[2], st));
   const int fp64 = args->accumulate_fp64 != 0;
   const size_t img_bytes = (size_t)args->npix_x * args->npix_y * (fp64 ? 8 : 4);
@@ -179,21 +273,27 @@ extern "C" cip_status cip_invert(cip_ctx* ctx, const cip_invert_args* args, void
   CIP_CHECK_CUDA(cudaMemsetAsync(image, 0, img_bytes, st));
 
   DevInputs in;
-  CIP_TRY(stage_inputs(ctx, args, &in, report ? &report->ms_h2d : nullptr));
-  StageTimer tm(ctx, report != nullptr);
+  VisFeed feed;
+  CopyStreamGuard guard(ctx);
+  CIP_TRY(stage_inputs(ctx, args, &in, &feed, false, report ? &report->ms_h2d : nullptr));
+  StageTimer tm(ctx, report != nullptr, args->memspace == 0);
   double dummy = 0;
+  trace_mark("staged");
   tm.start();
   cip_scan_result scan{};
   CIP_TRY(run_scan(ctx, in, args->do_wstacking, &scan));
   tm.stop(report ? &report->ms_scan : &dummy);
   if (scan_out) *scan_out = scan;
+  trace_mark("scanned");
   cip_plan plan{};
   CIP_TRY(cip_plan_make(args->npix_x, args->npix_y, args->pixsize_x, args->pixsize_y, args->epsilon,
                         args->do_wstacking, fp64, scan.wmin, scan.wmax, scan.nactive,
                         getenv("CIP_SIGMA") ? atof(getenv("CIP_SIGMA")) : 0.0,
                         getenv("CIP_SUPPORT") ? atoi(getenv("CIP_SUPPORT")) : 0, &plan));
+  trace_mark("planned");
   if (scan.nactive > 0) {
-    CIP_TRY(grid_accumulate_staged(ctx, in, &plan, image, report));
+    CIP_TRY(grid_accumulate_staged(ctx, in, feed, &plan, image, report));
+    trace_mark("accumulated");
     tm.start();
     CIP_TRY(run_correct(ctx, plan, image, 0, args->npix_x, 1.0));
     tm.stop(report ? &report->ms_correct : &dummy);
@@ -206,6 +306,7 @@ extern "C" cip_status cip_invert(cip_ctx* ctx, const cip_invert_args* args, void
   }
   CIP_CHECK_CUDA(cudaEventRecord(ctx->ev[3], st));
   CIP_CHECK_CUDA(cudaStreamSynchronize(st));
+  trace_mark("done");
   if (report) {
     report->ms_total = elapsed_ms(ctx, 2, 3);
     report->launches += ctx->launches - l0;

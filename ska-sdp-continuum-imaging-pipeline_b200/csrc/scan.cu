@@ -1,7 +1,11 @@
 // G1 scan: |w| range over the active samples, active count, and the weight sum that the
 // reference takes on the host (effective_weights.sum(), src/ska_sdp_cip/invert.py:184).
-// One pass over vis/wgt/mask (HBM-bound: 12-13 B per sample), block reduction, 4 atomics per CTA.
+// A sample is active when wgt * mask != 0.  (ducc0 also drops samples whose visibility is exactly
+// zero; they add nothing to the image either way, so here they merely may widen the planned w range.
+// Not reading the visibilities lets the planning start while they are still in flight from the
+// host.)  One pass over wgt/mask (HBM-bound: 4-5 B per sample), block reduction, 4 atomics per CTA.
 #include <algorithm>
+#include <cstdlib>
 #include <cstring>
 
 #include "geom.cuh"
@@ -17,10 +21,10 @@ struct ScanOut {
 struct ScanAcc {
   double lo = 1e300, hi = 0.0, sw = 0.0;
   unsigned long long na = 0;
-  __device__ __forceinline__ void add(float2 v, float w, bool masked, double aw) {
+  __device__ __forceinline__ void add(float w, bool masked, double aw) {
     if (masked) w = 0.0f;
     sw += (double)w;
-    if (w != 0.0f && (v.x != 0.0f || v.y != 0.0f)) {
+    if (w != 0.0f) {
       lo = fmin(lo, aw);
       hi = fmax(hi, aw);
       ++na;
@@ -60,11 +64,10 @@ __global__ void __launch_bounds__(256) scan_kernel(DevInputs in, int do_wstackin
   ScanAcc acc;
   for (int64_t k = (int64_t)blockIdx.x * blockDim.x + threadIdx.x; k < total; k += (int64_t)gridDim.x * blockDim.x) {
     int64_t r = k / nchan, c = k - r * nchan;
-    float2 v = in.vis[r * in.vstride + c];
     float w = in.wgt ? in.wgt[r * in.wstride + c] : 1.0f;
     bool masked = in.mask && in.mask[r * in.wstride + c] == 0;
     double aw = do_wstacking ? fabs(in.uvw[3 * r + 2]) * (in.freq[c] / kSpeedOfLight) : 0.0;
-    acc.add(v, w, masked, aw);
+    acc.add(w, masked, aw);
   }
   scan_finish(acc, out);
 }
@@ -78,8 +81,6 @@ __global__ void __launch_bounds__(256) scan_kernel_v4(DevInputs in, int do_wstac
   for (int64_t k = (int64_t)blockIdx.x * blockDim.x + threadIdx.x; k < total; k += (int64_t)gridDim.x * blockDim.x) {
     const int64_t r = k / nq;
     const int c = (int)(k - r * nq) << 2;
-    const float4* pv = reinterpret_cast<const float4*>(in.vis + r * in.vstride + c);
-    const float4 v0 = __ldg(pv), v1 = __ldg(pv + 1);
     float4 w = make_float4(1.f, 1.f, 1.f, 1.f);
     if (in.wgt) w = __ldg(reinterpret_cast<const float4*>(in.wgt + r * in.wstride + c));
     uint32_t mk = 0x01010101u;
@@ -92,12 +93,19 @@ __global__ void __launch_bounds__(256) scan_kernel_v4(DevInputs in, int do_wstac
       aw2 = wm * (in.freq[c + 2] / kSpeedOfLight);
       aw3 = wm * (in.freq[c + 3] / kSpeedOfLight);
     }
-    acc.add(make_float2(v0.x, v0.y), w.x, (mk & 0xffu) == 0, aw0);
-    acc.add(make_float2(v0.z, v0.w), w.y, (mk & 0xff00u) == 0, aw1);
-    acc.add(make_float2(v1.x, v1.y), w.z, (mk & 0xff0000u) == 0, aw2);
-    acc.add(make_float2(v1.z, v1.w), w.w, (mk & 0xff000000u) == 0, aw3);
+    acc.add(w.x, (mk & 0xffu) == 0, aw0);
+    acc.add(w.y, (mk & 0xff00u) == 0, aw1);
+    acc.add(w.z, (mk & 0xff0000u) == 0, aw2);
+    acc.add(w.w, (mk & 0xff000000u) == 0, aw3);
   }
   scan_finish(acc, out);
+}
+
+__global__ void scan_init_kernel(ScanOut* out) {
+  out->wmin_bits = 0x7ff0000000000000ull;  // +inf
+  out->wmax_bits = 0;
+  out->nactive = 0;
+  out->sum_wgt = 0.0;
 }
 
 static double bits_to_double(unsigned long long b) {
@@ -108,20 +116,12 @@ static double bits_to_double(unsigned long long b) {
 
 cip_status run_scan(cip_ctx* ctx, const DevInputs& in, int do_wstacking, cip_scan_result* out) {
   CIP_TRY(ctx->scan_out.ensure(sizeof(ScanOut)));
-  ScanOut init;
-  init.wmin_bits = (unsigned long long)0x7ff0000000000000ull;  // +inf
-  init.wmax_bits = 0;
-  init.nactive = 0;
-  init.sum_wgt = 0.0;
-  ScanOut* host = static_cast<ScanOut*>(ctx->scan_host);
-  *host = init;
   cudaStream_t st = ctx->stream;
-  CIP_CHECK_CUDA(cudaMemcpyAsync(ctx->scan_out.p, host, sizeof(ScanOut), cudaMemcpyHostToDevice, st));
+  scan_init_kernel<<<1, 1, 0, st>>>(ctx->scan_out.as<ScanOut>());
   int64_t total = in.nrow * in.nchan;
   if (total > 0) {
     auto al16 = [](const void* p) { return (reinterpret_cast<uintptr_t>(p) & 15) == 0; };
-    const bool v4 = in.nchan % 4 == 0 && in.vstride % 4 == 0 && in.wstride % 4 == 0 && al16(in.vis) &&
-                    al16(in.wgt) && al16(in.mask);
+    const bool v4 = in.nchan % 4 == 0 && in.wstride % 4 == 0 && al16(in.wgt) && al16(in.mask);
     if (v4) {
       int blocks = (int)std::min<int64_t>((total / 4 + 255) / 256, (int64_t)ctx->sm_count * 8);
       scan_kernel_v4<<<blocks, 256, 0, st>>>(in, do_wstacking, ctx->scan_out.as<ScanOut>());
@@ -132,8 +132,9 @@ cip_status run_scan(cip_ctx* ctx, const DevInputs& in, int do_wstacking, cip_sca
     ctx->launches++;
     CIP_CHECK_CUDA(cudaGetLastError());
   }
-  CIP_CHECK_CUDA(cudaMemcpyAsync(host, ctx->scan_out.p, sizeof(ScanOut), cudaMemcpyDeviceToHost, st));
-  CIP_CHECK_CUDA(cudaStreamSynchronize(st));
+  ScanOut res;
+  CIP_TRY(fetch_small(ctx, ctx->scan_out.p, sizeof(ScanOut), &res));
+  const ScanOut* host = &res;
   out->nactive = (int64_t)host->nactive;
   out->sum_wgt = host->sum_wgt;
   if (host->nactive) {

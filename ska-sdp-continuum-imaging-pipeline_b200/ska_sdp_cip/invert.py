@@ -211,11 +211,12 @@ def accumulate_shards(shards: Sequence[StokesIGridderInput], num_pixels: int, pi
     args_list, wmin, wmax, nactive, sumw = [], np.inf, 0.0, 0, 0.0
     torch.cuda.current_stream(dev).synchronize()
     for sh in shards:
-        if isinstance(sh.visibilities, np.ndarray):  # host shard: one upload, then the device path
-            up = lambda a, dt: torch.from_numpy(np.ascontiguousarray(a, dtype=dt)).to(dev, non_blocking=True)
-            sh = StokesIGridderInput(up(sh.channel_frequencies, np.float64), None, up(sh.uvw, np.float64),
-                                     up(sh.visibilities, np.complex64), up(sh.effective_weights(), np.float32))
-            torch.cuda.current_stream(dev).synchronize()
+        if isinstance(sh.visibilities, np.ndarray):
+            # host shard: handed to the library as host memory -- cip_scan stages weights and uvw only,
+            # cip_grid_accumulate reuses them and streams the visibilities in behind the binning/gridding
+            c = lambda a, dt: np.ascontiguousarray(a, dtype=dt)
+            sh = StokesIGridderInput(c(sh.channel_frequencies, np.float64), None, c(sh.uvw, np.float64),
+                                     c(sh.visibilities, np.complex64), c(sh.effective_weights(), np.float32))
         effw = sh.effective_weights()
         a = make_args(sh.uvw, sh.channel_frequencies, sh.visibilities, effw, None, num_pixels, num_pixels,
                       pixel_size_lm, pixel_size_lm, epsilon, True, accumulate_fp64,

@@ -42,6 +42,20 @@ def _prep_host(uvw, freq, ms, wgt, mask):
     return uvw, freq, ms, wgt, mask, fp64_in
 
 
+def _host_result(shape, dtype):
+    """A new array for the dirty image.  Large images come from torch's caching pinned-memory
+    allocator (a numpy view that keeps the block alive and returns it to the cache when collected):
+    the device -> host copy then runs at full PCIe speed and a fresh result does not page-fault."""
+    if int(np.prod(shape)) * np.dtype(dtype).itemsize >= (1 << 20):
+        try:
+            import torch
+            return torch.empty(shape, dtype=torch.float64 if dtype == np.float64 else torch.float32,
+                               pin_memory=True).numpy()
+        except Exception:  # noqa: BLE001  (no torch / no pinned memory: plain pageable memory works too)
+            pass
+    return np.empty(shape, dtype=dtype)
+
+
 def make_args(uvw, freq, ms, wgt, mask, npix_x, npix_y, pixsize_x, pixsize_y, epsilon, do_wstacking, fp64,
               memspace) -> InvertArgs:
     a = InvertArgs()
@@ -92,7 +106,7 @@ def ms2dirty(uvw, freq, ms, wgt=None, npix_x=0, npix_y=0, pixsize_x=0.0, pixsize
     else:
         uvw, freq, ms, wgt, mask, fp64_in = _prep_host(uvw, freq, ms, wgt, mask)
         fp64 = bool(double_precision_accumulation) or fp64_in
-        out = np.empty((npix_x, npix_y), dtype=np.float64 if fp64 else np.float32)
+        out = _host_result((npix_x, npix_y), np.float64 if fp64 else np.float32)
         memspace = 0
     args = make_args(uvw, freq, ms, wgt, mask, npix_x, npix_y, pixsize_x, pixsize_y, epsilon, do_wstacking, fp64,
                      memspace)

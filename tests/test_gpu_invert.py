@@ -246,6 +246,21 @@ def test_device_inputs_match_host_inputs(wg, small):
     assert dft.rel_rms(out.cpu().numpy(), host) <= 2e-6
 
 
+@pytest.mark.parametrize("chunks", [1, 3, 8])
+def test_streamed_host_chunks_give_the_same_image(wg, small, chunks):
+    """Host inputs are uploaded in row chunks that are binned and gridded as they arrive; the chunking
+    must not change the image (beyond float32 summation order)."""
+    (uvw, freq, vis, wgt, nx, px), ref = small
+    os.environ["CIP_STREAM_CHUNKS"] = str(chunks)
+    try:
+        img, info = wg.ms2dirty(uvw, freq, vis, wgt, nx, nx, px, px, epsilon=1e-4, do_wstacking=True,
+                                return_info=True)
+    finally:
+        os.environ.pop("CIP_STREAM_CHUNKS")
+    assert info["report"]["nblocks"] == chunks
+    assert dft.rel_rms(img, ref) <= TOL_FP32
+
+
 def test_repeatable_to_rounding(wg, small):
     """Tiles are accumulated in shared memory in a fixed order; only the final reductions of the sub-grids
     into the global plane stack (red.global.add) are unordered, so two runs agree to float32 rounding
