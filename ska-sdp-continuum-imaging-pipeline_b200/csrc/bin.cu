@@ -44,6 +44,7 @@ __global__ void __launch_bounds__(256) runs_kernel(DevInputs in, GridGeom g, int
   int64_t n = 0;
   int carry_ch0 = 0;
   const int64_t base = PASS ? row_off[row] : 0;
+  const int snap = g.W <= kFastSupport ? 9 - g.W : 1;
   for (int64_t c0 = 0; c0 < in.nchan; c0 += 32) {
     const int64_t c = c0 + lane;
     const bool valid = c < in.nchan;
@@ -96,7 +97,10 @@ __global__ void __launch_bounds__(256) runs_kernel(DevInputs in, GridGeom g, int
         const uint32_t j0r = (uint32_t)(s.j0 + kHalo - tv * kTile);
         const uint32_t p0r = (uint32_t)(s.p0 - win * g.win_step);
         Rec<R> rec;
+        // bits 16-20 / 21-25: origin of the gridder's register window (i0r, j0r snapped to the lattice)
+        const uint32_t wi = i0r - i0r % (uint32_t)snap, wj = j0r - j0r % (uint32_t)snap;
         rec.cell = i0r | (j0r << 5) | (p0r << 10);
+        if (g.W <= kFastSupport) rec.cell |= (wi << 16) | (wj << 21);  // wide supports: p0r may need the high bits
         if constexpr (sizeof(R) == 4) {
           rec.fu = s.fu;
           rec.fv = s.fv;

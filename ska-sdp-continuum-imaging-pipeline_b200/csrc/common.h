@@ -82,7 +82,8 @@ struct FftPlan {
 // One gridder-ready visibility: exactly one 32-byte sector, so that the scattered writes of the
 // record pass never touch a partial sector and the gridder's producer reads two 128-bit words.
 //   cell  bits 0-4 i0 (u cell of the support origin inside the tile, 0..kTile-1), 5-9 j0,
-//         10-13 first plane relative to the window start
+//         10-13 first plane relative to the window start, 16-20 / 21-25 origin of the 8 x 8 register
+//         window of the gridder (i0, j0 snapped to the lattice of 9-W cells)
 //   fu, fv, fw  distance of the first cell / plane from the left edge of the support, in [0,1)
 //               (float32 in Rec<float>, 0.32 fixed point in Rec<double>)
 //   re, im      weighted, conjugated-if-flipped, n-shift-rotated visibility (R = float or double)

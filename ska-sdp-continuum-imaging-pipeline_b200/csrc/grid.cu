@@ -18,6 +18,8 @@
 // row pitch kSub is odd) only when the window moves.  The operands of visibility k+1 are loaded
 // while visibility k is accumulated.  The finished sub-grid is added to the global plane stack with
 // vector reductions (red.global.add.v4.f32), skipping empty cells.
+#include <cstdlib>
+
 #include "geom.cuh"
 
 namespace cip {
@@ -61,6 +63,28 @@ __device__ __forceinline__ float es_fast(float x, float bw2) {
   float e;
   asm("ex2.approx.ftz.f32 %0, %1;" : "=f"(e) : "f"(fmaf(bw2, s, -bw2)));
   return t >= 0.0f ? e : 0.0f;
+}
+
+// exp(beta_w (sqrt(max(1 - x^2, 0)) - 1)): es_fast without the |x| > 1 test (the caller masks the taps outside
+// the support); pure inline PTX so that the compiler cannot turn the masking into a branch around it
+__device__ __forceinline__ float es_fast_nb(float x, float bw2) {
+  float e;
+  asm("{\n\t.reg .f32 t, s;\n\t"
+      "neg.f32 t, %1;\n\t"
+      "fma.rn.f32 t, t, %1, 0f3F800000;\n\t"
+      "max.f32 t, t, 0f00000000;\n\t"
+      "sqrt.approx.ftz.f32 s, t;\n\t"
+      "neg.f32 t, %2;\n\t"
+      "fma.rn.f32 s, %2, s, t;\n\t"
+      "ex2.approx.ftz.f32 %0, s;\n\t}"
+      : "=f"(e) : "f"(x), "f"(bw2));
+  return e;
+}
+// (unsigned)a < (unsigned)b ? v : 0
+__device__ __forceinline__ float sel_lt_u32(int a, int b, float v) {
+  float r;
+  asm("{\n\t.reg .pred p;\n\tsetp.lt.u32 p, %1, %2;\n\tselp.f32 %0, %3, 0f00000000, p;\n\t}" : "=f"(r) : "r"(a), "r"(b), "f"(v));
+  return r;
 }
 
 __device__ __forceinline__ void red_add_v4(float* addr, float a, float b, float c, float d) {
@@ -113,9 +137,10 @@ __device__ __forceinline__ Rec<R> load_rec(const Rec<R>* __restrict__ recs, int6
 // Register-window origin of a record and the "window moved" mask of the batch (common to both precisions).
 __device__ __forceinline__ uint32_t window_origin(uint32_t cell, bool valid, int lane, uint32_t& carry, int snap,
                                                   uint32_t* moved) {
-  const int i0 = cell & 31, j0 = (cell >> 5) & 31;
   // register window: origin snapped to a lattice of `snap` cells, so that nearby supports share it
-  const uint32_t wxy = (uint32_t)(i0 - i0 % snap) | ((uint32_t)(j0 - j0 % snap) << 5);
+  // (computed by the record pass of the binning, bits 16-25 of `cell`)
+  (void)snap;
+  const uint32_t wxy = (cell >> 16) & 0x3ffu;
   const uint32_t cxy = valid ? wxy : carry;
   uint32_t prev = __shfl_up_sync(0xffffffffu, cxy, 1);
   if (lane == 0) prev = carry;
@@ -502,6 +527,279 @@ __global__ void __launch_bounds__(kGridThreads) grid_kernel(const Item* __restri
   }
 }
 
+// ---- warp-autonomous float32 gridder ("rank-1 tiles") -----------------------------------------
+// One warp = one CTA = one work item.  Per batch of 32 visibilities the warp first PRODUCES (one
+// visibility per lane): the separable ES weights, the 64 products A[r_u][r_v] = ku[r_u] kv[r_v] of the
+// 8 x 8 register window (by residue class, 0 outside the support) and the 8 complex plane values
+// B[p] = V kw[p]; then it CONSUMES them: the update of the window is the rank-1 product A (x) B, and
+// lane (a, pq) owns the 8 x 2 block {u = a, all 8 v residues} x {planes 2pq, 2pq+1}: two 128-bit and
+// two 64-bit shared-memory loads (8 A values, 2 complex B values) feed 16 FFMA2 whose A operand is the
+// register-broadcast form (R.F32) -- 6 shared-memory wavefronts per visibility instead of the 14 of
+// the two-warp design, which ncu showed to be bound by shared-memory bandwidth.  No hand-over between
+// warps, hence no barriers besides __syncwarp.  Sub-grid, fold and epilogue are those of grid_kernel.
+constexpr int kARow = 64 * 4 + 16;  // bytes per visibility of the A stage; the pad makes the producer's
+constexpr int kBRow = 16 * 4 + 16;  // 128-bit stores (one row per lane) bank-conflict free
+constexpr int kWarpSubGridBytes = 16 * 4 * kSub * kSub;
+constexpr int kWarpSmemBytes = kWarpSubGridBytes + kBatch * (kARow + kBRow + 4);
+
+template <int OFF>
+__device__ __forceinline__ float4 lds_f4(uint32_t addr) {
+  float4 v;
+  asm volatile("ld.shared.v4.f32 {%0, %1, %2, %3}, [%4+%5];" : "=f"(v.x), "=f"(v.y), "=f"(v.z), "=f"(v.w) : "r"(addr), "n"(OFF));
+  return v;
+}
+template <int OFF>
+__device__ __forceinline__ ulonglong2 lds_u2(uint32_t addr) {
+  ulonglong2 v;
+  asm volatile("ld.shared.v2.b64 {%0, %1}, [%2+%3];" : "=l"(v.x), "=l"(v.y) : "r"(addr), "n"(OFF));
+  return v;
+}
+__device__ __forceinline__ void sts_u2(uint32_t addr, u64 a, u64 b) {
+  asm volatile("st.shared.v2.b64 [%0], {%1, %2};" ::"r"(addr), "l"(a), "l"(b) : "memory");
+}
+__device__ __forceinline__ void sts_f4(uint32_t addr, float a, float b, float c, float d) {
+  asm volatile("st.shared.v4.f32 [%0], {%1, %2, %3, %4};" ::"r"(addr), "f"(a), "f"(b), "f"(c), "f"(d) : "memory");
+}
+// ES tap exp(beta_w (sqrt(1 - x^2) - 1)), 0 where 1 - x^2 <= 0; pure PTX so that the mask stays a select
+__device__ __forceinline__ float es_tap(float x, float bw2) {
+  float e;
+  asm("{\n\t.reg .f32 t, s, nb;\n\t.reg .pred p;\n\t"
+      "neg.f32 t, %1;\n\t"
+      "fma.rn.f32 t, t, %1, 0f3F800000;\n\t"
+      "setp.gt.f32 p, t, 0f00000000;\n\t"
+      "sqrt.approx.ftz.f32 s, t;\n\t"
+      "neg.f32 nb, %2;\n\t"
+      "fma.rn.f32 s, %2, s, nb;\n\t"
+      "ex2.approx.ftz.f32 s, s;\n\t"
+      "selp.f32 %0, s, 0f00000000, p;\n\t}"
+      : "=f"(e) : "f"(x), "f"(bw2));
+  return e;
+}
+__device__ __forceinline__ uint32_t lds_u32(uint32_t addr) {
+  uint32_t v;
+  asm volatile("ld.shared.u32 %0, [%1];" : "=r"(v) : "r"(addr));
+  return v;
+}
+__device__ __forceinline__ u64 dup2(float x) { return pack2(x, x); }
+
+template <int OFF>
+__device__ __forceinline__ u64 lds_u1(uint32_t addr) {
+  u64 v;
+  asm volatile("ld.shared.b64 %0, [%1+%2];" : "=l"(v) : "r"(addr), "n"(OFF));
+  return v;
+}
+
+// Operands of one visibility for lane (a, pq): the row A[a][0..8] and the planes 2pq, 2pq+1 of B.
+// Wavefront cost measured with tools/experiments/lds_patterns.cu: a 128-bit load is one wavefront per
+// half-warp only when the lanes (2i, 2i+1) read the same 16 bytes (else one per quarter-warp), a 64-bit
+// load is one wavefront per warp when its distinct words are conflict-free.  With lane = 4a + pq the two
+// A loads cost 2 wavefronts each and the two B loads 1 each: 6 per visibility.
+struct WarpOps {
+  float4 a0, a1;
+  u64 b0, b1;
+};
+template <int U>
+__device__ __forceinline__ WarpOps warp_load(uint32_t pa, uint32_t pb) {
+  WarpOps o;
+  o.a0 = lds_f4<U * kARow>(pa);
+  o.a1 = lds_f4<U * kARow + 16>(pa);
+  o.b0 = lds_u1<U * kBRow>(pb);
+  o.b1 = lds_u1<U * kBRow + 8>(pb);
+  return o;
+}
+
+struct WarpAcc {
+  u64 c[8][2];  // [v residue][plane 2pq + h] = (re, im)
+  __device__ __forceinline__ void clear() {
+#pragma unroll
+    for (int t = 0; t < 8; ++t) c[t][0] = c[t][1] = 0ull;
+  }
+  __device__ __forceinline__ void update(const WarpOps& o) {
+    const float av[8] = {o.a0.x, o.a0.y, o.a0.z, o.a0.w, o.a1.x, o.a1.y, o.a1.z, o.a1.w};
+#pragma unroll
+    for (int t = 0; t < 8; ++t) {
+      const u64 ad = dup2(av[t]);  // register-broadcast operand (R.F32), no instruction
+      ffma2(c[t][0], ad, o.b0);
+      ffma2(c[t][1], ad, o.b1);
+    }
+  }
+  // sub-grid cell = float4 {re(2pp), im(2pp), re(2pp+1), im(2pp+1)} for plane pair pp = pq: one float4
+  // read-modify-write per owned cell (the lane owns row i, all 8 v residues of the window)
+  __device__ __forceinline__ void fold(float4* sg, int i, int wj, int pq) {
+    float4* row = sg + (pq * kSub + i) * kSub;
+#pragma unroll
+    for (int t = 0; t < 8; ++t) {
+      float4* p = row + wj + ((t - wj) & 7);
+      const float2 x = unpack2(c[t][0]), y = unpack2(c[t][1]);
+      float4 v = *p;
+      v.x += x.x; v.y += x.y; v.z += y.x; v.w += y.y;
+      *p = v;
+    }
+    clear();
+  }
+};
+
+struct WarpCells {
+  int i, wj;
+  __device__ __forceinline__ void set(uint32_t org, int a) {
+    const int wi = org & 31;
+    wj = (org >> 5) & 31;
+    i = wi + ((a - wi) & 7);
+  }
+};
+
+template <int U, bool CHECK>
+__device__ __forceinline__ void warp_consume1(uint32_t pa, uint32_t pb, uint32_t porg, uint32_t moved8, const WarpOps& cur,
+                                              WarpOps& nxt, WarpAcc& acc, float4* sg, WarpCells& cells, int a, int pq) {
+  nxt = warp_load<U + 1>(pa, pb);
+  if (CHECK && ((moved8 >> U) & 1u)) {
+    acc.fold(sg, cells.i, cells.wj, pq);
+    cells.set(lds_u32(porg + 4 * U), a);
+  }
+  acc.update(cur);
+}
+template <bool CHECK>
+__device__ __forceinline__ void warp_consume8(uint32_t pa, uint32_t pb, uint32_t porg, uint32_t moved8, WarpOps& x, WarpAcc& acc,
+                                              float4* sg, WarpCells& cells, int a, int pq) {
+  WarpOps y;
+  warp_consume1<0, CHECK>(pa, pb, porg, moved8, x, y, acc, sg, cells, a, pq);
+  warp_consume1<1, CHECK>(pa, pb, porg, moved8, y, x, acc, sg, cells, a, pq);
+  warp_consume1<2, CHECK>(pa, pb, porg, moved8, x, y, acc, sg, cells, a, pq);
+  warp_consume1<3, CHECK>(pa, pb, porg, moved8, y, x, acc, sg, cells, a, pq);
+  warp_consume1<4, CHECK>(pa, pb, porg, moved8, x, y, acc, sg, cells, a, pq);
+  warp_consume1<5, CHECK>(pa, pb, porg, moved8, y, x, acc, sg, cells, a, pq);
+  warp_consume1<6, CHECK>(pa, pb, porg, moved8, x, y, acc, sg, cells, a, pq);
+  warp_consume1<7, CHECK>(pa, pb, porg, moved8, y, x, acc, sg, cells, a, pq);
+}
+
+__global__ void __launch_bounds__(32) grid_warp_kernel(const Item* __restrict__ items, int64_t item_base,
+                                                       const Rec<float>* __restrict__ recs, GridGeom g,
+                                                       float* __restrict__ grid, int plane_base, int nslots) {
+  extern __shared__ __align__(16) unsigned char smem_raw[];
+  float4* sg = reinterpret_cast<float4*>(smem_raw);
+  const uint32_t sA = smem_u32(smem_raw + kWarpSubGridBytes);
+  const uint32_t sB = sA + kBatch * kARow;
+  const uint32_t sOrg = sB + kBatch * kBRow;
+
+  const Item item = items[item_base + blockIdx.x];
+  const int lane = threadIdx.x;
+  const int nrec = item.nrec;
+  const int nb = (nrec + kBatch - 1) / kBatch;
+  const int64_t base = item.rec_begin;
+
+  bool cur_valid = lane < nrec;
+  Rec<float> cur = load_rec(recs, base + lane, cur_valid);
+  for (int t = lane; t < 4 * kSub * kSub; t += 32) sg[t] = make_float4(0.f, 0.f, 0.f, 0.f);
+
+  // producer constants
+  const int W = g.W;
+  const float bw2 = g.beta_w * 1.4426950408889634f;
+  const float two_over_w = 2.0f / (float)W;
+  const int snap = 9 - W;  // windows of 8 cells hold the supports of `snap` consecutive origins
+  const bool wstack = g.do_wstacking != 0;
+  uint32_t carry = 0xffffffffu;
+  const uint32_t myA = sA + lane * kARow, myB = sB + lane * kBRow;
+  // consumer constants
+  const int a = lane >> 2, pq = lane & 3;
+  const uint32_t pa0 = sA + a * 32, pb0 = sB + pq * 16;
+  WarpAcc acc;
+  acc.clear();
+  WarpCells cells;
+  cells.set(0u, a);
+  __syncwarp();
+
+  for (int b = 0; b < nb; ++b) {
+    const int kn = (b + 1) * kBatch + lane;
+    const bool nxt_valid = kn < nrec;
+    const Rec<float> nxt = load_rec(recs, base + kn, nxt_valid);
+    // ---------------- produce: lane = visibility ----------------
+    uint32_t moved;
+    {
+      const int i0 = cur.cell & 31, j0 = (cur.cell >> 5) & 31, p0 = (cur.cell >> 10) & 15;
+      const uint32_t cxy = window_origin(cur.cell, cur_valid, lane, carry, snap, &moved);
+      // Taps by residue class r: the tap of cell r sits da = (r - i0) mod 8 cells from the first one, at
+      // x = (f + da) 2/W - 1; taps outside the support have |x| >= 1 and are masked by the sign of 1 - x^2
+      // (branch-free; at |x| = 1 exactly the kernel is exp(-beta W) ~ 1e-7 of its peak, i.e. nothing).
+      const float i0f = (float)i0, j0f = (float)j0, p0f = (float)p0;
+      const float xu0 = fmaf(cur.fu - i0f, two_over_w, -1.0f), xv0 = fmaf(cur.fv - j0f, two_over_w, -1.0f);
+      const float xw0 = fmaf(cur.fw - p0f, two_over_w, -1.0f);
+      float ku[8], kv[8], kw[8];
+#pragma unroll
+      for (int r = 0; r < 8; ++r) {
+        const float c0 = (float)r * two_over_w, c1 = (float)(r + 8) * two_over_w;
+        ku[r] = es_tap(xu0 + (r < i0 ? c1 : c0), bw2);
+        kv[r] = es_tap(xv0 + (r < j0 ? c1 : c0), bw2);
+        kw[r] = wstack ? es_tap(xw0 + c0, bw2) : (r == 0 ? 1.0f : 0.0f);
+      }
+#pragma unroll
+      for (int r = 0; r < 8; ++r) {
+        sts_f4(myA + r * 32, ku[r] * kv[0], ku[r] * kv[1], ku[r] * kv[2], ku[r] * kv[3]);
+        sts_f4(myA + r * 32 + 16, ku[r] * kv[4], ku[r] * kv[5], ku[r] * kv[6], ku[r] * kv[7]);
+      }
+      const float re = cur_valid ? cur.re : 0.0f, im = cur_valid ? cur.im : 0.0f;
+#pragma unroll
+      for (int q = 0; q < 8; q += 2) sts_f4(myB + q * 8, re * kw[q], im * kw[q], re * kw[q + 1], im * kw[q + 1]);
+      asm volatile("st.shared.u32 [%0], %1;" ::"r"(sOrg + 4 * lane), "r"(cxy) : "memory");
+    }
+    __syncwarp();
+    // ---------------- consume: lane = (a, bh, ph) ----------------
+    {
+      WarpOps x = warp_load<0>(pa0, pb0);
+#pragma unroll 1
+      for (int k0 = 0; k0 < kBatch; k0 += 8) {
+        const uint32_t pa = pa0 + k0 * kARow, pb = pb0 + k0 * kBRow, porg = sOrg + 4 * k0;
+        const uint32_t m8 = (moved >> k0) & 0xffu;
+        // most groups stay inside one register window: branch-free fast path.  The operands of visibility
+        // k0 + 8 are prefetched at the end of a group; past the last group that reads the rows after the
+        // stage (still inside the CTA's shared memory: kSlack), which are discarded.
+        if (m8 == 0) warp_consume8<false>(pa, pb, porg, m8, x, acc, sg, cells, a, pq);
+        else warp_consume8<true>(pa, pb, porg, m8, x, acc, sg, cells, a, pq);
+      }
+    }
+    __syncwarp();
+    cur = nxt;
+    cur_valid = nxt_valid;
+  }
+  acc.fold(sg, cells.i, cells.wj, pq);
+  __syncwarp();
+
+  // ---------------- sub-grid -> global plane stack (as in grid_kernel<float>) ----------------
+  const int P0 = item.win * g.win_step;
+  const int su0 = item.tu * kTile - kHalo + g.nu / 2;  // shifted -> FFT order: (s + nu/2) mod nu
+  const int sv0 = item.tv * kTile - kHalo + g.nv / 2;
+  constexpr int kPairs = (kSub + 1) / 2;
+  const int odd = sv0 & 1;
+  for (int t = lane; t < 4 * kSub * kPairs; t += 32) {
+    const int jp = t % kPairs, q = t / kPairs;
+    const int i = q % kSub, pp = q / kSub;
+    const int j = 2 * jp - odd;
+    const bool ok0 = j >= 0, ok1 = j + 1 < kSub;
+    const float4 c0 = ok0 ? sg[(pp * kSub + i) * kSub + j] : make_float4(0.f, 0.f, 0.f, 0.f);
+    const float4 c1 = ok1 ? sg[(pp * kSub + i) * kSub + j + 1] : make_float4(0.f, 0.f, 0.f, 0.f);
+    const int gi = (su0 + i) % g.nu;
+    const int gj = (sv0 + j + g.nv) % g.nv;
+#pragma unroll
+    for (int h = 0; h < 2; ++h) {
+      const int plane = P0 + 2 * pp + h;
+      if (plane >= g.nplanes) continue;
+      const int slot = plane - plane_base;
+      if (slot < 0 || slot >= nslots) continue;
+      const float va = h ? c0.z : c0.x, vb = h ? c0.w : c0.y, vc = h ? c1.z : c1.x, vd = h ? c1.w : c1.y;
+      if (va == 0.f && vb == 0.f && vc == 0.f && vd == 0.f) continue;
+      float* dst = grid + 2 * (((int64_t)slot * g.nu + gi) * g.nv + gj);
+      if (ok0 && ok1) {
+        red_add_v4(dst, va, vb, vc, vd);
+      } else if (ok0) {
+        atomicAdd(dst, va);
+        atomicAdd(dst + 1, vb);
+      } else {
+        atomicAdd(dst + 2, vc);
+        atomicAdd(dst + 3, vd);
+      }
+    }
+  }
+}
+
 // Wide supports (W > 8, only reached for very small epsilon): plain scatter with global atomics.
 template <typename R>
 __global__ void __launch_bounds__(128) grid_wide_kernel(const Item* __restrict__ items, int64_t item_base,
@@ -553,7 +851,14 @@ cip_status launch(cip_ctx* ctx, const GridGeom& g, int64_t nrec_total, int64_t i
   const int64_t n = item_end - item_begin;
   if (n <= 0) return CIP_OK;
   CIP_REQUIRE(n < ((int64_t)1 << 31), "too many work items");
-  if (g.W <= kFastSupport) {
+  if (g.W <= kFastSupport && sizeof(R) == 4 && !getenv("CIP_GRID_TWO_WARP")) {
+    auto kern = grid_warp_kernel;
+    CIP_CHECK_CUDA(cudaFuncSetAttribute(kern, cudaFuncAttributeMaxDynamicSharedMemorySize, kWarpSmemBytes));
+    CIP_CHECK_CUDA(cudaFuncSetAttribute(kern, cudaFuncAttributePreferredSharedMemoryCarveout,
+                                        (int)cudaSharedmemCarveoutMaxShared));
+    kern<<<(unsigned)n, 32, kWarpSmemBytes, ctx->stream>>>(items, item_begin, reinterpret_cast<const Rec<float>*>(recs), g,
+                                                           reinterpret_cast<float*>(grid), plane_base, nslots);
+  } else if (g.W <= kFastSupport) {
     constexpr size_t smem = grid_smem_bytes<R>();
     auto kern = grid_kernel<R>;
     CIP_CHECK_CUDA(cudaFuncSetAttribute(kern, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem));
