@@ -35,24 +35,26 @@ template <int PASS, typename R>
 __global__ void __launch_bounds__(256) runs_kernel(DevInputs in, GridGeom g, int64_t* __restrict__ row_nruns,
                                                    const int64_t* __restrict__ row_off, Run* __restrict__ runs,
                                                    uint64_t* __restrict__ keys, const int64_t* __restrict__ outpos,
-                                                   Rec<R>* __restrict__ recs) {
+                                                   Rec<R>* __restrict__ recs, const double* __restrict__ finv) {
   const int lane = threadIdx.x & 31;
   const int64_t row = ((int64_t)blockIdx.x * blockDim.x + threadIdx.x) >> 5;
   if (row >= in.nrow) return;
-  const double um = in.uvw[3 * row], vm = in.uvw[3 * row + 1], wm = in.uvw[3 * row + 2];
+  const BinConsts kc = bin_consts(g);
+  const RowGeom rg = row_geom(g, in.uvw[3 * row], in.uvw[3 * row + 1], in.uvw[3 * row + 2]);
   uint64_t carry = ~0ull;
   int64_t n = 0;
   int carry_ch0 = 0;
   const int64_t base = PASS ? row_off[row] : 0;
-  const int snap = g.W <= kFastSupport ? 9 - g.W : 1;
   for (int64_t c0 = 0; c0 < in.nchan; c0 += 32) {
     const int64_t c = c0 + lane;
     const bool valid = c < in.nchan;
     uint64_t key = ~0ull;
     SampleGeom s;
+    BinCell bc;
     if (valid) {
-      s = sample_geom(g, um, vm, wm, in.freq[c] / kSpeedOfLight);
-      key = (bin_key(g, s) << kSubKeyBits) | window_lattice(g, s);
+      s = sample_geom<PASS == 2>(g, kc, rg, finv[c]);
+      bc = bin_cell(g, kc, s);
+      key = bin_key(g, bc);
     }
     uint64_t prev = __shfl_up_sync(0xffffffffu, key, 1);
     if (lane == 0) prev = carry;
@@ -91,16 +93,11 @@ __global__ void __launch_bounds__(256) runs_kernel(DevInputs in, GridGeom g, int
             re = t;
           }
         }
-        const int tu = (s.i0 + kHalo) / kTile, tv = (s.j0 + kHalo) / kTile;
-        const int win = g.W <= kFastSupport ? s.p0 / g.win_step : 0;
-        const uint32_t i0r = (uint32_t)(s.i0 + kHalo - tu * kTile);
-        const uint32_t j0r = (uint32_t)(s.j0 + kHalo - tv * kTile);
-        const uint32_t p0r = (uint32_t)(s.p0 - win * g.win_step);
         Rec<R> rec;
-        // bits 16-20 / 21-25: origin of the gridder's register window (i0r, j0r snapped to the lattice)
-        const uint32_t wi = i0r - i0r % (uint32_t)snap, wj = j0r - j0r % (uint32_t)snap;
-        rec.cell = i0r | (j0r << 5) | (p0r << 10);
-        if (g.W <= kFastSupport) rec.cell |= (wi << 16) | (wj << 21);  // wide supports: p0r may need the high bits
+        rec.cell = bc.i0r | (bc.j0r << 5) | (bc.p0r << 10);
+        // bits 16-20 / 21-25: origin of the gridder's register window (i0r, j0r snapped to the lattice);
+        // wide supports have no windows and p0r may need the high bits
+        if (kc.fast) rec.cell |= ((bc.lu * kc.snap) << 16) | ((bc.lv * kc.snap) << 21);
         if constexpr (sizeof(R) == 4) {
           rec.fu = s.fu;
           rec.fv = s.fv;
@@ -124,6 +121,11 @@ __global__ void __launch_bounds__(256) runs_kernel(DevInputs in, GridGeom g, int
     carry = __shfl_sync(0xffffffffu, key, 31);
   }
   if (PASS == 0 && lane == 0) row_nruns[row] = n;
+}
+
+__global__ void finv_kernel(const double* __restrict__ freq, int64_t nchan, double* __restrict__ finv) {
+  int64_t c = (int64_t)blockIdx.x * blockDim.x + threadIdx.x;
+  if (c < nchan) finv[c] = freq[c] / kSpeedOfLight;
 }
 
 __global__ void run_len_kernel(const Run* __restrict__ runs, int64_t nruns, int32_t nchan, uint32_t* __restrict__ idx,
@@ -229,7 +231,11 @@ cip_status run_binning(cip_ctx* ctx, const DevInputs& in, const GridGeom& g, int
   int64_t* row_off = ctx->row_off.as<int64_t>();
   CIP_CHECK_CUDA(cudaMemsetAsync(row_nruns + nrow, 0, sizeof(int64_t), st));
   const int rblocks = nblk(nrow * 32, 256);
-  runs_kernel<0, float><<<rblocks, 256, 0, st>>>(in, g, row_nruns, nullptr, nullptr, nullptr, nullptr, (Rec<float>*)nullptr);
+  CIP_TRY(ctx->finv.ensure(sizeof(double) * nchan));
+  double* finv = ctx->finv.as<double>();
+  finv_kernel<<<nblk(nchan, 256), 256, 0, st>>>(in.freq, nchan, finv);
+  ctx->launches++;
+  runs_kernel<0, float><<<rblocks, 256, 0, st>>>(in, g, row_nruns, nullptr, nullptr, nullptr, nullptr, (Rec<float>*)nullptr, finv);
   ctx->launches++;
   size_t tmp_bytes = 0;
   CIP_CHECK_CUDA(cub::DeviceScan::ExclusiveSum(nullptr, tmp_bytes, row_nruns, row_off, nrow + 1, st));
@@ -250,7 +256,7 @@ cip_status run_binning(cip_ctx* ctx, const DevInputs& in, const GridGeom& g, int
   CIP_TRY(ctx->run_len.ensure(sizeof(int32_t) * nruns));
   Run* runs = ctx->runs.as<Run>();
   runs_kernel<1, float><<<rblocks, 256, 0, st>>>(in, g, nullptr, row_off, runs, ctx->run_keys.as<uint64_t>(), nullptr,
-                                                 (Rec<float>*)nullptr);
+                                                 (Rec<float>*)nullptr, finv);
   run_len_kernel<<<nblk(nruns, 256), 256, 0, st>>>(runs, nruns, (int32_t)nchan, ctx->run_idx.as<uint32_t>(),
                                                    ctx->run_len.as<int32_t>());
   ctx->launches += 2;
@@ -326,10 +332,10 @@ cip_status run_binning(cip_ctx* ctx, const DevInputs& in, const GridGeom& g, int
   CIP_TRY(ctx->recs.ensure(recs_bytes(nrec)));
   if (fp64)
     runs_kernel<2, double><<<rblocks, 256, 0, st>>>(in, g, nullptr, row_off, nullptr, nullptr, outpos,
-                                                    ctx->recs.as<Rec<double>>());
+                                                    ctx->recs.as<Rec<double>>(), finv);
   else
     runs_kernel<2, float><<<rblocks, 256, 0, st>>>(in, g, nullptr, row_off, nullptr, nullptr, outpos,
-                                                   ctx->recs.as<Rec<float>>());
+                                                   ctx->recs.as<Rec<float>>(), finv);
   ctx->launches++;
   CIP_CHECK_CUDA(cudaGetLastError());
 

@@ -165,7 +165,7 @@ struct cip_ctx {
   void* scan_host_dev = nullptr;  // its device-side address
   // binning
   cip::DevBuf row_nruns, row_off, runs, run_keys, run_keys_alt, run_idx, run_idx_alt, runs_sorted, run_len,
-      run_visoff, flags, group_start, item_idx, items, win_item_start, cub_tmp, recs;
+      run_visoff, flags, group_start, item_idx, items, win_item_start, cub_tmp, recs, finv;
   // grids, fft, image
   cip::DevBuf grid, image, tables;
   std::vector<double> tables_key;  // plan parameters the correction tables were built for

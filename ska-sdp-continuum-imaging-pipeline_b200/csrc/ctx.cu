@@ -248,7 +248,7 @@ extern "C" cip_status cip_ctx_destroy(cip_ctx* ctx) {
                     &ctx->scan_out, &ctx->row_nruns, &ctx->row_off, &ctx->runs, &ctx->run_keys,
                     &ctx->run_keys_alt, &ctx->run_idx, &ctx->run_idx_alt, &ctx->runs_sorted, &ctx->run_len,
                     &ctx->run_visoff, &ctx->flags, &ctx->group_start, &ctx->item_idx, &ctx->items,
-                    &ctx->win_item_start, &ctx->cub_tmp, &ctx->recs, &ctx->grid, &ctx->image, &ctx->tables,
+                    &ctx->win_item_start, &ctx->cub_tmp, &ctx->recs, &ctx->finv, &ctx->grid, &ctx->image, &ctx->tables,
                     &ctx->t_uvw, &ctx->t_freq, &ctx->t_vis};
   for (DevBuf* b : bufs) b->release();
   if (ctx->scan_host) cudaFreeHost(ctx->scan_host);

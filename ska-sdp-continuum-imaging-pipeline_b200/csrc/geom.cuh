@@ -13,43 +13,85 @@ struct SampleGeom {
   double w;           // |w| in wavelengths
 };
 
+// Constants of one binning launch derived from the geometry (loop-invariant, a few registers).
+struct BinConsts {
+  double nu_d, nv_d, off_u, off_v;  // left edge of the support: x * nu + (nu - W) / 2 (shifted coordinates)
+  double w_scale, w_off;            // first-plane coordinate: |w| * inv_dw - (w0 * inv_dw + W / 2)
+  uint32_t ws_magic;                // ceil(2^32 / win_step): p0 / win_step = umulhi(p0, ws_magic), exact for p0 < 2^29
+  uint32_t snap_rcp;                // ceil(256 / snap): i / snap = (i * snap_rcp) >> 8, exact for i < 8, snap <= 5
+  int snap, pmax;
+  bool fast;                        // W <= kFastSupport: windows and register-window lattice in use
+};
+__device__ __forceinline__ BinConsts bin_consts(const GridGeom& g) {
+  BinConsts k;
+  k.nu_d = (double)g.nu;
+  k.nv_d = (double)g.nv;
+  k.off_u = 0.5 * g.nu - 0.5 * g.W;
+  k.off_v = 0.5 * g.nv - 0.5 * g.W;
+  k.w_scale = g.inv_dw;
+  k.w_off = -g.w0 * g.inv_dw - 0.5 * g.W;
+  k.fast = g.W <= kFastSupport;
+  k.snap = k.fast ? 9 - g.W : 1;
+  k.snap_rcp = (256u + k.snap - 1) / k.snap;
+  k.ws_magic = g.win_step > 1 ? (uint32_t)((0x100000000ull + g.win_step - 1) / g.win_step) : 0u;
+  k.pmax = g.nplanes - g.W;
+  return k;
+}
+
+// Per-row part: the Hermitian flip depends only on the sign of w in metres (frequencies are positive),
+// and the pixel scale is folded into the row's coordinates.
+struct RowGeom {
+  double upx, vpy, wabs;
+  bool flip;
+};
+__device__ __forceinline__ RowGeom row_geom(const GridGeom& g, double um, double vm, double wm) {
+  RowGeom r;
+  r.flip = wm < 0.0;
+  const double sg = r.flip ? -1.0 : 1.0;
+  r.upx = sg * um * g.px;
+  r.vpy = sg * vm * g.py;
+  r.wabs = g.do_wstacking ? sg * wm : 0.0;
+  return r;
+}
+
 // Sample (row, chan) -> support origin on the oversampled grid and in the w-plane stack.
 // Follows the published improved w-stacking scheme (Arras et al. 2021, Ye et al. 2022) that
 // ducc0.wgridder.ms2dirty implements (reference call site src/ska_sdp_cip/invert.py:170-183).
 // All coordinate arithmetic is float64: grid indices reach 65536 and need ~1e-6 cell accuracy.
-__device__ __forceinline__ SampleGeom sample_geom(const GridGeom& g, double um, double vm, double wm, double finv) {
+// finv = frequency / c (tabulated once per call).  FRAC = false skips the fractional offsets (key passes).
+template <bool FRAC>
+__device__ __forceinline__ SampleGeom sample_geom(const GridGeom& g, const BinConsts& k, const RowGeom& r, double finv) {
   SampleGeom s;
-  double u = um * finv, v = vm * finv, w = wm * finv;
-  s.flip = w < 0.0;
-  if (s.flip) { u = -u; v = -v; w = -w; }
-  if (!g.do_wstacking) w = 0.0;
-  s.w = w;
-  double xu = u * g.px;
+  s.flip = r.flip;
+  double xu = r.upx * finv;
   xu -= rint(xu);
-  double xv = v * g.py;
+  double xv = r.vpy * finv;
   xv -= rint(xv);
-  double us = xu * g.nu + 0.5 * g.nu - 0.5 * g.W;  // left edge of the support, shifted coordinates
-  double vs = xv * g.nv + 0.5 * g.nv - 0.5 * g.W;
-  double ci = ceil(us), cj = ceil(vs);
+  const double us = fma(xu, k.nu_d, k.off_u), vs = fma(xv, k.nv_d, k.off_v);
+  const double ci = ceil(us), cj = ceil(vs);
   s.i0 = (int)ci;
   s.j0 = (int)cj;
-  s.dfu = ci - us;
-  s.dfv = cj - vs;
-  s.fu = (float)s.dfu;
-  s.fv = (float)s.dfv;
+  s.w = r.wabs * finv;
+  if (FRAC) {
+    s.dfu = ci - us;
+    s.dfv = cj - vs;
+    s.fu = (float)s.dfu;
+    s.fv = (float)s.dfv;
+  }
   if (g.do_wstacking) {
-    double ps = (w - g.w0) * g.inv_dw - 0.5 * g.W;
+    const double ps = fma(s.w, k.w_scale, k.w_off);
     double cp = ceil(ps);
     int p0 = (int)cp;
     // samples outside the scanned w range are inactive (zero weight); keep their window legal
-    int pmax = g.nplanes - g.W;
-    if (p0 < 0 || p0 > pmax) {
-      p0 = p0 < 0 ? 0 : pmax;
+    if (p0 < 0 || p0 > k.pmax) {
+      p0 = p0 < 0 ? 0 : k.pmax;
       cp = (double)p0;
     }
     s.p0 = p0;
-    s.dfw = fmin(fmax(cp - ps, 0.0), 1.0);
-    s.fw = (float)s.dfw;
+    if (FRAC) {
+      s.dfw = fmin(fmax(cp - ps, 0.0), 1.0);
+      s.fw = (float)s.dfw;
+    }
   } else {
     s.p0 = 0;
     s.fw = 0.0f;
@@ -58,20 +100,30 @@ __device__ __forceinline__ SampleGeom sample_geom(const GridGeom& g, double um, 
   return s;
 }
 
-__device__ __forceinline__ uint64_t bin_key(const GridGeom& g, const SampleGeom& s) {
-  int tu = (s.i0 + kHalo) / kTile, tv = (s.j0 + kHalo) / kTile;
-  int win = g.W <= kFastSupport ? s.p0 / g.win_step : 0;
-  return ((uint64_t)win * g.ntu + tu) * g.ntv + tv;
+// Decomposition of the support origin into (window, tile, position inside the tile, register-window lattice).
+struct BinCell {
+  int tu, tv, win;
+  uint32_t i0r, j0r, p0r;  // origin inside the tile / first plane inside the window
+  uint32_t lu, lv;         // lattice position of the register window (i0r / snap, j0r / snap)
+};
+__device__ __forceinline__ BinCell bin_cell(const GridGeom& g, const BinConsts& k, const SampleGeom& s) {
+  BinCell b;
+  const uint32_t iu = (uint32_t)(s.i0 + kHalo), iv = (uint32_t)(s.j0 + kHalo);  // non-negative by construction
+  b.tu = (int)(iu / kTile);
+  b.tv = (int)(iv / kTile);
+  b.i0r = iu % kTile;
+  b.j0r = iv % kTile;
+  b.win = k.fast && k.ws_magic ? (int)__umulhi((uint32_t)s.p0, k.ws_magic) : (k.fast ? s.p0 : 0);
+  b.p0r = (uint32_t)(s.p0 - b.win * g.win_step);
+  b.lu = k.fast ? (b.i0r * k.snap_rcp) >> 8 : 0u;
+  b.lv = k.fast ? (b.j0r * k.snap_rcp) >> 8 : 0u;
+  return b;
 }
 
-// Position of the sample's register window (8 x 8 cells, origin snapped to multiples of 9-W cells,
-// see grid.cu) inside its tile: 4 bits per axis.
 constexpr int kSubKeyBits = 8;
-__device__ __forceinline__ uint32_t window_lattice(const GridGeom& g, const SampleGeom& s) {
-  if (g.W > kFastSupport) return 0;
-  const int snap = 9 - g.W;
-  const int iu = (s.i0 + kHalo) % kTile, iv = (s.j0 + kHalo) % kTile;
-  return (uint32_t)((iu / snap) << 4 | (iv / snap));
+// sort key of a run: (window, tile) bin in the high bits, register-window lattice position in the low 8
+__device__ __forceinline__ uint64_t bin_key(const GridGeom& g, const BinCell& b) {
+  return ((((uint64_t)b.win * g.ntu + b.tu) * g.ntv + b.tv) << kSubKeyBits) | (b.lu << 4 | b.lv);
 }
 
 __device__ __forceinline__ bool sample_active(const float2 v, const float* wgt, const uint8_t* mask, int64_t k,

@@ -540,7 +540,8 @@ __global__ void __launch_bounds__(kGridThreads) grid_kernel(const Item* __restri
 constexpr int kARow = 64 * 4 + 16;  // bytes per visibility of the A stage; the pad makes the producer's
 constexpr int kBRow = 16 * 4 + 16;  // 128-bit stores (one row per lane) bank-conflict free
 constexpr int kWarpSubGridBytes = 16 * 4 * kSub * kSub;
-constexpr int kWarpSmemBytes = kWarpSubGridBytes + kBatch * (kARow + kBRow + 4);
+constexpr int kWarpStageBytes = kBatch * (kARow + kBRow + 4);
+constexpr int warp_smem_bytes(int nw) { return kWarpSubGridBytes + nw * kWarpStageBytes; }
 
 template <int OFF>
 __device__ __forceinline__ float4 lds_f4(uint32_t addr) {
@@ -603,8 +604,8 @@ __device__ __forceinline__ WarpOps warp_load(uint32_t pa, uint32_t pb) {
   WarpOps o;
   o.a0 = lds_f4<U * kARow>(pa);
   o.a1 = lds_f4<U * kARow + 16>(pa);
-  o.b0 = lds_u1<U * kBRow>(pb);
-  o.b1 = lds_u1<U * kBRow + 8>(pb);
+  o.b0 = lds_u1<U * kBRow>(pb);  // B row = [h][pq]: plane 2pq + h at h*32 + pq*8, so that the two loads are
+  o.b1 = lds_u1<U * kBRow + 32>(pb);  // not fused into one 128-bit load (4 wavefronts instead of 1 + 1)
   return o;
 }
 
@@ -625,15 +626,23 @@ struct WarpAcc {
   }
   // sub-grid cell = float4 {re(2pp), im(2pp), re(2pp+1), im(2pp+1)} for plane pair pp = pq: one float4
   // read-modify-write per owned cell (the lane owns row i, all 8 v residues of the window)
+  template <bool ATOMIC>
   __device__ __forceinline__ void fold(float4* sg, int i, int wj, int pq) {
     float4* row = sg + (pq * kSub + i) * kSub;
 #pragma unroll
     for (int t = 0; t < 8; ++t) {
       float4* p = row + wj + ((t - wj) & 7);
       const float2 x = unpack2(c[t][0]), y = unpack2(c[t][1]);
-      float4 v = *p;
-      v.x += x.x; v.y += x.y; v.z += y.x; v.w += y.y;
-      *p = v;
+      if (ATOMIC) {  // other warps of the CTA fold into the same sub-grid
+        const uint32_t ad = smem_u32(p);
+        asm volatile("red.shared.add.f32 [%0], %1;\n\tred.shared.add.f32 [%0+4], %2;\n\t"
+                     "red.shared.add.f32 [%0+8], %3;\n\tred.shared.add.f32 [%0+12], %4;"
+                     ::"r"(ad), "f"(x.x), "f"(x.y), "f"(y.x), "f"(y.y) : "memory");
+      } else {
+        float4 v = *p;
+        v.x += x.x; v.y += x.y; v.z += y.x; v.w += y.y;
+        *p = v;
+      }
     }
     clear();
   }
@@ -648,48 +657,53 @@ struct WarpCells {
   }
 };
 
-template <int U, bool CHECK>
+template <int U, bool CHECK, bool ATOMIC>
 __device__ __forceinline__ void warp_consume1(uint32_t pa, uint32_t pb, uint32_t porg, uint32_t moved8, const WarpOps& cur,
                                               WarpOps& nxt, WarpAcc& acc, float4* sg, WarpCells& cells, int a, int pq) {
   nxt = warp_load<U + 1>(pa, pb);
   if (CHECK && ((moved8 >> U) & 1u)) {
-    acc.fold(sg, cells.i, cells.wj, pq);
+    acc.template fold<ATOMIC>(sg, cells.i, cells.wj, pq);
     cells.set(lds_u32(porg + 4 * U), a);
   }
   acc.update(cur);
 }
-template <bool CHECK>
+template <bool CHECK, bool ATOMIC>
 __device__ __forceinline__ void warp_consume8(uint32_t pa, uint32_t pb, uint32_t porg, uint32_t moved8, WarpOps& x, WarpAcc& acc,
                                               float4* sg, WarpCells& cells, int a, int pq) {
   WarpOps y;
-  warp_consume1<0, CHECK>(pa, pb, porg, moved8, x, y, acc, sg, cells, a, pq);
-  warp_consume1<1, CHECK>(pa, pb, porg, moved8, y, x, acc, sg, cells, a, pq);
-  warp_consume1<2, CHECK>(pa, pb, porg, moved8, x, y, acc, sg, cells, a, pq);
-  warp_consume1<3, CHECK>(pa, pb, porg, moved8, y, x, acc, sg, cells, a, pq);
-  warp_consume1<4, CHECK>(pa, pb, porg, moved8, x, y, acc, sg, cells, a, pq);
-  warp_consume1<5, CHECK>(pa, pb, porg, moved8, y, x, acc, sg, cells, a, pq);
-  warp_consume1<6, CHECK>(pa, pb, porg, moved8, x, y, acc, sg, cells, a, pq);
-  warp_consume1<7, CHECK>(pa, pb, porg, moved8, y, x, acc, sg, cells, a, pq);
+  warp_consume1<0, CHECK, ATOMIC>(pa, pb, porg, moved8, x, y, acc, sg, cells, a, pq);
+  warp_consume1<1, CHECK, ATOMIC>(pa, pb, porg, moved8, y, x, acc, sg, cells, a, pq);
+  warp_consume1<2, CHECK, ATOMIC>(pa, pb, porg, moved8, x, y, acc, sg, cells, a, pq);
+  warp_consume1<3, CHECK, ATOMIC>(pa, pb, porg, moved8, y, x, acc, sg, cells, a, pq);
+  warp_consume1<4, CHECK, ATOMIC>(pa, pb, porg, moved8, x, y, acc, sg, cells, a, pq);
+  warp_consume1<5, CHECK, ATOMIC>(pa, pb, porg, moved8, y, x, acc, sg, cells, a, pq);
+  warp_consume1<6, CHECK, ATOMIC>(pa, pb, porg, moved8, x, y, acc, sg, cells, a, pq);
+  warp_consume1<7, CHECK, ATOMIC>(pa, pb, porg, moved8, y, x, acc, sg, cells, a, pq);
 }
 
-__global__ void __launch_bounds__(32) grid_warp_kernel(const Item* __restrict__ items, int64_t item_base,
-                                                       const Rec<float>* __restrict__ recs, GridGeom g,
-                                                       float* __restrict__ grid, int plane_base, int nslots) {
+// NW warps per CTA share the item and its sub-grid: warp w takes the w-th contiguous share of the
+// batches (the records are sorted by register window, so each warp sees only a few windows) and has a
+// private operand stage; folds into the shared sub-grid are shared-memory reductions when NW > 1.
+template <int NW>
+__global__ void __launch_bounds__(32 * NW) grid_warp_kernel(const Item* __restrict__ items, int64_t item_base,
+                                                            const Rec<float>* __restrict__ recs, GridGeom g,
+                                                            float* __restrict__ grid, int plane_base, int nslots) {
   extern __shared__ __align__(16) unsigned char smem_raw[];
   float4* sg = reinterpret_cast<float4*>(smem_raw);
-  const uint32_t sA = smem_u32(smem_raw + kWarpSubGridBytes);
+  const int lane = threadIdx.x & 31, warp = threadIdx.x >> 5;
+  const uint32_t sA = smem_u32(smem_raw + kWarpSubGridBytes + warp * kWarpStageBytes);
   const uint32_t sB = sA + kBatch * kARow;
   const uint32_t sOrg = sB + kBatch * kBRow;
 
   const Item item = items[item_base + blockIdx.x];
-  const int lane = threadIdx.x;
   const int nrec = item.nrec;
-  const int nb = (nrec + kBatch - 1) / kBatch;
+  const int nb_all = (nrec + kBatch - 1) / kBatch;
+  const int b_begin = warp * nb_all / NW, b_end = (warp + 1) * nb_all / NW;
   const int64_t base = item.rec_begin;
 
-  bool cur_valid = lane < nrec;
-  Rec<float> cur = load_rec(recs, base + lane, cur_valid);
-  for (int t = lane; t < 4 * kSub * kSub; t += 32) sg[t] = make_float4(0.f, 0.f, 0.f, 0.f);
+  bool cur_valid = b_begin * kBatch + lane < nrec;
+  Rec<float> cur = load_rec(recs, base + b_begin * kBatch + lane, cur_valid);
+  for (int t = threadIdx.x; t < 4 * kSub * kSub; t += 32 * NW) sg[t] = make_float4(0.f, 0.f, 0.f, 0.f);
 
   // producer constants
   const int W = g.W;
@@ -701,14 +715,15 @@ __global__ void __launch_bounds__(32) grid_warp_kernel(const Item* __restrict__ 
   const uint32_t myA = sA + lane * kARow, myB = sB + lane * kBRow;
   // consumer constants
   const int a = lane >> 2, pq = lane & 3;
-  const uint32_t pa0 = sA + a * 32, pb0 = sB + pq * 16;
+  const uint32_t pa0 = sA + a * 32, pb0 = sB + pq * 8;
   WarpAcc acc;
   acc.clear();
   WarpCells cells;
   cells.set(0u, a);
-  __syncwarp();
+  if (NW > 1) __syncthreads();
+  else __syncwarp();
 
-  for (int b = 0; b < nb; ++b) {
+  for (int b = b_begin; b < b_end; ++b) {
     const int kn = (b + 1) * kBatch + lane;
     const bool nxt_valid = kn < nrec;
     const Rec<float> nxt = load_rec(recs, base + kn, nxt_valid);
@@ -738,7 +753,10 @@ __global__ void __launch_bounds__(32) grid_warp_kernel(const Item* __restrict__ 
       }
       const float re = cur_valid ? cur.re : 0.0f, im = cur_valid ? cur.im : 0.0f;
 #pragma unroll
-      for (int q = 0; q < 8; q += 2) sts_f4(myB + q * 8, re * kw[q], im * kw[q], re * kw[q + 1], im * kw[q + 1]);
+      for (int q = 0; q < 8; q += 4) {
+        sts_f4(myB + q * 4, re * kw[q], im * kw[q], re * kw[q + 2], im * kw[q + 2]);                    // even planes
+        sts_f4(myB + 32 + q * 4, re * kw[q + 1], im * kw[q + 1], re * kw[q + 3], im * kw[q + 3]);  // odd planes
+      }
       asm volatile("st.shared.u32 [%0], %1;" ::"r"(sOrg + 4 * lane), "r"(cxy) : "memory");
     }
     __syncwarp();
@@ -752,16 +770,17 @@ __global__ void __launch_bounds__(32) grid_warp_kernel(const Item* __restrict__ 
         // most groups stay inside one register window: branch-free fast path.  The operands of visibility
         // k0 + 8 are prefetched at the end of a group; past the last group that reads the rows after the
         // stage (still inside the CTA's shared memory: kSlack), which are discarded.
-        if (m8 == 0) warp_consume8<false>(pa, pb, porg, m8, x, acc, sg, cells, a, pq);
-        else warp_consume8<true>(pa, pb, porg, m8, x, acc, sg, cells, a, pq);
+        if (m8 == 0) warp_consume8<false, (NW > 1)>(pa, pb, porg, m8, x, acc, sg, cells, a, pq);
+        else warp_consume8<true, (NW > 1)>(pa, pb, porg, m8, x, acc, sg, cells, a, pq);
       }
     }
     __syncwarp();
     cur = nxt;
     cur_valid = nxt_valid;
   }
-  acc.fold(sg, cells.i, cells.wj, pq);
-  __syncwarp();
+  acc.template fold<(NW > 1)>(sg, cells.i, cells.wj, pq);
+  if (NW > 1) __syncthreads();
+  else __syncwarp();
 
   // ---------------- sub-grid -> global plane stack (as in grid_kernel<float>) ----------------
   const int P0 = item.win * g.win_step;
@@ -769,7 +788,7 @@ __global__ void __launch_bounds__(32) grid_warp_kernel(const Item* __restrict__ 
   const int sv0 = item.tv * kTile - kHalo + g.nv / 2;
   constexpr int kPairs = (kSub + 1) / 2;
   const int odd = sv0 & 1;
-  for (int t = lane; t < 4 * kSub * kPairs; t += 32) {
+  for (int t = threadIdx.x; t < 4 * kSub * kPairs; t += 32 * NW) {
     const int jp = t % kPairs, q = t / kPairs;
     const int i = q % kSub, pp = q / kSub;
     const int j = 2 * jp - odd;
@@ -842,6 +861,17 @@ __global__ void __launch_bounds__(128) grid_wide_kernel(const Item* __restrict__
   }
 }
 
+template <int NW>
+cip_status launch_warp(cip_ctx* ctx, const Item* items, int64_t item_begin, int64_t n, const Rec<float>* recs,
+                       const GridGeom& g, float* grid, int plane_base, int nslots) {
+  auto kern = grid_warp_kernel<NW>;
+  constexpr int smem = warp_smem_bytes(NW);
+  CIP_CHECK_CUDA(cudaFuncSetAttribute(kern, cudaFuncAttributeMaxDynamicSharedMemorySize, smem));
+  CIP_CHECK_CUDA(cudaFuncSetAttribute(kern, cudaFuncAttributePreferredSharedMemoryCarveout, (int)cudaSharedmemCarveoutMaxShared));
+  kern<<<(unsigned)n, 32 * NW, smem, ctx->stream>>>(items, item_begin, recs, g, grid, plane_base, nslots);
+  return CIP_OK;
+}
+
 template <typename R>
 cip_status launch(cip_ctx* ctx, const GridGeom& g, int64_t nrec_total, int64_t item_begin, int64_t item_end,
                   void* grid, int plane_base, int nslots) {
@@ -852,12 +882,11 @@ cip_status launch(cip_ctx* ctx, const GridGeom& g, int64_t nrec_total, int64_t i
   if (n <= 0) return CIP_OK;
   CIP_REQUIRE(n < ((int64_t)1 << 31), "too many work items");
   if (g.W <= kFastSupport && sizeof(R) == 4 && !getenv("CIP_GRID_TWO_WARP")) {
-    auto kern = grid_warp_kernel;
-    CIP_CHECK_CUDA(cudaFuncSetAttribute(kern, cudaFuncAttributeMaxDynamicSharedMemorySize, kWarpSmemBytes));
-    CIP_CHECK_CUDA(cudaFuncSetAttribute(kern, cudaFuncAttributePreferredSharedMemoryCarveout,
-                                        (int)cudaSharedmemCarveoutMaxShared));
-    kern<<<(unsigned)n, 32, kWarpSmemBytes, ctx->stream>>>(items, item_begin, reinterpret_cast<const Rec<float>*>(recs), g,
-                                                           reinterpret_cast<float*>(grid), plane_base, nslots);
+    static const int nw = getenv("CIP_GRID_WARPS") ? atoi(getenv("CIP_GRID_WARPS")) : 1;
+    CIP_TRY((nw == 1 ? launch_warp<1> : nw == 2 ? launch_warp<2> : nw == 3 ? launch_warp<3> : nw == 5 ? launch_warp<5>
+                                                                                                : launch_warp<4>)(
+        ctx, items, item_begin, n, reinterpret_cast<const Rec<float>*>(recs), g, reinterpret_cast<float*>(grid), plane_base,
+        nslots));
   } else if (g.W <= kFastSupport) {
     constexpr size_t smem = grid_smem_bytes<R>();
     auto kern = grid_kernel<R>;
