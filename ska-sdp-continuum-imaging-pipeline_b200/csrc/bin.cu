@@ -9,6 +9,7 @@
 // gridder-ready records (all float64 coordinate arithmetic happens here, once) and cut into work
 // items of at most kItemVis records.
 #include <algorithm>
+#include <cstdlib>
 
 #include <cub/device/device_radix_sort.cuh>
 #include <cub/device/device_scan.cuh>
@@ -45,12 +46,25 @@ __global__ void __launch_bounds__(256) runs_kernel(DevInputs in, GridGeom g, int
   int64_t n = 0;
   int carry_ch0 = 0;
   const int64_t base = PASS ? row_off[row] : 0;
+  // record pass: the output positions of the row's first 32 runs are fetched up front (one coalesced load,
+  // in flight together with the samples) instead of one dependent gather after each ballot
+  int64_t pre_out = 0;
+  if (PASS == 2 && lane < row_nruns[row]) pre_out = outpos[base + lane];
   for (int64_t c0 = 0; c0 < in.nchan; c0 += 32) {
     const int64_t c = c0 + lane;
     const bool valid = c < in.nchan;
     uint64_t key = ~0ull;
     SampleGeom s;
     BinCell bc;
+    // record pass: issue the sample loads before the geometry, which does not depend on them (the pass is
+    // bound by memory latency: ncu showed 59 % of the stalls on these loads when they came after the ballot)
+    float2 v = make_float2(0.f, 0.f);
+    float wgt = 0.f;
+    if (PASS == 2 && valid) {
+      v = __ldcs(in.vis + row * in.vstride + c);
+      wgt = in.wgt ? __ldcs(in.wgt + row * in.wstride + c) : 1.0f;
+      if (in.mask && in.mask[row * in.wstride + c] == 0) wgt = 0.0f;
+    }
     if (valid) {
       s = sample_geom<PASS == 2>(g, kc, rg, finv[c]);
       bc = bin_cell(g, kc, s);
@@ -71,12 +85,13 @@ __global__ void __launch_bounds__(256) runs_kernel(DevInputs in, GridGeom g, int
     }
     if (PASS == 2) {
       const unsigned upto = m & (0xffffffffu >> (31 - lane));  // starts at or before this lane
-      const int64_t r = base + n + __popc(upto) - 1;           // input-order index of this sample's run
+      const int64_t rel = n + __popc(upto) - 1;                // index of this sample's run within the row
+      const int64_t r = base + rel;                            // input-order index of this sample's run
+      int64_t out0 = __shfl_sync(0xffffffffu, pre_out, (int)(rel & 31));
+      if (valid && rel >= 32) out0 = outpos[r];
       const int ch0 = upto ? (int)c0 + (31 - __clz(upto)) : carry_ch0;
       if (valid) {
-        const float2 v = in.vis[row * in.vstride + c];
-        float wgt;
-        const bool act = sample_active(v, in.wgt, in.mask, row * in.wstride + c, &wgt);
+        const bool act = wgt != 0.0f && (v.x != 0.0f || v.y != 0.0f);
         R re = 0, im = 0;
         if (act) {
           re = (R)v.x * (R)wgt;
@@ -110,7 +125,7 @@ __global__ void __launch_bounds__(256) runs_kernel(DevInputs in, GridGeom g, int
         rec.re = re;
         rec.im = im;
         if constexpr (sizeof(R) == 4) rec.pad[0] = rec.pad[1] = 0.f;
-        float4* dst = reinterpret_cast<float4*>(recs + outpos[r] + ((int)c - ch0));
+        float4* dst = reinterpret_cast<float4*>(recs + out0 + ((int)c - ch0));
         const float4* src = reinterpret_cast<const float4*>(&rec);
         dst[0] = src[0];
         dst[1] = src[1];
@@ -121,6 +136,85 @@ __global__ void __launch_bounds__(256) runs_kernel(DevInputs in, GridGeom g, int
     carry = __shfl_sync(0xffffffffu, key, 31);
   }
   if (PASS == 0 && lane == 0) row_nruns[row] = n;
+}
+
+// PASS 0 and PASS 1 in one kernel (rows of at most kFusedChan channels): each warp walks its row once, keeps
+// the sample keys in shared memory and counts its runs; the CTA reserves a contiguous block of run slots with
+// one atomic on a global cursor; the warps then write their runs from the cached keys.  Blocks of runs land in
+// CTA arrival order rather than row order, which only permutes the (float) accumulation order inside a bin.
+constexpr int kFusedWarps = 8;
+constexpr int kFusedChan = 768;
+__global__ void __launch_bounds__(32 * kFusedWarps) runs_fused_kernel(DevInputs in, GridGeom g, int64_t* __restrict__ row_nruns,
+                                                                      int64_t* __restrict__ row_off, Run* __restrict__ runs,
+                                                                      uint64_t* __restrict__ keys,
+                                                                      const double* __restrict__ finv, int nch32,
+                                                                      int64_t cap) {
+  extern __shared__ uint64_t skeys[];  // [warp][nch32]
+  __shared__ int s_cnt[kFusedWarps];
+  __shared__ unsigned long long s_base;
+  const int lane = threadIdx.x & 31, warp = threadIdx.x >> 5;
+  const int64_t row = (int64_t)blockIdx.x * kFusedWarps + warp;
+  const bool active = row < in.nrow;
+  uint64_t* mykeys = skeys + (size_t)warp * nch32;
+  int n = 0;
+  if (active) {
+    const BinConsts kc = bin_consts(g);
+    const RowGeom rg = row_geom(g, in.uvw[3 * row], in.uvw[3 * row + 1], in.uvw[3 * row + 2]);
+    uint64_t carry = ~0ull;
+    for (int c0 = 0; c0 < (int)in.nchan; c0 += 32) {
+      const int c = c0 + lane;
+      const bool valid = c < in.nchan;
+      uint64_t key = ~0ull;
+      if (valid) {
+        const SampleGeom s = sample_geom<false>(g, kc, rg, finv[c]);
+        key = bin_key(g, bin_cell(g, kc, s));
+      }
+      mykeys[c] = key;
+      uint64_t prev = __shfl_up_sync(0xffffffffu, key, 1);
+      if (lane == 0) prev = carry;
+      n += __popc(__ballot_sync(0xffffffffu, valid && key != prev));
+      carry = __shfl_sync(0xffffffffu, key, 31);
+    }
+  }
+  if (lane == 0) s_cnt[warp] = n;
+  __syncthreads();
+  if (threadIdx.x == 0) {
+    int total = 0;
+    for (int w = 0; w < kFusedWarps; ++w) total += s_cnt[w];
+    s_base = atomicAdd(reinterpret_cast<unsigned long long*>(row_off + in.nrow), (unsigned long long)total);
+  }
+  __syncthreads();
+  if (!active) return;
+  int64_t base = (int64_t)s_base;
+  for (int w = 0; w < warp; ++w) base += s_cnt[w];
+  if (lane == 0) {
+    row_off[row] = base;
+    row_nruns[row] = n;
+  }
+  uint64_t carry = ~0ull;
+  int m_before = 0;
+  for (int c0 = 0; c0 < (int)in.nchan; c0 += 32) {
+    const int c = c0 + lane;
+    const bool valid = c < in.nchan;
+    const uint64_t key = mykeys[c];
+    uint64_t prev = __shfl_up_sync(0xffffffffu, key, 1);
+    if (lane == 0) prev = carry;
+    const bool start = valid && key != prev;
+    const unsigned m = __ballot_sync(0xffffffffu, start);
+    if (start) {
+      const int64_t pos = base + m_before + __popc(m & ((1u << lane) - 1));
+      Run r;
+      r.key = key >> kSubKeyBits;
+      r.row = (int32_t)row;
+      r.ch0 = (int32_t)c;
+      if (pos < cap) {
+        runs[pos] = r;
+        keys[pos] = key;
+      }
+    }
+    m_before += __popc(m);
+    carry = __shfl_sync(0xffffffffu, key, 31);
+  }
 }
 
 __global__ void finv_kernel(const double* __restrict__ freq, int64_t nchan, double* __restrict__ finv) {
@@ -216,8 +310,9 @@ inline int nblk(int64_t n, int per) { return (int)((n + per - 1) / per); }
 
 }  // namespace
 
-cip_status run_binning(cip_ctx* ctx, const DevInputs& in, const GridGeom& g, int fp64, BinResult* out) {
+cip_status run_binning(cip_ctx* ctx, int slot, const DevInputs& in, const GridGeom& g, int fp64, BinResult* out) {
   cudaStream_t st = ctx->stream;
+  BinWork& w = ctx->work[slot];
   const int64_t nrow = in.nrow, nchan = in.nchan;
   out->nruns = out->nrec = out->nitems = 0;
   out->win_item_start.assign(g.nwin + 1, 0);
@@ -225,41 +320,65 @@ cip_status run_binning(cip_ctx* ctx, const DevInputs& in, const GridGeom& g, int
   const int64_t nrec = nrow * nchan;
 
   // --- runs per row, offsets -------------------------------------------------------
-  CIP_TRY(ctx->row_nruns.ensure(sizeof(int64_t) * (nrow + 1)));
-  CIP_TRY(ctx->row_off.ensure(sizeof(int64_t) * (nrow + 1)));
-  int64_t* row_nruns = ctx->row_nruns.as<int64_t>();
-  int64_t* row_off = ctx->row_off.as<int64_t>();
+  CIP_TRY(w.row_nruns.ensure(sizeof(int64_t) * (nrow + 1)));
+  CIP_TRY(w.row_off.ensure(sizeof(int64_t) * (nrow + 1)));
+  int64_t* row_nruns = w.row_nruns.as<int64_t>();
+  int64_t* row_off = w.row_off.as<int64_t>();
   CIP_CHECK_CUDA(cudaMemsetAsync(row_nruns + nrow, 0, sizeof(int64_t), st));
   const int rblocks = nblk(nrow * 32, 256);
-  CIP_TRY(ctx->finv.ensure(sizeof(double) * nchan));
-  double* finv = ctx->finv.as<double>();
+  CIP_TRY(w.finv.ensure(sizeof(double) * nchan));
+  double* finv = w.finv.as<double>();
   finv_kernel<<<nblk(nchan, 256), 256, 0, st>>>(in.freq, nchan, finv);
   ctx->launches++;
-  runs_kernel<0, float><<<rblocks, 256, 0, st>>>(in, g, row_nruns, nullptr, nullptr, nullptr, nullptr, (Rec<float>*)nullptr, finv);
-  ctx->launches++;
-  size_t tmp_bytes = 0;
-  CIP_CHECK_CUDA(cub::DeviceScan::ExclusiveSum(nullptr, tmp_bytes, row_nruns, row_off, nrow + 1, st));
-  CIP_TRY(ctx->cub_tmp.ensure(tmp_bytes));
-  tmp_bytes = ctx->cub_tmp.cap;
-  CIP_CHECK_CUDA(cub::DeviceScan::ExclusiveSum(ctx->cub_tmp.p, tmp_bytes, row_nruns, row_off, nrow + 1, st));
-  ctx->launches++;
   int64_t nruns = 0;
-  CIP_TRY(d2h_scalar(ctx, row_off + nrow, &nruns));
-  CIP_REQUIRE(nruns > 0 && nruns < ((int64_t)1 << 32), "unexpected number of runs %lld", (long long)nruns);
-
-  // --- write runs, lengths ---------------------------------------------------------
-  CIP_TRY(ctx->runs.ensure(sizeof(Run) * nruns));
-  CIP_TRY(ctx->run_keys.ensure(sizeof(uint64_t) * nruns));
-  CIP_TRY(ctx->run_keys_alt.ensure(sizeof(uint64_t) * nruns));
-  CIP_TRY(ctx->run_idx.ensure(sizeof(uint32_t) * nruns));
-  CIP_TRY(ctx->run_idx_alt.ensure(sizeof(uint32_t) * nruns));
-  CIP_TRY(ctx->run_len.ensure(sizeof(int32_t) * nruns));
-  Run* runs = ctx->runs.as<Run>();
-  runs_kernel<1, float><<<rblocks, 256, 0, st>>>(in, g, nullptr, row_off, runs, ctx->run_keys.as<uint64_t>(), nullptr,
-                                                 (Rec<float>*)nullptr, finv);
-  run_len_kernel<<<nblk(nruns, 256), 256, 0, st>>>(runs, nruns, (int32_t)nchan, ctx->run_idx.as<uint32_t>(),
-                                                   ctx->run_len.as<int32_t>());
-  ctx->launches += 2;
+  size_t tmp_bytes = 0;
+  Run* runs = nullptr;
+  if (nchan <= kFusedChan && !getenv("CIP_BIN_TWO_PASS")) {
+    // fused count + write: the run buffers are sized from a guess (what they already hold, or a mean run
+    // length of 4 channels) and the kernel drops writes past the capacity; a low guess costs one re-run
+    const int nch32 = (int)((nchan + 31) / 32) * 32;
+    const size_t smem = sizeof(uint64_t) * kFusedWarps * nch32;
+    CIP_CHECK_CUDA(cudaFuncSetAttribute(runs_fused_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem));
+    int64_t cap = std::max<int64_t>((int64_t)std::min(w.runs.cap / sizeof(Run), w.run_keys.cap / sizeof(uint64_t)),
+                                    nrec / 4 + 1024);
+    for (int attempt = 0;; ++attempt) {
+      CIP_TRY(w.runs.ensure(sizeof(Run) * cap));
+      CIP_TRY(w.run_keys.ensure(sizeof(uint64_t) * cap));
+      runs = w.runs.as<Run>();
+      CIP_CHECK_CUDA(cudaMemsetAsync(row_off + nrow, 0, sizeof(int64_t), st));
+      runs_fused_kernel<<<nblk(nrow, kFusedWarps), 32 * kFusedWarps, smem, st>>>(in, g, row_nruns, row_off, runs,
+                                                                                 w.run_keys.as<uint64_t>(), finv, nch32, cap);
+      ctx->launches++;
+      CIP_TRY(d2h_scalar(ctx, row_off + nrow, &nruns));
+      if (nruns <= cap) break;
+      CIP_REQUIRE(attempt == 0, "run count changed between two passes");
+      cap = nruns;
+    }
+    CIP_REQUIRE(nruns > 0 && nruns < ((int64_t)1 << 32), "unexpected number of runs %lld", (long long)nruns);
+  } else {
+    runs_kernel<0, float><<<rblocks, 256, 0, st>>>(in, g, row_nruns, nullptr, nullptr, nullptr, nullptr, (Rec<float>*)nullptr, finv);
+    ctx->launches++;
+    CIP_CHECK_CUDA(cub::DeviceScan::ExclusiveSum(nullptr, tmp_bytes, row_nruns, row_off, nrow + 1, st));
+    CIP_TRY(w.cub_tmp.ensure(tmp_bytes));
+    tmp_bytes = w.cub_tmp.cap;
+    CIP_CHECK_CUDA(cub::DeviceScan::ExclusiveSum(w.cub_tmp.p, tmp_bytes, row_nruns, row_off, nrow + 1, st));
+    ctx->launches++;
+    CIP_TRY(d2h_scalar(ctx, row_off + nrow, &nruns));
+    CIP_REQUIRE(nruns > 0 && nruns < ((int64_t)1 << 32), "unexpected number of runs %lld", (long long)nruns);
+    CIP_TRY(w.runs.ensure(sizeof(Run) * nruns));
+    CIP_TRY(w.run_keys.ensure(sizeof(uint64_t) * nruns));
+    runs = w.runs.as<Run>();
+    runs_kernel<1, float><<<rblocks, 256, 0, st>>>(in, g, nullptr, row_off, runs, w.run_keys.as<uint64_t>(), nullptr,
+                                                   (Rec<float>*)nullptr, finv);
+    ctx->launches++;
+  }
+  CIP_TRY(w.run_keys_alt.ensure(sizeof(uint64_t) * nruns));
+  CIP_TRY(w.run_idx.ensure(sizeof(uint32_t) * nruns));
+  CIP_TRY(w.run_idx_alt.ensure(sizeof(uint32_t) * nruns));
+  CIP_TRY(w.run_len.ensure(sizeof(int32_t) * nruns));
+  run_len_kernel<<<nblk(nruns, 256), 256, 0, st>>>(runs, nruns, (int32_t)nchan, w.run_idx.as<uint32_t>(),
+                                                   w.run_len.as<int32_t>());
+  ctx->launches++;
 
   // --- stable sort of the runs by key ----------------------------------------------
   uint64_t nkeys = (uint64_t)g.nwin * g.ntu * g.ntv;
@@ -267,75 +386,75 @@ cip_status run_binning(cip_ctx* ctx, const DevInputs& in, const GridGeom& g, int
   while (bits < 64 && (nkeys >> bits)) ++bits;
   bits += kSubKeyBits;
   CIP_REQUIRE(bits <= 64, "bin key too wide (%d bits)", bits);
-  CIP_CHECK_CUDA(cub::DeviceRadixSort::SortPairs(nullptr, tmp_bytes, ctx->run_keys.as<uint64_t>(),
-                                                 ctx->run_keys_alt.as<uint64_t>(), ctx->run_idx.as<uint32_t>(),
-                                                 ctx->run_idx_alt.as<uint32_t>(), nruns, 0, bits, st));
-  CIP_TRY(ctx->cub_tmp.ensure(tmp_bytes));
-  tmp_bytes = ctx->cub_tmp.cap;
-  CIP_CHECK_CUDA(cub::DeviceRadixSort::SortPairs(ctx->cub_tmp.p, tmp_bytes, ctx->run_keys.as<uint64_t>(),
-                                                 ctx->run_keys_alt.as<uint64_t>(), ctx->run_idx.as<uint32_t>(),
-                                                 ctx->run_idx_alt.as<uint32_t>(), nruns, 0, bits, st));
+  CIP_CHECK_CUDA(cub::DeviceRadixSort::SortPairs(nullptr, tmp_bytes, w.run_keys.as<uint64_t>(),
+                                                 w.run_keys_alt.as<uint64_t>(), w.run_idx.as<uint32_t>(),
+                                                 w.run_idx_alt.as<uint32_t>(), nruns, 0, bits, st));
+  CIP_TRY(w.cub_tmp.ensure(tmp_bytes));
+  tmp_bytes = w.cub_tmp.cap;
+  CIP_CHECK_CUDA(cub::DeviceRadixSort::SortPairs(w.cub_tmp.p, tmp_bytes, w.run_keys.as<uint64_t>(),
+                                                 w.run_keys_alt.as<uint64_t>(), w.run_idx.as<uint32_t>(),
+                                                 w.run_idx_alt.as<uint32_t>(), nruns, 0, bits, st));
   ctx->launches += 2 + (bits + 7) / 8;
 
   // --- sorted runs, record offsets, bins -------------------------------------------
-  CIP_TRY(ctx->runs_sorted.ensure(sizeof(Run) * nruns));
-  CIP_TRY(ctx->run_visoff.ensure(sizeof(int64_t) * (nruns + 1) * 2));  // lengths + offsets
-  CIP_TRY(ctx->flags.ensure(sizeof(int64_t) * nruns * 2));              // start flags + group index
-  Run* runs_sorted = ctx->runs_sorted.as<Run>();
-  int64_t* len_sorted = ctx->run_visoff.as<int64_t>();
+  CIP_TRY(w.runs_sorted.ensure(sizeof(Run) * nruns));
+  CIP_TRY(w.run_visoff.ensure(sizeof(int64_t) * (nruns + 1) * 2));  // lengths + offsets
+  CIP_TRY(w.flags.ensure(sizeof(int64_t) * nruns * 2));              // start flags + group index
+  Run* runs_sorted = w.runs_sorted.as<Run>();
+  int64_t* len_sorted = w.run_visoff.as<int64_t>();
   int64_t* visoff = len_sorted + (nruns + 1);
-  int64_t* start_flag = ctx->flags.as<int64_t>();
+  int64_t* start_flag = w.flags.as<int64_t>();
   int64_t* group_of = start_flag + nruns;
-  gather_kernel<<<nblk(nruns, 256), 256, 0, st>>>(runs, ctx->run_len.as<int32_t>(), ctx->run_idx_alt.as<uint32_t>(),
-                                                  ctx->run_keys_alt.as<uint64_t>(), nruns, runs_sorted, len_sorted,
+  gather_kernel<<<nblk(nruns, 256), 256, 0, st>>>(runs, w.run_len.as<int32_t>(), w.run_idx_alt.as<uint32_t>(),
+                                                  w.run_keys_alt.as<uint64_t>(), nruns, runs_sorted, len_sorted,
                                                   start_flag);
   ctx->launches++;
   CIP_CHECK_CUDA(cub::DeviceScan::ExclusiveSum(nullptr, tmp_bytes, len_sorted, visoff, nruns, st));
-  CIP_TRY(ctx->cub_tmp.ensure(tmp_bytes));
-  tmp_bytes = ctx->cub_tmp.cap;
-  CIP_CHECK_CUDA(cub::DeviceScan::ExclusiveSum(ctx->cub_tmp.p, tmp_bytes, len_sorted, visoff, nruns, st));
+  CIP_TRY(w.cub_tmp.ensure(tmp_bytes));
+  tmp_bytes = w.cub_tmp.cap;
+  CIP_CHECK_CUDA(cub::DeviceScan::ExclusiveSum(w.cub_tmp.p, tmp_bytes, len_sorted, visoff, nruns, st));
   CIP_CHECK_CUDA(cub::DeviceScan::InclusiveSum(nullptr, tmp_bytes, start_flag, group_of, nruns, st));
-  CIP_TRY(ctx->cub_tmp.ensure(tmp_bytes));
-  tmp_bytes = ctx->cub_tmp.cap;
-  CIP_CHECK_CUDA(cub::DeviceScan::InclusiveSum(ctx->cub_tmp.p, tmp_bytes, start_flag, group_of, nruns, st));
+  CIP_TRY(w.cub_tmp.ensure(tmp_bytes));
+  tmp_bytes = w.cub_tmp.cap;
+  CIP_CHECK_CUDA(cub::DeviceScan::InclusiveSum(w.cub_tmp.p, tmp_bytes, start_flag, group_of, nruns, st));
   ctx->launches += 2;
   int64_t ngroups = 0;
   CIP_TRY(d2h_scalar(ctx, group_of + nruns - 1, &ngroups));
 
-  CIP_TRY(ctx->group_start.ensure(sizeof(int64_t) * (ngroups + 1) * 3));
-  int64_t* group_first = ctx->group_start.as<int64_t>();
+  CIP_TRY(w.group_start.ensure(sizeof(int64_t) * (ngroups + 1) * 3));
+  int64_t* group_first = w.group_start.as<int64_t>();
   int64_t* group_nitems = group_first + (ngroups + 1);
   int64_t* group_item_off = group_nitems + (ngroups + 1);
-  CIP_TRY(ctx->item_idx.ensure(sizeof(int64_t) * nruns));
-  int64_t* outpos = ctx->item_idx.as<int64_t>();
-  groups_kernel<<<nblk(nruns, 256), 256, 0, st>>>(start_flag, group_of, visoff, ctx->run_idx_alt.as<uint32_t>(), nruns,
+  CIP_TRY(w.item_idx.ensure(sizeof(int64_t) * nruns));
+  int64_t* outpos = w.item_idx.as<int64_t>();
+  groups_kernel<<<nblk(nruns, 256), 256, 0, st>>>(start_flag, group_of, visoff, w.run_idx_alt.as<uint32_t>(), nruns,
                                                   nrec, group_first, outpos);
   group_items_kernel<<<nblk(ngroups + 1, 256), 256, 0, st>>>(group_first, visoff, ngroups, nruns, nrec, group_nitems);
   ctx->launches += 2;
   CIP_CHECK_CUDA(cub::DeviceScan::ExclusiveSum(nullptr, tmp_bytes, group_nitems, group_item_off, ngroups + 1, st));
-  CIP_TRY(ctx->cub_tmp.ensure(tmp_bytes));
-  tmp_bytes = ctx->cub_tmp.cap;
-  CIP_CHECK_CUDA(cub::DeviceScan::ExclusiveSum(ctx->cub_tmp.p, tmp_bytes, group_nitems, group_item_off, ngroups + 1, st));
+  CIP_TRY(w.cub_tmp.ensure(tmp_bytes));
+  tmp_bytes = w.cub_tmp.cap;
+  CIP_CHECK_CUDA(cub::DeviceScan::ExclusiveSum(w.cub_tmp.p, tmp_bytes, group_nitems, group_item_off, ngroups + 1, st));
   ctx->launches++;
   int64_t nitems = 0;
   CIP_TRY(d2h_scalar(ctx, group_item_off + ngroups, &nitems));
 
-  CIP_TRY(ctx->items.ensure(sizeof(Item) * std::max<int64_t>(nitems, 1)));
-  CIP_TRY(ctx->win_item_start.ensure(sizeof(int64_t) * (g.nwin + 1)));
-  int64_t* wis = ctx->win_item_start.as<int64_t>();
+  CIP_TRY(w.items.ensure(sizeof(Item) * std::max<int64_t>(nitems, 1)));
+  CIP_TRY(w.win_item_start.ensure(sizeof(int64_t) * (g.nwin + 1)));
+  int64_t* wis = w.win_item_start.as<int64_t>();
   fill_i64_kernel<<<nblk(g.nwin + 1, 256), 256, 0, st>>>(wis, g.nwin + 1, nitems);
   items_kernel<<<nblk(ngroups, 256), 256, 0, st>>>(group_first, group_item_off, visoff, runs_sorted, ngroups, nrec, g,
-                                                   ctx->items.as<Item>(), wis);
+                                                   w.items.as<Item>(), wis);
   ctx->launches += 2;
 
   // --- records ---------------------------------------------------------------------
-  CIP_TRY(ctx->recs.ensure(recs_bytes(nrec)));
+  CIP_TRY(w.recs.ensure(recs_bytes(nrec)));
   if (fp64)
-    runs_kernel<2, double><<<rblocks, 256, 0, st>>>(in, g, nullptr, row_off, nullptr, nullptr, outpos,
-                                                    ctx->recs.as<Rec<double>>(), finv);
+    runs_kernel<2, double><<<rblocks, 256, 0, st>>>(in, g, row_nruns, row_off, nullptr, nullptr, outpos,
+                                                    w.recs.as<Rec<double>>(), finv);
   else
-    runs_kernel<2, float><<<rblocks, 256, 0, st>>>(in, g, nullptr, row_off, nullptr, nullptr, outpos,
-                                                   ctx->recs.as<Rec<float>>(), finv);
+    runs_kernel<2, float><<<rblocks, 256, 0, st>>>(in, g, row_nruns, row_off, nullptr, nullptr, outpos,
+                                                   w.recs.as<Rec<float>>(), finv);
   ctx->launches++;
   CIP_CHECK_CUDA(cudaGetLastError());
 

@@ -74,6 +74,18 @@ struct DevBuf {
   template <typename T> T* as() const { return static_cast<T*>(p); }
 };
 
+// Workspaces of one binning pass (and the records / work items the gridder reads from it).
+struct BinWork {
+  DevBuf row_nruns, row_off, runs, run_keys, run_keys_alt, run_idx, run_idx_alt, runs_sorted, run_len, run_visoff,
+      flags, group_start, item_idx, items, win_item_start, cub_tmp, recs, finv;
+  void release() {
+    for (DevBuf* b : {&row_nruns, &row_off, &runs, &run_keys, &run_keys_alt, &run_idx, &run_idx_alt, &runs_sorted,
+                      &run_len, &run_visoff, &flags, &group_start, &item_idx, &items, &win_item_start, &cub_tmp, &recs,
+                      &finv})
+      b->release();
+  }
+};
+
 struct FftPlan {
   cufftHandle handle = 0;
   size_t work = 0;
@@ -163,9 +175,12 @@ struct cip_ctx {
   cip::DevBuf scan_out;
   void* scan_host = nullptr;      // pinned + mapped (kSmallHostBytes): small results land here without a copy engine
   void* scan_host_dev = nullptr;  // its device-side address
-  // binning
-  cip::DevBuf row_nruns, row_off, runs, run_keys, run_keys_alt, run_idx, run_idx_alt, runs_sorted, run_len,
-      run_visoff, flags, group_start, item_idx, items, win_item_start, cub_tmp, recs, finv;
+  // binning workspaces: two sets, so that chunk c+1 is binned (context stream) while chunk c is gridded
+  // (grid stream)
+  cip::BinWork work[2];
+  cudaStream_t grid_stream = nullptr;
+  cudaEvent_t binned_ev[2] = {}, gridded_ev[2] = {}, zero_ev = nullptr;  // non-timing
+  cudaEvent_t chunk_t[cip::kMaxChunks][4] = {};                          // timing: bin begin/end, grid begin/end
   // grids, fft, image
   cip::DevBuf grid, image, tables;
   std::vector<double> tables_key;  // plan parameters the correction tables were built for
@@ -227,11 +242,12 @@ struct BinResult {
   int64_t nitems = 0;
   std::vector<int64_t> win_item_start;  // (nwin+1,) first item of each window
 };
-cip_status run_binning(cip_ctx* ctx, const DevInputs& in, const GridGeom& g, int fp64, BinResult* out);
+cip_status run_binning(cip_ctx* ctx, int slot, const DevInputs& in, const GridGeom& g, int fp64, BinResult* out);
 
-// Grid the items [item_begin, item_end) into `grid` (planes slot = plane - plane_base).
-cip_status run_gridder(cip_ctx* ctx, const GridGeom& g, int fp64, int64_t nrec_total, int64_t item_begin,
-                       int64_t item_end, void* grid, int plane_base, int nslots);
+// Grid the items [item_begin, item_end) of binning workspace `slot` into `grid` (planes slot = plane -
+// plane_base), on `stream`.
+cip_status run_gridder(cip_ctx* ctx, int slot, cudaStream_t stream, const GridGeom& g, int fp64, int64_t nrec_total,
+                       int64_t item_begin, int64_t item_end, void* grid, int plane_base, int nslots);
 cip_status run_fft(cip_ctx* ctx, void* grid, int nu, int nv, int batch, int fp64);
 cip_status run_wscreen(cip_ctx* ctx, const cip_plan& p, const void* grid, int plane_base, int nslots, void* image);
 cip_status run_correct(cip_ctx* ctx, const cip_plan& p, void* image, int row_begin, int row_end, double scale);

@@ -116,10 +116,19 @@ cip_status stage_inputs(cip_ctx* ctx, const cip_invert_args* a, DevInputs* d, Vi
     d->vstride = vs;
     d->wstride = ws;
     if (feed) {
-      feed->nchunks = 1;
-      feed->row0[0] = 0;
-      feed->row0[1] = nrow;
-      feed->ready[0] = nullptr;  // nothing to wait for
+      // Device inputs are all there; they are still cut into row chunks so that the binning of chunk c+1
+      // (context stream, bound by memory latency) overlaps the gridding of chunk c (grid stream, bound by
+      // the FMA and shared-memory pipes).  More chunks hide more of the binning but multiply the work
+      // items (one sub-grid flush each).
+      const size_t vis_bytes = (size_t)nrow * nchan * sizeof(float2);
+      int nchunks = 1;  // measured on B200 (configs[1]): 1 chunk 22.8 ms, 2 chunks 23.5 ms, 3 chunks 24.2 ms -- next
+                        // to the gridder's CTAs the binning kernels get half their occupancy, so the default stays 1
+      (void)vis_bytes;
+      if (const char* e = getenv("CIP_DEVICE_CHUNKS")) nchunks = std::min(kMaxChunks, std::max(1, atoi(e)));
+      nchunks = (int)std::min<int64_t>(nchunks, std::max<int64_t>(nrow, 1));
+      feed->nchunks = nchunks;
+      for (int c = 0; c <= nchunks; ++c) feed->row0[c] = nrow * c / nchunks;
+      for (int c = 0; c < nchunks; ++c) feed->ready[c] = nullptr;  // nothing to wait for
     }
     return CIP_OK;
   }
@@ -228,6 +237,18 @@ extern "C" cip_status cip_ctx_create(int device, cip_ctx** out) {
   ctx->smem_optin = prop.sharedMemPerBlockOptin;
   CIP_CHECK_CUDA(cudaStreamCreateWithFlags(&ctx->stream, cudaStreamNonBlocking));
   CIP_CHECK_CUDA(cudaStreamCreateWithFlags(&ctx->copy_stream, cudaStreamNonBlocking));
+  {
+    int lo = 0, hi = 0;  // the gridder yields to the (short, latency-bound) binning kernels of the next chunk
+    CIP_CHECK_CUDA(cudaDeviceGetStreamPriorityRange(&lo, &hi));
+    CIP_CHECK_CUDA(cudaStreamCreateWithPriority(&ctx->grid_stream, cudaStreamNonBlocking, getenv("CIP_NO_PRIO") ? 0 : lo));
+  }
+  for (int s = 0; s < 2; ++s) {
+    CIP_CHECK_CUDA(cudaEventCreateWithFlags(&ctx->binned_ev[s], cudaEventDisableTiming));
+    CIP_CHECK_CUDA(cudaEventCreateWithFlags(&ctx->gridded_ev[s], cudaEventDisableTiming));
+  }
+  CIP_CHECK_CUDA(cudaEventCreateWithFlags(&ctx->zero_ev, cudaEventDisableTiming));
+  for (auto& row : ctx->chunk_t)
+    for (auto& ev : row) CIP_CHECK_CUDA(cudaEventCreate(&ev));
   for (auto& ev : ctx->ev) CIP_CHECK_CUDA(cudaEventCreate(&ev));
   for (auto& ev : ctx->chunk_ev) CIP_CHECK_CUDA(cudaEventCreateWithFlags(&ev, cudaEventDisableTiming));
   CIP_CHECK_CUDA(cudaEventCreateWithFlags(&ctx->sync_ev, cudaEventDisableTiming));
@@ -243,19 +264,26 @@ extern "C" cip_status cip_ctx_destroy(cip_ctx* ctx) {
   cudaSetDevice(ctx->device);
   if (ctx->copy_stream) cudaStreamSynchronize(ctx->copy_stream);
   if (ctx->stream) cudaStreamSynchronize(ctx->stream);
+  if (ctx->grid_stream) cudaStreamSynchronize(ctx->grid_stream);
   for (auto& kv : ctx->fft_plans) cufftDestroy(kv.second.handle);
   DevBuf* bufs[] = {&ctx->in_uvw, &ctx->in_freq, &ctx->in_vis, &ctx->in_wgt, &ctx->in_mask, &ctx->out_img,
-                    &ctx->scan_out, &ctx->row_nruns, &ctx->row_off, &ctx->runs, &ctx->run_keys,
-                    &ctx->run_keys_alt, &ctx->run_idx, &ctx->run_idx_alt, &ctx->runs_sorted, &ctx->run_len,
-                    &ctx->run_visoff, &ctx->flags, &ctx->group_start, &ctx->item_idx, &ctx->items,
-                    &ctx->win_item_start, &ctx->cub_tmp, &ctx->recs, &ctx->finv, &ctx->grid, &ctx->image, &ctx->tables,
-                    &ctx->t_uvw, &ctx->t_freq, &ctx->t_vis};
+                    &ctx->scan_out, &ctx->grid, &ctx->image, &ctx->tables, &ctx->t_uvw, &ctx->t_freq, &ctx->t_vis};
+  for (auto& w : ctx->work) w.release();
   for (DevBuf* b : bufs) b->release();
   if (ctx->scan_host) cudaFreeHost(ctx->scan_host);
   for (auto& ev : ctx->ev)
     if (ev) cudaEventDestroy(ev);
   for (auto& ev : ctx->chunk_ev)
     if (ev) cudaEventDestroy(ev);
+  for (int s = 0; s < 2; ++s) {
+    if (ctx->binned_ev[s]) cudaEventDestroy(ctx->binned_ev[s]);
+    if (ctx->gridded_ev[s]) cudaEventDestroy(ctx->gridded_ev[s]);
+  }
+  if (ctx->zero_ev) cudaEventDestroy(ctx->zero_ev);
+  for (auto& row : ctx->chunk_t)
+    for (auto& ev : row)
+      if (ev) cudaEventDestroy(ev);
+  if (ctx->grid_stream) cudaStreamDestroy(ctx->grid_stream);
   if (ctx->small_ev) cudaEventDestroy(ctx->small_ev);
   if (ctx->sync_ev) cudaEventDestroy(ctx->sync_ev);
   if (ctx->copy_stream) cudaStreamDestroy(ctx->copy_stream);

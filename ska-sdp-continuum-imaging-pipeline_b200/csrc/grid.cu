@@ -862,21 +862,21 @@ __global__ void __launch_bounds__(128) grid_wide_kernel(const Item* __restrict__
 }
 
 template <int NW>
-cip_status launch_warp(cip_ctx* ctx, const Item* items, int64_t item_begin, int64_t n, const Rec<float>* recs,
+cip_status launch_warp(cip_ctx* ctx, cudaStream_t stream, const Item* items, int64_t item_begin, int64_t n, const Rec<float>* recs,
                        const GridGeom& g, float* grid, int plane_base, int nslots) {
   auto kern = grid_warp_kernel<NW>;
   constexpr int smem = warp_smem_bytes(NW);
   CIP_CHECK_CUDA(cudaFuncSetAttribute(kern, cudaFuncAttributeMaxDynamicSharedMemorySize, smem));
   CIP_CHECK_CUDA(cudaFuncSetAttribute(kern, cudaFuncAttributePreferredSharedMemoryCarveout, (int)cudaSharedmemCarveoutMaxShared));
-  kern<<<(unsigned)n, 32 * NW, smem, ctx->stream>>>(items, item_begin, recs, g, grid, plane_base, nslots);
+  kern<<<(unsigned)n, 32 * NW, smem, stream>>>(items, item_begin, recs, g, grid, plane_base, nslots);
   return CIP_OK;
 }
 
 template <typename R>
-cip_status launch(cip_ctx* ctx, const GridGeom& g, int64_t nrec_total, int64_t item_begin, int64_t item_end,
-                  void* grid, int plane_base, int nslots) {
-  const Item* items = ctx->items.as<Item>();
-  const Rec<R>* recs = ctx->recs.as<Rec<R>>();
+cip_status launch(cip_ctx* ctx, int slot, cudaStream_t stream, const GridGeom& g, int64_t nrec_total, int64_t item_begin,
+                  int64_t item_end, void* grid, int plane_base, int nslots) {
+  const Item* items = ctx->work[slot].items.as<Item>();
+  const Rec<R>* recs = ctx->work[slot].recs.as<Rec<R>>();
   (void)nrec_total;
   const int64_t n = item_end - item_begin;
   if (n <= 0) return CIP_OK;
@@ -885,7 +885,7 @@ cip_status launch(cip_ctx* ctx, const GridGeom& g, int64_t nrec_total, int64_t i
     static const int nw = getenv("CIP_GRID_WARPS") ? atoi(getenv("CIP_GRID_WARPS")) : 1;
     CIP_TRY((nw == 1 ? launch_warp<1> : nw == 2 ? launch_warp<2> : nw == 3 ? launch_warp<3> : nw == 5 ? launch_warp<5>
                                                                                                 : launch_warp<4>)(
-        ctx, items, item_begin, n, reinterpret_cast<const Rec<float>*>(recs), g, reinterpret_cast<float*>(grid), plane_base,
+        ctx, stream, items, item_begin, n, reinterpret_cast<const Rec<float>*>(recs), g, reinterpret_cast<float*>(grid), plane_base,
         nslots));
   } else if (g.W <= kFastSupport) {
     constexpr size_t smem = grid_smem_bytes<R>();
@@ -893,10 +893,10 @@ cip_status launch(cip_ctx* ctx, const GridGeom& g, int64_t nrec_total, int64_t i
     CIP_CHECK_CUDA(cudaFuncSetAttribute(kern, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem));
     CIP_CHECK_CUDA(cudaFuncSetAttribute(kern, cudaFuncAttributePreferredSharedMemoryCarveout,
                                         (int)cudaSharedmemCarveoutMaxShared));
-    kern<<<(unsigned)n, kGridThreads, smem, ctx->stream>>>(items, item_begin, recs, g, static_cast<R*>(grid), plane_base,
+    kern<<<(unsigned)n, kGridThreads, smem, stream>>>(items, item_begin, recs, g, static_cast<R*>(grid), plane_base,
                                                           nslots);
   } else {
-    grid_wide_kernel<R><<<(unsigned)n, 128, 0, ctx->stream>>>(items, item_begin, recs, g, static_cast<R*>(grid),
+    grid_wide_kernel<R><<<(unsigned)n, 128, 0, stream>>>(items, item_begin, recs, g, static_cast<R*>(grid),
                                                               plane_base, nslots);
   }
   ctx->launches++;
@@ -906,10 +906,10 @@ cip_status launch(cip_ctx* ctx, const GridGeom& g, int64_t nrec_total, int64_t i
 
 }  // namespace
 
-cip_status run_gridder(cip_ctx* ctx, const GridGeom& g, int fp64, int64_t nrec_total, int64_t item_begin,
-                       int64_t item_end, void* grid, int plane_base, int nslots) {
-  if (fp64) return launch<double>(ctx, g, nrec_total, item_begin, item_end, grid, plane_base, nslots);
-  return launch<float>(ctx, g, nrec_total, item_begin, item_end, grid, plane_base, nslots);
+cip_status run_gridder(cip_ctx* ctx, int slot, cudaStream_t stream, const GridGeom& g, int fp64, int64_t nrec_total,
+                       int64_t item_begin, int64_t item_end, void* grid, int plane_base, int nslots) {
+  if (fp64) return launch<double>(ctx, slot, stream, g, nrec_total, item_begin, item_end, grid, plane_base, nslots);
+  return launch<float>(ctx, slot, stream, g, nrec_total, item_begin, item_end, grid, plane_base, nslots);
 }
 
 }  // namespace cip

@@ -4,6 +4,7 @@
 #include <algorithm>
 #include <cstdlib>
 #include <cstring>
+#include <vector>
 
 #include "common.h"
 
@@ -102,7 +103,7 @@ static cip_status grid_accumulate_staged(cip_ctx* ctx, const DevInputs& in, cons
     // not allocated yet
     size_t reserve = (size_t)768 << 20;
     const size_t nvis = (size_t)in.nrow * in.nchan;
-    if (ctx->recs.cap < recs_bytes(nvis) / std::max(feed.nchunks, 1)) reserve += 48 * nvis;
+    if (ctx->work[0].recs.cap < recs_bytes(nvis) / std::max(feed.nchunks, 1)) reserve += 48 * nvis;
     size_t avail = free_b + ctx->grid.cap;
     avail = avail > reserve ? avail - reserve : 0;
     max_slots = (int64_t)(avail / plane_bytes);
@@ -128,9 +129,19 @@ static cip_status grid_accumulate_staged(cip_ctx* ctx, const DevInputs& in, cons
     tm.start();
     CIP_CHECK_CUDA(cudaMemsetAsync(ctx->grid.p, 0, plane_bytes * plan->nplanes, ctx->stream));
     tm.stop(rep ? &rep->ms_zero : &dummy);
-    bool any = false;
+    // Chunk c is binned on the context stream into workspace c & 1 and gridded on the grid stream, so that
+    // the binning of chunk c+1 overlaps the gridding of chunk c.  Device inputs are timed with event pairs
+    // that nobody waits for until the end; host inputs (timed with the host clock, see StageTimer) give up
+    // the overlap when a report is requested.
+    const bool dev_timing = rep && !tm.host;
+    cudaStream_t gs = ctx->grid_stream;
+    CIP_CHECK_CUDA(cudaEventRecord(ctx->zero_ev, ctx->stream));
+    CIP_CHECK_CUDA(cudaStreamWaitEvent(gs, ctx->zero_ev, 0));
+    bool any = false, used[2] = {false, false};
+    std::vector<int> timed_bin, timed_grid;
     for (int c = 0; c < feed.nchunks; ++c) {
       if (feed.row0[c + 1] <= feed.row0[c]) continue;
+      const int slot = c & 1;
       if (feed.ready[c]) {
         if (rep) {  // timed call: the host waits for the chunk so that the stage times exclude the upload
           CIP_CHECK_CUDA(cudaEventSynchronize(feed.ready[c]));
@@ -139,18 +150,51 @@ static cip_status grid_accumulate_staged(cip_ctx* ctx, const DevInputs& in, cons
           CIP_CHECK_CUDA(cudaStreamWaitEvent(ctx->stream, feed.ready[c], 0));
         }
       }
+      if (used[slot]) CIP_CHECK_CUDA(cudaStreamWaitEvent(ctx->stream, ctx->gridded_ev[slot], 0));  // workspace in use
       const DevInputs chunk = row_slice(in, feed.row0[c], feed.row0[c + 1]);
-      tm.start();
+      if (dev_timing) CIP_CHECK_CUDA(cudaEventRecord(ctx->chunk_t[c][0], ctx->stream));
+      else tm.start();
       BinResult bins;
-      CIP_TRY(run_binning(ctx, chunk, g, fp64, &bins));
-      tm.stop(rep ? &rep->ms_bin : &dummy);
+      CIP_TRY(run_binning(ctx, slot, chunk, g, fp64, &bins));
+      if (dev_timing) {
+        CIP_CHECK_CUDA(cudaEventRecord(ctx->chunk_t[c][1], ctx->stream));
+        timed_bin.push_back(c);
+      } else {
+        tm.stop(rep ? &rep->ms_bin : &dummy);
+      }
       trace_mark("  chunk binned");
       if (bins.nitems == 0) continue;
       any = true;
-      tm.start();
-      CIP_TRY(run_gridder(ctx, g, fp64, bins.nrec, 0, bins.nitems, ctx->grid.p, 0, plan->nplanes));
-      tm.stop(rep ? &rep->ms_grid : &dummy);
+      CIP_CHECK_CUDA(cudaEventRecord(ctx->binned_ev[slot], ctx->stream));
+      CIP_CHECK_CUDA(cudaStreamWaitEvent(gs, ctx->binned_ev[slot], 0));
+      const double t0 = now_ms();
+      if (dev_timing) CIP_CHECK_CUDA(cudaEventRecord(ctx->chunk_t[c][2], gs));
+      CIP_TRY(run_gridder(ctx, slot, gs, g, fp64, bins.nrec, 0, bins.nitems, ctx->grid.p, 0, plan->nplanes));
+      if (dev_timing) {
+        CIP_CHECK_CUDA(cudaEventRecord(ctx->chunk_t[c][3], gs));
+        timed_grid.push_back(c);
+      }
+      CIP_CHECK_CUDA(cudaEventRecord(ctx->gridded_ev[slot], gs));
+      used[slot] = true;
+      if (rep && !dev_timing) {
+        CIP_CHECK_CUDA(cudaEventSynchronize(ctx->gridded_ev[slot]));
+        rep->ms_grid += now_ms() - t0;
+      }
       trace_mark("  chunk gridded");
+    }
+    for (int slot = 0; slot < 2; ++slot)
+      if (used[slot]) CIP_CHECK_CUDA(cudaStreamWaitEvent(ctx->stream, ctx->gridded_ev[slot], 0));
+    if (dev_timing) {
+      CIP_CHECK_CUDA(cudaStreamSynchronize(ctx->stream));
+      float ms = 0;
+      for (int c : timed_bin) {
+        CIP_CHECK_CUDA(cudaEventElapsedTime(&ms, ctx->chunk_t[c][0], ctx->chunk_t[c][1]));
+        rep->ms_bin += ms;
+      }
+      for (int c : timed_grid) {
+        CIP_CHECK_CUDA(cudaEventElapsedTime(&ms, ctx->chunk_t[c][2], ctx->chunk_t[c][3]));
+        rep->ms_grid += ms;
+      }
     }
     if (rep) rep->nblocks = feed.nchunks;
     if (!any) return CIP_OK;
@@ -167,7 +211,7 @@ static cip_status grid_accumulate_staged(cip_ctx* ctx, const DevInputs& in, cons
   CIP_TRY(wait_feed(ctx, feed));
   tm.start();
   BinResult bins;
-  CIP_TRY(run_binning(ctx, in, g, fp64, &bins));
+  CIP_TRY(run_binning(ctx, 0, in, g, fp64, &bins));
   tm.stop(rep ? &rep->ms_bin : &dummy);
   if (bins.nitems == 0) return CIP_OK;
 
@@ -180,7 +224,7 @@ static cip_status grid_accumulate_staged(cip_ctx* ctx, const DevInputs& in, cons
       CIP_CHECK_CUDA(cudaMemsetAsync(ctx->grid.p, 0, plane_bytes * used, ctx->stream));
       tm.stop(rep ? &rep->ms_zero : &dummy);
       tm.start();
-      CIP_TRY(run_gridder(ctx, g, fp64, bins.nrec, 0, bins.nitems, ctx->grid.p, pb, used));
+      CIP_TRY(run_gridder(ctx, 0, ctx->stream, g, fp64, bins.nrec, 0, bins.nitems, ctx->grid.p, pb, used));
       tm.stop(rep ? &rep->ms_grid : &dummy);
       tm.start();
       CIP_TRY(run_fft(ctx, ctx->grid.p, plan->nu, plan->nv, used, fp64));
@@ -211,7 +255,7 @@ static cip_status grid_accumulate_staged(cip_ctx* ctx, const DevInputs& in, cons
       CIP_CHECK_CUDA(cudaMemsetAsync(ctx->grid.p, 0, plane_bytes * used, ctx->stream));
       tm.stop(rep ? &rep->ms_zero : &dummy);
       tm.start();
-      CIP_TRY(run_gridder(ctx, g, fp64, bins.nrec, it0, it1, ctx->grid.p, pb, used));
+      CIP_TRY(run_gridder(ctx, 0, ctx->stream, g, fp64, bins.nrec, it0, it1, ctx->grid.p, pb, used));
       tm.stop(rep ? &rep->ms_grid : &dummy);
       tm.start();
       CIP_TRY(run_fft(ctx, ctx->grid.p, plan->nu, plan->nv, used, fp64));
