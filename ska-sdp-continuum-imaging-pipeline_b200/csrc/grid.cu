@@ -541,7 +541,7 @@ constexpr int kARow = 64 * 4 + 16;  // bytes per visibility of the A stage; the 
 constexpr int kBRow = 16 * 4 + 16;  // 128-bit stores (one row per lane) bank-conflict free
 constexpr int kWarpSubGridBytes = 16 * 4 * kSub * kSub;
 constexpr int kWarpStageBytes = kBatch * (kARow + kBRow + 4);
-constexpr int warp_smem_bytes(int nw) { return kWarpSubGridBytes + nw * kWarpStageBytes; }
+constexpr int warp_smem_bytes(int nw, bool direct) { return (direct ? 0 : kWarpSubGridBytes) + nw * kWarpStageBytes; }
 
 template <int OFF>
 __device__ __forceinline__ float4 lds_f4(uint32_t addr) {
@@ -595,6 +595,17 @@ __device__ __forceinline__ u64 lds_u1(uint32_t addr) {
 // half-warp only when the lanes (2i, 2i+1) read the same 16 bytes (else one per quarter-warp), a 64-bit
 // load is one wavefront per warp when its distinct words are conflict-free.  With lane = 4a + pq the two
 // A loads cost 2 wavefronts each and the two B loads 1 each: 6 per visibility.
+// Where a register window is folded to (see WarpAcc::fold).
+struct FoldSink {
+  float4* sg;                                              // sub-grid in shared memory (modes 0, 1)
+  float* grid;                                             // global plane stack (mode 2)
+  int nu, nv, su0, sv0, P0, nplanes, plane_base, nslots;   // su0, sv0 already reduced to [0, nu), [0, nv)
+};
+__device__ __forceinline__ void red_add_v2(float* addr, u64 v) {
+  const float2 f = unpack2(v);
+  asm volatile("red.global.add.v2.f32 [%0], {%1, %2};" ::"l"(addr), "f"(f.x), "f"(f.y) : "memory");
+}
+
 struct WarpOps {
   float4 a0, a1;
   u64 b0, b1;
@@ -626,22 +637,41 @@ struct WarpAcc {
   }
   // sub-grid cell = float4 {re(2pp), im(2pp), re(2pp+1), im(2pp+1)} for plane pair pp = pq: one float4
   // read-modify-write per owned cell (the lane owns row i, all 8 v residues of the window)
-  template <bool ATOMIC>
-  __device__ __forceinline__ void fold(float4* sg, int i, int wj, int pq) {
-    float4* row = sg + (pq * kSub + i) * kSub;
+  // MODE 0: plain read-modify-write of the CTA's sub-grid; 1: shared-memory reductions (several warps fold into
+  // one sub-grid); 2: no sub-grid, the window goes straight to the global plane stack with 8-byte reductions.
+  template <int MODE>
+  __device__ __forceinline__ void fold(const FoldSink& k, int i, int wj, int pq) {
+    if (MODE == 2) {
+      int gi = k.su0 + i;
+      gi -= gi >= k.nu ? k.nu : 0;
+      const int plane = k.P0 + 2 * pq, slot = plane - k.plane_base;
+      const bool ok0 = plane < k.nplanes && slot >= 0 && slot < k.nslots;
+      const bool ok1 = plane + 1 < k.nplanes && slot + 1 >= 0 && slot + 1 < k.nslots;
+      float* row0 = k.grid + 2 * (((int64_t)slot * k.nu + gi) * k.nv);
+      float* row1 = row0 + 2 * (int64_t)k.nu * k.nv;
 #pragma unroll
-    for (int t = 0; t < 8; ++t) {
-      float4* p = row + wj + ((t - wj) & 7);
-      const float2 x = unpack2(c[t][0]), y = unpack2(c[t][1]);
-      if (ATOMIC) {  // other warps of the CTA fold into the same sub-grid
-        const uint32_t ad = smem_u32(p);
-        asm volatile("red.shared.add.f32 [%0], %1;\n\tred.shared.add.f32 [%0+4], %2;\n\t"
-                     "red.shared.add.f32 [%0+8], %3;\n\tred.shared.add.f32 [%0+12], %4;"
-                     ::"r"(ad), "f"(x.x), "f"(x.y), "f"(y.x), "f"(y.y) : "memory");
-      } else {
-        float4 v = *p;
-        v.x += x.x; v.y += x.y; v.z += y.x; v.w += y.y;
-        *p = v;
+      for (int t = 0; t < 8; ++t) {
+        int gj = k.sv0 + wj + ((t - wj) & 7);
+        gj -= gj >= k.nv ? k.nv : 0;
+        if (ok0 && c[t][0] != 0ull) red_add_v2(row0 + 2 * gj, c[t][0]);
+        if (ok1 && c[t][1] != 0ull) red_add_v2(row1 + 2 * gj, c[t][1]);
+      }
+    } else {
+      float4* row = k.sg + (pq * kSub + i) * kSub;
+#pragma unroll
+      for (int t = 0; t < 8; ++t) {
+        float4* p = row + wj + ((t - wj) & 7);
+        const float2 x = unpack2(c[t][0]), y = unpack2(c[t][1]);
+        if (MODE == 1) {
+          const uint32_t ad = smem_u32(p);
+          asm volatile("red.shared.add.f32 [%0], %1;\n\tred.shared.add.f32 [%0+4], %2;\n\t"
+                       "red.shared.add.f32 [%0+8], %3;\n\tred.shared.add.f32 [%0+12], %4;"
+                       ::"r"(ad), "f"(x.x), "f"(x.y), "f"(y.x), "f"(y.y) : "memory");
+        } else {
+          float4 v = *p;
+          v.x += x.x; v.y += x.y; v.z += y.x; v.w += y.y;
+          *p = v;
+        }
       }
     }
     clear();
@@ -657,41 +687,46 @@ struct WarpCells {
   }
 };
 
-template <int U, bool CHECK, bool ATOMIC>
+template <int U, bool CHECK, int MODE>
 __device__ __forceinline__ void warp_consume1(uint32_t pa, uint32_t pb, uint32_t porg, uint32_t moved8, const WarpOps& cur,
-                                              WarpOps& nxt, WarpAcc& acc, float4* sg, WarpCells& cells, int a, int pq) {
+                                              WarpOps& nxt, WarpAcc& acc, const FoldSink& sg, WarpCells& cells, int a, int pq) {
   nxt = warp_load<U + 1>(pa, pb);
   if (CHECK && ((moved8 >> U) & 1u)) {
-    acc.template fold<ATOMIC>(sg, cells.i, cells.wj, pq);
+    acc.template fold<MODE>(sg, cells.i, cells.wj, pq);
     cells.set(lds_u32(porg + 4 * U), a);
   }
   acc.update(cur);
 }
-template <bool CHECK, bool ATOMIC>
+template <bool CHECK, int MODE>
 __device__ __forceinline__ void warp_consume8(uint32_t pa, uint32_t pb, uint32_t porg, uint32_t moved8, WarpOps& x, WarpAcc& acc,
-                                              float4* sg, WarpCells& cells, int a, int pq) {
+                                              const FoldSink& sg, WarpCells& cells, int a, int pq) {
   WarpOps y;
-  warp_consume1<0, CHECK, ATOMIC>(pa, pb, porg, moved8, x, y, acc, sg, cells, a, pq);
-  warp_consume1<1, CHECK, ATOMIC>(pa, pb, porg, moved8, y, x, acc, sg, cells, a, pq);
-  warp_consume1<2, CHECK, ATOMIC>(pa, pb, porg, moved8, x, y, acc, sg, cells, a, pq);
-  warp_consume1<3, CHECK, ATOMIC>(pa, pb, porg, moved8, y, x, acc, sg, cells, a, pq);
-  warp_consume1<4, CHECK, ATOMIC>(pa, pb, porg, moved8, x, y, acc, sg, cells, a, pq);
-  warp_consume1<5, CHECK, ATOMIC>(pa, pb, porg, moved8, y, x, acc, sg, cells, a, pq);
-  warp_consume1<6, CHECK, ATOMIC>(pa, pb, porg, moved8, x, y, acc, sg, cells, a, pq);
-  warp_consume1<7, CHECK, ATOMIC>(pa, pb, porg, moved8, y, x, acc, sg, cells, a, pq);
+  warp_consume1<0, CHECK, MODE>(pa, pb, porg, moved8, x, y, acc, sg, cells, a, pq);
+  warp_consume1<1, CHECK, MODE>(pa, pb, porg, moved8, y, x, acc, sg, cells, a, pq);
+  warp_consume1<2, CHECK, MODE>(pa, pb, porg, moved8, x, y, acc, sg, cells, a, pq);
+  warp_consume1<3, CHECK, MODE>(pa, pb, porg, moved8, y, x, acc, sg, cells, a, pq);
+  warp_consume1<4, CHECK, MODE>(pa, pb, porg, moved8, x, y, acc, sg, cells, a, pq);
+  warp_consume1<5, CHECK, MODE>(pa, pb, porg, moved8, y, x, acc, sg, cells, a, pq);
+  warp_consume1<6, CHECK, MODE>(pa, pb, porg, moved8, x, y, acc, sg, cells, a, pq);
+  warp_consume1<7, CHECK, MODE>(pa, pb, porg, moved8, y, x, acc, sg, cells, a, pq);
 }
 
 // NW warps per CTA share the item and its sub-grid: warp w takes the w-th contiguous share of the
 // batches (the records are sorted by register window, so each warp sees only a few windows) and has a
 // private operand stage; folds into the shared sub-grid are shared-memory reductions when NW > 1.
-template <int NW>
+// DIRECT: no sub-grid at all -- every register window is added to the global plane stack when the warp
+// leaves it (the records are sorted by window, so that happens ~ once per lattice position and item).  This
+// trades ~4x more L2 reductions for 14.4 KB of shared memory per warp, i.e. twice the resident warps.
+template <int NW, bool DIRECT>
 __global__ void __launch_bounds__(32 * NW) grid_warp_kernel(const Item* __restrict__ items, int64_t item_base,
                                                             const Rec<float>* __restrict__ recs, GridGeom g,
                                                             float* __restrict__ grid, int plane_base, int nslots) {
+  constexpr int MODE = DIRECT ? 2 : (NW > 1 ? 1 : 0);
+  constexpr int kSubBytes = DIRECT ? 0 : kWarpSubGridBytes;
   extern __shared__ __align__(16) unsigned char smem_raw[];
   float4* sg = reinterpret_cast<float4*>(smem_raw);
   const int lane = threadIdx.x & 31, warp = threadIdx.x >> 5;
-  const uint32_t sA = smem_u32(smem_raw + kWarpSubGridBytes + warp * kWarpStageBytes);
+  const uint32_t sA = smem_u32(smem_raw + kSubBytes + warp * kWarpStageBytes);
   const uint32_t sB = sA + kBatch * kARow;
   const uint32_t sOrg = sB + kBatch * kBRow;
 
@@ -703,7 +738,16 @@ __global__ void __launch_bounds__(32 * NW) grid_warp_kernel(const Item* __restri
 
   bool cur_valid = b_begin * kBatch + lane < nrec;
   Rec<float> cur = load_rec(recs, base + b_begin * kBatch + lane, cur_valid);
-  for (int t = threadIdx.x; t < 4 * kSub * kSub; t += 32 * NW) sg[t] = make_float4(0.f, 0.f, 0.f, 0.f);
+  if (!DIRECT)
+    for (int t = threadIdx.x; t < 4 * kSub * kSub; t += 32 * NW) sg[t] = make_float4(0.f, 0.f, 0.f, 0.f);
+  const int P0 = item.win * g.win_step;
+  int su0 = item.tu * kTile - kHalo + g.nu / 2;  // shifted -> FFT order: (s + nu/2) mod nu
+  int sv0 = item.tv * kTile - kHalo + g.nv / 2;
+  if (DIRECT) {  // reduced once here; su0 + i < 2 nu
+    su0 -= su0 >= g.nu ? g.nu : 0;
+    sv0 -= sv0 >= g.nv ? g.nv : 0;
+  }
+  const FoldSink sink{sg, grid, g.nu, g.nv, su0, sv0, P0, g.nplanes, plane_base, nslots};
 
   // producer constants
   const int W = g.W;
@@ -770,22 +814,20 @@ __global__ void __launch_bounds__(32 * NW) grid_warp_kernel(const Item* __restri
         // most groups stay inside one register window: branch-free fast path.  The operands of visibility
         // k0 + 8 are prefetched at the end of a group; past the last group that reads the rows after the
         // stage (still inside the CTA's shared memory: kSlack), which are discarded.
-        if (m8 == 0) warp_consume8<false, (NW > 1)>(pa, pb, porg, m8, x, acc, sg, cells, a, pq);
-        else warp_consume8<true, (NW > 1)>(pa, pb, porg, m8, x, acc, sg, cells, a, pq);
+        if (m8 == 0) warp_consume8<false, MODE>(pa, pb, porg, m8, x, acc, sink, cells, a, pq);
+        else warp_consume8<true, MODE>(pa, pb, porg, m8, x, acc, sink, cells, a, pq);
       }
     }
     __syncwarp();
     cur = nxt;
     cur_valid = nxt_valid;
   }
-  acc.template fold<(NW > 1)>(sg, cells.i, cells.wj, pq);
+  acc.template fold<MODE>(sink, cells.i, cells.wj, pq);
+  if (DIRECT) return;
   if (NW > 1) __syncthreads();
   else __syncwarp();
 
   // ---------------- sub-grid -> global plane stack (as in grid_kernel<float>) ----------------
-  const int P0 = item.win * g.win_step;
-  const int su0 = item.tu * kTile - kHalo + g.nu / 2;  // shifted -> FFT order: (s + nu/2) mod nu
-  const int sv0 = item.tv * kTile - kHalo + g.nv / 2;
   constexpr int kPairs = (kSub + 1) / 2;
   const int odd = sv0 & 1;
   for (int t = threadIdx.x; t < 4 * kSub * kPairs; t += 32 * NW) {
@@ -861,11 +903,11 @@ __global__ void __launch_bounds__(128) grid_wide_kernel(const Item* __restrict__
   }
 }
 
-template <int NW>
+template <int NW, bool DIRECT>
 cip_status launch_warp(cip_ctx* ctx, cudaStream_t stream, const Item* items, int64_t item_begin, int64_t n, const Rec<float>* recs,
                        const GridGeom& g, float* grid, int plane_base, int nslots) {
-  auto kern = grid_warp_kernel<NW>;
-  constexpr int smem = warp_smem_bytes(NW);
+  auto kern = grid_warp_kernel<NW, DIRECT>;
+  constexpr int smem = warp_smem_bytes(NW, DIRECT);
   CIP_CHECK_CUDA(cudaFuncSetAttribute(kern, cudaFuncAttributeMaxDynamicSharedMemorySize, smem));
   CIP_CHECK_CUDA(cudaFuncSetAttribute(kern, cudaFuncAttributePreferredSharedMemoryCarveout, (int)cudaSharedmemCarveoutMaxShared));
   kern<<<(unsigned)n, 32 * NW, smem, stream>>>(items, item_begin, recs, g, grid, plane_base, nslots);
@@ -883,10 +925,13 @@ cip_status launch(cip_ctx* ctx, int slot, cudaStream_t stream, const GridGeom& g
   CIP_REQUIRE(n < ((int64_t)1 << 31), "too many work items");
   if (g.W <= kFastSupport && sizeof(R) == 4 && !getenv("CIP_GRID_TWO_WARP")) {
     static const int nw = getenv("CIP_GRID_WARPS") ? atoi(getenv("CIP_GRID_WARPS")) : 1;
-    CIP_TRY((nw == 1 ? launch_warp<1> : nw == 2 ? launch_warp<2> : nw == 3 ? launch_warp<3> : nw == 5 ? launch_warp<5>
-                                                                                                : launch_warp<4>)(
-        ctx, stream, items, item_begin, n, reinterpret_cast<const Rec<float>*>(recs), g, reinterpret_cast<float*>(grid), plane_base,
-        nslots));
+    static const bool direct = getenv("CIP_GRID_DIRECT") ? atoi(getenv("CIP_GRID_DIRECT")) != 0 : true;
+    const Rec<float>* r32 = reinterpret_cast<const Rec<float>*>(recs);
+    float* g32 = reinterpret_cast<float*>(grid);
+    if (direct) CIP_TRY((launch_warp<1, true>(ctx, stream, items, item_begin, n, r32, g, g32, plane_base, nslots)));
+    else if (nw == 2) CIP_TRY((launch_warp<2, false>(ctx, stream, items, item_begin, n, r32, g, g32, plane_base, nslots)));
+    else if (nw == 4) CIP_TRY((launch_warp<4, false>(ctx, stream, items, item_begin, n, r32, g, g32, plane_base, nslots)));
+    else CIP_TRY((launch_warp<1, false>(ctx, stream, items, item_begin, n, r32, g, g32, plane_base, nslots)));
   } else if (g.W <= kFastSupport) {
     constexpr size_t smem = grid_smem_bytes<R>();
     auto kern = grid_kernel<R>;
