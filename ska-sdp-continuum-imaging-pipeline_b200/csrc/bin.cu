@@ -20,10 +20,6 @@ namespace cip {
 
 namespace {
 
-struct MaxOp {
-  __device__ __forceinline__ int64_t operator()(int64_t a, int64_t b) const { return a > b ? a : b; }
-};
-
 // One warp per row, lanes stride the channels; a run is a maximal stretch of channels of one row with
 // the same (window, tile) bin AND the same register-window lattice position inside the tile, so that
 // after the sort all records that share a register window of the gridder's consumer are contiguous.

@@ -2,22 +2,19 @@
 // SURVEY.md section 8a, the hot loop of ducc0.wgridder.ms2dirty (reference call site
 // src/ska_sdp_cip/invert.py:170-183).
 //
-// Design ("residue owner"): one CTA per work item = a slice of the records of one uv tile
-// (kTile x kTile support origins) and one window of kWin w planes.  The tile's sub-grid
-// (kSub x kSub cells x kWin planes) lives in shared memory.  Warp 0 (producer) streams the
-// 32-byte records with 128-bit loads, evaluates the ES kernel separably (8 u-, 8 v-,
-// 8 w-weights per visibility, one visibility per lane) and hands batches of 32 visibilities to
-// warp 1 (consumer) through a double buffer in shared memory (one named-barrier rendezvous per batch).  In the consumer,
-// lane (a, b) owns the grid cells with u index = a (mod 8) and v index = b or b+4 (mod 8): an
-// 8 x 8-cell register window that contains the support of the visibility (W <= 8) holds exactly one
-// cell of each residue class, so no two lanes ever touch the same cell and no atomics or shuffles are
-// needed.  The lane keeps its 2 cells x 8 planes in registers as packed pairs (FFMA2: fma.rn.f32x2)
-// while consecutive visibilities fall into the same register window -- the window origin is snapped
-// to a lattice of 9-W cells, and along a run of channels the support moves by a fraction of a cell
-// -- and folds them into the shared sub-grid (plain, conflict-free 128-bit read-modify-write; the
-// row pitch kSub is odd) only when the window moves.  The operands of visibility k+1 are loaded
-// while visibility k is accumulated.  The finished sub-grid is added to the global plane stack with
-// vector reductions (red.global.add.v4.f32), skipping empty cells.
+// Two kernels for supports W <= 8, both working on work items = the sorted records of one uv tile
+// (kTile x kTile support origins) and one window of kWin w planes, plus a plain scatter for W > 8:
+//
+// * float32, grid_warp_kernel ("rank-1 tiles"): one warp per item.  Per batch of 32 visibilities the warp
+//   first evaluates the ES kernel separably (one visibility per lane) and stages the 8 x 8 products
+//   ku kv and the 8 complex plane values V kw in shared memory, then applies the rank-1 update of the
+//   8 x 8 x 8 register window with 16 FFMA2 per lane.  Consecutive visibilities share the window (its
+//   origin is snapped to a lattice of 9-W cells and the records are sorted by lattice position); when
+//   the window moves it is added to the global plane stack with vector reductions.
+//
+// * float64, grid_kernel<double> ("residue owner"): a producer warp evaluates the kernel in float64 and
+//   hands batches to a consumer warp whose lane (a, b) owns the cells u = a, v = b or b+4 (mod 8) of the
+//   window; windows are folded into a sub-grid in shared memory that is flushed at the end of the item.
 #include <cstdlib>
 
 #include "geom.cuh"
@@ -49,43 +46,6 @@ __device__ __forceinline__ float2 unpack2(u64 v) {
 }
 // d = a * b + d on two packed floats (FFMA2 on sm_100a)
 __device__ __forceinline__ void ffma2(u64& d, u64 a, u64 b) { asm("fma.rn.f32x2 %0, %1, %2, %0;" : "+l"(d) : "l"(a), "l"(b)); }
-__device__ __forceinline__ u64 fmul2(u64 a, u64 b) {
-  u64 d;
-  asm("mul.rn.f32x2 %0, %1, %2;" : "=l"(d) : "l"(a), "l"(b));
-  return d;
-}
-
-// exp(beta_w (sqrt(t) - 1)) with the hardware approximations; bw2 = beta_w * log2(e)
-__device__ __forceinline__ float es_fast(float x, float bw2) {
-  float t = fmaf(-x, x, 1.0f);
-  float s;
-  asm("sqrt.approx.ftz.f32 %0, %1;" : "=f"(s) : "f"(fmaxf(t, 0.0f)));
-  float e;
-  asm("ex2.approx.ftz.f32 %0, %1;" : "=f"(e) : "f"(fmaf(bw2, s, -bw2)));
-  return t >= 0.0f ? e : 0.0f;
-}
-
-// exp(beta_w (sqrt(max(1 - x^2, 0)) - 1)): es_fast without the |x| > 1 test (the caller masks the taps outside
-// the support); pure inline PTX so that the compiler cannot turn the masking into a branch around it
-__device__ __forceinline__ float es_fast_nb(float x, float bw2) {
-  float e;
-  asm("{\n\t.reg .f32 t, s;\n\t"
-      "neg.f32 t, %1;\n\t"
-      "fma.rn.f32 t, t, %1, 0f3F800000;\n\t"
-      "max.f32 t, t, 0f00000000;\n\t"
-      "sqrt.approx.ftz.f32 s, t;\n\t"
-      "neg.f32 t, %2;\n\t"
-      "fma.rn.f32 s, %2, s, t;\n\t"
-      "ex2.approx.ftz.f32 %0, s;\n\t}"
-      : "=f"(e) : "f"(x), "f"(bw2));
-  return e;
-}
-// (unsigned)a < (unsigned)b ? v : 0
-__device__ __forceinline__ float sel_lt_u32(int a, int b, float v) {
-  float r;
-  asm("{\n\t.reg .pred p;\n\tsetp.lt.u32 p, %1, %2;\n\tselp.f32 %0, %3, 0f00000000, p;\n\t}" : "=f"(r) : "r"(a), "r"(b), "f"(v));
-  return r;
-}
 
 __device__ __forceinline__ void red_add_v4(float* addr, float a, float b, float c, float d) {
   asm volatile("red.global.add.v4.f32 [%0], {%1, %2, %3, %4};" ::"l"(addr), "f"(a), "f"(b), "f"(c), "f"(d) : "memory");
@@ -93,23 +53,10 @@ __device__ __forceinline__ void red_add_v4(float* addr, float a, float b, float 
 
 // ---- producer -> consumer hand-over ------------------------------------------------------
 template <typename R> struct StageVal;
-template <> struct StageVal<float> { using type = float4; };    // (re, re, im, im)
 template <> struct StageVal<double> { using type = double2; };  // (re, im)
 
 template <typename R>
 struct Stage;
-
-template <>
-struct alignas(16) Stage<float> {
-  using R = float;
-  float2 ku[kBatch][8];   // (k, k): weight of u residue class r for visibility k (0 outside the support)
-  float2 kv[kBatch][4];   // (class b, class b + 4)
-  float2 kw[kBatch][8];   // (k, k): the 8 plane weights of the window
-  typename StageVal<R>::type val[kBatch];
-  uint32_t org[kBatch];   // register-window origin: bits 0-4 u cell, 5-9 v cell (sub-grid coordinates)
-  uint32_t moved;         // bit k: the window of visibility k differs from that of visibility k-1
-  uint32_t pad[3];
-};
 
 // float64 path: weights in float64 (the float32 hardware approximations of es_fast would cap the
 // accuracy near 1e-6), no pair duplication (the consumer uses scalar DFMA)
@@ -171,125 +118,11 @@ __device__ __forceinline__ void produce(Stage<double>& st, const Rec<double>& re
   if (lane == 0) st.moved = moved;
 }
 
-__device__ __forceinline__ void produce(Stage<float>& st, const Rec<float>& rec, bool valid, int lane, uint32_t& carry,
-                                        const GridGeom& g, float bw2, float two_over_w, int snap) {
-  using R = float;
-  const int W = g.W;
-  const int i0 = rec.cell & 31, j0 = (rec.cell >> 5) & 31, p0 = (rec.cell >> 10) & 15;
-  uint32_t moved;
-  const uint32_t cxy = window_origin(rec.cell, valid, lane, carry, snap, &moved);
-  float ku[8], kv[8], kw[8];
-#pragma unroll
-  for (int r = 0; r < 8; ++r) {
-    int da = (r - i0) & 7, db = (r - j0) & 7, dc = r - p0;
-    float xu = fmaf(rec.fu + (float)da, two_over_w, -1.0f);
-    float xv = fmaf(rec.fv + (float)db, two_over_w, -1.0f);
-    float xw = fmaf(rec.fw + (float)dc, two_over_w, -1.0f);
-    ku[r] = da < W ? es_fast(xu, bw2) : 0.0f;
-    kv[r] = db < W ? es_fast(xv, bw2) : 0.0f;
-    kw[r] = (dc >= 0 && dc < W) ? es_fast(xw, bw2) : 0.0f;
-  }
-  if (!g.do_wstacking) {
-#pragma unroll
-    for (int r = 0; r < 8; ++r) kw[r] = r == 0 ? 1.0f : 0.0f;
-  }
-  // 16-byte chunks are XOR-swizzled with the visibility index so that the producer's 128-bit stores
-  // (row pitch 64 / 32 bytes) are bank-conflict free; the consumer applies the same permutation
-  const int sw = (lane >> 1) & 3, sv = (lane >> 2) & 1;
-  float4* pu = reinterpret_cast<float4*>(st.ku[lane]);
-  float4* pw = reinterpret_cast<float4*>(st.kw[lane]);
-#pragma unroll
-  for (int q = 0; q < 4; ++q) {
-    pu[q ^ sw] = make_float4(ku[2 * q], ku[2 * q], ku[2 * q + 1], ku[2 * q + 1]);
-    pw[q ^ sw] = make_float4(kw[2 * q], kw[2 * q], kw[2 * q + 1], kw[2 * q + 1]);
-  }
-  float4* pv = reinterpret_cast<float4*>(st.kv[lane]);
-  pv[0 ^ sv] = make_float4(kv[0], kv[4], kv[1], kv[5]);
-  pv[1 ^ sv] = make_float4(kv[2], kv[6], kv[3], kv[7]);
-  const R re = valid ? rec.re : (R)0, im = valid ? rec.im : (R)0;
-  st.val[lane] = make_float4(re, re, im, im);
-  st.org[lane] = cxy;
-  if (lane == 0) st.moved = moved;
-}
-
 // ---- consumer -------------------------------------------------------------------------
 template <typename R> struct SubGrid;
-template <> struct SubGrid<float> { using cell = float4; static constexpr int ncell = 4 * kSub * kSub; };
 template <> struct SubGrid<double> { using cell = double2; static constexpr int ncell = 8 * kSub * kSub; };
 
 template <typename R> struct Acc;
-
-// float: accumulators are packed pairs over the lane's two cells: re[p] = (cell0, cell1), im[p] likewise
-template <>
-struct Acc<float> {
-  struct Ops {
-    u64 ku, kv, rr, ii;
-    ulonglong2 kw[4];
-  };
-  u64 re[8], im[8];
-  __device__ __forceinline__ void clear() {
-#pragma unroll
-    for (int c = 0; c < 8; ++c) re[c] = im[c] = 0ull;
-  }
-  // Per-lane pointers to the rows of visibility k0 (a multiple of 8) of a stage, one per swizzle
-  // state, so that every operand of visibilities k0 .. k0+8 is a load at [register + immediate].
-  struct Group {
-    const char *ku[4], *kv[2], *kw, *val;
-  };
-  static __device__ __forceinline__ Group group(const Stage<float>& st, int k0, int a8, int b4) {
-    Group gp;
-#pragma unroll
-    for (int s = 0; s < 4; ++s) gp.ku[s] = reinterpret_cast<const char*>(st.ku[k0]) + (a8 ^ (2 * s)) * 8;
-#pragma unroll
-    for (int t = 0; t < 2; ++t)
-      gp.kv[t] = reinterpret_cast<const char*>(st.kv[k0]) + (((b4 >> 1) ^ t) * 2 + (b4 & 1)) * 8;
-    gp.kw = reinterpret_cast<const char*>(st.kw[k0]);
-    gp.val = reinterpret_cast<const char*>(&st.val[k0]);
-    return gp;
-  }
-  // Operands of visibility k0 + U, U = 0..8 (U = 8 is the first one of the next group; past the end of
-  // a stage it reads the following array of the struct and is discarded).
-  template <int U>
-  static __device__ __forceinline__ Ops load(const Group& gp) {
-    constexpr int sw = (U >> 1) & 3, sv = (U >> 2) & 1;
-    Ops o;
-    o.ku = *reinterpret_cast<const u64*>(gp.ku[sw] + U * 64);
-    o.kv = *reinterpret_cast<const u64*>(gp.kv[sv] + U * 32);
-    const ulonglong2 v = *reinterpret_cast<const ulonglong2*>(gp.val + U * 16);
-    o.rr = v.x;
-    o.ii = v.y;
-#pragma unroll
-    for (int q = 0; q < 4; ++q) o.kw[q] = *reinterpret_cast<const ulonglong2*>(gp.kw + U * 64 + (q ^ sw) * 16);
-    return o;
-  }
-  __device__ __forceinline__ void update(const Ops& o) {
-    const u64 w = fmul2(o.ku, o.kv);  // (ku kv0, ku kv1)
-    const u64 tr = fmul2(o.rr, w), ti = fmul2(o.ii, w);
-#pragma unroll
-    for (int q = 0; q < 4; ++q) {
-      ffma2(re[2 * q], tr, o.kw[q].x);
-      ffma2(im[2 * q], ti, o.kw[q].x);
-      ffma2(re[2 * q + 1], tr, o.kw[q].y);
-      ffma2(im[2 * q + 1], ti, o.kw[q].y);
-    }
-  }
-  // sub-grid cell = float4 {re(2pp), im(2pp), re(2pp+1), im(2pp+1)} for plane pair pp
-  __device__ __forceinline__ void fold(float4* sg, int i, int j0s, int j1s) {
-#pragma unroll
-    for (int pp = 0; pp < 4; ++pp) {
-      const float2 r0 = unpack2(re[2 * pp]), i0 = unpack2(im[2 * pp]);
-      const float2 r1 = unpack2(re[2 * pp + 1]), i1 = unpack2(im[2 * pp + 1]);
-      float4* p0 = sg + ((pp * kSub + i) * kSub + j0s);
-      float4* p1 = sg + ((pp * kSub + i) * kSub + j1s);
-      float4 v0 = *p0, v1 = *p1;
-      v0.x += r0.x; v0.y += i0.x; v0.z += r1.x; v0.w += i1.x;
-      v1.x += r0.y; v1.y += i0.y; v1.z += r1.y; v1.w += i1.y;
-      *p0 = v0;
-      *p1 = v1;
-    }
-    clear();
-  }
-};
 
 template <>
 struct Acc<double> {
@@ -474,40 +307,7 @@ __global__ void __launch_bounds__(kGridThreads) grid_kernel(const Item* __restri
   const int P0 = item.win * g.win_step;
   const int su0 = item.tu * kTile - kHalo + g.nu / 2;  // shifted -> FFT order: (s + nu/2) mod nu
   const int sv0 = item.tv * kTile - kHalo + g.nv / 2;
-  if constexpr (sizeof(R) == 4) {
-    // pairs of v-adjacent cells whose global index is even, so the 16-byte reduction is aligned
-    constexpr int kPairs = (kSub + 1) / 2;
-    const int odd = sv0 & 1;
-    for (int t = tid; t < 4 * kSub * kPairs; t += kGridThreads) {
-      int jp = t % kPairs, q = t / kPairs;
-      int i = q % kSub, pp = q / kSub;
-      int j = 2 * jp - odd;
-      const bool ok0 = j >= 0, ok1 = j + 1 < kSub;
-      float4 c0 = ok0 ? sg[(pp * kSub + i) * kSub + j] : make_float4(0.f, 0.f, 0.f, 0.f);
-      float4 c1 = ok1 ? sg[(pp * kSub + i) * kSub + j + 1] : make_float4(0.f, 0.f, 0.f, 0.f);
-      int gi = (su0 + i) % g.nu;
-      int gj = (sv0 + j + g.nv) % g.nv;
-#pragma unroll
-      for (int h = 0; h < 2; ++h) {
-        int plane = P0 + 2 * pp + h;
-        if (plane >= g.nplanes) continue;
-        int slot = plane - plane_base;
-        if (slot < 0 || slot >= nslots) continue;
-        float a = h ? c0.z : c0.x, bb = h ? c0.w : c0.y, c = h ? c1.z : c1.x, d = h ? c1.w : c1.y;
-        if (a == 0.f && bb == 0.f && c == 0.f && d == 0.f) continue;
-        float* dst = grid + 2 * (((int64_t)slot * g.nu + gi) * g.nv + gj);
-        if (ok0 && ok1) {
-          red_add_v4(dst, a, bb, c, d);
-        } else if (ok0) {
-          atomicAdd(dst, a);
-          atomicAdd(dst + 1, bb);
-        } else {
-          atomicAdd(dst + 2, c);
-          atomicAdd(dst + 3, d);
-        }
-      }
-    }
-  } else {
+  {
     for (int t = tid; t < 8 * kSub * kSub; t += kGridThreads) {
       int j = t % kSub, q = t / kSub;
       int i = q % kSub, c = q / kSub;
@@ -554,9 +354,6 @@ __device__ __forceinline__ ulonglong2 lds_u2(uint32_t addr) {
   ulonglong2 v;
   asm volatile("ld.shared.v2.b64 {%0, %1}, [%2+%3];" : "=l"(v.x), "=l"(v.y) : "r"(addr), "n"(OFF));
   return v;
-}
-__device__ __forceinline__ void sts_u2(uint32_t addr, u64 a, u64 b) {
-  asm volatile("st.shared.v2.b64 [%0], {%1, %2};" ::"r"(addr), "l"(a), "l"(b) : "memory");
 }
 __device__ __forceinline__ void sts_f4(uint32_t addr, float a, float b, float c, float d) {
   asm volatile("st.shared.v4.f32 [%0], {%1, %2, %3, %4};" ::"r"(addr), "f"(a), "f"(b), "f"(c), "f"(d) : "memory");
@@ -718,7 +515,7 @@ __device__ __forceinline__ void warp_consume8(uint32_t pa, uint32_t pb, uint32_t
 // leaves it (the records are sorted by window, so that happens ~ once per lattice position and item).  This
 // trades ~4x more L2 reductions for 14.4 KB of shared memory per warp, i.e. twice the resident warps.
 template <int NW, bool DIRECT>
-__global__ void __launch_bounds__(32 * NW) grid_warp_kernel(const Item* __restrict__ items, int64_t item_base,
+__global__ void __launch_bounds__(32 * NW, DIRECT ? 20 : 1) grid_warp_kernel(const Item* __restrict__ items, int64_t item_base,
                                                             const Rec<float>* __restrict__ recs, GridGeom g,
                                                             float* __restrict__ grid, int plane_base, int nslots) {
   constexpr int MODE = DIRECT ? 2 : (NW > 1 ? 1 : 0);
@@ -923,23 +720,25 @@ cip_status launch(cip_ctx* ctx, int slot, cudaStream_t stream, const GridGeom& g
   const int64_t n = item_end - item_begin;
   if (n <= 0) return CIP_OK;
   CIP_REQUIRE(n < ((int64_t)1 << 31), "too many work items");
-  if (g.W <= kFastSupport && sizeof(R) == 4 && !getenv("CIP_GRID_TWO_WARP")) {
-    static const int nw = getenv("CIP_GRID_WARPS") ? atoi(getenv("CIP_GRID_WARPS")) : 1;
-    static const bool direct = getenv("CIP_GRID_DIRECT") ? atoi(getenv("CIP_GRID_DIRECT")) != 0 : true;
-    const Rec<float>* r32 = reinterpret_cast<const Rec<float>*>(recs);
-    float* g32 = reinterpret_cast<float*>(grid);
-    if (direct) CIP_TRY((launch_warp<1, true>(ctx, stream, items, item_begin, n, r32, g, g32, plane_base, nslots)));
-    else if (nw == 2) CIP_TRY((launch_warp<2, false>(ctx, stream, items, item_begin, n, r32, g, g32, plane_base, nslots)));
-    else if (nw == 4) CIP_TRY((launch_warp<4, false>(ctx, stream, items, item_begin, n, r32, g, g32, plane_base, nslots)));
-    else CIP_TRY((launch_warp<1, false>(ctx, stream, items, item_begin, n, r32, g, g32, plane_base, nslots)));
-  } else if (g.W <= kFastSupport) {
-    constexpr size_t smem = grid_smem_bytes<R>();
-    auto kern = grid_kernel<R>;
-    CIP_CHECK_CUDA(cudaFuncSetAttribute(kern, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem));
-    CIP_CHECK_CUDA(cudaFuncSetAttribute(kern, cudaFuncAttributePreferredSharedMemoryCarveout,
-                                        (int)cudaSharedmemCarveoutMaxShared));
-    kern<<<(unsigned)n, kGridThreads, smem, stream>>>(items, item_begin, recs, g, static_cast<R*>(grid), plane_base,
-                                                          nslots);
+  if (g.W <= kFastSupport) {
+    if constexpr (sizeof(R) == 4) {
+      // float32: warp-autonomous kernel.  CIP_GRID_DIRECT=0 keeps the shared sub-grid (8 warps/SM, measured
+      // 10.8 ms on configs[1] against 10.0 ms for the direct fold), CIP_GRID_WARPS=2|4 shares it between warps.
+      static const int nw = getenv("CIP_GRID_WARPS") ? atoi(getenv("CIP_GRID_WARPS")) : 1;
+      static const bool direct = getenv("CIP_GRID_DIRECT") ? atoi(getenv("CIP_GRID_DIRECT")) != 0 : true;
+      if (direct) CIP_TRY((launch_warp<1, true>(ctx, stream, items, item_begin, n, recs, g, static_cast<float*>(grid), plane_base, nslots)));
+      else if (nw == 2) CIP_TRY((launch_warp<2, false>(ctx, stream, items, item_begin, n, recs, g, static_cast<float*>(grid), plane_base, nslots)));
+      else if (nw == 4) CIP_TRY((launch_warp<4, false>(ctx, stream, items, item_begin, n, recs, g, static_cast<float*>(grid), plane_base, nslots)));
+      else CIP_TRY((launch_warp<1, false>(ctx, stream, items, item_begin, n, recs, g, static_cast<float*>(grid), plane_base, nslots)));
+    } else {
+      // float64: producer / consumer warp pair ("residue owner")
+      constexpr size_t smem = grid_smem_bytes<R>();
+      auto kern = grid_kernel<R>;
+      CIP_CHECK_CUDA(cudaFuncSetAttribute(kern, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem));
+      CIP_CHECK_CUDA(cudaFuncSetAttribute(kern, cudaFuncAttributePreferredSharedMemoryCarveout,
+                                          (int)cudaSharedmemCarveoutMaxShared));
+      kern<<<(unsigned)n, kGridThreads, smem, stream>>>(items, item_begin, recs, g, static_cast<R*>(grid), plane_base, nslots);
+    }
   } else {
     grid_wide_kernel<R><<<(unsigned)n, 128, 0, stream>>>(items, item_begin, recs, g, static_cast<R*>(grid),
                                                               plane_base, nslots);
