@@ -74,24 +74,30 @@ __global__ void __launch_bounds__(256) scan_kernel(DevInputs in, int do_wstackin
 
 // nchan, strides multiples of 4 and 16-byte aligned pointers: four channels per thread and
 // iteration with 128-bit loads (2 x float4 vis, float4 wgt, one 32-bit word of mask)
+// (frequency / c per channel is tabulated in shared memory: a float64 division per sample made this kernel
+// compute-bound at a third of the HBM rate)
+template <typename Index>
 __global__ void __launch_bounds__(256) scan_kernel_v4(DevInputs in, int do_wstacking, ScanOut* out) {
-  const int nq = (int)(in.nchan >> 2);
-  const int64_t total = in.nrow * nq;
+  extern __shared__ double s_finv[];
+  for (int c = threadIdx.x; c < in.nchan; c += blockDim.x) s_finv[c] = in.freq[c] / kSpeedOfLight;
+  __syncthreads();
+  const Index nq = (Index)(in.nchan >> 2);
+  const Index total = (Index)(in.nrow * (int64_t)nq);
   ScanAcc acc;
-  for (int64_t k = (int64_t)blockIdx.x * blockDim.x + threadIdx.x; k < total; k += (int64_t)gridDim.x * blockDim.x) {
-    const int64_t r = k / nq;
+  for (Index k = (Index)blockIdx.x * blockDim.x + threadIdx.x; k < total; k += (Index)gridDim.x * blockDim.x) {
+    const Index r = k / nq;
     const int c = (int)(k - r * nq) << 2;
     float4 w = make_float4(1.f, 1.f, 1.f, 1.f);
-    if (in.wgt) w = __ldg(reinterpret_cast<const float4*>(in.wgt + r * in.wstride + c));
+    if (in.wgt) w = __ldg(reinterpret_cast<const float4*>(in.wgt + (int64_t)r * in.wstride + c));
     uint32_t mk = 0x01010101u;
-    if (in.mask) mk = __ldg(reinterpret_cast<const uint32_t*>(in.mask + r * in.wstride + c));
+    if (in.mask) mk = __ldg(reinterpret_cast<const uint32_t*>(in.mask + (int64_t)r * in.wstride + c));
     double aw0 = 0.0, aw1 = 0.0, aw2 = 0.0, aw3 = 0.0;
     if (do_wstacking) {
-      const double wm = fabs(in.uvw[3 * r + 2]);
-      aw0 = wm * (in.freq[c] / kSpeedOfLight);
-      aw1 = wm * (in.freq[c + 1] / kSpeedOfLight);
-      aw2 = wm * (in.freq[c + 2] / kSpeedOfLight);
-      aw3 = wm * (in.freq[c + 3] / kSpeedOfLight);
+      const double wm = fabs(in.uvw[3 * (int64_t)r + 2]);
+      aw0 = wm * s_finv[c];
+      aw1 = wm * s_finv[c + 1];
+      aw2 = wm * s_finv[c + 2];
+      aw3 = wm * s_finv[c + 3];
     }
     acc.add(w.x, (mk & 0xffu) == 0, aw0);
     acc.add(w.y, (mk & 0xff00u) == 0, aw1);
@@ -121,10 +127,14 @@ cip_status run_scan(cip_ctx* ctx, const DevInputs& in, int do_wstacking, cip_sca
   int64_t total = in.nrow * in.nchan;
   if (total > 0) {
     auto al16 = [](const void* p) { return (reinterpret_cast<uintptr_t>(p) & 15) == 0; };
-    const bool v4 = in.nchan % 4 == 0 && in.wstride % 4 == 0 && al16(in.wgt) && al16(in.mask);
+    const bool v4 = in.nchan % 4 == 0 && in.wstride % 4 == 0 && al16(in.wgt) && al16(in.mask) && in.nchan <= 4096;
     if (v4) {
       int blocks = (int)std::min<int64_t>((total / 4 + 255) / 256, (int64_t)ctx->sm_count * 8);
-      scan_kernel_v4<<<blocks, 256, 0, st>>>(in, do_wstacking, ctx->scan_out.as<ScanOut>());
+      const size_t smem = sizeof(double) * in.nchan;
+      if (total / 4 < ((int64_t)1 << 31))  // 32-bit index arithmetic (the row index costs a division per thread)
+        scan_kernel_v4<uint32_t><<<blocks, 256, smem, st>>>(in, do_wstacking, ctx->scan_out.as<ScanOut>());
+      else
+        scan_kernel_v4<int64_t><<<blocks, 256, smem, st>>>(in, do_wstacking, ctx->scan_out.as<ScanOut>());
     } else {
       int blocks = (int)std::min<int64_t>((total + 255) / 256, (int64_t)ctx->sm_count * 8);
       scan_kernel<<<blocks, 256, 0, st>>>(in, do_wstacking, ctx->scan_out.as<ScanOut>());
