@@ -50,6 +50,16 @@ def measured_peaks():
     return 6650.0, "fallback"
 
 
+def ncu_traffic():
+    """dram__bytes_read.sum + dram__bytes_write.sum of one gridding launch, from the committed `ncu --set full`
+    capture of this workload (profiles/grid_kernel_traffic.json, written by tools/ncu_summary.py); None if absent."""
+    p = ROOT / "profiles" / "grid_kernel_traffic.json"
+    try:
+        return int(json.loads(p.read_text())["dram_bytes"])
+    except Exception:  # noqa: BLE001
+        return None
+
+
 class ClockSampler:
     """nvidia-smi clocks / throttle reasons sampled DURING the timed region."""
 
@@ -326,8 +336,8 @@ def run_b200(args):
                              ("ms_h2d", "ms_scan", "ms_bin", "ms_grid", "ms_fft", "ms_d2h", "ms_total")}
                 if host_reports else None},
         "gpu_launches": int(launches),
-        "roofline": {"bound": "hbm", "kernel": "grid_kernel<float>", "achieved": achieved, "peak": peak,
-                     "unit": "GB/s", "frac": achieved / peak, "traffic": None, "peak_source": peak_kind,
+        "roofline": {"bound": "hbm", "kernel": "grid_warp_kernel<1, true>", "achieved": achieved, "peak": peak,
+                     "unit": "GB/s", "frac": achieved / peak, "traffic": ncu_traffic(), "peak_source": peak_kind,
                      "ms_per_launch": ms_grid, "algorithmic_bytes": int(alg_bytes)},
         "stage_ms": stage,
         "cpu_baseline": cpu,

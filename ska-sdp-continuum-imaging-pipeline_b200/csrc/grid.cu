@@ -724,8 +724,8 @@ cip_status launch(cip_ctx* ctx, int slot, cudaStream_t stream, const GridGeom& g
     if constexpr (sizeof(R) == 4) {
       // float32: warp-autonomous kernel.  CIP_GRID_DIRECT=0 keeps the shared sub-grid (8 warps/SM, measured
       // 10.8 ms on configs[1] against 10.0 ms for the direct fold), CIP_GRID_WARPS=2|4 shares it between warps.
-      static const int nw = getenv("CIP_GRID_WARPS") ? atoi(getenv("CIP_GRID_WARPS")) : 1;
-      static const bool direct = getenv("CIP_GRID_DIRECT") ? atoi(getenv("CIP_GRID_DIRECT")) != 0 : true;
+      const int nw = getenv("CIP_GRID_WARPS") ? atoi(getenv("CIP_GRID_WARPS")) : 1;
+      const bool direct = getenv("CIP_GRID_DIRECT") ? atoi(getenv("CIP_GRID_DIRECT")) != 0 : true;
       if (direct) CIP_TRY((launch_warp<1, true>(ctx, stream, items, item_begin, n, recs, g, static_cast<float*>(grid), plane_base, nslots)));
       else if (nw == 2) CIP_TRY((launch_warp<2, false>(ctx, stream, items, item_begin, n, recs, g, static_cast<float*>(grid), plane_base, nslots)));
       else if (nw == 4) CIP_TRY((launch_warp<4, false>(ctx, stream, items, item_begin, n, recs, g, static_cast<float*>(grid), plane_base, nslots)));

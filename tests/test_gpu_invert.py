@@ -274,6 +274,39 @@ def test_repeatable_to_rounding(wg, small):
     assert dft.rel_rms(a, b) <= 1e-14
 
 
+def _with_env(name, value, fn):
+    os.environ[name] = value
+    try:
+        return fn()
+    finally:
+        os.environ.pop(name)
+
+
+@pytest.mark.parametrize("env", [("CIP_GRID_DIRECT", "0"), ("CIP_GRID_WARPS", "2"), ("CIP_BIN_TWO_PASS", "1"),
+                                 ("CIP_DEVICE_CHUNKS", "3")])
+def test_kernel_variants_agree(wg, small, env):
+    """The measured alternatives kept behind environment switches -- register windows folded through a
+    shared sub-grid (one or two warps per item) instead of straight into the plane stack, runs counted and
+    written in two passes instead of one, device inputs cut into chunks that are binned and gridded on two
+    streams -- compute the same sums in another order."""
+    prob, ref = small
+    base, _ = invert(wg, prob)
+    name, value = env
+    if name == "CIP_GRID_WARPS":
+        alt, _ = _with_env("CIP_GRID_DIRECT", "0", lambda: _with_env(name, value, lambda: invert(wg, prob)))
+    elif name == "CIP_DEVICE_CHUNKS":
+        import torch
+        dev = torch.device("cuda", 0)
+        uvw, freq, vis, wgt, nx, px = prob
+        t = lambda a: torch.from_numpy(a).to(dev)
+        alt = _with_env(name, value, lambda: wg.ms2dirty(t(uvw), t(freq), t(vis), t(wgt), nx, nx, px, px, epsilon=1e-4,
+                                                         do_wstacking=True)).cpu().numpy()
+    else:
+        alt, _ = _with_env(name, value, lambda: invert(wg, prob))
+    assert dft.rel_rms(alt, base) <= 2e-6
+    assert dft.rel_rms(alt, ref) <= TOL_FP32
+
+
 def test_invalid_arguments_raise(wg, small):
     (uvw, freq, vis, wgt, nx, px), _ = small
     with pytest.raises(ValueError):

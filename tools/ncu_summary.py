@@ -28,3 +28,14 @@ rows=list(csv.reader(raw.splitlines()))
 for h,u,v in zip(rows[0],rows[1],rows[2]):
     if h in ('gpu__time_duration.sum','l1tex__data_pipe_lsu_wavefronts_mem_shared.sum','l1tex__data_pipe_lsu_wavefronts_mem_shared_op_ld.sum','l1tex__data_pipe_lsu_wavefronts_mem_shared_op_st.sum','l1tex__data_pipe_lsu_wavefronts.avg.pct_of_peak_sustained_elapsed','sm__inst_executed.avg.per_cycle_elapsed','l1tex__data_bank_conflicts_pipe_lsu_mem_shared.sum','dram__bytes_read.sum','dram__bytes_write.sum','sm__warps_active.avg.pct_of_peak_sustained_active','launch__grid_size','launch__registers_per_thread','sm__inst_executed_pipe_fma.avg.pct_of_peak_sustained_active','sm__inst_executed_pipe_fmaheavy.avg.pct_of_peak_sustained_active','sm__pipe_fma_cycles_active.avg.pct_of_peak_sustained_active','sm__pipe_fmaheavy_cycles_active.avg.pct_of_peak_sustained_active'):
         print(h,u,v)
+
+# optional 4th argument: write the DRAM traffic of this launch for bench.py's roofline.traffic
+if len(sys.argv) > 4:
+    import json
+    vals = {h: (u, v) for h, u, v in zip(rows[0], rows[1], rows[2])}
+    def to_bytes(name):
+        u, v = vals[name]
+        return float(v.replace(',', '')) * {'byte': 1, 'Kbyte': 1e3, 'Mbyte': 1e6, 'Gbyte': 1e9}[u]
+    d = {'kernel': vals.get('Kernel Name', ('', ''))[1], 'dram_bytes': int(to_bytes('dram__bytes_read.sum') + to_bytes('dram__bytes_write.sum')),
+         'source': rep}
+    open(sys.argv[4], 'w').write(json.dumps(d) + '\n')
