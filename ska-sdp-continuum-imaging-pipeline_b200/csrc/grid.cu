@@ -434,6 +434,34 @@ struct WarpAcc {
   }
   // sub-grid cell = float4 {re(2pp), im(2pp), re(2pp+1), im(2pp+1)} for plane pair pp = pq: one float4
   // read-modify-write per owned cell (the lane owns row i, all 8 v residues of the window)
+  template <int T0>
+  __device__ __forceinline__ void fold_pairs(const FoldSink& k, float* row0, float* row1, bool ok0, bool ok1, int wj) {
+#pragma unroll
+    for (int q = 0; q < 4; ++q) {
+      constexpr int dummy = 0;
+      (void)dummy;
+      const int ta = (T0 + 2 * q) & 7, tb = (T0 + 2 * q + 1) & 7;
+      const int ja = wj + ((ta - wj) & 7), jb = wj + ((tb - wj) & 7);
+      int ga = k.sv0 + ja, gb = k.sv0 + jb;
+      ga -= ga >= k.nv ? k.nv : 0;
+      gb -= gb >= k.nv ? k.nv : 0;
+      const bool adj = gb == ga + 1;
+#pragma unroll
+      for (int h = 0; h < 2; ++h) {
+        if (!(h ? ok1 : ok0)) continue;
+        float* row = h ? row1 : row0;
+        const u64 va = c[ta][h], vb = c[tb][h];
+        if ((va | vb) == 0ull) continue;
+        if (adj) {
+          const float2 x = unpack2(va), y = unpack2(vb);
+          red_add_v4(row + 2 * ga, x.x, x.y, y.x, y.y);
+        } else {
+          if (va != 0ull) red_add_v2(row + 2 * ga, va);
+          if (vb != 0ull) red_add_v2(row + 2 * gb, vb);
+        }
+      }
+    }
+  }
   // MODE 0: plain read-modify-write of the CTA's sub-grid; 1: shared-memory reductions (several warps fold into
   // one sub-grid); 2: no sub-grid, the window goes straight to the global plane stack with 8-byte reductions.
   template <int MODE>
@@ -446,13 +474,12 @@ struct WarpAcc {
       const bool ok1 = plane + 1 < k.nplanes && slot + 1 >= 0 && slot + 1 < k.nslots;
       float* row0 = k.grid + 2 * (((int64_t)slot * k.nu + gi) * k.nv);
       float* row1 = row0 + 2 * (int64_t)k.nu * k.nv;
-#pragma unroll
-      for (int t = 0; t < 8; ++t) {
-        int gj = k.sv0 + wj + ((t - wj) & 7);
-        gj -= gj >= k.nv ? k.nv : 0;
-        if (ok0 && c[t][0] != 0ull) red_add_v2(row0 + 2 * gj, c[t][0]);
-        if (ok1 && c[t][1] != 0ull) red_add_v2(row1 + 2 * gj, c[t][1]);
-      }
+      // Residue t sits at window column (t - wj) & 7, i.e. global column parity = parity(sv0 + t): the
+      // residue pairs (t, t+1) that start on an even global column are 16-byte aligned neighbours unless the
+      // window wraps between them, so most of the window goes out as 128-bit reductions (one sector per
+      // request lane instead of two 8-byte requests to the same sector).
+      if (k.sv0 & 1) fold_pairs<1>(k, row0, row1, ok0, ok1, wj);
+      else fold_pairs<0>(k, row0, row1, ok0, ok1, wj);
     } else {
       float4* row = k.sg + (pq * kSub + i) * kSub;
 #pragma unroll
@@ -611,8 +638,22 @@ __global__ void __launch_bounds__(32 * NW, DIRECT ? 20 : 1) grid_warp_kernel(con
         // most groups stay inside one register window: branch-free fast path.  The operands of visibility
         // k0 + 8 are prefetched at the end of a group; past the last group that reads the rows after the
         // stage (still inside the CTA's shared memory: kSlack), which are discarded.
-        if (m8 == 0) warp_consume8<false, MODE>(pa, pb, porg, m8, x, acc, sink, cells, a, pq);
-        else warp_consume8<true, MODE>(pa, pb, porg, m8, x, acc, sink, cells, a, pq);
+        if (m8 == 0) {
+          warp_consume8<false, MODE>(pa, pb, porg, m8, x, acc, sink, cells, a, pq);
+        } else {
+          // a window moves inside this group (rare): rolled loop, so that the fold is not inlined eight times
+          // (the unrolled variant doubled the code size and a third of the stalls were instruction fetches)
+#pragma unroll 1
+          for (int u = 0; u < 8; ++u) {
+            const WarpOps nxt = warp_load<1>(pa + u * kARow, pb + u * kBRow);
+            if ((m8 >> u) & 1u) {
+              acc.template fold<MODE>(sink, cells.i, cells.wj, pq);
+              cells.set(lds_u32(porg + 4 * u), a);
+            }
+            acc.update(x);
+            x = nxt;
+          }
+        }
       }
     }
     __syncwarp();
