@@ -162,8 +162,19 @@ cip_status stage_inputs(cip_ctx* ctx, const cip_invert_args* a, DevInputs* d, Vi
     nchunks = (int)std::min<int64_t>(nchunks, std::max<int64_t>(nrow, 1));
     feed->nchunks = nchunks;
     CIP_CHECK_CUDA(cudaStreamWaitEvent(ctx->copy_stream, ctx->small_ev, 0));
+    // The compute keeps up with the upload, so what the caller waits for after the last byte has arrived is
+    // the binning and gridding of the LAST chunk: the final three chunks taper (1/2, 1/4, 1/8 of the others).
+    double wsum = 0.0, wacc = 0.0, wgt_c[kMaxChunks];
     for (int c = 0; c < nchunks; ++c) {
-      const int64_t r0 = nrow * c / nchunks, r1 = nrow * (c + 1) / nchunks;
+      const int from_end = nchunks - 1 - c;
+      wgt_c[c] = (nchunks >= 4 && from_end < 3 && !getenv("CIP_STREAM_CHUNKS")) ? 1.0 / (double)(1 << (3 - from_end)) : 1.0;
+      wsum += wgt_c[c];
+    }
+    int64_t r_prev = 0;
+    for (int c = 0; c < nchunks; ++c) {
+      wacc += wgt_c[c];
+      const int64_t r0 = r_prev, r1 = c == nchunks - 1 ? nrow : std::max(r_prev, (int64_t)((double)nrow * (wacc / wsum)));
+      r_prev = r1;
       feed->row0[c] = r0;
       feed->row0[c + 1] = r1;
       if (r1 > r0 && nchan)
