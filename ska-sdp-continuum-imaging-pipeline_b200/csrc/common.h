@@ -248,7 +248,7 @@ cip_status run_binning(cip_ctx* ctx, int slot, const DevInputs& in, const GridGe
 // plane_base), on `stream`.
 cip_status run_gridder(cip_ctx* ctx, int slot, cudaStream_t stream, const GridGeom& g, int fp64, int64_t nrec_total,
                        int64_t item_begin, int64_t item_end, void* grid, int plane_base, int nslots);
-cip_status run_fft(cip_ctx* ctx, void* grid, int nu, int nv, int batch, int fp64);
+cip_status run_fft(cip_ctx* ctx, void* grid, int nu, int nv, int batch, int fp64, int keep_v = 0);
 cip_status run_wscreen(cip_ctx* ctx, const cip_plan& p, const void* grid, int plane_base, int nslots, void* image);
 cip_status run_correct(cip_ctx* ctx, const cip_plan& p, void* image, int row_begin, int row_end, double scale);
 
