@@ -29,7 +29,7 @@ namespace {
 //           (outpos[r] = first record of input-order run r); all float64 coordinate arithmetic of the
 //           gridder happens here.  Reads are row-contiguous, writes contiguous per run.
 template <int PASS, typename R>
-__global__ void __launch_bounds__(256) runs_kernel(DevInputs in, GridGeom g, int64_t* __restrict__ row_nruns,
+__global__ void __launch_bounds__(256, 6) runs_kernel(DevInputs in, GridGeom g, int64_t* __restrict__ row_nruns,
                                                    const int64_t* __restrict__ row_off, Run* __restrict__ runs,
                                                    uint64_t* __restrict__ keys, const int64_t* __restrict__ outpos,
                                                    Rec<R>* __restrict__ recs, const double* __restrict__ finv) {
