@@ -20,6 +20,16 @@ namespace cip {
 
 namespace {
 
+// Sort keys are stored as 32-bit words when they fit (they do up to ~ 8192^2-cell grids): the radix sort moves
+// a third fewer bytes per pass.
+__device__ __forceinline__ void store_key(void* keys, int64_t pos, uint64_t key, bool key32) {
+  if (key32) static_cast<uint32_t*>(keys)[pos] = (uint32_t)key;
+  else static_cast<uint64_t*>(keys)[pos] = key;
+}
+__device__ __forceinline__ uint64_t load_key(const void* keys, int64_t pos, bool key32) {
+  return key32 ? (uint64_t)static_cast<const uint32_t*>(keys)[pos] : static_cast<const uint64_t*>(keys)[pos];
+}
+
 // One warp per row, lanes stride the channels; a run is a maximal stretch of channels of one row with
 // the same (window, tile) bin AND the same register-window lattice position inside the tile, so that
 // after the sort all records that share a register window of the gridder's consumer are contiguous.
@@ -31,8 +41,8 @@ namespace {
 template <int PASS, typename R>
 __global__ void __launch_bounds__(256, 6) runs_kernel(DevInputs in, GridGeom g, int64_t* __restrict__ row_nruns,
                                                    const int64_t* __restrict__ row_off, Run* __restrict__ runs,
-                                                   uint64_t* __restrict__ keys, const int64_t* __restrict__ outpos,
-                                                   Rec<R>* __restrict__ recs, const double* __restrict__ finv) {
+                                                   void* __restrict__ keys, const int64_t* __restrict__ outpos,
+                                                   Rec<R>* __restrict__ recs, const double* __restrict__ finv, bool key32) {
   const int lane = threadIdx.x & 31;
   const int64_t row = ((int64_t)blockIdx.x * blockDim.x + threadIdx.x) >> 5;
   if (row >= in.nrow) return;
@@ -77,7 +87,7 @@ __global__ void __launch_bounds__(256, 6) runs_kernel(DevInputs in, GridGeom g, 
       r.row = (int32_t)row;
       r.ch0 = (int32_t)c;
       runs[pos] = r;
-      keys[pos] = key;
+      store_key(keys, pos, key, key32);
     }
     if (PASS == 2) {
       const unsigned upto = m & (0xffffffffu >> (31 - lane));  // starts at or before this lane
@@ -142,9 +152,9 @@ constexpr int kFusedWarps = 8;
 constexpr int kFusedChan = 768;
 __global__ void __launch_bounds__(32 * kFusedWarps) runs_fused_kernel(DevInputs in, GridGeom g, int64_t* __restrict__ row_nruns,
                                                                       int64_t* __restrict__ row_off, Run* __restrict__ runs,
-                                                                      uint64_t* __restrict__ keys,
+                                                                      void* __restrict__ keys,
                                                                       const double* __restrict__ finv, int nch32,
-                                                                      int64_t cap) {
+                                                                      int64_t cap, bool key32) {
   extern __shared__ uint64_t skeys[];  // [warp][nch32]
   __shared__ int s_cnt[kFusedWarps];
   __shared__ unsigned long long s_base;
@@ -205,7 +215,7 @@ __global__ void __launch_bounds__(32 * kFusedWarps) runs_fused_kernel(DevInputs 
       r.ch0 = (int32_t)c;
       if (pos < cap) {
         runs[pos] = r;
-        keys[pos] = key;
+        store_key(keys, pos, key, key32);
       }
     }
     m_before += __popc(m);
@@ -234,7 +244,7 @@ __global__ void run_len_kernel(const Run* __restrict__ runs, int64_t nruns, int3
 
 // sorted order: gather run + length, flag bin starts
 __global__ void gather_kernel(const Run* __restrict__ runs, const int32_t* __restrict__ len,
-                              const uint32_t* __restrict__ idx, const uint64_t* __restrict__ keys_sorted, int64_t nruns,
+                              const uint32_t* __restrict__ idx, const void* __restrict__ keys_sorted, bool key32, int64_t nruns,
                               Run* __restrict__ runs_sorted, int64_t* __restrict__ len_sorted,
                               int64_t* __restrict__ start_flag) {
   int64_t i = (int64_t)blockIdx.x * blockDim.x + threadIdx.x;
@@ -242,7 +252,7 @@ __global__ void gather_kernel(const Run* __restrict__ runs, const int32_t* __res
   uint32_t r = idx[i];
   runs_sorted[i] = runs[r];
   len_sorted[i] = len[r];
-  start_flag[i] = (i == 0 || (keys_sorted[i] >> kSubKeyBits) != (keys_sorted[i - 1] >> kSubKeyBits)) ? 1 : 0;
+  start_flag[i] = (i == 0 || (load_key(keys_sorted, i, key32) >> kSubKeyBits) != (load_key(keys_sorted, i - 1, key32) >> kSubKeyBits)) ? 1 : 0;
 }
 
 // group g = g-th distinct key; first run of each group, number of items of each group
@@ -326,6 +336,12 @@ cip_status run_binning(cip_ctx* ctx, int slot, const DevInputs& in, const GridGe
   double* finv = w.finv.as<double>();
   finv_kernel<<<nblk(nchan, 256), 256, 0, st>>>(in.freq, nchan, finv);
   ctx->launches++;
+  uint64_t nkeys = (uint64_t)g.nwin * g.ntu * g.ntv;
+  int bits = 1;
+  while (bits < 64 && (nkeys >> bits)) ++bits;
+  bits += kSubKeyBits;
+  CIP_REQUIRE(bits <= 64, "bin key too wide (%d bits)", bits);
+  const bool key32 = bits <= 32 && !getenv("CIP_BIN_KEY64");
   int64_t nruns = 0;
   size_t tmp_bytes = 0;
   Run* runs = nullptr;
@@ -343,7 +359,7 @@ cip_status run_binning(cip_ctx* ctx, int slot, const DevInputs& in, const GridGe
       runs = w.runs.as<Run>();
       CIP_CHECK_CUDA(cudaMemsetAsync(row_off + nrow, 0, sizeof(int64_t), st));
       runs_fused_kernel<<<nblk(nrow, kFusedWarps), 32 * kFusedWarps, smem, st>>>(in, g, row_nruns, row_off, runs,
-                                                                                 w.run_keys.as<uint64_t>(), finv, nch32, cap);
+                                                                                 w.run_keys.p, finv, nch32, cap, key32);
       ctx->launches++;
       CIP_TRY(d2h_scalar(ctx, row_off + nrow, &nruns));
       if (nruns <= cap) break;
@@ -352,7 +368,7 @@ cip_status run_binning(cip_ctx* ctx, int slot, const DevInputs& in, const GridGe
     }
     CIP_REQUIRE(nruns > 0 && nruns < ((int64_t)1 << 32), "unexpected number of runs %lld", (long long)nruns);
   } else {
-    runs_kernel<0, float><<<rblocks, 256, 0, st>>>(in, g, row_nruns, nullptr, nullptr, nullptr, nullptr, (Rec<float>*)nullptr, finv);
+    runs_kernel<0, float><<<rblocks, 256, 0, st>>>(in, g, row_nruns, nullptr, nullptr, nullptr, nullptr, (Rec<float>*)nullptr, finv, key32);
     ctx->launches++;
     CIP_CHECK_CUDA(cub::DeviceScan::ExclusiveSum(nullptr, tmp_bytes, row_nruns, row_off, nrow + 1, st));
     CIP_TRY(w.cub_tmp.ensure(tmp_bytes));
@@ -364,8 +380,8 @@ cip_status run_binning(cip_ctx* ctx, int slot, const DevInputs& in, const GridGe
     CIP_TRY(w.runs.ensure(sizeof(Run) * nruns));
     CIP_TRY(w.run_keys.ensure(sizeof(uint64_t) * nruns));
     runs = w.runs.as<Run>();
-    runs_kernel<1, float><<<rblocks, 256, 0, st>>>(in, g, nullptr, row_off, runs, w.run_keys.as<uint64_t>(), nullptr,
-                                                   (Rec<float>*)nullptr, finv);
+    runs_kernel<1, float><<<rblocks, 256, 0, st>>>(in, g, nullptr, row_off, runs, w.run_keys.p, nullptr,
+                                                   (Rec<float>*)nullptr, finv, key32);
     ctx->launches++;
   }
   CIP_TRY(w.run_keys_alt.ensure(sizeof(uint64_t) * nruns));
@@ -377,19 +393,25 @@ cip_status run_binning(cip_ctx* ctx, int slot, const DevInputs& in, const GridGe
   ctx->launches++;
 
   // --- stable sort of the runs by key ----------------------------------------------
-  uint64_t nkeys = (uint64_t)g.nwin * g.ntu * g.ntv;
-  int bits = 1;
-  while (bits < 64 && (nkeys >> bits)) ++bits;
-  bits += kSubKeyBits;
-  CIP_REQUIRE(bits <= 64, "bin key too wide (%d bits)", bits);
-  CIP_CHECK_CUDA(cub::DeviceRadixSort::SortPairs(nullptr, tmp_bytes, w.run_keys.as<uint64_t>(),
-                                                 w.run_keys_alt.as<uint64_t>(), w.run_idx.as<uint32_t>(),
-                                                 w.run_idx_alt.as<uint32_t>(), nruns, 0, bits, st));
-  CIP_TRY(w.cub_tmp.ensure(tmp_bytes));
-  tmp_bytes = w.cub_tmp.cap;
-  CIP_CHECK_CUDA(cub::DeviceRadixSort::SortPairs(w.cub_tmp.p, tmp_bytes, w.run_keys.as<uint64_t>(),
-                                                 w.run_keys_alt.as<uint64_t>(), w.run_idx.as<uint32_t>(),
-                                                 w.run_idx_alt.as<uint32_t>(), nruns, 0, bits, st));
+  if (key32) {
+    CIP_CHECK_CUDA(cub::DeviceRadixSort::SortPairs(nullptr, tmp_bytes, w.run_keys.as<uint32_t>(),
+                                                   w.run_keys_alt.as<uint32_t>(), w.run_idx.as<uint32_t>(),
+                                                   w.run_idx_alt.as<uint32_t>(), nruns, 0, bits, st));
+    CIP_TRY(w.cub_tmp.ensure(tmp_bytes));
+    tmp_bytes = w.cub_tmp.cap;
+    CIP_CHECK_CUDA(cub::DeviceRadixSort::SortPairs(w.cub_tmp.p, tmp_bytes, w.run_keys.as<uint32_t>(),
+                                                   w.run_keys_alt.as<uint32_t>(), w.run_idx.as<uint32_t>(),
+                                                   w.run_idx_alt.as<uint32_t>(), nruns, 0, bits, st));
+  } else {
+    CIP_CHECK_CUDA(cub::DeviceRadixSort::SortPairs(nullptr, tmp_bytes, w.run_keys.as<uint64_t>(),
+                                                   w.run_keys_alt.as<uint64_t>(), w.run_idx.as<uint32_t>(),
+                                                   w.run_idx_alt.as<uint32_t>(), nruns, 0, bits, st));
+    CIP_TRY(w.cub_tmp.ensure(tmp_bytes));
+    tmp_bytes = w.cub_tmp.cap;
+    CIP_CHECK_CUDA(cub::DeviceRadixSort::SortPairs(w.cub_tmp.p, tmp_bytes, w.run_keys.as<uint64_t>(),
+                                                   w.run_keys_alt.as<uint64_t>(), w.run_idx.as<uint32_t>(),
+                                                   w.run_idx_alt.as<uint32_t>(), nruns, 0, bits, st));
+  }
   ctx->launches += 2 + (bits + 7) / 8;
 
   // --- sorted runs, record offsets, bins -------------------------------------------
@@ -402,7 +424,7 @@ cip_status run_binning(cip_ctx* ctx, int slot, const DevInputs& in, const GridGe
   int64_t* start_flag = w.flags.as<int64_t>();
   int64_t* group_of = start_flag + nruns;
   gather_kernel<<<nblk(nruns, 256), 256, 0, st>>>(runs, w.run_len.as<int32_t>(), w.run_idx_alt.as<uint32_t>(),
-                                                  w.run_keys_alt.as<uint64_t>(), nruns, runs_sorted, len_sorted,
+                                                  w.run_keys_alt.p, key32, nruns, runs_sorted, len_sorted,
                                                   start_flag);
   ctx->launches++;
   CIP_CHECK_CUDA(cub::DeviceScan::ExclusiveSum(nullptr, tmp_bytes, len_sorted, visoff, nruns, st));
@@ -447,10 +469,10 @@ cip_status run_binning(cip_ctx* ctx, int slot, const DevInputs& in, const GridGe
   CIP_TRY(w.recs.ensure(recs_bytes(nrec)));
   if (fp64)
     runs_kernel<2, double><<<rblocks, 256, 0, st>>>(in, g, row_nruns, row_off, nullptr, nullptr, outpos,
-                                                    w.recs.as<Rec<double>>(), finv);
+                                                    w.recs.as<Rec<double>>(), finv, key32);
   else
     runs_kernel<2, float><<<rblocks, 256, 0, st>>>(in, g, row_nruns, row_off, nullptr, nullptr, outpos,
-                                                   w.recs.as<Rec<float>>(), finv);
+                                                   w.recs.as<Rec<float>>(), finv, key32);
   ctx->launches++;
   CIP_CHECK_CUDA(cudaGetLastError());
 
