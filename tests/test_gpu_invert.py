@@ -86,7 +86,7 @@ def test_complex128_input_selects_fp64(wg, small):
     assert dft.rel_rms(img, ref) <= 1e-6
 
 
-# every branch of the gridder: the fast residue-owner path (W <= 8) at each support, the wide path
+# every branch of the gridder: the register-window kernels (W <= 8) at each support, the wide path
 # (W > 8), each oversampling factor
 @pytest.mark.parametrize("sigma,W,tol", [(2.0, 4, 2e-3), (2.0, 5, 3e-4), (2.0, 6, 1e-4), (2.0, 7, 1e-4), (2.0, 8, 1e-4),
                                          (1.5, 6, 3e-4), (1.5, 7, 1e-4), (1.5, 8, 1e-4), (1.75, 5, 5e-4),
@@ -242,7 +242,7 @@ def test_device_inputs_match_host_inputs(wg, small):
     t = lambda a: torch.from_numpy(a).to(dev)
     out = wg.ms2dirty(t(uvw), t(freq), t(vis), t(wgt), nx, nx, px, px, epsilon=1e-4, do_wstacking=True)
     assert out.is_cuda and out.dtype == torch.float32
-    # same kernels on the same data; only the order of the sub-grid reductions into the plane stack differs
+    # same kernels on the same data; only the order of the reductions into the plane stack differs
     assert dft.rel_rms(out.cpu().numpy(), host) <= 2e-6
 
 
@@ -262,9 +262,10 @@ def test_streamed_host_chunks_give_the_same_image(wg, small, chunks):
 
 
 def test_repeatable_to_rounding(wg, small):
-    """Tiles are accumulated in shared memory in a fixed order; only the final reductions of the sub-grids
-    into the global plane stack (red.global.add) are unordered, so two runs agree to float32 rounding
-    in fp32 and to float64 rounding in fp64."""
+    """Register windows are accumulated in a fixed order per work item; the order in which runs land in a bin
+    (one cursor atomic per CTA of the fused runs pass) and the reductions of the windows into the global plane
+    stack (red.global.add) are unordered, so two runs agree to float32 rounding in fp32 and to float64
+    rounding in fp64."""
     prob, _ = small
     a, _ = invert(wg, prob)
     b, _ = invert(wg, prob)
