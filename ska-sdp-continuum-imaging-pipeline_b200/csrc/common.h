@@ -182,7 +182,7 @@ struct cip_ctx {
   cudaEvent_t binned_ev[2] = {}, gridded_ev[2] = {}, zero_ev = nullptr;  // non-timing
   cudaEvent_t chunk_t[cip::kMaxChunks][4] = {};                          // timing: bin begin/end, grid begin/end
   // grids, fft, image
-  cip::DevBuf grid, image, tables;
+  cip::DevBuf grid, image, tables, fft_t;  // fft_t: one transposed, cropped plane (ny x nu)
   std::vector<double> tables_key;  // plan parameters the correction tables were built for
   int tables_ncheb = 0;
   std::map<std::tuple<int, int, int, int>, cip::FftPlan> fft_plans;  // (nu, nv, batch, fp64)
@@ -249,6 +249,12 @@ cip_status run_binning(cip_ctx* ctx, int slot, const DevInputs& in, const GridGe
 cip_status run_gridder(cip_ctx* ctx, int slot, cudaStream_t stream, const GridGeom& g, int fp64, int64_t nrec_total,
                        int64_t item_begin, int64_t item_end, void* grid, int plane_base, int nslots);
 cip_status run_fft(cip_ctx* ctx, void* grid, int nu, int nv, int batch, int fp64, int keep_v = 0);
+cip_status fft_rows(cip_ctx* ctx, void* data, int n, int batch, int fp64);  // data == nullptr: plan only
+// FFT + w-screen of the resident planes [plane_base, plane_base + nslots) into the image.  Default: per plane,
+// 1-D transforms along v, transpose of the retained columns, 1-D transforms along u, w-screen from the
+// transposed plane (see image.cu); CIP_FFT_2D=1: cuFFT's 2-D plan on every plane, then one w-screen pass.
+cip_status run_fft_screen(cip_ctx* ctx, const cip_plan& p, void* grid, int plane_base, int nslots, void* image,
+                          double* ms_fft, double* ms_wscreen);
 cip_status run_wscreen(cip_ctx* ctx, const cip_plan& p, const void* grid, int plane_base, int nslots, void* image);
 cip_status run_correct(cip_ctx* ctx, const cip_plan& p, void* image, int row_begin, int row_end, double scale);
 

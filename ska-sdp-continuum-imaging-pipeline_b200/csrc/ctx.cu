@@ -278,7 +278,7 @@ extern "C" cip_status cip_ctx_destroy(cip_ctx* ctx) {
   if (ctx->grid_stream) cudaStreamSynchronize(ctx->grid_stream);
   for (auto& kv : ctx->fft_plans) cufftDestroy(kv.second.handle);
   DevBuf* bufs[] = {&ctx->in_uvw, &ctx->in_freq, &ctx->in_vis, &ctx->in_wgt, &ctx->in_mask, &ctx->out_img,
-                    &ctx->scan_out, &ctx->grid, &ctx->image, &ctx->tables, &ctx->t_uvw, &ctx->t_freq, &ctx->t_vis};
+                    &ctx->scan_out, &ctx->grid, &ctx->image, &ctx->tables, &ctx->fft_t, &ctx->t_uvw, &ctx->t_freq, &ctx->t_vis};
   for (auto& w : ctx->work) w.release();
   for (DevBuf* b : bufs) b->release();
   if (ctx->scan_host) cudaFreeHost(ctx->scan_host);

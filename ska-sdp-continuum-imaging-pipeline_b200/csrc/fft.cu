@@ -31,6 +31,18 @@ cip_status exec(cufftHandle h, void* p, int fp64) {
 
 }  // namespace
 
+// Contiguous batched 1-D transform (`batch` rows of length n), cached per (n, batch, precision).
+cip_status fft_rows(cip_ctx* ctx, void* data, int n, int batch, int fp64) {
+  int nn[1] = {n};
+  cufftHandle h;
+  CIP_TRY(get_plan(ctx, std::make_tuple(n, batch, -1, fp64), 1, nn, nn, 1, n, batch, fp64, &h));
+  if (data) {
+    CIP_TRY(exec(h, data, fp64));
+    ctx->launches++;
+  }
+  return CIP_OK;
+}
+
 // keep_v: number of v columns of the transformed plane that the w-screen reads (the image width ny; they
 // are the columns [0, ny/2) and [nv - ny/2, nv) in FFT order).  When keep_v < nv the transform is pruned:
 // contiguous 1-D transforms along v for every row, then strided 1-D transforms along u for the retained

@@ -9,6 +9,7 @@
 // each transformed plane and touches the image once per block of planes.
 #include <algorithm>
 #include <cmath>
+#include <cstdlib>
 
 #include "common.h"
 
@@ -51,6 +52,74 @@ __global__ void __launch_bounds__(256) wscreen_kernel(ScreenParams p, const R* _
     }
   }
   image[(size_t)i * p.ny + j] += acc;
+}
+
+template <typename R> struct Cplx;
+template <> struct Cplx<float> { using type = float2; };
+template <> struct Cplx<double> { using type = double2; };
+
+// T[j][iu] = F[iu][(j - ny/2) mod nv]: the ny retained v columns of a plane that has been transformed along v,
+// transposed so that the transforms along u are contiguous rows.  32 x 32 tiles through shared memory.
+template <typename R>
+__global__ void __launch_bounds__(256) transpose_crop_kernel(const typename Cplx<R>::type* __restrict__ f,
+                                                             typename Cplx<R>::type* __restrict__ t, int nu, int nv, int ny) {
+  using C = typename Cplx<R>::type;
+  __shared__ C tile[32][33];
+  const int j0 = blockIdx.x * 32, i0 = blockIdx.y * 32;
+  const int tx = threadIdx.x & 31, ty = threadIdx.x >> 5;
+  for (int r = ty; r < 32; r += 8) {
+    const int i = i0 + r, j = j0 + tx;
+    if (i < nu && j < ny) {
+      int gj = j - ny / 2;
+      gj += gj < 0 ? nv : 0;
+      tile[r][tx] = f[(size_t)i * nv + gj];
+    }
+  }
+  __syncthreads();
+  for (int r = ty; r < 32; r += 8) {
+    const int j = j0 + r, i = i0 + tx;
+    if (i < nu && j < ny) t[(size_t)j * nu + i] = tile[tx][r];
+  }
+}
+
+// D[i,j] += Re( T[j][(i - nx/2) mod nu] * exp(-2 pi i w_p (n-1+s)) ) for one transformed, transposed plane.
+template <typename R>
+__global__ void __launch_bounds__(256) wscreen_t_kernel(ScreenParams p, int plane, const typename Cplx<R>::type* __restrict__ t,
+                                                        R* __restrict__ image) {
+  __shared__ R tile[32][33];
+  const int j0 = blockIdx.x * 32, i0 = blockIdx.y * 32;
+  const int tx = threadIdx.x & 31, ty = threadIdx.x >> 5;
+  const double wp = p.w0 + plane * p.dw;
+  for (int r = ty; r < 32; r += 8) {  // lanes along i: coalesced reads of T
+    const int j = j0 + r, i = i0 + tx;
+    R val = 0;
+    if (i < p.nx && j < p.ny) {
+      const double l = (i - p.nx / 2) * p.px, m = (j - p.ny / 2) * p.py, e = l * l + m * m;
+      if (e < 1.0) {
+        int gi = i - p.nx / 2;
+        gi += gi < 0 ? p.nu : 0;
+        const auto f = t[(size_t)j * p.nu + gi];
+        const double z = p.do_wstacking ? -e / (sqrt(1.0 - e) + 1.0) + p.nshift : 0.0;
+        double ph = wp * z;
+        ph -= rint(ph);
+        if constexpr (sizeof(R) == 4) {
+          float sn, cs;
+          sincospif(2.0f * (float)ph, &sn, &cs);
+          val = f.x * cs + f.y * sn;
+        } else {
+          double sn, cs;
+          sincospi(2.0 * ph, &sn, &cs);
+          val = f.x * cs + f.y * sn;
+        }
+      }
+    }
+    tile[r][tx] = val;
+  }
+  __syncthreads();
+  for (int r = ty; r < 32; r += 8) {  // lanes along j: coalesced image update
+    const int i = i0 + r, j = j0 + tx;
+    if (i < p.nx && j < p.ny) image[(size_t)i * p.ny + j] += tile[tx][r];
+  }
 }
 
 struct CorrectParams {
@@ -104,6 +173,49 @@ cip_status run_wscreen(cip_ctx* ctx, const cip_plan& pl, const void* grid, int p
   ctx->launches++;
   CIP_CHECK_CUDA(cudaGetLastError());
   return CIP_OK;
+}
+
+template <typename R>
+static cip_status fft_screen_transposed(cip_ctx* ctx, const cip_plan& pl, const ScreenParams& p, void* grid, int nslots,
+                                        void* image) {
+  using C = typename Cplx<R>::type;
+  const int nu = pl.nu, nv = pl.nv, nx = pl.npix_x, ny = pl.npix_y;
+  CIP_TRY(ctx->fft_t.ensure(sizeof(C) * (size_t)ny * nu));
+  C* t = ctx->fft_t.as<C>();
+  const dim3 tg((ny + 31) / 32, (nu + 31) / 32), sg((ny + 31) / 32, (nx + 31) / 32);
+  for (int s = 0; s < nslots; ++s) {
+    const int plane = p.plane_base + s;
+    if (plane >= p.nplanes) break;
+    C* f = static_cast<C*>(grid) + (size_t)s * nu * nv;
+    CIP_TRY(fft_rows(ctx, f, nv, nu, sizeof(R) == 8));                     // along v, every row
+    transpose_crop_kernel<R><<<tg, 256, 0, ctx->stream>>>(f, t, nu, nv, ny);  // retained columns only
+    CIP_TRY(fft_rows(ctx, t, nu, ny, sizeof(R) == 8));                     // along u, ny rows of the transpose
+    wscreen_t_kernel<R><<<sg, 256, 0, ctx->stream>>>(p, plane, t, static_cast<R*>(image));
+    ctx->launches += 2;
+  }
+  CIP_CHECK_CUDA(cudaGetLastError());
+  return CIP_OK;
+}
+
+cip_status run_fft_screen(cip_ctx* ctx, const cip_plan& pl, void* grid, int plane_base, int nslots, void* image,
+                          double* ms_fft, double* ms_wscreen) {
+  (void)ms_wscreen;
+  if (grid == nullptr) {  // plans only
+    if (getenv("CIP_FFT_2D")) return run_fft(ctx, nullptr, pl.nu, pl.nv, 0, pl.accumulate_fp64, pl.npix_y);
+    // plans, their work areas and the transposed plane exist before the plane stack is sized from what is free
+    CIP_TRY(ctx->fft_t.ensure((size_t)(pl.accumulate_fp64 ? 16 : 8) * pl.npix_y * pl.nu));
+    CIP_TRY(fft_rows(ctx, nullptr, pl.nv, pl.nu, pl.accumulate_fp64));
+    return fft_rows(ctx, nullptr, pl.nu, pl.npix_y, pl.accumulate_fp64);
+  }
+  (void)ms_fft;
+  if (getenv("CIP_FFT_2D")) {
+    CIP_TRY(run_fft(ctx, grid, pl.nu, pl.nv, std::min(nslots, pl.nplanes - plane_base), pl.accumulate_fp64, pl.npix_y));
+    return run_wscreen(ctx, pl, grid, plane_base, nslots, image);
+  }
+  ScreenParams p{pl.npix_x, pl.npix_y, pl.nu, pl.nv, pl.pixsize_x, pl.pixsize_y, pl.w0, pl.dw, pl.nshift,
+                 plane_base, nslots, pl.nplanes, pl.do_wstacking};
+  if (pl.accumulate_fp64) return fft_screen_transposed<double>(ctx, pl, p, grid, nslots, image);
+  return fft_screen_transposed<float>(ctx, pl, p, grid, nslots, image);
 }
 
 // Chebyshev coefficients of c(xi) on |xi| <= ximax in the variable t = 2 (xi/ximax)^2 - 1.

@@ -50,9 +50,7 @@ struct CopyStreamGuard {
   ~CopyStreamGuard() { cudaStreamSynchronize(ctx->copy_stream); }
 };
 
-cip_status fft_prepare(cip_ctx* ctx, int nu, int nv, int fp64, int keep_v) {
-  return run_fft(ctx, nullptr, nu, nv, 0, fp64, keep_v);  // batch 0: only creates and caches the plans
-}
+
 
 }  // namespace
 
@@ -91,7 +89,7 @@ static cip_status grid_accumulate_staged(cip_ctx* ctx, const DevInputs& in, cons
   double dummy = 0;
 
   // how many planes fit
-  CIP_TRY(fft_prepare(ctx, plan->nu, plan->nv, fp64, plan->npix_y));
+  CIP_TRY(run_fft_screen(ctx, *plan, nullptr, 0, 0, nullptr, nullptr, nullptr));  // creates and caches the plans
   const size_t plane_bytes = (size_t)plan->nu * plan->nv * (fp64 ? 16 : 8);
   // cudaMemGetInfo is a device-wide driver call (it can wait behind in-flight copies): only ask when the
   // plane stack has to grow
@@ -198,12 +196,9 @@ static cip_status grid_accumulate_staged(cip_ctx* ctx, const DevInputs& in, cons
     }
     if (rep) rep->nblocks = feed.nchunks;
     if (!any) return CIP_OK;
-    tm.start();
-    CIP_TRY(run_fft(ctx, ctx->grid.p, plan->nu, plan->nv, plan->nplanes, fp64, plan->npix_y));
+    tm.start();  // ms_fft includes the w-screen (they alternate per plane)
+    CIP_TRY(run_fft_screen(ctx, *plan, ctx->grid.p, 0, plan->nplanes, image_dev, nullptr, nullptr));
     tm.stop(rep ? &rep->ms_fft : &dummy);
-    tm.start();
-    CIP_TRY(run_wscreen(ctx, *plan, ctx->grid.p, 0, plan->nplanes, image_dev));
-    tm.stop(rep ? &rep->ms_wscreen : &dummy);
     return CIP_OK;
   }
 
@@ -227,11 +222,8 @@ static cip_status grid_accumulate_staged(cip_ctx* ctx, const DevInputs& in, cons
       CIP_TRY(run_gridder(ctx, 0, ctx->stream, g, fp64, bins.nrec, 0, bins.nitems, ctx->grid.p, pb, used));
       tm.stop(rep ? &rep->ms_grid : &dummy);
       tm.start();
-      CIP_TRY(run_fft(ctx, ctx->grid.p, plan->nu, plan->nv, used, fp64, plan->npix_y));
+      CIP_TRY(run_fft_screen(ctx, *plan, ctx->grid.p, pb, used, image_dev, nullptr, nullptr));
       tm.stop(rep ? &rep->ms_fft : &dummy);
-      tm.start();
-      CIP_TRY(run_wscreen(ctx, *plan, ctx->grid.p, pb, used, image_dev));
-      tm.stop(rep ? &rep->ms_wscreen : &dummy);
       if (rep) rep->nblocks++;
     }
     return CIP_OK;
@@ -258,11 +250,8 @@ static cip_status grid_accumulate_staged(cip_ctx* ctx, const DevInputs& in, cons
       CIP_TRY(run_gridder(ctx, 0, ctx->stream, g, fp64, bins.nrec, it0, it1, ctx->grid.p, pb, used));
       tm.stop(rep ? &rep->ms_grid : &dummy);
       tm.start();
-      CIP_TRY(run_fft(ctx, ctx->grid.p, plan->nu, plan->nv, used, fp64, plan->npix_y));
+      CIP_TRY(run_fft_screen(ctx, *plan, ctx->grid.p, pb, used, image_dev, nullptr, nullptr));
       tm.stop(rep ? &rep->ms_fft : &dummy);
-      tm.start();
-      CIP_TRY(run_wscreen(ctx, *plan, ctx->grid.p, pb, used, image_dev));
-      tm.stop(rep ? &rep->ms_wscreen : &dummy);
       if (rep) rep->nblocks++;
     }
     w = wl + 1;
