@@ -134,12 +134,16 @@ struct CorrectParams {
 template <typename R>
 __global__ void __launch_bounds__(256) correct_kernel(CorrectParams p, const double* __restrict__ tables,
                                                       R* __restrict__ image) {
+  // the Chebyshev coefficients are read by every thread in the same order: shared memory (one broadcast
+  // load each) instead of ncheb global loads per pixel, which bound the kernel
+  __shared__ double ck[64];
+  for (int q = threadIdx.x; q < p.ncheb; q += blockDim.x) ck[q] = tables[p.nx + p.ny + q];
+  __syncthreads();
   const int j = blockIdx.x * blockDim.x + threadIdx.x;
   const int i = p.row_begin + blockIdx.y;
   if (j >= p.ny || i >= p.row_end) return;
   const double* cu = tables;
   const double* cv = tables + p.nx;
-  const double* ck = cv + p.ny;
   const double l = (i - p.nx / 2) * p.px, m = (j - p.ny / 2) * p.py, e = l * l + m * m;
   const size_t k = (size_t)i * p.ny + j;
   if (e >= 1.0) { image[k] = 0; return; }
