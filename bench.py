@@ -37,6 +37,7 @@ sys.path.insert(0, str(ROOT))
 sys.path.insert(0, str(ROOT / "ska-sdp-continuum-imaging-pipeline_b200"))
 
 METRIC = "invert_throughput"
+CPU_SAMPLE_TIMES = 32  # time steps of the workload given to the CPU port (about 10 s on 16 threads)
 UNIT = "Mvis/s"
 
 
@@ -153,7 +154,7 @@ def run_reference(args):
     if rank != 0:
         return
     cfg, px = workload(args.times)
-    sample_times = 4
+    sample_times = CPU_SAMPLE_TIMES
     rates = []
     for _ in range(args.warmup):
         cpu_port_rate(cfg, px, 1)
@@ -317,9 +318,10 @@ def run_b200(args):
     # ---- CPU baseline on a bounded sample -----------------------------------------------------
     cpu = None
     if not args.no_cpu and world == 1:  # rank 0 at N = 1 only
-        r, dt, nv_s, cores = cpu_port_rate(cfg, px, 4)
+        r, dt, nv_s, cores = cpu_port_rate(cfg, px, CPU_SAMPLE_TIMES)
         cpu = {"value": r, "unit": UNIT, "cores": cores, "kind": "port",
-               "sample": f"first 4 of {cfg.n_times} time steps ({nv_s} visibilities), full {N}^2 image, {dt:.1f} s"}
+               "sample": f"first {CPU_SAMPLE_TIMES} of {cfg.n_times} time steps ({nv_s} visibilities), full {N}^2 image, "
+                         f"{dt:.1f} s"}
     total_vis = nvis * world
     line = {
         "metric": METRIC, "value": total_vis * args.steps / ms_dev / 1e3, "unit": UNIT, "n_gpus": world,
