@@ -38,7 +38,7 @@ __device__ __forceinline__ uint64_t load_key(const void* keys, int64_t pos, bool
 //   PASS 2: after the sort, expand the samples into gridder-ready records at their sorted positions
 //           (outpos[r] = first record of input-order run r); all float64 coordinate arithmetic of the
 //           gridder happens here.  Reads are row-contiguous, writes contiguous per run.
-template <int PASS, typename R>
+template <int PASS, typename R, bool PACK = false>
 __global__ void __launch_bounds__(256, 6) runs_kernel(DevInputs in, GridGeom g, int64_t* __restrict__ row_nruns,
                                                    const int64_t* __restrict__ row_off, Run* __restrict__ runs,
                                                    void* __restrict__ keys, const int64_t* __restrict__ outpos,
@@ -114,6 +114,14 @@ __global__ void __launch_bounds__(256, 6) runs_kernel(DevInputs in, GridGeom g, 
             re = t;
           }
         }
+        if constexpr (PACK) {  // float32 register-window gridder: 16-byte record, one 128-bit store
+          RecP rp;
+          rp.geo = (uint64_t)(bc.i0r | (bc.j0r << 3) | (bc.p0r << 6)) | (to_fix18(s.dfu) << 10) | (to_fix18(s.dfv) << 28) |
+                   (to_fix18(s.dfw) << 46);
+          rp.re = (float)re;
+          rp.im = (float)im;
+          *reinterpret_cast<float4*>(reinterpret_cast<RecP*>(recs) + out0 + ((int)c - ch0)) = *reinterpret_cast<const float4*>(&rp);
+        } else {
         Rec<R> rec;
         rec.cell = bc.i0r | (bc.j0r << 5) | (bc.p0r << 10);
         // bits 16-20 / 21-25: origin of the gridder's register window (i0r, j0r snapped to the lattice);
@@ -135,6 +143,7 @@ __global__ void __launch_bounds__(256, 6) runs_kernel(DevInputs in, GridGeom g, 
         const float4* src = reinterpret_cast<const float4*>(&rec);
         dst[0] = src[0];
         dst[1] = src[1];
+        }
       }
       if (m) carry_ch0 = (int)c0 + (31 - __clz(m));
     }
@@ -470,6 +479,9 @@ cip_status run_binning(cip_ctx* ctx, int slot, const DevInputs& in, const GridGe
   if (fp64)
     runs_kernel<2, double><<<rblocks, 256, 0, st>>>(in, g, row_nruns, row_off, nullptr, nullptr, outpos,
                                                     w.recs.as<Rec<double>>(), finv, key32);
+  else if (g.W <= kFastSupport)
+    runs_kernel<2, float, true><<<rblocks, 256, 0, st>>>(in, g, row_nruns, row_off, nullptr, nullptr, outpos,
+                                                         w.recs.as<Rec<float>>(), finv, key32);
   else
     runs_kernel<2, float><<<rblocks, 256, 0, st>>>(in, g, row_nruns, row_off, nullptr, nullptr, outpos,
                                                    w.recs.as<Rec<float>>(), finv, key32);

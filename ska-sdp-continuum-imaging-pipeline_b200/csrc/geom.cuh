@@ -145,6 +145,10 @@ __device__ __forceinline__ double es_kernel(double x, double beta_w) {
   return t >= 0.0 ? exp(beta_w * (sqrt(t) - 1.0)) : 0.0;
 }
 
+__device__ __forceinline__ uint64_t to_fix18(double f) {
+  const uint32_t q = (uint32_t)(f * kFix18 + 0.5);
+  return q > 262143u ? 262143u : q;
+}
 __device__ __forceinline__ uint32_t to_fix32(double f) {
   double v = f * kFix32;
   return v >= 4294967295.0 ? 0xffffffffu : (uint32_t)v;

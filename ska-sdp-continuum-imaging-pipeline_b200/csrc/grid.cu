@@ -81,6 +81,12 @@ __device__ __forceinline__ Rec<R> load_rec(const Rec<R>* __restrict__ recs, int6
   return r;
 }
 
+__device__ __forceinline__ RecP load_recp(const RecP* __restrict__ recs, int64_t k, bool valid) {
+  RecP r;
+  *reinterpret_cast<float4*>(&r) = valid ? __ldg(reinterpret_cast<const float4*>(recs + k)) : make_float4(0.f, 0.f, 0.f, 0.f);
+  return r;
+}
+
 // Register-window origin of a record and the "window moved" mask of the batch (common to both precisions).
 __device__ __forceinline__ uint32_t window_origin(uint32_t cell, bool valid, int lane, uint32_t& carry, int snap,
                                                   uint32_t* moved) {
@@ -543,7 +549,7 @@ __device__ __forceinline__ void warp_consume8(uint32_t pa, uint32_t pb, uint32_t
 // trades ~4x more L2 reductions for 14.4 KB of shared memory per warp, i.e. twice the resident warps.
 template <int NW, bool DIRECT>
 __global__ void __launch_bounds__(32 * NW, DIRECT ? 20 : 1) grid_warp_kernel(const Item* __restrict__ items, int64_t item_base,
-                                                            const Rec<float>* __restrict__ recs, GridGeom g,
+                                                            const RecP* __restrict__ recs, GridGeom g,
                                                             float* __restrict__ grid, int plane_base, int nslots) {
   constexpr int MODE = DIRECT ? 2 : (NW > 1 ? 1 : 0);
   constexpr int kSubBytes = DIRECT ? 0 : kWarpSubGridBytes;
@@ -561,7 +567,7 @@ __global__ void __launch_bounds__(32 * NW, DIRECT ? 20 : 1) grid_warp_kernel(con
   const int64_t base = item.rec_begin;
 
   bool cur_valid = b_begin * kBatch + lane < nrec;
-  Rec<float> cur = load_rec(recs, base + b_begin * kBatch + lane, cur_valid);
+  RecP cur = load_recp(recs, base + b_begin * kBatch + lane, cur_valid);
   if (!DIRECT)
     for (int t = threadIdx.x; t < 4 * kSub * kSub; t += 32 * NW) sg[t] = make_float4(0.f, 0.f, 0.f, 0.f);
   const int P0 = item.win * g.win_step;
@@ -578,6 +584,7 @@ __global__ void __launch_bounds__(32 * NW, DIRECT ? 20 : 1) grid_warp_kernel(con
   const float bw2 = g.beta_w * 1.4426950408889634f;
   const float two_over_w = 2.0f / (float)W;
   const int snap = 9 - W;  // windows of 8 cells hold the supports of `snap` consecutive origins
+  const uint32_t snap_rcp = (256u + snap - 1) / snap;
   const bool wstack = g.do_wstacking != 0;
   uint32_t carry = 0xffffffffu;
   const uint32_t myA = sA + lane * kARow, myB = sB + lane * kBRow;
@@ -594,18 +601,25 @@ __global__ void __launch_bounds__(32 * NW, DIRECT ? 20 : 1) grid_warp_kernel(con
   for (int b = b_begin; b < b_end; ++b) {
     const int kn = (b + 1) * kBatch + lane;
     const bool nxt_valid = kn < nrec;
-    const Rec<float> nxt = load_rec(recs, base + kn, nxt_valid);
+    const RecP nxt = load_recp(recs, base + kn, nxt_valid);
     // ---------------- produce: lane = visibility ----------------
     uint32_t moved;
     {
-      const int i0 = cur.cell & 31, j0 = (cur.cell >> 5) & 31, p0 = (cur.cell >> 10) & 15;
-      const uint32_t cxy = window_origin(cur.cell, cur_valid, lane, carry, snap, &moved);
+      // unpack: origin inside the tile, first plane, 0.18 fixed-point fractions; the register window's origin
+      // is the support origin snapped to the lattice (i / snap by multiplication, exact for i < 8)
+      const uint32_t glo = (uint32_t)cur.geo, ghi = (uint32_t)(cur.geo >> 32);
+      const int i0 = glo & 7, j0 = (glo >> 3) & 7, p0 = (glo >> 6) & 15;
+      const float cur_fu = (float)((glo >> 10) & 0x3ffffu) * (1.0f / 262144.0f);
+      const float cur_fv = (float)((uint32_t)(cur.geo >> 28) & 0x3ffffu) * (1.0f / 262144.0f);
+      const float cur_fw = (float)(ghi >> 14) * (1.0f / 262144.0f);
+      const uint32_t wi = ((i0 * snap_rcp) >> 8) * snap, wj = ((j0 * snap_rcp) >> 8) * snap;
+      const uint32_t cxy = window_origin((wi | (wj << 5)) << 16, cur_valid, lane, carry, snap, &moved);
       // Taps by residue class r: the tap of cell r sits da = (r - i0) mod 8 cells from the first one, at
       // x = (f + da) 2/W - 1; taps outside the support have |x| >= 1 and are masked by the sign of 1 - x^2
       // (branch-free; at |x| = 1 exactly the kernel is exp(-beta W) ~ 1e-7 of its peak, i.e. nothing).
       const float i0f = (float)i0, j0f = (float)j0, p0f = (float)p0;
-      const float xu0 = fmaf(cur.fu - i0f, two_over_w, -1.0f), xv0 = fmaf(cur.fv - j0f, two_over_w, -1.0f);
-      const float xw0 = fmaf(cur.fw - p0f, two_over_w, -1.0f);
+      const float xu0 = fmaf(cur_fu - i0f, two_over_w, -1.0f), xv0 = fmaf(cur_fv - j0f, two_over_w, -1.0f);
+      const float xw0 = fmaf(cur_fw - p0f, two_over_w, -1.0f);
       float ku[8], kv[8], kw[8];
 #pragma unroll
       for (int r = 0; r < 8; ++r) {
@@ -742,7 +756,7 @@ __global__ void __launch_bounds__(128) grid_wide_kernel(const Item* __restrict__
 }
 
 template <int NW, bool DIRECT>
-cip_status launch_warp(cip_ctx* ctx, cudaStream_t stream, const Item* items, int64_t item_begin, int64_t n, const Rec<float>* recs,
+cip_status launch_warp(cip_ctx* ctx, cudaStream_t stream, const Item* items, int64_t item_begin, int64_t n, const RecP* recs,
                        const GridGeom& g, float* grid, int plane_base, int nslots) {
   auto kern = grid_warp_kernel<NW, DIRECT>;
   constexpr int smem = warp_smem_bytes(NW, DIRECT);
@@ -767,10 +781,10 @@ cip_status launch(cip_ctx* ctx, int slot, cudaStream_t stream, const GridGeom& g
       // 10.8 ms on configs[1] against 10.0 ms for the direct fold), CIP_GRID_WARPS=2|4 shares it between warps.
       const int nw = getenv("CIP_GRID_WARPS") ? atoi(getenv("CIP_GRID_WARPS")) : 1;
       const bool direct = getenv("CIP_GRID_DIRECT") ? atoi(getenv("CIP_GRID_DIRECT")) != 0 : true;
-      if (direct) CIP_TRY((launch_warp<1, true>(ctx, stream, items, item_begin, n, recs, g, static_cast<float*>(grid), plane_base, nslots)));
-      else if (nw == 2) CIP_TRY((launch_warp<2, false>(ctx, stream, items, item_begin, n, recs, g, static_cast<float*>(grid), plane_base, nslots)));
-      else if (nw == 4) CIP_TRY((launch_warp<4, false>(ctx, stream, items, item_begin, n, recs, g, static_cast<float*>(grid), plane_base, nslots)));
-      else CIP_TRY((launch_warp<1, false>(ctx, stream, items, item_begin, n, recs, g, static_cast<float*>(grid), plane_base, nslots)));
+      if (direct) CIP_TRY((launch_warp<1, true>(ctx, stream, items, item_begin, n, reinterpret_cast<const RecP*>(recs), g, static_cast<float*>(grid), plane_base, nslots)));
+      else if (nw == 2) CIP_TRY((launch_warp<2, false>(ctx, stream, items, item_begin, n, reinterpret_cast<const RecP*>(recs), g, static_cast<float*>(grid), plane_base, nslots)));
+      else if (nw == 4) CIP_TRY((launch_warp<4, false>(ctx, stream, items, item_begin, n, reinterpret_cast<const RecP*>(recs), g, static_cast<float*>(grid), plane_base, nslots)));
+      else CIP_TRY((launch_warp<1, false>(ctx, stream, items, item_begin, n, reinterpret_cast<const RecP*>(recs), g, static_cast<float*>(grid), plane_base, nslots)));
     } else {
       // float64: producer / consumer warp pair ("residue owner")
       constexpr size_t smem = grid_smem_bytes<R>();
