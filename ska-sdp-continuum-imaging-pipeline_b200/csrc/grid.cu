@@ -7,10 +7,15 @@
 //
 // * float32, grid_warp_kernel ("rank-1 tiles"): one warp per item.  Per batch of 32 visibilities the warp
 //   first evaluates the ES kernel separably (one visibility per lane) and stages the 8 x 8 products
-//   ku kv and the 8 complex plane values V kw in shared memory, then applies the rank-1 update of the
-//   8 x 8 x 8 register window with 16 FFMA2 per lane.  Consecutive visibilities share the window (its
-//   origin is snapped to a lattice of 9-W cells and the records are sorted by lattice position); when
-//   the window moves it is added to the global plane stack with vector reductions.
+//   ku kv and the 8 complex plane values V kw in shared memory, then updates the 8 x 8 x 8 register
+//   window: groups of 8 visibilities that share it go through the tensor cores as C[64 x 16] += A[64 x 8]
+//   B[8 x 16] (mma.sync m16n8k8, every operand split into two TF32 terms, three products per tile, tiles
+//   added in float32 -- accuracy of the FFMA path, see tests/accuracy_modes.py); the group in which the
+//   window moves takes the rank-1 updates with 16 FFMA2 per lane and visibility.  Consecutive visibilities
+//   share the window (its origin is snapped to a lattice of 9-W cells and the records are sorted by
+//   lattice position); when the window moves it is added to the global plane stack with vector reductions.
+//   CIP_GRID_MMA=0 selects FFMA2 for all groups, =2 accumulates inside the tensor core (faster by 0.2 ms,
+//   but its truncating accumulator costs 4x in error on dense tiles at tight kernels).
 //
 // * float64, grid_kernel<double> ("residue owner"): a producer warp evaluates the kernel in float64 and
 //   hands batches to a consumer warp whose lane (a, b) owns the cells u = a, v = b or b+4 (mod 8) of the
@@ -409,17 +414,50 @@ __device__ __forceinline__ void red_add_v2(float* addr, u64 v) {
   asm volatile("red.global.add.v2.f32 [%0], {%1, %2};" ::"l"(addr), "f"(f.x), "f"(f.y) : "memory");
 }
 
+// Row layouts of the operand stage, chosen so that BOTH consumers read them without bank conflicts:
+//   A row (272 B): the four v residues 0..3 of u-row r at 16-byte unit (r >> 1) + 4 (r & 1), residues 4..7
+//     eight units further.  The FFMA path reads one u-row per lane group a (lanes 2i, 2i+1 share the unit:
+//     2 wavefronts per 128-bit load); the tensor path reads the same unit of four DIFFERENT visibilities
+//     (row stride 17 units) for two neighbouring a in a quarter-warp: units pq + {0, 4} mod 8, conflict-free.
+//   B row (80 B = 20 words): value (plane, re|im) = column n of the 8 x 16 operand, n = 8 (plane & 1) +
+//     2 (plane >> 1) + (re|im).  Even planes at words {0..3, 16..19}, odd planes at words 4..11: the word
+//     sets read from the rows of the four visibilities pq (row stride 20 words) are disjoint mod 32.
+__device__ __forceinline__ constexpr int arow_unit(int r) { return (r >> 1) + 4 * (r & 1); }
+
+// Tensor-core update of the register window by 8 visibilities that share it: C[64 x 16] += A[64 x 8] B[8 x 16]
+// as 4 x 2 tiles of mma.m16n8k8 (legacy tensor path, 8 cycles per instruction and sub-partition measured with
+// tools/experiments/mma_rate.cu -- 24 cycles per visibility with the split below, against 32 for the 16
+// half-rate FFMA2).  TF32 operands carry 10 mantissa bits, so every operand is split x = hi + lo with hi the
+// upper 19 bits and the three products lo*hi + hi*lo + hi*hi are accumulated from zero inside the tensor core,
+// smallest first; the tile is then added to the window with IEEE float32 additions (the tensor core's own
+// accumulator truncates).  Error per product ~ 2^-20.  Row m = 16 mt + g + 8 s of A is (u = g, v = 2 mt + s), so
+// lane 4 g + t holds exactly the accumulators of the FFMA path (a = g, pq = t) and the folds are shared.
+__device__ __forceinline__ void tf32_split(float x, uint32_t& hi, uint32_t& lo) {
+  hi = __float_as_uint(x) & 0xffffe000u;
+  lo = __float_as_uint(x - __uint_as_float(hi));
+}
+__device__ __forceinline__ void mma_tf32(float (&d)[4], const uint32_t (&a)[4], uint32_t b0, uint32_t b1) {
+  asm("mma.sync.aligned.m16n8k8.row.col.f32.tf32.tf32.f32 {%0,%1,%2,%3}, {%4,%5,%6,%7}, {%8,%9}, {%0,%1,%2,%3};"
+               : "+f"(d[0]), "+f"(d[1]), "+f"(d[2]), "+f"(d[3])
+               : "r"(a[0]), "r"(a[1]), "r"(a[2]), "r"(a[3]), "r"(b0), "r"(b1));
+}
+__device__ __forceinline__ float lds_f32(uint32_t addr) {
+  float v;
+  asm volatile("ld.shared.f32 %0, [%1];" : "=f"(v) : "r"(addr));
+  return v;
+}
+
 struct WarpOps {
   float4 a0, a1;
   u64 b0, b1;
 };
 template <int U>
-__device__ __forceinline__ WarpOps warp_load(uint32_t pa, uint32_t pb) {
+__device__ __forceinline__ WarpOps warp_load(uint32_t pa, uint32_t pb, uint32_t pb1) {
   WarpOps o;
-  o.a0 = lds_f4<U * kARow>(pa);
-  o.a1 = lds_f4<U * kARow + 16>(pa);
-  o.b0 = lds_u1<U * kBRow>(pb);  // B row = [h][pq]: plane 2pq + h at h*32 + pq*8, so that the two loads are
-  o.b1 = lds_u1<U * kBRow + 32>(pb);  // not fused into one 128-bit load (4 wavefronts instead of 1 + 1)
+  o.a0 = lds_f4<U * kARow>(pa);        // A row: v residues 0..3 of u-row a at 16 arow_unit(a), 4..7 at + 128
+  o.a1 = lds_f4<U * kARow + 128>(pa);
+  o.b0 = lds_u1<U * kBRow>(pb);        // plane 2pq     (pb = row + brow_even(pq))
+  o.b1 = lds_u1<U * kBRow>(pb1);       // plane 2pq + 1 (pb1 = row + 16 + 8 pq)
   return o;
 }
 
@@ -437,6 +475,84 @@ struct WarpAcc {
       ffma2(c[t][0], ad, o.b0);
       ffma2(c[t][1], ad, o.b1);
     }
+  }
+  // pam: A unit of this lane's u-row in the row of visibility pq of the group; pbm0 / pbm1: this lane's column
+  // (n = a) of the even / odd plane block in the same row.  Visibility pq + 4 sits four rows further.
+  __device__ __forceinline__ void update_mma(uint32_t pam, uint32_t pbm0, uint32_t pbm1) {
+    const float4 p0 = lds_f4<0>(pam), p1 = lds_f4<128>(pam);
+    const float4 q0 = lds_f4<4 * kARow>(pam), q1 = lds_f4<4 * kARow + 128>(pam);
+    uint32_t bh[2][2], bl[2][2];
+    tf32_split(lds_f32(pbm0), bh[0][0], bl[0][0]);
+    tf32_split(lds_f32(pbm0 + 4 * kBRow), bh[0][1], bl[0][1]);
+    tf32_split(lds_f32(pbm1), bh[1][0], bl[1][0]);
+    tf32_split(lds_f32(pbm1 + 4 * kBRow), bh[1][1], bl[1][1]);
+    const float pv[8] = {p0.x, p0.y, p0.z, p0.w, p1.x, p1.y, p1.z, p1.w};
+    const float qv[8] = {q0.x, q0.y, q0.z, q0.w, q1.x, q1.y, q1.z, q1.w};
+#pragma unroll
+    for (int mt = 0; mt < 4; ++mt) {
+      uint32_t ah[4], al[4];
+      tf32_split(pv[2 * mt], ah[0], al[0]);
+      tf32_split(pv[2 * mt + 1], ah[1], al[1]);
+      tf32_split(qv[2 * mt], ah[2], al[2]);
+      tf32_split(qv[2 * mt + 1], ah[3], al[3]);
+#pragma unroll
+      for (int nt = 0; nt < 2; ++nt) {
+        float d[4] = {0.f, 0.f, 0.f, 0.f};
+        mma_tf32(d, al, bh[nt][0], bh[nt][1]);
+        mma_tf32(d, ah, bl[nt][0], bl[nt][1]);
+        mma_tf32(d, ah, bh[nt][0], bh[nt][1]);
+        const float2 x = unpack2(c[2 * mt][nt]), y = unpack2(c[2 * mt + 1][nt]);
+        c[2 * mt][nt] = pack2(x.x + d[0], x.y + d[1]);
+        c[2 * mt + 1][nt] = pack2(y.x + d[2], y.y + d[3]);
+      }
+    }
+  }
+  // Same update with the window accumulated inside the tensor core (no float32 additions): term-major order,
+  // so that the three instructions of a tile are 8 instructions apart.  The tensor core truncates its
+  // accumulator: measured against the FADD variant with tests/accuracy_modes.py.
+  __device__ __forceinline__ void update_mma_direct(uint32_t pam, uint32_t pbm0, uint32_t pbm1) {
+    const float4 p0 = lds_f4<0>(pam), p1 = lds_f4<128>(pam);
+    const float4 q0 = lds_f4<4 * kARow>(pam), q1 = lds_f4<4 * kARow + 128>(pam);
+    uint32_t bh[2][2], bl[2][2];
+    tf32_split(lds_f32(pbm0), bh[0][0], bl[0][0]);
+    tf32_split(lds_f32(pbm0 + 4 * kBRow), bh[0][1], bl[0][1]);
+    tf32_split(lds_f32(pbm1), bh[1][0], bl[1][0]);
+    tf32_split(lds_f32(pbm1 + 4 * kBRow), bh[1][1], bl[1][1]);
+    const float pv[8] = {p0.x, p0.y, p0.z, p0.w, p1.x, p1.y, p1.z, p1.w};
+    const float qv[8] = {q0.x, q0.y, q0.z, q0.w, q1.x, q1.y, q1.z, q1.w};
+    uint32_t ah[4][4], al[4][4];
+#pragma unroll
+    for (int mt = 0; mt < 4; ++mt) {
+      tf32_split(pv[2 * mt], ah[mt][0], al[mt][0]);
+      tf32_split(pv[2 * mt + 1], ah[mt][1], al[mt][1]);
+      tf32_split(qv[2 * mt], ah[mt][2], al[mt][2]);
+      tf32_split(qv[2 * mt + 1], ah[mt][3], al[mt][3]);
+    }
+    float d[4][2][4];
+#pragma unroll
+    for (int mt = 0; mt < 4; ++mt)
+#pragma unroll
+      for (int nt = 0; nt < 2; ++nt) {
+        const float2 x = unpack2(c[2 * mt][nt]), y = unpack2(c[2 * mt + 1][nt]);
+        d[mt][nt][0] = x.x; d[mt][nt][1] = x.y; d[mt][nt][2] = y.x; d[mt][nt][3] = y.y;
+      }
+#pragma unroll
+    for (int term = 0; term < 3; ++term)
+#pragma unroll
+      for (int mt = 0; mt < 4; ++mt)
+#pragma unroll
+        for (int nt = 0; nt < 2; ++nt) {
+          if (term == 0) mma_tf32(d[mt][nt], al[mt], bh[nt][0], bh[nt][1]);
+          else if (term == 1) mma_tf32(d[mt][nt], ah[mt], bl[nt][0], bl[nt][1]);
+          else mma_tf32(d[mt][nt], ah[mt], bh[nt][0], bh[nt][1]);
+        }
+#pragma unroll
+    for (int mt = 0; mt < 4; ++mt)
+#pragma unroll
+      for (int nt = 0; nt < 2; ++nt) {
+        c[2 * mt][nt] = pack2(d[mt][nt][0], d[mt][nt][1]);
+        c[2 * mt + 1][nt] = pack2(d[mt][nt][2], d[mt][nt][3]);
+      }
   }
   // sub-grid cell = float4 {re(2pp), im(2pp), re(2pp+1), im(2pp+1)} for plane pair pp = pq: one float4
   // read-modify-write per owned cell (the lane owns row i, all 8 v residues of the window)
@@ -518,9 +634,9 @@ struct WarpCells {
 };
 
 template <int U, bool CHECK, int MODE>
-__device__ __forceinline__ void warp_consume1(uint32_t pa, uint32_t pb, uint32_t porg, uint32_t moved8, const WarpOps& cur,
+__device__ __forceinline__ void warp_consume1(uint32_t pa, uint32_t pb, uint32_t pb1, uint32_t porg, uint32_t moved8, const WarpOps& cur,
                                               WarpOps& nxt, WarpAcc& acc, const FoldSink& sg, WarpCells& cells, int a, int pq) {
-  nxt = warp_load<U + 1>(pa, pb);
+  nxt = warp_load<U + 1>(pa, pb, pb1);
   if (CHECK && ((moved8 >> U) & 1u)) {
     acc.template fold<MODE>(sg, cells.i, cells.wj, pq);
     cells.set(lds_u32(porg + 4 * U), a);
@@ -528,17 +644,17 @@ __device__ __forceinline__ void warp_consume1(uint32_t pa, uint32_t pb, uint32_t
   acc.update(cur);
 }
 template <bool CHECK, int MODE>
-__device__ __forceinline__ void warp_consume8(uint32_t pa, uint32_t pb, uint32_t porg, uint32_t moved8, WarpOps& x, WarpAcc& acc,
+__device__ __forceinline__ void warp_consume8(uint32_t pa, uint32_t pb, uint32_t pb1, uint32_t porg, uint32_t moved8, WarpOps& x, WarpAcc& acc,
                                               const FoldSink& sg, WarpCells& cells, int a, int pq) {
   WarpOps y;
-  warp_consume1<0, CHECK, MODE>(pa, pb, porg, moved8, x, y, acc, sg, cells, a, pq);
-  warp_consume1<1, CHECK, MODE>(pa, pb, porg, moved8, y, x, acc, sg, cells, a, pq);
-  warp_consume1<2, CHECK, MODE>(pa, pb, porg, moved8, x, y, acc, sg, cells, a, pq);
-  warp_consume1<3, CHECK, MODE>(pa, pb, porg, moved8, y, x, acc, sg, cells, a, pq);
-  warp_consume1<4, CHECK, MODE>(pa, pb, porg, moved8, x, y, acc, sg, cells, a, pq);
-  warp_consume1<5, CHECK, MODE>(pa, pb, porg, moved8, y, x, acc, sg, cells, a, pq);
-  warp_consume1<6, CHECK, MODE>(pa, pb, porg, moved8, x, y, acc, sg, cells, a, pq);
-  warp_consume1<7, CHECK, MODE>(pa, pb, porg, moved8, y, x, acc, sg, cells, a, pq);
+  warp_consume1<0, CHECK, MODE>(pa, pb, pb1, porg, moved8, x, y, acc, sg, cells, a, pq);
+  warp_consume1<1, CHECK, MODE>(pa, pb, pb1, porg, moved8, y, x, acc, sg, cells, a, pq);
+  warp_consume1<2, CHECK, MODE>(pa, pb, pb1, porg, moved8, x, y, acc, sg, cells, a, pq);
+  warp_consume1<3, CHECK, MODE>(pa, pb, pb1, porg, moved8, y, x, acc, sg, cells, a, pq);
+  warp_consume1<4, CHECK, MODE>(pa, pb, pb1, porg, moved8, x, y, acc, sg, cells, a, pq);
+  warp_consume1<5, CHECK, MODE>(pa, pb, pb1, porg, moved8, y, x, acc, sg, cells, a, pq);
+  warp_consume1<6, CHECK, MODE>(pa, pb, pb1, porg, moved8, x, y, acc, sg, cells, a, pq);
+  warp_consume1<7, CHECK, MODE>(pa, pb, pb1, porg, moved8, y, x, acc, sg, cells, a, pq);
 }
 
 // NW warps per CTA share the item and its sub-grid: warp w takes the w-th contiguous share of the
@@ -547,7 +663,7 @@ __device__ __forceinline__ void warp_consume8(uint32_t pa, uint32_t pb, uint32_t
 // DIRECT: no sub-grid at all -- every register window is added to the global plane stack when the warp
 // leaves it (the records are sorted by window, so that happens ~ once per lattice position and item).  This
 // trades ~4x more L2 reductions for 14.4 KB of shared memory per warp, i.e. twice the resident warps.
-template <int NW, bool DIRECT>
+template <int NW, bool DIRECT, int MMA>
 __global__ void __launch_bounds__(32 * NW, DIRECT ? 20 : 1) grid_warp_kernel(const Item* __restrict__ items, int64_t item_base,
                                                             const RecP* __restrict__ recs, GridGeom g,
                                                             float* __restrict__ grid, int plane_base, int nslots) {
@@ -590,7 +706,10 @@ __global__ void __launch_bounds__(32 * NW, DIRECT ? 20 : 1) grid_warp_kernel(con
   const uint32_t myA = sA + lane * kARow, myB = sB + lane * kBRow;
   // consumer constants
   const int a = lane >> 2, pq = lane & 3;
-  const uint32_t pa0 = sA + a * 32, pb0 = sB + pq * 8;
+  const uint32_t pa0 = sA + 16 * arow_unit(a), pb0 = sB + (pq < 2 ? pq * 8 : 48 + pq * 8), pb10 = sB + 16 + pq * 8;
+  // tensor path: rows of visibilities pq and pq + 4 of a group, column n = a of the B blocks
+  const uint32_t pam0 = pa0 + pq * kARow;
+  const uint32_t pbm00 = sB + pq * kBRow + 4 * (a < 4 ? a : 12 + a), pbm10 = sB + pq * kBRow + 4 * (4 + a);
   WarpAcc acc;
   acc.clear();
   WarpCells cells;
@@ -630,36 +749,40 @@ __global__ void __launch_bounds__(32 * NW, DIRECT ? 20 : 1) grid_warp_kernel(con
       }
 #pragma unroll
       for (int r = 0; r < 8; ++r) {
-        sts_f4(myA + r * 32, ku[r] * kv[0], ku[r] * kv[1], ku[r] * kv[2], ku[r] * kv[3]);
-        sts_f4(myA + r * 32 + 16, ku[r] * kv[4], ku[r] * kv[5], ku[r] * kv[6], ku[r] * kv[7]);
+        sts_f4(myA + 16 * arow_unit(r), ku[r] * kv[0], ku[r] * kv[1], ku[r] * kv[2], ku[r] * kv[3]);
+        sts_f4(myA + 16 * arow_unit(r) + 128, ku[r] * kv[4], ku[r] * kv[5], ku[r] * kv[6], ku[r] * kv[7]);
       }
       const float re = cur_valid ? cur.re : 0.0f, im = cur_valid ? cur.im : 0.0f;
 #pragma unroll
       for (int q = 0; q < 8; q += 4) {
-        sts_f4(myB + q * 4, re * kw[q], im * kw[q], re * kw[q + 2], im * kw[q + 2]);                    // even planes
-        sts_f4(myB + 32 + q * 4, re * kw[q + 1], im * kw[q + 1], re * kw[q + 3], im * kw[q + 3]);  // odd planes
+        sts_f4(myB + q * 16, re * kw[q], im * kw[q], re * kw[q + 2], im * kw[q + 2]);                       // even planes
+        sts_f4(myB + 16 + q * 4, re * kw[q + 1], im * kw[q + 1], re * kw[q + 3], im * kw[q + 3]);  // odd planes
       }
       asm volatile("st.shared.u32 [%0], %1;" ::"r"(sOrg + 4 * lane), "r"(cxy) : "memory");
     }
     __syncwarp();
     // ---------------- consume: lane = (a, bh, ph) ----------------
     {
-      WarpOps x = warp_load<0>(pa0, pb0);
+      WarpOps x;
+      if (!MMA) x = warp_load<0>(pa0, pb0, pb10);
 #pragma unroll 1
       for (int k0 = 0; k0 < kBatch; k0 += 8) {
-        const uint32_t pa = pa0 + k0 * kARow, pb = pb0 + k0 * kBRow, porg = sOrg + 4 * k0;
+        const uint32_t pa = pa0 + k0 * kARow, pb = pb0 + k0 * kBRow, pb1 = pb10 + k0 * kBRow, porg = sOrg + 4 * k0;
         const uint32_t m8 = (moved >> k0) & 0xffu;
         // most groups stay inside one register window: branch-free fast path.  The operands of visibility
         // k0 + 8 are prefetched at the end of a group; past the last group that reads the rows after the
         // stage (still inside the CTA's shared memory: kSlack), which are discarded.
         if (m8 == 0) {
-          warp_consume8<false, MODE>(pa, pb, porg, m8, x, acc, sink, cells, a, pq);
+          if (MMA == 2) acc.update_mma_direct(pam0 + k0 * kARow, pbm00 + k0 * kBRow, pbm10 + k0 * kBRow);
+          else if (MMA) acc.update_mma(pam0 + k0 * kARow, pbm00 + k0 * kBRow, pbm10 + k0 * kBRow);
+          else warp_consume8<false, MODE>(pa, pb, pb1, porg, m8, x, acc, sink, cells, a, pq);
         } else {
+          if (MMA) x = warp_load<0>(pa, pb, pb1);
           // a window moves inside this group (rare): rolled loop, so that the fold is not inlined eight times
           // (the unrolled variant doubled the code size and a third of the stalls were instruction fetches)
 #pragma unroll 1
           for (int u = 0; u < 8; ++u) {
-            const WarpOps nxt = warp_load<1>(pa + u * kARow, pb + u * kBRow);
+            const WarpOps nxt = warp_load<1>(pa + u * kARow, pb + u * kBRow, pb1 + u * kBRow);
             if ((m8 >> u) & 1u) {
               acc.template fold<MODE>(sink, cells.i, cells.wj, pq);
               cells.set(lds_u32(porg + 4 * u), a);
@@ -755,10 +878,10 @@ __global__ void __launch_bounds__(128) grid_wide_kernel(const Item* __restrict__
   }
 }
 
-template <int NW, bool DIRECT>
+template <int NW, bool DIRECT, int MMA = 0>
 cip_status launch_warp(cip_ctx* ctx, cudaStream_t stream, const Item* items, int64_t item_begin, int64_t n, const RecP* recs,
                        const GridGeom& g, float* grid, int plane_base, int nslots) {
-  auto kern = grid_warp_kernel<NW, DIRECT>;
+  auto kern = grid_warp_kernel<NW, DIRECT, MMA>;
   constexpr int smem = warp_smem_bytes(NW, DIRECT);
   CIP_CHECK_CUDA(cudaFuncSetAttribute(kern, cudaFuncAttributeMaxDynamicSharedMemorySize, smem));
   CIP_CHECK_CUDA(cudaFuncSetAttribute(kern, cudaFuncAttributePreferredSharedMemoryCarveout, (int)cudaSharedmemCarveoutMaxShared));
@@ -781,7 +904,10 @@ cip_status launch(cip_ctx* ctx, int slot, cudaStream_t stream, const GridGeom& g
       // 10.8 ms on configs[1] against 10.0 ms for the direct fold), CIP_GRID_WARPS=2|4 shares it between warps.
       const int nw = getenv("CIP_GRID_WARPS") ? atoi(getenv("CIP_GRID_WARPS")) : 1;
       const bool direct = getenv("CIP_GRID_DIRECT") ? atoi(getenv("CIP_GRID_DIRECT")) != 0 : true;
-      if (direct) CIP_TRY((launch_warp<1, true>(ctx, stream, items, item_begin, n, reinterpret_cast<const RecP*>(recs), g, static_cast<float*>(grid), plane_base, nslots)));
+      const int mma = getenv("CIP_GRID_MMA") ? atoi(getenv("CIP_GRID_MMA")) : 1;
+      if (direct && mma == 2) CIP_TRY((launch_warp<1, true, 2>(ctx, stream, items, item_begin, n, reinterpret_cast<const RecP*>(recs), g, static_cast<float*>(grid), plane_base, nslots)));
+      else if (direct && mma) CIP_TRY((launch_warp<1, true, 1>(ctx, stream, items, item_begin, n, reinterpret_cast<const RecP*>(recs), g, static_cast<float*>(grid), plane_base, nslots)));
+      else if (direct) CIP_TRY((launch_warp<1, true>(ctx, stream, items, item_begin, n, reinterpret_cast<const RecP*>(recs), g, static_cast<float*>(grid), plane_base, nslots)));
       else if (nw == 2) CIP_TRY((launch_warp<2, false>(ctx, stream, items, item_begin, n, reinterpret_cast<const RecP*>(recs), g, static_cast<float*>(grid), plane_base, nslots)));
       else if (nw == 4) CIP_TRY((launch_warp<4, false>(ctx, stream, items, item_begin, n, reinterpret_cast<const RecP*>(recs), g, static_cast<float*>(grid), plane_base, nslots)));
       else CIP_TRY((launch_warp<1, false>(ctx, stream, items, item_begin, n, reinterpret_cast<const RecP*>(recs), g, static_cast<float*>(grid), plane_base, nslots)));

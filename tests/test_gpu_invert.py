@@ -284,9 +284,11 @@ def _with_env(name, value, fn):
 
 
 @pytest.mark.parametrize("env", [("CIP_GRID_DIRECT", "0"), ("CIP_GRID_WARPS", "2"), ("CIP_BIN_TWO_PASS", "1"),
-                                 ("CIP_DEVICE_CHUNKS", "3"), ("CIP_FFT_2D", "1")])
+                                 ("CIP_DEVICE_CHUNKS", "3"), ("CIP_FFT_2D", "1"), ("CIP_GRID_MMA", "0"),
+                                 ("CIP_GRID_MMA", "2")])
 def test_kernel_variants_agree(wg, small, env):
-    """The measured alternatives kept behind environment switches -- register windows folded through a
+    """The measured alternatives kept behind environment switches -- FFMA2 rank-1 updates (0) or tensor-core
+    accumulation (2) instead of 3xTF32 tiles added in float32, register windows folded through a
     shared sub-grid (one or two warps per item) instead of straight into the plane stack, runs counted and
     written in two passes instead of one, device inputs cut into chunks that are binned and gridded on two
     streams, cuFFT's 2-D plan and one w-screen pass instead of the per-plane transposed transform -- compute
