@@ -433,13 +433,19 @@ __device__ __forceinline__ constexpr int arow_unit(int r) { return (r >> 1) + 4 
 // accumulator truncates).  Error per product ~ 2^-20.  Row m = 16 mt + g + 8 s of A is (u = g, v = 2 mt + s), so
 // lane 4 g + t holds exactly the accumulators of the FFMA path (a = g, pq = t) and the folds are shared.
 __device__ __forceinline__ void tf32_split(float x, uint32_t& hi, uint32_t& lo) {
-  hi = __float_as_uint(x) & 0xffffe000u;
-  lo = __float_as_uint(x - __uint_as_float(hi));
+  hi = __float_as_uint(x);  // the tensor core reads the upper 19 bits only
+  lo = __float_as_uint(x - __uint_as_float(hi & 0xffffe000u));
 }
 __device__ __forceinline__ void mma_tf32(float (&d)[4], const uint32_t (&a)[4], uint32_t b0, uint32_t b1) {
   asm("mma.sync.aligned.m16n8k8.row.col.f32.tf32.tf32.f32 {%0,%1,%2,%3}, {%4,%5,%6,%7}, {%8,%9}, {%0,%1,%2,%3};"
                : "+f"(d[0]), "+f"(d[1]), "+f"(d[2]), "+f"(d[3])
                : "r"(a[0]), "r"(a[1]), "r"(a[2]), "r"(a[3]), "r"(b0), "r"(b1));
+}
+template <int OFF>
+__device__ __forceinline__ float2 lds_f2(uint32_t addr) {
+  float2 v;
+  asm volatile("ld.shared.v2.f32 {%0, %1}, [%2+%3];" : "=f"(v.x), "=f"(v.y) : "r"(addr), "n"(OFF));
+  return v;
 }
 __device__ __forceinline__ float lds_f32(uint32_t addr) {
   float v;
@@ -478,23 +484,26 @@ struct WarpAcc {
   }
   // pam: A unit of this lane's u-row in the row of visibility pq of the group; pbm0 / pbm1: this lane's column
   // (n = a) of the even / odd plane block in the same row.  Visibility pq + 4 sits four rows further.
-  __device__ __forceinline__ void update_mma(uint32_t pam, uint32_t pbm0, uint32_t pbm1) {
-    const float4 p0 = lds_f4<0>(pam), p1 = lds_f4<128>(pam);
-    const float4 q0 = lds_f4<4 * kARow>(pam), q1 = lds_f4<4 * kARow + 128>(pam);
+  __device__ __forceinline__ void update_mma(uint32_t pam, uint32_t pam8, uint32_t pbm0, uint32_t pbm1) {
+    // 64-bit loads: the pair (v = 2 mt, 2 mt + 1) of visibility pq and the same pair of visibility pq + 4 land
+    // in one aligned register quad = the A fragment of tile mt, with no register moves (128-bit loads of one
+    // visibility's row cost 16 moves per group to regroup); 2-way bank conflicts are the price
+    // (pam8 = pam + 8 through a value ptxas cannot see, or it fuses the neighbours back into 128-bit loads)
+    const float2 pp[4] = {lds_f2<0>(pam), lds_f2<0>(pam8), lds_f2<128>(pam), lds_f2<128>(pam8)};
+    const float2 qq[4] = {lds_f2<4 * kARow>(pam), lds_f2<4 * kARow>(pam8), lds_f2<4 * kARow + 128>(pam),
+                          lds_f2<4 * kARow + 128>(pam8)};
     uint32_t bh[2][2], bl[2][2];
     tf32_split(lds_f32(pbm0), bh[0][0], bl[0][0]);
     tf32_split(lds_f32(pbm0 + 4 * kBRow), bh[0][1], bl[0][1]);
     tf32_split(lds_f32(pbm1), bh[1][0], bl[1][0]);
     tf32_split(lds_f32(pbm1 + 4 * kBRow), bh[1][1], bl[1][1]);
-    const float pv[8] = {p0.x, p0.y, p0.z, p0.w, p1.x, p1.y, p1.z, p1.w};
-    const float qv[8] = {q0.x, q0.y, q0.z, q0.w, q1.x, q1.y, q1.z, q1.w};
 #pragma unroll
     for (int mt = 0; mt < 4; ++mt) {
       uint32_t ah[4], al[4];
-      tf32_split(pv[2 * mt], ah[0], al[0]);
-      tf32_split(pv[2 * mt + 1], ah[1], al[1]);
-      tf32_split(qv[2 * mt], ah[2], al[2]);
-      tf32_split(qv[2 * mt + 1], ah[3], al[3]);
+      tf32_split(pp[mt].x, ah[0], al[0]);
+      tf32_split(pp[mt].y, ah[1], al[1]);
+      tf32_split(qq[mt].x, ah[2], al[2]);
+      tf32_split(qq[mt].y, ah[3], al[3]);
 #pragma unroll
       for (int nt = 0; nt < 2; ++nt) {
         float d[4] = {0.f, 0.f, 0.f, 0.f};
@@ -708,7 +717,7 @@ __global__ void __launch_bounds__(32 * NW, DIRECT ? 20 : 1) grid_warp_kernel(con
   const int a = lane >> 2, pq = lane & 3;
   const uint32_t pa0 = sA + 16 * arow_unit(a), pb0 = sB + (pq < 2 ? pq * 8 : 48 + pq * 8), pb10 = sB + 16 + pq * 8;
   // tensor path: rows of visibilities pq and pq + 4 of a group, column n = a of the B blocks
-  const uint32_t pam0 = pa0 + pq * kARow;
+  const uint32_t pam0 = pa0 + pq * kARow, pam80 = pam0 + 8 + (g.W >> 4);  // W <= 8: + 8
   const uint32_t pbm00 = sB + pq * kBRow + 4 * (a < 4 ? a : 12 + a), pbm10 = sB + pq * kBRow + 4 * (4 + a);
   WarpAcc acc;
   acc.clear();
@@ -774,7 +783,7 @@ __global__ void __launch_bounds__(32 * NW, DIRECT ? 20 : 1) grid_warp_kernel(con
         // stage (still inside the CTA's shared memory: kSlack), which are discarded.
         if (m8 == 0) {
           if (MMA == 2) acc.update_mma_direct(pam0 + k0 * kARow, pbm00 + k0 * kBRow, pbm10 + k0 * kBRow);
-          else if (MMA) acc.update_mma(pam0 + k0 * kARow, pbm00 + k0 * kBRow, pbm10 + k0 * kBRow);
+          else if (MMA) acc.update_mma(pam0 + k0 * kARow, pam80 + k0 * kARow, pbm00 + k0 * kBRow, pbm10 + k0 * kBRow);
           else warp_consume8<false, MODE>(pa, pb, pb1, porg, m8, x, acc, sink, cells, a, pq);
         } else {
           if (MMA) x = warp_load<0>(pa, pb, pb1);
