@@ -339,7 +339,7 @@ def run_b200(args):
                              ("ms_h2d", "ms_scan", "ms_bin", "ms_grid", "ms_fft", "ms_d2h", "ms_total")}
                 if host_reports else None},
         "gpu_launches": int(launches),
-        "roofline": {"bound": "hbm", "kernel": "grid_warp_kernel<1, true>", "achieved": achieved, "peak": peak,
+        "roofline": {"bound": "hbm", "kernel": "grid_warp_kernel<1, true, 1>", "achieved": achieved, "peak": peak,
                      "unit": "GB/s", "frac": achieved / peak, "traffic": ncu_traffic(), "peak_source": peak_kind,
                      "ms_per_launch": ms_grid, "algorithmic_bytes": int(alg_bytes)},
         "stage_ms": stage,

@@ -351,8 +351,15 @@ __global__ void __launch_bounds__(kGridThreads) grid_kernel(const Item* __restri
 constexpr int kARow = 64 * 4 + 16;  // bytes per visibility of the A stage; the pad makes the producer's
 constexpr int kBRow = 16 * 4 + 16;  // 128-bit stores (one row per lane) bank-conflict free
 constexpr int kWarpSubGridBytes = 16 * 4 * kSub * kSub;
-constexpr int kWarpStageBytes = kBatch * (kARow + kBRow + 4);
-constexpr int warp_smem_bytes(int nw, bool direct) { return (direct ? 0 : kWarpSubGridBytes) + nw * kWarpStageBytes; }
+// The tensor-path kernels stage the FACTORS ku[8], kv[8] instead of their 64 products (80 instead of 272 bytes per
+// visibility; the consumer multiplies the 16 products of its fragment itself -- the FMA pipe has room once the
+// window update is on the tensor pipe, the shared-memory pipe does not).  Factor row, in words: ku[0..3] at 0..3,
+// kv[0..7] at 4..11, ku[4..7] at 16..19 -- the same bank argument as for the B row.
+constexpr int kKRow = 80;
+constexpr int warp_stage_bytes(bool fact) { return kBatch * ((fact ? kKRow : kARow) + kBRow + 4); }
+constexpr int warp_smem_bytes(int nw, bool direct, bool fact) {
+  return (direct ? 0 : kWarpSubGridBytes) + nw * warp_stage_bytes(fact);
+}
 
 template <int OFF>
 __device__ __forceinline__ float4 lds_f4(uint32_t addr) {
@@ -457,11 +464,19 @@ struct WarpOps {
   float4 a0, a1;
   u64 b0, b1;
 };
-template <int U>
-__device__ __forceinline__ WarpOps warp_load(uint32_t pa, uint32_t pb, uint32_t pb1) {
+template <int U, bool FACT>
+__device__ __forceinline__ WarpOps warp_load(uint32_t pa, uint32_t pkv, uint32_t pb, uint32_t pb1) {
   WarpOps o;
-  o.a0 = lds_f4<U * kARow>(pa);        // A row: v residues 0..3 of u-row a at 16 arow_unit(a), 4..7 at + 128
-  o.a1 = lds_f4<U * kARow + 128>(pa);
+  if (FACT) {  // pa: this lane's ku word, pkv: kv[0] of the same row
+    const float ku = lds_f32(pa + U * kKRow);
+    o.a0 = lds_f4<U * kKRow>(pkv);
+    o.a1 = lds_f4<U * kKRow + 16>(pkv);
+    o.a0.x *= ku; o.a0.y *= ku; o.a0.z *= ku; o.a0.w *= ku;
+    o.a1.x *= ku; o.a1.y *= ku; o.a1.z *= ku; o.a1.w *= ku;
+  } else {
+    o.a0 = lds_f4<U * kARow>(pa);        // A row: v residues 0..3 of u-row a at 16 arow_unit(a), 4..7 at + 128
+    o.a1 = lds_f4<U * kARow + 128>(pa);
+  }
   o.b0 = lds_u1<U * kBRow>(pb);        // plane 2pq     (pb = row + brow_even(pq))
   o.b1 = lds_u1<U * kBRow>(pb1);       // plane 2pq + 1 (pb1 = row + 16 + 8 pq)
   return o;
@@ -484,14 +499,21 @@ struct WarpAcc {
   }
   // pam: A unit of this lane's u-row in the row of visibility pq of the group; pbm0 / pbm1: this lane's column
   // (n = a) of the even / odd plane block in the same row.  Visibility pq + 4 sits four rows further.
-  __device__ __forceinline__ void update_mma(uint32_t pam, uint32_t pam8, uint32_t pbm0, uint32_t pbm1) {
-    // 64-bit loads: the pair (v = 2 mt, 2 mt + 1) of visibility pq and the same pair of visibility pq + 4 land
-    // in one aligned register quad = the A fragment of tile mt, with no register moves (128-bit loads of one
-    // visibility's row cost 16 moves per group to regroup); 2-way bank conflicts are the price
-    // (pam8 = pam + 8 through a value ptxas cannot see, or it fuses the neighbours back into 128-bit loads)
-    const float2 pp[4] = {lds_f2<0>(pam), lds_f2<0>(pam8), lds_f2<128>(pam), lds_f2<128>(pam8)};
-    const float2 qq[4] = {lds_f2<4 * kARow>(pam), lds_f2<4 * kARow>(pam8), lds_f2<4 * kARow + 128>(pam),
-                          lds_f2<4 * kARow + 128>(pam8)};
+  // Products of this lane's fragment rows for the visibilities pq and pq + 4 of a group: pam = factor row of
+  // visibility pq, kuoff = byte offset of ku[a] in it.  The products are born in the registers the A fragments
+  // need (aligned quads), so nothing is moved.
+  __device__ __forceinline__ static void load_products(uint32_t pam, uint32_t kuoff, float (&pv)[8], float (&qv)[8]) {
+    const float kup = lds_f32(pam + kuoff), kuq = lds_f32(pam + kuoff + 4 * kKRow);
+    const float4 p0 = lds_f4<16>(pam), p1 = lds_f4<32>(pam);
+    const float4 q0 = lds_f4<4 * kKRow + 16>(pam), q1 = lds_f4<4 * kKRow + 32>(pam);
+    pv[0] = kup * p0.x; pv[1] = kup * p0.y; pv[2] = kup * p0.z; pv[3] = kup * p0.w;
+    pv[4] = kup * p1.x; pv[5] = kup * p1.y; pv[6] = kup * p1.z; pv[7] = kup * p1.w;
+    qv[0] = kuq * q0.x; qv[1] = kuq * q0.y; qv[2] = kuq * q0.z; qv[3] = kuq * q0.w;
+    qv[4] = kuq * q1.x; qv[5] = kuq * q1.y; qv[6] = kuq * q1.z; qv[7] = kuq * q1.w;
+  }
+  __device__ __forceinline__ void update_mma(uint32_t pam, uint32_t kuoff, uint32_t pbm0, uint32_t pbm1) {
+    float pv[8], qv[8];
+    load_products(pam, kuoff, pv, qv);
     uint32_t bh[2][2], bl[2][2];
     tf32_split(lds_f32(pbm0), bh[0][0], bl[0][0]);
     tf32_split(lds_f32(pbm0 + 4 * kBRow), bh[0][1], bl[0][1]);
@@ -500,10 +522,10 @@ struct WarpAcc {
 #pragma unroll
     for (int mt = 0; mt < 4; ++mt) {
       uint32_t ah[4], al[4];
-      tf32_split(pp[mt].x, ah[0], al[0]);
-      tf32_split(pp[mt].y, ah[1], al[1]);
-      tf32_split(qq[mt].x, ah[2], al[2]);
-      tf32_split(qq[mt].y, ah[3], al[3]);
+      tf32_split(pv[2 * mt], ah[0], al[0]);
+      tf32_split(pv[2 * mt + 1], ah[1], al[1]);
+      tf32_split(qv[2 * mt], ah[2], al[2]);
+      tf32_split(qv[2 * mt + 1], ah[3], al[3]);
 #pragma unroll
       for (int nt = 0; nt < 2; ++nt) {
         float d[4] = {0.f, 0.f, 0.f, 0.f};
@@ -519,16 +541,14 @@ struct WarpAcc {
   // Same update with the window accumulated inside the tensor core (no float32 additions): term-major order,
   // so that the three instructions of a tile are 8 instructions apart.  The tensor core truncates its
   // accumulator: measured against the FADD variant with tests/accuracy_modes.py.
-  __device__ __forceinline__ void update_mma_direct(uint32_t pam, uint32_t pbm0, uint32_t pbm1) {
-    const float4 p0 = lds_f4<0>(pam), p1 = lds_f4<128>(pam);
-    const float4 q0 = lds_f4<4 * kARow>(pam), q1 = lds_f4<4 * kARow + 128>(pam);
+  __device__ __forceinline__ void update_mma_direct(uint32_t pam, uint32_t kuoff, uint32_t pbm0, uint32_t pbm1) {
+    float pv[8], qv[8];
+    load_products(pam, kuoff, pv, qv);
     uint32_t bh[2][2], bl[2][2];
     tf32_split(lds_f32(pbm0), bh[0][0], bl[0][0]);
     tf32_split(lds_f32(pbm0 + 4 * kBRow), bh[0][1], bl[0][1]);
     tf32_split(lds_f32(pbm1), bh[1][0], bl[1][0]);
     tf32_split(lds_f32(pbm1 + 4 * kBRow), bh[1][1], bl[1][1]);
-    const float pv[8] = {p0.x, p0.y, p0.z, p0.w, p1.x, p1.y, p1.z, p1.w};
-    const float qv[8] = {q0.x, q0.y, q0.z, q0.w, q1.x, q1.y, q1.z, q1.w};
     uint32_t ah[4][4], al[4][4];
 #pragma unroll
     for (int mt = 0; mt < 4; ++mt) {
@@ -645,7 +665,7 @@ struct WarpCells {
 template <int U, bool CHECK, int MODE>
 __device__ __forceinline__ void warp_consume1(uint32_t pa, uint32_t pb, uint32_t pb1, uint32_t porg, uint32_t moved8, const WarpOps& cur,
                                               WarpOps& nxt, WarpAcc& acc, const FoldSink& sg, WarpCells& cells, int a, int pq) {
-  nxt = warp_load<U + 1>(pa, pb, pb1);
+  nxt = warp_load<U + 1, false>(pa, 0u, pb, pb1);
   if (CHECK && ((moved8 >> U) & 1u)) {
     acc.template fold<MODE>(sg, cells.i, cells.wj, pq);
     cells.set(lds_u32(porg + 4 * U), a);
@@ -681,8 +701,10 @@ __global__ void __launch_bounds__(32 * NW, DIRECT ? 20 : 1) grid_warp_kernel(con
   extern __shared__ __align__(16) unsigned char smem_raw[];
   float4* sg = reinterpret_cast<float4*>(smem_raw);
   const int lane = threadIdx.x & 31, warp = threadIdx.x >> 5;
-  const uint32_t sA = smem_u32(smem_raw + kSubBytes + warp * kWarpStageBytes);
-  const uint32_t sB = sA + kBatch * kARow;
+  constexpr bool FACT = MMA != 0;
+  constexpr int ROW = FACT ? kKRow : kARow;
+  const uint32_t sA = smem_u32(smem_raw + kSubBytes + warp * warp_stage_bytes(FACT));
+  const uint32_t sB = sA + kBatch * ROW;
   const uint32_t sOrg = sB + kBatch * kBRow;
 
   const Item item = items[item_base + blockIdx.x];
@@ -712,12 +734,14 @@ __global__ void __launch_bounds__(32 * NW, DIRECT ? 20 : 1) grid_warp_kernel(con
   const uint32_t snap_rcp = (256u + snap - 1) / snap;
   const bool wstack = g.do_wstacking != 0;
   uint32_t carry = 0xffffffffu;
-  const uint32_t myA = sA + lane * kARow, myB = sB + lane * kBRow;
+  const uint32_t myA = sA + lane * ROW, myB = sB + lane * kBRow;
   // consumer constants
   const int a = lane >> 2, pq = lane & 3;
-  const uint32_t pa0 = sA + 16 * arow_unit(a), pb0 = sB + (pq < 2 ? pq * 8 : 48 + pq * 8), pb10 = sB + 16 + pq * 8;
+  const uint32_t kuoff = 4 * (a < 4 ? a : 12 + a);
+  const uint32_t pa0 = sA + (FACT ? kuoff : 16 * arow_unit(a)), pkv0 = sA + 16;
+  const uint32_t pb0 = sB + (pq < 2 ? pq * 8 : 48 + pq * 8), pb10 = sB + 16 + pq * 8;
   // tensor path: rows of visibilities pq and pq + 4 of a group, column n = a of the B blocks
-  const uint32_t pam0 = pa0 + pq * kARow, pam80 = pam0 + 8 + (g.W >> 4);  // W <= 8: + 8
+  const uint32_t pam0 = sA + pq * kKRow;
   const uint32_t pbm00 = sB + pq * kBRow + 4 * (a < 4 ? a : 12 + a), pbm10 = sB + pq * kBRow + 4 * (4 + a);
   WarpAcc acc;
   acc.clear();
@@ -756,10 +780,17 @@ __global__ void __launch_bounds__(32 * NW, DIRECT ? 20 : 1) grid_warp_kernel(con
         kv[r] = es_tap(xv0 + (r < j0 ? c1 : c0), bw2);
         kw[r] = wstack ? es_tap(xw0 + c0, bw2) : (r == 0 ? 1.0f : 0.0f);
       }
+      if (FACT) {
+        sts_f4(myA, ku[0], ku[1], ku[2], ku[3]);
+        sts_f4(myA + 16, kv[0], kv[1], kv[2], kv[3]);
+        sts_f4(myA + 32, kv[4], kv[5], kv[6], kv[7]);
+        sts_f4(myA + 64, ku[4], ku[5], ku[6], ku[7]);
+      } else {
 #pragma unroll
-      for (int r = 0; r < 8; ++r) {
-        sts_f4(myA + 16 * arow_unit(r), ku[r] * kv[0], ku[r] * kv[1], ku[r] * kv[2], ku[r] * kv[3]);
-        sts_f4(myA + 16 * arow_unit(r) + 128, ku[r] * kv[4], ku[r] * kv[5], ku[r] * kv[6], ku[r] * kv[7]);
+        for (int r = 0; r < 8; ++r) {
+          sts_f4(myA + 16 * arow_unit(r), ku[r] * kv[0], ku[r] * kv[1], ku[r] * kv[2], ku[r] * kv[3]);
+          sts_f4(myA + 16 * arow_unit(r) + 128, ku[r] * kv[4], ku[r] * kv[5], ku[r] * kv[6], ku[r] * kv[7]);
+        }
       }
       const float re = cur_valid ? cur.re : 0.0f, im = cur_valid ? cur.im : 0.0f;
 #pragma unroll
@@ -773,25 +804,26 @@ __global__ void __launch_bounds__(32 * NW, DIRECT ? 20 : 1) grid_warp_kernel(con
     // ---------------- consume: lane = (a, bh, ph) ----------------
     {
       WarpOps x;
-      if (!MMA) x = warp_load<0>(pa0, pb0, pb10);
+      if (!MMA) x = warp_load<0, false>(pa0, 0u, pb0, pb10);
 #pragma unroll 1
       for (int k0 = 0; k0 < kBatch; k0 += 8) {
-        const uint32_t pa = pa0 + k0 * kARow, pb = pb0 + k0 * kBRow, pb1 = pb10 + k0 * kBRow, porg = sOrg + 4 * k0;
+        const uint32_t pa = pa0 + k0 * ROW, pkv = pkv0 + k0 * ROW, pb = pb0 + k0 * kBRow, pb1 = pb10 + k0 * kBRow;
+        const uint32_t porg = sOrg + 4 * k0;
         const uint32_t m8 = (moved >> k0) & 0xffu;
         // most groups stay inside one register window: branch-free fast path.  The operands of visibility
         // k0 + 8 are prefetched at the end of a group; past the last group that reads the rows after the
         // stage (still inside the CTA's shared memory: kSlack), which are discarded.
         if (m8 == 0) {
-          if (MMA == 2) acc.update_mma_direct(pam0 + k0 * kARow, pbm00 + k0 * kBRow, pbm10 + k0 * kBRow);
-          else if (MMA) acc.update_mma(pam0 + k0 * kARow, pam80 + k0 * kARow, pbm00 + k0 * kBRow, pbm10 + k0 * kBRow);
+          if (MMA == 2) acc.update_mma_direct(pam0 + k0 * kKRow, kuoff, pbm00 + k0 * kBRow, pbm10 + k0 * kBRow);
+          else if (MMA) acc.update_mma(pam0 + k0 * kKRow, kuoff, pbm00 + k0 * kBRow, pbm10 + k0 * kBRow);
           else warp_consume8<false, MODE>(pa, pb, pb1, porg, m8, x, acc, sink, cells, a, pq);
         } else {
-          if (MMA) x = warp_load<0>(pa, pb, pb1);
+          if (MMA) x = warp_load<0, FACT>(pa, pkv, pb, pb1);
           // a window moves inside this group (rare): rolled loop, so that the fold is not inlined eight times
           // (the unrolled variant doubled the code size and a third of the stalls were instruction fetches)
 #pragma unroll 1
           for (int u = 0; u < 8; ++u) {
-            const WarpOps nxt = warp_load<1>(pa + u * kARow, pb + u * kBRow, pb1 + u * kBRow);
+            const WarpOps nxt = warp_load<1, FACT>(pa + u * ROW, pkv + u * ROW, pb + u * kBRow, pb1 + u * kBRow);
             if ((m8 >> u) & 1u) {
               acc.template fold<MODE>(sink, cells.i, cells.wj, pq);
               cells.set(lds_u32(porg + 4 * u), a);
@@ -891,7 +923,7 @@ template <int NW, bool DIRECT, int MMA = 0>
 cip_status launch_warp(cip_ctx* ctx, cudaStream_t stream, const Item* items, int64_t item_begin, int64_t n, const RecP* recs,
                        const GridGeom& g, float* grid, int plane_base, int nslots) {
   auto kern = grid_warp_kernel<NW, DIRECT, MMA>;
-  constexpr int smem = warp_smem_bytes(NW, DIRECT);
+  constexpr int smem = warp_smem_bytes(NW, DIRECT, MMA != 0);
   CIP_CHECK_CUDA(cudaFuncSetAttribute(kern, cudaFuncAttributeMaxDynamicSharedMemorySize, smem));
   CIP_CHECK_CUDA(cudaFuncSetAttribute(kern, cudaFuncAttributePreferredSharedMemoryCarveout, (int)cudaSharedmemCarveoutMaxShared));
   kern<<<(unsigned)n, 32 * NW, smem, stream>>>(items, item_begin, recs, g, grid, plane_base, nslots);
