@@ -693,7 +693,7 @@ __device__ __forceinline__ void warp_consume8(uint32_t pa, uint32_t pb, uint32_t
 // leaves it (the records are sorted by window, so that happens ~ once per lattice position and item).  This
 // trades ~4x more L2 reductions for 14.4 KB of shared memory per warp, i.e. twice the resident warps.
 template <int NW, bool DIRECT, int MMA>
-__global__ void __launch_bounds__(32 * NW, DIRECT ? 20 : 1) grid_warp_kernel(const Item* __restrict__ items, int64_t item_base,
+__global__ void __launch_bounds__(32 * NW, DIRECT ? (MMA == 2 ? 24 : 20) : 1) grid_warp_kernel(const Item* __restrict__ items, int64_t item_base,
                                                             const RecP* __restrict__ recs, GridGeom g,
                                                             float* __restrict__ grid, int plane_base, int nslots) {
   constexpr int MODE = DIRECT ? 2 : (NW > 1 ? 1 : 0);
