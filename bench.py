@@ -367,10 +367,17 @@ def main():
     ap.add_argument("--no-cpu", action="store_true", help="skip the CPU baseline leg")
     ap.add_argument("--verbose", action="store_true", help="per-step host timings on stderr")
     args = ap.parse_args()
+    # stdout carries exactly one JSON line: libraries that write to file descriptor 1 behind Python's back (the
+    # NCCL version banner) go to stderr while the benchmark runs
+    sys.stdout.flush()
+    json_fd = os.dup(1)
+    os.dup2(2, 1)
+    sys.stdout = os.fdopen(json_fd, "w")
     if args.impl == "reference":
         run_reference(args)
     else:
         run_b200(args)
+    sys.stdout.flush()
 
 
 if __name__ == "__main__":
