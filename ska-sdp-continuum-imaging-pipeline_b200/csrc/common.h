@@ -25,7 +25,7 @@ constexpr int kHalo = 8;          // shift that keeps window origins non-negativ
 constexpr int kSub = kTile + kFastSupport - 1;  // sub-grid edge held in shared memory (15, odd on purpose)
 constexpr int kWin = 8;           // w planes of one gridding window (= planes per consumer thread)
 constexpr int kBatch = 32;        // visibilities per producer/consumer hand-over
-constexpr int kItemVis = 2048;    // visibilities per gridding work item (measured on configs[1]: 512: 9.22, 1024: 9.15, 2048: 9.18, 4096: 9.40, 16384: 10.4 ms gridding; binning grows with the item count)
+constexpr int kItemVis = 2048;    // visibilities per gridding work item (measured on configs[1], FFMA2 gridder: 512: 9.22, 1024: 9.15, 2048: 9.18, 4096: 9.40, 16384: 10.4 ms gridding; tensor-path gridder: 2048: 7.87, 4096: 8.02; binning grows with the item count)
 constexpr int kMaxChunks = 8;     // row chunks of the host -> device visibility stream
 
 void set_error(const char* fmt, ...);

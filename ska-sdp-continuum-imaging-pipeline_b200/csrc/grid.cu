@@ -51,6 +51,11 @@ __device__ __forceinline__ float2 unpack2(u64 v) {
 }
 // d = a * b + d on two packed floats (FFMA2 on sm_100a)
 __device__ __forceinline__ void ffma2(u64& d, u64 a, u64 b) { asm("fma.rn.f32x2 %0, %1, %2, %0;" : "+l"(d) : "l"(a), "l"(b)); }
+// packed float32 pairs: one issue slot for two operations (the FMA pipe is busy for two cycles)
+__device__ __forceinline__ u64 fadd2(u64 a, u64 b) { u64 d; asm("add.rn.f32x2 %0, %1, %2;" : "=l"(d) : "l"(a), "l"(b)); return d; }
+__device__ __forceinline__ u64 fsub2(u64 a, u64 b) { u64 d; asm("sub.rn.f32x2 %0, %1, %2;" : "=l"(d) : "l"(a), "l"(b)); return d; }
+__device__ __forceinline__ u64 fmul2(u64 a, u64 b) { u64 d; asm("mul.rn.f32x2 %0, %1, %2;" : "=l"(d) : "l"(a), "l"(b)); return d; }
+__device__ __forceinline__ void unpack2u(u64 v, uint32_t& lo, uint32_t& hi) { asm("mov.b64 {%0, %1}, %2;" : "=r"(lo), "=r"(hi) : "l"(v)); }
 
 __device__ __forceinline__ void red_add_v4(float* addr, float a, float b, float c, float d) {
   asm volatile("red.global.add.v4.f32 [%0], {%1, %2, %3, %4};" ::"l"(addr), "f"(a), "f"(b), "f"(c), "f"(d) : "memory");
@@ -376,6 +381,9 @@ __device__ __forceinline__ ulonglong2 lds_u2(uint32_t addr) {
 __device__ __forceinline__ void sts_f4(uint32_t addr, float a, float b, float c, float d) {
   asm volatile("st.shared.v4.f32 [%0], {%1, %2, %3, %4};" ::"r"(addr), "f"(a), "f"(b), "f"(c), "f"(d) : "memory");
 }
+__device__ __forceinline__ void sts_u2(uint32_t addr, u64 a, u64 b) {
+  asm volatile("st.shared.v2.b64 [%0], {%1, %2};" ::"r"(addr), "l"(a), "l"(b) : "memory");
+}
 // ES tap exp(beta_w (sqrt(1 - x^2) - 1)), 0 where 1 - x^2 <= 0; pure PTX so that the mask stays a select
 __device__ __forceinline__ float es_tap(float x, float bw2) {
   float e;
@@ -511,31 +519,62 @@ struct WarpAcc {
     qv[0] = kuq * q0.x; qv[1] = kuq * q0.y; qv[2] = kuq * q0.z; qv[3] = kuq * q0.w;
     qv[4] = kuq * q1.x; qv[5] = kuq * q1.y; qv[6] = kuq * q1.z; qv[7] = kuq * q1.w;
   }
+  // Pair form of load_products: (v = 2m, 2m+1) of the visibilities pq (pp) and pq + 4 (qq) as packed float32 pairs
+  __device__ __forceinline__ static void load_product_pairs(uint32_t pam, uint32_t kuoff, u64 (&pp)[4], u64 (&qq)[4]) {
+    const u64 kup = dup2(lds_f32(pam + kuoff)), kuq = dup2(lds_f32(pam + kuoff + 4 * kKRow));
+    const float4 p0 = lds_f4<16>(pam), p1 = lds_f4<32>(pam);
+    const float4 q0 = lds_f4<4 * kKRow + 16>(pam), q1 = lds_f4<4 * kKRow + 32>(pam);
+    pp[0] = fmul2(kup, pack2(p0.x, p0.y)); pp[1] = fmul2(kup, pack2(p0.z, p0.w));
+    pp[2] = fmul2(kup, pack2(p1.x, p1.y)); pp[3] = fmul2(kup, pack2(p1.z, p1.w));
+    qq[0] = fmul2(kuq, pack2(q0.x, q0.y)); qq[1] = fmul2(kuq, pack2(q0.z, q0.w));
+    qq[2] = fmul2(kuq, pack2(q1.x, q1.y)); qq[3] = fmul2(kuq, pack2(q1.z, q1.w));
+  }
+  // Products, operand split and the float32 addition of the tiles work on packed pairs (FMUL2 / FADD2): the pairs
+  // (v = 2 mt, 2 mt + 1) and (re, im) are exactly the register pairs of the fragments.
   __device__ __forceinline__ void update_mma(uint32_t pam, uint32_t kuoff, uint32_t pbm0, uint32_t pbm1) {
-    float pv[8], qv[8];
-    load_products(pam, kuoff, pv, qv);
+    u64 pp[4], qq[4];
+    load_product_pairs(pam, kuoff, pp, qq);
     uint32_t bh[2][2], bl[2][2];
     tf32_split(lds_f32(pbm0), bh[0][0], bl[0][0]);
     tf32_split(lds_f32(pbm0 + 4 * kBRow), bh[0][1], bl[0][1]);
     tf32_split(lds_f32(pbm1), bh[1][0], bl[1][0]);
     tf32_split(lds_f32(pbm1 + 4 * kBRow), bh[1][1], bl[1][1]);
+    // two row tiles at a time: four independent accumulation chains (a dependent mma.sync issued after only
+    // one other instruction of the tensor pipe waits for its accumulator)
 #pragma unroll
-    for (int mt = 0; mt < 4; ++mt) {
-      uint32_t ah[4], al[4];
-      tf32_split(pv[2 * mt], ah[0], al[0]);
-      tf32_split(pv[2 * mt + 1], ah[1], al[1]);
-      tf32_split(qv[2 * mt], ah[2], al[2]);
-      tf32_split(qv[2 * mt + 1], ah[3], al[3]);
+    for (int mp = 0; mp < 4; mp += 2) {
+      uint32_t ah[2][4], al[2][4];
 #pragma unroll
-      for (int nt = 0; nt < 2; ++nt) {
-        float d[4] = {0.f, 0.f, 0.f, 0.f};
-        mma_tf32(d, al, bh[nt][0], bh[nt][1]);
-        mma_tf32(d, ah, bl[nt][0], bl[nt][1]);
-        mma_tf32(d, ah, bh[nt][0], bh[nt][1]);
-        const float2 x = unpack2(c[2 * mt][nt]), y = unpack2(c[2 * mt + 1][nt]);
-        c[2 * mt][nt] = pack2(x.x + d[0], x.y + d[1]);
-        c[2 * mt + 1][nt] = pack2(y.x + d[2], y.y + d[3]);
+      for (int m = 0; m < 2; ++m) {
+        const u64 x = pp[mp + m], y = qq[mp + m];
+        const u64 lp = fsub2(x, x & 0xffffe000ffffe000ull), lq = fsub2(y, y & 0xffffe000ffffe000ull);
+        unpack2u(x, ah[m][0], ah[m][1]);  // hi = the raw bits: the tensor core reads the upper 19 only
+        unpack2u(y, ah[m][2], ah[m][3]);
+        unpack2u(lp, al[m][0], al[m][1]);
+        unpack2u(lq, al[m][2], al[m][3]);
       }
+      float d[2][2][4];
+#pragma unroll
+      for (int m = 0; m < 2; ++m)
+#pragma unroll
+        for (int nt = 0; nt < 2; ++nt) d[m][nt][0] = d[m][nt][1] = d[m][nt][2] = d[m][nt][3] = 0.f;
+#pragma unroll
+      for (int term = 0; term < 3; ++term)
+#pragma unroll
+        for (int m = 0; m < 2; ++m)
+#pragma unroll
+          for (int nt = 0; nt < 2; ++nt) {
+            if (term == 0) mma_tf32(d[m][nt], al[m], bh[nt][0], bh[nt][1]);
+            else if (term == 1) mma_tf32(d[m][nt], ah[m], bl[nt][0], bl[nt][1]);
+            else mma_tf32(d[m][nt], ah[m], bh[nt][0], bh[nt][1]);
+          }
+#pragma unroll
+      for (int m = 0; m < 2; ++m)
+#pragma unroll
+        for (int nt = 0; nt < 2; ++nt) {
+          c[2 * (mp + m)][nt] = fadd2(c[2 * (mp + m)][nt], pack2(d[m][nt][0], d[m][nt][1]));
+          c[2 * (mp + m) + 1][nt] = fadd2(c[2 * (mp + m) + 1][nt], pack2(d[m][nt][2], d[m][nt][3]));
+        }
     }
   }
   // Same update with the window accumulated inside the tensor core (no float32 additions): term-major order,
@@ -792,11 +831,11 @@ __global__ void __launch_bounds__(32 * NW, DIRECT ? (MMA == 2 ? 24 : 20) : 1) gr
           sts_f4(myA + 16 * arow_unit(r) + 128, ku[r] * kv[4], ku[r] * kv[5], ku[r] * kv[6], ku[r] * kv[7]);
         }
       }
-      const float re = cur_valid ? cur.re : 0.0f, im = cur_valid ? cur.im : 0.0f;
+      const u64 v2 = cur_valid ? pack2(cur.re, cur.im) : 0ull;
 #pragma unroll
       for (int q = 0; q < 8; q += 4) {
-        sts_f4(myB + q * 16, re * kw[q], im * kw[q], re * kw[q + 2], im * kw[q + 2]);                       // even planes
-        sts_f4(myB + 16 + q * 4, re * kw[q + 1], im * kw[q + 1], re * kw[q + 3], im * kw[q + 3]);  // odd planes
+        sts_u2(myB + q * 16, fmul2(v2, dup2(kw[q])), fmul2(v2, dup2(kw[q + 2])));               // even planes
+        sts_u2(myB + 16 + q * 4, fmul2(v2, dup2(kw[q + 1])), fmul2(v2, dup2(kw[q + 3])));  // odd planes
       }
       asm volatile("st.shared.u32 [%0], %1;" ::"r"(sOrg + 4 * lane), "r"(cxy) : "memory");
     }
