@@ -58,6 +58,11 @@ void* cip_ctx_stream(cip_ctx* ctx);
 cip_status cip_ctx_synchronize(cip_ctx* ctx);
 /* Number of kernels this library has launched on the context so far (own kernels, CUB passes, cuFFT execs). */
 int64_t cip_ctx_launches(cip_ctx* ctx);
+/* The CUDA device index the context is bound to.  Every entry point makes it current for the call and restores
+ * the caller's current device before it returns. */
+int cip_ctx_device(cip_ctx* ctx);
+/* The calling thread's current CUDA device (what device < 0 resolves to). */
+cip_status cip_current_device(int* device);
 
 /* ---- ms2dirty arguments, 1:1 (invert.py:170-183) -------------------------------- */
 typedef struct {
@@ -80,7 +85,7 @@ typedef struct {
 
 typedef struct {
   double wmin, wmax;        /* range of |w| in wavelengths over active samples       */
-  int64_t nactive;          /* samples with wgt*mask != 0 and vis != 0               */
+  int64_t nactive;          /* samples with wgt*mask != 0 (the visibilities are not read) */
   double sum_wgt;           /* sum of wgt*mask over ALL samples (invert.py:184)      */
 } cip_scan_result;
 
@@ -119,7 +124,9 @@ cip_status cip_kernel_table(double sigma, int support, double* beta, double* rms
 /* Gridding-kernel Fourier transform c(xi) used by the correction (host, float64). */
 cip_status cip_kernel_ft(const cip_plan* plan, const double* xi, int64_t n, double* out);
 
-/* G1 scan: w-range, active count and weight sum of one shard. */
+/* G1 scan: w-range, active count and weight sum of one shard.  With host arguments (memspace 0) the staged
+ * uvw / freq / weights / mask are reused by a cip_grid_accumulate that follows with the SAME pointers and
+ * sizes: the arrays must not change in between. */
 cip_status cip_scan(cip_ctx* ctx, const cip_invert_args* args, cip_scan_result* out);
 
 /* G1 binning + G2 gridding + G3 FFT + G4 w-screen: ADD the uncorrected dirty image of the

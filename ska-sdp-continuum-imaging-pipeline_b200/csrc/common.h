@@ -65,6 +65,28 @@ double now_ms();  // host monotonic clock
     }                                  \
   } while (0)
 
+// Makes the context's device current for the duration of an entry point and restores the caller's device.
+struct DeviceScope {
+  int prev = -1;
+  bool switched = false;
+  cudaError_t err = cudaSuccess;
+  explicit DeviceScope(int dev) {
+    err = cudaGetDevice(&prev);
+    if (err == cudaSuccess && prev != dev) {
+      err = cudaSetDevice(dev);
+      switched = err == cudaSuccess;
+    }
+  }
+  ~DeviceScope() {
+    if (switched) cudaSetDevice(prev);
+  }
+  DeviceScope(const DeviceScope&) = delete;
+  DeviceScope& operator=(const DeviceScope&) = delete;
+};
+#define CIP_ENTER_DEVICE(ctx)                    \
+  ::cip::DeviceScope _dev_scope((ctx)->device);  \
+  CIP_CHECK_CUDA(_dev_scope.err)
+
 // Grow-only device buffer owned by the context.
 struct DevBuf {
   void* p = nullptr;

@@ -239,7 +239,8 @@ extern "C" cip_status cip_ctx_create(int device, cip_ctx** out) {
   }
   if (device < 0) CIP_CHECK_CUDA(cudaGetDevice(&device));
   CIP_REQUIRE(device < ndev, "device %d out of range (%d devices)", device, ndev);
-  CIP_CHECK_CUDA(cudaSetDevice(device));
+  DeviceScope scope(device);
+  CIP_CHECK_CUDA(scope.err);
   cip_ctx* ctx = new cip_ctx();
   ctx->device = device;
   cudaDeviceProp prop{};
@@ -272,7 +273,7 @@ extern "C" cip_status cip_ctx_create(int device, cip_ctx** out) {
 
 extern "C" cip_status cip_ctx_destroy(cip_ctx* ctx) {
   if (!ctx) return CIP_OK;
-  cudaSetDevice(ctx->device);
+  DeviceScope scope(ctx->device);
   if (ctx->copy_stream) cudaStreamSynchronize(ctx->copy_stream);
   if (ctx->stream) cudaStreamSynchronize(ctx->stream);
   if (ctx->grid_stream) cudaStreamSynchronize(ctx->grid_stream);
@@ -306,6 +307,12 @@ extern "C" cip_status cip_ctx_destroy(cip_ctx* ctx) {
 extern "C" void* cip_ctx_stream(cip_ctx* ctx) { return ctx ? (void*)ctx->stream : nullptr; }
 
 extern "C" int64_t cip_ctx_launches(cip_ctx* ctx) { return ctx ? ctx->launches : 0; }
+extern "C" int cip_ctx_device(cip_ctx* ctx) { return ctx ? ctx->device : -1; }
+extern "C" cip_status cip_current_device(int* device) {
+  CIP_REQUIRE(device != nullptr, "device output is NULL");
+  CIP_CHECK_CUDA(cudaGetDevice(device));
+  return CIP_OK;
+}
 
 extern "C" cip_status cip_ctx_synchronize(cip_ctx* ctx) {
   CIP_REQUIRE(ctx != nullptr, "ctx is NULL");

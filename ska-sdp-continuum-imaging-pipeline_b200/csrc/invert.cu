@@ -57,7 +57,7 @@ struct CopyStreamGuard {
 extern "C" cip_status cip_scan(cip_ctx* ctx, const cip_invert_args* args, cip_scan_result* out) {
   CIP_REQUIRE(ctx && out, "NULL argument");
   CIP_TRY(validate_args(args));
-  CIP_CHECK_CUDA(cudaSetDevice(ctx->device));
+  CIP_ENTER_DEVICE(ctx);
   DevInputs in;
   CIP_TRY(stage_inputs(ctx, args, &in, nullptr, false, nullptr));  // no visibilities: the scan reads weights only
   CIP_TRY(run_scan(ctx, in, args->do_wstacking, out));
@@ -264,7 +264,7 @@ extern "C" cip_status cip_grid_accumulate(cip_ctx* ctx, const cip_invert_args* a
   CIP_REQUIRE(ctx && plan && image_dev, "NULL argument");
   CIP_TRY(validate_args(args));
   CIP_REQUIRE(plan->npix_x == args->npix_x && plan->npix_y == args->npix_y, "plan and args disagree on the image size");
-  CIP_CHECK_CUDA(cudaSetDevice(ctx->device));
+  CIP_ENTER_DEVICE(ctx);
   if (report) memset(report, 0, sizeof(*report));
   const int64_t l0 = ctx->launches;
   DevInputs in;
@@ -280,7 +280,7 @@ extern "C" cip_status cip_grid_accumulate(cip_ctx* ctx, const cip_invert_args* a
 extern "C" cip_status cip_correct_image(cip_ctx* ctx, const cip_plan* plan, void* image_dev, int row_begin,
                                         int row_end, double scale) {
   CIP_REQUIRE(ctx && plan && image_dev, "NULL argument");
-  CIP_CHECK_CUDA(cudaSetDevice(ctx->device));
+  CIP_ENTER_DEVICE(ctx);
   CIP_TRY(run_correct(ctx, *plan, image_dev, row_begin, row_end, scale));
   CIP_CHECK_CUDA(cudaStreamSynchronize(ctx->stream));
   return CIP_OK;
@@ -290,7 +290,7 @@ extern "C" cip_status cip_invert(cip_ctx* ctx, const cip_invert_args* args, void
                                  cip_plan* plan_out, cip_report* report) {
   CIP_REQUIRE(ctx && dirty_out, "NULL argument");
   CIP_TRY(validate_args(args));
-  CIP_CHECK_CUDA(cudaSetDevice(ctx->device));
+  CIP_ENTER_DEVICE(ctx);
   if (report) memset(report, 0, sizeof(*report));
   const int64_t l0 = ctx->launches;
   cudaStream_t st = ctx->stream;

@@ -38,7 +38,7 @@ extern "C" cip_status cip_stokes_i(cip_ctx* ctx, const void* vis4, const uint8_t
   CIP_REQUIRE(ctx && vis4 && flags4 && wgt4 && vis_out && effw_out, "NULL argument");
   CIP_REQUIRE(nrow >= 0 && nchan >= 0, "negative nrow/nchan");
   CIP_REQUIRE(memspace == 0 || memspace == 1, "memspace must be 0 or 1");
-  CIP_CHECK_CUDA(cudaSetDevice(ctx->device));
+  CIP_ENTER_DEVICE(ctx);
   const int64_t n = nrow * nchan;
   if (n == 0) return CIP_OK;
   cudaStream_t st = ctx->stream;
@@ -56,6 +56,7 @@ extern "C" cip_status cip_stokes_i(cip_ctx* ctx, const void* vis4, const uint8_t
     dv = base;
     dw = base + (size_t)n * 32;
     df = base + (size_t)n * 48;
+    ctx->staged_valid = false;  // the outputs overwrite the staged inputs of a preceding cip_scan
     CIP_TRY(ctx->in_vis.ensure((size_t)n * 8));
     CIP_TRY(ctx->in_wgt.ensure((size_t)n * 4));
     ov = ctx->in_vis.p;

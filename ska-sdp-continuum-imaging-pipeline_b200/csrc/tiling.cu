@@ -228,7 +228,7 @@ extern "C" cip_status cip_tile_bin(cip_ctx* ctx, const double* uvw, int64_t nrow
   CIP_REQUIRE(memspace == 0 || memspace == 1, "memspace must be 0 or 1");
   for (int k = 0; k < 3; ++k)
     CIP_REQUIRE(tile_size[k] > 0 && tile_size[k] < HUGE_VAL, "tile_size[%d] must be positive and finite", k);
-  CIP_CHECK_CUDA(cudaSetDevice(ctx->device));
+  CIP_ENTER_DEVICE(ctx);
   *result = nullptr;
   cudaStream_t st = ctx->stream;
   cip_tile_result* R = new cip_tile_result();
@@ -379,7 +379,7 @@ extern "C" cip_status cip_tile_fetch(cip_ctx* ctx, const cip_tile_result* r, int
                                      int64_t* tile_offsets, int64_t* slice_irow, int32_t* slice_ch_start,
                                      int32_t* slice_ch_stop) {
   CIP_REQUIRE(ctx && r, "NULL argument");
-  CIP_CHECK_CUDA(cudaSetDevice(ctx->device));
+  CIP_ENTER_DEVICE(ctx);
   cudaStream_t st = ctx->stream;
   if (tile_offsets)
     CIP_CHECK_CUDA(cudaMemcpyAsync(tile_offsets, r->tile_offsets.p, sizeof(int64_t) * (r->n_tiles + 1), cudaMemcpyDeviceToHost, st));
@@ -404,7 +404,7 @@ extern "C" cip_status cip_tile_gather(cip_ctx* ctx, const cip_tile_result* r, co
   CIP_REQUIRE(nrow == r->nrow && nchan == r->nchan, "shape differs from the binned uvw (%lld x %lld)",
               (long long)r->nrow, (long long)r->nchan);
   CIP_REQUIRE(memspace == 0 || memspace == 1, "memspace must be 0 or 1");
-  CIP_CHECK_CUDA(cudaSetDevice(ctx->device));
+  CIP_ENTER_DEVICE(ctx);
   cudaStream_t st = ctx->stream;
   const int64_t ns = r->n_slices, nvis = nrow * nchan;
   if (ns == 0) {

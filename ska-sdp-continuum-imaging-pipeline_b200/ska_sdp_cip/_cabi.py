@@ -80,6 +80,9 @@ def lib():
             L.cip_ctx_synchronize.argtypes = [C.c_void_p]
             L.cip_ctx_launches.argtypes = [C.c_void_p]
             L.cip_ctx_launches.restype = C.c_int64
+            L.cip_ctx_device.argtypes = [C.c_void_p]
+            L.cip_ctx_device.restype = C.c_int
+            L.cip_current_device.argtypes = [C.POINTER(C.c_int)]
             L.cip_plan_make.argtypes = [C.c_int, C.c_int, C.c_double, C.c_double, C.c_double, C.c_int, C.c_int,
                                         C.c_double, C.c_double, C.c_int64, C.c_double, C.c_int, C.POINTER(Plan)]
             L.cip_kernel_table.argtypes = [C.c_double, C.c_int, C.POINTER(C.c_double), C.POINTER(C.c_double)]
@@ -104,7 +107,7 @@ def lib():
 
 
 EXPORTS = ["cip_last_error", "cip_version", "cip_ctx_create", "cip_ctx_destroy", "cip_ctx_stream",
-           "cip_ctx_synchronize", "cip_ctx_launches", "cip_plan_make", "cip_kernel_table", "cip_kernel_ft", "cip_scan",
+           "cip_ctx_synchronize", "cip_ctx_launches", "cip_ctx_device", "cip_current_device", "cip_plan_make", "cip_kernel_table", "cip_kernel_ft", "cip_scan",
            "cip_grid_accumulate", "cip_correct_image", "cip_invert", "cip_stokes_i", "cip_tile_bin",
            "cip_tile_fetch", "cip_tile_gather", "cip_tile_free"]
 
@@ -121,24 +124,35 @@ def check(status: int) -> None:
     raise CipError(f"libcip_b200 status {status}: {msg}")
 
 
+def current_device() -> int:
+    """Index of the calling thread's current CUDA device (what ``device=-1`` means)."""
+    dev = C.c_int(-1)
+    check(lib().cip_current_device(C.byref(dev)))
+    return dev.value
+
+
 class Context:
     """One context per process and GPU (cip_ctx is not re-entrant; calls are serialised by a lock)."""
 
     _instances: dict[int, "Context"] = {}
+    _create_lock = threading.Lock()
 
     def __init__(self, device: int = -1):
         self._h = C.c_void_p()
         check(lib().cip_ctx_create(device, C.byref(self._h)))
+        self.device = int(lib().cip_ctx_device(self._h))
         self.lock = threading.Lock()
 
     @classmethod
     def get(cls, device: int = -1) -> "Context":
-        with _lock:
+        """The context of ``device`` (-1 or None: the current CUDA device, resolved to its index first, so that
+        a process never holds two contexts -- two plane stacks -- on one GPU)."""
+        if device is None or device < 0:
+            device = current_device()
+        with cls._create_lock:
             inst = cls._instances.get(device)
-        if inst is None:
-            inst = cls(device)
-            with _lock:
-                cls._instances[device] = inst
+            if inst is None:
+                inst = cls._instances[device] = cls(device)
         return inst
 
     @property

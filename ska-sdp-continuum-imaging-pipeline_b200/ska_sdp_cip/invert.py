@@ -126,10 +126,10 @@ def ducc_invert(gridder_input: StokesIGridderInput, num_pixels: int, pixel_size_
     return image, total
 
 
-def worker_ducc_invert(gridder_input: StokesIGridderInput, num_pixels: int, pixel_size_asec: float
-                       ) -> tuple[NDArray, float]:
+def worker_ducc_invert(gridder_input: StokesIGridderInput, num_pixels: int, pixel_size_asec: float, *,
+                       epsilon: float = EPSILON, accumulate_fp64: bool = False) -> tuple[NDArray, float]:
     """Same as ducc_invert, for use as a dask task (reference: invert.py:187-197)."""
-    return ducc_invert(gridder_input, num_pixels, pixel_size_asec)
+    return ducc_invert(gridder_input, num_pixels, pixel_size_asec, epsilon=epsilon, accumulate_fp64=accumulate_fp64)
 
 
 def integrate_weighted_images(weighted_images: Iterable[tuple[NDArray, float]]) -> NDArray:
@@ -299,6 +299,7 @@ def dask_invert_measurement_set(ms_reader: MeasurementSetReader, client, num_pix
         for chunk in chunks:
             gridder_input = client.submit(StokesIGridderInput.from_measurement_set_reader, chunk)
             weighted_images.append(client.submit(worker_ducc_invert, gridder_input, num_pixels, pixel_size_asec,
+                                                 epsilon=epsilon, accumulate_fp64=accumulate_fp64,
                                                  resources={"processing_slots": 1}))
         return client.submit(integrate_weighted_images, weighted_images).result()
 

@@ -103,6 +103,11 @@ class _BoundedReader:
         return out
 
 
+class UnsupportedMeasurementSetLayout(Exception):
+    """Raised when a MeasurementSet deviates from the supported layout (one spectral window, one field,
+    one 4-correlation polarisation setup) -- same name as the reference's (measurement_set.py:12-16)."""
+
+
 class ArrayMeasurementSetReader(_BoundedReader):
     """Reader over arrays held in host memory, with the reference reader's interface.
 
@@ -118,7 +123,7 @@ class ArrayMeasurementSetReader(_BoundedReader):
         if uvw.shape != (nrow, 3) or freqs.shape != (nchan,):
             raise ValueError("uvw must be (nrow, 3) and freqs (nchan,)")
         self._uvw, self._freqs, self._vis, self._flags, self._weights = uvw, freqs, vis, flags, weights
-        self._path = Path(path).absolute()
+        self._path = Path(path).resolve()
         self._init_bounds(nrow, nchan)
 
     @property
@@ -155,23 +160,24 @@ class MeasurementSetReader(_BoundedReader):
     (measurement_set.py:130-358).  Single spectral window, 4 correlations assumed, as there."""
 
     def __init__(self, path: Union[str, os.PathLike], *, validate_layout: bool = True) -> None:
-        self._path = Path(path).absolute()
+        self._path = Path(path).resolve()
         if not self._path.is_dir():
             raise FileNotFoundError(f"Measurement set {str(self._path)!r} does not exist")
         with self._table("MAIN") as tbl:
             nrows = tbl.nrows()
         with self._table("SPECTRAL_WINDOW") as tbl:
             if validate_layout and tbl.nrows() != 1:
-                raise ValueError("MeasurementSet must have exactly one spectral window")
+                raise UnsupportedMeasurementSetLayout("MeasurementSet must have exactly one spectral window")
             nchan = len(tbl.getcol("CHAN_FREQ")[0])
         if validate_layout:
             with self._table("POLARIZATION") as tbl:
                 corr = list(tbl.getcol("CORR_TYPE")[0])
                 if tbl.nrows() != 1 or corr not in ([9, 10, 11, 12], [5, 6, 7, 8]):
-                    raise ValueError("MeasurementSet must hold one linear or circular 4-correlation setup")
+                    raise UnsupportedMeasurementSetLayout(
+                        "MeasurementSet must hold one linear or circular 4-correlation setup")
             with self._table("FIELD") as tbl:
                 if tbl.nrows() != 1:
-                    raise ValueError("MeasurementSet must have exactly one field")
+                    raise UnsupportedMeasurementSetLayout("MeasurementSet must have exactly one field")
         self._init_bounds(nrows, nchan)
 
     def _table(self, name: str):

@@ -1,6 +1,6 @@
-"""UVW tiling partition API (reference surface: src/ska_sdp_cip/uvw_tiling/__init__.py:1-17).
-``reorder_by_uvw_tile`` (dask/disk orchestration) is out of the hot-path scope."""
-from .tile import Tile, tiles_from_device_mapping
+"""UVW tiling partition API (reference surface: src/ska_sdp_cip/uvw_tiling/__init__.py:1-17)."""
+from .reorder import reorder_by_uvw_tile
+from .tile import Tile, concatenate_tiles, rechunk_tiles_on_disk, split_tile, tiles_from_device_mapping
 from .tiling_plan import (
     DeviceTileMapping,
     RowSliceId,
@@ -14,6 +14,7 @@ from .tiling_plan import (
 
 __all__ = [
     "create_uvw_tile_mapping",
+    "reorder_by_uvw_tile",
     "RowSliceId",
     "TileCoords",
     "TileMapping",

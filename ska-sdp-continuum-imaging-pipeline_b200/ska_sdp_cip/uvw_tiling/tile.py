@@ -1,11 +1,13 @@
-"""Drop-in for the ``Tile`` container of the reference (src/ska_sdp_cip/uvw_tiling/tile.py:14-124):
-same fields, npz format and constructor helpers.  ``tiles_from_device_mapping`` builds all tiles
-of a block from one GPU gather (cip_tile_gather) instead of a Python loop per slice."""
+"""Drop-in for ``ska_sdp_cip.uvw_tiling.tile`` (reference: src/ska_sdp_cip/uvw_tiling/tile.py): the ``Tile``
+container (:14-124: same fields, npz format, constructor helpers), ``concatenate_tiles`` (:127-152),
+``split_tile`` (:155-213) and ``rechunk_tiles_on_disk`` (:216-265).  ``tiles_from_device_mapping`` builds all
+tiles of a block from one GPU gather (cip_tile_gather) instead of a Python loop per slice."""
 from __future__ import annotations
 
 import os
 from dataclasses import dataclass
-from typing import Union
+from pathlib import Path
+from typing import Iterable, Sequence, Union
 
 import numpy as np
 from numpy.typing import NDArray
@@ -75,3 +77,64 @@ def tiles_from_device_mapping(dm: DeviceTileMapping, vis: NDArray, uvw: NDArray)
         tiles.append(Tile(tuple(int(x) for x in coords[t]), suvw[a:b].copy(), flat[voff[a]:voff[b]].copy(),
                           c0[a:b].astype(int), c1[a:b].astype(int)))
     return tiles
+
+
+_ARRAY_FIELDS = ("uvw", "visibilities", "channel_start_indices", "channel_stop_indices")
+
+
+def concatenate_tiles(tiles: Sequence[Tile]) -> Tile:
+    """One tile holding the rows of all ``tiles`` in order (tile.py:127-152); they must share coordinates."""
+    if not tiles:
+        raise ValueError("Cannot concatenate empty sequence of tiles")
+    coords = tiles[0].coords
+    if any(t.coords != coords for t in tiles):
+        raise ValueError("Cannot merge tiles with different coordinates")
+    return Tile(coords, *(np.concatenate([getattr(t, name) for t in tiles]) for name in _ARRAY_FIELDS))
+
+
+def split_tile(tile: Tile, max_vis_per_chunk: int) -> list[Tile]:
+    """Cut a tile into consecutive chunks of at most ``max_vis_per_chunk`` visibilities (tile.py:155-213).
+    Row slices are never split, so a single slice longer than the limit becomes a chunk of its own; the
+    chunks are views of the tile's arrays.  Greedy like the reference: a chunk is closed when the next row
+    slice would take it over the limit -- found by bisection on the cumulative sizes instead of a row loop."""
+    sizes = (np.asarray(tile.channel_stop_indices, dtype=np.int64)
+             - np.asarray(tile.channel_start_indices, dtype=np.int64))
+    ends = np.cumsum(sizes)  # ends[i] = visibilities in rows 0..i
+    nrows = len(sizes)
+    chunks: list[Tile] = []
+    row = 0
+    while row < nrows:
+        done = int(ends[row - 1]) if row else 0
+        # last row whose cumulative count still fits; at least one row per chunk
+        stop = max(int(np.searchsorted(ends, done + max_vis_per_chunk, side="right")), row + 1)
+        vis_stop = int(ends[stop - 1])
+        chunks.append(Tile(tile.coords, tile.uvw[row:stop], tile.visibilities[done:vis_stop],
+                           tile.channel_start_indices[row:stop], tile.channel_stop_indices[row:stop]))
+        row = stop
+    return chunks
+
+
+def rechunk_tiles_on_disk(tile_paths: Iterable[Path], outdir: Path, basename: str, *,
+                          max_vis_per_chunk: int = 5_000_000) -> list[Path]:
+    """Rewrite the tile chunk files ``tile_paths`` (same tile coordinates) as files named
+    ``{basename}_chunkNNN.npz`` that are as full as possible without exceeding ``max_vis_per_chunk``
+    visibilities; returns the written paths in order (tile.py:216-265)."""
+    written: list[Path] = []
+
+    def write(tile: Tile) -> None:
+        path = outdir / f"{basename}_chunk{len(written):03d}.npz"
+        tile.save_npz(path)
+        written.append(path)
+
+    pending: list[Tile] = []   # read but not yet written: together below the limit, or a single remainder
+    for path in tile_paths:
+        pending.append(Tile.load_npz(path))
+        if sum(t.num_visibilities for t in pending) > max_vis_per_chunk:
+            *full, rest = split_tile(concatenate_tiles(pending) if len(pending) > 1 else pending[0],
+                                     max_vis_per_chunk)
+            for chunk in full:
+                write(chunk)
+            pending = [rest]
+    if pending:
+        write(concatenate_tiles(pending) if len(pending) > 1 else pending[0])
+    return written

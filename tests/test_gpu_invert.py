@@ -368,6 +368,19 @@ def test_invert_measurement_set(built_lib, reader):
     assert dft.rel_rms(img, reference_invert(reader, npix, asec)) <= TOL_FP32
 
 
+def test_pipeline_app_writes_the_dirty_image(built_lib, reader, tmp_path):
+    """tests/test_pipeline_app.py:23-46 of the reference: run_program writes a (n, n) array next to the given
+    path; here it must also equal invert_measurement_set's result."""
+    from ska_sdp_cip import invert_measurement_set
+    from ska_sdp_cip.apps.pipeline_app import run_program
+    out = tmp_path / "image.npy"
+    run_program(["-n", "128", "-p", "20.0", "x.ms", str(out)], reader_factory=lambda path: reader)
+    data = np.load(out)
+    assert data.shape == (128, 128)
+    ref = invert_measurement_set(reader, 128, 20.0)
+    assert dft.rel_rms(data, ref) <= 2e-6
+
+
 @pytest.mark.parametrize("row_chunks,freq_chunks", [(1, None), (2, 3), (3, 1), (1, 8)])
 def test_chunked_invert_is_chunk_invariant(built_lib, reader, row_chunks, freq_chunks):
     """tests/test_dask_invert_measurement_set.py:31-34: the chunked image equals the unchunked one

@@ -175,3 +175,73 @@ def test_full_size_ska_low_binning_properties(T):
     assert np.array_equal(idx(irow[pick], c1[pick] - 1), want)
     inner = pick[c0[pick] > 0]
     assert np.all(np.any(idx(irow[inner], c0[inner] - 1) != coords[tile_of_slice[inner]], axis=1))
+
+
+# ---- reorder_by_uvw_tile on the GPU path (reference tests/uvw_tiling/test_uvw_reordering.py) ----
+
+def assert_all_visibilities_accounted_for(reader, paths):
+    """The reference's acceptance check: the (u, v, w) in wavelengths of every sample appears exactly once."""
+    from ska_sdp_cip.uvw_tiling import Tile
+    c = 299792458.0
+    freqs = reader.channel_frequencies()
+    want = np.sort((reader.uvw().reshape(-1, 1, 3) / c * freqs.reshape(1, -1, 1)).reshape(-1, 3), axis=0)
+    got, n = [], 0
+    for p in paths:
+        t = Tile.load_npz(p)
+        for i, (a, b) in enumerate(zip(t.channel_start_indices, t.channel_stop_indices)):
+            got.append(t.uvw[i] / c * freqs[a:b].reshape(-1, 1))
+            n += b - a
+    assert n == len(want)
+    assert np.array_equal(want, np.sort(np.concatenate(got), axis=0))
+
+
+@pytest.mark.gpu
+def test_reorder_by_uvw_tile_matches_reference_golden(T, golden, tmp_path):
+    from test_host_logic import check_reorder_against_golden, reorder_case
+    from ska_sdp_cip.uvw_tiling import reorder_by_uvw_tile
+    reader, tile_size, intervals, limit = reorder_case()
+    paths = reorder_by_uvw_tile(reader, tile_size, tmp_path, None, num_time_intervals=intervals,
+                                max_vis_per_chunk=limit)
+    assert sorted(p.name for p in paths) == sorted(p.name for p in tmp_path.iterdir())
+    check_reorder_against_golden(paths, golden("reorder_small"))
+    assert_all_visibilities_accounted_for(reader, paths)
+
+
+@pytest.mark.gpu
+def test_reorder_with_a_stub_client_and_the_reference_test_parameters(T, tmp_path):
+    """tile size, interval count and chunk limit of the reference's own reorder test, through the dask branch
+    with an in-process stand-in for the client."""
+    from test_host_logic import make_reader
+    from ska_sdp_cip.uvw_tiling import reorder_by_uvw_tile
+
+    class Future:
+        def __init__(self, value): self.value = value
+        def result(self): return self.value
+
+    class StubClient:
+        def __init__(self): self.resources = []
+        def scheduler_info(self): return {"workers": {"a": {}, "b": {}}}
+        def submit(self, fn, *args, resources=None, **kw):
+            self.resources.append(resources)
+            return Future(fn(*[a.result() if isinstance(a, Future) else a for a in args], **kw))
+
+    reader = make_reader(nrow=3000, nchan=16, seed=5, dense=True)
+    client = StubClient()
+    paths = reorder_by_uvw_tile(reader, (3000.0, 3000.0, 6000.0), tmp_path, client, num_time_intervals=4,
+                                max_vis_per_chunk=10_000)
+    assert {"processing_slots": 1} in client.resources
+    assert_all_visibilities_accounted_for(reader, paths)
+    from ska_sdp_cip.uvw_tiling import Tile
+    assert max(Tile.load_npz(p).num_visibilities for p in paths) <= 10_000
+
+
+@pytest.mark.gpu
+def test_reorder_app_runs_in_process(T, tmp_path):
+    from test_host_logic import make_reader
+    from ska_sdp_cip.apps import uvw_reorder_app
+    reader = make_reader(nrow=800, nchan=8, seed=6, dense=True)
+    out = tmp_path / "tiles"
+    paths = uvw_reorder_app.run_program(["-t", "2000", "2000", "4000", "-o", str(out), "-n", "2", "-m", "5000", "x.ms"],
+                                        reader_factory=lambda path: reader)
+    assert out.is_dir() and paths
+    assert_all_visibilities_accounted_for(reader, paths)

@@ -1,6 +1,8 @@
 """Host-side mirror of the reference interface (no GPU): partitioning, chunked reads, result types,
 Tile containers, synthetic generators.  The cases follow the reference's own tests
 (tests/test_measurement_set_partition_indices.py, tests/test_measurement_set_chunked_read.py)."""
+from pathlib import Path
+
 import numpy as np
 import pytest
 
@@ -9,6 +11,8 @@ from oracle import partition as opart
 from ska_sdp_cip import measurement_set as MS
 from ska_sdp_cip import synthetic as S
 from ska_sdp_cip.uvw_tiling import RowSliceId, Tile, merge_tile_mappings
+
+GOLDEN_DIR = Path(__file__).resolve().parent / "golden"
 
 
 def make_reader(nrow=74214, nchan=4, seed=0, dense=False):
@@ -187,3 +191,133 @@ def test_synthetic_visibilities_image_to_their_sources():
                              pixels=pix)[0] / wgt.sum() * (1 + nm1)
         assert peak == pytest.approx(flux[k], rel=1e-5)
     assert np.allclose(vis, model.astype(np.complex64), atol=1e-5)
+
+
+# ---- tile helpers, reorder passes, task metrics, command lines ------------------------
+
+def _random_tile(seed, nrows, nchan=40):
+    """Same generator as tools/make_golden.py::random_tile."""
+    rng = np.random.default_rng(seed)
+    start = rng.integers(0, nchan // 2, size=nrows)
+    stop = start + rng.integers(1, nchan // 2, size=nrows)
+    nvis = int((stop - start).sum())
+    vis = (rng.normal(size=nvis) + 1j * rng.normal(size=nvis)).astype(np.complex64)
+    return Tile((1, -2, 3), rng.normal(size=(nrows, 3)), vis, start.astype(int), stop.astype(int))
+
+
+def test_split_and_concatenate_match_reference_golden(golden):
+    from ska_sdp_cip.uvw_tiling import concatenate_tiles, split_tile
+    g = golden("tile_ops")
+    tile = _random_tile(31, 97)
+    for limit in (1, 7, 19, 20, 64, 333, 10**6):
+        chunks = split_tile(tile, limit)
+        assert [c.num_rows for c in chunks] == g[f"split_{limit}_rows"].tolist(), limit
+        assert [c.num_visibilities for c in chunks] == g[f"split_{limit}_nvis"].tolist(), limit
+        back = concatenate_tiles(chunks)
+        assert np.array_equal(back.visibilities, tile.visibilities) and np.array_equal(back.uvw, tile.uvw)
+        assert all(c.coords == tile.coords for c in chunks)
+    parts = [_random_tile(40 + i, n) for i, n in enumerate((5, 1, 30, 12, 3, 50))]
+    cat = concatenate_tiles(parts)
+    assert np.array_equal(cat.uvw, g["cat_uvw"]) and np.array_equal(cat.visibilities, g["cat_vis"])
+    assert np.array_equal(cat.channel_start_indices, g["cat_start"])
+    assert np.array_equal(cat.channel_stop_indices, g["cat_stop"])
+    with pytest.raises(ValueError):
+        concatenate_tiles([])
+    other = _random_tile(1, 2)
+    other.coords = (0, 0, 0)
+    with pytest.raises(ValueError):
+        concatenate_tiles([parts[0], other])
+    empty = Tile._zeros((0, 0, 0), 0, 0)
+    assert split_tile(empty, 10) == []
+
+
+def test_rechunk_on_disk_matches_reference_golden(golden, tmp_path):
+    from ska_sdp_cip.uvw_tiling import rechunk_tiles_on_disk
+    g = golden("tile_ops")
+    parts = [_random_tile(40 + i, n) for i, n in enumerate((5, 1, 30, 12, 3, 50))]
+    for limit in (50, 200, 10**6):
+        d = tmp_path / f"limit{limit}"
+        d.mkdir()
+        paths = []
+        for i, t in enumerate(parts):
+            paths.append(d / f"in{i}.npz")
+            t.save_npz(paths[-1])
+        written = rechunk_tiles_on_disk(paths, d, "tile_x", max_vis_per_chunk=limit)
+        assert [w.name for w in written] == g[f"rechunk_{limit}_names"].tolist()
+        tiles = [Tile.load_npz(w) for w in written]
+        assert [t.num_visibilities for t in tiles] == g[f"rechunk_{limit}_nvis"].tolist()
+        assert [t.num_rows for t in tiles] == g[f"rechunk_{limit}_rows"].tolist()
+        assert np.array_equal(np.concatenate([t.visibilities for t in tiles]), g["cat_vis"])
+
+
+def reorder_case():
+    """Inputs of tests/golden/reorder_small.npz (tools/make_golden.py::reorder_reader)."""
+    nrow, nchan = 600, 24
+    rng = np.random.default_rng(51)
+    uvw = rng.normal(size=(nrow, 3)) * np.array([1500.0, 1500.0, 200.0])
+    vis = (rng.normal(size=(nrow, nchan, 4)) + 1j * rng.normal(size=(nrow, nchan, 4))).astype(np.complex64)
+    freqs = 1.0e9 + 2.0e6 * np.arange(nchan)
+    flags = np.zeros(vis.shape, dtype=bool)
+    wgt = np.ones(vis.shape, dtype=np.float32)
+    return MS.ArrayMeasurementSetReader(uvw, freqs, vis, flags, wgt), (1500.0, 1500.0, 3000.0), 3, 700
+
+
+def check_reorder_against_golden(paths, g):
+    by_tile = {}
+    for p in sorted(paths):
+        t = Tile.load_npz(p)
+        by_tile.setdefault(t.coords, []).append((p.name, t))
+    coords = [tuple(int(x) for x in c) for c in g["coords"]]
+    assert set(by_tile) == set(coords)
+    for i, key in enumerate(coords):
+        names = [n for n, _ in by_tile[key]]
+        tiles = [t for _, t in by_tile[key]]
+        assert names == g[f"t{i}_names"].tolist(), key
+        assert [t.num_visibilities for t in tiles] == g[f"t{i}_nvis"].tolist(), key
+        assert np.array_equal(np.concatenate([t.visibilities for t in tiles]), g[f"t{i}_vis"]), key
+        assert np.array_equal(np.concatenate([t.uvw for t in tiles]), g[f"t{i}_uvw"]), key
+        assert np.array_equal(np.concatenate([t.channel_start_indices for t in tiles]), g[f"t{i}_start"]), key
+
+
+def test_reorder_passes_with_host_mapping_match_reference_golden(golden, tmp_path):
+    """The reference's calling convention (pre-computed TileMapping) on the host: interval files, then the
+    rechunk of every tile -- bit-identical file contents and names."""
+    from oracle import tiling
+    from ska_sdp_cip.uvw_tiling import reorder as R
+    reader, tile_size, intervals, limit = reorder_case()
+    freqs = reader.channel_frequencies()
+    present = set()
+    for i, chunk in enumerate(reader.partition(intervals, 1)):
+        mapping = {k: [RowSliceId(*s) for s in v] for k, v in tiling.tile_mapping(chunk.uvw(), tile_size, freqs).items()}
+        present.update(R.reorder_time_interval(chunk, mapping, tmp_path, interval_index=i))
+    assert (tmp_path / R._tile_filename(next(iter(present)), 0)).name.startswith("tile_iu")
+    paths = [p for key in present for p in R.rechunk_tile_chunk_group(key, tmp_path, max_vis_per_chunk=limit)]
+    assert not list(tmp_path.glob("*_interval*.npz"))
+    check_reorder_against_golden(paths, golden("reorder_small"))
+
+
+def test_task_metrics_match_reference_golden(tmp_path):
+    import json
+    from ska_sdp_cip.task_metrics import Task, TaskMetrics
+    g = json.loads((GOLDEN_DIR / "task_metrics.json").read_text())
+    stream = [dict(e, startstops=tuple(e["startstops"])) for e in g["stream"]]
+    metrics = TaskMetrics(stream)
+    assert len(metrics) == 3 and isinstance(metrics[0], Task)
+    assert metrics[2].name == "integrate_weighted_images-multi-dash" and metrics[1].duration == 3.5
+    metrics.save_json(tmp_path / "m.json", indent=4, sort_keys=True)
+    assert json.loads((tmp_path / "m.json").read_text()) == g["expected"]
+    staged = TaskMetrics.from_stage_reports([{"ms_scan": 1.0, "ms_bin": 2.0, "ms_total": 9.0, "launches": 5}], start=5.0)
+    assert [t.name for t in staged] == ["scan", "bin"] and abs(staged[1].stop - 5.003) < 1e-12
+
+
+def test_command_lines_parse_like_the_reference():
+    from ska_sdp_cip.apps import pipeline_app, uvw_reorder_app
+    a = pipeline_app.get_parser().parse_args(["-n", "2048", "-p", "5.0", "in.ms", "out.npy"])
+    assert (a.num_pixels, a.pixel_size, a.dask_scheduler, a.row_chunks, a.freq_chunks) == (2048, 5.0, None, 1, None)
+    a = pipeline_app.get_parser().parse_args(["--num-pixels", "64", "--pixel-size", "1", "-d", "tcp://x:1", "-rc", "2",
+                                              "-fc", "3", "in.ms", "out"])
+    assert (a.dask_scheduler, a.row_chunks, a.freq_chunks) == ("tcp://x:1", 2, 3)
+    b = uvw_reorder_app.get_parser().parse_args(["-t", "3000", "3000", "6000", "-n", "4", "-m", "10000", "in.ms"])
+    assert b.tile_size == [3000.0, 3000.0, 6000.0] and b.num_time_intervals == 4 and b.max_vis_per_chunk == 10000
+    with pytest.raises(SystemExit):
+        pipeline_app.get_parser().parse_args(["in.ms", "out.npy"])  # -n and -p are required

@@ -100,7 +100,7 @@ constexpr int kMaxG = 4;
 // A: (G*8, M) row k, column m (k-major list of columns of A);  B: (G*8, N);  D: (M, N) row-major.
 template <int M, int N, bool TS>
 __global__ void __launch_bounds__(128) check_kernel(const float* __restrict__ A, const float* __restrict__ B, float* __restrict__ D,
-                                                    int G, uint32_t idesc, int reps, long long* cycles) {
+                                                    int G, uint32_t idesc, int reps, long long* cycles, int variant) {
   extern __shared__ __align__(1024) unsigned char smem[];
   __shared__ uint32_t s_tmem;
   __shared__ __align__(8) unsigned long long s_bar;
@@ -117,12 +117,20 @@ __global__ void __launch_bounds__(128) check_kernel(const float* __restrict__ A,
   // operands -> shared memory in the canonical MN-major layout
   for (int i = tid; i < G * 8 * N; i += 128) {
     const int k = i / N, n = i % N, g = k / 8;
-    sB[g * N * 8 + (n / 4) * 32 + (k % 8) * 4 + (n % 4)] = B[(size_t)k * N + n];
+    if (variant & 8) sB[g * N * 8 + (n / 8) * 64 + ((k % 8) / 4) * 32 + (n % 8) * 4 + (k % 4)] = B[(size_t)k * N + n];  // K-major: 8 n-rows x 16 B core matrices, the two k-chunks 128 B apart, n-groups 256 B apart
+    else sB[g * N * 8 + (n / 4) * 32 + (k % 8) * 4 + (n % 4)] = B[(size_t)k * N + n];
+  }
+  if (variant & 1) {  // sentinel in the accumulator columns
+    uint32_t one[8];
+    for (int k = 0; k < 8; ++k) one[k] = __float_as_uint(1.0f + k);
+    for (int c = 0; c < N; c += 8) tmem_st8(tbase + ((uint32_t)(warp * 32) << 16) + dcol + c, one);
+    tmem_wait_st();
   }
   if (!TS)
     for (int i = tid; i < G * 8 * M; i += 128) {
       const int k = i / M, m = i % M, g = k / 8;
-      sA[g * M * 8 + (m / 4) * 32 + (k % 8) * 4 + (m % 4)] = A[(size_t)k * M + m];
+      if (variant & 16) sA[g * M * 8 + (m / 4) * 32 + (k % 8) * 4 + (m % 4)] = A[(size_t)k * M + m];  // MN-major
+      else sA[g * M * 8 + (m / 8) * 64 + ((k % 8) / 4) * 32 + (m % 8) * 4 + (k % 4)] = A[(size_t)k * M + m];  // K-major
     }
   if (TS && tid < M) {  // thread = row of A: 8 columns per k-group
     for (int g = 0; g < G; ++g) {
@@ -141,11 +149,15 @@ __global__ void __launch_bounds__(128) check_kernel(const float* __restrict__ A,
     t0 = clock64();
     for (int r = 0; r < reps; ++r)
       for (int g = 0; g < G; ++g) {
-        const uint64_t bd = make_sdesc(smem_u32(sB + g * N * 8), 128u * (N / 4), 128u);
+        uint64_t bd = make_sdesc(smem_u32(sB + g * N * 8), 128u * (N / 4), 128u);
+        if (variant & 4) bd = make_sdesc(smem_u32(sB + g * N * 8), 128u, 128u * (N / 4));
+        if (variant & 8) bd = make_sdesc(smem_u32(sB + g * N * 8), 128u, 256u);
+        if (variant & 2) continue;
         if (TS) {
-          mma_ts(tbase + dcol, tbase + acol + 8 * g, bd, idesc, (r | g) != 0);
+          mma_ts(tbase + dcol + ((variant & 32) ? (g & 1) * N : 0), tbase + acol + 8 * g, bd, idesc, ((variant & 32) ? (r | (g >> 1)) : (r | g)) != 0);
         } else {
-          const uint64_t ad = make_sdesc(smem_u32(sA + g * M * 8), 128u * (M / 4), 128u);
+          const uint64_t ad = (variant & 16) ? make_sdesc(smem_u32(sA + g * M * 8), 128u * (M / 4), 128u)
+                                             : make_sdesc(smem_u32(sA + g * M * 8), 128u, 256u);
           mma_ss(tbase + dcol, ad, bd, idesc, (r | g) != 0);
         }
       }
@@ -173,6 +185,93 @@ __global__ void __launch_bounds__(128) check_kernel(const float* __restrict__ A,
   if (warp == 0) tmem_dealloc(tbase, 512);
 }
 
+
+__device__ __forceinline__ uint32_t elect_one() {
+  uint32_t pred;
+  asm volatile("{\n\t.reg .pred p;\n\telect.sync _|p, 0xffffffff;\n\tselp.u32 %0, 1, 0, p;\n\t}" : "=r"(pred)::"memory");
+  return pred;
+}
+
+// Issue rate with the descriptors prepared outside the loop: warp 0 enters uniformly, one elected lane issues
+// 8 mma per iteration (4 k-groups x 2 accumulators when ALT, else one accumulator).
+template <int M, int N, bool TS, bool ALT>
+__global__ void __launch_bounds__(128) rate_kernel(int reps, long long* cycles, float* sink) {
+  extern __shared__ __align__(1024) unsigned char smem[];
+  __shared__ uint32_t s_tmem;
+  __shared__ __align__(8) unsigned long long s_bar;
+  const int tid = threadIdx.x, warp = tid >> 5;
+  for (int i = tid; i < (4 * 256 * 8 + 4 * 128 * 8); i += 128) reinterpret_cast<float*>(smem)[i] = 0.001f * (i & 63);
+  if (warp == 0) tmem_alloc(smem_u32(&s_tmem), 512);
+  if (tid == 0) mbar_init(smem_u32(&s_bar), 1);
+  fence_async_smem();
+  fence_before();
+  __syncthreads();
+  fence_after();
+  const uint32_t tbase = s_tmem;
+  const uint32_t idesc = make_idesc(M, N, 0, 0);
+  if (warp == 0) {
+    uint64_t bd[4], ad[4];
+    for (int g = 0; g < 4; ++g) {
+      bd[g] = make_sdesc(smem_u32(smem + g * N * 32), 128u, 256u);
+      ad[g] = make_sdesc(smem_u32(smem + 4 * 256 * 32 + g * M * 32), 128u, 256u);
+    }
+    const uint32_t d0 = tbase, d1 = tbase + (ALT ? N : 0), a0 = tbase + 256;
+    __syncwarp();
+    const long long t0 = clock64();
+    if (elect_one()) {
+      for (int r = 0; r < reps; ++r) {
+#pragma unroll
+        for (int g = 0; g < 4; ++g) {
+          if (TS) {
+            mma_ts(d0, a0 + 8 * g, bd[g], idesc, 1);
+            mma_ts(d1, a0 + 32 + 8 * g, bd[g], idesc, 1);
+          } else {
+            mma_ss(d0, ad[g], bd[g], idesc, 1);
+            mma_ss(d1, ad[g], bd[g], idesc, 1);
+          }
+        }
+      }
+      commit(smem_u32(&s_bar));
+    }
+    __syncwarp();
+    const long long t1 = clock64();
+    mbar_wait(smem_u32(&s_bar), 0);
+    const long long t2 = clock64();
+    if (tid == 0) {
+      cycles[0] = t1 - t0;
+      cycles[1] = t2 - t0;
+    }
+  }
+  __syncthreads();
+  fence_after();
+  uint32_t v[16];
+  tmem_ld16(tbase + ((uint32_t)(warp * 32) << 16), v);
+  tmem_wait_ld();
+  sink[tid] = __uint_as_float(v[0]);
+  fence_before();
+  __syncthreads();
+  if (warp == 0) tmem_dealloc(tbase, 512);
+}
+
+template <int M, int N, bool TS, bool ALT>
+static void run_rate(int reps) {
+  long long* cyc;
+  float* sink;
+  CK(cudaMallocManaged(&cyc, 16));
+  CK(cudaMalloc(&sink, 128 * 4));
+  const int smem = 4 * 256 * 32 + 4 * 128 * 32;
+  auto kern = rate_kernel<M, N, TS, ALT>;
+  CK(cudaFuncSetAttribute(kern, cudaFuncAttributeMaxDynamicSharedMemorySize, smem));
+  for (int it = 0; it < 2; ++it) {
+    kern<<<1, 128, smem>>>(reps, cyc, sink);
+    CK(cudaDeviceSynchronize());
+  }
+  printf("lean rate %s M=%3d N=%3d %s: %5d mma: issue %.2f cycles per mma, complete %.2f cycles per mma\n", TS ? "TS" : "SS", M, N,
+         ALT ? "2 accumulators" : "1 accumulator ", reps * 8, (double)cyc[0] / (reps * 8), (double)cyc[1] / (reps * 8));
+  cudaFree(cyc);
+  cudaFree(sink);
+}
+
 static float tf32_trunc(float x) {
   uint32_t u;
   memcpy(&u, &x, 4);
@@ -189,7 +288,7 @@ static float tf32_round(float x) {
 }
 
 template <int M, int N, bool TS>
-static void run_check(int G, int reps, bool verbose) {
+static void run_check(int G, int reps, bool verbose, int variant = 0) {
   const int K = G * 8;
   std::vector<float> A((size_t)K * M), B((size_t)K * N), D((size_t)M * N, -1.f);
   uint32_t s = 12345u + M * 7 + N * 3 + TS;
@@ -208,11 +307,11 @@ static void run_check(int G, int reps, bool verbose) {
   CK(cudaMemcpy(dA, A.data(), A.size() * 4, cudaMemcpyHostToDevice));
   CK(cudaMemcpy(dB, B.data(), B.size() * 4, cudaMemcpyHostToDevice));
   CK(cudaMemset(dD, 0xff, D.size() * 4));
-  const uint32_t idesc = make_idesc(M, N, TS ? 0 : 1, 1);
+  const uint32_t idesc = make_idesc(M, N, (variant & 16) ? 1 : 0, (variant & 8) ? 0 : 1);
   const int smem = kMaxG * 256 * 8 * 4 + kMaxG * 128 * 8 * 4;
   auto kern = check_kernel<M, N, TS>;
   CK(cudaFuncSetAttribute(kern, cudaFuncAttributeMaxDynamicSharedMemorySize, smem));
-  kern<<<1, 128, smem>>>(dA, dB, dD, G, idesc, reps, cyc);
+  kern<<<1, 128, smem>>>(dA, dB, dD, G, idesc, reps, cyc, variant);
   cudaError_t e = cudaDeviceSynchronize();
   if (e != cudaSuccess) {
     printf("%s M=%d N=%d G=%d: kernel failed: %s\n", TS ? "TS" : "SS", M, N, G, cudaGetErrorString(e));
@@ -233,14 +332,16 @@ static void run_check(int G, int reps, bool verbose) {
         err_r += (d - rr) * (d - rr);
         nrm += rt * rt;
       }
+    printf("variant %2d ", variant);
     printf("check %s M=%3d N=%3d K=%2d: rel err vs truncated operands %.3e, vs rounded operands %.3e  %s\n", TS ? "TS" : "SS", M,
            N, K, sqrt(err_t / nrm), sqrt(err_r / nrm), sqrt(err_t / nrm) < 1e-5 || sqrt(err_r / nrm) < 1e-5 ? "OK" : "MISMATCH");
-    if (verbose && sqrt(err_t / nrm) > 1e-5)
+    if (verbose && !(sqrt(err_t / nrm) < 1e-5))
       for (int m = 0; m < 4; ++m) {
         for (int n = 0; n < 8; ++n) printf(" %9.5f", D[(size_t)m * N + n]);
         printf("\n");
       }
   } else {
+    printf("variant %2d ", variant);
     printf("rate  %s M=%3d N=%3d: %d back-to-back mma in %lld cycles = %.2f cycles per mma (K = 8)\n", TS ? "TS" : "SS", M, N,
            reps * G, *cyc, (double)*cyc / (reps * G));
   }
@@ -251,28 +352,51 @@ static void run_check(int G, int reps, bool verbose) {
 }
 
 int main(int argc, char** argv) {
+  // variant bits: 1 sentinel in D, 2 skip the mma, 4 MN-major B with LBO/SBO swapped, 8 K-major B (the layout that
+  // works; MN-major no-swizzle operands gave all-zero products on B200 / CUDA 12.9), 16 MN-major A (SS), 32 two
+  // alternating accumulators (rate only)
   const char* mode = argc > 1 ? argv[1] : "all";
   const bool all = !strcmp(mode, "all");
-  if (all || !strcmp(mode, "check_ss")) {
-    run_check<64, 16, false>(1, 1, true);
-    run_check<64, 16, false>(4, 1, true);
-    run_check<128, 32, false>(4, 1, true);
+  if (!strcmp(mode, "diag")) {
+    for (int v : {1, 3, 0, 4, 8, 9}) run_check<128, 32, true>(1, 1, true, v);
+    for (int v : {16, 20, 24, 8}) run_check<64, 16, false>(1, 1, true, v);
   }
-  if (all || !strcmp(mode, "check_ts")) {
-    run_check<128, 32, true>(1, 1, true);
-    run_check<128, 32, true>(4, 1, true);
-    run_check<128, 16, true>(4, 1, true);
+  if (all || !strcmp(mode, "check")) {
+    run_check<64, 16, false>(1, 1, true, 8);
+    run_check<64, 16, false>(4, 1, true, 8);
+    run_check<128, 32, false>(4, 1, true, 8);
+    run_check<128, 32, true>(1, 1, true, 8);
+    run_check<128, 32, true>(4, 1, true, 8);
+    run_check<128, 16, true>(4, 1, true, 8);
+    run_check<128, 64, true>(4, 1, true, 8);
   }
-  if (all || !strcmp(mode, "rate")) {
-    for (int reps : {64, 512}) {
-      run_check<64, 16, false>(4, reps, false);
-      run_check<128, 16, false>(4, reps, false);
-      run_check<128, 32, false>(4, reps, false);
-      run_check<128, 64, false>(4, reps, false);
-      run_check<128, 16, true>(4, reps, false);
-      run_check<128, 32, true>(4, reps, false);
-      run_check<128, 64, true>(4, reps, false);
+  if (all || !strcmp(mode, "lean")) {
+    for (int reps : {32, 256}) {
+      run_rate<64, 16, false, false>(reps);
+      run_rate<64, 16, false, true>(reps);
+      run_rate<128, 16, false, true>(reps);
+      run_rate<128, 32, false, true>(reps);
+      run_rate<128, 16, true, false>(reps);
+      run_rate<128, 16, true, true>(reps);
+      run_rate<128, 32, true, false>(reps);
+      run_rate<128, 32, true, true>(reps);
+      run_rate<128, 64, true, true>(reps);
+      run_rate<128, 128, true, true>(reps);
+      run_rate<128, 256, true, false>(reps);
     }
+  }
+  if (!strcmp(mode, "rate")) {
+    for (int reps : {64, 512})
+      for (int v : {8, 40}) {
+        run_check<64, 16, false>(4, reps, false, v);
+        run_check<128, 16, false>(4, reps, false, v);
+        run_check<128, 32, false>(4, reps, false, v);
+        run_check<128, 64, false>(4, reps, false, v);
+        run_check<128, 16, true>(4, reps, false, v);
+        run_check<128, 32, true>(4, reps, false, v);
+        run_check<128, 64, true>(4, reps, false, v);
+        run_check<128, 128, true>(4, reps, false, v);
+      }
   }
   return 0;
 }

@@ -12,6 +12,10 @@ numpy are exercised:
   stokes_*.npz   StokesIGridderInput.from_measurement_set_reader / effective_weights /
                  integrate_weighted_images (src/ska_sdp_cip/invert.py:72-116, 200-209)
   partition.npz  balanced_chunk_bounds (src/ska_sdp_cip/measurement_set.py:361-391)
+  tile_ops.npz   split_tile, concatenate_tiles, rechunk_tiles_on_disk (src/ska_sdp_cip/uvw_tiling/tile.py:127-265)
+  reorder_small.npz  reorder_time_interval + rechunk_tile_chunk_group run interval by interval
+                 (src/ska_sdp_cip/uvw_tiling/reorder.py:129-183): per tile, the visibilities in file order
+  task_metrics.json  TaskMetrics(...).to_json of a synthetic task stream (src/ska_sdp_cip/task_metrics.py)
 
 /root/reference does not exist on the GPU box, so the outputs are committed as fixtures.
 Run:  python tools/make_golden.py
@@ -158,7 +162,125 @@ def main():
     arr = {f"b_{a}_{b}_{k}": np.array(list(balanced_chunk_bounds(a, b, k)), dtype=np.int64) for a, b, k in cases}
     np.savez_compressed(OUT / "partition.npz", **arr)
     print("partition:", len(arr), "cases")
+    golden_tile_ops()
+    golden_reorder()
+    golden_task_metrics()
     del ref
+
+
+def random_tile(Tile, seed, nrows, nchan=40):
+    rng = np.random.default_rng(seed)
+    start = rng.integers(0, nchan // 2, size=nrows)
+    stop = start + rng.integers(1, nchan // 2, size=nrows)
+    nvis = int((stop - start).sum())
+    vis = (rng.normal(size=nvis) + 1j * rng.normal(size=nvis)).astype(np.complex64)
+    return Tile(coords=(1, -2, 3), uvw=rng.normal(size=(nrows, 3)), visibilities=vis,
+                channel_start_indices=start.astype(int), channel_stop_indices=stop.astype(int))
+
+
+TILE_OPS_LIMITS = (1, 7, 19, 20, 64, 333, 10**6)
+
+
+def golden_tile_ops():
+    import tempfile
+    from ska_sdp_cip.uvw_tiling.tile import Tile, concatenate_tiles, rechunk_tiles_on_disk, split_tile
+    out = {}
+    tile = random_tile(Tile, 31, 97)
+    for limit in TILE_OPS_LIMITS:
+        chunks = split_tile(tile, limit)
+        out[f"split_{limit}_rows"] = np.array([c.num_rows for c in chunks], dtype=np.int64)
+        out[f"split_{limit}_nvis"] = np.array([c.num_visibilities for c in chunks], dtype=np.int64)
+    parts = [random_tile(Tile, 40 + i, n) for i, n in enumerate((5, 1, 30, 12, 3, 50))]
+    cat = concatenate_tiles(parts)
+    out["cat_uvw"], out["cat_vis"] = cat.uvw, cat.visibilities
+    out["cat_start"], out["cat_stop"] = cat.channel_start_indices, cat.channel_stop_indices
+    for limit in (50, 200, 10**6):
+        with tempfile.TemporaryDirectory() as d:
+            d = Path(d)
+            paths = []
+            for i, t in enumerate(parts):
+                paths.append(d / f"in{i}.npz")
+                t.save_npz(paths[-1])
+            written = rechunk_tiles_on_disk(paths, d, "tile_x", max_vis_per_chunk=limit)
+            out[f"rechunk_{limit}_names"] = np.array([w.name for w in written])
+            out[f"rechunk_{limit}_nvis"] = np.array([Tile.load_npz(w).num_visibilities for w in written], dtype=np.int64)
+            out[f"rechunk_{limit}_rows"] = np.array([Tile.load_npz(w).num_rows for w in written], dtype=np.int64)
+    np.savez_compressed(OUT / "tile_ops.npz", **out)
+    print("tile_ops:", len(out), "arrays")
+
+
+REORDER_CASE = dict(nrow=600, nchan=24, seed=51, tile_size=(1500.0, 1500.0, 3000.0), intervals=3, limit=700)
+
+
+def reorder_reader(seed, nrow, nchan):
+    rng = np.random.default_rng(seed)
+    uvw = rng.normal(size=(nrow, 3)) * np.array([1500.0, 1500.0, 200.0])
+    vis = (rng.normal(size=(nrow, nchan, 4)) + 1j * rng.normal(size=(nrow, nchan, 4))).astype(np.complex64)
+    freqs = 1.0e9 + 2.0e6 * np.arange(nchan)
+    return uvw, vis, freqs
+
+
+def golden_reorder():
+    """The reference's two reorder passes without dask: tile files per interval in time order, then the rechunk
+    of each tile with its interval files taken in interval order (the reference globs them in directory order,
+    which is not defined; the per-tile visibility SET is)."""
+    import tempfile
+    from ska_sdp_cip.measurement_set import balanced_chunk_bounds
+    from ska_sdp_cip.uvw_tiling import reorder as R
+    from ska_sdp_cip.uvw_tiling.tile import Tile, rechunk_tiles_on_disk
+    from ska_sdp_cip.uvw_tiling.tiling_plan import create_uvw_tile_mapping_sequential
+    c = REORDER_CASE
+    uvw, vis, freqs = reorder_reader(c["seed"], c["nrow"], c["nchan"])
+
+    class IntervalReader:
+        def __init__(self, a, b): self.a, self.b = a, b
+        def uvw(self): return uvw[self.a:self.b]
+        def visibilities(self): return vis[self.a:self.b]
+
+    out = {}
+    with tempfile.TemporaryDirectory() as d:
+        d = Path(d)
+        present = []
+        for i, (a, b) in enumerate(balanced_chunk_bounds(0, c["nrow"], c["intervals"])):
+            rd = IntervalReader(a, b)
+            mapping = create_uvw_tile_mapping_sequential(rd.uvw(), c["tile_size"], freqs)
+            for key in R.reorder_time_interval(rd, mapping, d, interval_index=i):
+                if key not in present:
+                    present.append(key)
+        out["coords"] = np.array(present, dtype=np.int64)
+        for t, key in enumerate(present):
+            u, v, w = key
+            base = f"tile_iu{u:+03d}_iv{v:+03d}_iw{w:+03d}"
+            inputs = sorted(d.glob(base + "_interval*.npz"))
+            written = rechunk_tiles_on_disk(inputs, d, base, max_vis_per_chunk=c["limit"])
+            tiles = [Tile.load_npz(p) for p in written]
+            out[f"t{t}_names"] = np.array([p.name for p in written])
+            out[f"t{t}_vis"] = np.concatenate([x.visibilities for x in tiles])
+            out[f"t{t}_uvw"] = np.concatenate([x.uvw for x in tiles])
+            out[f"t{t}_start"] = np.concatenate([x.channel_start_indices for x in tiles])
+            out[f"t{t}_nvis"] = np.array([x.num_visibilities for x in tiles], dtype=np.int64)
+    np.savez_compressed(OUT / "reorder_small.npz", **out)
+    print("reorder_small:", len(present), "tiles")
+
+
+TASK_STREAM = [
+    {"key": "from_measurement_set_reader-0a1b", "worker": "tcp://10.0.0.1:4000", "status": "OK",
+     "startstops": ({"action": "compute", "start": 10.0, "stop": 11.5},)},
+    {"key": "worker_ducc_invert-77ff", "worker": "tcp://10.0.0.2:4000", "status": "OK",
+     "startstops": ({"action": "transfer", "start": 11.5, "stop": 11.75, "source": "tcp://10.0.0.1:4000"},
+                    {"action": "compute", "start": 12.0, "stop": 15.0})},
+    {"key": "integrate_weighted_images-multi-dash-9c", "worker": "tcp://10.0.0.1:4000", "status": "error",
+     "startstops": ({"action": "compute", "start": 15.0, "stop": 15.25},
+                    {"action": "transfer", "start": 14.5, "stop": 14.75})},
+]
+
+
+def golden_task_metrics():
+    import json
+    from ska_sdp_cip.task_metrics import TaskMetrics
+    (OUT / "task_metrics.json").write_text(json.dumps(
+        {"stream": TASK_STREAM, "expected": json.loads(TaskMetrics(TASK_STREAM).to_json())}, indent=1))
+    print("task_metrics: ok")
 
 
 if __name__ == "__main__":
