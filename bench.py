@@ -4,16 +4,20 @@
     python bench.py [--gpus N] [--steps K] [--warmup W] [--impl reference] [--times T]
 
 A "step" is one complete invert (scan, binning, gridding, FFTs, w-screen, correction) of one batch
-of synthetic SKA-Mid AA* visibilities (BASELINE.json configs[1]: 144 dishes = 10,296 baselines x 256
-times x 64 channels = 168.7 M visibilities, 4096^2 image, epsilon 1e-4, w-stacking).  With N > 1
-(launched under torchrun, one rank per GPU) every rank grids its own 256-time shard of a longer
-observation and the partial images are combined by one NCCL reduce-scatter / all-gather around the
-correction: weak scaling, no other collective.
+of synthetic SKA-Mid AA* visibilities.  N = 1: BASELINE.json configs[1] (144 dishes = 10,296 baselines x
+256 times x 64 channels = 168.7 M visibilities, 4096^2 image, epsilon 1e-4, w-stacking).  N > 1 (launched
+under torchrun, one rank per GPU): BASELINE.json configs[3], the stated multi-GPU target -- 10,296
+baselines x 512 times x 256 channels = 1.35e9 visibilities, 16384^2 image, sharded by frequency chunk with
+the reference's partition(1, freq_chunks=N); every rank grids its channels into a partial image and one
+NCCL reduce-scatter / all-gather around the correction combines them: STRONG scaling (the total work is
+fixed).  `--workload cfg1|cfg3` overrides the choice (cfg1 at N > 1 is the weak-scaling run of round 1).
 
 Printed JSON (one line, rank 0): `value` = device-resident inputs, timed with CUDA events on the
 library's stream; `e2e` = the same step through the reference-facing call
 (`ska_sdp_cip.wgridder.ms2dirty` with HOST arrays: pinned host -> device copies and the image read-back
 inside the timed region); `roofline` = the gridding kernel against measured HBM bandwidth;
+`parity` = relative RMS of the timed path's image against the float64 DFT on the 8 source pixels + 1024
+random pixels (each rank transforms its own shard, the sums are all-reduced);
 `cpu_baseline` = the oracle's C/OpenMP w-stacking port on a bounded sample, on this box's host cores.
 `--impl reference` times that CPU port alone (the reference's own gridder, ducc0, is a third-party
 wheel that is not installable here -- see DESIGN.md).
@@ -121,22 +125,41 @@ class ClockSampler:
         return out
 
 
-def workload(times: int):
+def workload(args, world: int = 1, rank: int = 0):
+    """(cfg of the whole job, pixel size, name, uvw of this rank, frequencies of this rank, description)."""
     from ska_sdp_cip import synthetic as S
-    cfg = S.ska_mid(n_times=times)
+    from ska_sdp_cip.measurement_set import balanced_chunk_bounds
+    name = args.workload or ("cfg1" if world == 1 else "cfg3")
+    if name == "cfg3":
+        cfg = S.ska_mid(n_times=512, n_chan=256, num_pixels=16384, dfreq_hz=0.5e6)
+        uvw = S.make_uvw(cfg)
+        px = S.pixel_size_lm(cfg, uvw)
+        c0, c1 = list(balanced_chunk_bounds(0, cfg.n_chan, world))[rank]  # the reference's partition(1, world)
+        desc = (f"{cfg.name}: {cfg.n_baselines} baselines x {cfg.n_times} times x {cfg.n_chan} channels "
+                f"({cfg.n_vis} visibilities in total, {cfg.n_chan // world} channels per GPU), {cfg.num_pixels}^2 image, "
+                f"epsilon {cfg.epsilon}, w-stacking (BASELINE.json configs[3])")
+        return cfg, px, name, uvw, cfg.frequencies()[c0:c1], desc
+    cfg = S.ska_mid(n_times=args.times)
     full = S.ska_mid()  # the pixel size is that of the full 256-time configuration
     px = S.pixel_size_lm(full, S.make_uvw(full, (0, full.n_times)))
-    return cfg, px
+    # rank r observes times [r*T, (r+1)*T) of a world*T-step observation (weak scaling)
+    long_cfg = S.ska_mid(n_times=cfg.n_times * world)
+    uvw = S.make_uvw(long_cfg, (rank * cfg.n_times, (rank + 1) * cfg.n_times))
+    desc = (f"{cfg.name}: {cfg.n_baselines} baselines x {cfg.n_times} times x {cfg.n_chan} channels per GPU "
+            f"({cfg.n_vis} visibilities), {cfg.num_pixels}^2 image, epsilon {cfg.epsilon}, w-stacking "
+            f"(BASELINE.json configs[1])")
+    return cfg, px, name, uvw, cfg.frequencies(), desc
 
 
-def cpu_port_rate(cfg, px, sample_times: int, repeats: int = 1):
-    """The oracle's C/OpenMP w-stacking port on the first `sample_times` time steps of the workload."""
+def cpu_port_rate(cfg, px, sample_times: int, chan=None, repeats: int = 1):
+    """The oracle's C/OpenMP w-stacking port on the first `sample_times` time steps (channels `chan`) of the
+    workload, full image size.  Returns (Mvis/s, seconds, visibilities, threads)."""
+    import dataclasses
     from oracle import wstack
     from ska_sdp_cip import synthetic as S
-    sub = S.ska_mid(n_times=sample_times)
-    sub.seed = cfg.seed
+    sub = dataclasses.replace(cfg, n_times=sample_times)
     uvw = S.make_uvw(cfg, (0, sample_times))
-    freq = cfg.frequencies()
+    freq = cfg.frequencies() if chan is None else cfg.frequencies()[chan]
     vis, wgt = S.make_vis_numpy(sub, uvw, freq, px)
     wstack.lib()
     best = None
@@ -149,30 +172,52 @@ def cpu_port_rate(cfg, px, sample_times: int, repeats: int = 1):
     return nvis / best / 1e6, best, nvis, wstack.lib().oracle_num_threads()
 
 
+REFERENCE_BUDGET_S = 240.0  # the whole --impl reference run stays within a few minutes
+
+
+def cpu_sample(cfg, wname, world):
+    """Bounded sample of the workload for the CPU port: (time steps, channel slice, description)."""
+    from ska_sdp_cip.measurement_set import balanced_chunk_bounds
+    if wname == "cfg3":
+        c0, c1 = list(balanced_chunk_bounds(0, cfg.n_chan, max(world, 8)))[0]
+        return 2, slice(c0, c1), f"first 2 of {cfg.n_times} time steps x channels {c0}..{c1 - 1} of {cfg.n_chan}"
+    return CPU_SAMPLE_TIMES, None, f"first {CPU_SAMPLE_TIMES} of {cfg.n_times} time steps, all channels"
+
+
 def run_reference(args):
     rank = int(os.environ.get("RANK", "0"))
     if rank != 0:
         return
-    cfg, px = workload(args.times)
-    sample_times = CPU_SAMPLE_TIMES
-    rates = []
+    cfg, px, wname, _uvw, _freq, desc = workload(args, args.gpus, 0)
+    sample_times, chan, sample_desc = cpu_sample(cfg, wname, args.gpus)
+    t_begin = time.perf_counter()
+    # warm-up: W steps of the same sample unless one of them already shows that the budget does not allow it
+    warm_done = 0
+    step_s = None
     for _ in range(args.warmup):
-        cpu_port_rate(cfg, px, 1)
-    t_total = 0.0
-    for _ in range(args.steps):
-        r, dt, nvis, cores = cpu_port_rate(cfg, px, sample_times)
+        _, step_s, _, _ = cpu_port_rate(cfg, px, sample_times, chan)
+        warm_done += 1
+        if step_s * (args.warmup - warm_done + args.steps) > REFERENCE_BUDGET_S:
+            break
+    left = REFERENCE_BUDGET_S - (time.perf_counter() - t_begin)
+    steps = args.steps if step_s is None else max(1, min(args.steps, int(left / max(step_s, 1e-3))))
+    rates, t_total, nvis, cores = [], 0.0, 0, 1
+    for _ in range(steps):
+        r, dt, nvis, cores = cpu_port_rate(cfg, px, sample_times, chan)
         rates.append(r)
         t_total += dt
     value = float(np.mean(rates))
-    sample = (f"first {sample_times} of {cfg.n_times} time steps ({nvis} visibilities) of the same workload, "
-              f"full {cfg.num_pixels}^2 image, per step")
+    sample = f"{sample_desc} ({nvis} visibilities) of the same workload, full {cfg.num_pixels}^2 image, per step"
     line = {"impl": "reference", "metric": METRIC, "value": value, "unit": UNIT, "n_gpus": args.gpus,
-            "steps": args.steps, "warmup": args.warmup, "ms_per_step": 1e3 * t_total / max(args.steps, 1),
-            "higher_is_better": True, "scaling": "weak", "vs_baseline": None, "dtype": "f32", "data": "synthetic",
-            "config": {"workload": f"{cfg.name}: {cfg.n_baselines} baselines x {cfg.n_times} times x {cfg.n_chan} "
-                                   f"channels, {cfg.num_pixels}^2 image, epsilon {cfg.epsilon}, w-stacking",
+            "steps": steps, "warmup": warm_done, "ms_per_step": 1e3 * t_total / max(steps, 1),
+            "higher_is_better": True, "scaling": "weak" if wname == "cfg1" else "strong", "vs_baseline": None,
+            "dtype": "f32", "data": "synthetic",
+            "config": {"workload": desc,
                        "note": "ducc0 (the reference's gridder) is not installable here; this is the oracle's "
-                               "C/OpenMP port of the same algorithm"},
+                               "C/OpenMP port of the same algorithm"
+                               + ("" if (steps, warm_done) == (args.steps, args.warmup) else
+                                  f"; {steps} timed / {warm_done} warm-up steps instead of {args.steps} / {args.warmup} "
+                                  f"to stay within {REFERENCE_BUDGET_S:.0f} s")},
             "cpu_baseline": {"value": value, "unit": UNIT, "cores": cores, "kind": "port", "sample": sample},
             "e2e": {"value": value, "unit": UNIT, "h2d_bytes_per_step": 0, "d2h_bytes_per_step": 0},
             "gpu_launches": 0}
@@ -193,15 +238,16 @@ def run_b200(args):
     if world > 1:
         os.environ.setdefault("NCCL_DEBUG_FILE", "/dev/stderr")  # keep stdout to the one JSON line
         dist.init_process_group("nccl", device_id=dev)
-    cfg, px = workload(args.times)
+    cfg, px, wname, uvw, freq, desc = workload(args, world, rank)
     N = cfg.num_pixels
-    # rank r observes times [r*T, (r+1)*T) of a world*T-step observation (weak scaling)
-    long_cfg = S.ska_mid(n_times=cfg.n_times * world)
-    uvw = S.make_uvw(long_cfg, (rank * cfg.n_times, (rank + 1) * cfg.n_times))
-    freq = cfg.frequencies()
     d_vis, d_wgt = S.make_vis_torch(cfg, uvw, freq, px, dev, seed=1234 + rank)
     d_uvw, d_freq = torch.from_numpy(uvw).to(dev), torch.from_numpy(freq).to(dev)
-    nvis = cfg.n_vis
+    nvis = uvw.shape[0] * freq.shape[0]        # this rank's visibilities
+    total_vis = nvis
+    if world > 1:
+        t = torch.tensor([nvis], dtype=torch.int64, device=dev)
+        dist.all_reduce(t)
+        total_vis = int(t.item())
     ctx = _cabi.Context.get(local)
     stream = torch.cuda.ExternalStream(_cabi.lib().cip_ctx_stream(ctx.handle), device=dev)
     flush_buf = torch.empty(256 << 20, dtype=torch.uint8, device=dev)  # > 126 MB L2
@@ -263,7 +309,24 @@ def run_b200(args):
     launches = ctx_launches(ctx) - l0
     clocks = sampler.stop() if rank == 0 else {}
     timed_reports = list(reports)
-    _, plan = step_device()
+    img, plan = step_device()
+
+    # ---- parity of the timed path: sampled pixels against the float64 DFT ------------------------------
+    parity = None
+    if not args.no_parity:
+        from oracle import dft, dft_torch
+        _, _, _, pi, pj = S.source_list(cfg, px)
+        pix = dft_torch.sample_pixels(N, N, 1024, seed=0, always=np.asarray(pi) * N + np.asarray(pj))
+        got = img.reshape(-1)[torch.from_numpy(pix).to(dev)].to(torch.float64)
+        del img
+        torch.cuda.empty_cache()
+        ref = torch.from_numpy(dft_torch.dft_pixels(d_uvw, d_freq, d_vis, d_wgt, N, N, px, px, pix, device=dev)).to(dev)
+        if world > 1:
+            dist.all_reduce(ref)  # the DFT is linear in the samples: the ranks' partial sums add up
+        parity = {"rel_rms_dft": dft.rel_rms(got.cpu().numpy(), ref.cpu().numpy()), "pixels": int(len(pix)),
+                  "tolerance": 1e-4, "checker": "oracle/dft_torch.py (float64 DFT of all samples of the timed input)"}
+    else:
+        del img
 
     # ---- e2e: host buffers through the public call ------------------------------------------
     h_vis = torch.empty(d_vis.shape, dtype=d_vis.dtype, pin_memory=True)
@@ -299,6 +362,7 @@ def run_b200(args):
     if world == 1:
         step_host(with_report=True)  # untimed: stage breakdown of one e2e step, for information
     h2d = int(n_vis_np.nbytes + n_wgt_np.nbytes + uvw.nbytes + freq.nbytes)
+    del h_vis, h_wgt, n_vis_np, n_wgt_np
     d2h = int(N * N * 4)
 
     if rank != 0:
@@ -318,21 +382,21 @@ def run_b200(args):
     # ---- CPU baseline on a bounded sample -----------------------------------------------------
     cpu = None
     if not args.no_cpu and world == 1:  # rank 0 at N = 1 only
-        r, dt, nv_s, cores = cpu_port_rate(cfg, px, CPU_SAMPLE_TIMES)
+        st_, ch_, sd_ = cpu_sample(cfg, wname, world)
+        r, dt, nv_s, cores = cpu_port_rate(cfg, px, st_, ch_)
         cpu = {"value": r, "unit": UNIT, "cores": cores, "kind": "port",
-               "sample": f"first {CPU_SAMPLE_TIMES} of {cfg.n_times} time steps ({nv_s} visibilities), full {N}^2 image, "
-                         f"{dt:.1f} s"}
-    total_vis = nvis * world
+               "sample": f"{sd_} ({nv_s} visibilities), full {N}^2 image, {dt:.1f} s"}
     line = {
         "metric": METRIC, "value": total_vis * args.steps / ms_dev / 1e3, "unit": UNIT, "n_gpus": world,
         "steps": args.steps, "warmup": args.warmup, "ms_per_step": ms_dev / args.steps, "higher_is_better": True,
-        "scaling": "weak", "vs_baseline": None, "dtype": "f32", "data": "synthetic",
-        "config": {"workload": f"{cfg.name}: {cfg.n_baselines} baselines x {cfg.n_times} times x {cfg.n_chan} channels "
-                               f"per GPU ({nvis} visibilities), {N}^2 image, epsilon {cfg.epsilon}, w-stacking",
+        "scaling": "weak" if wname == "cfg1" else "strong", "vs_baseline": None, "dtype": "f32", "data": "synthetic",
+        "config": {"workload": desc,
                    "sigma": plan["sigma"], "support": plan["support"], "nu": plan["nu"], "nv": plan["nv"],
                    "nplanes": plan["nplanes"], "l2": "256 MB buffer written between iterations; inputs 2 GB >> L2",
-                   "sharding": "time ranges per rank, NCCL reduce-scatter + all-gather of the dirty image" if world > 1
-                   else "single GPU"},
+                   "sharding": ("single GPU" if world == 1 else
+                                ("frequency chunks of the reference's partition(1, N)" if wname == "cfg3" else
+                                 "time ranges per rank") + ", NCCL reduce-scatter + all-gather of the dirty image")},
+        "parity": parity,
         "e2e": {"value": total_vis * e2e_steps / ms_e2e / 1e3, "unit": UNIT, "h2d_bytes_per_step": h2d,
                 "d2h_bytes_per_step": d2h, "steps": e2e_steps,
                 "stage_ms": {k: float(np.mean([r[k] for r in host_reports])) for k in
@@ -364,7 +428,11 @@ def main():
     ap.add_argument("--warmup", type=int, default=3)
     ap.add_argument("--impl", default="b200", choices=["b200", "reference"])
     ap.add_argument("--times", type=int, default=256, help="time steps per GPU (256 = BASELINE.json configs[1])")
+    ap.add_argument("--workload", default=None, choices=["cfg1", "cfg3"],
+                    help="cfg1 = BASELINE.json configs[1] per GPU (default at N = 1), cfg3 = configs[3] sharded by "
+                         "frequency chunk (default at N > 1)")
     ap.add_argument("--no-cpu", action="store_true", help="skip the CPU baseline leg")
+    ap.add_argument("--no-parity", action="store_true", help="skip the sampled-pixel DFT check of the timed path")
     ap.add_argument("--verbose", action="store_true", help="per-step host timings on stderr")
     args = ap.parse_args()
     # stdout carries exactly one JSON line: libraries that write to file descriptor 1 behind Python's back (the

@@ -1,0 +1,62 @@
+"""Run under torchrun (one rank per GPU): the N > 1 path of dask_invert_measurement_set(client=None) over real
+NCCL -- reference partition, round-robin shards, common plan, reduce-scatter of the uncorrected images,
+per-rank correction, all-gather -- compared on rank 0 with (a) the single-GPU image of the concatenated
+input and (b) the float64 DFT.  Prints one JSON line; exit code 1 on a tolerance failure.
+Used by tests/test_gpu_nccl.py and by hand:  torchrun --nproc-per-node 2 tests/nccl_parity_main.py"""
+import json
+import os
+import sys
+from pathlib import Path
+
+import numpy as np
+
+ROOT = Path(__file__).resolve().parent.parent
+sys.path.insert(0, str(ROOT))
+sys.path.insert(0, str(ROOT / "ska-sdp-continuum-imaging-pipeline_b200"))
+
+
+def main():
+    import torch
+    import torch.distributed as dist
+    from oracle import dft, stokes
+    from ska_sdp_cip import synthetic as S
+    from ska_sdp_cip.invert import dask_invert_measurement_set, invert_measurement_set
+    from ska_sdp_cip.measurement_set import ArrayMeasurementSetReader
+
+    local = int(os.environ.get("LOCAL_RANK", "0"))
+    torch.cuda.set_device(local)
+    dist.init_process_group("nccl", device_id=torch.device("cuda", local))
+    rank, world = dist.get_rank(), dist.get_world_size()
+    results = {}
+    for name, npix, n_times, n_chan, row_chunks, freq_chunks in (("even", 256, 6, 16, 1, None),
+                                                                 ("ragged", 250, 5, 7, 3, 2)):
+        cfg = S.meerkat_like(num_pixels=npix)
+        cfg.n_times, cfg.n_chan = n_times, n_chan
+        uvw = S.make_uvw(cfg)
+        freq = cfg.frequencies()
+        px = S.pixel_size_lm(cfg, uvw)
+        vis, wgt = S.make_vis_numpy(cfg, uvw, freq, px)
+        vis4, flags4, wgt4 = S.four_pol(vis, wgt)
+        reader = ArrayMeasurementSetReader(uvw, freq, vis4, flags4, wgt4)
+        asec = S.lm_to_asec(px)
+        img = dask_invert_measurement_set(reader, None, npix, asec, row_chunks=row_chunks, freq_chunks=freq_chunks)
+        if rank == 0:
+            single = invert_measurement_set(reader, npix, asec)
+            # the reference's arithmetic around the gridder (invert.py:78-184) with the DFT in its place
+            v, f, w = stokes.stokes_i(vis4, flags4, wgt4)
+            effw = stokes.effective_weights(f, w)
+            px_used = stokes.pixel_size_lm(asec)
+            ref = dft.dft_dirty(uvw, freq, v, effw, npix, npix, px_used, px_used) / effw.sum()
+            results[name] = {"vs_single_gpu": dft.rel_rms(img, single), "vs_dft": dft.rel_rms(img, ref),
+                             "active": int((effw != 0).sum()), "shape": list(img.shape), "world": world}
+    ok = True
+    if rank == 0:
+        ok = all(r["vs_single_gpu"] <= 2e-6 and r["vs_dft"] <= 1e-4 for r in results.values())
+        print(json.dumps({"nccl_parity": results, "ok": ok}), flush=True)
+    dist.barrier()
+    dist.destroy_process_group()
+    sys.exit(0 if ok else 1)
+
+
+if __name__ == "__main__":
+    main()

@@ -114,3 +114,22 @@ def test_plan_oracle_basic_properties():
     assert oplan.ES_TABLE[p.sigma][p.W][1] <= 1e-4 / 3
     # planes are centred on the data range
     assert abs((p.w0 + 0.5 * (p.nplanes - 1) * p.dw) - 500.0) < 1e-9
+
+
+def test_torch_dft_checker_is_pinned_to_the_dft_oracle():
+    """oracle/dft_torch.py (used on the device for the BASELINE-size parity checks) against oracle/dft.py."""
+    from oracle import dft_torch
+    nx, ny, px, py = 96, 64, 2.1e-4, 1.7e-4
+    rng = np.random.default_rng(11)
+    uvw = rng.normal(size=(700, 3)) * np.array([900.0, 700.0, 150.0])
+    freq = 1.0e9 + 3.0e6 * np.arange(5)
+    vis = (rng.normal(size=(700, 5)) + 1j * rng.normal(size=(700, 5))).astype(np.complex64)
+    wgt = rng.uniform(0.0, 2.0, size=(700, 5)).astype(np.float32)
+    pix = dft_torch.sample_pixels(nx, ny, 200, seed=3, always=[0, nx * ny - 1, (nx // 2) * ny + ny // 2])
+    ref = dft.dft_dirty(uvw, freq, vis, wgt, nx, ny, px, py, pixels=pix)
+    got = dft_torch.dft_pixels(uvw, freq, vis, wgt, nx, ny, px, py, pix, rows_per_block=97)
+    assert dft.rel_rms(got, ref) < 1e-12
+    sub = dft_torch.dft_pixels(uvw, freq, vis, wgt, nx, ny, px, py, pix, row_step=7)
+    assert dft.rel_rms(sub, dft.dft_dirty(uvw[::7], freq, vis[::7], wgt[::7], nx, ny, px, py, pixels=pix)) < 1e-12
+    assert dft.rel_rms(dft_torch.dft_pixels(uvw, freq, vis, None, nx, ny, px, py, pix),
+                       dft.dft_dirty(uvw, freq, vis, None, nx, ny, px, py, pixels=pix)) < 1e-12
