@@ -1,18 +1,23 @@
-// Kernel 1 (gridder side): binning of (row, channel) visibilities into uv tiles and w-plane
-// windows -- stage G1 of SURVEY.md section 8a, the work ducc0.wgridder.ms2dirty does internally
-// before gridding (reference call site src/ska_sdp_cip/invert.py:170-183).
+// Kernel 1 (gridder side): counting sort of (row, channel) visibilities into uv tiles, w-plane windows and
+// register-window lattice positions -- stage G1 of SURVEY.md section 8a, the work ducc0.wgridder.ms2dirty does
+// internally before gridding (reference call site src/ska_sdp_cip/invert.py:170-183).
 //
-// Per row the channels are run-length encoded by their (window, tile_u, tile_v) key (one warp per
-// row, ballot on "key differs from the previous channel"); the runs are ordered by key with a
-// stable LSD radix sort, so inside a bin they stay in (row, channel) order and the accumulation
-// order of the gridder is reproducible; the sorted runs are then expanded into 24-byte
-// gridder-ready records (all float64 coordinate arithmetic happens here, once) and cut into work
-// items of at most kItemVis records.
+// The sort key of a sample is dense: (window, tile_u, tile_v, lattice_u, lattice_v); all samples of one key share
+// one 8 x 8 x 8 accumulator window of the gridder.  Three passes over the samples' geometry, no sort of anything:
+//   1. histogram   one warp per row, lanes stride the channels; a maximal stretch of equal keys inside a
+//                  32-channel chunk (a "segment") adds its length to count[key] with one atomic;
+//   2. scan        count -> padded k-groups of 8 records and jobs per key, exclusive prefix over the key table
+//                  (tile sums, one-CTA scan of the sums, apply); the apply pass leaves the first record position
+//                  of every key in the table, writes the jobs (key order = window-major) and the zero records
+//                  that pad every key's group to whole k-groups;
+//   3. records     one warp per row again: all float64 coordinate arithmetic of the gridder happens here, once;
+//                  each segment reserves its positions with one atomic on the key's cursor and writes the
+//                  gridder-ready records (16 bytes packed on the float32 W <= 8 path, else 32).
+// Nothing is read back by the host: sizes are capacities, the totals and an overflow flag stay on the device
+// (mirrored into mapped host memory), and every consumer skips its work when the flag is set; the caller checks it
+// once after the whole call has drained, grows the buffers and repeats the call (never in steady state).
 #include <algorithm>
 #include <cstdlib>
-
-#include <cub/device/device_radix_sort.cuh>
-#include <cub/device/device_scan.cuh>
 
 #include "geom.cuh"
 
@@ -20,487 +25,449 @@ namespace cip {
 
 namespace {
 
-// Sort keys are stored as 32-bit words when they fit (they do up to ~ 8192^2-cell grids): the radix sort moves
-// a third fewer bytes per pass.
-__device__ __forceinline__ void store_key(void* keys, int64_t pos, uint64_t key, bool key32) {
-  if (key32) static_cast<uint32_t*>(keys)[pos] = (uint32_t)key;
-  else static_cast<uint64_t*>(keys)[pos] = key;
-}
-__device__ __forceinline__ uint64_t load_key(const void* keys, int64_t pos, bool key32) {
-  return key32 ? (uint64_t)static_cast<const uint32_t*>(keys)[pos] : static_cast<const uint64_t*>(keys)[pos];
-}
-
-// One warp per row, lanes stride the channels; a run is a maximal stretch of channels of one row with
-// the same (window, tile) bin AND the same register-window lattice position inside the tile, so that
-// after the sort all records that share a register window of the gridder's consumer are contiguous.
-//   PASS 0: count the runs of each row.
-//   PASS 1: write the runs (input order) at row_off[row] and their sort keys.
-//   PASS 2: after the sort, expand the samples into gridder-ready records at their sorted positions
-//           (outpos[r] = first record of input-order run r); all float64 coordinate arithmetic of the
-//           gridder happens here.  Reads are row-contiguous, writes contiguous per run.
-template <int PASS, typename R, bool PACK = false>
-__global__ void __launch_bounds__(256, 6) runs_kernel(DevInputs in, GridGeom g, int64_t* __restrict__ row_nruns,
-                                                   const int64_t* __restrict__ row_off, Run* __restrict__ runs,
-                                                   void* __restrict__ keys, const int64_t* __restrict__ outpos,
-                                                   Rec<R>* __restrict__ recs, const double* __restrict__ finv, bool key32) {
-  const int lane = threadIdx.x & 31;
-  const int64_t row = ((int64_t)blockIdx.x * blockDim.x + threadIdx.x) >> 5;
-  if (row >= in.nrow) return;
-  const BinConsts kc = bin_consts(g);
-  const RowGeom rg = row_geom(g, in.uvw[3 * row], in.uvw[3 * row + 1], in.uvw[3 * row + 2]);
-  uint64_t carry = ~0ull;
-  int64_t n = 0;
-  int carry_ch0 = 0;
-  const int64_t base = PASS ? row_off[row] : 0;
-  // record pass: the output positions of the row's first 32 runs are fetched up front (one coalesced load,
-  // in flight together with the samples) instead of one dependent gather after each ballot
-  int64_t pre_out = 0;
-  if (PASS == 2 && lane < row_nruns[row]) pre_out = outpos[base + lane];
-  for (int64_t c0 = 0; c0 < in.nchan; c0 += 32) {
-    const int64_t c = c0 + lane;
-    const bool valid = c < in.nchan;
-    uint64_t key = ~0ull;
-    SampleGeom s;
-    BinCell bc;
-    // record pass: issue the sample loads before the geometry, which does not depend on them (the pass is
-    // bound by memory latency: ncu showed 59 % of the stalls on these loads when they came after the ballot)
-    float2 v = make_float2(0.f, 0.f);
-    float wgt = 0.f;
-    if (PASS == 2 && valid) {
-      v = __ldcs(in.vis + row * in.vstride + c);
-      wgt = in.wgt ? __ldcs(in.wgt + row * in.wstride + c) : 1.0f;
-      if (in.mask && in.mask[row * in.wstride + c] == 0) wgt = 0.0f;
-    }
-    if (valid) {
-      s = sample_geom<PASS == 2>(g, kc, rg, finv[c]);
-      bc = bin_cell(g, kc, s);
-      key = bin_key(g, bc);
-    }
-    uint64_t prev = __shfl_up_sync(0xffffffffu, key, 1);
-    if (lane == 0) prev = carry;
-    const bool start = valid && key != prev;
-    const unsigned m = __ballot_sync(0xffffffffu, start);
-    if (PASS == 1 && start) {
-      const int64_t pos = base + n + __popc(m & ((1u << lane) - 1));
-      Run r;
-      r.key = key >> kSubKeyBits;
-      r.row = (int32_t)row;
-      r.ch0 = (int32_t)c;
-      runs[pos] = r;
-      store_key(keys, pos, key, key32);
-    }
-    if (PASS == 2) {
-      const unsigned upto = m & (0xffffffffu >> (31 - lane));  // starts at or before this lane
-      const int64_t rel = n + __popc(upto) - 1;                // index of this sample's run within the row
-      const int64_t r = base + rel;                            // input-order index of this sample's run
-      int64_t out0 = __shfl_sync(0xffffffffu, pre_out, (int)(rel & 31));
-      if (valid && rel >= 32) out0 = outpos[r];
-      const int ch0 = upto ? (int)c0 + (31 - __clz(upto)) : carry_ch0;
-      if (valid) {
-        const bool act = wgt != 0.0f && (v.x != 0.0f || v.y != 0.0f);
-        R re = 0, im = 0;
-        if (act) {
-          re = (R)v.x * (R)wgt;
-          im = (R)v.y * (R)wgt;
-          if (s.flip) im = -im;
-          if (g.do_wstacking && g.nshift != 0.0) {  // V' = V exp(+2 pi i w s); phase reduced in float64
-            double ph = s.w * g.nshift;
-            ph -= rint(ph);
-            R sn, cs;
-            if constexpr (sizeof(R) == 4) sincospif(2.0f * (float)ph, &sn, &cs);
-            else sincospi(2.0 * ph, &sn, &cs);
-            const R t = re * cs - im * sn;
-            im = re * sn + im * cs;
-            re = t;
-          }
-        }
-        if constexpr (PACK) {  // float32 register-window gridder: 16-byte record, one 128-bit store
-          RecP rp;
-          rp.geo = (uint64_t)(bc.i0r | (bc.j0r << 3) | (bc.p0r << 6)) | (to_fix18(s.dfu) << 10) | (to_fix18(s.dfv) << 28) |
-                   (to_fix18(s.dfw) << 46);
-          rp.re = (float)re;
-          rp.im = (float)im;
-          *reinterpret_cast<float4*>(reinterpret_cast<RecP*>(recs) + out0 + ((int)c - ch0)) = *reinterpret_cast<const float4*>(&rp);
-        } else {
-        Rec<R> rec;
-        rec.cell = bc.i0r | (bc.j0r << 5) | (bc.p0r << 10);
-        // bits 16-20 / 21-25: origin of the gridder's register window (i0r, j0r snapped to the lattice);
-        // wide supports have no windows and p0r may need the high bits
-        if (kc.fast) rec.cell |= ((bc.lu * kc.snap) << 16) | ((bc.lv * kc.snap) << 21);
-        if constexpr (sizeof(R) == 4) {
-          rec.fu = s.fu;
-          rec.fv = s.fv;
-          rec.fw = s.fw;
-        } else {
-          rec.fu = to_fix32(s.dfu);
-          rec.fv = to_fix32(s.dfv);
-          rec.fw = to_fix32(s.dfw);
-        }
-        rec.re = re;
-        rec.im = im;
-        if constexpr (sizeof(R) == 4) rec.pad[0] = rec.pad[1] = 0.f;
-        float4* dst = reinterpret_cast<float4*>(recs + out0 + ((int)c - ch0));
-        const float4* src = reinterpret_cast<const float4*>(&rec);
-        dst[0] = src[0];
-        dst[1] = src[1];
-        }
-      }
-      if (m) carry_ch0 = (int)c0 + (31 - __clz(m));
-    }
-    n += __popc(m);
-    carry = __shfl_sync(0xffffffffu, key, 31);
-  }
-  if (PASS == 0 && lane == 0) row_nruns[row] = n;
-}
-
-// PASS 0 and PASS 1 in one kernel (rows of at most kFusedChan channels): each warp walks its row once, keeps
-// the sample keys in shared memory and counts its runs; the CTA reserves a contiguous block of run slots with
-// one atomic on a global cursor; the warps then write their runs from the cached keys.  Blocks of runs land in
-// CTA arrival order rather than row order, which only permutes the (float) accumulation order inside a bin.
-constexpr int kFusedWarps = 8;
-constexpr int kFusedChan = 768;
-__global__ void __launch_bounds__(32 * kFusedWarps) runs_fused_kernel(DevInputs in, GridGeom g, int64_t* __restrict__ row_nruns,
-                                                                      int64_t* __restrict__ row_off, Run* __restrict__ runs,
-                                                                      void* __restrict__ keys,
-                                                                      const double* __restrict__ finv, int nch32,
-                                                                      int64_t cap, bool key32) {
-  extern __shared__ uint64_t skeys[];  // [warp][nch32]
-  __shared__ int s_cnt[kFusedWarps];
-  __shared__ unsigned long long s_base;
-  const int lane = threadIdx.x & 31, warp = threadIdx.x >> 5;
-  const int64_t row = (int64_t)blockIdx.x * kFusedWarps + warp;
-  const bool active = row < in.nrow;
-  uint64_t* mykeys = skeys + (size_t)warp * nch32;
-  int n = 0;
-  if (active) {
-    const BinConsts kc = bin_consts(g);
-    const RowGeom rg = row_geom(g, in.uvw[3 * row], in.uvw[3 * row + 1], in.uvw[3 * row + 2]);
-    uint64_t carry = ~0ull;
-    for (int c0 = 0; c0 < (int)in.nchan; c0 += 32) {
-      const int c = c0 + lane;
-      const bool valid = c < in.nchan;
-      uint64_t key = ~0ull;
-      if (valid) {
-        const SampleGeom s = sample_geom<false>(g, kc, rg, finv[c]);
-        key = bin_key(g, bin_cell(g, kc, s));
-      }
-      mykeys[c] = key;
-      uint64_t prev = __shfl_up_sync(0xffffffffu, key, 1);
-      if (lane == 0) prev = carry;
-      n += __popc(__ballot_sync(0xffffffffu, valid && key != prev));
-      carry = __shfl_sync(0xffffffffu, key, 31);
-    }
-  }
-  if (lane == 0) s_cnt[warp] = n;
-  __syncthreads();
-  if (threadIdx.x == 0) {
-    int total = 0;
-    for (int w = 0; w < kFusedWarps; ++w) total += s_cnt[w];
-    s_base = atomicAdd(reinterpret_cast<unsigned long long*>(row_off + in.nrow), (unsigned long long)total);
-  }
-  __syncthreads();
-  if (!active) return;
-  int64_t base = (int64_t)s_base;
-  for (int w = 0; w < warp; ++w) base += s_cnt[w];
-  if (lane == 0) {
-    row_off[row] = base;
-    row_nruns[row] = n;
-  }
-  uint64_t carry = ~0ull;
-  int m_before = 0;
-  for (int c0 = 0; c0 < (int)in.nchan; c0 += 32) {
-    const int c = c0 + lane;
-    const bool valid = c < in.nchan;
-    const uint64_t key = mykeys[c];
-    uint64_t prev = __shfl_up_sync(0xffffffffu, key, 1);
-    if (lane == 0) prev = carry;
-    const bool start = valid && key != prev;
-    const unsigned m = __ballot_sync(0xffffffffu, start);
-    if (start) {
-      const int64_t pos = base + m_before + __popc(m & ((1u << lane) - 1));
-      Run r;
-      r.key = key >> kSubKeyBits;
-      r.row = (int32_t)row;
-      r.ch0 = (int32_t)c;
-      if (pos < cap) {
-        runs[pos] = r;
-        store_key(keys, pos, key, key32);
-      }
-    }
-    m_before += __popc(m);
-    carry = __shfl_sync(0xffffffffu, key, 31);
-  }
-}
+constexpr int kScanTile = 2048;      // table entries per CTA of the scan passes
+constexpr int kScanThreads = 256;
+constexpr int kScanPer = kScanTile / kScanThreads;
+constexpr int64_t kMaxTableEntries = (int64_t)1 << 30;  // 4 GB of u32
 
 __global__ void finv_kernel(const double* __restrict__ freq, int64_t nchan, double* __restrict__ finv) {
   int64_t c = (int64_t)blockIdx.x * blockDim.x + threadIdx.x;
   if (c < nchan) finv[c] = freq[c] / kSpeedOfLight;
 }
 
-__global__ void run_len_kernel(const Run* __restrict__ runs, int64_t nruns, int32_t nchan, uint32_t* __restrict__ idx,
-                               int32_t* __restrict__ len) {
-  int64_t r = (int64_t)blockIdx.x * blockDim.x + threadIdx.x;
-  if (r >= nruns) return;
-  Run a = runs[r];
-  int32_t stop = nchan;
-  if (r + 1 < nruns) {
-    Run b = runs[r + 1];
-    if (b.row == a.row) stop = b.ch0;
-  }
-  len[r] = stop - a.ch0;
-  idx[r] = (uint32_t)r;
-}
-
-// sorted order: gather run + length, flag bin starts
-__global__ void gather_kernel(const Run* __restrict__ runs, const int32_t* __restrict__ len,
-                              const uint32_t* __restrict__ idx, const void* __restrict__ keys_sorted, bool key32, int64_t nruns,
-                              Run* __restrict__ runs_sorted, int64_t* __restrict__ len_sorted,
-                              int64_t* __restrict__ start_flag) {
-  int64_t i = (int64_t)blockIdx.x * blockDim.x + threadIdx.x;
-  if (i >= nruns) return;
-  uint32_t r = idx[i];
-  runs_sorted[i] = runs[r];
-  len_sorted[i] = len[r];
-  start_flag[i] = (i == 0 || (load_key(keys_sorted, i, key32) >> kSubKeyBits) != (load_key(keys_sorted, i - 1, key32) >> kSubKeyBits)) ? 1 : 0;
-}
-
-// group g = g-th distinct key; first run of each group, number of items of each group
-__global__ void groups_kernel(const int64_t* __restrict__ start_flag, const int64_t* __restrict__ group_of /*inclusive scan*/,
-                              const int64_t* __restrict__ visoff, const uint32_t* __restrict__ idx, int64_t nruns,
-                              int64_t nrec, int64_t* __restrict__ group_first, int64_t* __restrict__ outpos) {
-  int64_t i = (int64_t)blockIdx.x * blockDim.x + threadIdx.x;
-  if (i >= nruns) return;
-  outpos[idx[i]] = visoff[i];  // first record of input-order run idx[i]
-  if (start_flag[i]) group_first[group_of[i] - 1] = i;
-}
-
-__global__ void group_items_kernel(const int64_t* __restrict__ group_first, const int64_t* __restrict__ visoff,
-                                   int64_t ngroups, int64_t nruns, int64_t nrec, int64_t* __restrict__ group_nitems) {
-  int64_t gidx = (int64_t)blockIdx.x * blockDim.x + threadIdx.x;
-  if (gidx > ngroups) return;
-  if (gidx == ngroups) { group_nitems[gidx] = 0; return; }
-  int64_t b = visoff[group_first[gidx]];
-  int64_t e = gidx + 1 < ngroups ? visoff[group_first[gidx + 1]] : nrec;
-  group_nitems[gidx] = (e - b + kItemVis - 1) / kItemVis;
-}
-
-__global__ void items_kernel(const int64_t* __restrict__ group_first, const int64_t* __restrict__ group_item_off,
-                             const int64_t* __restrict__ visoff, const Run* __restrict__ runs_sorted, int64_t ngroups,
-                             int64_t nrec, GridGeom g, Item* __restrict__ items, int64_t* __restrict__ win_item_start) {
-  int64_t gidx = (int64_t)blockIdx.x * blockDim.x + threadIdx.x;
-  if (gidx >= ngroups) return;
-  int64_t fr = group_first[gidx];
-  int64_t b = visoff[fr];
-  int64_t e = gidx + 1 < ngroups ? visoff[group_first[gidx + 1]] : nrec;
-  uint64_t key = runs_sorted[fr].key;
-  int tv = (int)(key % g.ntv);
-  uint64_t q = key / g.ntv;
-  int tu = (int)(q % g.ntu);
-  int win = (int)(q / g.ntu);
-  int64_t it = group_item_off[gidx];
-  atomicMin((unsigned long long*)&win_item_start[win], (unsigned long long)it);
-  for (int64_t r = b; r < e; r += kItemVis, ++it) {
-    Item item;
-    item.rec_begin = r;
-    item.nrec = (int32_t)std::min<int64_t>(kItemVis, e - r);
-    item.tu = tu;
-    item.tv = tv;
-    item.win = win;
-    item.pad[0] = item.pad[1] = 0;
-    items[it] = item;
+// ---- pass 1: histogram of the keys ------------------------------------------------------------------------
+__global__ void __launch_bounds__(256) hist_kernel(DevInputs in, GridGeom g, const double* __restrict__ finv,
+                                                   uint32_t* __restrict__ table) {
+  const int lane = threadIdx.x & 31;
+  const int64_t row = ((int64_t)blockIdx.x * blockDim.x + threadIdx.x) >> 5;
+  if (row >= in.nrow) return;
+  const BinConsts kc = bin_consts(g);
+  const RowGeom rg = row_geom(g, in.uvw[3 * row], in.uvw[3 * row + 1], in.uvw[3 * row + 2]);
+  for (int c0 = 0; c0 < (int)in.nchan; c0 += 32) {
+    const int c = c0 + lane;
+    uint32_t key = kNoKey;
+    if (c < in.nchan) key = bin_key(g, bin_cell(g, kc, sample_geom<false>(g, kc, rg, finv[c])));
+    uint32_t prev = __shfl_up_sync(0xffffffffu, key, 1);
+    const unsigned bound = __ballot_sync(0xffffffffu, lane == 0 || key != prev);  // segment starts (incl. skipped ones)
+    if (((bound >> lane) & 1u) && key != kNoKey) {
+      const unsigned after = lane == 31 ? 0u : bound >> (lane + 1);
+      const int len = after ? __ffs(after) : 32 - lane;  // up to the next boundary or the end of the chunk
+      atomicAdd(table + key, (uint32_t)min(len, (int)in.nchan - c));
+    }
   }
 }
 
-__global__ void fill_i64_kernel(int64_t* p, int64_t n, int64_t v) {
-  int64_t i = (int64_t)blockIdx.x * blockDim.x + threadIdx.x;
-  if (i < n) p[i] = v;
+// ---- pass 2: scan of the key table ------------------------------------------------------------------------
+__device__ __forceinline__ uint2 entry_cost(uint32_t count) {
+  const uint32_t ngroups = (count + kGroup - 1) / kGroup;
+  return make_uint2(ngroups, (ngroups + kJobGroups - 1) / kJobGroups);
 }
 
-template <typename T>
-cip_status d2h_scalar(cip_ctx* ctx, const T* dev, T* out) {
-  return fetch_small(ctx, dev, sizeof(T), out);
+__global__ void __launch_bounds__(kScanThreads) scan_reduce_kernel(const uint32_t* __restrict__ table, int64_t n,
+                                                                   uint2* __restrict__ tile_sums) {
+  __shared__ uint2 s_part[kScanThreads / 32];
+  const int64_t base = (int64_t)blockIdx.x * kScanTile + (int64_t)threadIdx.x * kScanPer;
+  uint32_t gsum = 0, jsum = 0;
+  if (base + kScanPer <= n) {
+    const uint4 a = *reinterpret_cast<const uint4*>(table + base), b = *reinterpret_cast<const uint4*>(table + base + 4);
+    const uint32_t v[8] = {a.x, a.y, a.z, a.w, b.x, b.y, b.z, b.w};
+#pragma unroll
+    for (int i = 0; i < kScanPer; ++i) {
+      const uint2 e = entry_cost(v[i]);
+      gsum += e.x;
+      jsum += e.y;
+    }
+  } else {
+    for (int i = 0; i < kScanPer; ++i)
+      if (base + i < n) {
+        const uint2 e = entry_cost(table[base + i]);
+        gsum += e.x;
+        jsum += e.y;
+      }
+  }
+#pragma unroll
+  for (int o = 16; o; o >>= 1) {
+    gsum += __shfl_xor_sync(0xffffffffu, gsum, o);
+    jsum += __shfl_xor_sync(0xffffffffu, jsum, o);
+  }
+  if ((threadIdx.x & 31) == 0) s_part[threadIdx.x >> 5] = make_uint2(gsum, jsum);
+  __syncthreads();
+  if (threadIdx.x == 0) {
+    uint2 t = make_uint2(0, 0);
+    for (int w = 0; w < kScanThreads / 32; ++w) {
+      t.x += s_part[w].x;
+      t.y += s_part[w].y;
+    }
+    tile_sums[blockIdx.x] = t;
+  }
+}
+
+// One CTA: exclusive prefix of the tile sums in place, totals and capacity check into the header.
+__global__ void __launch_bounds__(1024) scan_tiles_kernel(uint2* __restrict__ tile_sums, int64_t ntiles, BinHeader* __restrict__ hdr,
+                                                          uint32_t cap_groups, uint32_t cap_jobs, uint32_t* __restrict__ call_flags,
+                                                          uint32_t* __restrict__ win_job_total, BinHeader* __restrict__ hdr_host,
+                                                          uint32_t* __restrict__ flags_host) {
+  __shared__ uint2 s_warp[32];
+  __shared__ uint2 s_carry;
+  const int lane = threadIdx.x & 31, warp = threadIdx.x >> 5;
+  if (threadIdx.x == 0) s_carry = make_uint2(0, 0);
+  __syncthreads();
+  for (int64_t t0 = 0; t0 < ntiles; t0 += 1024) {
+    const int64_t t = t0 + threadIdx.x;
+    const uint2 mine = t < ntiles ? tile_sums[t] : make_uint2(0, 0);
+    uint2 inc = mine;
+#pragma unroll
+    for (int o = 1; o < 32; o <<= 1) {
+      const uint32_t gx = __shfl_up_sync(0xffffffffu, inc.x, o), jx = __shfl_up_sync(0xffffffffu, inc.y, o);
+      if (lane >= o) {
+        inc.x += gx;
+        inc.y += jx;
+      }
+    }
+    if (lane == 31) s_warp[warp] = inc;
+    __syncthreads();
+    if (warp == 0) {
+      uint2 w = s_warp[lane];
+#pragma unroll
+      for (int o = 1; o < 32; o <<= 1) {
+        const uint32_t gx = __shfl_up_sync(0xffffffffu, w.x, o), jx = __shfl_up_sync(0xffffffffu, w.y, o);
+        if (lane >= o) {
+          w.x += gx;
+          w.y += jx;
+        }
+      }
+      s_warp[lane] = w;  // inclusive over warps
+    }
+    __syncthreads();
+    const uint2 carry = s_carry;
+    const uint2 wbase = warp ? s_warp[warp - 1] : make_uint2(0, 0);
+    if (t < ntiles) tile_sums[t] = make_uint2(carry.x + wbase.x + inc.x - mine.x, carry.y + wbase.y + inc.y - mine.y);
+    __syncthreads();
+    if (threadIdx.x == 0) s_carry = make_uint2(carry.x + s_warp[31].x, carry.y + s_warp[31].y);
+    __syncthreads();
+  }
+  if (threadIdx.x == 0) {
+    const uint2 tot = s_carry;
+    BinHeader h;
+    h.ngroups = tot.x;
+    h.njobs = tot.y;
+    h.overflow = (tot.x > cap_groups ? 1u : 0u) | (tot.y > cap_jobs ? 2u : 0u);
+    h.pad = 0;
+    *hdr = h;
+    *win_job_total = tot.y;
+    if (h.overflow) atomicOr(call_flags, h.overflow);
+    // mirrors for the host's check after the call has drained: the largest demand seen so far in this call
+    hdr_host->ngroups = max(hdr_host->ngroups, tot.x);
+    hdr_host->njobs = max(hdr_host->njobs, tot.y);
+    if (h.overflow) *flags_host |= h.overflow;
+    __threadfence_system();
+  }
+}
+
+// Apply: per key its first record position into the table, the jobs, the padding records, the first job of
+// every window.  REC_BYTES = 16 (packed float32 records) or 32.
+template <int REC_BYTES>
+__global__ void __launch_bounds__(kScanThreads) scan_apply_kernel(uint32_t* __restrict__ table, int64_t n, const uint2* __restrict__ tile_prefix,
+                                                                  const BinHeader* __restrict__ hdr, GridGeom g, int64_t entries_per_window,
+                                                                  Job* __restrict__ jobs, unsigned char* __restrict__ recs,
+                                                                  uint32_t* __restrict__ win_job_start) {
+  __shared__ uint2 s_warp[kScanThreads / 32];
+  if (hdr->overflow) return;
+  const int lane = threadIdx.x & 31, warp = threadIdx.x >> 5;
+  const int64_t base = (int64_t)blockIdx.x * kScanTile + (int64_t)threadIdx.x * kScanPer;
+  uint32_t cnt[kScanPer];
+  uint2 cost[kScanPer];
+  uint2 sum = make_uint2(0, 0);
+#pragma unroll
+  for (int i = 0; i < kScanPer; ++i) {
+    cnt[i] = base + i < n ? table[base + i] : 0u;
+    cost[i] = entry_cost(cnt[i]);
+    sum.x += cost[i].x;
+    sum.y += cost[i].y;
+  }
+  uint2 inc = sum;
+#pragma unroll
+  for (int o = 1; o < 32; o <<= 1) {
+    const uint32_t gx = __shfl_up_sync(0xffffffffu, inc.x, o), jx = __shfl_up_sync(0xffffffffu, inc.y, o);
+    if (lane >= o) {
+      inc.x += gx;
+      inc.y += jx;
+    }
+  }
+  if (lane == 31) s_warp[warp] = inc;
+  __syncthreads();
+  uint2 off = tile_prefix[blockIdx.x];
+  for (int w = 0; w < warp; ++w) {
+    off.x += s_warp[w].x;
+    off.y += s_warp[w].y;
+  }
+  off.x += inc.x - sum.x;
+  off.y += inc.y - sum.y;
+  const uint32_t snap = g.W <= kFastSupport ? 9 - g.W : 1;
+#pragma unroll
+  for (int i = 0; i < kScanPer; ++i) {
+    const int64_t idx = base + i;
+    if (idx >= n) break;
+    if (idx % entries_per_window == 0) win_job_start[idx / entries_per_window] = off.y;
+    if (cnt[i]) {
+      const uint32_t ngroups = cost[i].x;
+      table[idx] = off.x * kGroup;  // the key's record cursor
+      const KeyParts kp = key_parts(g, (uint32_t)idx);
+      for (uint32_t j = 0; j < cost[i].y; ++j) {
+        Job job;
+        job.group_begin = off.x + j * kJobGroups;
+        job.ngroups = min((uint32_t)kJobGroups, ngroups - j * kJobGroups);
+        job.tu = (uint16_t)kp.tu;
+        job.tv = (uint16_t)kp.tv;
+        job.win = (uint16_t)kp.win;
+        job.lu = (uint8_t)kp.lu;
+        job.lv = (uint8_t)kp.lv;
+        jobs[off.y + j] = job;
+      }
+      // zero records up to the end of the last k-group; the packed ones carry the window's lattice origin so that
+      // a consumer that tracks the window by the records' origins sees no change
+      const uint32_t lv = (uint32_t)kp.lv, lu = (uint32_t)kp.lu;
+      const uint4 zero = make_uint4(REC_BYTES == 16 ? (lu * snap) | ((lv * snap) << 3) : 0u, 0u, 0u, 0u);
+      for (uint32_t r = cnt[i]; r < ngroups * kGroup; ++r) {
+        uint4* dst = reinterpret_cast<uint4*>(recs + ((size_t)off.x * kGroup + r) * REC_BYTES);
+        dst[0] = zero;
+        if (REC_BYTES == 32) dst[1] = make_uint4(0u, 0u, 0u, 0u);
+      }
+      off.x += ngroups;
+      off.y += cost[i].y;
+    }
+  }
+}
+
+// Work items of the register-window gridders (grid.cu): a job starts an item when it is the first of its (window,
+// tile) bin or crosses a multiple of kItemGroups k-groups; the item runs up to the next such job.  The start flag
+// goes into bit 31 of the job's ngroups, the starts into a list (in job order inside a CTA of this kernel, CTAs in
+// arrival order, so neighbouring items mostly stay neighbours and share grid lines in L2).
+__global__ void __launch_bounds__(256) items_kernel(Job* __restrict__ jobs, const BinHeader* __restrict__ hdr,
+                                                    uint32_t* __restrict__ items, uint32_t* __restrict__ nitems) {
+  __shared__ uint32_t s_warp[8];
+  __shared__ uint32_t s_base;
+  if (hdr->overflow) return;
+  const uint32_t njobs = hdr->njobs;
+  const uint32_t j = blockIdx.x * blockDim.x + threadIdx.x;
+  if (blockIdx.x * blockDim.x >= njobs) return;
+  bool start = false;
+  if (j < njobs) {
+    const Job me = jobs[j];
+    start = j == 0;
+    if (j > 0) {
+      const Job prev = jobs[j - 1];
+      start = prev.tu != me.tu || prev.tv != me.tv || prev.win != me.win ||
+              (prev.group_begin / kItemGroups) != (me.group_begin / kItemGroups);
+    }
+    if (start) jobs[j].ngroups = me.ngroups | kJobStartsItem;
+  }
+  const int lane = threadIdx.x & 31, warp = threadIdx.x >> 5;
+  const unsigned m = __ballot_sync(0xffffffffu, start);
+  if (lane == 0) s_warp[warp] = __popc(m);
+  __syncthreads();
+  if (threadIdx.x == 0) {
+    uint32_t tot = 0;
+    for (int w = 0; w < 8; ++w) {
+      const uint32_t c = s_warp[w];
+      s_warp[w] = tot;
+      tot += c;
+    }
+    s_base = atomicAdd(nitems, tot);
+  }
+  __syncthreads();
+  if (start) items[s_base + s_warp[warp] + __popc(m & ((1u << lane) - 1))] = j;
+}
+
+// ---- pass 3: records --------------------------------------------------------------------------------------
+// One warp per row, lanes stride the channels.  Reads are row-contiguous; a segment's records are contiguous.
+template <typename R, bool PACK>
+__global__ void __launch_bounds__(256, 6) records_kernel(DevInputs in, GridGeom g, const double* __restrict__ finv,
+                                                         uint32_t* __restrict__ table, const BinHeader* __restrict__ hdr,
+                                                         Rec<R>* __restrict__ recs) {
+  if (hdr->overflow) return;
+  const int lane = threadIdx.x & 31;
+  const int64_t row = ((int64_t)blockIdx.x * blockDim.x + threadIdx.x) >> 5;
+  if (row >= in.nrow) return;
+  const BinConsts kc = bin_consts(g);
+  const RowGeom rg = row_geom(g, in.uvw[3 * row], in.uvw[3 * row + 1], in.uvw[3 * row + 2]);
+  for (int c0 = 0; c0 < (int)in.nchan; c0 += 32) {
+    const int c = c0 + lane;
+    const bool valid = c < in.nchan;
+    // the sample loads are issued before the geometry, which does not depend on them (the pass is bound by
+    // memory latency)
+    float2 v = make_float2(0.f, 0.f);
+    float wgt = 0.f;
+    if (valid) {
+      v = __ldcs(in.vis + row * in.vstride + c);
+      wgt = in.wgt ? __ldcs(in.wgt + row * in.wstride + c) : 1.0f;
+      if (in.mask && in.mask[row * in.wstride + c] == 0) wgt = 0.0f;
+    }
+    uint32_t key = kNoKey;
+    SampleGeom s;
+    BinCell bc;
+    if (valid) {
+      s = sample_geom<true>(g, kc, rg, finv[c]);
+      bc = bin_cell(g, kc, s);
+      key = bin_key(g, bc);
+    }
+    const uint32_t prev = __shfl_up_sync(0xffffffffu, key, 1);
+    const unsigned bound = __ballot_sync(0xffffffffu, lane == 0 || key != prev);
+    const int lead = 31 - __clz(bound & (0xffffffffu >> (31 - lane)));  // first lane of this lane's segment
+    uint32_t pos = 0;
+    if (lead == lane && key != kNoKey) {
+      const unsigned after = lane == 31 ? 0u : bound >> (lane + 1);
+      const int len = after ? __ffs(after) : 32 - lane;
+      pos = atomicAdd(table + key, (uint32_t)min(len, (int)in.nchan - c));
+    }
+    pos = __shfl_sync(0xffffffffu, pos, lead) + (uint32_t)(lane - lead);
+    if (key == kNoKey) continue;
+    const bool act = wgt != 0.0f && (v.x != 0.0f || v.y != 0.0f);
+    R re = 0, im = 0;
+    if (act) {
+      re = (R)v.x * (R)wgt;
+      im = (R)v.y * (R)wgt;
+      if (s.flip) im = -im;
+      if (g.do_wstacking && g.nshift != 0.0) {  // V' = V exp(+2 pi i w s); phase reduced in float64
+        double ph = s.w * g.nshift;
+        ph -= rint(ph);
+        R sn, cs;
+        if constexpr (sizeof(R) == 4) sincospif(2.0f * (float)ph, &sn, &cs);
+        else sincospi(2.0 * ph, &sn, &cs);
+        const R t = re * cs - im * sn;
+        im = re * sn + im * cs;
+        re = t;
+      }
+    }
+    if constexpr (PACK) {  // float32 register-window gridder: 16-byte record, one 128-bit store
+      RecP rp;
+      rp.geo = (uint64_t)(bc.i0r | (bc.j0r << 3) | (bc.p0r << 6)) | (to_fix18(s.dfu) << 10) | (to_fix18(s.dfv) << 28) |
+               (to_fix18(s.dfw) << 46);
+      rp.re = (float)re;
+      rp.im = (float)im;
+      *reinterpret_cast<float4*>(reinterpret_cast<RecP*>(recs) + pos) = *reinterpret_cast<const float4*>(&rp);
+    } else {
+      Rec<R> rec;
+      rec.cell = bc.i0r | (bc.j0r << 5) | (bc.p0r << 10);
+      // bits 16-20 / 21-25: origin of the gridder's register window (i0r, j0r snapped to the lattice);
+      // wide supports have no windows and p0r may need the high bits
+      if (kc.fast) rec.cell |= ((bc.lu * kc.snap) << 16) | ((bc.lv * kc.snap) << 21);
+      if constexpr (sizeof(R) == 4) {
+        rec.fu = s.fu;
+        rec.fv = s.fv;
+        rec.fw = s.fw;
+      } else {
+        rec.fu = to_fix32(s.dfu);
+        rec.fv = to_fix32(s.dfv);
+        rec.fw = to_fix32(s.dfw);
+      }
+      rec.re = re;
+      rec.im = im;
+      if constexpr (sizeof(R) == 4) rec.pad[0] = rec.pad[1] = 0.f;
+      float4* dst = reinterpret_cast<float4*>(recs + pos);
+      const float4* src = reinterpret_cast<const float4*>(&rec);
+      dst[0] = src[0];
+      dst[1] = src[1];
+    }
+  }
 }
 
 inline int nblk(int64_t n, int per) { return (int)((n + per - 1) / per); }
 
+int64_t entries_per_window(const GridGeom& g) { return (int64_t)g.ntu * g.ntv * g.nlat * g.nlat; }
+
 }  // namespace
 
-cip_status run_binning(cip_ctx* ctx, int slot, const DevInputs& in, const GridGeom& g, int fp64, BinResult* out) {
+int max_windows_per_pass(const GridGeom& g) {
+  int64_t lim = kMaxTableEntries;
+  if (const char* e = getenv("CIP_BIN_TABLE_ENTRIES")) lim = std::max<int64_t>(atoll(e), 1);  // tests: force window chunks
+  return (int)std::max<int64_t>(1, std::min<int64_t>(g.nwin, lim / std::max<int64_t>(entries_per_window(g), 1)));
+}
+
+cip_status run_binning(cip_ctx* ctx, int slot, const DevInputs& in, const GridGeom& g, int fp64, bool want_items) {
   cudaStream_t st = ctx->stream;
   BinWork& w = ctx->work[slot];
   const int64_t nrow = in.nrow, nchan = in.nchan;
-  out->nruns = out->nrec = out->nitems = 0;
-  out->win_item_start.assign(g.nwin + 1, 0);
-  if (nrow == 0 || nchan == 0) return CIP_OK;
+  const int nwin_pass = g.win_end - g.win_begin;
+  CIP_REQUIRE(nwin_pass >= 1, "empty window range");
+  const int64_t epw = entries_per_window(g);
+  const int64_t n = epw * nwin_pass;
+  CIP_REQUIRE(epw <= kMaxTableEntries && n < ((int64_t)1 << 32), "key table too large (%lld entries per window)", (long long)epw);
+  CIP_REQUIRE(g.ntu < 65536 && g.ntv < 65536 && g.nwin < 65536, "grid or plane stack too large for the job format");
   const int64_t nrec = nrow * nchan;
+  CIP_REQUIRE(nrec + 8 * n / 1 >= 0 && nrec < ((int64_t)1 << 32) - ((int64_t)1 << 28), "too many samples for one binning pass");
+  const bool pack = !fp64 && g.W <= kFastSupport;
+  const size_t rec_bytes = pack ? 16 : 32;
 
-  // --- runs per row, offsets -------------------------------------------------------
-  CIP_TRY(w.row_nruns.ensure(sizeof(int64_t) * (nrow + 1)));
-  CIP_TRY(w.row_off.ensure(sizeof(int64_t) * (nrow + 1)));
-  int64_t* row_nruns = w.row_nruns.as<int64_t>();
-  int64_t* row_off = w.row_off.as<int64_t>();
-  CIP_CHECK_CUDA(cudaMemsetAsync(row_nruns + nrow, 0, sizeof(int64_t), st));
-  const int rblocks = nblk(nrow * 32, 256);
-  CIP_TRY(w.finv.ensure(sizeof(double) * nchan));
+  // capacities: what the buffers hold already, or a first guess (12.5 % padding, one job per 64 records); a pass
+  // that needs more sets the overflow flag and the call is repeated with the demand it reported
+  const int64_t want_groups = std::max<int64_t>(w.cap_groups, (nrec + nrec / 8) / kGroup + 1024);
+  const int64_t want_jobs = std::max<int64_t>(w.cap_jobs, nrec / 64 + 1024);
+  CIP_TRY(w.recs.ensure((size_t)want_groups * kGroup * 32));  // sized for 32-byte records: both formats fit
+  CIP_TRY(w.jobs.ensure(sizeof(Job) * (size_t)want_jobs));
+  w.cap_groups = (int64_t)(w.recs.cap / (kGroup * 32));
+  w.cap_jobs = (int64_t)(w.jobs.cap / sizeof(Job));
+  (void)rec_bytes;
+  CIP_TRY(w.table.ensure(sizeof(uint32_t) * (size_t)n + 64));
+  const int64_t ntiles = (n + kScanTile - 1) / kScanTile;
+  CIP_TRY(w.tile_sums.ensure(sizeof(uint2) * (size_t)ntiles));
+  CIP_TRY(w.hdr.ensure(sizeof(BinHeader)));
+  CIP_TRY(w.win_job_start.ensure(sizeof(uint32_t) * (size_t)(g.nwin + 2)));
+  CIP_TRY(w.finv.ensure(sizeof(double) * std::max<int64_t>(nchan, 1)));
+  uint32_t* table = w.table.as<uint32_t>();
   double* finv = w.finv.as<double>();
+  BinHeader* hdr = w.hdr.as<BinHeader>();
+  uint32_t* wjs = w.win_job_start.as<uint32_t>();
+
+  CIP_CHECK_CUDA(cudaMemsetAsync(table, 0, sizeof(uint32_t) * (size_t)n, st));
+  if (nrec == 0) {
+    CIP_CHECK_CUDA(cudaMemsetAsync(hdr, 0, sizeof(BinHeader), st));
+    CIP_CHECK_CUDA(cudaMemsetAsync(wjs, 0, sizeof(uint32_t) * (size_t)(g.nwin + 2), st));
+    return CIP_OK;
+  }
   finv_kernel<<<nblk(nchan, 256), 256, 0, st>>>(in.freq, nchan, finv);
-  ctx->launches++;
-  uint64_t nkeys = (uint64_t)g.nwin * g.ntu * g.ntv;
-  int bits = 1;
-  while (bits < 64 && (nkeys >> bits)) ++bits;
-  bits += kSubKeyBits;
-  CIP_REQUIRE(bits <= 64, "bin key too wide (%d bits)", bits);
-  const bool key32 = bits <= 32 && !getenv("CIP_BIN_KEY64");
-  int64_t nruns = 0;
-  size_t tmp_bytes = 0;
-  Run* runs = nullptr;
-  if (nchan <= kFusedChan && !getenv("CIP_BIN_TWO_PASS")) {
-    // fused count + write: the run buffers are sized from a guess (what they already hold, or a mean run
-    // length of 4 channels) and the kernel drops writes past the capacity; a low guess costs one re-run
-    const int nch32 = (int)((nchan + 31) / 32) * 32;
-    const size_t smem = sizeof(uint64_t) * kFusedWarps * nch32;
-    CIP_CHECK_CUDA(cudaFuncSetAttribute(runs_fused_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem));
-    int64_t cap = std::max<int64_t>((int64_t)std::min(w.runs.cap / sizeof(Run), w.run_keys.cap / sizeof(uint64_t)),
-                                    nrec / 4 + 1024);
-    for (int attempt = 0;; ++attempt) {
-      CIP_TRY(w.runs.ensure(sizeof(Run) * cap));
-      CIP_TRY(w.run_keys.ensure(sizeof(uint64_t) * cap));
-      runs = w.runs.as<Run>();
-      CIP_CHECK_CUDA(cudaMemsetAsync(row_off + nrow, 0, sizeof(int64_t), st));
-      runs_fused_kernel<<<nblk(nrow, kFusedWarps), 32 * kFusedWarps, smem, st>>>(in, g, row_nruns, row_off, runs,
-                                                                                 w.run_keys.p, finv, nch32, cap, key32);
-      ctx->launches++;
-      CIP_TRY(d2h_scalar(ctx, row_off + nrow, &nruns));
-      if (nruns <= cap) break;
-      CIP_REQUIRE(attempt == 0, "run count changed between two passes");
-      cap = nruns;
-    }
-    CIP_REQUIRE(nruns > 0 && nruns < ((int64_t)1 << 32), "unexpected number of runs %lld", (long long)nruns);
+  const int rblocks = nblk(nrow * 32, 256);
+  hist_kernel<<<rblocks, 256, 0, st>>>(in, g, finv, table);
+  scan_reduce_kernel<<<(unsigned)ntiles, kScanThreads, 0, st>>>(table, n, w.tile_sums.as<uint2>());
+  scan_tiles_kernel<<<1, 1024, 0, st>>>(w.tile_sums.as<uint2>(), ntiles, hdr, (uint32_t)std::min<int64_t>(w.cap_groups, 0xffffffffll),
+                                        (uint32_t)std::min<int64_t>(w.cap_jobs, 0xffffffffll), ctx->call_flags.as<uint32_t>(),
+                                        wjs + nwin_pass, static_cast<BinHeader*>(ctx->flags_host_dev) + 1,
+                                        static_cast<uint32_t*>(ctx->flags_host_dev));
+  if (pack) {
+    scan_apply_kernel<16><<<(unsigned)ntiles, kScanThreads, 0, st>>>(table, n, w.tile_sums.as<uint2>(), hdr, g, epw, w.jobs.as<Job>(),
+                                                                     w.recs.as<unsigned char>(), wjs);
+    records_kernel<float, true><<<rblocks, 256, 0, st>>>(in, g, finv, table, hdr, w.recs.as<Rec<float>>());
   } else {
-    runs_kernel<0, float><<<rblocks, 256, 0, st>>>(in, g, row_nruns, nullptr, nullptr, nullptr, nullptr, (Rec<float>*)nullptr, finv, key32);
-    ctx->launches++;
-    CIP_CHECK_CUDA(cub::DeviceScan::ExclusiveSum(nullptr, tmp_bytes, row_nruns, row_off, nrow + 1, st));
-    CIP_TRY(w.cub_tmp.ensure(tmp_bytes));
-    tmp_bytes = w.cub_tmp.cap;
-    CIP_CHECK_CUDA(cub::DeviceScan::ExclusiveSum(w.cub_tmp.p, tmp_bytes, row_nruns, row_off, nrow + 1, st));
-    ctx->launches++;
-    CIP_TRY(d2h_scalar(ctx, row_off + nrow, &nruns));
-    CIP_REQUIRE(nruns > 0 && nruns < ((int64_t)1 << 32), "unexpected number of runs %lld", (long long)nruns);
-    CIP_TRY(w.runs.ensure(sizeof(Run) * nruns));
-    CIP_TRY(w.run_keys.ensure(sizeof(uint64_t) * nruns));
-    runs = w.runs.as<Run>();
-    runs_kernel<1, float><<<rblocks, 256, 0, st>>>(in, g, nullptr, row_off, runs, w.run_keys.p, nullptr,
-                                                   (Rec<float>*)nullptr, finv, key32);
+    scan_apply_kernel<32><<<(unsigned)ntiles, kScanThreads, 0, st>>>(table, n, w.tile_sums.as<uint2>(), hdr, g, epw, w.jobs.as<Job>(),
+                                                                     w.recs.as<unsigned char>(), wjs);
+    if (fp64) records_kernel<double, false><<<rblocks, 256, 0, st>>>(in, g, finv, table, hdr, w.recs.as<Rec<double>>());
+    else records_kernel<float, false><<<rblocks, 256, 0, st>>>(in, g, finv, table, hdr, w.recs.as<Rec<float>>());
+  }
+  ctx->launches += 6;
+  if (want_items) {
+    // capacity: one item per job at most
+    CIP_TRY(w.items.ensure(sizeof(uint32_t) * (size_t)w.cap_jobs + 64));
+    uint32_t* nitems = w.items.as<uint32_t>() + w.cap_jobs;  // [0] item count, [1] the gridder's work counter
+    CIP_CHECK_CUDA(cudaMemsetAsync(nitems, 0, 2 * sizeof(uint32_t), st));
+    items_kernel<<<nblk(w.cap_jobs, 256), 256, 0, st>>>(w.jobs.as<Job>(), hdr, w.items.as<uint32_t>(), nitems);
     ctx->launches++;
   }
-  CIP_TRY(w.run_keys_alt.ensure(sizeof(uint64_t) * nruns));
-  CIP_TRY(w.run_idx.ensure(sizeof(uint32_t) * nruns));
-  CIP_TRY(w.run_idx_alt.ensure(sizeof(uint32_t) * nruns));
-  CIP_TRY(w.run_len.ensure(sizeof(int32_t) * nruns));
-  run_len_kernel<<<nblk(nruns, 256), 256, 0, st>>>(runs, nruns, (int32_t)nchan, w.run_idx.as<uint32_t>(),
-                                                   w.run_len.as<int32_t>());
-  ctx->launches++;
-
-  // --- stable sort of the runs by key ----------------------------------------------
-  if (key32) {
-    CIP_CHECK_CUDA(cub::DeviceRadixSort::SortPairs(nullptr, tmp_bytes, w.run_keys.as<uint32_t>(),
-                                                   w.run_keys_alt.as<uint32_t>(), w.run_idx.as<uint32_t>(),
-                                                   w.run_idx_alt.as<uint32_t>(), nruns, 0, bits, st));
-    CIP_TRY(w.cub_tmp.ensure(tmp_bytes));
-    tmp_bytes = w.cub_tmp.cap;
-    CIP_CHECK_CUDA(cub::DeviceRadixSort::SortPairs(w.cub_tmp.p, tmp_bytes, w.run_keys.as<uint32_t>(),
-                                                   w.run_keys_alt.as<uint32_t>(), w.run_idx.as<uint32_t>(),
-                                                   w.run_idx_alt.as<uint32_t>(), nruns, 0, bits, st));
-  } else {
-    CIP_CHECK_CUDA(cub::DeviceRadixSort::SortPairs(nullptr, tmp_bytes, w.run_keys.as<uint64_t>(),
-                                                   w.run_keys_alt.as<uint64_t>(), w.run_idx.as<uint32_t>(),
-                                                   w.run_idx_alt.as<uint32_t>(), nruns, 0, bits, st));
-    CIP_TRY(w.cub_tmp.ensure(tmp_bytes));
-    tmp_bytes = w.cub_tmp.cap;
-    CIP_CHECK_CUDA(cub::DeviceRadixSort::SortPairs(w.cub_tmp.p, tmp_bytes, w.run_keys.as<uint64_t>(),
-                                                   w.run_keys_alt.as<uint64_t>(), w.run_idx.as<uint32_t>(),
-                                                   w.run_idx_alt.as<uint32_t>(), nruns, 0, bits, st));
-  }
-  ctx->launches += 2 + (bits + 7) / 8;
-
-  // --- sorted runs, record offsets, bins -------------------------------------------
-  CIP_TRY(w.runs_sorted.ensure(sizeof(Run) * nruns));
-  CIP_TRY(w.run_visoff.ensure(sizeof(int64_t) * (nruns + 1) * 2));  // lengths + offsets
-  CIP_TRY(w.flags.ensure(sizeof(int64_t) * nruns * 2));              // start flags + group index
-  Run* runs_sorted = w.runs_sorted.as<Run>();
-  int64_t* len_sorted = w.run_visoff.as<int64_t>();
-  int64_t* visoff = len_sorted + (nruns + 1);
-  int64_t* start_flag = w.flags.as<int64_t>();
-  int64_t* group_of = start_flag + nruns;
-  gather_kernel<<<nblk(nruns, 256), 256, 0, st>>>(runs, w.run_len.as<int32_t>(), w.run_idx_alt.as<uint32_t>(),
-                                                  w.run_keys_alt.p, key32, nruns, runs_sorted, len_sorted,
-                                                  start_flag);
-  ctx->launches++;
-  CIP_CHECK_CUDA(cub::DeviceScan::ExclusiveSum(nullptr, tmp_bytes, len_sorted, visoff, nruns, st));
-  CIP_TRY(w.cub_tmp.ensure(tmp_bytes));
-  tmp_bytes = w.cub_tmp.cap;
-  CIP_CHECK_CUDA(cub::DeviceScan::ExclusiveSum(w.cub_tmp.p, tmp_bytes, len_sorted, visoff, nruns, st));
-  CIP_CHECK_CUDA(cub::DeviceScan::InclusiveSum(nullptr, tmp_bytes, start_flag, group_of, nruns, st));
-  CIP_TRY(w.cub_tmp.ensure(tmp_bytes));
-  tmp_bytes = w.cub_tmp.cap;
-  CIP_CHECK_CUDA(cub::DeviceScan::InclusiveSum(w.cub_tmp.p, tmp_bytes, start_flag, group_of, nruns, st));
-  ctx->launches += 2;
-  int64_t ngroups = 0;
-  CIP_TRY(d2h_scalar(ctx, group_of + nruns - 1, &ngroups));
-
-  CIP_TRY(w.group_start.ensure(sizeof(int64_t) * (ngroups + 1) * 3));
-  int64_t* group_first = w.group_start.as<int64_t>();
-  int64_t* group_nitems = group_first + (ngroups + 1);
-  int64_t* group_item_off = group_nitems + (ngroups + 1);
-  CIP_TRY(w.item_idx.ensure(sizeof(int64_t) * nruns));
-  int64_t* outpos = w.item_idx.as<int64_t>();
-  groups_kernel<<<nblk(nruns, 256), 256, 0, st>>>(start_flag, group_of, visoff, w.run_idx_alt.as<uint32_t>(), nruns,
-                                                  nrec, group_first, outpos);
-  group_items_kernel<<<nblk(ngroups + 1, 256), 256, 0, st>>>(group_first, visoff, ngroups, nruns, nrec, group_nitems);
-  ctx->launches += 2;
-  CIP_CHECK_CUDA(cub::DeviceScan::ExclusiveSum(nullptr, tmp_bytes, group_nitems, group_item_off, ngroups + 1, st));
-  CIP_TRY(w.cub_tmp.ensure(tmp_bytes));
-  tmp_bytes = w.cub_tmp.cap;
-  CIP_CHECK_CUDA(cub::DeviceScan::ExclusiveSum(w.cub_tmp.p, tmp_bytes, group_nitems, group_item_off, ngroups + 1, st));
-  ctx->launches++;
-  int64_t nitems = 0;
-  CIP_TRY(d2h_scalar(ctx, group_item_off + ngroups, &nitems));
-
-  CIP_TRY(w.items.ensure(sizeof(Item) * std::max<int64_t>(nitems, 1)));
-  CIP_TRY(w.win_item_start.ensure(sizeof(int64_t) * (g.nwin + 1)));
-  int64_t* wis = w.win_item_start.as<int64_t>();
-  fill_i64_kernel<<<nblk(g.nwin + 1, 256), 256, 0, st>>>(wis, g.nwin + 1, nitems);
-  items_kernel<<<nblk(ngroups, 256), 256, 0, st>>>(group_first, group_item_off, visoff, runs_sorted, ngroups, nrec, g,
-                                                   w.items.as<Item>(), wis);
-  ctx->launches += 2;
-
-  // --- records ---------------------------------------------------------------------
-  CIP_TRY(w.recs.ensure(recs_bytes(nrec)));
-  if (fp64)
-    runs_kernel<2, double><<<rblocks, 256, 0, st>>>(in, g, row_nruns, row_off, nullptr, nullptr, outpos,
-                                                    w.recs.as<Rec<double>>(), finv, key32);
-  else if (g.W <= kFastSupport)
-    runs_kernel<2, float, true><<<rblocks, 256, 0, st>>>(in, g, row_nruns, row_off, nullptr, nullptr, outpos,
-                                                         w.recs.as<Rec<float>>(), finv, key32);
-  else
-    runs_kernel<2, float><<<rblocks, 256, 0, st>>>(in, g, row_nruns, row_off, nullptr, nullptr, outpos,
-                                                   w.recs.as<Rec<float>>(), finv, key32);
-  ctx->launches++;
   CIP_CHECK_CUDA(cudaGetLastError());
+  return CIP_OK;
+}
 
-  std::vector<int64_t> h(g.nwin + 1);
-  if (sizeof(int64_t) * (g.nwin + 1) <= kSmallHostBytes) {
-    CIP_TRY(fetch_small(ctx, wis, sizeof(int64_t) * (g.nwin + 1), h.data()));
-  } else {
-    CIP_CHECK_CUDA(cudaMemcpyAsync(h.data(), wis, sizeof(int64_t) * (g.nwin + 1), cudaMemcpyDeviceToHost, st));
-    CIP_CHECK_CUDA(cudaStreamSynchronize(st));
+cip_status binning_overflowed(cip_ctx* ctx, bool* again) {
+  // mirrors written by scan_tiles_kernel: [0] flags, BinHeader at +1 (largest demand of the call)
+  volatile uint32_t* flags = static_cast<volatile uint32_t*>(ctx->flags_host);
+  const BinHeader* demand = static_cast<const BinHeader*>(ctx->flags_host) + 1;
+  *again = flags[0] != 0;
+  if (*again) {
+    for (BinWork& w : ctx->work) {
+      const int64_t g = (int64_t)demand->ngroups + demand->ngroups / 16 + 1024, j = (int64_t)demand->njobs + demand->njobs / 16 + 1024;
+      w.cap_groups = std::max(w.cap_groups, g);
+      w.cap_jobs = std::max(w.cap_jobs, j);
+    }
   }
-  h[g.nwin] = nitems;
-  for (int w = g.nwin - 1; w >= 0; --w) h[w] = std::min(h[w], h[w + 1]);  // empty windows start where the next does
-  out->win_item_start = h;
-  out->nruns = nruns;
-  out->nrec = nrec;
-  out->nitems = nitems;
   return CIP_OK;
 }
 

@@ -25,7 +25,10 @@ constexpr int kHalo = 8;          // shift that keeps window origins non-negativ
 constexpr int kSub = kTile + kFastSupport - 1;  // sub-grid edge held in shared memory (15, odd on purpose)
 constexpr int kWin = 8;           // w planes of one gridding window (= planes per consumer thread)
 constexpr int kBatch = 32;        // visibilities per producer/consumer hand-over
-constexpr int kItemVis = 2048;    // visibilities per gridding work item (measured on configs[1], FFMA2 gridder: 512: 9.22, 1024: 9.15, 2048: 9.18, 4096: 9.40, 16384: 10.4 ms gridding; tensor-path gridder: 2048: 7.87, 4096: 8.02; binning grows with the item count)
+constexpr int kGroup = 8;          // records per k-group of the tensor-core gridder: every window job is padded to a multiple
+constexpr int kItemGroups = 256;  // k-groups per work item of the register-window gridders (2048 records, measured in round 1)
+constexpr uint32_t kJobStartsItem = 0x80000000u;  // bit 31 of Job::ngroups: the job starts a work item
+constexpr int kJobGroups = 512;   // k-groups (of 8 records) per gridding job at most: bounds the length of one accumulation
 constexpr int kMaxChunks = 8;     // row chunks of the host -> device visibility stream
 
 void set_error(const char* fmt, ...);
@@ -96,14 +99,33 @@ struct DevBuf {
   template <typename T> T* as() const { return static_cast<T*>(p); }
 };
 
-// Workspaces of one binning pass (and the records / work items the gridder reads from it).
+// Counters of one binning pass, in device memory (and mirrored into mapped host memory by the scan): nothing of
+// the binning is read by the host before the end of the call.
+struct BinHeader {
+  uint32_t ngroups;    // k-groups of 8 records (padded) written by this pass
+  uint32_t njobs;      // gridding jobs
+  uint32_t overflow;   // != 0: a capacity (jobs, records) was too small -- everything downstream skips its work
+  uint32_t pad;
+};
+
+// Workspaces of one binning pass (and the records / jobs the gridder reads from it).
 struct BinWork {
-  DevBuf row_nruns, row_off, runs, run_keys, run_keys_alt, run_idx, run_idx_alt, runs_sorted, run_len, run_visoff,
-      flags, group_start, item_idx, items, win_item_start, cub_tmp, recs, finv;
+  DevBuf table;          // u32 per sort key: sample count, then the running record cursor of the key's group
+  DevBuf tile_sums;      // per scan tile: (k-groups, jobs), then their exclusive prefixes
+  DevBuf jobs, recs, finv, hdr, win_job_start;
+  DevBuf items;          // first job of every work item (u32, cap_jobs entries), then the item count and a work counter
+  int64_t cap_jobs = 0, cap_groups = 0;  // what jobs / recs currently hold
   void release() {
-    for (DevBuf* b : {&row_nruns, &row_off, &runs, &run_keys, &run_keys_alt, &run_idx, &run_idx_alt, &runs_sorted,
-                      &run_len, &run_visoff, &flags, &group_start, &item_idx, &items, &win_item_start, &cub_tmp, &recs,
-                      &finv})
+    for (DevBuf* b : {&table, &tile_sums, &jobs, &recs, &finv, &hdr, &win_job_start, &items}) b->release();
+  }
+};
+
+// Workspaces of the uvw_tiling binning (tiling.cu).
+struct TileWork {
+  DevBuf row_nruns, row_off, runs, run_keys, run_keys_alt, run_idx, run_idx_alt, run_len, flags, group_start, cub_tmp;
+  void release() {
+    for (DevBuf* b : {&row_nruns, &row_off, &runs, &run_keys, &run_keys_alt, &run_idx, &run_idx_alt, &run_len, &flags,
+                      &group_start, &cub_tmp})
       b->release();
   }
 };
@@ -151,21 +173,16 @@ constexpr double kFix32 = 4294967296.0;
 static_assert(sizeof(Rec<float>) == 32 && sizeof(Rec<double>) == 32, "records are one sector");
 inline size_t recs_bytes(int64_t nrec) { return (size_t)nrec * 32; }
 
-// A run of channels of one row that fall into the same (window, tile) bin.
-struct __align__(16) Run {
-  uint64_t key;   // (window * ntu + tu) * ntv + tv
-  int32_t row;
-  int32_t ch0;
+// One gridding job: the records of one sort key = one (w window, uv tile, register-window lattice position), i.e.
+// one accumulator window of the gridder, padded with zero records to whole k-groups; long ones are cut.
+struct __align__(16) Job {
+  uint32_t group_begin;  // first k-group (records group_begin * 8 ...)
+  uint32_t ngroups;      // <= kJobGroups; bit 31 (kJobStartsItem) marks the first job of a work item
+  uint16_t tu, tv;       // uv tile
+  uint16_t win;          // window: planes [win * win_step, win * win_step + kWin)
+  uint8_t lu, lv;        // lattice position of the register window inside the tile
 };
-
-// One gridding work item = one CTA: a slice of the sorted records of one (window, tile) bin.
-struct __align__(16) Item {
-  int64_t rec_begin;
-  int32_t nrec;
-  int32_t tu, tv;  // tile coordinates
-  int32_t win;     // window index: planes [win*win_step, win*win_step + kWin)
-  int32_t pad[2];
-};
+static_assert(sizeof(Job) == 16, "jobs are read with one 128-bit load");
 
 // Geometry shared by the scan / binning / record / gridding kernels.
 struct GridGeom {
@@ -178,6 +195,8 @@ struct GridGeom {
   int win_step;           // first-plane stride between windows = kWin - W + 1
   int nwin;               // number of windows
   int ntu, ntv;           // tiles per axis
+  int nlat;               // register-window lattice positions per tile edge (1 for wide supports)
+  int win_begin, win_end; // windows binned by the current pass (keys of other windows are skipped)
   int do_wstacking;
   float beta_w;           // beta * W
   double beta_wd;         // the same in float64 (float64 path)
@@ -211,6 +230,9 @@ struct cip_ctx {
   // binning workspaces: two sets, so that chunk c+1 is binned (context stream) while chunk c is gridded
   // (grid stream)
   cip::BinWork work[2];
+  cip::DevBuf call_flags;         // u32[4]: [0] sticky overflow of the binning passes of the current call
+  void* flags_host = nullptr;     // mapped pinned mirror of call_flags and the last BinHeader (read after the sync)
+  void* flags_host_dev = nullptr;
   cudaStream_t grid_stream = nullptr;
   cudaEvent_t binned_ev[2] = {}, gridded_ev[2] = {}, zero_ev = nullptr;  // non-timing
   cudaEvent_t chunk_t[cip::kMaxChunks][4] = {};                          // timing: bin begin/end, grid begin/end
@@ -221,6 +243,7 @@ struct cip_ctx {
   std::map<std::tuple<int, int, int, int>, cip::FftPlan> fft_plans;  // (nu, nv, batch, fp64)
   // tiling
   cip::DevBuf t_uvw, t_freq, t_vis;
+  cip::TileWork twork;
 };
 
 namespace cip {
@@ -269,18 +292,21 @@ cip_status fetch_small(cip_ctx* ctx, const void* dev, size_t bytes, void* host_o
 // ---- stages -----------------------------------------------------------------------
 cip_status run_scan(cip_ctx* ctx, const DevInputs& in, int do_wstacking, cip_scan_result* out);
 
-struct BinResult {
-  int64_t nruns = 0;
-  int64_t nrec = 0;
-  int64_t nitems = 0;
-  std::vector<int64_t> win_item_start;  // (nwin+1,) first item of each window
-};
-cip_status run_binning(cip_ctx* ctx, int slot, const DevInputs& in, const GridGeom& g, int fp64, BinResult* out);
+// Bin the samples whose window lies in [g.win_begin, g.win_end) into workspace `slot`: records + jobs + header,
+// all on the device (see bin.cu).  `call_flags` (device, u32) collects overflow over all passes of a call.
+cip_status run_binning(cip_ctx* ctx, int slot, const DevInputs& in, const GridGeom& g, int fp64, bool want_items);
+// Which float32 W <= 8 gridder runs: true = the tcgen05 kernel (grid_tc.cu, jobs), false = the register-window mma.sync
+// kernel (grid.cu, work items).
+bool use_tc_gridder();
+// Largest number of windows one binning pass may cover (bounded by the size of the key table).
+int max_windows_per_pass(const GridGeom& g);
+// After the stream has drained: did any binning pass of the call overflow its buffers?  Grows them if so.
+cip_status binning_overflowed(cip_ctx* ctx, bool* again);
 
-// Grid the items [item_begin, item_end) of binning workspace `slot` into `grid` (planes slot = plane -
+// Grid the jobs of windows [win_first, win_last] of binning workspace `slot` into `grid` (planes slot = plane -
 // plane_base), on `stream`.
-cip_status run_gridder(cip_ctx* ctx, int slot, cudaStream_t stream, const GridGeom& g, int fp64, int64_t nrec_total,
-                       int64_t item_begin, int64_t item_end, void* grid, int plane_base, int nslots);
+cip_status run_gridder(cip_ctx* ctx, int slot, cudaStream_t stream, const GridGeom& g, int fp64, int win_first,
+                       int win_last, void* grid, int plane_base, int nslots);
 cip_status run_fft(cip_ctx* ctx, void* grid, int nu, int nv, int batch, int fp64, int keep_v = 0);
 cip_status fft_rows(cip_ctx* ctx, void* data, int n, int batch, int fp64);  // data == nullptr: plan only
 // FFT + w-screen of the resident planes [plane_base, plane_base + nslots) into the image.  Default: per plane,

@@ -267,6 +267,11 @@ extern "C" cip_status cip_ctx_create(int device, cip_ctx** out) {
   CIP_CHECK_CUDA(cudaEventCreateWithFlags(&ctx->small_ev, cudaEventDisableTiming));
   CIP_CHECK_CUDA(cudaHostAlloc(&ctx->scan_host, kSmallHostBytes, cudaHostAllocMapped));
   CIP_CHECK_CUDA(cudaHostGetDevicePointer(&ctx->scan_host_dev, ctx->scan_host, 0));
+  CIP_CHECK_CUDA(cudaHostAlloc(&ctx->flags_host, 256, cudaHostAllocMapped));
+  CIP_CHECK_CUDA(cudaHostGetDevicePointer(&ctx->flags_host_dev, ctx->flags_host, 0));
+  memset(ctx->flags_host, 0, 256);
+  CIP_TRY(ctx->call_flags.ensure(64));
+  CIP_CHECK_CUDA(cudaMemset(ctx->call_flags.p, 0, 64));
   *out = ctx;
   return CIP_OK;
 }
@@ -279,10 +284,13 @@ extern "C" cip_status cip_ctx_destroy(cip_ctx* ctx) {
   if (ctx->grid_stream) cudaStreamSynchronize(ctx->grid_stream);
   for (auto& kv : ctx->fft_plans) cufftDestroy(kv.second.handle);
   DevBuf* bufs[] = {&ctx->in_uvw, &ctx->in_freq, &ctx->in_vis, &ctx->in_wgt, &ctx->in_mask, &ctx->out_img,
-                    &ctx->scan_out, &ctx->grid, &ctx->image, &ctx->tables, &ctx->fft_t, &ctx->t_uvw, &ctx->t_freq, &ctx->t_vis};
+                    &ctx->scan_out, &ctx->grid, &ctx->image, &ctx->tables, &ctx->fft_t, &ctx->t_uvw, &ctx->t_freq, &ctx->t_vis,
+                    &ctx->call_flags};
   for (auto& w : ctx->work) w.release();
+  ctx->twork.release();
   for (DevBuf* b : bufs) b->release();
   if (ctx->scan_host) cudaFreeHost(ctx->scan_host);
+  if (ctx->flags_host) cudaFreeHost(ctx->flags_host);
   for (auto& ev : ctx->ev)
     if (ev) cudaEventDestroy(ev);
   for (auto& ev : ctx->chunk_ev)

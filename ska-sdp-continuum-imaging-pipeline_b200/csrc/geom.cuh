@@ -120,10 +120,29 @@ __device__ __forceinline__ BinCell bin_cell(const GridGeom& g, const BinConsts& 
   return b;
 }
 
-constexpr int kSubKeyBits = 8;
-// sort key of a run: (window, tile) bin in the high bits, register-window lattice position in the low 8
-__device__ __forceinline__ uint64_t bin_key(const GridGeom& g, const BinCell& b) {
-  return ((((uint64_t)b.win * g.ntu + b.tu) * g.ntv + b.tv) << kSubKeyBits) | (b.lu << 4 | b.lv);
+constexpr uint32_t kNoKey = 0xffffffffu;
+// Sort key of a sample: its (window, tile) bin and the register-window lattice position inside the tile, dense;
+// kNoKey for samples whose window the current binning pass does not cover.
+__device__ __forceinline__ uint32_t bin_key(const GridGeom& g, const BinCell& b) {
+  if (b.win < g.win_begin || b.win >= g.win_end) return kNoKey;
+  const uint32_t bin = ((uint32_t)(b.win - g.win_begin) * (uint32_t)g.ntu + (uint32_t)b.tu) * (uint32_t)g.ntv + (uint32_t)b.tv;
+  return (bin * (uint32_t)g.nlat + b.lu) * (uint32_t)g.nlat + b.lv;
+}
+// Inverse, for the consumers of a job.
+struct KeyParts {
+  int win, tu, tv, lu, lv;
+};
+__device__ __forceinline__ KeyParts key_parts(const GridGeom& g, uint32_t key) {
+  KeyParts k;
+  k.lv = (int)(key % (uint32_t)g.nlat);
+  key /= (uint32_t)g.nlat;
+  k.lu = (int)(key % (uint32_t)g.nlat);
+  key /= (uint32_t)g.nlat;
+  k.tv = (int)(key % (uint32_t)g.ntv);
+  key /= (uint32_t)g.ntv;
+  k.tu = (int)(key % (uint32_t)g.ntu);
+  k.win = (int)(key / (uint32_t)g.ntu) + g.win_begin;
+  return k;
 }
 
 __device__ __forceinline__ bool sample_active(const float2 v, const float* wgt, const uint8_t* mask, int64_t k,

@@ -2,8 +2,9 @@
 // SURVEY.md section 8a, the hot loop of ducc0.wgridder.ms2dirty (reference call site
 // src/ska_sdp_cip/invert.py:170-183).
 //
-// Two kernels for supports W <= 8, both working on work items = the sorted records of one uv tile
-// (kTile x kTile support origins) and one window of kWin w planes, plus a plain scatter for W > 8:
+// float32 grids with W <= 8 are gridded by the tcgen05 kernel of grid_tc.cu.  This file holds the other paths, all
+// working on the jobs of bin.cu (the records of one uv tile, one window of kWin w planes and one register-window
+// lattice position), each CTA striding over the job list:
 //
 // * float32, grid_warp_kernel ("rank-1 tiles"): one warp per item.  Per batch of 32 visibilities the warp
 //   first evaluates the ES kernel separably (one visibility per lane) and stages the 8 x 8 products
@@ -32,6 +33,37 @@ constexpr int kStages = 2;
 constexpr int kGridThreads = 64;
 
 using u64 = unsigned long long;
+
+// A job as the kernels below see it.
+struct Item {
+  int64_t rec_begin;
+  int32_t nrec, tu, tv, win;
+};
+__device__ __forceinline__ Item job_item(const Job& job, const GridGeom& g) {
+  (void)g;
+  Item it;
+  it.rec_begin = (int64_t)job.group_begin * kGroup;
+  it.nrec = (int32_t)(job.ngroups & ~kJobStartsItem) * kGroup;
+  it.tu = job.tu;
+  it.tv = job.tv;
+  it.win = job.win;
+  return it;
+}
+// The jobs of windows [win_first, win_last] (bin.cu leaves the first job of every window of the pass on the device).
+struct JobList {
+  const Job* jobs;
+  const uint32_t* win_job_start;
+  const BinHeader* hdr;
+  int win_first, win_last;
+};
+__device__ __forceinline__ void job_range(const JobList& jl, const GridGeom& g, uint32_t* jb, uint32_t* je) {
+  if (jl.hdr->overflow) {
+    *jb = *je = 0;
+    return;
+  }
+  *jb = jl.win_job_start[jl.win_first - g.win_begin];
+  *je = jl.win_job_start[jl.win_last + 1 - g.win_begin];
+}
 
 // ---- small PTX helpers ----------------------------------------------------------------
 __device__ __forceinline__ uint32_t smem_u32(const void* p) { return (uint32_t)__cvta_generic_to_shared(p); }
@@ -246,15 +278,16 @@ __device__ __forceinline__ void consume8(const Stage<R>& st, const typename Acc<
 
 // ---- the kernel -----------------------------------------------------------------------
 template <typename R>
-__global__ void __launch_bounds__(kGridThreads) grid_kernel(const Item* __restrict__ items, int64_t item_base,
-                                                            const Rec<R>* __restrict__ recs, GridGeom g, R* __restrict__ grid,
+__global__ void __launch_bounds__(kGridThreads) grid_kernel(JobList jl, const Rec<R>* __restrict__ recs, GridGeom g, R* __restrict__ grid,
                                                             int plane_base, int nslots) {
   using Cell = typename SubGrid<R>::cell;
   extern __shared__ __align__(16) unsigned char smem_raw[];
   Cell* sg = reinterpret_cast<Cell*>(smem_raw);
   Stage<R>* stages = reinterpret_cast<Stage<R>*>(smem_raw + sizeof(Cell) * SubGrid<R>::ncell);
-
-  const Item item = items[item_base + blockIdx.x];
+  uint32_t jb, je;
+  job_range(jl, g, &jb, &je);
+  for (uint32_t jix = jb + blockIdx.x; jix < je; jix += gridDim.x) {
+  const Item item = job_item(jl.jobs[jix], g);
   const int tid = threadIdx.x, lane = tid & 31, warp = tid >> 5;
   const int nrec = item.nrec;
   const int nb = (nrec + kBatch - 1) / kBatch;
@@ -340,6 +373,8 @@ __global__ void __launch_bounds__(kGridThreads) grid_kernel(const Item* __restri
       atomicAdd(dst, v.x);
       atomicAdd(dst + 1, v.y);
     }
+  }
+  __syncthreads();  // the sub-grid and the stages are reused by the CTA's next job
   }
 }
 
@@ -732,9 +767,8 @@ __device__ __forceinline__ void warp_consume8(uint32_t pa, uint32_t pb, uint32_t
 // leaves it (the records are sorted by window, so that happens ~ once per lattice position and item).  This
 // trades ~4x more L2 reductions for 14.4 KB of shared memory per warp, i.e. twice the resident warps.
 template <int NW, bool DIRECT, int MMA>
-__global__ void __launch_bounds__(32 * NW, DIRECT ? (MMA == 2 ? 24 : 20) : 1) grid_warp_kernel(const Item* __restrict__ items, int64_t item_base,
-                                                            const RecP* __restrict__ recs, GridGeom g,
-                                                            float* __restrict__ grid, int plane_base, int nslots) {
+__device__ __forceinline__ void grid_warp_item(const Item& item, const RecP* __restrict__ recs, const GridGeom& g,
+                                               float* __restrict__ grid, int plane_base, int nslots) {
   constexpr int MODE = DIRECT ? 2 : (NW > 1 ? 1 : 0);
   constexpr int kSubBytes = DIRECT ? 0 : kWarpSubGridBytes;
   extern __shared__ __align__(16) unsigned char smem_raw[];
@@ -746,7 +780,6 @@ __global__ void __launch_bounds__(32 * NW, DIRECT ? (MMA == 2 ? 24 : 20) : 1) gr
   const uint32_t sB = sA + kBatch * ROW;
   const uint32_t sOrg = sB + kBatch * kBRow;
 
-  const Item item = items[item_base + blockIdx.x];
   const int nrec = item.nrec;
   const int nb_all = (nrec + kBatch - 1) / kBatch;
   const int b_begin = warp * nb_all / NW, b_end = (warp + 1) * nb_all / NW;
@@ -916,12 +949,62 @@ __global__ void __launch_bounds__(32 * NW, DIRECT ? (MMA == 2 ? 24 : 20) : 1) gr
   }
 }
 
+// The work items of the pass (bin.cu): the list of their first jobs; an item runs up to the next job that starts one.
+struct ItemList {
+  const Job* jobs;
+  const uint32_t* items;
+  uint32_t* counters;  // [0] number of items, [1] next item to hand out
+  const BinHeader* hdr;
+  int win_first, win_last;
+};
+
+template <int NW, bool DIRECT, int MMA>
+__global__ void __launch_bounds__(32 * NW, DIRECT ? (MMA == 2 ? 24 : 20) : 1) grid_warp_kernel(ItemList il, const RecP* __restrict__ recs, GridGeom g,
+                                                            float* __restrict__ grid, int plane_base, int nslots) {
+  static_assert(NW == 1, "one warp per CTA");
+  if (il.hdr->overflow) return;
+  const uint32_t n = il.counters[0], njobs = il.hdr->njobs;
+  const int lane = threadIdx.x & 31;
+  for (;;) {
+    // items are handed out dynamically: their sizes differ by orders of magnitude
+    uint32_t i = 0;
+    if (lane == 0) i = atomicAdd(il.counters + 1, 1u);
+    i = __shfl_sync(0xffffffffu, i, 0);
+    if (i >= n) break;
+    const uint32_t ja = il.items[i];
+    const Job a = il.jobs[ja];
+    if ((int)a.win < il.win_first || (int)a.win > il.win_last) continue;
+    // the item ends before the next job that starts one
+    uint32_t jb = ja + 1;
+    for (;; jb += 32) {
+      const uint32_t k = jb + lane;
+      const bool stop = k >= njobs || (il.jobs[k].ngroups & kJobStartsItem);
+      const unsigned m = __ballot_sync(0xffffffffu, stop);
+      if (m) {
+        jb += __ffs(m) - 1;
+        break;
+      }
+    }
+    const Job b = il.jobs[jb - 1];
+    Item item;
+    item.rec_begin = (int64_t)a.group_begin * kGroup;
+    item.nrec = (int32_t)((b.group_begin + (b.ngroups & ~kJobStartsItem) - a.group_begin) * kGroup);
+    item.tu = a.tu;
+    item.tv = a.tv;
+    item.win = a.win;
+    grid_warp_item<NW, DIRECT, MMA>(item, recs, g, grid, plane_base, nslots);
+    __syncwarp();
+  }
+}
+
 // Wide supports (W > 8, only reached for very small epsilon): plain scatter with global atomics.
 template <typename R>
-__global__ void __launch_bounds__(128) grid_wide_kernel(const Item* __restrict__ items, int64_t item_base,
-                                                        const Rec<R>* __restrict__ recs, GridGeom g, R* __restrict__ grid,
+__global__ void __launch_bounds__(128) grid_wide_kernel(JobList jl, const Rec<R>* __restrict__ recs, GridGeom g, R* __restrict__ grid,
                                                         int plane_base, int nslots) {
-  const Item item = items[item_base + blockIdx.x];
+  uint32_t jb, je;
+  job_range(jl, g, &jb, &je);
+  for (uint32_t jix = jb + blockIdx.x; jix < je; jix += gridDim.x) {
+  const Item item = job_item(jl.jobs[jix], g);
   const int W = g.W;
   const int su0 = item.tu * kTile - kHalo + g.nu / 2, sv0 = item.tv * kTile - kHalo + g.nv / 2;
   for (int k = threadIdx.x; k < item.nrec; k += blockDim.x) {
@@ -956,41 +1039,47 @@ __global__ void __launch_bounds__(128) grid_wide_kernel(const Item* __restrict__
       }
     }
   }
+  }
 }
 
-template <int NW, bool DIRECT, int MMA = 0>
-cip_status launch_warp(cip_ctx* ctx, cudaStream_t stream, const Item* items, int64_t item_begin, int64_t n, const RecP* recs,
-                       const GridGeom& g, float* grid, int plane_base, int nslots) {
-  auto kern = grid_warp_kernel<NW, DIRECT, MMA>;
-  constexpr int smem = warp_smem_bytes(NW, DIRECT, MMA != 0);
+}  // namespace
+
+cip_status run_gridder_tc(cip_ctx* ctx, int slot, cudaStream_t stream, const GridGeom& g, int win_first, int win_last, float* grid,
+                          int plane_base, int nslots);
+
+namespace {
+
+template <int MMA>
+cip_status launch_warp(cip_ctx* ctx, cudaStream_t stream, const ItemList& jl, const RecP* recs, const GridGeom& g, float* grid,
+                       int plane_base, int nslots) {
+  auto kern = grid_warp_kernel<1, true, MMA>;
+  constexpr int smem = warp_smem_bytes(1, true, MMA != 0);
   CIP_CHECK_CUDA(cudaFuncSetAttribute(kern, cudaFuncAttributeMaxDynamicSharedMemorySize, smem));
   CIP_CHECK_CUDA(cudaFuncSetAttribute(kern, cudaFuncAttributePreferredSharedMemoryCarveout, (int)cudaSharedmemCarveoutMaxShared));
-  kern<<<(unsigned)n, 32 * NW, smem, stream>>>(items, item_begin, recs, g, grid, plane_base, nslots);
+  kern<<<ctx->sm_count * 20, 32, smem, stream>>>(jl, recs, g, grid, plane_base, nslots);
   return CIP_OK;
 }
 
 template <typename R>
-cip_status launch(cip_ctx* ctx, int slot, cudaStream_t stream, const GridGeom& g, int64_t nrec_total, int64_t item_begin,
-                  int64_t item_end, void* grid, int plane_base, int nslots) {
-  const Item* items = ctx->work[slot].items.as<Item>();
-  const Rec<R>* recs = ctx->work[slot].recs.as<Rec<R>>();
-  (void)nrec_total;
-  const int64_t n = item_end - item_begin;
-  if (n <= 0) return CIP_OK;
-  CIP_REQUIRE(n < ((int64_t)1 << 31), "too many work items");
+cip_status launch(cip_ctx* ctx, int slot, cudaStream_t stream, const GridGeom& g, int win_first, int win_last, void* grid,
+                  int plane_base, int nslots) {
+  const BinWork& w = ctx->work[slot];
+  const JobList jl{w.jobs.as<Job>(), w.win_job_start.as<uint32_t>(), w.hdr.as<BinHeader>(), win_first, win_last};
+  const Rec<R>* recs = w.recs.as<Rec<R>>();
   if (g.W <= kFastSupport) {
     if constexpr (sizeof(R) == 4) {
-      // float32: warp-autonomous kernel.  CIP_GRID_DIRECT=0 keeps the shared sub-grid (8 warps/SM, measured
-      // 10.8 ms on configs[1] against 10.0 ms for the direct fold), CIP_GRID_WARPS=2|4 shares it between warps.
-      const int nw = getenv("CIP_GRID_WARPS") ? atoi(getenv("CIP_GRID_WARPS")) : 1;
-      const bool direct = getenv("CIP_GRID_DIRECT") ? atoi(getenv("CIP_GRID_DIRECT")) != 0 : true;
+      // float32: the register-window kernel (3xTF32 mma.sync tiles, float32 additions) on the work items of the
+      // pass; CIP_GRID_MMA=0 selects its FFMA2 form (A/B).  CIP_GRID_TC=1 selects the tcgen05 kernel of grid_tc.cu
+      // instead -- correct, and the tensor pipe itself is fast there, but feeding its A operand through tensor
+      // memory costs more shared-memory bandwidth and issue overhead than the whole of this kernel.
+      if (use_tc_gridder())
+        return run_gridder_tc(ctx, slot, stream, g, win_first, win_last, static_cast<float*>(grid), plane_base, nslots);
+      uint32_t* counters = w.items.as<uint32_t>() + w.cap_jobs;
+      CIP_CHECK_CUDA(cudaMemsetAsync(counters + 1, 0, sizeof(uint32_t), stream));  // the same items may be gridded again (plane blocks)
+      const ItemList il{w.jobs.as<Job>(), w.items.as<uint32_t>(), counters, w.hdr.as<BinHeader>(), win_first, win_last};
       const int mma = getenv("CIP_GRID_MMA") ? atoi(getenv("CIP_GRID_MMA")) : 1;
-      if (direct && mma == 2) CIP_TRY((launch_warp<1, true, 2>(ctx, stream, items, item_begin, n, reinterpret_cast<const RecP*>(recs), g, static_cast<float*>(grid), plane_base, nslots)));
-      else if (direct && mma) CIP_TRY((launch_warp<1, true, 1>(ctx, stream, items, item_begin, n, reinterpret_cast<const RecP*>(recs), g, static_cast<float*>(grid), plane_base, nslots)));
-      else if (direct) CIP_TRY((launch_warp<1, true>(ctx, stream, items, item_begin, n, reinterpret_cast<const RecP*>(recs), g, static_cast<float*>(grid), plane_base, nslots)));
-      else if (nw == 2) CIP_TRY((launch_warp<2, false>(ctx, stream, items, item_begin, n, reinterpret_cast<const RecP*>(recs), g, static_cast<float*>(grid), plane_base, nslots)));
-      else if (nw == 4) CIP_TRY((launch_warp<4, false>(ctx, stream, items, item_begin, n, reinterpret_cast<const RecP*>(recs), g, static_cast<float*>(grid), plane_base, nslots)));
-      else CIP_TRY((launch_warp<1, false>(ctx, stream, items, item_begin, n, reinterpret_cast<const RecP*>(recs), g, static_cast<float*>(grid), plane_base, nslots)));
+      if (mma == 0) CIP_TRY((launch_warp<0>(ctx, stream, il, reinterpret_cast<const RecP*>(recs), g, static_cast<float*>(grid), plane_base, nslots)));
+      else CIP_TRY((launch_warp<1>(ctx, stream, il, reinterpret_cast<const RecP*>(recs), g, static_cast<float*>(grid), plane_base, nslots)));
     } else {
       // float64: producer / consumer warp pair ("residue owner")
       constexpr size_t smem = grid_smem_bytes<R>();
@@ -998,11 +1087,10 @@ cip_status launch(cip_ctx* ctx, int slot, cudaStream_t stream, const GridGeom& g
       CIP_CHECK_CUDA(cudaFuncSetAttribute(kern, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem));
       CIP_CHECK_CUDA(cudaFuncSetAttribute(kern, cudaFuncAttributePreferredSharedMemoryCarveout,
                                           (int)cudaSharedmemCarveoutMaxShared));
-      kern<<<(unsigned)n, kGridThreads, smem, stream>>>(items, item_begin, recs, g, static_cast<R*>(grid), plane_base, nslots);
+      kern<<<ctx->sm_count * 8, kGridThreads, smem, stream>>>(jl, recs, g, static_cast<R*>(grid), plane_base, nslots);
     }
   } else {
-    grid_wide_kernel<R><<<(unsigned)n, 128, 0, stream>>>(items, item_begin, recs, g, static_cast<R*>(grid),
-                                                              plane_base, nslots);
+    grid_wide_kernel<R><<<ctx->sm_count * 16, 128, 0, stream>>>(jl, recs, g, static_cast<R*>(grid), plane_base, nslots);
   }
   ctx->launches++;
   CIP_CHECK_CUDA(cudaGetLastError());
@@ -1011,10 +1099,15 @@ cip_status launch(cip_ctx* ctx, int slot, cudaStream_t stream, const GridGeom& g
 
 }  // namespace
 
-cip_status run_gridder(cip_ctx* ctx, int slot, cudaStream_t stream, const GridGeom& g, int fp64, int64_t nrec_total,
-                       int64_t item_begin, int64_t item_end, void* grid, int plane_base, int nslots) {
-  if (fp64) return launch<double>(ctx, slot, stream, g, nrec_total, item_begin, item_end, grid, plane_base, nslots);
-  return launch<float>(ctx, slot, stream, g, nrec_total, item_begin, item_end, grid, plane_base, nslots);
+bool use_tc_gridder() {
+  const char* e = getenv("CIP_GRID_TC");
+  return e && atoi(e) != 0;
+}
+
+cip_status run_gridder(cip_ctx* ctx, int slot, cudaStream_t stream, const GridGeom& g, int fp64, int win_first, int win_last,
+                       void* grid, int plane_base, int nslots) {
+  if (fp64) return launch<double>(ctx, slot, stream, g, win_first, win_last, grid, plane_base, nslots);
+  return launch<float>(ctx, slot, stream, g, win_first, win_last, grid, plane_base, nslots);
 }
 
 }  // namespace cip

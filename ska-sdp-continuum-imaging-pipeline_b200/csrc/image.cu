@@ -21,13 +21,14 @@ struct ScreenParams {
   int nx, ny, nu, nv;
   double px, py, w0, dw, nshift;
   int plane_base, nslots, nplanes, do_wstacking;
+  const uint32_t* skip;  // != 0 on the device: a binning pass of this call overflowed, the image must stay untouched
 };
 
 template <typename R>
 __global__ void __launch_bounds__(256) wscreen_kernel(ScreenParams p, const R* __restrict__ grid, R* __restrict__ image) {
   const int j = blockIdx.x * blockDim.x + threadIdx.x;
   const int i = blockIdx.y;
-  if (j >= p.ny) return;
+  if (j >= p.ny || *p.skip) return;
   const int gi = (i - p.nx / 2 + p.nu) % p.nu, gj = (j - p.ny / 2 + p.nv) % p.nv;
   const double l = (i - p.nx / 2) * p.px, m = (j - p.ny / 2) * p.py, e = l * l + m * m;
   if (e >= 1.0) return;
@@ -87,6 +88,7 @@ template <typename R>
 __global__ void __launch_bounds__(256) wscreen_t_kernel(ScreenParams p, int plane, const typename Cplx<R>::type* __restrict__ t,
                                                         R* __restrict__ image) {
   __shared__ R tile[32][33];
+  if (*p.skip) return;
   const int j0 = blockIdx.x * 32, i0 = blockIdx.y * 32;
   const int tx = threadIdx.x & 31, ty = threadIdx.x >> 5;
   const double wp = p.w0 + plane * p.dw;
@@ -168,7 +170,7 @@ __global__ void __launch_bounds__(256) correct_kernel(CorrectParams p, const dou
 
 cip_status run_wscreen(cip_ctx* ctx, const cip_plan& pl, const void* grid, int plane_base, int nslots, void* image) {
   ScreenParams p{pl.npix_x, pl.npix_y, pl.nu, pl.nv, pl.pixsize_x, pl.pixsize_y, pl.w0, pl.dw, pl.nshift,
-                 plane_base, nslots, pl.nplanes, pl.do_wstacking};
+                 plane_base, nslots, pl.nplanes, pl.do_wstacking, ctx->call_flags.as<uint32_t>()};
   dim3 grd((pl.npix_y + 255) / 256, pl.npix_x);
   if (pl.accumulate_fp64)
     wscreen_kernel<double><<<grd, 256, 0, ctx->stream>>>(p, static_cast<const double*>(grid), static_cast<double*>(image));
@@ -217,7 +219,7 @@ cip_status run_fft_screen(cip_ctx* ctx, const cip_plan& pl, void* grid, int plan
     return run_wscreen(ctx, pl, grid, plane_base, nslots, image);
   }
   ScreenParams p{pl.npix_x, pl.npix_y, pl.nu, pl.nv, pl.pixsize_x, pl.pixsize_y, pl.w0, pl.dw, pl.nshift,
-                 plane_base, nslots, pl.nplanes, pl.do_wstacking};
+                 plane_base, nslots, pl.nplanes, pl.do_wstacking, ctx->call_flags.as<uint32_t>()};
   if (pl.accumulate_fp64) return fft_screen_transposed<double>(ctx, pl, p, grid, nslots, image);
   return fft_screen_transposed<float>(ctx, pl, p, grid, nslots, image);
 }

@@ -76,15 +76,13 @@ static DevInputs row_slice(const DevInputs& in, int64_t r0, int64_t r1) {
   return c;
 }
 
-static cip_status grid_accumulate_staged(cip_ctx* ctx, const DevInputs& in, const VisFeed& feed, cip_plan* plan,
-                                         void* image_dev, cip_report* rep) {
+// One attempt: everything is enqueued without a single read-back; `rep` stage times come from event pairs (device
+// inputs) or the host clock around event synchronisations (streamed host inputs, see StageTimer).
+static cip_status grid_accumulate_attempt(cip_ctx* ctx, const DevInputs& in, const VisFeed& feed, cip_plan* plan,
+                                          void* image_dev, cip_report* rep) {
   const int fp64 = plan->accumulate_fp64;
-  CIP_REQUIRE(plan->support >= kMinSupport && plan->support <= kMaxSupport, "bad support %d", plan->support);
-  CIP_REQUIRE(plan->nu >= plan->npix_x && plan->nv >= plan->npix_y && plan->nu % 2 == 0 && plan->nv % 2 == 0,
-              "bad grid size %d x %d", plan->nu, plan->nv);
-  CIP_REQUIRE(plan->nplanes >= 1 && plan->dw > 0, "bad w-plane layout");
-  CIP_REQUIRE(plan->nu >= 2 * kFastSupport + kTile && plan->nv >= 2 * kFastSupport + kTile, "grid too small");
-  const GridGeom g = make_geom(*plan);
+  GridGeom g = make_geom(*plan);
+  const bool want_items = !fp64 && g.W <= kFastSupport && !use_tc_gridder();
   StageTimer tm(ctx, rep != nullptr, feed.nchunks > 0 && feed.ready[0] != nullptr);
   double dummy = 0;
 
@@ -97,11 +95,10 @@ static cip_status grid_accumulate_staged(cip_ctx* ctx, const DevInputs& in, cons
   if (max_slots < plan->nplanes) {
     size_t free_b = 0, total_b = 0;
     CIP_CHECK_CUDA(cudaMemGetInfo(&free_b, &total_b));
-    // keep room for the binning workspaces (records 32 B + runs/keys ~16 B per visibility) if they are
-    // not allocated yet
+    // keep room for the binning workspaces (records 16 .. 32 B per visibility, padded) if they are not allocated yet
     size_t reserve = (size_t)768 << 20;
     const size_t nvis = (size_t)in.nrow * in.nchan;
-    if (ctx->work[0].recs.cap < recs_bytes(nvis) / std::max(feed.nchunks, 1)) reserve += 48 * nvis;
+    if (ctx->work[0].recs.cap < 36 * nvis / std::max(feed.nchunks, 1)) reserve += 40 * nvis;
     size_t avail = free_b + ctx->grid.cap;
     avail = avail > reserve ? avail - reserve : 0;
     max_slots = (int64_t)(avail / plane_bytes);
@@ -120,6 +117,7 @@ static cip_status grid_accumulate_staged(cip_ctx* ctx, const DevInputs& in, cons
   plan->plane_block = nslots_alloc;
   CIP_TRY(ctx->grid.ensure(plane_bytes * nslots_alloc));
   trace_mark("  grid ensured");
+  const int wpp = max_windows_per_pass(g);  // windows one binning pass may cover (size of the key table)
 
   if (nslots_alloc >= plan->nplanes) {
     // All planes resident: bin and grid each row chunk as soon as its visibilities have arrived (host
@@ -127,19 +125,18 @@ static cip_status grid_accumulate_staged(cip_ctx* ctx, const DevInputs& in, cons
     tm.start();
     CIP_CHECK_CUDA(cudaMemsetAsync(ctx->grid.p, 0, plane_bytes * plan->nplanes, ctx->stream));
     tm.stop(rep ? &rep->ms_zero : &dummy);
-    // Chunk c is binned on the context stream into workspace c & 1 and gridded on the grid stream, so that
-    // the binning of chunk c+1 overlaps the gridding of chunk c.  Device inputs are timed with event pairs
+    // Pass k is binned on the context stream into workspace k & 1 and gridded on the grid stream, so that
+    // the binning of the next pass overlaps the gridding of this one.  Device inputs are timed with event pairs
     // that nobody waits for until the end; host inputs (timed with the host clock, see StageTimer) give up
     // the overlap when a report is requested.
     const bool dev_timing = rep && !tm.host;
     cudaStream_t gs = ctx->grid_stream;
     CIP_CHECK_CUDA(cudaEventRecord(ctx->zero_ev, ctx->stream));
     CIP_CHECK_CUDA(cudaStreamWaitEvent(gs, ctx->zero_ev, 0));
-    bool any = false, used[2] = {false, false};
-    std::vector<int> timed_bin, timed_grid;
+    bool used[2] = {false, false};
+    int pass = 0, ntimed = 0;
     for (int c = 0; c < feed.nchunks; ++c) {
       if (feed.row0[c + 1] <= feed.row0[c]) continue;
-      const int slot = c & 1;
       if (feed.ready[c]) {
         if (rep) {  // timed call: the host waits for the chunk so that the stage times exclude the upload
           CIP_CHECK_CUDA(cudaEventSynchronize(feed.ready[c]));
@@ -148,78 +145,69 @@ static cip_status grid_accumulate_staged(cip_ctx* ctx, const DevInputs& in, cons
           CIP_CHECK_CUDA(cudaStreamWaitEvent(ctx->stream, feed.ready[c], 0));
         }
       }
-      if (used[slot]) CIP_CHECK_CUDA(cudaStreamWaitEvent(ctx->stream, ctx->gridded_ev[slot], 0));  // workspace in use
       const DevInputs chunk = row_slice(in, feed.row0[c], feed.row0[c + 1]);
-      if (dev_timing) CIP_CHECK_CUDA(cudaEventRecord(ctx->chunk_t[c][0], ctx->stream));
-      else tm.start();
-      BinResult bins;
-      CIP_TRY(run_binning(ctx, slot, chunk, g, fp64, &bins));
-      if (dev_timing) {
-        CIP_CHECK_CUDA(cudaEventRecord(ctx->chunk_t[c][1], ctx->stream));
-        timed_bin.push_back(c);
-      } else {
-        tm.stop(rep ? &rep->ms_bin : &dummy);
+      for (int wa = 0; wa < g.nwin; wa += wpp, ++pass) {
+        const int slot = pass & 1;
+        g.win_begin = wa;
+        g.win_end = std::min(g.nwin, wa + wpp);
+        if (used[slot]) CIP_CHECK_CUDA(cudaStreamWaitEvent(ctx->stream, ctx->gridded_ev[slot], 0));  // workspace in use
+        const bool timed = dev_timing && ntimed < kMaxChunks;
+        if (timed) CIP_CHECK_CUDA(cudaEventRecord(ctx->chunk_t[ntimed][0], ctx->stream));
+        else tm.start();
+        CIP_TRY(run_binning(ctx, slot, chunk, g, fp64, want_items));
+        if (timed) CIP_CHECK_CUDA(cudaEventRecord(ctx->chunk_t[ntimed][1], ctx->stream));
+        else tm.stop(rep ? &rep->ms_bin : &dummy);
+        trace_mark("  pass binned");
+        CIP_CHECK_CUDA(cudaEventRecord(ctx->binned_ev[slot], ctx->stream));
+        CIP_CHECK_CUDA(cudaStreamWaitEvent(gs, ctx->binned_ev[slot], 0));
+        const double t0 = now_ms();
+        if (timed) CIP_CHECK_CUDA(cudaEventRecord(ctx->chunk_t[ntimed][2], gs));
+        CIP_TRY(run_gridder(ctx, slot, gs, g, fp64, g.win_begin, g.win_end - 1, ctx->grid.p, 0, plan->nplanes));
+        if (timed) CIP_CHECK_CUDA(cudaEventRecord(ctx->chunk_t[ntimed][3], gs));
+        CIP_CHECK_CUDA(cudaEventRecord(ctx->gridded_ev[slot], gs));
+        used[slot] = true;
+        if (timed) ++ntimed;
+        if (rep) rep->nblocks++;
+        if (rep && !dev_timing) {
+          CIP_CHECK_CUDA(cudaEventSynchronize(ctx->gridded_ev[slot]));
+          rep->ms_grid += now_ms() - t0;
+        }
+        trace_mark("  pass gridded");
       }
-      trace_mark("  chunk binned");
-      if (bins.nitems == 0) continue;
-      any = true;
-      CIP_CHECK_CUDA(cudaEventRecord(ctx->binned_ev[slot], ctx->stream));
-      CIP_CHECK_CUDA(cudaStreamWaitEvent(gs, ctx->binned_ev[slot], 0));
-      const double t0 = now_ms();
-      if (dev_timing) CIP_CHECK_CUDA(cudaEventRecord(ctx->chunk_t[c][2], gs));
-      CIP_TRY(run_gridder(ctx, slot, gs, g, fp64, bins.nrec, 0, bins.nitems, ctx->grid.p, 0, plan->nplanes));
-      if (dev_timing) {
-        CIP_CHECK_CUDA(cudaEventRecord(ctx->chunk_t[c][3], gs));
-        timed_grid.push_back(c);
-      }
-      CIP_CHECK_CUDA(cudaEventRecord(ctx->gridded_ev[slot], gs));
-      used[slot] = true;
-      if (rep && !dev_timing) {
-        CIP_CHECK_CUDA(cudaEventSynchronize(ctx->gridded_ev[slot]));
-        rep->ms_grid += now_ms() - t0;
-      }
-      trace_mark("  chunk gridded");
     }
     for (int slot = 0; slot < 2; ++slot)
       if (used[slot]) CIP_CHECK_CUDA(cudaStreamWaitEvent(ctx->stream, ctx->gridded_ev[slot], 0));
     if (dev_timing) {
       CIP_CHECK_CUDA(cudaStreamSynchronize(ctx->stream));
       float ms = 0;
-      for (int c : timed_bin) {
-        CIP_CHECK_CUDA(cudaEventElapsedTime(&ms, ctx->chunk_t[c][0], ctx->chunk_t[c][1]));
+      for (int k = 0; k < ntimed; ++k) {
+        CIP_CHECK_CUDA(cudaEventElapsedTime(&ms, ctx->chunk_t[k][0], ctx->chunk_t[k][1]));
         rep->ms_bin += ms;
-      }
-      for (int c : timed_grid) {
-        CIP_CHECK_CUDA(cudaEventElapsedTime(&ms, ctx->chunk_t[c][2], ctx->chunk_t[c][3]));
+        CIP_CHECK_CUDA(cudaEventElapsedTime(&ms, ctx->chunk_t[k][2], ctx->chunk_t[k][3]));
         rep->ms_grid += ms;
       }
     }
-    if (rep) rep->nblocks = feed.nchunks;
-    if (!any) return CIP_OK;
     tm.start();  // ms_fft includes the w-screen (they alternate per plane)
     CIP_TRY(run_fft_screen(ctx, *plan, ctx->grid.p, 0, plan->nplanes, image_dev, nullptr, nullptr));
     tm.stop(rep ? &rep->ms_fft : &dummy);
     return CIP_OK;
   }
 
-  // Blocks of planes: every block needs all visibilities, so bin them once, unchunked.
+  // Blocks of planes: every block needs all visibilities.
   CIP_TRY(wait_feed(ctx, feed));
-  tm.start();
-  BinResult bins;
-  CIP_TRY(run_binning(ctx, 0, in, g, fp64, &bins));
-  tm.stop(rep ? &rep->ms_bin : &dummy);
-  if (bins.nitems == 0) return CIP_OK;
-
-  if (g.W > kFastSupport && nslots_alloc < plan->nplanes) {
-    // Wide supports have a single window; blocks of resident planes each take a pass over all
+  if (g.W > kFastSupport) {
+    // Wide supports have a single window: bin once; blocks of resident planes each take a pass over all
     // records (the kernel skips contributions to planes outside the block).
+    tm.start();
+    CIP_TRY(run_binning(ctx, 0, in, g, fp64, want_items));
+    tm.stop(rep ? &rep->ms_bin : &dummy);
     for (int pb = 0; pb < plan->nplanes; pb += nslots_alloc) {
       const int used = std::min(nslots_alloc, plan->nplanes - pb);
       tm.start();
       CIP_CHECK_CUDA(cudaMemsetAsync(ctx->grid.p, 0, plane_bytes * used, ctx->stream));
       tm.stop(rep ? &rep->ms_zero : &dummy);
       tm.start();
-      CIP_TRY(run_gridder(ctx, 0, ctx->stream, g, fp64, bins.nrec, 0, bins.nitems, ctx->grid.p, pb, used));
+      CIP_TRY(run_gridder(ctx, 0, ctx->stream, g, fp64, 0, 0, ctx->grid.p, pb, used));
       tm.stop(rep ? &rep->ms_grid : &dummy);
       tm.start();
       CIP_TRY(run_fft_screen(ctx, *plan, ctx->grid.p, pb, used, image_dev, nullptr, nullptr));
@@ -229,34 +217,65 @@ static cip_status grid_accumulate_staged(cip_ctx* ctx, const DevInputs& in, cons
     return CIP_OK;
   }
 
-  int w = 0;
-  while (w < g.nwin) {
-    int pb, wl, used;
-    if (nslots_alloc >= plan->nplanes) {
-      pb = 0;
-      wl = g.nwin - 1;
-      used = plan->nplanes;
-    } else {
-      pb = w * g.win_step;
-      wl = std::min(g.nwin - 1, w + (nslots_alloc - kWin) / g.win_step);
-      used = std::min(plan->nplanes, wl * g.win_step + kWin) - pb;
-    }
-    const int64_t it0 = bins.win_item_start[w], it1 = bins.win_item_start[wl + 1];
-    if (it1 > it0) {
-      tm.start();
-      CIP_CHECK_CUDA(cudaMemsetAsync(ctx->grid.p, 0, plane_bytes * used, ctx->stream));
-      tm.stop(rep ? &rep->ms_zero : &dummy);
-      tm.start();
-      CIP_TRY(run_gridder(ctx, 0, ctx->stream, g, fp64, bins.nrec, it0, it1, ctx->grid.p, pb, used));
-      tm.stop(rep ? &rep->ms_grid : &dummy);
-      tm.start();
-      CIP_TRY(run_fft_screen(ctx, *plan, ctx->grid.p, pb, used, image_dev, nullptr, nullptr));
-      tm.stop(rep ? &rep->ms_fft : &dummy);
-      if (rep) rep->nblocks++;
-    }
-    w = wl + 1;
+  // Windows in blocks whose planes fit the stack: one binning pass per block, restricted to its windows.
+  const int wblock = std::max(1, std::min(wpp, (nslots_alloc - kWin) / g.win_step + 1));
+  for (int wa = 0; wa < g.nwin; wa += wblock) {
+    const int wl = std::min(g.nwin, wa + wblock) - 1;
+    const int pb = wa * g.win_step;
+    const int used = std::min(plan->nplanes, wl * g.win_step + kWin) - pb;
+    g.win_begin = wa;
+    g.win_end = wl + 1;
+    tm.start();
+    CIP_TRY(run_binning(ctx, 0, in, g, fp64, want_items));
+    tm.stop(rep ? &rep->ms_bin : &dummy);
+    tm.start();
+    CIP_CHECK_CUDA(cudaMemsetAsync(ctx->grid.p, 0, plane_bytes * used, ctx->stream));
+    tm.stop(rep ? &rep->ms_zero : &dummy);
+    tm.start();
+    CIP_TRY(run_gridder(ctx, 0, ctx->stream, g, fp64, wa, wl, ctx->grid.p, pb, used));
+    tm.stop(rep ? &rep->ms_grid : &dummy);
+    tm.start();
+    CIP_TRY(run_fft_screen(ctx, *plan, ctx->grid.p, pb, used, image_dev, nullptr, nullptr));
+    tm.stop(rep ? &rep->ms_fft : &dummy);
+    if (rep) rep->nblocks++;
   }
   return CIP_OK;
+}
+
+// The binning sizes its buffers from capacities and reports a shortfall through a flag that everything downstream
+// honours (nothing touches the image then); the flag is looked at once here, after the attempt has drained.  A
+// shortfall grows the buffers to the reported demand and repeats the attempt -- the first call of a new problem
+// size at most.
+static cip_status grid_accumulate_staged(cip_ctx* ctx, const DevInputs& in, const VisFeed& feed, cip_plan* plan,
+                                         void* image_dev, cip_report* rep) {
+  CIP_REQUIRE(plan->support >= kMinSupport && plan->support <= kMaxSupport, "bad support %d", plan->support);
+  CIP_REQUIRE(plan->nu >= plan->npix_x && plan->nv >= plan->npix_y && plan->nu % 2 == 0 && plan->nv % 2 == 0,
+              "bad grid size %d x %d", plan->nu, plan->nv);
+  CIP_REQUIRE(plan->nplanes >= 1 && plan->dw > 0, "bad w-plane layout");
+  CIP_REQUIRE(plan->nu >= 2 * kFastSupport + kTile && plan->nv >= 2 * kFastSupport + kTile, "grid too small");
+  for (int attempt = 0; attempt < 3; ++attempt) {
+    memset(ctx->flags_host, 0, 64);
+    CIP_CHECK_CUDA(cudaMemsetAsync(ctx->call_flags.p, 0, 64, ctx->stream));
+    cip_report scratch{};
+    CIP_TRY(grid_accumulate_attempt(ctx, in, feed, plan, image_dev, rep ? &scratch : nullptr));
+    CIP_CHECK_CUDA(cudaStreamSynchronize(ctx->stream));
+    bool again = false;
+    CIP_TRY(binning_overflowed(ctx, &again));
+    if (!again) {
+      if (rep) {
+        rep->ms_zero += scratch.ms_zero;
+        rep->ms_bin += scratch.ms_bin;
+        rep->ms_grid += scratch.ms_grid;
+        rep->ms_fft += scratch.ms_fft;
+        rep->nblocks += scratch.nblocks;
+        if (scratch.ms_h2d > 0) rep->ms_h2d = scratch.ms_h2d;
+      }
+      return CIP_OK;
+    }
+    trace_mark("  binning buffers were too small: repeating the pass");
+  }
+  set_error("binning buffers still too small after two repeats");
+  return CIP_ECUDA;
 }
 
 extern "C" cip_status cip_grid_accumulate(cip_ctx* ctx, const cip_invert_args* args, cip_plan* plan, void* image_dev,

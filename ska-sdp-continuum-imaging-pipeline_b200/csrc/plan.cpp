@@ -131,6 +131,10 @@ GridGeom make_geom(const cip_plan& p) {
   }
   g.ntu = (p.nu + 2 * kHalo) / kTile + 1;
   g.ntv = (p.nv + 2 * kHalo) / kTile + 1;
+  // origins i0r in 0..7 snapped to a lattice of 9 - W cells: ceil(8 / snap) positions per tile edge
+  g.nlat = p.support <= kFastSupport ? (kTile + (9 - p.support) - 1) / (9 - p.support) : 1;
+  g.win_begin = 0;
+  g.win_end = g.nwin;
   return g;
 }
 

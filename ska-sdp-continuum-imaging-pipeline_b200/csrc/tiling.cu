@@ -258,19 +258,19 @@ extern "C" cip_status cip_tile_bin(cip_ctx* ctx, const double* uvw, int64_t nrow
     d_freq = ctx->t_freq.as<double>();
   }
   // --- runs per row ---------------------------------------------------------------------
-  TTRY(ctx->work[0].row_nruns.ensure(sizeof(int64_t) * (nrow + 1)));
-  TTRY(ctx->work[0].row_off.ensure(sizeof(int64_t) * (nrow + 1)));
-  int64_t* row_n = ctx->work[0].row_nruns.as<int64_t>();
-  int64_t* row_off = ctx->work[0].row_off.as<int64_t>();
+  TTRY(ctx->twork.row_nruns.ensure(sizeof(int64_t) * (nrow + 1)));
+  TTRY(ctx->twork.row_off.ensure(sizeof(int64_t) * (nrow + 1)));
+  int64_t* row_n = ctx->twork.row_nruns.as<int64_t>();
+  int64_t* row_off = ctx->twork.row_off.as<int64_t>();
   TCUDA(cudaMemsetAsync(row_n + nrow, 0, sizeof(int64_t), st));
   const int rblocks = nblk(nrow * 32, 256);
   tile_runs_kernel<0><<<rblocks, 256, 0, st>>>(d_uvw, d_freq, nrow, nchan, tile_size[0], tile_size[1], tile_size[2],
                                                row_n, nullptr, nullptr, nullptr, nullptr, nullptr);
   size_t tmp = 0;
   TCUDA(cub::DeviceScan::ExclusiveSum(nullptr, tmp, row_n, row_off, nrow + 1, st));
-  TTRY(ctx->work[0].cub_tmp.ensure(tmp));
-  tmp = ctx->work[0].cub_tmp.cap;
-  TCUDA(cub::DeviceScan::ExclusiveSum(ctx->work[0].cub_tmp.p, tmp, row_n, row_off, nrow + 1, st));
+  TTRY(ctx->twork.cub_tmp.ensure(tmp));
+  tmp = ctx->twork.cub_tmp.cap;
+  TCUDA(cub::DeviceScan::ExclusiveSum(ctx->twork.cub_tmp.p, tmp, row_n, row_off, nrow + 1, st));
   int64_t ns = 0;
   TCUDA(cudaMemcpyAsync(ctx->scan_host, row_off + nrow, sizeof(int64_t), cudaMemcpyDeviceToHost, st));
   TCUDA(cudaStreamSynchronize(st));
@@ -281,17 +281,17 @@ extern "C" cip_status cip_tile_bin(cip_ctx* ctx, const double* uvw, int64_t nrow
   }
   // --- slices in (row, channel) order ---------------------------------------------------
   // workspace: s_row (8) + s_idx (24) + keys 2x8 + flags 2x8, s_ch0/ch1 (4+4), ids 2x4
-  TTRY(ctx->work[0].runs.ensure((size_t)ns * 32));
-  TTRY(ctx->work[0].run_keys.ensure((size_t)ns * 8));
-  TTRY(ctx->work[0].run_keys_alt.ensure((size_t)ns * 8));
-  TTRY(ctx->work[0].run_idx.ensure((size_t)ns * 4));
-  TTRY(ctx->work[0].run_idx_alt.ensure((size_t)ns * 4));
-  TTRY(ctx->work[0].run_len.ensure((size_t)ns * 8));
-  TTRY(ctx->work[0].flags.ensure((size_t)ns * 16));
+  TTRY(ctx->twork.runs.ensure((size_t)ns * 32));
+  TTRY(ctx->twork.run_keys.ensure((size_t)ns * 8));
+  TTRY(ctx->twork.run_keys_alt.ensure((size_t)ns * 8));
+  TTRY(ctx->twork.run_idx.ensure((size_t)ns * 4));
+  TTRY(ctx->twork.run_idx_alt.ensure((size_t)ns * 4));
+  TTRY(ctx->twork.run_len.ensure((size_t)ns * 8));
+  TTRY(ctx->twork.flags.ensure((size_t)ns * 16));
   TTRY(ctx->scan_out.ensure(sizeof(Range)));
-  int64_t* s_row = ctx->work[0].runs.as<int64_t>();
+  int64_t* s_row = ctx->twork.runs.as<int64_t>();
   long long* s_idx = reinterpret_cast<long long*>(s_row + ns);
-  int32_t* s_ch0 = ctx->work[0].run_len.as<int32_t>();
+  int32_t* s_ch0 = ctx->twork.run_len.as<int32_t>();
   int32_t* s_ch1 = s_ch0 + ns;
   Range* d_range = ctx->scan_out.as<Range>();
   Range h_range;
@@ -314,30 +314,30 @@ extern "C" cip_status cip_tile_bin(cip_ctx* ctx, const double* uvw, int64_t nrow
   }
   // pad extents to powers of two so the packed key never overflows
   const unsigned long long rv = 1ull << bits_for(ext[1]), rw = 1ull << bits_for(ext[2]);
-  uint64_t* keys = ctx->work[0].run_keys.as<uint64_t>();
-  uint64_t* keys_s = ctx->work[0].run_keys_alt.as<uint64_t>();
-  uint32_t* ids = ctx->work[0].run_idx.as<uint32_t>();
-  uint32_t* ids_s = ctx->work[0].run_idx_alt.as<uint32_t>();
+  uint64_t* keys = ctx->twork.run_keys.as<uint64_t>();
+  uint64_t* keys_s = ctx->twork.run_keys_alt.as<uint64_t>();
+  uint32_t* ids = ctx->twork.run_idx.as<uint32_t>();
+  uint32_t* ids_s = ctx->twork.run_idx_alt.as<uint32_t>();
   slice_finish_kernel<<<nblk(ns, 256), 256, 0, st>>>(s_row, s_ch0, s_idx, ns, (int32_t)nchan, h_range, rv, rw, s_ch1,
                                                      keys, ids);
   TCUDA(cub::DeviceRadixSort::SortPairs(nullptr, tmp, keys, keys_s, ids, ids_s, ns, 0, total_bits, st));
-  TTRY(ctx->work[0].cub_tmp.ensure(tmp));
-  tmp = ctx->work[0].cub_tmp.cap;
-  TCUDA(cub::DeviceRadixSort::SortPairs(ctx->work[0].cub_tmp.p, tmp, keys, keys_s, ids, ids_s, ns, 0, total_bits, st));
+  TTRY(ctx->twork.cub_tmp.ensure(tmp));
+  tmp = ctx->twork.cub_tmp.cap;
+  TCUDA(cub::DeviceRadixSort::SortPairs(ctx->twork.cub_tmp.p, tmp, keys, keys_s, ids, ids_s, ns, 0, total_bits, st));
   // --- tiles ----------------------------------------------------------------------------
-  int64_t* flag = ctx->work[0].flags.as<int64_t>();
+  int64_t* flag = ctx->twork.flags.as<int64_t>();
   int64_t* tile_of = flag + ns;
   tile_flags_kernel<<<nblk(ns, 256), 256, 0, st>>>(keys_s, ns, flag);
   TCUDA(cub::DeviceScan::InclusiveSum(nullptr, tmp, flag, tile_of, ns, st));
-  TTRY(ctx->work[0].cub_tmp.ensure(tmp));
-  tmp = ctx->work[0].cub_tmp.cap;
-  TCUDA(cub::DeviceScan::InclusiveSum(ctx->work[0].cub_tmp.p, tmp, flag, tile_of, ns, st));
+  TTRY(ctx->twork.cub_tmp.ensure(tmp));
+  tmp = ctx->twork.cub_tmp.cap;
+  TCUDA(cub::DeviceScan::InclusiveSum(ctx->twork.cub_tmp.p, tmp, flag, tile_of, ns, st));
   TCUDA(cudaMemcpyAsync(ctx->scan_host, tile_of + ns - 1, sizeof(int64_t), cudaMemcpyDeviceToHost, st));
   TCUDA(cudaStreamSynchronize(st));
   const int64_t nt = *static_cast<int64_t*>(ctx->scan_host);
   // per-tile scratch: first_pos (8) | sizes (8, nt+1) | first_id 2x4 | tile_id 2x4
-  TTRY(ctx->work[0].group_start.ensure((size_t)(nt + 1) * 40));
-  int64_t* first_pos = ctx->work[0].group_start.as<int64_t>();
+  TTRY(ctx->twork.group_start.ensure((size_t)(nt + 1) * 40));
+  int64_t* first_pos = ctx->twork.group_start.as<int64_t>();
   int64_t* sizes = first_pos + (nt + 1);
   uint32_t* first_id = reinterpret_cast<uint32_t*>(sizes + (nt + 1));
   uint32_t* first_id_s = first_id + (nt + 1);
@@ -345,9 +345,9 @@ extern "C" cip_status cip_tile_bin(cip_ctx* ctx, const double* uvw, int64_t nrow
   uint32_t* tile_id_s = tile_id + (nt + 1);
   tile_first_kernel<<<nblk(ns, 256), 256, 0, st>>>(flag, tile_of, ids_s, ns, first_pos, first_id, tile_id);
   TCUDA(cub::DeviceRadixSort::SortPairs(nullptr, tmp, first_id, first_id_s, tile_id, tile_id_s, nt, 0, 32, st));
-  TTRY(ctx->work[0].cub_tmp.ensure(tmp));
-  tmp = ctx->work[0].cub_tmp.cap;
-  TCUDA(cub::DeviceRadixSort::SortPairs(ctx->work[0].cub_tmp.p, tmp, first_id, first_id_s, tile_id, tile_id_s, nt, 0, 32, st));
+  TTRY(ctx->twork.cub_tmp.ensure(tmp));
+  tmp = ctx->twork.cub_tmp.cap;
+  TCUDA(cub::DeviceRadixSort::SortPairs(ctx->twork.cub_tmp.p, tmp, first_id, first_id_s, tile_id, tile_id_s, nt, 0, 32, st));
   TTRY(R->tile_coords.ensure(sizeof(int64_t) * 3 * nt));
   TTRY(R->tile_offsets.ensure(sizeof(int64_t) * (nt + 1)));
   TTRY(R->slice_irow.ensure(sizeof(int64_t) * ns));
@@ -356,9 +356,9 @@ extern "C" cip_status cip_tile_bin(cip_ctx* ctx, const double* uvw, int64_t nrow
   tile_order_kernel<<<nblk(nt + 1, 256), 256, 0, st>>>(tile_id_s, first_pos, ids_s, s_idx, nt, ns, sizes,
                                                        R->tile_coords.as<int64_t>());
   TCUDA(cub::DeviceScan::ExclusiveSum(nullptr, tmp, sizes, R->tile_offsets.as<int64_t>(), nt + 1, st));
-  TTRY(ctx->work[0].cub_tmp.ensure(tmp));
-  tmp = ctx->work[0].cub_tmp.cap;
-  TCUDA(cub::DeviceScan::ExclusiveSum(ctx->work[0].cub_tmp.p, tmp, sizes, R->tile_offsets.as<int64_t>(), nt + 1, st));
+  TTRY(ctx->twork.cub_tmp.ensure(tmp));
+  tmp = ctx->twork.cub_tmp.cap;
+  TCUDA(cub::DeviceScan::ExclusiveSum(ctx->twork.cub_tmp.p, tmp, sizes, R->tile_offsets.as<int64_t>(), nt + 1, st));
   tile_emit_kernel<<<(unsigned)nt, 128, 0, st>>>(tile_id_s, first_pos, R->tile_offsets.as<int64_t>(), ids_s, s_row,
                                                  s_ch0, s_ch1, row_offset, R->slice_irow.as<int64_t>(),
                                                  R->slice_ch0.as<int32_t>(), R->slice_ch1.as<int32_t>());
@@ -431,14 +431,14 @@ extern "C" cip_status cip_tile_gather(cip_ctx* ctx, const cip_tile_result* r, co
     CIP_CHECK_CUDA(cudaMemcpyAsync((void*)d_vis, vis, (size_t)nvis * 8, cudaMemcpyHostToDevice, st));
     CIP_CHECK_CUDA(cudaMemcpyAsync((void*)d_uvw, uvw, (size_t)nrow * 24, cudaMemcpyHostToDevice, st));
   }
-  CIP_TRY(ctx->work[0].flags.ensure((size_t)(ns + 1) * 8));
-  int64_t* len = ctx->work[0].flags.as<int64_t>();
+  CIP_TRY(ctx->twork.flags.ensure((size_t)(ns + 1) * 8));
+  int64_t* len = ctx->twork.flags.as<int64_t>();
   slice_len_kernel<<<nblk(ns + 1, 256), 256, 0, st>>>(r->slice_ch0.as<int32_t>(), r->slice_ch1.as<int32_t>(), ns, len);
   size_t tmp = 0;
   CIP_CHECK_CUDA(cub::DeviceScan::ExclusiveSum(nullptr, tmp, len, d_off, ns + 1, st));
-  CIP_TRY(ctx->work[0].cub_tmp.ensure(tmp));
-  tmp = ctx->work[0].cub_tmp.cap;
-  CIP_CHECK_CUDA(cub::DeviceScan::ExclusiveSum(ctx->work[0].cub_tmp.p, tmp, len, d_off, ns + 1, st));
+  CIP_TRY(ctx->twork.cub_tmp.ensure(tmp));
+  tmp = ctx->twork.cub_tmp.cap;
+  CIP_CHECK_CUDA(cub::DeviceScan::ExclusiveSum(ctx->twork.cub_tmp.p, tmp, len, d_off, ns + 1, st));
   gather_kernel<<<nblk(ns * 32, 256), 256, 0, st>>>(d_vis, d_uvw, nchan, r->row_offset, r->slice_irow.as<int64_t>(),
                                                     r->slice_ch0.as<int32_t>(), d_off, ns, d_vout, d_uout);
   ctx->launches += 3;

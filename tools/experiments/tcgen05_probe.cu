@@ -195,11 +195,13 @@ __device__ __forceinline__ uint32_t elect_one() {
 // Issue rate with the descriptors prepared outside the loop: warp 0 enters uniformly, one elected lane issues
 // 8 mma per iteration (4 k-groups x 2 accumulators when ALT, else one accumulator).
 template <int M, int N, bool TS, bool ALT>
-__global__ void __launch_bounds__(128) rate_kernel(int reps, long long* cycles, float* sink) {
+__global__ void __launch_bounds__(128) rate_kernel(int reps, long long* cycles, float* sink, int variant) {
   extern __shared__ __align__(1024) unsigned char smem[];
   __shared__ uint32_t s_tmem;
   __shared__ __align__(8) unsigned long long s_bar;
+  __shared__ __align__(8) unsigned long long s_bar2;
   const int tid = threadIdx.x, warp = tid >> 5;
+  if (tid == 0) mbar_init(smem_u32(&s_bar2), 1);
   for (int i = tid; i < (4 * 256 * 8 + 4 * 128 * 8); i += 128) reinterpret_cast<float*>(smem)[i] = 0.001f * (i & 63);
   if (warp == 0) tmem_alloc(smem_u32(&s_tmem), 512);
   if (tid == 0) mbar_init(smem_u32(&s_bar), 1);
@@ -212,7 +214,7 @@ __global__ void __launch_bounds__(128) rate_kernel(int reps, long long* cycles, 
   if (warp == 0) {
     uint64_t bd[4], ad[4];
     for (int g = 0; g < 4; ++g) {
-      bd[g] = make_sdesc(smem_u32(smem + g * N * 32), 128u, 256u);
+      bd[g] = (variant & 1) ? make_sdesc(smem_u32(smem + g * 1184), 144u, 288u) : make_sdesc(smem_u32(smem + g * N * 32), 128u, 256u);
       ad[g] = make_sdesc(smem_u32(smem + 4 * 256 * 32 + g * M * 32), 128u, 256u);
     }
     const uint32_t d0 = tbase, d1 = tbase + (ALT ? N : 0), a0 = tbase + 256;
@@ -225,6 +227,7 @@ __global__ void __launch_bounds__(128) rate_kernel(int reps, long long* cycles, 
           if (TS) {
             mma_ts(d0, a0 + 8 * g, bd[g], idesc, 1);
             mma_ts(d1, a0 + 32 + 8 * g, bd[g], idesc, 1);
+            if ((variant & 2) && g == 3) commit(smem_u32(&s_bar2));
           } else {
             mma_ss(d0, ad[g], bd[g], idesc, 1);
             mma_ss(d1, ad[g], bd[g], idesc, 1);
@@ -254,7 +257,7 @@ __global__ void __launch_bounds__(128) rate_kernel(int reps, long long* cycles, 
 }
 
 template <int M, int N, bool TS, bool ALT>
-static void run_rate(int reps) {
+static void run_rate(int reps, int variant = 0) {
   long long* cyc;
   float* sink;
   CK(cudaMallocManaged(&cyc, 16));
@@ -263,9 +266,10 @@ static void run_rate(int reps) {
   auto kern = rate_kernel<M, N, TS, ALT>;
   CK(cudaFuncSetAttribute(kern, cudaFuncAttributeMaxDynamicSharedMemorySize, smem));
   for (int it = 0; it < 2; ++it) {
-    kern<<<1, 128, smem>>>(reps, cyc, sink);
+    kern<<<1, 128, smem>>>(reps, cyc, sink, variant);
     CK(cudaDeviceSynchronize());
   }
+  printf("variant %d ", variant);
   printf("lean rate %s M=%3d N=%3d %s: %5d mma: issue %.2f cycles per mma, complete %.2f cycles per mma\n", TS ? "TS" : "SS", M, N,
          ALT ? "2 accumulators" : "1 accumulator ", reps * 8, (double)cyc[0] / (reps * 8), (double)cyc[1] / (reps * 8));
   cudaFree(cyc);
@@ -369,6 +373,9 @@ int main(int argc, char** argv) {
     run_check<128, 32, true>(4, 1, true, 8);
     run_check<128, 16, true>(4, 1, true, 8);
     run_check<128, 64, true>(4, 1, true, 8);
+  }
+  if (!strcmp(mode, "pad")) {
+    for (int v : {0, 1, 2, 3}) run_rate<128, 32, true, true>(256, v);
   }
   if (all || !strcmp(mode, "lean")) {
     for (int reps : {32, 256}) {
