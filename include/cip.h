@@ -136,6 +136,22 @@ cip_status cip_scan(cip_ctx* ctx, const cip_invert_args* args, cip_scan_result* 
 cip_status cip_grid_accumulate(cip_ctx* ctx, const cip_invert_args* args, cip_plan* plan, void* image_dev,
                                cip_report* report /* may be NULL */);
 
+/* Inspection of stage G1 (tests; not needed by callers): bin the samples of `args` for `plan` and copy the gridding
+ * jobs and the gridder-ready records to host memory.  Call with jobs_out = recs_out = NULL for the counts first.
+ * A job is the group of records of one (w window, uv tile, register-window lattice position), padded with zero
+ * records to a multiple of 8; record r of job j is records[(jobs[j].group_begin * 8 + r) * rec_bytes].
+ * rec_bytes = 16: { u64 geo: bits 0-2 i0, 3-5 j0 (support origin inside the tile), 6-9 first plane inside the window,
+ *                   10-27 / 28-45 / 46-63 fractional offsets fu, fv, fw as 0.18 fixed point; f32 re, im }
+ * rec_bytes = 32: { u32 cell: bits 0-4 i0, 5-9 j0, 10+ first plane; fu, fv, fw as f32 (float32 grids) or 0.32 fixed point
+ *                   (float64 grids); re, im as f32 + 8 bytes pad, or f64 } */
+typedef struct {
+  uint32_t group_begin, ngroups; /* ngroups: bit 31 is a flag, mask it */
+  uint16_t tu, tv, win;
+  uint8_t lu, lv;
+} cip_job;
+cip_status cip_bin_inspect(cip_ctx* ctx, const cip_invert_args* args, const cip_plan* plan, int64_t* njobs,
+                           int64_t* ngroups, int* rec_bytes, cip_job* jobs_out, void* recs_out);
+
 /* G4 final + P4: image[r,:] *= scale / (c_u c_v c_w n) for rows row_begin..row_end-1.
  * `image_dev` points at row 0 of the full image. */
 cip_status cip_correct_image(cip_ctx* ctx, const cip_plan* plan, void* image_dev, int row_begin, int row_end,

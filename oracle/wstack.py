@@ -60,6 +60,25 @@ def scan(uvw, freq, vis, wgt):
     return wmin.value, wmax.value, na.value, sumw.value
 
 
+def bin_records(uvw, freq, vis, wgt, pl: Plan):
+    """The oracle's gridder-ready records of all ACTIVE samples (oracle_wg_bin, csrc/wgrid.c): structured array with
+    i0, j0 (first cell, shifted coordinates), p0 (first plane), fu, fv, fw (offsets in [0, 1)), vr, vi."""
+    L = lib()
+    uvw = np.ascontiguousarray(uvw, dtype=np.float64)
+    freq = np.ascontiguousarray(freq, dtype=np.float64)
+    vis = np.ascontiguousarray(vis, dtype=np.complex64)
+    if wgt is not None:
+        wgt = np.ascontiguousarray(wgt, dtype=np.float32)
+    nrow, nchan = vis.shape
+    cp = _cplan(pl)
+    ntu, ntv = (pl.nu + 32) // 32 + 1, (pl.nv + 32) // 32 + 1
+    recs = (_Rec * (nrow * nchan))()
+    offsets = np.zeros(ntu * ntv + 1, dtype=np.int64)
+    n = L.oracle_wg_bin(C.byref(cp), _p(uvw), C.c_int64(nrow), _p(freq), C.c_int64(nchan), _p(vis),
+                        _p(wgt) if wgt is not None else None, recs, _p(offsets), C.c_int(ntu), C.c_int(ntv))
+    return np.frombuffer(recs, dtype=np.dtype(_Rec), count=n).copy()
+
+
 def kernel_ft(pl: Plan, xi, nq=None):
     """c(xi) for the plan's ES kernel."""
     nq = nq or (2 * pl.W + 40)

@@ -296,6 +296,41 @@ extern "C" cip_status cip_grid_accumulate(cip_ctx* ctx, const cip_invert_args* a
   return CIP_OK;
 }
 
+extern "C" cip_status cip_bin_inspect(cip_ctx* ctx, const cip_invert_args* args, const cip_plan* plan, int64_t* njobs,
+                                      int64_t* ngroups, int* rec_bytes, cip_job* jobs_out, void* recs_out) {
+  CIP_REQUIRE(ctx && plan && njobs && ngroups && rec_bytes, "NULL argument");
+  static_assert(sizeof(cip_job) == sizeof(Job), "cip_job mirrors the internal job");
+  CIP_TRY(validate_args(args));
+  CIP_ENTER_DEVICE(ctx);
+  DevInputs in;
+  VisFeed feed;
+  CopyStreamGuard guard(ctx);
+  CIP_TRY(stage_inputs(ctx, args, &in, &feed, false, nullptr));
+  CIP_TRY(wait_feed(ctx, feed));
+  const GridGeom g = make_geom(*plan);
+  CIP_REQUIRE(max_windows_per_pass(g) >= g.nwin, "the key table of this plan does not fit one binning pass");
+  const int fp64 = plan->accumulate_fp64;
+  for (int attempt = 0;; ++attempt) {
+    memset(ctx->flags_host, 0, 64);
+    CIP_CHECK_CUDA(cudaMemsetAsync(ctx->call_flags.p, 0, 64, ctx->stream));
+    CIP_TRY(run_binning(ctx, 0, in, g, fp64, false));
+    CIP_CHECK_CUDA(cudaStreamSynchronize(ctx->stream));
+    bool again = false;
+    CIP_TRY(binning_overflowed(ctx, &again));
+    if (!again) break;
+    CIP_REQUIRE(attempt < 2, "binning buffers still too small after two repeats");
+  }
+  BinHeader h{};
+  CIP_CHECK_CUDA(cudaMemcpy(&h, ctx->work[0].hdr.p, sizeof(h), cudaMemcpyDeviceToHost));
+  *njobs = h.njobs;
+  *ngroups = h.ngroups;
+  *rec_bytes = (!fp64 && g.W <= kFastSupport) ? 16 : 32;
+  if (jobs_out && h.njobs) CIP_CHECK_CUDA(cudaMemcpy(jobs_out, ctx->work[0].jobs.p, sizeof(Job) * h.njobs, cudaMemcpyDeviceToHost));
+  if (recs_out && h.ngroups)
+    CIP_CHECK_CUDA(cudaMemcpy(recs_out, ctx->work[0].recs.p, (size_t)h.ngroups * kGroup * *rec_bytes, cudaMemcpyDeviceToHost));
+  return CIP_OK;
+}
+
 extern "C" cip_status cip_correct_image(cip_ctx* ctx, const cip_plan* plan, void* image_dev, int row_begin,
                                         int row_end, double scale) {
   CIP_REQUIRE(ctx && plan && image_dev, "NULL argument");

@@ -90,6 +90,8 @@ def lib():
             L.cip_scan.argtypes = [C.c_void_p, C.POINTER(InvertArgs), C.POINTER(ScanResult)]
             L.cip_grid_accumulate.argtypes = [C.c_void_p, C.POINTER(InvertArgs), C.POINTER(Plan), C.c_void_p,
                                               C.POINTER(Report)]
+            L.cip_bin_inspect.argtypes = [C.c_void_p, C.POINTER(InvertArgs), C.POINTER(Plan), C.POINTER(C.c_int64),
+                                          C.POINTER(C.c_int64), C.POINTER(C.c_int), C.c_void_p, C.c_void_p]
             L.cip_correct_image.argtypes = [C.c_void_p, C.POINTER(Plan), C.c_void_p, C.c_int, C.c_int, C.c_double]
             L.cip_invert.argtypes = [C.c_void_p, C.POINTER(InvertArgs), C.c_void_p, C.POINTER(ScanResult),
                                      C.POINTER(Plan), C.POINTER(Report)]
@@ -108,7 +110,7 @@ def lib():
 
 EXPORTS = ["cip_last_error", "cip_version", "cip_ctx_create", "cip_ctx_destroy", "cip_ctx_stream",
            "cip_ctx_synchronize", "cip_ctx_launches", "cip_ctx_device", "cip_current_device", "cip_plan_make", "cip_kernel_table", "cip_kernel_ft", "cip_scan",
-           "cip_grid_accumulate", "cip_correct_image", "cip_invert", "cip_stokes_i", "cip_tile_bin",
+           "cip_grid_accumulate", "cip_bin_inspect", "cip_correct_image", "cip_invert", "cip_stokes_i", "cip_tile_bin",
            "cip_tile_fetch", "cip_tile_gather", "cip_tile_free"]
 
 
@@ -186,6 +188,23 @@ def plan_make(nx, ny, px, py, epsilon, wmin, wmax, nactive, *, do_wstacking=True
     check(lib().cip_plan_make(nx, ny, px, py, epsilon, int(do_wstacking), int(fp64), wmin, wmax, int(nactive),
                               float(sigma or 0.0), int(support or 0), C.byref(p)))
     return p
+
+
+JOB_DTYPE = np.dtype([("group_begin", "<u4"), ("ngroups", "<u4"), ("tu", "<u2"), ("tv", "<u2"), ("win", "<u2"),
+                      ("lu", "u1"), ("lv", "u1")])
+
+
+def bin_inspect(ctx: "Context", args: InvertArgs, plan: Plan):
+    """(jobs structured array, records as bytes (ngroups * 8, rec_bytes)) of stage G1 -- see cip_bin_inspect."""
+    nj, ng, rb = C.c_int64(), C.c_int64(), C.c_int()
+    with ctx.lock:
+        check(lib().cip_bin_inspect(ctx.handle, C.byref(args), C.byref(plan), C.byref(nj), C.byref(ng), C.byref(rb), None,
+                                    None))
+        jobs = np.zeros(nj.value, dtype=JOB_DTYPE)
+        recs = np.zeros((ng.value * 8, rb.value), dtype=np.uint8)
+        check(lib().cip_bin_inspect(ctx.handle, C.byref(args), C.byref(plan), C.byref(nj), C.byref(ng), C.byref(rb),
+                                    jobs.ctypes.data, recs.ctypes.data))
+    return jobs, recs
 
 
 def kernel_ft(plan: Plan, xi) -> np.ndarray:

@@ -460,3 +460,71 @@ def test_headline_configuration_slice_recovers_sources(built_lib):
     got = img_sub.reshape(-1)[pix]
     assert dft.rel_rms(got, ref) <= TOL_FP32
     assert np.isfinite(img).all() and np.abs(img).max() > 0
+
+
+# ---- stage G1 on its own: the binning's records against the oracle's (oracle_wg_bin) -----------------------
+
+def _product_records(wg, prob, fp64):
+    """Decode cip_bin_inspect's output into absolute (i0, j0, p0, fu, fv, fw, re, im) per record."""
+    import ctypes as C
+    from ska_sdp_cip import _cabi
+    uvw, freq, vis, wgt, nx, px = prob
+    _, info = invert(wg, prob, double_precision_accumulation=fp64)
+    p = info["plan"]
+    plan = _cabi.Plan(**{k: p[k] for k, _ in _cabi.Plan._fields_})
+    from ska_sdp_cip.wgridder import make_args
+    args = make_args(uvw, freq, vis, wgt, None, nx, nx, px, px, 1e-4, True, fp64, 0)
+    jobs, recs = _cabi.bin_inspect(_cabi.Context.get(-1), args, plan)
+    W = p["support"]
+    win_step = 8 - W + 1 if W <= 8 else 1
+    ngroups = jobs["ngroups"] & 0x7fffffff
+    assert np.all(ngroups >= 1) and np.all(ngroups <= 512)
+    assert np.array_equal(jobs["group_begin"][1:], (jobs["group_begin"] + ngroups)[:-1])  # jobs tile the record array
+    job_of = np.repeat(np.arange(len(jobs)), ngroups * 8)
+    tu, tv, win = (jobs[k][job_of].astype(np.int64) for k in ("tu", "tv", "win"))
+    if recs.shape[1] == 16:
+        geo = recs[:, :8].copy().view("<u8").reshape(-1)
+        val = recs[:, 8:].copy().view("<f4").reshape(-1, 2).astype(np.float64)
+        i0r, j0r, p0r = geo & 7, (geo >> 3) & 7, (geo >> 6) & 15
+        fu, fv, fw = (((geo >> s) & 0x3ffff) / 262144.0 for s in (10, 28, 46))
+        snap = 9 - W  # every record of a job lies in the job's register window
+        assert np.array_equal(i0r // snap, jobs["lu"][job_of]) and np.array_equal(j0r // snap, jobs["lv"][job_of])
+    else:
+        cell = recs[:, :4].copy().view("<u4").reshape(-1)
+        i0r, j0r, p0r = cell & 31, (cell >> 5) & 31, (cell >> 10) & (15 if W <= 8 else 0x3fffff)
+        if fp64:
+            fu, fv, fw = (recs[:, o:o + 4].copy().view("<u4").reshape(-1) / 4294967296.0 for o in (4, 8, 12))
+            val = recs[:, 16:32].copy().view("<f8").reshape(-1, 2)
+        else:
+            fu, fv, fw = (recs[:, o:o + 4].copy().view("<f4").reshape(-1).astype(np.float64) for o in (4, 8, 12))
+            val = recs[:, 16:24].copy().view("<f4").reshape(-1, 2).astype(np.float64)
+    i0 = tu * 8 - 8 + i0r.astype(np.int64)
+    j0 = tv * 8 - 8 + j0r.astype(np.int64)
+    p0 = win * win_step + p0r.astype(np.int64)
+    keep = (val[:, 0] != 0) | (val[:, 1] != 0)   # padding and inactive samples carry zero values
+    out = np.stack([i0, j0, p0, fu, fv, fw, val[:, 0], val[:, 1]], axis=1)[keep]
+    return out, p
+
+
+@pytest.mark.parametrize("which,fp64", [("small", False), ("wide", False), ("small", True)])
+def test_binning_records_match_the_oracle(wg, small, wide, which, fp64):
+    """Stage G1: every active sample appears exactly once, in the right (window, tile, lattice) job, with the oracle's
+    support origin, first plane, fractional offsets (to the record format's resolution) and weighted,
+    conjugated, n-shift-rotated value."""
+    from oracle import plan as oplan
+    prob, _ = small if which == "small" else wide
+    uvw, freq, vis, wgt, nx, px = prob
+    got, p = _product_records(wg, prob, fp64)
+    opl = oplan.Plan(nx=nx, ny=nx, px=px, py=px, sigma=p["sigma"], W=p["support"], beta=p["beta"], nu=p["nu"], nv=p["nv"],
+                     nshift=p["nshift"], dw=p["dw"], w0=p["w0"], nplanes=p["nplanes"], nm1_min=0.0)
+    o = wstack.bin_records(uvw, freq, vis, wgt, opl)
+    want = np.stack([o[k].astype(np.float64) for k in ("i0", "j0", "p0", "fu", "fv", "fw", "vr", "vi")], axis=1)
+    assert len(got) == len(want) == int(np.count_nonzero((wgt != 0) & (vis != 0)))
+    order = lambda a: a[np.lexsort((a[:, 7], a[:, 6], a[:, 2], a[:, 1], a[:, 0]))]
+    got, want = order(got), order(want)
+    # a fraction that rounds to 1.0 in the record is stored as the largest value below it; origins are exact
+    assert np.array_equal(got[:, :3], want[:, :3])
+    ftol = 2.0 ** -18 if (not fp64 and p["support"] <= 8) else (1e-9 if fp64 else 1e-6)
+    assert np.abs(got[:, 3:6] - want[:, 3:6]).max() <= ftol
+    vtol = 1e-12 if fp64 else 2e-7
+    assert np.abs(got[:, 6:] - want[:, 6:]).max() <= vtol * np.abs(want[:, 6:]).max()
