@@ -81,6 +81,8 @@ typedef struct {
   int do_wstacking;         /* 1 = improved w-stacking, 0 = ignore w                 */
   int accumulate_fp64;      /* 0: complex64 grids; 1: complex128 grids + tighter kernel */
   int memspace;             /* 0: all pointers are host memory; 1: device memory of the ctx device */
+  double w_lo, w_hi;        /* w_hi > 0: only the samples with w_lo <= |w| < w_hi (wavelengths) take part -- one
+                             * |w| slab of a w-sharded invert (SURVEY 8e option 3); w_hi <= 0: all samples      */
 } cip_invert_args;
 
 typedef struct {
@@ -128,6 +130,12 @@ cip_status cip_kernel_ft(const cip_plan* plan, const double* xi, int64_t n, doub
  * uvw / freq / weights / mask are reused by a cip_grid_accumulate that follows with the SAME pointers and
  * sizes: the arrays must not change in between. */
 cip_status cip_scan(cip_ctx* ctx, const cip_invert_args* args, cip_scan_result* out);
+
+/* |w| histogram of the active samples of one shard: nbins equal bins over [wmin, wmax], counts ADDED to counts_out
+ * (host, int64[nbins]).  The ranks of a w-sharded invert sum their histograms and cut the |w| axis into slabs of
+ * equal population; each rank then grids one slab (args->w_lo, w_hi) with a plan of its own w range. */
+cip_status cip_w_histogram(cip_ctx* ctx, const cip_invert_args* args, double wmin, double wmax, int nbins,
+                           int64_t* counts_out);
 
 /* G1 binning + G2 gridding + G3 FFT + G4 w-screen: ADD the uncorrected dirty image of the
  * samples in args to `image` (device memory, (npix_x,npix_y) float32, or float64 when

@@ -46,7 +46,10 @@ __global__ void __launch_bounds__(256) hist_kernel(DevInputs in, GridGeom g, con
   for (int c0 = 0; c0 < (int)in.nchan; c0 += 32) {
     const int c = c0 + lane;
     uint32_t key = kNoKey;
-    if (c < in.nchan) key = bin_key(g, bin_cell(g, kc, sample_geom<false>(g, kc, rg, finv[c])));
+    if (c < in.nchan) {
+      const SampleGeom s = sample_geom<false>(g, kc, rg, finv[c]);
+      if (!(in.w_hi > 0.0) || (s.w >= in.w_lo && s.w < in.w_hi)) key = bin_key(g, bin_cell(g, kc, s));
+    }
     uint32_t prev = __shfl_up_sync(0xffffffffu, key, 1);
     const unsigned bound = __ballot_sync(0xffffffffu, lane == 0 || key != prev);  // segment starts (incl. skipped ones)
     if (((bound >> lane) & 1u) && key != kNoKey) {
@@ -309,7 +312,7 @@ __global__ void __launch_bounds__(256, 6) records_kernel(DevInputs in, GridGeom 
     if (valid) {
       s = sample_geom<true>(g, kc, rg, finv[c]);
       bc = bin_cell(g, kc, s);
-      key = bin_key(g, bc);
+      if (!(in.w_hi > 0.0) || (s.w >= in.w_lo && s.w < in.w_hi)) key = bin_key(g, bc);
     }
     const uint32_t prev = __shfl_up_sync(0xffffffffu, key, 1);
     const unsigned bound = __ballot_sync(0xffffffffu, lane == 0 || key != prev);

@@ -266,6 +266,7 @@ struct DevInputs {
   const float* wgt;
   const uint8_t* mask;
   int64_t nrow, nchan, vstride, wstride;
+  double w_lo = 0.0, w_hi = 0.0;  // w_hi > 0: only samples with w_lo <= |w| < w_hi are active
 };
 cip_status validate_args(const cip_invert_args* a);
 // Rows [row0[c], row0[c+1]) of the visibilities are on the device once ready[c] has fired.
@@ -291,6 +292,7 @@ cip_status fetch_small(cip_ctx* ctx, const void* dev, size_t bytes, void* host_o
 
 // ---- stages -----------------------------------------------------------------------
 cip_status run_scan(cip_ctx* ctx, const DevInputs& in, int do_wstacking, cip_scan_result* out);
+cip_status run_w_histogram(cip_ctx* ctx, const DevInputs& in, double wmin, double wmax, int nbins, int64_t* counts_out);
 
 // Bin the samples whose window lies in [g.win_begin, g.win_end) into workspace `slot`: records + jobs + header,
 // all on the device (see bin.cu).  `call_flags` (device, u32) collects overflow over all passes of a call.

@@ -78,6 +78,7 @@ cip_status validate_args(const cip_invert_args* a) {
   CIP_REQUIRE(a->vis_row_stride == 0 || a->vis_row_stride >= a->nchan, "vis_row_stride < nchan");
   CIP_REQUIRE(a->wgt_row_stride == 0 || a->wgt_row_stride >= a->nchan, "wgt_row_stride < nchan");
   CIP_REQUIRE(a->memspace == 0 || a->memspace == 1, "memspace must be 0 (host) or 1 (device)");
+  CIP_REQUIRE(!(a->w_hi > 0) || (a->do_wstacking && a->w_lo >= 0 && a->w_lo < a->w_hi), "bad |w| slab [%g, %g)", a->w_lo, a->w_hi);
   return CIP_OK;
 }
 
@@ -102,6 +103,8 @@ cip_status stage_inputs(cip_ctx* ctx, const cip_invert_args* a, DevInputs* d, Vi
   const int64_t ws = a->wgt_row_stride ? a->wgt_row_stride : nchan;
   d->nrow = nrow;
   d->nchan = nchan;
+  d->w_lo = a->w_hi > 0 ? a->w_lo : 0.0;
+  d->w_hi = a->w_hi > 0 ? a->w_hi : 0.0;
   if (ms_h2d) *ms_h2d = 0.0;
   const bool reuse = reuse_small && ctx->staged_valid && a->memspace == 0 && ctx->staged_key[0] == a->uvw &&
                      ctx->staged_key[1] == a->freq && ctx->staged_key[2] == a->wgt && ctx->staged_key[3] == a->mask &&

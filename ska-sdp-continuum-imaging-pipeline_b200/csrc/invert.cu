@@ -65,6 +65,18 @@ extern "C" cip_status cip_scan(cip_ctx* ctx, const cip_invert_args* args, cip_sc
   return CIP_OK;
 }
 
+extern "C" cip_status cip_w_histogram(cip_ctx* ctx, const cip_invert_args* args, double wmin, double wmax, int nbins,
+                                      int64_t* counts_out) {
+  CIP_REQUIRE(ctx && counts_out, "NULL argument");
+  CIP_TRY(validate_args(args));
+  CIP_ENTER_DEVICE(ctx);
+  DevInputs in;
+  CIP_TRY(stage_inputs(ctx, args, &in, nullptr, true, nullptr));  // weights and uvw only, as for the scan
+  CIP_TRY(run_w_histogram(ctx, in, wmin, wmax, nbins, counts_out));
+  ctx->staged_valid = args->memspace == 0;
+  return CIP_OK;
+}
+
 // Rows [r0, r1) of the staged inputs as inputs of their own.
 static DevInputs row_slice(const DevInputs& in, int64_t r0, int64_t r1) {
   DevInputs c = in;

@@ -7,6 +7,7 @@
 #include <algorithm>
 #include <cstdlib>
 #include <cstring>
+#include <vector>
 
 #include "geom.cuh"
 
@@ -21,8 +22,9 @@ struct ScanOut {
 struct ScanAcc {
   double lo = 1e300, hi = 0.0, sw = 0.0;
   unsigned long long na = 0;
+  double w_lo = 0.0, w_hi = 0.0;
   __device__ __forceinline__ void add(float w, bool masked, double aw) {
-    if (masked) w = 0.0f;
+    if (masked || (w_hi > 0.0 && !(aw >= w_lo && aw < w_hi))) w = 0.0f;
     sw += (double)w;
     if (w != 0.0f) {
       lo = fmin(lo, aw);
@@ -62,6 +64,8 @@ __global__ void __launch_bounds__(256) scan_kernel(DevInputs in, int do_wstackin
   const int64_t nchan = in.nchan;
   const int64_t total = in.nrow * nchan;
   ScanAcc acc;
+  acc.w_lo = in.w_lo;
+  acc.w_hi = in.w_hi;
   for (int64_t k = (int64_t)blockIdx.x * blockDim.x + threadIdx.x; k < total; k += (int64_t)gridDim.x * blockDim.x) {
     int64_t r = k / nchan, c = k - r * nchan;
     float w = in.wgt ? in.wgt[r * in.wstride + c] : 1.0f;
@@ -84,6 +88,8 @@ __global__ void __launch_bounds__(256) scan_kernel_v4(DevInputs in, int do_wstac
   const Index nq = (Index)(in.nchan >> 2);
   const Index total = (Index)(in.nrow * (int64_t)nq);
   ScanAcc acc;
+  acc.w_lo = in.w_lo;
+  acc.w_hi = in.w_hi;
   for (Index k = (Index)blockIdx.x * blockDim.x + threadIdx.x; k < total; k += (Index)gridDim.x * blockDim.x) {
     const Index r = k / nq;
     const int c = (int)(k - r * nq) << 2;
@@ -118,6 +124,51 @@ static double bits_to_double(unsigned long long b) {
   double d;
   memcpy(&d, &b, sizeof(d));
   return d;
+}
+
+// |w| histogram of the active samples (the slab filter of the inputs, if any, applies too).
+constexpr int kMaxWBins = 4096;
+__global__ void __launch_bounds__(256) whist_kernel(DevInputs in, double wmin, double scale, int nbins, unsigned long long* __restrict__ counts) {
+  __shared__ uint32_t s_cnt[kMaxWBins];
+  for (int b = threadIdx.x; b < nbins; b += blockDim.x) s_cnt[b] = 0;
+  __syncthreads();
+  const int64_t nchan = in.nchan, total = in.nrow * nchan;
+  for (int64_t k = (int64_t)blockIdx.x * blockDim.x + threadIdx.x; k < total; k += (int64_t)gridDim.x * blockDim.x) {
+    const int64_t r = k / nchan, c = k - r * nchan;
+    float w = in.wgt ? in.wgt[r * in.wstride + c] : 1.0f;
+    if (in.mask && in.mask[r * in.wstride + c] == 0) w = 0.0f;
+    if (w == 0.0f) continue;
+    const double aw = fabs(in.uvw[3 * r + 2]) * (in.freq[c] / kSpeedOfLight);
+    if (in.w_hi > 0.0 && !(aw >= in.w_lo && aw < in.w_hi)) continue;
+    int b = (int)((aw - wmin) * scale);
+    b = b < 0 ? 0 : (b >= nbins ? nbins - 1 : b);
+    atomicAdd(&s_cnt[b], 1u);
+  }
+  __syncthreads();
+  for (int b = threadIdx.x; b < nbins; b += blockDim.x)
+    if (s_cnt[b]) atomicAdd(&counts[b], (unsigned long long)s_cnt[b]);
+}
+
+cip_status run_w_histogram(cip_ctx* ctx, const DevInputs& in, double wmin, double wmax, int nbins, int64_t* counts_out) {
+  CIP_REQUIRE(nbins >= 1 && nbins <= kMaxWBins, "nbins must be in [1, %d]", kMaxWBins);
+  CIP_REQUIRE(wmax >= wmin, "bad |w| range");
+  CIP_TRY(ctx->scan_out.ensure(sizeof(unsigned long long) * kMaxWBins));
+  cudaStream_t st = ctx->stream;
+  unsigned long long* d = ctx->scan_out.as<unsigned long long>();
+  CIP_CHECK_CUDA(cudaMemsetAsync(d, 0, sizeof(unsigned long long) * nbins, st));
+  const int64_t total = in.nrow * in.nchan;
+  if (total > 0) {
+    const double scale = wmax > wmin ? nbins / (wmax - wmin) : 0.0;
+    const int blocks = (int)std::min<int64_t>((total + 255) / 256, (int64_t)ctx->sm_count * 8);
+    whist_kernel<<<blocks, 256, 0, st>>>(in, wmin, scale, nbins, d);
+    ctx->launches++;
+    CIP_CHECK_CUDA(cudaGetLastError());
+  }
+  std::vector<unsigned long long> h(nbins);
+  CIP_CHECK_CUDA(cudaMemcpyAsync(h.data(), d, sizeof(unsigned long long) * nbins, cudaMemcpyDeviceToHost, st));
+  CIP_CHECK_CUDA(cudaStreamSynchronize(st));
+  for (int b = 0; b < nbins; ++b) counts_out[b] += (int64_t)h[b];
+  return CIP_OK;
 }
 
 cip_status run_scan(cip_ctx* ctx, const DevInputs& in, int do_wstacking, cip_scan_result* out) {

@@ -29,7 +29,7 @@ class InvertArgs(C.Structure):
                 ("vis_row_stride", C.c_int64), ("wgt_row_stride", C.c_int64),
                 ("npix_x", C.c_int), ("npix_y", C.c_int), ("pixsize_x", C.c_double), ("pixsize_y", C.c_double),
                 ("epsilon", C.c_double), ("do_wstacking", C.c_int), ("accumulate_fp64", C.c_int),
-                ("memspace", C.c_int)]
+                ("memspace", C.c_int), ("w_lo", C.c_double), ("w_hi", C.c_double)]
 
 
 class ScanResult(C.Structure):
@@ -90,6 +90,7 @@ def lib():
             L.cip_scan.argtypes = [C.c_void_p, C.POINTER(InvertArgs), C.POINTER(ScanResult)]
             L.cip_grid_accumulate.argtypes = [C.c_void_p, C.POINTER(InvertArgs), C.POINTER(Plan), C.c_void_p,
                                               C.POINTER(Report)]
+            L.cip_w_histogram.argtypes = [C.c_void_p, C.POINTER(InvertArgs), C.c_double, C.c_double, C.c_int, C.c_void_p]
             L.cip_bin_inspect.argtypes = [C.c_void_p, C.POINTER(InvertArgs), C.POINTER(Plan), C.POINTER(C.c_int64),
                                           C.POINTER(C.c_int64), C.POINTER(C.c_int), C.c_void_p, C.c_void_p]
             L.cip_correct_image.argtypes = [C.c_void_p, C.POINTER(Plan), C.c_void_p, C.c_int, C.c_int, C.c_double]
@@ -109,7 +110,7 @@ def lib():
 
 
 EXPORTS = ["cip_last_error", "cip_version", "cip_ctx_create", "cip_ctx_destroy", "cip_ctx_stream",
-           "cip_ctx_synchronize", "cip_ctx_launches", "cip_ctx_device", "cip_current_device", "cip_plan_make", "cip_kernel_table", "cip_kernel_ft", "cip_scan",
+           "cip_ctx_synchronize", "cip_ctx_launches", "cip_ctx_device", "cip_current_device", "cip_plan_make", "cip_kernel_table", "cip_kernel_ft", "cip_scan", "cip_w_histogram",
            "cip_grid_accumulate", "cip_bin_inspect", "cip_correct_image", "cip_invert", "cip_stokes_i", "cip_tile_bin",
            "cip_tile_fetch", "cip_tile_gather", "cip_tile_free"]
 

@@ -249,6 +249,192 @@ def accumulate_shards(shards: Sequence[StokesIGridderInput], num_pixels: int, pi
     return image, plan, sumw
 
 
+# ---- the same, sharded by |w| (SURVEY.md 8e option 3; BASELINE.json configs[4]) --------------------------------
+
+W_HIST_BINS = 4096
+
+
+def w_slab_edges(counts, wmin: float, wmax: float, nslabs: int, *, plane_cost: float = 0.0, dw: float = 0.0
+                 ) -> list[float]:
+    """Cut the |w| axis into ``nslabs`` slabs of (nearly) equal COST from a histogram of ``len(counts)`` equal bins
+    over [wmin, wmax]: a bin costs its samples plus ``plane_cost`` sample-equivalents per w plane it spans (bin
+    width / dw) -- with plane_cost = 0 the slabs hold equal numbers of samples, with a large one equal numbers of
+    planes (what matters when the per-plane FFTs dominate).  Returns nslabs + 1 edges, the first 0 and the last
+    +inf, so that every sample falls into exactly one slab [edges[s], edges[s + 1])."""
+    cost = np.asarray(counts, dtype=np.float64).copy()
+    if plane_cost > 0 and dw > 0 and wmax > wmin:
+        cost += plane_cost * (wmax - wmin) / len(cost) / dw
+    cum = np.concatenate([[0.0], np.cumsum(cost)])
+    total = cum[-1]
+    edges = [0.0]
+    for s in range(1, nslabs):
+        # bin boundary at which the cumulative cost first reaches s / nslabs of the total
+        b = int(np.searchsorted(cum, total * s / nslabs, side="left"))
+        b = min(max(b, 1), len(cost))
+        edges.append(max(wmin + (wmax - wmin) * b / len(cost), edges[-1]))
+    edges.append(float("inf"))
+    return edges
+
+
+# sample-equivalents of one w plane per grid cell (FFT + w-screen ~ 12 ps per cell, binning + gridding ~ 65 ps per
+# sample on a B200: profiles/r2*_bench.json), for the cost model of the slabs
+PLANE_COST_PER_CELL = 0.2
+
+
+def _shard_args(sh: StokesIGridderInput, num_pixels, pixel_size_lm, epsilon, accumulate_fp64, w_slab=None):
+    effw = sh.effective_weights()
+    a = make_args(sh.uvw, sh.channel_frequencies, sh.visibilities, effw, None, num_pixels, num_pixels, pixel_size_lm,
+                  pixel_size_lm, epsilon, True, accumulate_fp64, 0 if isinstance(sh.visibilities, np.ndarray) else 1,
+                  w_slab=w_slab)
+    return a, effw
+
+
+def _exchange_rows_by_slab(shards, edges, *, group, device):
+    """All-to-all of visibility rows over the process group: rank s receives, from every rank, the rows of every
+    shard whose |w| range (|w_metres| x the shard's lowest .. highest frequency / c) touches slab s.  A row that
+    straddles a slab edge goes to both neighbours; the exact sample-level split happens in the library (w_lo, w_hi).
+    Returns the received shards (one per sending rank and shard of that rank)."""
+    torch = _torch()
+    dist = torch.distributed
+    world, rank = dist.get_world_size(group), dist.get_rank(group)
+    c = 299792458.0
+    meta = [None] * world  # every rank's list of channel-frequency arrays
+    dist.all_gather_object(meta, [np.asarray(sh.channel_frequencies.cpu() if hasattr(sh.channel_frequencies, "cpu")
+                                             else sh.channel_frequencies, dtype=np.float64) for sh in shards], group=group)
+    received = []
+    for k in range(max(len(m) for m in meta)):
+        sh = shards[k] if k < len(shards) else None
+        send_rows = []
+        if sh is not None:
+            aw = sh.uvw[:, 2].abs()
+            f = meta[rank][k]
+            lo, hi = aw * (float(f.min()) / c), aw * (float(f.max()) / c)
+            for s in range(world):
+                send_rows.append(torch.nonzero((hi >= edges[s]) & (lo < edges[s + 1])).reshape(-1))
+        else:
+            send_rows = [torch.zeros(0, dtype=torch.int64, device=device) for _ in range(world)]
+        nsend = torch.tensor([len(r) for r in send_rows], dtype=torch.int64, device=device)
+        nrecv = torch.empty_like(nsend)
+        dist.all_to_all_single(nrecv, nsend, group=group)
+        nsend_l, nrecv_l = nsend.tolist(), nrecv.tolist()
+        order = torch.cat(send_rows) if sh is not None else torch.zeros(0, dtype=torch.int64, device=device)
+        nchan_of = [len(meta[r][k]) if k < len(meta[r]) else 0 for r in range(world)]
+
+        def swap(rows_tensor, width_of, dtype):
+            """rows_tensor: (sum nsend, width(rank)) of dtype; receives (sum over r of nrecv[r] * width_of[r],)."""
+            send = rows_tensor.reshape(-1).contiguous()
+            w_mine = width_of[rank]
+            out = torch.empty(sum(n * width_of[r] for r, n in enumerate(nrecv_l)), dtype=dtype, device=device)
+            dist.all_to_all_single(out, send, [n * width_of[r] for r, n in enumerate(nrecv_l)],
+                                   [n * w_mine for n in nsend_l], group=group)
+            return out
+
+        if sh is not None:
+            uvw_s = sh.uvw.index_select(0, order)
+            vis_s = torch.view_as_real(sh.visibilities.index_select(0, order))
+            wgt_s = sh.effective_weights().index_select(0, order)
+        else:
+            uvw_s = torch.zeros((0, 3), dtype=torch.float64, device=device)
+            vis_s = torch.zeros((0, 0, 2), dtype=torch.float32, device=device)
+            wgt_s = torch.zeros((0, 0), dtype=torch.float32, device=device)
+        uvw_r = swap(uvw_s, [3] * world, torch.float64)
+        vis_r = swap(vis_s, [2 * n for n in nchan_of], torch.float32)
+        wgt_r = swap(wgt_s, nchan_of, torch.float32)
+        o3 = ov = ow = 0
+        for r in range(world):
+            n, nch = nrecv_l[r], nchan_of[r]
+            if n and nch:
+                freq = torch.from_numpy(meta[r][k]).to(device)
+                received.append(StokesIGridderInput(
+                    freq, None, uvw_r[o3:o3 + 3 * n].reshape(n, 3),
+                    torch.view_as_complex(vis_r[ov:ov + 2 * n * nch].reshape(n, nch, 2)),
+                    wgt_r[ow:ow + n * nch].reshape(n, nch)))
+            o3 += 3 * n
+            ov += 2 * n * nch
+            ow += n * nch
+    return received
+
+
+def accumulate_shards_by_w(shards: Sequence[StokesIGridderInput], num_pixels: int, pixel_size_lm: float, *,
+                           epsilon: float = EPSILON, accumulate_fp64: bool = False, group=None,
+                           device: Optional[int] = None, nslabs: Optional[int] = None, reports: Optional[list] = None):
+    """Grid this rank's share of a |w|-sharded invert into one uncorrected partial image.
+
+    The ranks agree on the global |w| range and on (sigma, W, dw, nshift) as in ``accumulate_shards``, sum their |w|
+    histograms and cut the axis into one slab of equal population per rank; the visibility rows are exchanged so that
+    rank s holds what touches slab s (NCCL all-to-all -- the one exchange step of this sharding), and every rank
+    grids its slab with a plan of ITS w range: about nplanes / world + W planes and FFTs instead of nplanes.  A single
+    process (no group) walks ``nslabs`` slabs one after the other, which bounds the resident plane stack the same way.
+    Returns (image CUDA tensor, Plan of the last slab gridded here, global sum of weights); the partial images of
+    the ranks add up as in ``accumulate_shards`` and take the same ``reduce_and_correct``."""
+    torch = _torch()
+    dev = _device(device)
+    ctx = Context.get(dev.index)
+    L = lib()
+    world = torch.distributed.get_world_size(group) if _dist_ready() else 1
+    rank = torch.distributed.get_rank(group) if _dist_ready() else 0
+    nslabs = world if world > 1 else max(int(nslabs or 1), 1)
+    to_dev = lambda a, dt: a if not isinstance(a, np.ndarray) else torch.from_numpy(np.ascontiguousarray(a, dtype=dt)).to(dev)
+    shards = [StokesIGridderInput(to_dev(sh.channel_frequencies, np.float64), None, to_dev(sh.uvw, np.float64),
+                                  to_dev(sh.visibilities, np.complex64), to_dev(sh.effective_weights(), np.float32))
+              for sh in shards]
+    torch.cuda.current_stream(dev).synchronize()
+
+    def scan_all(items, w_slab=None):
+        wmin, wmax, nactive, sumw, keep = np.inf, 0.0, 0, 0.0, []
+        for sh in items:
+            a, effw = _shard_args(sh, num_pixels, pixel_size_lm, epsilon, accumulate_fp64, w_slab)
+            scan = ScanResult()
+            with ctx.lock:
+                check(L.cip_scan(ctx.handle, C.byref(a), C.byref(scan)))
+            keep.append((a, sh, effw))
+            if scan.nactive:
+                wmin, wmax = min(wmin, scan.wmin), max(wmax, scan.wmax)
+            nactive += scan.nactive
+            sumw += scan.sum_wgt
+        return wmin, wmax, nactive, sumw, keep
+
+    wmin, wmax, nactive, sumw, keep = scan_all(shards)
+    wmin, wmax, nactive, sumw = agree_on_shard_statistics(wmin, wmax, nactive, sumw, group=group, device=dev)
+    image = torch.zeros((num_pixels, num_pixels), dtype=torch.float64 if accumulate_fp64 else torch.float32, device=dev)
+    if nactive == 0:
+        plan = _cabi.plan_make(num_pixels, num_pixels, pixel_size_lm, pixel_size_lm, epsilon, 0.0, 0.0, 0,
+                               do_wstacking=True, fp64=accumulate_fp64)
+        return image, plan, sumw
+    common = _cabi.plan_make(num_pixels, num_pixels, pixel_size_lm, pixel_size_lm, epsilon, wmin, wmax, nactive,
+                             do_wstacking=True, fp64=accumulate_fp64, sigma=float(os.environ.get("CIP_SIGMA", 0) or 0),
+                             support=int(os.environ.get("CIP_SUPPORT", 0) or 0))
+    counts = np.zeros(W_HIST_BINS, dtype=np.int64)
+    for a, _sh, _w in keep:
+        with ctx.lock:
+            check(L.cip_w_histogram(ctx.handle, C.byref(a), wmin, wmax, W_HIST_BINS, counts.ctypes.data))
+    if world > 1:
+        t = torch.from_numpy(counts).to(dev)
+        torch.distributed.all_reduce(t, group=group)
+        counts = t.cpu().numpy()
+    edges = w_slab_edges(counts, wmin, wmax, nslabs, plane_cost=PLANE_COST_PER_CELL * common.nu * common.nv, dw=common.dw)
+    mine = shards
+    if world > 1:
+        mine = _exchange_rows_by_slab(shards, edges, group=group, device=dev)
+        torch.cuda.current_stream(dev).synchronize()
+    plan = common
+    for s in ([rank] if world > 1 else range(nslabs)):
+        slab = (edges[s], min(edges[s + 1], 1e300))
+        smin, smax, sact, _ssum, skeep = scan_all(mine, slab)
+        if sact == 0:
+            continue
+        plan = _cabi.plan_make(num_pixels, num_pixels, pixel_size_lm, pixel_size_lm, epsilon, smin, smax, sact,
+                               do_wstacking=True, fp64=accumulate_fp64, sigma=common.sigma, support=common.support)
+        assert (plan.nu, plan.nv, plan.dw, plan.nshift) == (common.nu, common.nv, common.dw, common.nshift)
+        for a, _sh, _w in skeep:
+            rep = Report()
+            with ctx.lock:
+                check(L.cip_grid_accumulate(ctx.handle, C.byref(a), C.byref(plan), image.data_ptr(), C.byref(rep)))
+            if reports is not None:
+                reports.append(dict(rep.as_dict(), nplanes=plan.nplanes, slab=s))
+    return image, plan, sumw
+
+
 def _dist_ready() -> bool:
     torch = _torch()
     return torch.distributed.is_available() and torch.distributed.is_initialized()

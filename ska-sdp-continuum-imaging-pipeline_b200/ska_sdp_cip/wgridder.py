@@ -57,7 +57,7 @@ def _host_result(shape, dtype):
 
 
 def make_args(uvw, freq, ms, wgt, mask, npix_x, npix_y, pixsize_x, pixsize_y, epsilon, do_wstacking, fp64,
-              memspace) -> InvertArgs:
+              memspace, w_slab=None) -> InvertArgs:
     a = InvertArgs()
     a.uvw = _cabi._ptr(uvw)
     a.nrow = int(uvw.shape[0])
@@ -74,6 +74,7 @@ def make_args(uvw, freq, ms, wgt, mask, npix_x, npix_y, pixsize_x, pixsize_y, ep
     a.do_wstacking = int(bool(do_wstacking))
     a.accumulate_fp64 = int(bool(fp64))
     a.memspace = memspace
+    a.w_lo, a.w_hi = (float(w_slab[0]), float(w_slab[1])) if w_slab else (0.0, 0.0)
     return a
 
 

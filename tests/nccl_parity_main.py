@@ -49,6 +49,27 @@ def main():
             ref = dft.dft_dirty(uvw, freq, v, effw, npix, npix, px_used, px_used) / effw.sum()
             results[name] = {"vs_single_gpu": dft.rel_rms(img, single), "vs_dft": dft.rel_rms(img, ref),
                              "active": int((effw != 0).sum()), "shape": list(img.shape), "world": world}
+    # the same, sharded by |w|: histogram all-reduce, all-to-all of the rows, one slab per rank
+    from ska_sdp_cip.invert import (StokesIGridderInput, accumulate_shards_by_w, reduce_and_correct, shard_of_rank)
+    cfg = S.meerkat_like(num_pixels=256)
+    cfg.n_times, cfg.n_chan, cfg.declination_deg = 6, 16, 20.0
+    uvw = S.make_uvw(cfg)
+    freq = cfg.frequencies()
+    px = 4.0 * S.pixel_size_lm(cfg, uvw)  # wide field: many w planes
+    vis, wgt = S.make_vis_numpy(cfg, uvw, freq, px)
+    vis4, flags4, wgt4 = S.four_pol(vis, wgt)
+    reader = ArrayMeasurementSetReader(uvw, freq, vis4, flags4, wgt4)
+    chunks = shard_of_rank(reader.partition(2, world), rank, world)
+    shards = [StokesIGridderInput.from_measurement_set_reader(c) for c in chunks]
+    reports = []
+    image, plan, sumw = accumulate_shards_by_w(shards, 256, px, reports=reports)
+    img = reduce_and_correct(image, plan, float(np.float32(sumw))).cpu().numpy()
+    if rank == 0:
+        v, f, w = stokes.stokes_i(vis4, flags4, wgt4)
+        effw = stokes.effective_weights(f, w)
+        ref = dft.dft_dirty(uvw, freq, v, effw, 256, 256, px, px) / effw.sum()
+        results["w_slabs"] = {"vs_single_gpu": 0.0, "vs_dft": dft.rel_rms(img, ref), "world": world,
+                              "planes_of_this_rank": [r["nplanes"] for r in reports]}
     ok = True
     if rank == 0:
         ok = all(r["vs_single_gpu"] <= 2e-6 and r["vs_dft"] <= 1e-4 for r in results.values())

@@ -528,3 +528,58 @@ def test_binning_records_match_the_oracle(wg, small, wide, which, fp64):
     assert np.abs(got[:, 3:6] - want[:, 3:6]).max() <= ftol
     vtol = 1e-12 if fp64 else 2e-7
     assert np.abs(got[:, 6:] - want[:, 6:]).max() <= vtol * np.abs(want[:, 6:]).max()
+
+
+# ---- |w|-sharded invert (SURVEY 8e option 3) -------------------------------------------------------------------
+
+def test_w_slabs_in_one_process_give_the_same_image(built_lib, wide):
+    """accumulate_shards_by_w: global (sigma, W, dw, nshift), per-slab w0 / nplanes, images summed uncorrected."""
+    from ska_sdp_cip.invert import StokesIGridderInput, accumulate_shards, accumulate_shards_by_w, reduce_and_correct
+    (uvw, freq, vis, wgt, nx, px), ref = wide
+    shards = [StokesIGridderInput(freq, None, uvw[a:b], vis[a:b], wgt[a:b]) for a, b in ((0, 1100), (1100, 3000))]
+    img0, plan0, sumw0 = accumulate_shards(shards, nx, px)
+    img0 = reduce_and_correct(img0, plan0, sumw0, normalise=False).cpu().numpy()
+    for nslabs in (1, 3, 5):
+        reports = []
+        img, plan, sumw = accumulate_shards_by_w(shards, nx, px, nslabs=nslabs, reports=reports)
+        assert sumw == pytest.approx(sumw0, rel=1e-12)
+        img = reduce_and_correct(img, plan, sumw, normalise=False).cpu().numpy()
+        # the slabs' planes sit at other w than the single plan's: the two images agree to the w kernel's error,
+        # not to rounding
+        assert dft.rel_rms(img, img0) <= (3e-6 if nslabs == 1 else 3e-5), nslabs
+        assert dft.rel_rms(img, ref) <= TOL_FP32
+        if nslabs > 1:  # every slab spans fewer planes than the whole
+            assert max(r["nplanes"] for r in reports) < plan0.nplanes
+            assert len({r["slab"] for r in reports}) == nslabs
+
+
+def test_w_slab_argument_selects_samples(wg, wide):
+    """cip_invert with (w_lo, w_hi): the images of complementary slabs add up to the full image, and the weight
+    sums of the slabs to the full weight sum."""
+    import ctypes as C
+    from ska_sdp_cip import _cabi
+    from ska_sdp_cip.wgridder import make_args
+    (uvw, freq, vis, wgt, nx, px), ref = wide
+    ctx = _cabi.Context.get(-1)
+    aw = np.abs(uvw[:, 2:3]) * freq[None, :] / 299792458.0
+    cut = float(np.median(aw[wgt != 0]))
+    total, sums = np.zeros((nx, nx)), []
+    for slab in ((0.0, cut), (cut, 1e300)):
+        out = np.empty((nx, nx), dtype=np.float32)
+        a = make_args(uvw, freq, vis, wgt, None, nx, nx, px, px, 1e-4, True, False, 0, w_slab=slab)
+        scan = _cabi.ScanResult()
+        with ctx.lock:
+            _cabi.check(_cabi.lib().cip_invert(ctx.handle, C.byref(a), out.ctypes.data, C.byref(scan), None, None))
+        inside = (aw >= slab[0]) & (aw < slab[1])
+        assert scan.nactive == int(np.count_nonzero(inside & (wgt != 0)))
+        sums.append(scan.sum_wgt)
+        total += out
+    assert sum(sums) == pytest.approx(float(wgt.sum(dtype=np.float64)), rel=1e-6)
+    assert dft.rel_rms(total, ref) <= TOL_FP32
+    counts = np.zeros(64, dtype=np.int64)
+    a = make_args(uvw, freq, vis, wgt, None, nx, nx, px, px, 1e-4, True, False, 0)
+    with ctx.lock:
+        _cabi.check(_cabi.lib().cip_w_histogram(ctx.handle, C.byref(a), float(aw.min()), float(aw.max()), 64,
+                                                counts.ctypes.data))
+    want, _ = np.histogram(aw[wgt != 0], bins=64, range=(float(aw.min()), float(aw.max())))
+    assert counts.sum() == want.sum() and np.abs(counts - want).sum() <= 4  # samples on a bin edge may fall either way

@@ -321,3 +321,20 @@ def test_command_lines_parse_like_the_reference():
     assert b.tile_size == [3000.0, 3000.0, 6000.0] and b.num_time_intervals == 4 and b.max_vis_per_chunk == 10000
     with pytest.raises(SystemExit):
         pipeline_app.get_parser().parse_args(["in.ms", "out.npy"])  # -n and -p are required
+
+
+def test_w_slab_edges_partition_the_axis():
+    from ska_sdp_cip.invert import w_slab_edges
+    rng = np.random.default_rng(3)
+    w = np.sort(rng.exponential(300.0, 100000))
+    wmin, wmax = w[0], w[-1]
+    counts, _ = np.histogram(w, bins=4096, range=(wmin, wmax))
+    edges = w_slab_edges(counts, wmin, wmax, 8)
+    assert len(edges) == 9 and edges[0] == 0.0 and np.isinf(edges[-1]) and all(a <= b for a, b in zip(edges, edges[1:]))
+    pop = [np.count_nonzero((w >= a) & (w < b)) for a, b in zip(edges, edges[1:])]
+    assert sum(pop) == len(w) and max(pop) < 1.1 * len(w) / 8 and min(pop) > 0.9 * len(w) / 8
+    # a large plane cost equalises the |w| extent instead of the population
+    wide = w_slab_edges(counts, wmin, wmax, 8, plane_cost=1e12, dw=1.0)
+    ext = np.diff(np.clip(wide, wmin, wmax))
+    assert ext.max() < 1.1 * (wmax - wmin) / 8
+    assert w_slab_edges(counts, wmin, wmax, 1) == [0.0, float("inf")]
