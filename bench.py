@@ -228,7 +228,7 @@ def run_b200(args):
     import torch
     import torch.distributed as dist
     from ska_sdp_cip import _cabi, synthetic as S, wgridder
-    from ska_sdp_cip.invert import StokesIGridderInput, accumulate_shards, reduce_and_correct
+    from ska_sdp_cip.invert import StokesIGridderInput, accumulate_shards, accumulate_shards_by_w, reduce_and_correct
 
     world = int(os.environ.get("WORLD_SIZE", "1"))
     rank = int(os.environ.get("RANK", "0"))
@@ -263,7 +263,8 @@ def run_b200(args):
             return img, info["plan"]
         shard = StokesIGridderInput(d_freq, None, d_uvw, d_vis, d_wgt)
         reps = []
-        img, plan, sumw = accumulate_shards([shard], N, px, epsilon=cfg.epsilon, reports=reps)
+        acc = accumulate_shards_by_w if args.sharding == "w" else accumulate_shards
+        img, plan, sumw = acc([shard], N, px, epsilon=cfg.epsilon, reports=reps)
         reports.extend(reps)
         img = reduce_and_correct(img, plan, sumw, normalise=False)
         return img, plan.as_dict()
@@ -352,7 +353,8 @@ def run_b200(args):
             host_reports.append(info["report"])
             return img
         shard = StokesIGridderInput(freq_p, None, uvw_p, n_vis_np, n_wgt_np)
-        img, plan_, sumw = accumulate_shards([shard], N, px, epsilon=cfg.epsilon)
+        acc = accumulate_shards_by_w if args.sharding == "w" else accumulate_shards
+        img, plan_, sumw = acc([shard], N, px, epsilon=cfg.epsilon)
         return reduce_and_correct(img, plan_, sumw, normalise=False).cpu().numpy()
 
     e2e_steps = max(1, min(args.steps, 3))
@@ -377,8 +379,13 @@ def run_b200(args):
     # plane stack written once (DESIGN.md "kernel 2")
     alg_bytes = nvis * 12 + uvw.shape[0] * 24 + freq.shape[0] * 8 + plan["nplanes"] * plan["nu"] * plan["nv"] * 8
     achieved = alg_bytes / (ms_grid * 1e-3) / 1e9
-    stage = {k: float(np.mean([r[k] for r in timed_reports])) for k in
+    stage = {k: float(np.sum([r[k] for r in timed_reports]) / args.steps) for k in
              ("ms_scan", "ms_bin", "ms_zero", "ms_grid", "ms_fft", "ms_wscreen", "ms_correct", "ms_total")}
+    phase_keys = sorted({k for r in timed_reports for k in r.get("phases_ms", {})})
+    if phase_keys:
+        stage["w_sharding_phases_ms"] = {k: float(np.sum([r["phases_ms"].get(k, 0.0) for r in timed_reports
+                                                           if "phases_ms" in r]) / args.steps) for k in phase_keys}
+        stage["nplanes_of_rank0"] = [r["nplanes"] for r in timed_reports if "nplanes" in r][:4]
     # ---- CPU baseline on a bounded sample -----------------------------------------------------
     cpu = None
     if not args.no_cpu and world == 1:  # rank 0 at N = 1 only
@@ -395,7 +402,10 @@ def run_b200(args):
                    "nplanes": plan["nplanes"], "l2": "256 MB buffer written between iterations; inputs 2 GB >> L2",
                    "sharding": ("single GPU" if world == 1 else
                                 ("frequency chunks of the reference's partition(1, N)" if wname == "cfg3" else
-                                 "time ranges per rank") + ", NCCL reduce-scatter + all-gather of the dirty image")},
+                                 "time ranges per rank")
+                                + (", rows exchanged by |w| slab (NCCL all-to-all), one slab per rank" if args.sharding == "w"
+                                   else "")
+                                + ", NCCL reduce-scatter + all-gather of the dirty image")},
         "parity": parity,
         "e2e": {"value": total_vis * e2e_steps / ms_e2e / 1e3, "unit": UNIT, "h2d_bytes_per_step": h2d,
                 "d2h_bytes_per_step": d2h, "steps": e2e_steps,
@@ -431,6 +441,9 @@ def main():
     ap.add_argument("--workload", default=None, choices=["cfg1", "cfg3"],
                     help="cfg1 = BASELINE.json configs[1] per GPU (default at N = 1), cfg3 = configs[3] sharded by "
                          "frequency chunk (default at N > 1)")
+    ap.add_argument("--sharding", default="freq", choices=["freq", "w"],
+                    help="N > 1: grid the rank's own frequency chunk (freq), or exchange the rows by |w| slab first so "
+                         "that every rank transforms only the planes of its slab (w)")
     ap.add_argument("--no-cpu", action="store_true", help="skip the CPU baseline leg")
     ap.add_argument("--no-parity", action="store_true", help="skip the sampled-pixel DFT check of the timed path")
     ap.add_argument("--verbose", action="store_true", help="per-step host timings on stderr")

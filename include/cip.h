@@ -160,6 +160,12 @@ typedef struct {
 cip_status cip_bin_inspect(cip_ctx* ctx, const cip_invert_args* args, const cip_plan* plan, int64_t* njobs,
                            int64_t* ngroups, int* rec_bytes, cip_job* jobs_out, void* recs_out);
 
+/* The same for several device-resident shards (memspace 1; e.g. the chunks of the reference's partition that one
+ * GPU owns, or what a |w| slab received from the other ranks): all shards are gridded into ONE plane stack, which
+ * is transformed once -- instead of one set of per-plane FFTs per shard. */
+cip_status cip_grid_accumulate_many(cip_ctx* ctx, const cip_invert_args* args, int nshards, cip_plan* plan,
+                                    void* image_dev, cip_report* report /* may be NULL */);
+
 /* G4 final + P4: image[r,:] *= scale / (c_u c_v c_w n) for rows row_begin..row_end-1.
  * `image_dev` points at row 0 of the full image. */
 cip_status cip_correct_image(cip_ctx* ctx, const cip_plan* plan, void* image_dev, int row_begin, int row_end,

@@ -90,11 +90,13 @@ static DevInputs row_slice(const DevInputs& in, int64_t r0, int64_t r1) {
 
 // One attempt: everything is enqueued without a single read-back; `rep` stage times come from event pairs (device
 // inputs) or the host clock around event synchronisations (streamed host inputs, see StageTimer).
-static cip_status grid_accumulate_attempt(cip_ctx* ctx, const DevInputs& in, const VisFeed& feed, cip_plan* plan,
+static cip_status grid_accumulate_attempt(cip_ctx* ctx, const DevInputs* ins, const VisFeed* feeds, int nshards, cip_plan* plan,
                                           void* image_dev, cip_report* rep) {
   const int fp64 = plan->accumulate_fp64;
   GridGeom g = make_geom(*plan);
   const bool want_items = !fp64 && g.W <= kFastSupport && !use_tc_gridder();
+  const DevInputs& in = ins[0];
+  const VisFeed& feed = feeds[0];
   StageTimer tm(ctx, rep != nullptr, feed.nchunks > 0 && feed.ready[0] != nullptr);
   double dummy = 0;
 
@@ -109,7 +111,8 @@ static cip_status grid_accumulate_attempt(cip_ctx* ctx, const DevInputs& in, con
     CIP_CHECK_CUDA(cudaMemGetInfo(&free_b, &total_b));
     // keep room for the binning workspaces (records 16 .. 32 B per visibility, padded) if they are not allocated yet
     size_t reserve = (size_t)768 << 20;
-    const size_t nvis = (size_t)in.nrow * in.nchan;
+    size_t nvis = 0;
+    for (int k = 0; k < nshards; ++k) nvis = std::max(nvis, (size_t)ins[k].nrow * ins[k].nchan);
     if (ctx->work[0].recs.cap < 36 * nvis / std::max(feed.nchunks, 1)) reserve += 40 * nvis;
     size_t avail = free_b + ctx->grid.cap;
     avail = avail > reserve ? avail - reserve : 0;
@@ -147,6 +150,9 @@ static cip_status grid_accumulate_attempt(cip_ctx* ctx, const DevInputs& in, con
     CIP_CHECK_CUDA(cudaStreamWaitEvent(gs, ctx->zero_ev, 0));
     bool used[2] = {false, false};
     int pass = 0, ntimed = 0;
+    for (int k = 0; k < nshards; ++k) {
+    const DevInputs& in = ins[k];
+    const VisFeed& feed = feeds[k];
     for (int c = 0; c < feed.nchunks; ++c) {
       if (feed.row0[c + 1] <= feed.row0[c]) continue;
       if (feed.ready[c]) {
@@ -187,6 +193,7 @@ static cip_status grid_accumulate_attempt(cip_ctx* ctx, const DevInputs& in, con
         trace_mark("  pass gridded");
       }
     }
+    }
     for (int slot = 0; slot < 2; ++slot)
       if (used[slot]) CIP_CHECK_CUDA(cudaStreamWaitEvent(ctx->stream, ctx->gridded_ev[slot], 0));
     if (dev_timing) {
@@ -206,21 +213,32 @@ static cip_status grid_accumulate_attempt(cip_ctx* ctx, const DevInputs& in, con
   }
 
   // Blocks of planes: every block needs all visibilities.
-  CIP_TRY(wait_feed(ctx, feed));
+  for (int k = 0; k < nshards; ++k) CIP_TRY(wait_feed(ctx, feeds[k]));
   if (g.W > kFastSupport) {
-    // Wide supports have a single window: bin once; blocks of resident planes each take a pass over all
-    // records (the kernel skips contributions to planes outside the block).
-    tm.start();
-    CIP_TRY(run_binning(ctx, 0, in, g, fp64, want_items));
-    tm.stop(rep ? &rep->ms_bin : &dummy);
+    // Wide supports have a single window: blocks of resident planes each take a pass over all records (the kernel
+    // skips contributions to planes outside the block); one shard is binned once for all blocks.
+    if (nshards == 1) {
+      tm.start();
+      CIP_TRY(run_binning(ctx, 0, in, g, fp64, want_items));
+      tm.stop(rep ? &rep->ms_bin : &dummy);
+    }
     for (int pb = 0; pb < plan->nplanes; pb += nslots_alloc) {
       const int used = std::min(nslots_alloc, plan->nplanes - pb);
       tm.start();
       CIP_CHECK_CUDA(cudaMemsetAsync(ctx->grid.p, 0, plane_bytes * used, ctx->stream));
       tm.stop(rep ? &rep->ms_zero : &dummy);
+      for (int k = 0; k < nshards; ++k) {
+        if (nshards > 1) {
+          tm.start();
+          CIP_TRY(run_binning(ctx, 0, ins[k], g, fp64, want_items));
+          tm.stop(rep ? &rep->ms_bin : &dummy);
+        }
+        tm.start();
+        CIP_TRY(run_gridder(ctx, 0, ctx->stream, g, fp64, 0, 0, ctx->grid.p, pb, used));
+        tm.stop(rep ? &rep->ms_grid : &dummy);
+      }
       tm.start();
-      CIP_TRY(run_gridder(ctx, 0, ctx->stream, g, fp64, 0, 0, ctx->grid.p, pb, used));
-      tm.stop(rep ? &rep->ms_grid : &dummy);
+      tm.stop(&dummy);
       tm.start();
       CIP_TRY(run_fft_screen(ctx, *plan, ctx->grid.p, pb, used, image_dev, nullptr, nullptr));
       tm.stop(rep ? &rep->ms_fft : &dummy);
@@ -238,14 +256,16 @@ static cip_status grid_accumulate_attempt(cip_ctx* ctx, const DevInputs& in, con
     g.win_begin = wa;
     g.win_end = wl + 1;
     tm.start();
-    CIP_TRY(run_binning(ctx, 0, in, g, fp64, want_items));
-    tm.stop(rep ? &rep->ms_bin : &dummy);
-    tm.start();
     CIP_CHECK_CUDA(cudaMemsetAsync(ctx->grid.p, 0, plane_bytes * used, ctx->stream));
     tm.stop(rep ? &rep->ms_zero : &dummy);
-    tm.start();
-    CIP_TRY(run_gridder(ctx, 0, ctx->stream, g, fp64, wa, wl, ctx->grid.p, pb, used));
-    tm.stop(rep ? &rep->ms_grid : &dummy);
+    for (int k = 0; k < nshards; ++k) {
+      tm.start();
+      CIP_TRY(run_binning(ctx, 0, ins[k], g, fp64, want_items));
+      tm.stop(rep ? &rep->ms_bin : &dummy);
+      tm.start();
+      CIP_TRY(run_gridder(ctx, 0, ctx->stream, g, fp64, wa, wl, ctx->grid.p, pb, used));
+      tm.stop(rep ? &rep->ms_grid : &dummy);
+    }
     tm.start();
     CIP_TRY(run_fft_screen(ctx, *plan, ctx->grid.p, pb, used, image_dev, nullptr, nullptr));
     tm.stop(rep ? &rep->ms_fft : &dummy);
@@ -258,7 +278,7 @@ static cip_status grid_accumulate_attempt(cip_ctx* ctx, const DevInputs& in, con
 // honours (nothing touches the image then); the flag is looked at once here, after the attempt has drained.  A
 // shortfall grows the buffers to the reported demand and repeats the attempt -- the first call of a new problem
 // size at most.
-static cip_status grid_accumulate_staged(cip_ctx* ctx, const DevInputs& in, const VisFeed& feed, cip_plan* plan,
+static cip_status grid_accumulate_staged(cip_ctx* ctx, const DevInputs* ins, const VisFeed* feeds, int nshards, cip_plan* plan,
                                          void* image_dev, cip_report* rep) {
   CIP_REQUIRE(plan->support >= kMinSupport && plan->support <= kMaxSupport, "bad support %d", plan->support);
   CIP_REQUIRE(plan->nu >= plan->npix_x && plan->nv >= plan->npix_y && plan->nu % 2 == 0 && plan->nv % 2 == 0,
@@ -269,7 +289,7 @@ static cip_status grid_accumulate_staged(cip_ctx* ctx, const DevInputs& in, cons
     memset(ctx->flags_host, 0, 64);
     CIP_CHECK_CUDA(cudaMemsetAsync(ctx->call_flags.p, 0, 64, ctx->stream));
     cip_report scratch{};
-    CIP_TRY(grid_accumulate_attempt(ctx, in, feed, plan, image_dev, rep ? &scratch : nullptr));
+    CIP_TRY(grid_accumulate_attempt(ctx, ins, feeds, nshards, plan, image_dev, rep ? &scratch : nullptr));
     CIP_CHECK_CUDA(cudaStreamSynchronize(ctx->stream));
     bool again = false;
     CIP_TRY(binning_overflowed(ctx, &again));
@@ -302,7 +322,27 @@ extern "C" cip_status cip_grid_accumulate(cip_ctx* ctx, const cip_invert_args* a
   VisFeed feed;
   CopyStreamGuard guard(ctx);
   CIP_TRY(stage_inputs(ctx, args, &in, &feed, true, report ? &report->ms_h2d : nullptr));
-  CIP_TRY(grid_accumulate_staged(ctx, in, feed, plan, image_dev, report));
+  CIP_TRY(grid_accumulate_staged(ctx, &in, &feed, 1, plan, image_dev, report));
+  CIP_CHECK_CUDA(cudaStreamSynchronize(ctx->stream));
+  if (report) report->launches += ctx->launches - l0;
+  return CIP_OK;
+}
+
+extern "C" cip_status cip_grid_accumulate_many(cip_ctx* ctx, const cip_invert_args* args, int nshards, cip_plan* plan,
+                                               void* image_dev, cip_report* report) {
+  CIP_REQUIRE(ctx && plan && image_dev && args && nshards >= 1, "NULL argument");
+  CIP_ENTER_DEVICE(ctx);
+  if (report) memset(report, 0, sizeof(*report));
+  const int64_t l0 = ctx->launches;
+  std::vector<DevInputs> ins(nshards);
+  std::vector<VisFeed> feeds(nshards);
+  for (int k = 0; k < nshards; ++k) {
+    CIP_TRY(validate_args(&args[k]));
+    CIP_REQUIRE(args[k].memspace == 1, "cip_grid_accumulate_many takes device-resident shards (memspace 1)");
+    CIP_REQUIRE(plan->npix_x == args[k].npix_x && plan->npix_y == args[k].npix_y, "plan and args disagree on the image size");
+    CIP_TRY(stage_inputs(ctx, &args[k], &ins[k], &feeds[k], false, nullptr));
+  }
+  CIP_TRY(grid_accumulate_staged(ctx, ins.data(), feeds.data(), nshards, plan, image_dev, report));
   CIP_CHECK_CUDA(cudaStreamSynchronize(ctx->stream));
   if (report) report->launches += ctx->launches - l0;
   return CIP_OK;
@@ -391,7 +431,7 @@ extern "C" cip_status cip_invert(cip_ctx* ctx, const cip_invert_args* args, void
                         getenv("CIP_SUPPORT") ? atoi(getenv("CIP_SUPPORT")) : 0, &plan));
   trace_mark("planned");
   if (scan.nactive > 0) {
-    CIP_TRY(grid_accumulate_staged(ctx, in, feed, &plan, image, report));
+    CIP_TRY(grid_accumulate_staged(ctx, &in, &feed, 1, &plan, image, report));
     trace_mark("accumulated");
     tm.start();
     CIP_TRY(run_correct(ctx, plan, image, 0, args->npix_x, 1.0));

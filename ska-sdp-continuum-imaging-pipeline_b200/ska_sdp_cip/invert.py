@@ -240,13 +240,30 @@ def accumulate_shards(shards: Sequence[StokesIGridderInput], num_pixels: int, pi
                         device=dev)
     torch.cuda.current_stream(dev).synchronize()
     if nactive:
-        for a, _sh, _w in args_list:
-            rep = Report()
-            with ctx.lock:
-                check(L.cip_grid_accumulate(ctx.handle, C.byref(a), C.byref(plan), image.data_ptr(), C.byref(rep)))
+        for rep in _grid_shards(ctx, [a for a, _sh, _w in args_list], plan, image):
             if reports is not None:
-                reports.append(rep.as_dict())
+                reports.append(rep)
     return image, plan, sumw
+
+
+def _grid_shards(ctx: Context, args: list, plan: Plan, image) -> list[dict]:
+    """Add the shards' uncorrected dirty images to ``image``.  Device-resident shards go through ONE call
+    (cip_grid_accumulate_many: one plane stack, one set of FFTs for all of them); host shards one by one, each
+    streamed in behind its own binning and gridding."""
+    L = lib()
+    reports = []
+    if len(args) > 1 and all(a.memspace == 1 for a in args):
+        arr = (_cabi.InvertArgs * len(args))(*args)
+        rep = Report()
+        with ctx.lock:
+            check(L.cip_grid_accumulate_many(ctx.handle, arr, len(args), C.byref(plan), image.data_ptr(), C.byref(rep)))
+        return [rep.as_dict()]
+    for a in args:
+        rep = Report()
+        with ctx.lock:
+            check(L.cip_grid_accumulate(ctx.handle, C.byref(a), C.byref(plan), image.data_ptr(), C.byref(rep)))
+        reports.append(rep.as_dict())
+    return reports
 
 
 # ---- the same, sharded by |w| (SURVEY.md 8e option 3; BASELINE.json configs[4]) --------------------------------
@@ -394,8 +411,19 @@ def accumulate_shards_by_w(shards: Sequence[StokesIGridderInput], num_pixels: in
             sumw += scan.sum_wgt
         return wmin, wmax, nactive, sumw, keep
 
+    import time
+    phases, t_last = {}, time.perf_counter()
+
+    def mark(name):  # host clock between points where the device is idle anyway
+        nonlocal t_last
+        torch.cuda.current_stream(dev).synchronize()
+        now = time.perf_counter()
+        phases[name] = phases.get(name, 0.0) + 1e3 * (now - t_last)
+        t_last = now
+
     wmin, wmax, nactive, sumw, keep = scan_all(shards)
     wmin, wmax, nactive, sumw = agree_on_shard_statistics(wmin, wmax, nactive, sumw, group=group, device=dev)
+    mark("ms_scan")
     image = torch.zeros((num_pixels, num_pixels), dtype=torch.float64 if accumulate_fp64 else torch.float32, device=dev)
     if nactive == 0:
         plan = _cabi.plan_make(num_pixels, num_pixels, pixel_size_lm, pixel_size_lm, epsilon, 0.0, 0.0, 0,
@@ -413,25 +441,27 @@ def accumulate_shards_by_w(shards: Sequence[StokesIGridderInput], num_pixels: in
         torch.distributed.all_reduce(t, group=group)
         counts = t.cpu().numpy()
     edges = w_slab_edges(counts, wmin, wmax, nslabs, plane_cost=PLANE_COST_PER_CELL * common.nu * common.nv, dw=common.dw)
+    mark("ms_histogram")
     mine = shards
     if world > 1:
         mine = _exchange_rows_by_slab(shards, edges, group=group, device=dev)
-        torch.cuda.current_stream(dev).synchronize()
+        mark("ms_exchange")
     plan = common
     for s in ([rank] if world > 1 else range(nslabs)):
         slab = (edges[s], min(edges[s + 1], 1e300))
         smin, smax, sact, _ssum, skeep = scan_all(mine, slab)
+        mark("ms_slab_scan")
         if sact == 0:
             continue
         plan = _cabi.plan_make(num_pixels, num_pixels, pixel_size_lm, pixel_size_lm, epsilon, smin, smax, sact,
                                do_wstacking=True, fp64=accumulate_fp64, sigma=common.sigma, support=common.support)
         assert (plan.nu, plan.nv, plan.dw, plan.nshift) == (common.nu, common.nv, common.dw, common.nshift)
-        for a, _sh, _w in skeep:
-            rep = Report()
-            with ctx.lock:
-                check(L.cip_grid_accumulate(ctx.handle, C.byref(a), C.byref(plan), image.data_ptr(), C.byref(rep)))
+        for rep in _grid_shards(ctx, [a for a, _sh, _w in skeep], plan, image):
             if reports is not None:
-                reports.append(dict(rep.as_dict(), nplanes=plan.nplanes, slab=s))
+                reports.append(dict(rep, nplanes=plan.nplanes, slab=s))
+        mark("ms_grid_call")
+    if reports:
+        reports[-1]["phases_ms"] = phases
     return image, plan, sumw
 
 

@@ -561,7 +561,7 @@ def test_w_slab_argument_selects_samples(wg, wide):
     from ska_sdp_cip.wgridder import make_args
     (uvw, freq, vis, wgt, nx, px), ref = wide
     ctx = _cabi.Context.get(-1)
-    aw = np.abs(uvw[:, 2:3]) * freq[None, :] / 299792458.0
+    aw = np.abs(uvw[:, 2:3]) * (freq[None, :] / 299792458.0)  # the library's own order of operations
     cut = float(np.median(aw[wgt != 0]))
     total, sums = np.zeros((nx, nx)), []
     for slab in ((0.0, cut), (cut, 1e300)):
