@@ -80,11 +80,13 @@ def make_args(uvw, freq, ms, wgt, mask, npix_x, npix_y, pixsize_x, pixsize_y, ep
 
 def ms2dirty(uvw, freq, ms, wgt=None, npix_x=0, npix_y=0, pixsize_x=0.0, pixsize_y=0.0, nu=0, nv=0,
              epsilon=1e-4, do_wstacking=False, nthreads=1, verbosity=0, mask=None,
-             double_precision_accumulation=False, *, device: int = -1, return_info: bool = False):
+             double_precision_accumulation=False, *, device: int = -1, return_info: bool = False, w_slab=None):
     """Dirty image (npix_x, npix_y) of the given visibilities; see the module docstring.
 
     ``nthreads``, ``nu``, ``nv`` and ``verbosity`` are accepted for signature compatibility and ignored.
     complex128 ``ms`` or ``double_precision_accumulation=True`` selects float64 grids and a float64 result.
+    ``w_slab=(w_lo, w_hi)`` (an extension) restricts the image to the samples with w_lo <= |w| < w_hi wavelengths:
+    one share of a |w|-sharded invert (SURVEY.md 8e option 3).
     """
     del nthreads, nu, nv, verbosity
     dev_in = _is_torch_cuda(ms)
@@ -110,7 +112,7 @@ def ms2dirty(uvw, freq, ms, wgt=None, npix_x=0, npix_y=0, pixsize_x=0.0, pixsize
         out = _host_result((npix_x, npix_y), np.float64 if fp64 else np.float32)
         memspace = 0
     args = make_args(uvw, freq, ms, wgt, mask, npix_x, npix_y, pixsize_x, pixsize_y, epsilon, do_wstacking, fp64,
-                     memspace)
+                     memspace, w_slab=w_slab)
     ctx = Context.get(device)
     scan, plan, rep = ScanResult(), Plan(), Report()
     with ctx.lock:

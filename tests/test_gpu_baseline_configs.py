@@ -79,3 +79,44 @@ def test_configs3_per_gpu_share_matches_dft_on_sampled_pixels(dev):
     got, ref, info = run_config(cfg, dev, chan=slice(c0, c1))
     assert info["plan"]["nu"] >= 16384 * 1.25 and info["plan"]["nplanes"] >= 10
     assert dft.rel_rms(got, ref) <= TOL_FP32
+
+
+def test_configs4_w_slab_share_fp64_matches_dft_on_sampled_pixels(dev):
+    """BASELINE.json configs[4]: high-w SKA-Low, 32768^2 image, epsilon 1e-5, float64 grids, w planes sharded over 8
+    GPUs.  One time step of the configuration (130,816 rows x 128 channels = 16.7 M samples); of its 8 |w| slabs of
+    equal cost (invert.w_slab_edges) the share of ONE GPU is gridded -- tens of planes of 40960^2 complex128
+    processed in blocks of the few that fit 180 GB -- and checked against the DFT of the slab's samples."""
+    import torch
+    from ska_sdp_cip import _cabi, synthetic as S, wgridder
+    from ska_sdp_cip.invert import PLANE_COST_PER_CELL, w_slab_edges
+    cfg = S.ska_low(high_w=True, num_pixels=32768)
+    assert cfg.fp64 and cfg.epsilon == 1e-5
+    uvw_all = S.make_uvw(cfg)
+    px = S.pixel_size_lm(cfg, uvw_all)
+    t = cfg.n_times // 2
+    uvw = np.ascontiguousarray(uvw_all[t * cfg.n_baselines:(t + 1) * cfg.n_baselines])
+    freq = cfg.frequencies()
+    vis, wgt = S.make_vis_torch(cfg, uvw, freq, px, dev)
+    aw = np.abs(uvw[:, 2:3]) * (freq[None, :] / 299792458.0)
+    wmin, wmax = float(aw.min()), float(aw.max())
+    n = cfg.num_pixels
+    common = _cabi.plan_make(n, n, px, px, cfg.epsilon, wmin, wmax, aw.size, fp64=True)
+    counts, _ = np.histogram(aw, bins=4096, range=(wmin, wmax))
+    edges = w_slab_edges(counts, wmin, wmax, 8, plane_cost=PLANE_COST_PER_CELL * common.nu * common.nv, dw=common.dw)
+    slab = (edges[3], edges[4])
+    d_uvw, d_freq = torch.from_numpy(uvw).to(dev), torch.from_numpy(freq).to(dev)
+    img, info = wgridder.ms2dirty(d_uvw, d_freq, vis, wgt, n, n, px, px, epsilon=cfg.epsilon, do_wstacking=True,
+                                  double_precision_accumulation=True, return_info=True, w_slab=slab)
+    plan, rep = info["plan"], info["report"]
+    assert plan["accumulate_fp64"] == 1 and plan["nu"] >= 40960
+    assert plan["nplanes"] < common.nplanes / 4            # the slab spans a fraction of the 600+ planes of the whole
+    assert rep["nblocks"] >= 2 and plan["plane_block"] < plan["nplanes"]   # processed in plane blocks
+    _, _, _, pi, pj = S.source_list(cfg, px)
+    pix = dft_torch.sample_pixels(n, n, 1024, seed=0, always=np.asarray(pi) * n + np.asarray(pj))
+    got = img.reshape(-1)[torch.from_numpy(pix).to(dev)].cpu().numpy()
+    del img
+    torch.cuda.empty_cache()
+    inside = torch.from_numpy((aw >= slab[0]) & (aw < slab[1])).to(dev)
+    assert int(inside.sum()) == info["scan"]["nactive"] + int((inside & (wgt == 0)).sum())
+    ref = dft_torch.dft_pixels(d_uvw, d_freq, vis, wgt * inside, n, n, px, px, pix, device=dev)
+    assert dft.rel_rms(got, ref) <= TOL_FP64
