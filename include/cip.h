@@ -182,6 +182,11 @@ cip_status cip_invert(cip_ctx* ctx, const cip_invert_args* args, void* dirty_out
 cip_status cip_stokes_i(cip_ctx* ctx, const void* vis4, const uint8_t* flags4, const float* wgt4,
                         int64_t nrow, int64_t nchan, void* vis_out, float* effw_out, int memspace);
 
+/* The same on device memory, enqueued on cip_ctx_stream without waiting: for callers that pipeline their own
+ * uploads (order them against the stream with events). */
+cip_status cip_stokes_i_async(cip_ctx* ctx, const void* vis4, const uint8_t* flags4, const float* wgt4, int64_t nrow,
+                              int64_t nchan, void* vis_out, float* effw_out);
+
 /* ---- T1-T3: uvw tile binning (tiling_plan.py:29-181), bit-exact ------------------ */
 typedef struct cip_tile_result cip_tile_result; /* device-resident result of one binning */
 

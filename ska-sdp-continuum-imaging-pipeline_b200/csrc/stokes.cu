@@ -75,3 +75,20 @@ extern "C" cip_status cip_stokes_i(cip_ctx* ctx, const void* vis4, const uint8_t
   CIP_CHECK_CUDA(cudaStreamSynchronize(st));
   return CIP_OK;
 }
+
+// The same on device-resident blocks without waiting for the kernel: the caller orders it against its uploads with
+// events on cip_ctx_stream (the pinned double-buffered reader pipeline of ska_sdp_cip.invert).
+extern "C" cip_status cip_stokes_i_async(cip_ctx* ctx, const void* vis4, const uint8_t* flags4, const float* wgt4, int64_t nrow,
+                                         int64_t nchan, void* vis_out, float* effw_out) {
+  CIP_REQUIRE(ctx && vis4 && flags4 && wgt4 && vis_out && effw_out, "NULL argument");
+  CIP_REQUIRE(nrow >= 0 && nchan >= 0, "negative nrow/nchan");
+  CIP_ENTER_DEVICE(ctx);
+  const int64_t n = nrow * nchan;
+  if (n == 0) return CIP_OK;
+  int blocks = (int)std::min<int64_t>((n + 255) / 256, (int64_t)ctx->sm_count * 16);
+  stokes_kernel<<<blocks, 256, 0, ctx->stream>>>(static_cast<const float4*>(vis4), reinterpret_cast<const uint32_t*>(flags4),
+                                                 reinterpret_cast<const float4*>(wgt4), n, static_cast<float2*>(vis_out), effw_out);
+  ctx->launches++;
+  CIP_CHECK_CUDA(cudaGetLastError());
+  return CIP_OK;
+}

@@ -100,6 +100,8 @@ def lib():
                                      C.POINTER(Plan), C.POINTER(Report)]
             L.cip_stokes_i.argtypes = [C.c_void_p, C.c_void_p, C.c_void_p, C.c_void_p, C.c_int64, C.c_int64,
                                        C.c_void_p, C.c_void_p, C.c_int]
+            L.cip_stokes_i_async.argtypes = [C.c_void_p, C.c_void_p, C.c_void_p, C.c_void_p, C.c_int64, C.c_int64,
+                                             C.c_void_p, C.c_void_p]
             L.cip_tile_bin.argtypes = [C.c_void_p, C.c_void_p, C.c_int64, C.c_void_p, C.c_int64,
                                        C.POINTER(C.c_double * 3), C.c_int64, C.c_int, C.POINTER(C.c_void_p),
                                        C.POINTER(C.c_int64), C.POINTER(C.c_int64)]
@@ -113,7 +115,7 @@ def lib():
 
 EXPORTS = ["cip_last_error", "cip_version", "cip_ctx_create", "cip_ctx_destroy", "cip_ctx_stream",
            "cip_ctx_synchronize", "cip_ctx_launches", "cip_ctx_device", "cip_current_device", "cip_plan_make", "cip_kernel_table", "cip_kernel_ft", "cip_scan", "cip_w_histogram",
-           "cip_grid_accumulate", "cip_grid_accumulate_many", "cip_bin_inspect", "cip_correct_image", "cip_invert", "cip_stokes_i", "cip_tile_bin",
+           "cip_grid_accumulate", "cip_grid_accumulate_many", "cip_bin_inspect", "cip_correct_image", "cip_invert", "cip_stokes_i", "cip_stokes_i_async", "cip_tile_bin",
            "cip_tile_fetch", "cip_tile_gather", "cip_tile_free"]
 
 

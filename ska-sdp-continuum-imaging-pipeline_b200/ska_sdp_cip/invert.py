@@ -65,28 +65,61 @@ class StokesIGridderInput:
         return self.flags.logical_not() * self.weights
 
     @classmethod
-    def from_measurement_set_reader(cls, ms_reader: MeasurementSetReader, *, device: Optional[int] = None
-                                    ) -> "StokesIGridderInput":
+    def from_measurement_set_reader(cls, ms_reader: MeasurementSetReader, *, device: Optional[int] = None,
+                                    upload_rows: Optional[int] = None) -> "StokesIGridderInput":
         """Read one chunk and convert to Stokes I on the GPU: vis_I = (v0+v3)/2,
-        w_I = 4/(1/w0+1/w3), flagged if either hand is flagged (invert.py:78-116)."""
+        w_I = 4/(1/w0+1/w3), flagged if either hand is flagged (invert.py:78-116).
+
+        The chunk is read and uploaded in row blocks of ``upload_rows`` (default: about 256 MB of 4-polarisation
+        data) through two pinned staging buffers: while block k is converted on the GPU (cip_stokes_i) block k+1 is
+        read from the reader, copied into the other pinned buffer and sent host -> device on a copy stream.  Only
+        the Stokes-I visibilities and effective weights (12 of the 52 bytes per sample) stay resident."""
         torch = _torch()
         dev = _device(device)
-        vis = np.ascontiguousarray(ms_reader.visibilities(), dtype=np.complex64)
-        flags = np.ascontiguousarray(ms_reader.flags(), dtype=np.bool_)
-        weights = np.ascontiguousarray(ms_reader.weights(), dtype=np.float32)
-        if vis.ndim != 3 or vis.shape[2] != 4:
-            raise ValueError("expected 4 polarisation products")
-        nrow, nchan = vis.shape[:2]
-        d_vis4 = torch.from_numpy(vis).to(dev, non_blocking=False)
-        d_flags4 = torch.from_numpy(flags.view(np.uint8)).to(dev)
-        d_wgt4 = torch.from_numpy(weights).to(dev)
-        d_vis = torch.empty((nrow, nchan), dtype=torch.complex64, device=dev)
-        d_effw = torch.empty((nrow, nchan), dtype=torch.float32, device=dev)
-        torch.cuda.current_stream(dev).synchronize()
+        nrow_total, nchan = int(ms_reader.num_data_rows), int(ms_reader.num_channels)
+        d_vis = torch.empty((nrow_total, nchan), dtype=torch.complex64, device=dev)
+        d_effw = torch.empty((nrow_total, nchan), dtype=torch.float32, device=dev)
         ctx = Context.get(dev.index)
-        with ctx.lock:
-            check(lib().cip_stokes_i(ctx.handle, d_vis4.data_ptr(), d_flags4.data_ptr(), d_wgt4.data_ptr(),
-                                     nrow, nchan, d_vis.data_ptr(), d_effw.data_ptr(), 1))
+        if nrow_total and nchan:
+            per_row = nchan * 4 * (8 + 4 + 1)
+            rows = int(upload_rows or max(1, (256 << 20) // per_row))
+            nblocks = min(nrow_total, max(1, -(-nrow_total // rows)))
+            blocks = ms_reader.partition(nblocks, 1) if nblocks > 1 else [ms_reader]
+            rows = max(int(b.num_data_rows) for b in blocks)
+            copy_stream = torch.cuda.Stream(device=dev)
+            stage = [dict(vis=torch.empty((rows, nchan, 4), dtype=torch.complex64, pin_memory=True),
+                          flg=torch.empty((rows, nchan, 4), dtype=torch.uint8, pin_memory=True),
+                          wgt=torch.empty((rows, nchan, 4), dtype=torch.float32, pin_memory=True),
+                          d_vis=torch.empty((rows, nchan, 4), dtype=torch.complex64, device=dev),
+                          d_flg=torch.empty((rows, nchan, 4), dtype=torch.uint8, device=dev),
+                          d_wgt=torch.empty((rows, nchan, 4), dtype=torch.float32, device=dev),
+                          sent=torch.cuda.Event(), used=torch.cuda.Event()) for _ in range(min(2, len(blocks)))]
+            lib_stream = torch.cuda.ExternalStream(lib().cip_ctx_stream(ctx.handle), device=dev)
+            row0 = 0
+            for k, blk in enumerate(blocks):
+                st = stage[k % len(stage)]
+                n = int(blk.num_data_rows)
+                vis = np.asarray(blk.visibilities())
+                if vis.ndim != 3 or vis.shape[2] != 4:
+                    raise ValueError("expected 4 polarisation products")
+                st["used"].synchronize()  # the conversion that last read this pair of buffers has finished
+                st["vis"][:n].numpy()[...] = vis
+                st["flg"][:n].numpy()[...] = np.asarray(blk.flags()).view(np.uint8) if np.asarray(blk.flags()).dtype == np.bool_ \
+                    else np.asarray(blk.flags(), dtype=np.uint8)
+                st["wgt"][:n].numpy()[...] = blk.weights()
+                with torch.cuda.stream(copy_stream):
+                    st["d_vis"][:n].copy_(st["vis"][:n], non_blocking=True)
+                    st["d_flg"][:n].copy_(st["flg"][:n], non_blocking=True)
+                    st["d_wgt"][:n].copy_(st["wgt"][:n], non_blocking=True)
+                    st["sent"].record(copy_stream)
+                lib_stream.wait_event(st["sent"])
+                with ctx.lock:  # asynchronous: the call returns once the kernel is enqueued behind the copy
+                    check(lib().cip_stokes_i_async(ctx.handle, st["d_vis"].data_ptr(), st["d_flg"].data_ptr(),
+                                                   st["d_wgt"].data_ptr(), n, nchan, d_vis[row0:row0 + n].data_ptr(),
+                                                   d_effw[row0:row0 + n].data_ptr()))
+                st["used"].record(lib_stream)
+                row0 += n
+            lib_stream.synchronize()
         freqs = torch.from_numpy(np.ascontiguousarray(ms_reader.channel_frequencies(), dtype=np.float64)).to(dev)
         uvw = torch.from_numpy(np.ascontiguousarray(ms_reader.uvw(), dtype=np.float64)).to(dev)
         return cls(freqs, None, uvw, d_vis, d_effw)
