@@ -81,6 +81,15 @@ typedef struct {
   int do_wstacking;         /* 1 = improved w-stacking, 0 = ignore w                 */
   int accumulate_fp64;      /* 0: complex64 grids; 1: complex128 grids + tighter kernel */
   int memspace;             /* 0: all pointers are host memory; 1: device memory of the ctx device */
+  /* Jagged rows (all NULL / 0 for the dense (nrow,nchan) layout): row r holds the channels
+   * [row_chan_start[r], row_chan_stop[r]) only, its visibilities (and weights, mask) are the row_chan_stop[r] -
+   * row_chan_start[r] elements starting at element row_vis_offset[r] of vis (wgt, mask), nvis elements in total.
+   * This is the layout of the reference's uvw tiles (Tile.uvw / visibilities / channel_start_indices /
+   * channel_stop_indices, src/ska_sdp_cip/uvw_tiling/tile.py:14-50): tiles are gridded as they are stored.   */
+  const int64_t* row_vis_offset;
+  const int32_t* row_chan_start;
+  const int32_t* row_chan_stop;
+  int64_t nvis;
   double w_lo, w_hi;        /* w_hi > 0: only the samples with w_lo <= |w| < w_hi (wavelengths) take part -- one
                              * |w| slab of a w-sharded invert (SURVEY 8e option 3); w_hi <= 0: all samples      */
 } cip_invert_args;

@@ -43,10 +43,11 @@ __global__ void __launch_bounds__(256) hist_kernel(DevInputs in, GridGeom g, con
   if (row >= in.nrow) return;
   const BinConsts kc = bin_consts(g);
   const RowGeom rg = row_geom(g, in.uvw[3 * row], in.uvw[3 * row + 1], in.uvw[3 * row + 2]);
-  for (int c0 = 0; c0 < (int)in.nchan; c0 += 32) {
+  const RowSpan sp = row_span(in, row);
+  for (int c0 = sp.c_begin & ~31; c0 < sp.c_end; c0 += 32) {
     const int c = c0 + lane;
     uint32_t key = kNoKey;
-    if (c < in.nchan) {
+    if (c >= sp.c_begin && c < sp.c_end) {
       const SampleGeom s = sample_geom<false>(g, kc, rg, finv[c]);
       if (!(in.w_hi > 0.0) || (s.w >= in.w_lo && s.w < in.w_hi)) key = bin_key(g, bin_cell(g, kc, s));
     }
@@ -55,7 +56,7 @@ __global__ void __launch_bounds__(256) hist_kernel(DevInputs in, GridGeom g, con
     if (((bound >> lane) & 1u) && key != kNoKey) {
       const unsigned after = lane == 31 ? 0u : bound >> (lane + 1);
       const int len = after ? __ffs(after) : 32 - lane;  // up to the next boundary or the end of the chunk
-      atomicAdd(table + key, (uint32_t)min(len, (int)in.nchan - c));
+      atomicAdd(table + key, (uint32_t)min(len, sp.c_end - c));
     }
   }
 }
@@ -294,17 +295,18 @@ __global__ void __launch_bounds__(256, 6) records_kernel(DevInputs in, GridGeom 
   if (row >= in.nrow) return;
   const BinConsts kc = bin_consts(g);
   const RowGeom rg = row_geom(g, in.uvw[3 * row], in.uvw[3 * row + 1], in.uvw[3 * row + 2]);
-  for (int c0 = 0; c0 < (int)in.nchan; c0 += 32) {
+  const RowSpan sp = row_span(in, row);
+  for (int c0 = sp.c_begin & ~31; c0 < sp.c_end; c0 += 32) {
     const int c = c0 + lane;
-    const bool valid = c < in.nchan;
+    const bool valid = c >= sp.c_begin && c < sp.c_end;
     // the sample loads are issued before the geometry, which does not depend on them (the pass is bound by
     // memory latency)
     float2 v = make_float2(0.f, 0.f);
     float wgt = 0.f;
     if (valid) {
-      v = __ldcs(in.vis + row * in.vstride + c);
-      wgt = in.wgt ? __ldcs(in.wgt + row * in.wstride + c) : 1.0f;
-      if (in.mask && in.mask[row * in.wstride + c] == 0) wgt = 0.0f;
+      v = __ldcs(in.vis + sp.vbase + c);
+      wgt = in.wgt ? __ldcs(in.wgt + sp.wbase + c) : 1.0f;
+      if (in.mask && in.mask[sp.wbase + c] == 0) wgt = 0.0f;
     }
     uint32_t key = kNoKey;
     SampleGeom s;
@@ -321,7 +323,7 @@ __global__ void __launch_bounds__(256, 6) records_kernel(DevInputs in, GridGeom 
     if (lead == lane && key != kNoKey) {
       const unsigned after = lane == 31 ? 0u : bound >> (lane + 1);
       const int len = after ? __ffs(after) : 32 - lane;
-      pos = atomicAdd(table + key, (uint32_t)min(len, (int)in.nchan - c));
+      pos = atomicAdd(table + key, (uint32_t)min(len, sp.c_end - c));
     }
     pos = __shfl_sync(0xffffffffu, pos, lead) + (uint32_t)(lane - lead);
     if (key == kNoKey) continue;
@@ -397,8 +399,8 @@ cip_status run_binning(cip_ctx* ctx, int slot, const DevInputs& in, const GridGe
   const int64_t n = epw * nwin_pass;
   CIP_REQUIRE(epw <= kMaxTableEntries && n < ((int64_t)1 << 32), "key table too large (%lld entries per window)", (long long)epw);
   CIP_REQUIRE(g.ntu < 65536 && g.ntv < 65536 && g.nwin < 65536, "grid or plane stack too large for the job format");
-  const int64_t nrec = nrow * nchan;
-  CIP_REQUIRE(nrec + 8 * n / 1 >= 0 && nrec < ((int64_t)1 << 32) - ((int64_t)1 << 28), "too many samples for one binning pass");
+  const int64_t nrec = in.voff ? in.nvis : nrow * nchan;
+  CIP_REQUIRE(nrec < ((int64_t)1 << 32) - ((int64_t)1 << 28), "too many samples for one binning pass");
   const bool pack = !fp64 && g.W <= kFastSupport;
   const size_t rec_bytes = pack ? 16 : 32;
 

@@ -221,7 +221,7 @@ struct cip_ctx {
   int64_t staged_dims[4] = {};
   int64_t launches = 0;
   // inputs staged on the device when the caller passes host memory
-  cip::DevBuf in_uvw, in_freq, in_vis, in_wgt, in_mask;
+  cip::DevBuf in_uvw, in_freq, in_vis, in_wgt, in_mask, in_rows;
   cip::DevBuf out_img;
   // scan
   cip::DevBuf scan_out;
@@ -267,6 +267,11 @@ struct DevInputs {
   const uint8_t* mask;
   int64_t nrow, nchan, vstride, wstride;
   double w_lo = 0.0, w_hi = 0.0;  // w_hi > 0: only samples with w_lo <= |w| < w_hi are active
+  // jagged rows (nullptr: dense): channels [ch0[r], ch1[r]) of row r at elements voff[r] ... of vis / wgt / mask
+  const int64_t* voff = nullptr;
+  const int32_t* ch0 = nullptr;
+  const int32_t* ch1 = nullptr;
+  int64_t nvis = 0;
 };
 cip_status validate_args(const cip_invert_args* a);
 // Rows [row0[c], row0[c+1]) of the visibilities are on the device once ready[c] has fired.

@@ -78,6 +78,10 @@ cip_status validate_args(const cip_invert_args* a) {
   CIP_REQUIRE(a->vis_row_stride == 0 || a->vis_row_stride >= a->nchan, "vis_row_stride < nchan");
   CIP_REQUIRE(a->wgt_row_stride == 0 || a->wgt_row_stride >= a->nchan, "wgt_row_stride < nchan");
   CIP_REQUIRE(a->memspace == 0 || a->memspace == 1, "memspace must be 0 (host) or 1 (device)");
+  if (a->row_vis_offset || a->row_chan_start || a->row_chan_stop) {
+    CIP_REQUIRE(a->row_vis_offset && a->row_chan_start && a->row_chan_stop, "jagged rows need all three row tables");
+    CIP_REQUIRE(a->nvis >= 0 && a->nvis < (int64_t)1 << 32, "bad nvis for jagged rows");
+  }
   CIP_REQUIRE(!(a->w_hi > 0) || (a->do_wstacking && a->w_lo >= 0 && a->w_lo < a->w_hi), "bad |w| slab [%g, %g)", a->w_lo, a->w_hi);
   return CIP_OK;
 }
@@ -118,6 +122,10 @@ cip_status stage_inputs(cip_ctx* ctx, const cip_invert_args* a, DevInputs* d, Vi
     d->mask = a->mask;
     d->vstride = vs;
     d->wstride = ws;
+    d->voff = a->row_vis_offset;
+    d->ch0 = a->row_chan_start;
+    d->ch1 = a->row_chan_stop;
+    d->nvis = a->row_vis_offset ? a->nvis : 0;
     if (feed) {
       // Device inputs are all there; they are still cut into row chunks so that the binning of chunk c+1
       // (context stream, bound by memory latency) overlaps the gridding of chunk c (grid stream, bound by
@@ -129,6 +137,7 @@ cip_status stage_inputs(cip_ctx* ctx, const cip_invert_args* a, DevInputs* d, Vi
       (void)vis_bytes;
       if (const char* e = getenv("CIP_DEVICE_CHUNKS")) nchunks = std::min(kMaxChunks, std::max(1, atoi(e)));
       nchunks = (int)std::min<int64_t>(nchunks, std::max<int64_t>(nrow, 1));
+      if (a->row_vis_offset) nchunks = 1;
       feed->nchunks = nchunks;
       for (int c = 0; c <= nchunks; ++c) feed->row0[c] = nrow * c / nchunks;
       for (int c = 0; c < nchunks; ++c) feed->ready[c] = nullptr;  // nothing to wait for
@@ -137,6 +146,51 @@ cip_status stage_inputs(cip_ctx* ctx, const cip_invert_args* a, DevInputs* d, Vi
   }
   cudaStream_t st = ctx->stream;
   ctx->t_stage_begin = now_ms();
+  if (a->row_vis_offset) {
+    // jagged rows from host memory: everything in one piece (no chunked stream)
+    const size_t nvis = (size_t)a->nvis;
+    CIP_TRY(ctx->in_uvw.ensure(sizeof(double) * 3 * (size_t)nrow + 8));
+    CIP_TRY(ctx->in_freq.ensure(sizeof(double) * (size_t)nchan + 8));
+    CIP_TRY(ctx->in_rows.ensure(16 * (size_t)nrow + 64));
+    if (a->wgt) CIP_TRY(ctx->in_wgt.ensure(sizeof(float) * nvis + 8));
+    if (a->mask) CIP_TRY(ctx->in_mask.ensure(nvis + 8));
+    if (feed) CIP_TRY(ctx->in_vis.ensure(sizeof(float2) * nvis + 8));
+    int64_t* d_off = ctx->in_rows.as<int64_t>();
+    int32_t* d_c0 = reinterpret_cast<int32_t*>(d_off + nrow);
+    int32_t* d_c1 = d_c0 + nrow;
+    d->uvw = ctx->in_uvw.as<double>();
+    d->freq = ctx->in_freq.as<double>();
+    d->vis = feed ? ctx->in_vis.as<float2>() : nullptr;
+    d->wgt = a->wgt ? ctx->in_wgt.as<float>() : nullptr;
+    d->mask = a->mask ? ctx->in_mask.as<uint8_t>() : nullptr;
+    d->vstride = d->wstride = nchan;
+    d->voff = d_off;
+    d->ch0 = d_c0;
+    d->ch1 = d_c1;
+    d->nvis = a->nvis;
+    if (nrow) {
+      CIP_CHECK_CUDA(cudaMemcpyAsync(ctx->in_uvw.p, a->uvw, sizeof(double) * 3 * nrow, cudaMemcpyHostToDevice, st));
+      CIP_CHECK_CUDA(cudaMemcpyAsync(ctx->in_freq.p, a->freq, sizeof(double) * nchan, cudaMemcpyHostToDevice, st));
+      CIP_CHECK_CUDA(cudaMemcpyAsync(d_off, a->row_vis_offset, sizeof(int64_t) * nrow, cudaMemcpyHostToDevice, st));
+      CIP_CHECK_CUDA(cudaMemcpyAsync(d_c0, a->row_chan_start, sizeof(int32_t) * nrow, cudaMemcpyHostToDevice, st));
+      CIP_CHECK_CUDA(cudaMemcpyAsync(d_c1, a->row_chan_stop, sizeof(int32_t) * nrow, cudaMemcpyHostToDevice, st));
+      if (a->wgt && nvis) CIP_CHECK_CUDA(cudaMemcpyAsync(ctx->in_wgt.p, a->wgt, sizeof(float) * nvis, cudaMemcpyHostToDevice, st));
+      if (a->mask && nvis) CIP_CHECK_CUDA(cudaMemcpyAsync(ctx->in_mask.p, a->mask, nvis, cudaMemcpyHostToDevice, st));
+      if (feed && nvis) CIP_CHECK_CUDA(cudaMemcpyAsync(ctx->in_vis.p, a->vis, sizeof(float2) * nvis, cudaMemcpyHostToDevice, st));
+    }
+    CIP_CHECK_CUDA(cudaEventRecord(ctx->small_ev, st));
+    if (feed) {
+      feed->nchunks = 1;
+      feed->row0[0] = 0;
+      feed->row0[1] = nrow;
+      feed->ready[0] = nullptr;  // same stream: already ordered
+    }
+    if (ms_h2d) {
+      CIP_CHECK_CUDA(cudaEventSynchronize(ctx->small_ev));
+      *ms_h2d = now_ms() - ctx->t_stage_begin;
+    }
+    return CIP_OK;
+  }
   CIP_TRY(ctx->in_uvw.ensure(sizeof(double) * 3 * (size_t)nrow + 8));
   CIP_TRY(ctx->in_freq.ensure(sizeof(double) * (size_t)nchan + 8));
   if (a->wgt) CIP_TRY(ctx->in_wgt.ensure(sizeof(float) * (size_t)nrow * nchan + 8));
@@ -286,7 +340,7 @@ extern "C" cip_status cip_ctx_destroy(cip_ctx* ctx) {
   if (ctx->stream) cudaStreamSynchronize(ctx->stream);
   if (ctx->grid_stream) cudaStreamSynchronize(ctx->grid_stream);
   for (auto& kv : ctx->fft_plans) cufftDestroy(kv.second.handle);
-  DevBuf* bufs[] = {&ctx->in_uvw, &ctx->in_freq, &ctx->in_vis, &ctx->in_wgt, &ctx->in_mask, &ctx->out_img,
+  DevBuf* bufs[] = {&ctx->in_uvw, &ctx->in_freq, &ctx->in_vis, &ctx->in_wgt, &ctx->in_mask, &ctx->in_rows, &ctx->out_img,
                     &ctx->scan_out, &ctx->grid, &ctx->image, &ctx->tables, &ctx->fft_t, &ctx->t_uvw, &ctx->t_freq, &ctx->t_vis,
                     &ctx->call_flags};
   for (auto& w : ctx->work) w.release();

@@ -153,6 +153,27 @@ __device__ __forceinline__ bool sample_active(const float2 v, const float* wgt, 
   return w != 0.0f && (v.x != 0.0f || v.y != 0.0f);
 }
 
+// Channels of a row and where its samples live: sample (row, c) is element vbase + c of vis and wbase + c of
+// wgt / mask (dense rows: all channels at row * stride; jagged rows: see DevInputs).
+struct RowSpan {
+  int c_begin, c_end;
+  int64_t vbase, wbase;
+};
+__device__ __forceinline__ RowSpan row_span(const DevInputs& in, int64_t row) {
+  RowSpan s;
+  if (in.voff) {
+    s.c_begin = in.ch0[row];
+    s.c_end = in.ch1[row];
+    s.vbase = s.wbase = in.voff[row] - s.c_begin;
+  } else {
+    s.c_begin = 0;
+    s.c_end = (int)in.nchan;
+    s.vbase = row * in.vstride;
+    s.wbase = row * in.wstride;
+  }
+  return s;
+}
+
 // ES kernel phi(x) = exp(betaW (sqrt(1-x^2) - 1)) for |x| < 1, else 0.
 __device__ __forceinline__ float es_kernel(float x, float beta_w) {
   float t = 1.0f - x * x;

@@ -82,6 +82,12 @@ static DevInputs row_slice(const DevInputs& in, int64_t r0, int64_t r1) {
   DevInputs c = in;
   c.nrow = r1 - r0;
   c.uvw = in.uvw + 3 * r0;
+  if (in.voff) {  // jagged rows: the offsets are absolute, only the row tables move
+    c.voff = in.voff + r0;
+    c.ch0 = in.ch0 + r0;
+    c.ch1 = in.ch1 + r0;
+    return c;
+  }
   c.vis = in.vis + r0 * in.vstride;
   if (in.wgt) c.wgt = in.wgt + r0 * in.wstride;
   if (in.mask) c.mask = in.mask + r0 * in.wstride;

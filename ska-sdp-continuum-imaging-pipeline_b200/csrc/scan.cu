@@ -76,6 +76,24 @@ __global__ void __launch_bounds__(256) scan_kernel(DevInputs in, int do_wstackin
   scan_finish(acc, out);
 }
 
+// jagged rows (and any other layout): one warp per row, lanes stride the row's channels
+__global__ void __launch_bounds__(256) scan_rows_kernel(DevInputs in, int do_wstacking, ScanOut* out) {
+  ScanAcc acc;
+  acc.w_lo = in.w_lo;
+  acc.w_hi = in.w_hi;
+  const int lane = threadIdx.x & 31;
+  for (int64_t row = ((int64_t)blockIdx.x * blockDim.x + threadIdx.x) >> 5; row < in.nrow; row += ((int64_t)gridDim.x * blockDim.x) >> 5) {
+    const RowSpan sp = row_span(in, row);
+    const double wm = do_wstacking ? fabs(in.uvw[3 * row + 2]) : 0.0;
+    for (int c = sp.c_begin + lane; c < sp.c_end; c += 32) {
+      const float w = in.wgt ? in.wgt[sp.wbase + c] : 1.0f;
+      const bool masked = in.mask && in.mask[sp.wbase + c] == 0;
+      acc.add(w, masked, wm * (in.freq[c] / kSpeedOfLight));
+    }
+  }
+  scan_finish(acc, out);
+}
+
 // nchan, strides multiples of 4 and 16-byte aligned pointers: four channels per thread and
 // iteration with 128-bit loads (2 x float4 vis, float4 wgt, one 32-bit word of mask)
 // (frequency / c per channel is tabulated in shared memory: a float64 division per sample made this kernel
@@ -132,17 +150,20 @@ __global__ void __launch_bounds__(256) whist_kernel(DevInputs in, double wmin, d
   __shared__ uint32_t s_cnt[kMaxWBins];
   for (int b = threadIdx.x; b < nbins; b += blockDim.x) s_cnt[b] = 0;
   __syncthreads();
-  const int64_t nchan = in.nchan, total = in.nrow * nchan;
-  for (int64_t k = (int64_t)blockIdx.x * blockDim.x + threadIdx.x; k < total; k += (int64_t)gridDim.x * blockDim.x) {
-    const int64_t r = k / nchan, c = k - r * nchan;
-    float w = in.wgt ? in.wgt[r * in.wstride + c] : 1.0f;
-    if (in.mask && in.mask[r * in.wstride + c] == 0) w = 0.0f;
-    if (w == 0.0f) continue;
-    const double aw = fabs(in.uvw[3 * r + 2]) * (in.freq[c] / kSpeedOfLight);
-    if (in.w_hi > 0.0 && !(aw >= in.w_lo && aw < in.w_hi)) continue;
-    int b = (int)((aw - wmin) * scale);
-    b = b < 0 ? 0 : (b >= nbins ? nbins - 1 : b);
-    atomicAdd(&s_cnt[b], 1u);
+  const int lane = threadIdx.x & 31;
+  for (int64_t row = ((int64_t)blockIdx.x * blockDim.x + threadIdx.x) >> 5; row < in.nrow; row += ((int64_t)gridDim.x * blockDim.x) >> 5) {
+    const RowSpan sp = row_span(in, row);
+    const double wm = fabs(in.uvw[3 * row + 2]);
+    for (int c = sp.c_begin + lane; c < sp.c_end; c += 32) {
+      float w = in.wgt ? in.wgt[sp.wbase + c] : 1.0f;
+      if (in.mask && in.mask[sp.wbase + c] == 0) w = 0.0f;
+      if (w == 0.0f) continue;
+      const double aw = wm * (in.freq[c] / kSpeedOfLight);
+      if (in.w_hi > 0.0 && !(aw >= in.w_lo && aw < in.w_hi)) continue;
+      int b = (int)((aw - wmin) * scale);
+      b = b < 0 ? 0 : (b >= nbins ? nbins - 1 : b);
+      atomicAdd(&s_cnt[b], 1u);
+    }
   }
   __syncthreads();
   for (int b = threadIdx.x; b < nbins; b += blockDim.x)
@@ -159,7 +180,7 @@ cip_status run_w_histogram(cip_ctx* ctx, const DevInputs& in, double wmin, doubl
   const int64_t total = in.nrow * in.nchan;
   if (total > 0) {
     const double scale = wmax > wmin ? nbins / (wmax - wmin) : 0.0;
-    const int blocks = (int)std::min<int64_t>((total + 255) / 256, (int64_t)ctx->sm_count * 8);
+    const int blocks = (int)std::min<int64_t>((in.nrow * 32 + 255) / 256, (int64_t)ctx->sm_count * 8);
     whist_kernel<<<blocks, 256, 0, st>>>(in, wmin, scale, nbins, d);
     ctx->launches++;
     CIP_CHECK_CUDA(cudaGetLastError());
@@ -175,8 +196,13 @@ cip_status run_scan(cip_ctx* ctx, const DevInputs& in, int do_wstacking, cip_sca
   CIP_TRY(ctx->scan_out.ensure(sizeof(ScanOut)));
   cudaStream_t st = ctx->stream;
   scan_init_kernel<<<1, 1, 0, st>>>(ctx->scan_out.as<ScanOut>());
-  int64_t total = in.nrow * in.nchan;
-  if (total > 0) {
+  int64_t total = in.voff ? in.nvis : in.nrow * in.nchan;
+  if (total > 0 && in.voff) {
+    const int blocks = (int)std::min<int64_t>((in.nrow * 32 + 255) / 256, (int64_t)ctx->sm_count * 8);
+    scan_rows_kernel<<<blocks, 256, 0, st>>>(in, do_wstacking, ctx->scan_out.as<ScanOut>());
+    ctx->launches++;
+    CIP_CHECK_CUDA(cudaGetLastError());
+  } else if (total > 0) {
     auto al16 = [](const void* p) { return (reinterpret_cast<uintptr_t>(p) & 15) == 0; };
     const bool v4 = in.nchan % 4 == 0 && in.wstride % 4 == 0 && al16(in.wgt) && al16(in.mask) && in.nchan <= 4096;
     if (v4) {

@@ -159,6 +159,22 @@ def ducc_invert(gridder_input: StokesIGridderInput, num_pixels: int, pixel_size_
     return image, total
 
 
+def invert_tiles(tiles, channel_frequencies, num_pixels: int, pixel_size_asec: float, *, epsilon: float = EPSILON,
+                 accumulate_fp64: bool = False) -> NDArray:
+    """Dirty image of a measurement set that was reordered into uvw tiles (``uvw_tiling.reorder_by_uvw_tile``):
+    ``tiles`` are ``Tile`` objects or paths of tile chunk files; normalised by the number of samples (tiles carry
+    Stokes-I visibilities without weights).  Same image arguments as ``invert_measurement_set``."""
+    from pathlib import Path as _Path
+    from .uvw_tiling import Tile
+    from .wgridder import tiles2dirty
+    loaded = [Tile.load_npz(t) if isinstance(t, (str, _Path)) else t for t in tiles]
+    px = _pixel_size_lm(pixel_size_asec)
+    image, info = tiles2dirty(loaded, channel_frequencies, num_pixels, num_pixels, px, px, epsilon=epsilon,
+                              double_precision_accumulation=accumulate_fp64, return_info=True)
+    total = np.float32(info["scan"]["sum_wgt"])
+    return (1.0 / total) * image if total else image
+
+
 def worker_ducc_invert(gridder_input: StokesIGridderInput, num_pixels: int, pixel_size_asec: float, *,
                        epsilon: float = EPSILON, accumulate_fp64: bool = False) -> tuple[NDArray, float]:
     """Same as ducc_invert, for use as a dask task (reference: invert.py:187-197)."""

@@ -78,6 +78,53 @@ def make_args(uvw, freq, ms, wgt, mask, npix_x, npix_y, pixsize_x, pixsize_y, ep
     return a
 
 
+def make_jagged_args(uvw, freq, vis_flat, row_offsets, chan_start, chan_stop, wgt_flat, npix_x, npix_y, pixsize_x,
+                     pixsize_y, epsilon, do_wstacking, fp64, memspace) -> InvertArgs:
+    """Arguments for rows that hold only a range of channels each (the uvw tile layout): row r = channels
+    [chan_start[r], chan_stop[r]) at elements row_offsets[r] ... of the flat vis (and wgt)."""
+    a = make_args(uvw, freq, vis_flat, wgt_flat, None, npix_x, npix_y, pixsize_x, pixsize_y, epsilon, do_wstacking, fp64,
+                  memspace)
+    a.row_vis_offset = _cabi._ptr(row_offsets)
+    a.row_chan_start = _cabi._ptr(chan_start)
+    a.row_chan_stop = _cabi._ptr(chan_stop)
+    a.nvis = int(vis_flat.shape[0])
+    return a
+
+
+def tiles2dirty(tiles, freq, npix_x, npix_y, pixsize_x, pixsize_y, epsilon=1e-4, do_wstacking=True,
+                double_precision_accumulation=False, *, device: int = -1, return_info: bool = False):
+    """Dirty image of the visibilities held in uvw tiles (``ska_sdp_cip.uvw_tiling.Tile``: uvw per row slice, flat
+    visibilities, channel_start_indices / channel_stop_indices), gridded as they are stored -- the link between the
+    reorder step and the gridder that the reference has not made (src/ska_sdp_cip/uvw_tiling/reorder.py:129-155
+    writes the tiles, nothing reads them).  Tiles carry no weights: every sample has weight 1.  ``freq`` are the
+    channel frequencies the tiles' channel indices refer to."""
+    tiles = list(tiles)
+    freq = np.ascontiguousarray(freq, dtype=np.float64)
+    cat = lambda name, dt: (np.ascontiguousarray(np.concatenate([np.asarray(getattr(t, name)) for t in tiles]), dtype=dt)
+                            if tiles else np.zeros(0, dtype=dt))
+    uvw = cat("uvw", np.float64).reshape(-1, 3)
+    c0, c1 = cat("channel_start_indices", np.int32), cat("channel_stop_indices", np.int32)
+    vis = cat("visibilities", np.complex64)
+    if len(c0) and (c0.min() < 0 or c1.max() > len(freq) or np.any(c1 < c0)):
+        raise ValueError("tile channel ranges do not fit the given channel frequencies")
+    lens = (c1 - c0).astype(np.int64)
+    off = np.concatenate([[0], np.cumsum(lens)[:-1]]).astype(np.int64) if len(lens) else np.zeros(0, dtype=np.int64)
+    if int(lens.sum()) != len(vis):
+        raise ValueError("tile visibilities do not match their channel ranges")
+    fp64 = bool(double_precision_accumulation)
+    out = _host_result((npix_x, npix_y), np.float64 if fp64 else np.float32)
+    args = make_jagged_args(uvw, freq, vis, off, c0, c1, None, npix_x, npix_y, pixsize_x, pixsize_y, epsilon,
+                            do_wstacking, fp64, 0)
+    ctx = Context.get(device)
+    scan, plan, rep = ScanResult(), Plan(), Report()
+    with ctx.lock:
+        check(lib().cip_invert(ctx.handle, C.byref(args), _cabi._ptr(out), C.byref(scan), C.byref(plan), C.byref(rep)))
+    if return_info:
+        return out, {"scan": {n: getattr(scan, n) for n, _ in scan._fields_}, "plan": plan.as_dict(),
+                     "report": rep.as_dict()}
+    return out
+
+
 def ms2dirty(uvw, freq, ms, wgt=None, npix_x=0, npix_y=0, pixsize_x=0.0, pixsize_y=0.0, nu=0, nv=0,
              epsilon=1e-4, do_wstacking=False, nthreads=1, verbosity=0, mask=None,
              double_precision_accumulation=False, *, device: int = -1, return_info: bool = False, w_slab=None):

@@ -245,3 +245,43 @@ def test_reorder_app_runs_in_process(T, tmp_path):
                                         reader_factory=lambda path: reader)
     assert out.is_dir() and paths
     assert_all_visibilities_accounted_for(reader, paths)
+
+
+# ---- gridding straight from the reordered tiles -------------------------------------------------
+
+@pytest.mark.gpu
+def test_dirty_image_from_tiles_equals_the_image_from_the_rows(T, tmp_path):
+    """reorder_by_uvw_tile -> tile chunk files -> invert_tiles: the tiles are gridded in their own (jagged) layout
+    and give the image of the original rows (unit weights, no flags) and the DFT's."""
+    from oracle import dft
+    from test_host_logic import make_reader
+    from ska_sdp_cip import invert_measurement_set
+    from ska_sdp_cip.invert import invert_tiles
+    from ska_sdp_cip.uvw_tiling import Tile, reorder_by_uvw_tile
+    nrow, nchan, npix = 2500, 24, 160
+    rng = np.random.default_rng(8)
+    uvw = rng.normal(size=(nrow, 3)) * np.array([900.0, 900.0, 120.0])
+    freqs = 1.2e9 + 2.5e6 * np.arange(nchan)
+    vis_i = (rng.normal(size=(nrow, nchan)) + 1j * rng.normal(size=(nrow, nchan))).astype(np.complex64)
+    vis4 = np.zeros((nrow, nchan, 4), dtype=np.complex64)
+    vis4[..., 0] = vis4[..., 3] = vis_i
+    from ska_sdp_cip.measurement_set import ArrayMeasurementSetReader
+    reader = ArrayMeasurementSetReader(uvw, freqs, vis4, np.zeros(vis4.shape, dtype=bool),
+                                       np.ones(vis4.shape, dtype=np.float32))
+    paths = reorder_by_uvw_tile(reader, (700.0, 700.0, 1400.0), tmp_path, None, num_time_intervals=3,
+                                max_vis_per_chunk=4000)
+    assert len(paths) > 10
+    px = 0.4 / (np.abs(uvw[:, :2]).max() * freqs.max() / 299792458.0)
+    asec = float(np.degrees(np.arcsin(px)) * 3600.0)
+    img_tiles = invert_tiles(paths, freqs, npix, asec)
+    img_rows = invert_measurement_set(reader, npix, asec)
+    assert img_tiles.shape == (npix, npix) and img_tiles.dtype == np.float32
+    assert dft.rel_rms(img_tiles, img_rows) <= 2e-6
+    px_used = float(np.sin(np.radians(asec / 3600.0)))
+    ref = dft.dft_dirty(uvw, freqs, vis_i, None, npix, npix, px_used, px_used) / vis_i.size
+    assert dft.rel_rms(img_tiles, ref) <= 1e-4
+    # Tile objects work like paths; an empty list gives an empty image
+    tiles = [Tile.load_npz(p) for p in paths[:5]]
+    part = invert_tiles(tiles, freqs, npix, asec)
+    assert np.isfinite(part).all() and np.abs(part).max() > 0
+    assert not invert_tiles([], freqs, npix, asec).any()
