@@ -10,7 +10,7 @@ from pathlib import Path
 
 HERE = Path(__file__).resolve().parent
 OUT = HERE / "_build" / "liboracle.so"
-SRCS = [HERE / "csrc" / "dft.c", HERE / "csrc" / "wgrid.c"]
+SRCS = [HERE / "csrc" / "dft.c", HERE / "csrc" / "wgrid.c", HERE / "csrc" / "wgrid_fast.c"]
 
 
 def build(force: bool = False) -> Path:
@@ -18,7 +18,7 @@ def build(force: bool = False) -> Path:
     if not force and OUT.exists() and all(OUT.stat().st_mtime >= d.stat().st_mtime for d in deps):
         return OUT
     OUT.parent.mkdir(exist_ok=True)
-    cmd = ["gcc", "-O3", "-fopenmp", "-fPIC", "-shared", "-std=gnu11", "-fno-math-errno",
+    cmd = ["gcc", "-O3", "-march=x86-64-v3", "-fopenmp", "-fPIC", "-shared", "-std=gnu11", "-fno-math-errno",
            "-o", str(OUT)] + [str(s) for s in SRCS] + ["-lm"]
     subprocess.run(cmd, check=True)
     return OUT

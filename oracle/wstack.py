@@ -135,3 +135,51 @@ def ms2dirty(uvw, freq, vis, wgt, nx, ny, px, py, epsilon=1e-4, *, fp64=False, s
     cv = kernel_ft(pl, (np.arange(ny) - ny // 2) / pl.nv)
     L.oracle_wg_correct(C.byref(cp), _p(x), _p(w), C.c_int(nq), _p(cu), _p(cv), _p(img))
     return (img, pl) if return_plan else img
+
+
+class _FastRec(C.Structure):
+    _fields_ = [("i0", C.c_int32), ("j0", C.c_int32), ("p0", C.c_int32), ("fu", C.c_float), ("fv", C.c_float),
+                ("fw", C.c_float), ("vr", C.c_float), ("vi", C.c_float)]
+
+
+def ms2dirty_fast(uvw, freq, vis, wgt, nx, ny, px, py, epsilon=1e-4, *, sigma=None, W=None, max_stack_bytes=12 << 30):
+    """The timed CPU baseline (csrc/wgrid_fast.c): float32 grids like ms2dirty's complex64 path, parallel binning,
+    kernel taps evaluated once per record for all its planes (planes resident in blocks of ``max_stack_bytes``),
+    pocketfft (scipy.fft) with all threads per plane, tabulated w correction.  Returns the float64 image."""
+    L = lib()
+    L.oracle_fast_bin.restype = C.c_int64
+    uvw = np.ascontiguousarray(uvw, dtype=np.float64)
+    freq = np.ascontiguousarray(freq, dtype=np.float64)
+    vis = np.ascontiguousarray(vis, dtype=np.complex64)
+    if wgt is not None:
+        wgt = np.ascontiguousarray(wgt, dtype=np.float32)
+    nrow, nchan = vis.shape
+    wmin, wmax, nact, _ = scan(uvw, freq, vis, wgt)
+    img = np.zeros((nx, ny), dtype=np.float64)
+    if nact == 0:
+        return img
+    pl = make_plan(nx, ny, px, py, epsilon, wmin, wmax, nact, fp64=False, sigma=sigma, W=W)
+    cp = _cplan(pl)
+    ntu, ntv = (pl.nu + 32) // 32 + 1, (pl.nv + 32) // 32 + 1
+    recs = np.empty(nrow * nchan, dtype=np.dtype(_FastRec))
+    offsets = np.zeros(ntu * ntv + 1, dtype=np.int64)
+    L.oracle_fast_bin(C.byref(cp), _p(uvw), C.c_int64(nrow), _p(freq), C.c_int64(nchan), _p(vis),
+                      _p(wgt) if wgt is not None else None, _p(recs), _p(offsets), C.c_int(ntu), C.c_int(ntv))
+    nthreads = os.cpu_count() or 1
+    plane_bytes = pl.nu * pl.nv * 8
+    block = max(1, min(pl.nplanes, int(max_stack_bytes // plane_bytes)))
+    for p_lo in range(0, pl.nplanes, block):
+        p_hi = min(pl.nplanes, p_lo + block)
+        stack = np.zeros((p_hi - p_lo, pl.nu, pl.nv), dtype=np.complex64)
+        L.oracle_fast_grid(C.byref(cp), _p(recs), _p(offsets), C.c_int(ntu), C.c_int(ntv), C.c_int(p_lo), C.c_int(p_hi),
+                           _p(stack))
+        for p in range(p_lo, p_hi):
+            F = scipy.fft.ifft2(stack[p - p_lo], norm="forward", workers=nthreads, overwrite_x=True)
+            L.oracle_fast_wscreen(C.byref(cp), _p(np.ascontiguousarray(F, dtype=np.complex64)), C.c_int(p), _p(img))
+    cu = kernel_ft(pl, (np.arange(nx) - nx // 2) / pl.nu)
+    cv = kernel_ft(pl, (np.arange(ny) - ny // 2) / pl.nv)
+    ntab = 4097
+    tab_x = np.linspace(pl.nm1_min, 0.0, ntab)
+    cw = kernel_ft(pl, (tab_x + pl.nshift) * pl.dw)
+    L.oracle_fast_correct(C.byref(cp), _p(cu), _p(cv), _p(cw), C.c_int(ntab), C.c_double(pl.nm1_min), _p(img))
+    return img

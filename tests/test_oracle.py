@@ -133,3 +133,15 @@ def test_torch_dft_checker_is_pinned_to_the_dft_oracle():
     assert dft.rel_rms(sub, dft.dft_dirty(uvw[::7], freq, vis[::7], wgt[::7], nx, ny, px, py, pixels=pix)) < 1e-12
     assert dft.rel_rms(dft_torch.dft_pixels(uvw, freq, vis, None, nx, ny, px, py, pix),
                        dft.dft_dirty(uvw, freq, vis, None, nx, ny, px, py, pixels=pix)) < 1e-12
+
+
+def test_fast_cpu_baseline_reproduces_the_dft():
+    """oracle/csrc/wgrid_fast.c (the timed CPU arm of bench.py) computes the same image as the float64 checker to
+    float32 accuracy, also when the plane stack is processed in blocks."""
+    from conftest import random_problem
+    uvw, freq, vis, wgt, nx, px = random_problem(nrow=3000, nchan=4, nx=192, wscale=400.0, seed=2, uvscale=30.0)
+    ref = dft.dft_dirty(uvw, freq, vis, wgt, nx, nx, px, px)
+    fast = wstack.ms2dirty_fast(uvw, freq, vis, wgt, nx, nx, px, px, 1e-4)
+    blocks = wstack.ms2dirty_fast(uvw, freq, vis, wgt, nx, nx, px, px, 1e-4, max_stack_bytes=3 * 8 * 288 * 288)
+    assert dft.rel_rms(fast, ref) < 1e-4 and dft.rel_rms(blocks, ref) < 1e-4
+    assert dft.rel_rms(fast, wstack.ms2dirty(uvw, freq, vis, wgt, nx, nx, px, px, 1e-4)) < 5e-6
