@@ -388,6 +388,30 @@ def run_b200(args):
         stage["w_sharding_phases_ms"] = {k: float(np.sum([r["phases_ms"].get(k, 0.0) for r in timed_reports
                                                            if "phases_ms" in r]) / args.steps) for k in phase_keys}
         stage["nplanes_of_rank0"] = [r["nplanes"] for r in timed_reports if "nplanes" in r][:4]
+    # ---- per-stage rooflines and the whole-invert fraction of SURVEY.md 8(d) --------------------------------
+    nrow_, nchan_ = uvw.shape[0], freq.shape[0]
+    nu_, nv_, npl_, sg_ = plan["nu"], plan["nv"], plan["nplanes"], plan["sigma"]
+    stage_bytes = {
+        "ms_scan": nvis * 4 + nrow_ * 24 + nchan_ * 8,                        # weights once, uvw, frequencies
+        "ms_bin": nvis * (12 + 16) + 2 * nrow_ * 24,                          # samples read once, 16-byte records written
+        "ms_zero": npl_ * nu_ * nv_ * 8,
+        "ms_grid": int(alg_bytes),
+        "ms_fft": npl_ * (2 * nu_ * nv_ * 8 + 4 * N * nu_ * 8 + N * N * 16),  # v pass, transpose-crop, u pass, w-screen
+        "ms_correct": 2 * N * N * 4,
+    }
+    roofline_stages = {k: {"ms": stage[k], "algorithmic_bytes": int(b),
+                           "frac": (b / (stage[k] * 1e-3) / 1e9 / peak) if stage[k] > 0 else None}
+                       for k, b in stage_bytes.items()}
+    b_in = nvis * 12 + nrow_ * 24 + nchan_ * 8
+    b_plane = (1 + 4 + 1 / sg_ ** 2) * nu_ * nv_ * 8 + 2 * N * N * 4
+    b_alg = b_in + npl_ * b_plane + 2 * N * N * 4
+    rate_dev = nvis * args.steps / ms_dev / 1e3 if world == 1 else None       # Mvis/s of one GPU's share
+    invert_roofline_mvis = nvis / (b_alg / (peak * 1e9)) / 1e6
+    sm_hz = 1e6 * float((clocks or {}).get("sm_mhz") or 1965.0)
+    grid_compute = {
+        "tflops_3xtf32": nvis * 3 * 2 * 1024 / (stage["ms_grid"] * 1e-3) / 1e12,       # 8 x 8 x 8 window x (re, im), three split products
+        "tensor_pipe_frac": nvis * 24.0 / (4 * 148 * sm_hz * stage["ms_grid"] * 1e-3),  # 24 mma.sync cycles per visibility and SMSP
+    }
     # ---- CPU baseline on a bounded sample -----------------------------------------------------
     cpu = None
     if not args.no_cpu and world == 1:  # rank 0 at N = 1 only
@@ -417,7 +441,12 @@ def run_b200(args):
         "gpu_launches": int(launches),
         "roofline": {"bound": "hbm", "kernel": "grid_warp_kernel<1, true, 1>", "achieved": achieved, "peak": peak,
                      "unit": "GB/s", "frac": achieved / peak, "traffic": ncu_traffic(), "peak_source": peak_kind,
-                     "ms_per_launch": ms_grid, "algorithmic_bytes": int(alg_bytes)},
+                     "ms_per_launch": ms_grid, "algorithmic_bytes": int(alg_bytes), "compute": grid_compute,
+                     "invert": {"B_alg_bytes": int(b_alg), "roofline_mvis_per_gpu": invert_roofline_mvis,
+                                "frac": (rate_dev / invert_roofline_mvis) if rate_dev else
+                                        (nvis / (ms_dev / args.steps * 1e-3) / 1e6 / invert_roofline_mvis),
+                                "formula": "SURVEY.md 8(d): B_in + nplanes * ((5 + 1/sigma^2) nu nv 8 + 2 nx ny 4) + 2 nx ny 4"}},
+        "roofline_stages": roofline_stages,
         "stage_ms": stage,
         "cpu_baseline": cpu,
         "clocks": clocks,

@@ -390,6 +390,7 @@ int max_windows_per_pass(const GridGeom& g) {
 }
 
 cip_status run_binning(cip_ctx* ctx, int slot, const DevInputs& in, const GridGeom& g, int fp64, bool want_items) {
+  NvtxRange nvtx("cip:binning");
   cudaStream_t st = ctx->stream;
   BinWork& w = ctx->work[slot];
   const int64_t nrow = in.nrow, nchan = in.nchan;

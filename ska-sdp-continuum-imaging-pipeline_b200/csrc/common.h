@@ -11,6 +11,7 @@
 
 #include <cuda_runtime.h>
 #include <cufft.h>
+#include <nvtx3/nvToolsExt.h>
 
 #include "cip.h"
 
@@ -67,6 +68,14 @@ double now_ms();  // host monotonic clock
       return CIP_EINVAL;               \
     }                                  \
   } while (0)
+
+// NVTX range around a stage (visible in Nsight timelines; a no-op when no tool is attached).
+struct NvtxRange {
+  explicit NvtxRange(const char* name) { nvtxRangePushA(name); }
+  ~NvtxRange() { nvtxRangePop(); }
+  NvtxRange(const NvtxRange&) = delete;
+  NvtxRange& operator=(const NvtxRange&) = delete;
+};
 
 // Makes the context's device current for the duration of an entry point and restores the caller's device.
 struct DeviceScope {

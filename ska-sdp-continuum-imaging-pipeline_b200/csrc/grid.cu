@@ -1106,6 +1106,7 @@ bool use_tc_gridder() {
 
 cip_status run_gridder(cip_ctx* ctx, int slot, cudaStream_t stream, const GridGeom& g, int fp64, int win_first, int win_last,
                        void* grid, int plane_base, int nslots) {
+  NvtxRange nvtx("cip:gridding");
   if (fp64) return launch<double>(ctx, slot, stream, g, win_first, win_last, grid, plane_base, nslots);
   return launch<float>(ctx, slot, stream, g, win_first, win_last, grid, plane_base, nslots);
 }

@@ -205,6 +205,7 @@ static cip_status fft_screen_transposed(cip_ctx* ctx, const cip_plan& pl, const 
 
 cip_status run_fft_screen(cip_ctx* ctx, const cip_plan& pl, void* grid, int plane_base, int nslots, void* image,
                           double* ms_fft, double* ms_wscreen) {
+  NvtxRange nvtx("cip:fft+wscreen");
   (void)ms_wscreen;
   if (grid == nullptr) {  // plans only
     if (getenv("CIP_FFT_2D")) return run_fft(ctx, nullptr, pl.nu, pl.nv, 0, pl.accumulate_fp64, pl.npix_y);
@@ -257,6 +258,7 @@ static double clenshaw(const std::vector<double>& c, double t) {
 }
 
 cip_status run_correct(cip_ctx* ctx, const cip_plan& pl, void* image, int row_begin, int row_end, double scale) {
+  NvtxRange nvtx("cip:correction");
   CIP_REQUIRE(row_begin >= 0 && row_end <= pl.npix_x && row_begin <= row_end, "bad row range [%d,%d)", row_begin, row_end);
   if (row_begin == row_end) return CIP_OK;
   const int nx = pl.npix_x, ny = pl.npix_y, W = pl.support;

@@ -401,6 +401,7 @@ extern "C" cip_status cip_correct_image(cip_ctx* ctx, const cip_plan* plan, void
 extern "C" cip_status cip_invert(cip_ctx* ctx, const cip_invert_args* args, void* dirty_out, cip_scan_result* scan_out,
                                  cip_plan* plan_out, cip_report* report) {
   CIP_REQUIRE(ctx && dirty_out, "NULL argument");
+  NvtxRange nvtx("cip_invert");
   CIP_TRY(validate_args(args));
   CIP_ENTER_DEVICE(ctx);
   if (report) memset(report, 0, sizeof(*report));

@@ -193,6 +193,7 @@ cip_status run_w_histogram(cip_ctx* ctx, const DevInputs& in, double wmin, doubl
 }
 
 cip_status run_scan(cip_ctx* ctx, const DevInputs& in, int do_wstacking, cip_scan_result* out) {
+  NvtxRange nvtx("cip:scan");
   CIP_TRY(ctx->scan_out.ensure(sizeof(ScanOut)));
   cudaStream_t st = ctx->stream;
   scan_init_kernel<<<1, 1, 0, st>>>(ctx->scan_out.as<ScanOut>());
