@@ -366,6 +366,22 @@ def run_b200(args):
     if world == 1:
         step_host(with_report=True)  # untimed: stage breakdown of one e2e step, for information
     h2d = int(n_vis_np.nbytes + n_wgt_np.nbytes + uvw.nbytes + freq.nbytes)
+    # floor of the e2e step: the same pinned buffers copied host -> device with nothing else going on (all ranks at
+    # once: they share the host's memory and PCIe root complexes)
+    barrier()
+    f0, f1 = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
+    f0.record()
+    for _ in range(e2e_steps):
+        d_vis.copy_(h_vis, non_blocking=True)
+        d_wgt.copy_(h_wgt, non_blocking=True)
+        d_uvw.copy_(h_uvw, non_blocking=True)
+    f1.record()
+    torch.cuda.synchronize()
+    h2d_floor_ms = f0.elapsed_time(f1) / e2e_steps
+    if world > 1:
+        t = torch.tensor([h2d_floor_ms], dtype=torch.float64, device=dev)
+        dist.all_reduce(t, op=dist.ReduceOp.MAX)
+        h2d_floor_ms = float(t.item())
     del h_vis, h_wgt, n_vis_np, n_wgt_np
     d2h = int(N * N * 4)
 
@@ -434,7 +450,8 @@ def run_b200(args):
                                 + ", NCCL reduce-scatter + all-gather of the dirty image")},
         "parity": parity,
         "e2e": {"value": total_vis * e2e_steps / ms_e2e / 1e3, "unit": UNIT, "h2d_bytes_per_step": h2d,
-                "d2h_bytes_per_step": d2h, "steps": e2e_steps,
+                "d2h_bytes_per_step": d2h, "steps": e2e_steps, "ms_per_step": ms_e2e / e2e_steps,
+                "h2d_floor_ms": h2d_floor_ms, "h2d_floor_GBps_per_gpu": h2d / h2d_floor_ms / 1e6,
                 "stage_ms": {k: float(np.mean([r[k] for r in host_reports])) for k in
                              ("ms_h2d", "ms_scan", "ms_bin", "ms_grid", "ms_fft", "ms_d2h", "ms_total")}
                 if host_reports else None},
