@@ -390,16 +390,13 @@ __global__ void __launch_bounds__(kGridThreads) grid_kernel(JobList jl, const Re
 // warps, hence no barriers besides __syncwarp.  Sub-grid, fold and epilogue are those of grid_kernel.
 constexpr int kARow = 64 * 4 + 16;  // bytes per visibility of the A stage; the pad makes the producer's
 constexpr int kBRow = 16 * 4 + 16;  // 128-bit stores (one row per lane) bank-conflict free
-constexpr int kWarpSubGridBytes = 16 * 4 * kSub * kSub;
 // The tensor-path kernels stage the FACTORS ku[8], kv[8] instead of their 64 products (80 instead of 272 bytes per
 // visibility; the consumer multiplies the 16 products of its fragment itself -- the FMA pipe has room once the
 // window update is on the tensor pipe, the shared-memory pipe does not).  Factor row, in words: ku[0..3] at 0..3,
 // kv[0..7] at 4..11, ku[4..7] at 16..19 -- the same bank argument as for the B row.
 constexpr int kKRow = 80;
 constexpr int warp_stage_bytes(bool fact) { return kBatch * ((fact ? kKRow : kARow) + kBRow + 4); }
-constexpr int warp_smem_bytes(int nw, bool direct, bool fact) {
-  return (direct ? 0 : kWarpSubGridBytes) + nw * warp_stage_bytes(fact);
-}
+constexpr int warp_smem_bytes(bool fact) { return warp_stage_bytes(fact); }
 
 template <int OFF>
 __device__ __forceinline__ float4 lds_f4(uint32_t addr) {
@@ -455,8 +452,7 @@ __device__ __forceinline__ u64 lds_u1(uint32_t addr) {
 // A loads cost 2 wavefronts each and the two B loads 1 each: 6 per visibility.
 // Where a register window is folded to (see WarpAcc::fold).
 struct FoldSink {
-  float4* sg;                                              // sub-grid in shared memory (modes 0, 1)
-  float* grid;                                             // global plane stack (mode 2)
+  float* grid;                                             // global plane stack
   int nu, nv, su0, sv0, P0, nplanes, plane_base, nslots;   // su0, sv0 already reduced to [0, nu), [0, nv)
 };
 __device__ __forceinline__ void red_add_v2(float* addr, u64 v) {
@@ -545,16 +541,7 @@ struct WarpAcc {
   // Products of this lane's fragment rows for the visibilities pq and pq + 4 of a group: pam = factor row of
   // visibility pq, kuoff = byte offset of ku[a] in it.  The products are born in the registers the A fragments
   // need (aligned quads), so nothing is moved.
-  __device__ __forceinline__ static void load_products(uint32_t pam, uint32_t kuoff, float (&pv)[8], float (&qv)[8]) {
-    const float kup = lds_f32(pam + kuoff), kuq = lds_f32(pam + kuoff + 4 * kKRow);
-    const float4 p0 = lds_f4<16>(pam), p1 = lds_f4<32>(pam);
-    const float4 q0 = lds_f4<4 * kKRow + 16>(pam), q1 = lds_f4<4 * kKRow + 32>(pam);
-    pv[0] = kup * p0.x; pv[1] = kup * p0.y; pv[2] = kup * p0.z; pv[3] = kup * p0.w;
-    pv[4] = kup * p1.x; pv[5] = kup * p1.y; pv[6] = kup * p1.z; pv[7] = kup * p1.w;
-    qv[0] = kuq * q0.x; qv[1] = kuq * q0.y; qv[2] = kuq * q0.z; qv[3] = kuq * q0.w;
-    qv[4] = kuq * q1.x; qv[5] = kuq * q1.y; qv[6] = kuq * q1.z; qv[7] = kuq * q1.w;
-  }
-  // Pair form of load_products: (v = 2m, 2m+1) of the visibilities pq (pp) and pq + 4 (qq) as packed float32 pairs
+  // (v = 2m, 2m+1) of the visibilities pq (pp) and pq + 4 (qq) as packed float32 pairs
   __device__ __forceinline__ static void load_product_pairs(uint32_t pam, uint32_t kuoff, u64 (&pp)[4], u64 (&qq)[4]) {
     const u64 kup = dup2(lds_f32(pam + kuoff)), kuq = dup2(lds_f32(pam + kuoff + 4 * kKRow));
     const float4 p0 = lds_f4<16>(pam), p1 = lds_f4<32>(pam);
@@ -612,53 +599,7 @@ struct WarpAcc {
         }
     }
   }
-  // Same update with the window accumulated inside the tensor core (no float32 additions): term-major order,
-  // so that the three instructions of a tile are 8 instructions apart.  The tensor core truncates its
-  // accumulator: measured against the FADD variant with tests/accuracy_modes.py.
-  __device__ __forceinline__ void update_mma_direct(uint32_t pam, uint32_t kuoff, uint32_t pbm0, uint32_t pbm1) {
-    float pv[8], qv[8];
-    load_products(pam, kuoff, pv, qv);
-    uint32_t bh[2][2], bl[2][2];
-    tf32_split(lds_f32(pbm0), bh[0][0], bl[0][0]);
-    tf32_split(lds_f32(pbm0 + 4 * kBRow), bh[0][1], bl[0][1]);
-    tf32_split(lds_f32(pbm1), bh[1][0], bl[1][0]);
-    tf32_split(lds_f32(pbm1 + 4 * kBRow), bh[1][1], bl[1][1]);
-    uint32_t ah[4][4], al[4][4];
-#pragma unroll
-    for (int mt = 0; mt < 4; ++mt) {
-      tf32_split(pv[2 * mt], ah[mt][0], al[mt][0]);
-      tf32_split(pv[2 * mt + 1], ah[mt][1], al[mt][1]);
-      tf32_split(qv[2 * mt], ah[mt][2], al[mt][2]);
-      tf32_split(qv[2 * mt + 1], ah[mt][3], al[mt][3]);
-    }
-    float d[4][2][4];
-#pragma unroll
-    for (int mt = 0; mt < 4; ++mt)
-#pragma unroll
-      for (int nt = 0; nt < 2; ++nt) {
-        const float2 x = unpack2(c[2 * mt][nt]), y = unpack2(c[2 * mt + 1][nt]);
-        d[mt][nt][0] = x.x; d[mt][nt][1] = x.y; d[mt][nt][2] = y.x; d[mt][nt][3] = y.y;
-      }
-#pragma unroll
-    for (int term = 0; term < 3; ++term)
-#pragma unroll
-      for (int mt = 0; mt < 4; ++mt)
-#pragma unroll
-        for (int nt = 0; nt < 2; ++nt) {
-          if (term == 0) mma_tf32(d[mt][nt], al[mt], bh[nt][0], bh[nt][1]);
-          else if (term == 1) mma_tf32(d[mt][nt], ah[mt], bl[nt][0], bl[nt][1]);
-          else mma_tf32(d[mt][nt], ah[mt], bh[nt][0], bh[nt][1]);
-        }
-#pragma unroll
-    for (int mt = 0; mt < 4; ++mt)
-#pragma unroll
-      for (int nt = 0; nt < 2; ++nt) {
-        c[2 * mt][nt] = pack2(d[mt][nt][0], d[mt][nt][1]);
-        c[2 * mt + 1][nt] = pack2(d[mt][nt][2], d[mt][nt][3]);
-      }
-  }
-  // sub-grid cell = float4 {re(2pp), im(2pp), re(2pp+1), im(2pp+1)} for plane pair pp = pq: one float4
-  // read-modify-write per owned cell (the lane owns row i, all 8 v residues of the window)
+  // the lane owns row i of the window (all 8 v residues) for the plane pair pq
   template <int T0>
   __device__ __forceinline__ void fold_pairs(const FoldSink& k, float* row0, float* row1, bool ok0, bool ok1, int wj) {
 #pragma unroll
@@ -687,42 +628,23 @@ struct WarpAcc {
       }
     }
   }
-  // MODE 0: plain read-modify-write of the CTA's sub-grid; 1: shared-memory reductions (several warps fold into
-  // one sub-grid); 2: no sub-grid, the window goes straight to the global plane stack with 8-byte reductions.
-  template <int MODE>
+  // The window goes straight to the global plane stack (no sub-grid in shared memory: the records are sorted by
+  // window, so a warp leaves a window about once per lattice position and item; measured 10.8 -> 10.0 ms in round 1
+  // against a shared sub-grid, which halves the resident warps).
   __device__ __forceinline__ void fold(const FoldSink& k, int i, int wj, int pq) {
-    if (MODE == 2) {
-      int gi = k.su0 + i;
-      gi -= gi >= k.nu ? k.nu : 0;
-      const int plane = k.P0 + 2 * pq, slot = plane - k.plane_base;
-      const bool ok0 = plane < k.nplanes && slot >= 0 && slot < k.nslots;
-      const bool ok1 = plane + 1 < k.nplanes && slot + 1 >= 0 && slot + 1 < k.nslots;
-      float* row0 = k.grid + 2 * (((int64_t)slot * k.nu + gi) * k.nv);
-      float* row1 = row0 + 2 * (int64_t)k.nu * k.nv;
-      // Residue t sits at window column (t - wj) & 7, i.e. global column parity = parity(sv0 + t): the
-      // residue pairs (t, t+1) that start on an even global column are 16-byte aligned neighbours unless the
-      // window wraps between them, so most of the window goes out as 128-bit reductions (one sector per
-      // request lane instead of two 8-byte requests to the same sector).
-      if (k.sv0 & 1) fold_pairs<1>(k, row0, row1, ok0, ok1, wj);
-      else fold_pairs<0>(k, row0, row1, ok0, ok1, wj);
-    } else {
-      float4* row = k.sg + (pq * kSub + i) * kSub;
-#pragma unroll
-      for (int t = 0; t < 8; ++t) {
-        float4* p = row + wj + ((t - wj) & 7);
-        const float2 x = unpack2(c[t][0]), y = unpack2(c[t][1]);
-        if (MODE == 1) {
-          const uint32_t ad = smem_u32(p);
-          asm volatile("red.shared.add.f32 [%0], %1;\n\tred.shared.add.f32 [%0+4], %2;\n\t"
-                       "red.shared.add.f32 [%0+8], %3;\n\tred.shared.add.f32 [%0+12], %4;"
-                       ::"r"(ad), "f"(x.x), "f"(x.y), "f"(y.x), "f"(y.y) : "memory");
-        } else {
-          float4 v = *p;
-          v.x += x.x; v.y += x.y; v.z += y.x; v.w += y.y;
-          *p = v;
-        }
-      }
-    }
+    int gi = k.su0 + i;
+    gi -= gi >= k.nu ? k.nu : 0;
+    const int plane = k.P0 + 2 * pq, slot = plane - k.plane_base;
+    const bool ok0 = plane < k.nplanes && slot >= 0 && slot < k.nslots;
+    const bool ok1 = plane + 1 < k.nplanes && slot + 1 >= 0 && slot + 1 < k.nslots;
+    float* row0 = k.grid + 2 * (((int64_t)slot * k.nu + gi) * k.nv);
+    float* row1 = row0 + 2 * (int64_t)k.nu * k.nv;
+    // Residue t sits at window column (t - wj) & 7, i.e. global column parity = parity(sv0 + t): the
+    // residue pairs (t, t+1) that start on an even global column are 16-byte aligned neighbours unless the
+    // window wraps between them, so most of the window goes out as 128-bit reductions (one sector per
+    // request lane instead of two 8-byte requests to the same sector).
+    if (k.sv0 & 1) fold_pairs<1>(k, row0, row1, ok0, ok1, wj);
+    else fold_pairs<0>(k, row0, row1, ok0, ok1, wj);
     clear();
   }
 };
@@ -736,67 +658,55 @@ struct WarpCells {
   }
 };
 
-template <int U, bool CHECK, int MODE>
+template <int U, bool CHECK>
 __device__ __forceinline__ void warp_consume1(uint32_t pa, uint32_t pb, uint32_t pb1, uint32_t porg, uint32_t moved8, const WarpOps& cur,
                                               WarpOps& nxt, WarpAcc& acc, const FoldSink& sg, WarpCells& cells, int a, int pq) {
   nxt = warp_load<U + 1, false>(pa, 0u, pb, pb1);
   if (CHECK && ((moved8 >> U) & 1u)) {
-    acc.template fold<MODE>(sg, cells.i, cells.wj, pq);
+    acc.fold(sg, cells.i, cells.wj, pq);
     cells.set(lds_u32(porg + 4 * U), a);
   }
   acc.update(cur);
 }
-template <bool CHECK, int MODE>
+template <bool CHECK>
 __device__ __forceinline__ void warp_consume8(uint32_t pa, uint32_t pb, uint32_t pb1, uint32_t porg, uint32_t moved8, WarpOps& x, WarpAcc& acc,
                                               const FoldSink& sg, WarpCells& cells, int a, int pq) {
   WarpOps y;
-  warp_consume1<0, CHECK, MODE>(pa, pb, pb1, porg, moved8, x, y, acc, sg, cells, a, pq);
-  warp_consume1<1, CHECK, MODE>(pa, pb, pb1, porg, moved8, y, x, acc, sg, cells, a, pq);
-  warp_consume1<2, CHECK, MODE>(pa, pb, pb1, porg, moved8, x, y, acc, sg, cells, a, pq);
-  warp_consume1<3, CHECK, MODE>(pa, pb, pb1, porg, moved8, y, x, acc, sg, cells, a, pq);
-  warp_consume1<4, CHECK, MODE>(pa, pb, pb1, porg, moved8, x, y, acc, sg, cells, a, pq);
-  warp_consume1<5, CHECK, MODE>(pa, pb, pb1, porg, moved8, y, x, acc, sg, cells, a, pq);
-  warp_consume1<6, CHECK, MODE>(pa, pb, pb1, porg, moved8, x, y, acc, sg, cells, a, pq);
-  warp_consume1<7, CHECK, MODE>(pa, pb, pb1, porg, moved8, y, x, acc, sg, cells, a, pq);
+  warp_consume1<0, CHECK>(pa, pb, pb1, porg, moved8, x, y, acc, sg, cells, a, pq);
+  warp_consume1<1, CHECK>(pa, pb, pb1, porg, moved8, y, x, acc, sg, cells, a, pq);
+  warp_consume1<2, CHECK>(pa, pb, pb1, porg, moved8, x, y, acc, sg, cells, a, pq);
+  warp_consume1<3, CHECK>(pa, pb, pb1, porg, moved8, y, x, acc, sg, cells, a, pq);
+  warp_consume1<4, CHECK>(pa, pb, pb1, porg, moved8, x, y, acc, sg, cells, a, pq);
+  warp_consume1<5, CHECK>(pa, pb, pb1, porg, moved8, y, x, acc, sg, cells, a, pq);
+  warp_consume1<6, CHECK>(pa, pb, pb1, porg, moved8, x, y, acc, sg, cells, a, pq);
+  warp_consume1<7, CHECK>(pa, pb, pb1, porg, moved8, y, x, acc, sg, cells, a, pq);
 }
 
-// NW warps per CTA share the item and its sub-grid: warp w takes the w-th contiguous share of the
-// batches (the records are sorted by register window, so each warp sees only a few windows) and has a
-// private operand stage; folds into the shared sub-grid are shared-memory reductions when NW > 1.
-// DIRECT: no sub-grid at all -- every register window is added to the global plane stack when the warp
-// leaves it (the records are sorted by window, so that happens ~ once per lattice position and item).  This
-// trades ~4x more L2 reductions for 14.4 KB of shared memory per warp, i.e. twice the resident warps.
-template <int NW, bool DIRECT, int MMA>
+// One warp = one work item.  MMA = 1: tensor-core tiles for the groups that stay inside one window; 0: FFMA2
+// rank-1 updates throughout (A/B reference).
+template <int MMA>
 __device__ __forceinline__ void grid_warp_item(const Item& item, const RecP* __restrict__ recs, const GridGeom& g,
                                                float* __restrict__ grid, int plane_base, int nslots) {
-  constexpr int MODE = DIRECT ? 2 : (NW > 1 ? 1 : 0);
-  constexpr int kSubBytes = DIRECT ? 0 : kWarpSubGridBytes;
   extern __shared__ __align__(16) unsigned char smem_raw[];
-  float4* sg = reinterpret_cast<float4*>(smem_raw);
-  const int lane = threadIdx.x & 31, warp = threadIdx.x >> 5;
+  const int lane = threadIdx.x & 31;
   constexpr bool FACT = MMA != 0;
   constexpr int ROW = FACT ? kKRow : kARow;
-  const uint32_t sA = smem_u32(smem_raw + kSubBytes + warp * warp_stage_bytes(FACT));
+  const uint32_t sA = smem_u32(smem_raw);
   const uint32_t sB = sA + kBatch * ROW;
   const uint32_t sOrg = sB + kBatch * kBRow;
 
   const int nrec = item.nrec;
-  const int nb_all = (nrec + kBatch - 1) / kBatch;
-  const int b_begin = warp * nb_all / NW, b_end = (warp + 1) * nb_all / NW;
+  const int b_begin = 0, b_end = (nrec + kBatch - 1) / kBatch;
   const int64_t base = item.rec_begin;
 
-  bool cur_valid = b_begin * kBatch + lane < nrec;
-  RecP cur = load_recp(recs, base + b_begin * kBatch + lane, cur_valid);
-  if (!DIRECT)
-    for (int t = threadIdx.x; t < 4 * kSub * kSub; t += 32 * NW) sg[t] = make_float4(0.f, 0.f, 0.f, 0.f);
+  bool cur_valid = lane < nrec;
+  RecP cur = load_recp(recs, base + lane, cur_valid);
   const int P0 = item.win * g.win_step;
   int su0 = item.tu * kTile - kHalo + g.nu / 2;  // shifted -> FFT order: (s + nu/2) mod nu
   int sv0 = item.tv * kTile - kHalo + g.nv / 2;
-  if (DIRECT) {  // reduced once here; su0 + i < 2 nu
-    su0 -= su0 >= g.nu ? g.nu : 0;
-    sv0 -= sv0 >= g.nv ? g.nv : 0;
-  }
-  const FoldSink sink{sg, grid, g.nu, g.nv, su0, sv0, P0, g.nplanes, plane_base, nslots};
+  su0 -= su0 >= g.nu ? g.nu : 0;  // reduced once here; su0 + i < 2 nu
+  sv0 -= sv0 >= g.nv ? g.nv : 0;
+  const FoldSink sink{grid, g.nu, g.nv, su0, sv0, P0, g.nplanes, plane_base, nslots};
 
   // producer constants
   const int W = g.W;
@@ -819,8 +729,7 @@ __device__ __forceinline__ void grid_warp_item(const Item& item, const RecP* __r
   acc.clear();
   WarpCells cells;
   cells.set(0u, a);
-  if (NW > 1) __syncthreads();
-  else __syncwarp();
+  __syncwarp();
 
   for (int b = b_begin; b < b_end; ++b) {
     const int kn = (b + 1) * kBatch + lane;
@@ -886,9 +795,8 @@ __device__ __forceinline__ void grid_warp_item(const Item& item, const RecP* __r
         // k0 + 8 are prefetched at the end of a group; past the last group that reads the rows after the
         // stage (still inside the CTA's shared memory: kSlack), which are discarded.
         if (m8 == 0) {
-          if (MMA == 2) acc.update_mma_direct(pam0 + k0 * kKRow, kuoff, pbm00 + k0 * kBRow, pbm10 + k0 * kBRow);
-          else if (MMA) acc.update_mma(pam0 + k0 * kKRow, kuoff, pbm00 + k0 * kBRow, pbm10 + k0 * kBRow);
-          else warp_consume8<false, MODE>(pa, pb, pb1, porg, m8, x, acc, sink, cells, a, pq);
+          if (MMA) acc.update_mma(pam0 + k0 * kKRow, kuoff, pbm00 + k0 * kBRow, pbm10 + k0 * kBRow);
+          else warp_consume8<false>(pa, pb, pb1, porg, m8, x, acc, sink, cells, a, pq);
         } else {
           if (MMA) x = warp_load<0, FACT>(pa, pkv, pb, pb1);
           // a window moves inside this group (rare): rolled loop, so that the fold is not inlined eight times
@@ -897,7 +805,7 @@ __device__ __forceinline__ void grid_warp_item(const Item& item, const RecP* __r
           for (int u = 0; u < 8; ++u) {
             const WarpOps nxt = warp_load<1, FACT>(pa + u * ROW, pkv + u * ROW, pb + u * kBRow, pb1 + u * kBRow);
             if ((m8 >> u) & 1u) {
-              acc.template fold<MODE>(sink, cells.i, cells.wj, pq);
+              acc.fold(sink, cells.i, cells.wj, pq);
               cells.set(lds_u32(porg + 4 * u), a);
             }
             acc.update(x);
@@ -910,43 +818,7 @@ __device__ __forceinline__ void grid_warp_item(const Item& item, const RecP* __r
     cur = nxt;
     cur_valid = nxt_valid;
   }
-  acc.template fold<MODE>(sink, cells.i, cells.wj, pq);
-  if (DIRECT) return;
-  if (NW > 1) __syncthreads();
-  else __syncwarp();
-
-  // ---------------- sub-grid -> global plane stack (as in grid_kernel<float>) ----------------
-  constexpr int kPairs = (kSub + 1) / 2;
-  const int odd = sv0 & 1;
-  for (int t = threadIdx.x; t < 4 * kSub * kPairs; t += 32 * NW) {
-    const int jp = t % kPairs, q = t / kPairs;
-    const int i = q % kSub, pp = q / kSub;
-    const int j = 2 * jp - odd;
-    const bool ok0 = j >= 0, ok1 = j + 1 < kSub;
-    const float4 c0 = ok0 ? sg[(pp * kSub + i) * kSub + j] : make_float4(0.f, 0.f, 0.f, 0.f);
-    const float4 c1 = ok1 ? sg[(pp * kSub + i) * kSub + j + 1] : make_float4(0.f, 0.f, 0.f, 0.f);
-    const int gi = (su0 + i) % g.nu;
-    const int gj = (sv0 + j + g.nv) % g.nv;
-#pragma unroll
-    for (int h = 0; h < 2; ++h) {
-      const int plane = P0 + 2 * pp + h;
-      if (plane >= g.nplanes) continue;
-      const int slot = plane - plane_base;
-      if (slot < 0 || slot >= nslots) continue;
-      const float va = h ? c0.z : c0.x, vb = h ? c0.w : c0.y, vc = h ? c1.z : c1.x, vd = h ? c1.w : c1.y;
-      if (va == 0.f && vb == 0.f && vc == 0.f && vd == 0.f) continue;
-      float* dst = grid + 2 * (((int64_t)slot * g.nu + gi) * g.nv + gj);
-      if (ok0 && ok1) {
-        red_add_v4(dst, va, vb, vc, vd);
-      } else if (ok0) {
-        atomicAdd(dst, va);
-        atomicAdd(dst + 1, vb);
-      } else {
-        atomicAdd(dst + 2, vc);
-        atomicAdd(dst + 3, vd);
-      }
-    }
-  }
+  acc.fold(sink, cells.i, cells.wj, pq);
 }
 
 // The work items of the pass (bin.cu): the list of their first jobs; an item runs up to the next job that starts one.
@@ -958,10 +830,9 @@ struct ItemList {
   int win_first, win_last;
 };
 
-template <int NW, bool DIRECT, int MMA>
-__global__ void __launch_bounds__(32 * NW, DIRECT ? (MMA == 2 ? 24 : 20) : 1) grid_warp_kernel(ItemList il, const RecP* __restrict__ recs, GridGeom g,
+template <int MMA>
+__global__ void __launch_bounds__(32, 20) grid_warp_kernel(ItemList il, const RecP* __restrict__ recs, GridGeom g,
                                                             float* __restrict__ grid, int plane_base, int nslots) {
-  static_assert(NW == 1, "one warp per CTA");
   if (il.hdr->overflow) return;
   const uint32_t n = il.counters[0], njobs = il.hdr->njobs;
   const int lane = threadIdx.x & 31;
@@ -992,7 +863,7 @@ __global__ void __launch_bounds__(32 * NW, DIRECT ? (MMA == 2 ? 24 : 20) : 1) gr
     item.tu = a.tu;
     item.tv = a.tv;
     item.win = a.win;
-    grid_warp_item<NW, DIRECT, MMA>(item, recs, g, grid, plane_base, nslots);
+    grid_warp_item<MMA>(item, recs, g, grid, plane_base, nslots);
     __syncwarp();
   }
 }
@@ -1052,8 +923,8 @@ namespace {
 template <int MMA>
 cip_status launch_warp(cip_ctx* ctx, cudaStream_t stream, const ItemList& jl, const RecP* recs, const GridGeom& g, float* grid,
                        int plane_base, int nslots) {
-  auto kern = grid_warp_kernel<1, true, MMA>;
-  constexpr int smem = warp_smem_bytes(1, true, MMA != 0);
+  auto kern = grid_warp_kernel<MMA>;
+  constexpr int smem = warp_smem_bytes(MMA != 0);
   CIP_CHECK_CUDA(cudaFuncSetAttribute(kern, cudaFuncAttributeMaxDynamicSharedMemorySize, smem));
   CIP_CHECK_CUDA(cudaFuncSetAttribute(kern, cudaFuncAttributePreferredSharedMemoryCarveout, (int)cudaSharedmemCarveoutMaxShared));
   kern<<<ctx->sm_count * 20, 32, smem, stream>>>(jl, recs, g, grid, plane_base, nslots);

@@ -113,11 +113,6 @@ __device__ __forceinline__ void tmem_ld32(uint32_t taddr, uint32_t (&v)[32]) {
       : "memory");
 }
 __device__ __forceinline__ void sts32(uint32_t addr, float v) { asm volatile("st.shared.f32 [%0], %1;" ::"r"(addr), "f"(v) : "memory"); }
-__device__ __forceinline__ float4 lds128(uint32_t addr) {
-  float4 v;
-  asm volatile("ld.shared.v4.f32 {%0, %1, %2, %3}, [%4];" : "=f"(v.x), "=f"(v.y), "=f"(v.z), "=f"(v.w) : "r"(addr));
-  return v;
-}
 // ES tap exp(beta_w (sqrt(1 - x^2) - 1)), 0 where 1 - x^2 <= 0; pure PTX so that the mask stays a select
 __device__ __forceinline__ float es_tap(float x, float bw2) {
   float e;
@@ -285,9 +280,9 @@ __global__ void __launch_bounds__(kTcThreads, 1) grid_tc_kernel(const Job* __res
       timed_wait(smem_u32(&sh->f_full[s]), ph, t_wait0);
       const long long tb0 = PROF ? clock64() : 0;
       uint32_t a[32];
-#pragma unroll
       const float4* fu4 = reinterpret_cast<const float4*>(smem + s * kStageBytes + fu_off);
       const float4* fv4 = reinterpret_cast<const float4*>(smem + s * kStageBytes + fv_off);
+#pragma unroll
       for (int q = 0; q < 8; ++q) {
         float4 x, y;
         if (PROF && (dbg & 8)) {
