@@ -230,7 +230,8 @@ def run_b200(args):
     import torch
     import torch.distributed as dist
     from ska_sdp_cip import _cabi, synthetic as S, wgridder
-    from ska_sdp_cip.invert import StokesIGridderInput, accumulate_shards, accumulate_shards_by_w, reduce_and_correct
+    from ska_sdp_cip.invert import (StokesIGridderInput, accumulate_shards, accumulate_shards_by_w, image_to_host,
+                                    reduce_and_correct)
 
     world = int(os.environ.get("WORLD_SIZE", "1"))
     rank = int(os.environ.get("RANK", "0"))
@@ -357,7 +358,7 @@ def run_b200(args):
         shard = StokesIGridderInput(freq_p, None, uvw_p, n_vis_np, n_wgt_np)
         acc = accumulate_shards_by_w if args.sharding == "w" else accumulate_shards
         img, plan_, sumw = acc([shard], N, px, epsilon=cfg.epsilon)
-        return reduce_and_correct(img, plan_, sumw, normalise=False).cpu().numpy()
+        return image_to_host(reduce_and_correct(img, plan_, sumw, normalise=False))
 
     e2e_steps = max(1, min(args.steps, 3))
     step_host()

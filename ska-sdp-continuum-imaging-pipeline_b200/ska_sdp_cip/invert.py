@@ -289,30 +289,46 @@ def accumulate_shards(shards: Sequence[StokesIGridderInput], num_pixels: int, pi
                         device=dev)
     torch.cuda.current_stream(dev).synchronize()
     if nactive:
-        for rep in _grid_shards(ctx, [a for a, _sh, _w in args_list], plan, image):
-            if reports is not None:
-                reports.append(rep)
+        for rep in _grid_shards(ctx, [a for a, _sh, _w in args_list], plan, image, reports is not None):
+            reports.append(rep)
     return image, plan, sumw
 
 
-def _grid_shards(ctx: Context, args: list, plan: Plan, image) -> list[dict]:
+def _grid_shards(ctx: Context, args: list, plan: Plan, image, want_reports: bool = True) -> list[dict]:
     """Add the shards' uncorrected dirty images to ``image``.  Device-resident shards go through ONE call
     (cip_grid_accumulate_many: one plane stack, one set of FFTs for all of them); host shards one by one, each
-    streamed in behind its own binning and gridding."""
+    streamed in behind its own binning and gridding.  Stage reports are only requested when wanted: timing the
+    stages of a streamed host shard makes the host wait for every chunk, i.e. gives up the overlap of upload and
+    compute."""
     L = lib()
     reports = []
     if len(args) > 1 and all(a.memspace == 1 for a in args):
         arr = (_cabi.InvertArgs * len(args))(*args)
         rep = Report()
         with ctx.lock:
-            check(L.cip_grid_accumulate_many(ctx.handle, arr, len(args), C.byref(plan), image.data_ptr(), C.byref(rep)))
-        return [rep.as_dict()]
+            check(L.cip_grid_accumulate_many(ctx.handle, arr, len(args), C.byref(plan), image.data_ptr(),
+                                             C.byref(rep) if want_reports else None))
+        return [rep.as_dict()] if want_reports else []
     for a in args:
         rep = Report()
         with ctx.lock:
-            check(L.cip_grid_accumulate(ctx.handle, C.byref(a), C.byref(plan), image.data_ptr(), C.byref(rep)))
-        reports.append(rep.as_dict())
+            check(L.cip_grid_accumulate(ctx.handle, C.byref(a), C.byref(plan), image.data_ptr(),
+                                        C.byref(rep) if want_reports else None))
+        if want_reports:
+            reports.append(rep.as_dict())
     return reports
+
+
+def image_to_host(image) -> NDArray:
+    """Device image -> numpy array through pinned memory (torch's caching pinned allocator keeps the block):
+    a pageable read-back of a 16384^2 image runs at a fifth of the PCIe rate."""
+    torch = _torch()
+    if image.numel() * image.element_size() < (1 << 20):
+        return image.cpu().numpy()
+    host = torch.empty(image.shape, dtype=image.dtype, pin_memory=True)
+    host.copy_(image, non_blocking=True)
+    torch.cuda.current_stream(image.device).synchronize()
+    return host.numpy()
 
 
 # ---- the same, sharded by |w| (SURVEY.md 8e option 3; BASELINE.json configs[4]) --------------------------------
@@ -505,9 +521,8 @@ def accumulate_shards_by_w(shards: Sequence[StokesIGridderInput], num_pixels: in
         plan = _cabi.plan_make(num_pixels, num_pixels, pixel_size_lm, pixel_size_lm, epsilon, smin, smax, sact,
                                do_wstacking=True, fp64=accumulate_fp64, sigma=common.sigma, support=common.support)
         assert (plan.nu, plan.nv, plan.dw, plan.nshift) == (common.nu, common.nv, common.dw, common.nshift)
-        for rep in _grid_shards(ctx, [a for a, _sh, _w in skeep], plan, image):
-            if reports is not None:
-                reports.append(dict(rep, nplanes=plan.nplanes, slab=s))
+        for rep in _grid_shards(ctx, [a for a, _sh, _w in skeep], plan, image, reports is not None):
+            reports.append(dict(rep, nplanes=plan.nplanes, slab=s))
         mark("ms_grid_call")
     if reports:
         reports[-1]["phases_ms"] = phases
@@ -574,4 +589,4 @@ def dask_invert_measurement_set(ms_reader: MeasurementSetReader, client, num_pix
     image, plan, sumw = accumulate_shards(shards, num_pixels, _pixel_size_lm(pixel_size_asec), epsilon=epsilon,
                                           accumulate_fp64=accumulate_fp64)
     image = reduce_and_correct(image, plan, float(np.float32(sumw)))
-    return image.cpu().numpy()
+    return image_to_host(image)
