@@ -487,6 +487,12 @@ __device__ __forceinline__ void mma_tf32(float (&d)[4], const uint32_t (&a)[4], 
                : "+f"(d[0]), "+f"(d[1]), "+f"(d[2]), "+f"(d[3])
                : "r"(a[0]), "r"(a[1]), "r"(a[2]), "r"(a[3]), "r"(b0), "r"(b1));
 }
+// The first product of a chain: C = 0 comes from the zero register, so the accumulators need no clearing moves.
+__device__ __forceinline__ void mma_tf32_first(float (&d)[4], const uint32_t (&a)[4], uint32_t b0, uint32_t b1) {
+  asm("mma.sync.aligned.m16n8k8.row.col.f32.tf32.tf32.f32 {%0,%1,%2,%3}, {%4,%5,%6,%7}, {%8,%9}, {%10,%10,%10,%10};"
+               : "=f"(d[0]), "=f"(d[1]), "=f"(d[2]), "=f"(d[3])
+               : "r"(a[0]), "r"(a[1]), "r"(a[2]), "r"(a[3]), "r"(b0), "r"(b1), "f"(0.0f));
+}
 template <int OFF>
 __device__ __forceinline__ float2 lds_f2(uint32_t addr) {
   float2 v;
@@ -577,16 +583,12 @@ struct WarpAcc {
       }
       float d[2][2][4];
 #pragma unroll
-      for (int m = 0; m < 2; ++m)
-#pragma unroll
-        for (int nt = 0; nt < 2; ++nt) d[m][nt][0] = d[m][nt][1] = d[m][nt][2] = d[m][nt][3] = 0.f;
-#pragma unroll
       for (int term = 0; term < 3; ++term)
 #pragma unroll
         for (int m = 0; m < 2; ++m)
 #pragma unroll
           for (int nt = 0; nt < 2; ++nt) {
-            if (term == 0) mma_tf32(d[m][nt], al[m], bh[nt][0], bh[nt][1]);
+            if (term == 0) mma_tf32_first(d[m][nt], al[m], bh[nt][0], bh[nt][1]);
             else if (term == 1) mma_tf32(d[m][nt], ah[m], bl[nt][0], bl[nt][1]);
             else mma_tf32(d[m][nt], ah[m], bh[nt][0], bh[nt][1]);
           }
