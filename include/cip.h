@@ -70,8 +70,8 @@ typedef struct {
   int64_t nrow;
   const double* freq;       /* (nchan,) Hz                                           */
   int64_t nchan;
-  const void* vis;          /* (nrow,nchan) complex64                                */
-  const float* wgt;         /* (nrow,nchan) float32 or NULL (= all ones)             */
+  const void* vis;          /* (nrow,nchan) complex64 (complex128 if vis_c128)       */
+  const void* wgt;          /* (nrow,nchan) float32 (float64 if vis_c128) or NULL (= all ones) */
   const uint8_t* mask;      /* (nrow,nchan) or NULL; 0 = skip sample                 */
   int64_t vis_row_stride;   /* elements between rows of vis (>= nchan; 0 = nchan)    */
   int64_t wgt_row_stride;   /* same for wgt and mask                                 */
@@ -92,6 +92,10 @@ typedef struct {
   int64_t nvis;
   double w_lo, w_hi;        /* w_hi > 0: only the samples with w_lo <= |w| < w_hi (wavelengths) take part -- one
                              * |w| slab of a w-sharded invert (SURVEY 8e option 3); w_hi <= 0: all samples      */
+  int32_t vis_c128;         /* 1: vis is complex128 and wgt (if given) float64 -- ducc0's double-precision call.  The
+                             * samples are read as they are (no down-cast anywhere: the records of the float64
+                             * gridder carry float64 visibilities); combine with accumulate_fp64 = 1 for ducc0's
+                             * behaviour on complex128 input.  0: complex64 / float32                              */
 } cip_invert_args;
 
 typedef struct {

@@ -18,6 +18,7 @@
 // once after the whole call has drained, grows the buffers and repeats the call (never in steady state).
 #include <algorithm>
 #include <cstdlib>
+#include <type_traits>
 
 #include "geom.cuh"
 
@@ -285,7 +286,7 @@ __global__ void __launch_bounds__(256) items_kernel(Job* __restrict__ jobs, cons
 
 // ---- pass 3: records --------------------------------------------------------------------------------------
 // One warp per row, lanes stride the channels.  Reads are row-contiguous; a segment's records are contiguous.
-template <typename R, bool PACK>
+template <typename R, bool PACK, bool WIDE>
 __global__ void __launch_bounds__(256, 6) records_kernel(DevInputs in, GridGeom g, const double* __restrict__ finv,
                                                          uint32_t* __restrict__ table, const BinHeader* __restrict__ hdr,
                                                          Rec<R>* __restrict__ recs) {
@@ -301,12 +302,15 @@ __global__ void __launch_bounds__(256, 6) records_kernel(DevInputs in, GridGeom 
     const bool valid = c >= sp.c_begin && c < sp.c_end;
     // the sample loads are issued before the geometry, which does not depend on them (the pass is bound by
     // memory latency)
-    float2 v = make_float2(0.f, 0.f);
-    float wgt = 0.f;
+    using V = typename std::conditional<WIDE, double, float>::type;  // precision of the inputs
+    using V2 = typename std::conditional<WIDE, double2, float2>::type;
+    V2 v;
+    v.x = v.y = 0;
+    V wgt = 0;
     if (valid) {
-      v = __ldcs(in.vis + sp.vbase + c);
-      wgt = in.wgt ? __ldcs(in.wgt + sp.wbase + c) : 1.0f;
-      if (in.mask && in.mask[sp.wbase + c] == 0) wgt = 0.0f;
+      v = __ldcs(reinterpret_cast<const V2*>(in.vis) + sp.vbase + c);
+      wgt = in.wgt ? __ldcs(reinterpret_cast<const V*>(in.wgt) + sp.wbase + c) : (V)1;
+      if (in.mask && in.mask[sp.wbase + c] == 0) wgt = 0;
     }
     uint32_t key = kNoKey;
     SampleGeom s;
@@ -327,11 +331,13 @@ __global__ void __launch_bounds__(256, 6) records_kernel(DevInputs in, GridGeom 
     }
     pos = __shfl_sync(0xffffffffu, pos, lead) + (uint32_t)(lane - lead);
     if (key == kNoKey) continue;
-    const bool act = wgt != 0.0f && (v.x != 0.0f || v.y != 0.0f);
+    const bool act = wgt != 0 && (v.x != 0 || v.y != 0);
     R re = 0, im = 0;
     if (act) {
-      re = (R)v.x * (R)wgt;
-      im = (R)v.y * (R)wgt;
+      // the product in the wider of the two precisions (float32 inputs: exactly the float32 product of before)
+      using P = typename std::conditional<(sizeof(V) > sizeof(R)), V, R>::type;
+      re = (R)((P)v.x * (P)wgt);
+      im = (R)((P)v.y * (P)wgt);
       if (s.flip) im = -im;
       if (g.do_wstacking && g.nshift != 0.0) {  // V' = V exp(+2 pi i w s); phase reduced in float64
         double ph = s.w * g.nshift;
@@ -442,12 +448,15 @@ cip_status run_binning(cip_ctx* ctx, int slot, const DevInputs& in, const GridGe
   if (pack) {
     scan_apply_kernel<16><<<(unsigned)ntiles, kScanThreads, 0, st>>>(table, n, w.tile_sums.as<uint2>(), hdr, g, epw, w.jobs.as<Job>(),
                                                                      w.recs.as<unsigned char>(), wjs);
-    records_kernel<float, true><<<rblocks, 256, 0, st>>>(in, g, finv, table, hdr, w.recs.as<Rec<float>>());
+    if (in.wide) records_kernel<float, true, true><<<rblocks, 256, 0, st>>>(in, g, finv, table, hdr, w.recs.as<Rec<float>>());
+    else records_kernel<float, true, false><<<rblocks, 256, 0, st>>>(in, g, finv, table, hdr, w.recs.as<Rec<float>>());
   } else {
     scan_apply_kernel<32><<<(unsigned)ntiles, kScanThreads, 0, st>>>(table, n, w.tile_sums.as<uint2>(), hdr, g, epw, w.jobs.as<Job>(),
                                                                      w.recs.as<unsigned char>(), wjs);
-    if (fp64) records_kernel<double, false><<<rblocks, 256, 0, st>>>(in, g, finv, table, hdr, w.recs.as<Rec<double>>());
-    else records_kernel<float, false><<<rblocks, 256, 0, st>>>(in, g, finv, table, hdr, w.recs.as<Rec<float>>());
+    if (fp64 && in.wide) records_kernel<double, false, true><<<rblocks, 256, 0, st>>>(in, g, finv, table, hdr, w.recs.as<Rec<double>>());
+    else if (fp64) records_kernel<double, false, false><<<rblocks, 256, 0, st>>>(in, g, finv, table, hdr, w.recs.as<Rec<double>>());
+    else if (in.wide) records_kernel<float, false, true><<<rblocks, 256, 0, st>>>(in, g, finv, table, hdr, w.recs.as<Rec<float>>());
+    else records_kernel<float, false, false><<<rblocks, 256, 0, st>>>(in, g, finv, table, hdr, w.recs.as<Rec<float>>());
   }
   ctx->launches += 6;
   if (want_items) {

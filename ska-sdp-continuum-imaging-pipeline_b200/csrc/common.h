@@ -271,9 +271,10 @@ GridGeom make_geom(const cip_plan& p);
 struct DevInputs {
   const double* uvw;
   const double* freq;
-  const float2* vis;
-  const float* wgt;
+  const float2* vis;   // wide: really const double2*
+  const float* wgt;    // wide: really const double*
   const uint8_t* mask;
+  int wide = 0;        // 1: complex128 visibilities and float64 weights (cip_invert_args.vis_c128)
   int64_t nrow, nchan, vstride, wstride;
   double w_lo = 0.0, w_hi = 0.0;  // w_hi > 0: only samples with w_lo <= |w| < w_hi are active
   // jagged rows (nullptr: dense): channels [ch0[r], ch1[r]) of row r at elements voff[r] ... of vis / wgt / mask

@@ -109,16 +109,18 @@ cip_status stage_inputs(cip_ctx* ctx, const cip_invert_args* a, DevInputs* d, Vi
   d->nchan = nchan;
   d->w_lo = a->w_hi > 0 ? a->w_lo : 0.0;
   d->w_hi = a->w_hi > 0 ? a->w_hi : 0.0;
+  d->wide = a->vis_c128 ? 1 : 0;
+  const size_t vis_elem = d->wide ? sizeof(double2) : sizeof(float2), wgt_elem = d->wide ? sizeof(double) : sizeof(float);
   if (ms_h2d) *ms_h2d = 0.0;
   const bool reuse = reuse_small && ctx->staged_valid && a->memspace == 0 && ctx->staged_key[0] == a->uvw &&
                      ctx->staged_key[1] == a->freq && ctx->staged_key[2] == a->wgt && ctx->staged_key[3] == a->mask &&
-                     ctx->staged_dims[0] == nrow && ctx->staged_dims[1] == nchan && ctx->staged_dims[2] == ws;
+                     ctx->staged_dims[0] == nrow && ctx->staged_dims[1] == nchan && ctx->staged_dims[2] == ws && ctx->staged_dims[3] == d->wide;
   ctx->staged_valid = false;
   if (a->memspace == 1) {
     d->uvw = a->uvw;
     d->freq = a->freq;
     d->vis = static_cast<const float2*>(a->vis);
-    d->wgt = a->wgt;
+    d->wgt = static_cast<const float*>(a->wgt);
     d->mask = a->mask;
     d->vstride = vs;
     d->wstride = ws;
@@ -131,7 +133,7 @@ cip_status stage_inputs(cip_ctx* ctx, const cip_invert_args* a, DevInputs* d, Vi
       // (context stream, bound by memory latency) overlaps the gridding of chunk c (grid stream, bound by
       // the FMA and shared-memory pipes).  More chunks hide more of the binning but multiply the work
       // items (one sub-grid flush each).
-      const size_t vis_bytes = (size_t)nrow * nchan * sizeof(float2);
+      const size_t vis_bytes = (size_t)nrow * nchan * vis_elem;
       int nchunks = 1;  // measured on B200 (configs[1]): 1 chunk 22.8 ms, 2 chunks 23.5 ms, 3 chunks 24.2 ms -- next
                         // to the gridder's CTAs the binning kernels get half their occupancy, so the default stays 1
       (void)vis_bytes;
@@ -152,9 +154,9 @@ cip_status stage_inputs(cip_ctx* ctx, const cip_invert_args* a, DevInputs* d, Vi
     CIP_TRY(ctx->in_uvw.ensure(sizeof(double) * 3 * (size_t)nrow + 8));
     CIP_TRY(ctx->in_freq.ensure(sizeof(double) * (size_t)nchan + 8));
     CIP_TRY(ctx->in_rows.ensure(16 * (size_t)nrow + 64));
-    if (a->wgt) CIP_TRY(ctx->in_wgt.ensure(sizeof(float) * nvis + 8));
+    if (a->wgt) CIP_TRY(ctx->in_wgt.ensure(wgt_elem * nvis + 8));
     if (a->mask) CIP_TRY(ctx->in_mask.ensure(nvis + 8));
-    if (feed) CIP_TRY(ctx->in_vis.ensure(sizeof(float2) * nvis + 8));
+    if (feed) CIP_TRY(ctx->in_vis.ensure(vis_elem * nvis + 8));
     int64_t* d_off = ctx->in_rows.as<int64_t>();
     int32_t* d_c0 = reinterpret_cast<int32_t*>(d_off + nrow);
     int32_t* d_c1 = d_c0 + nrow;
@@ -174,9 +176,9 @@ cip_status stage_inputs(cip_ctx* ctx, const cip_invert_args* a, DevInputs* d, Vi
       CIP_CHECK_CUDA(cudaMemcpyAsync(d_off, a->row_vis_offset, sizeof(int64_t) * nrow, cudaMemcpyHostToDevice, st));
       CIP_CHECK_CUDA(cudaMemcpyAsync(d_c0, a->row_chan_start, sizeof(int32_t) * nrow, cudaMemcpyHostToDevice, st));
       CIP_CHECK_CUDA(cudaMemcpyAsync(d_c1, a->row_chan_stop, sizeof(int32_t) * nrow, cudaMemcpyHostToDevice, st));
-      if (a->wgt && nvis) CIP_CHECK_CUDA(cudaMemcpyAsync(ctx->in_wgt.p, a->wgt, sizeof(float) * nvis, cudaMemcpyHostToDevice, st));
+      if (a->wgt && nvis) CIP_CHECK_CUDA(cudaMemcpyAsync(ctx->in_wgt.p, a->wgt, wgt_elem * nvis, cudaMemcpyHostToDevice, st));
       if (a->mask && nvis) CIP_CHECK_CUDA(cudaMemcpyAsync(ctx->in_mask.p, a->mask, nvis, cudaMemcpyHostToDevice, st));
-      if (feed && nvis) CIP_CHECK_CUDA(cudaMemcpyAsync(ctx->in_vis.p, a->vis, sizeof(float2) * nvis, cudaMemcpyHostToDevice, st));
+      if (feed && nvis) CIP_CHECK_CUDA(cudaMemcpyAsync(ctx->in_vis.p, a->vis, vis_elem * nvis, cudaMemcpyHostToDevice, st));
     }
     CIP_CHECK_CUDA(cudaEventRecord(ctx->small_ev, st));
     if (feed) {
@@ -193,9 +195,9 @@ cip_status stage_inputs(cip_ctx* ctx, const cip_invert_args* a, DevInputs* d, Vi
   }
   CIP_TRY(ctx->in_uvw.ensure(sizeof(double) * 3 * (size_t)nrow + 8));
   CIP_TRY(ctx->in_freq.ensure(sizeof(double) * (size_t)nchan + 8));
-  if (a->wgt) CIP_TRY(ctx->in_wgt.ensure(sizeof(float) * (size_t)nrow * nchan + 8));
+  if (a->wgt) CIP_TRY(ctx->in_wgt.ensure(wgt_elem * (size_t)nrow * nchan + 8));
   if (a->mask) CIP_TRY(ctx->in_mask.ensure((size_t)nrow * nchan + 8));
-  if (feed) CIP_TRY(ctx->in_vis.ensure(sizeof(float2) * (size_t)nrow * nchan + 8));
+  if (feed) CIP_TRY(ctx->in_vis.ensure(vis_elem * (size_t)nrow * nchan + 8));
   d->uvw = ctx->in_uvw.as<double>();
   d->freq = ctx->in_freq.as<double>();
   d->vis = feed ? ctx->in_vis.as<float2>() : nullptr;
@@ -206,14 +208,14 @@ cip_status stage_inputs(cip_ctx* ctx, const cip_invert_args* a, DevInputs* d, Vi
   if (nrow && nchan && !reuse) {
     CIP_CHECK_CUDA(cudaMemcpyAsync(ctx->in_uvw.p, a->uvw, sizeof(double) * 3 * nrow, cudaMemcpyHostToDevice, st));
     CIP_CHECK_CUDA(cudaMemcpyAsync(ctx->in_freq.p, a->freq, sizeof(double) * nchan, cudaMemcpyHostToDevice, st));
-    if (a->wgt) CIP_TRY(copy_rows(ctx->in_wgt.p, a->wgt, sizeof(float), nrow, nchan, ws, st));
+    if (a->wgt) CIP_TRY(copy_rows(ctx->in_wgt.p, a->wgt, wgt_elem, nrow, nchan, ws, st));
     if (a->mask) CIP_TRY(copy_rows(ctx->in_mask.p, a->mask, 1, nrow, nchan, ws, st));
   }
   CIP_CHECK_CUDA(cudaEventRecord(ctx->small_ev, st));
   if (feed) {
     // visibilities: row chunks of >= 64 MB on the copy stream, behind the small inputs so that the scan
     // and the planning can start as early as possible
-    const size_t vis_bytes = sizeof(float2) * (size_t)nrow * nchan;
+    const size_t vis_bytes = vis_elem * (size_t)nrow * nchan;
     int nchunks = (int)std::min<size_t>(kMaxChunks, std::max<size_t>(1, vis_bytes >> 26));
     if (const char* e = getenv("CIP_STREAM_CHUNKS")) nchunks = std::min(kMaxChunks, std::max(1, atoi(e)));  // tests
     nchunks = (int)std::min<int64_t>(nchunks, std::max<int64_t>(nrow, 1));
@@ -235,8 +237,8 @@ cip_status stage_inputs(cip_ctx* ctx, const cip_invert_args* a, DevInputs* d, Vi
       feed->row0[c] = r0;
       feed->row0[c + 1] = r1;
       if (r1 > r0 && nchan)
-        CIP_TRY(copy_rows(ctx->in_vis.as<float2>() + r0 * nchan, static_cast<const float2*>(a->vis) + r0 * vs,
-                          sizeof(float2), r1 - r0, nchan, vs, ctx->copy_stream));
+        CIP_TRY(copy_rows(static_cast<char*>(ctx->in_vis.p) + vis_elem * r0 * nchan, static_cast<const char*>(a->vis) + vis_elem * r0 * vs,
+                          vis_elem, r1 - r0, nchan, vs, ctx->copy_stream));
       CIP_CHECK_CUDA(cudaEventRecord(ctx->chunk_ev[c], ctx->copy_stream));
       feed->ready[c] = ctx->chunk_ev[c];
     }
@@ -252,6 +254,7 @@ cip_status stage_inputs(cip_ctx* ctx, const cip_invert_args* a, DevInputs* d, Vi
   ctx->staged_dims[0] = nrow;
   ctx->staged_dims[1] = nchan;
   ctx->staged_dims[2] = ws;
+  ctx->staged_dims[3] = d->wide;
   return CIP_OK;
 }
 

@@ -145,12 +145,12 @@ __device__ __forceinline__ KeyParts key_parts(const GridGeom& g, uint32_t key) {
   return k;
 }
 
-__device__ __forceinline__ bool sample_active(const float2 v, const float* wgt, const uint8_t* mask, int64_t k,
-                                              float* wout) {
-  float w = wgt ? wgt[k] : 1.0f;
-  if (mask && mask[k] == 0) w = 0.0f;
-  *wout = w;
-  return w != 0.0f && (v.x != 0.0f || v.y != 0.0f);
+// Weight (mask applied) and visibility of the sample at element k of wgt / mask resp. vis, in the input precision.
+__device__ __forceinline__ double sample_weight(const DevInputs& in, int64_t k) {
+  double w = 1.0;
+  if (in.wgt) w = in.wide ? reinterpret_cast<const double*>(in.wgt)[k] : (double)in.wgt[k];
+  if (in.mask && in.mask[k] == 0) w = 0.0;
+  return w;
 }
 
 // Channels of a row and where its samples live: sample (row, c) is element vbase + c of vis and wbase + c of

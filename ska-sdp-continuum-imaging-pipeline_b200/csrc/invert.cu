@@ -88,8 +88,9 @@ static DevInputs row_slice(const DevInputs& in, int64_t r0, int64_t r1) {
     c.ch1 = in.ch1 + r0;
     return c;
   }
-  c.vis = in.vis + r0 * in.vstride;
-  if (in.wgt) c.wgt = in.wgt + r0 * in.wstride;
+  const int64_t ws = in.wide ? 2 : 1;  // the typed pointers count float2 / float elements
+  c.vis = in.vis + ws * r0 * in.vstride;
+  if (in.wgt) c.wgt = in.wgt + ws * r0 * in.wstride;
   if (in.mask) c.mask = in.mask + r0 * in.wstride;
   return c;
 }

@@ -23,10 +23,10 @@ struct ScanAcc {
   double lo = 1e300, hi = 0.0, sw = 0.0;
   unsigned long long na = 0;
   double w_lo = 0.0, w_hi = 0.0;
-  __device__ __forceinline__ void add(float w, bool masked, double aw) {
-    if (masked || (w_hi > 0.0 && !(aw >= w_lo && aw < w_hi))) w = 0.0f;
-    sw += (double)w;
-    if (w != 0.0f) {
+  __device__ __forceinline__ void add(double w, bool masked, double aw) {
+    if (masked || (w_hi > 0.0 && !(aw >= w_lo && aw < w_hi))) w = 0.0;
+    sw += w;
+    if (w != 0.0) {
       lo = fmin(lo, aw);
       hi = fmax(hi, aw);
       ++na;
@@ -68,10 +68,8 @@ __global__ void __launch_bounds__(256) scan_kernel(DevInputs in, int do_wstackin
   acc.w_hi = in.w_hi;
   for (int64_t k = (int64_t)blockIdx.x * blockDim.x + threadIdx.x; k < total; k += (int64_t)gridDim.x * blockDim.x) {
     int64_t r = k / nchan, c = k - r * nchan;
-    float w = in.wgt ? in.wgt[r * in.wstride + c] : 1.0f;
-    bool masked = in.mask && in.mask[r * in.wstride + c] == 0;
     double aw = do_wstacking ? fabs(in.uvw[3 * r + 2]) * (in.freq[c] / kSpeedOfLight) : 0.0;
-    acc.add(w, masked, aw);
+    acc.add(sample_weight(in, r * in.wstride + c), false, aw);
   }
   scan_finish(acc, out);
 }
@@ -86,9 +84,7 @@ __global__ void __launch_bounds__(256) scan_rows_kernel(DevInputs in, int do_wst
     const RowSpan sp = row_span(in, row);
     const double wm = do_wstacking ? fabs(in.uvw[3 * row + 2]) : 0.0;
     for (int c = sp.c_begin + lane; c < sp.c_end; c += 32) {
-      const float w = in.wgt ? in.wgt[sp.wbase + c] : 1.0f;
-      const bool masked = in.mask && in.mask[sp.wbase + c] == 0;
-      acc.add(w, masked, wm * (in.freq[c] / kSpeedOfLight));
+      acc.add(sample_weight(in, sp.wbase + c), false, wm * (in.freq[c] / kSpeedOfLight));
     }
   }
   scan_finish(acc, out);
@@ -155,9 +151,7 @@ __global__ void __launch_bounds__(256) whist_kernel(DevInputs in, double wmin, d
     const RowSpan sp = row_span(in, row);
     const double wm = fabs(in.uvw[3 * row + 2]);
     for (int c = sp.c_begin + lane; c < sp.c_end; c += 32) {
-      float w = in.wgt ? in.wgt[sp.wbase + c] : 1.0f;
-      if (in.mask && in.mask[sp.wbase + c] == 0) w = 0.0f;
-      if (w == 0.0f) continue;
+      if (sample_weight(in, sp.wbase + c) == 0.0) continue;
       const double aw = wm * (in.freq[c] / kSpeedOfLight);
       if (in.w_hi > 0.0 && !(aw >= in.w_lo && aw < in.w_hi)) continue;
       int b = (int)((aw - wmin) * scale);
@@ -205,7 +199,7 @@ cip_status run_scan(cip_ctx* ctx, const DevInputs& in, int do_wstacking, cip_sca
     CIP_CHECK_CUDA(cudaGetLastError());
   } else if (total > 0) {
     auto al16 = [](const void* p) { return (reinterpret_cast<uintptr_t>(p) & 15) == 0; };
-    const bool v4 = in.nchan % 4 == 0 && in.wstride % 4 == 0 && al16(in.wgt) && al16(in.mask) && in.nchan <= 4096;
+    const bool v4 = !in.wide && in.nchan % 4 == 0 && in.wstride % 4 == 0 && al16(in.wgt) && al16(in.mask) && in.nchan <= 4096;
     if (v4) {
       int blocks = (int)std::min<int64_t>((total / 4 + 255) / 256, (int64_t)ctx->sm_count * 8);
       const size_t smem = sizeof(double) * in.nchan;

@@ -30,7 +30,8 @@ class InvertArgs(C.Structure):
                 ("npix_x", C.c_int), ("npix_y", C.c_int), ("pixsize_x", C.c_double), ("pixsize_y", C.c_double),
                 ("epsilon", C.c_double), ("do_wstacking", C.c_int), ("accumulate_fp64", C.c_int),
                 ("memspace", C.c_int), ("row_vis_offset", C.c_void_p), ("row_chan_start", C.c_void_p),
-                ("row_chan_stop", C.c_void_p), ("nvis", C.c_int64), ("w_lo", C.c_double), ("w_hi", C.c_double)]
+                ("row_chan_stop", C.c_void_p), ("nvis", C.c_int64), ("w_lo", C.c_double), ("w_hi", C.c_double),
+                ("vis_c128", C.c_int32)]
 
 
 class ScanResult(C.Structure):

@@ -21,6 +21,10 @@ def _is_torch_cuda(a) -> bool:
     return a is not None and not isinstance(a, np.ndarray) and hasattr(a, "is_cuda") and a.is_cuda
 
 
+def _is_c128(a) -> bool:
+    return a is not None and str(a.dtype) in ("complex128", "torch.complex128")
+
+
 def _prep_host(uvw, freq, ms, wgt, mask):
     uvw = np.ascontiguousarray(uvw, dtype=np.float64)
     freq = np.ascontiguousarray(freq, dtype=np.float64)
@@ -29,10 +33,11 @@ def _prep_host(uvw, freq, ms, wgt, mask):
     ms = np.asarray(ms)
     if ms.ndim != 2 or ms.shape != (uvw.shape[0], freq.shape[0]):
         raise ValueError(f"ms must have shape (nrow, nchan) = {(uvw.shape[0], freq.shape[0])}, got {ms.shape}")
+    # complex128 visibilities go through as they are, with float64 weights (ducc0's double-precision call)
     fp64_in = ms.dtype == np.complex128
-    ms = np.ascontiguousarray(ms, dtype=np.complex64)
+    ms = np.ascontiguousarray(ms, dtype=np.complex128 if fp64_in else np.complex64)
     if wgt is not None:
-        wgt = np.ascontiguousarray(wgt, dtype=np.float32)
+        wgt = np.ascontiguousarray(wgt, dtype=np.float64 if fp64_in else np.float32)
         if wgt.shape != ms.shape:
             raise ValueError("wgt must have the shape of ms")
     if mask is not None:
@@ -75,6 +80,7 @@ def make_args(uvw, freq, ms, wgt, mask, npix_x, npix_y, pixsize_x, pixsize_y, ep
     a.accumulate_fp64 = int(bool(fp64))
     a.memspace = memspace
     a.w_lo, a.w_hi = (float(w_slab[0]), float(w_slab[1])) if w_slab else (0.0, 0.0)
+    a.vis_c128 = int(_is_c128(ms))
     return a
 
 
@@ -142,13 +148,14 @@ def ms2dirty(uvw, freq, ms, wgt=None, npix_x=0, npix_y=0, pixsize_x=0.0, pixsize
         for t in (uvw, freq, ms):
             if not (_is_torch_cuda(t) and t.is_contiguous()):
                 raise ValueError("with CUDA inputs, uvw, freq and ms must all be contiguous CUDA tensors")
-        if uvw.dtype != torch.float64 or freq.dtype != torch.float64 or ms.dtype != torch.complex64:
-            raise ValueError("CUDA inputs must be float64 uvw/freq and complex64 ms")
-        if wgt is not None and (not _is_torch_cuda(wgt) or wgt.dtype != torch.float32 or not wgt.is_contiguous()):
-            raise ValueError("wgt must be a contiguous float32 CUDA tensor")
+        if uvw.dtype != torch.float64 or freq.dtype != torch.float64 or ms.dtype not in (torch.complex64, torch.complex128):
+            raise ValueError("CUDA inputs must be float64 uvw/freq and complex64 or complex128 ms")
+        wdt = torch.float64 if ms.dtype == torch.complex128 else torch.float32
+        if wgt is not None and (not _is_torch_cuda(wgt) or wgt.dtype != wdt or not wgt.is_contiguous()):
+            raise ValueError(f"wgt must be a contiguous {wdt} CUDA tensor (the real type of ms)")
         if mask is not None and (not _is_torch_cuda(mask) or mask.dtype != torch.uint8 or not mask.is_contiguous()):
             raise ValueError("mask must be a contiguous uint8 CUDA tensor")
-        fp64 = bool(double_precision_accumulation)
+        fp64 = bool(double_precision_accumulation) or ms.dtype == torch.complex128
         device = ms.device.index
         out = torch.empty((npix_x, npix_y), dtype=torch.float64 if fp64 else torch.float32, device=ms.device)
         torch.cuda.current_stream(ms.device).synchronize()

@@ -86,6 +86,42 @@ def test_complex128_input_selects_fp64(wg, small):
     assert dft.rel_rms(img, ref) <= 1e-6
 
 
+def test_complex128_input_is_read_natively(wg, small):
+    """complex128 visibilities / float64 weights go through the boundary as they are (cip_invert_args.vis_c128):
+    values that complex64 cannot hold (relative rounding 3e-8) must not cost accuracy, from host and from device
+    memory, for float64 and float32 grids."""
+    import torch
+    (uvw, freq, vis, wgt, nx, px), _ = small
+    rng = np.random.default_rng(11)
+    vis128 = vis.astype(np.complex128) * (1.0 + 1e-3 * rng.standard_normal(vis.shape)) + 1e-5j * rng.standard_normal(vis.shape)
+    wgt64 = wgt.astype(np.float64) * (1.0 + 1e-3 * rng.standard_normal(wgt.shape))
+    ref = dft.dft_dirty(uvw, freq, vis128, wgt64, nx, nx, px, px)
+    rounded = dft.dft_dirty(uvw, freq, vis128.astype(np.complex64), wgt64.astype(np.float32), nx, nx, px, px)
+    floor32 = dft.rel_rms(rounded, ref)
+    assert floor32 > 1e-8  # what a down-cast at the boundary would cost
+    with forced_plan(2.0, 14):
+        img = wg.ms2dirty(uvw, freq, vis128, wgt64, nx, nx, px, px, epsilon=1e-9, do_wstacking=True)
+        dev = lambda a: torch.as_tensor(a).cuda()
+        img_d = wg.ms2dirty(dev(uvw), dev(freq), dev(vis128), dev(wgt64), nx, nx, px, px, epsilon=1e-9, do_wstacking=True)
+    assert img.dtype == np.float64 and img_d.dtype == torch.float64
+    assert dft.rel_rms(img, ref) <= 2e-9 < floor32 / 5
+    assert dft.rel_rms(img_d.cpu().numpy(), ref) <= 2e-9
+    # masked samples and float32 grids with complex128 input (values are rounded once, into the records)
+    mask = (rng.random(vis.shape) > 0.3).astype(np.uint8)
+    ref_m = dft.dft_dirty(uvw, freq, vis128, wgt64 * mask, nx, nx, px, px)
+    args = wg.make_args(uvw, freq, vis128, wgt64, mask, nx, nx, px, px, 1e-4, True, False, 0)
+    assert args.vis_c128 == 1
+    from ska_sdp_cip._cabi import Context, Plan, Report, ScanResult, _ptr, check, lib
+    out = np.empty((nx, nx), dtype=np.float32)
+    ctx = Context.get(-1)
+    scan = ScanResult()
+    with ctx.lock:
+        check(lib().cip_invert(ctx.handle, C.byref(args), _ptr(out), C.byref(scan), C.byref(Plan()), C.byref(Report())))
+    assert dft.rel_rms(out, ref_m) <= TOL_FP32
+    assert scan.nactive == int(np.count_nonzero((wgt64 * mask) != 0))
+    assert abs(scan.sum_wgt - float((wgt64 * mask).sum())) <= 1e-9 * abs(scan.sum_wgt)
+
+
 # every branch of the gridder: the register-window kernels (W <= 8) at each support, the wide path
 # (W > 8), each oversampling factor
 @pytest.mark.parametrize("sigma,W,tol", [(2.0, 4, 2e-3), (2.0, 5, 3e-4), (2.0, 6, 1e-4), (2.0, 7, 1e-4), (2.0, 8, 1e-4),
