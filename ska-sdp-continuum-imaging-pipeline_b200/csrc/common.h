@@ -143,6 +143,7 @@ struct FftPlan {
   cufftHandle handle = 0;
   size_t work = 0;
 };
+struct PfftPlan;  // tables of the own transform (pfft.cu)
 
 // One gridder-ready visibility: exactly one 32-byte sector, so that the scattered writes of the
 // record pass never touch a partial sector and the gridder's producer reads two 128-bit words.
@@ -250,6 +251,7 @@ struct cip_ctx {
   std::vector<double> tables_key;  // plan parameters the correction tables were built for
   int tables_ncheb = 0;
   std::map<std::tuple<int, int, int, int>, cip::FftPlan> fft_plans;  // (nu, nv, batch, fp64)
+  std::map<std::tuple<int, int, int>, cip::PfftPlan*> pfft_plans;     // (nu, nv, fp64)
   // tiling
   cip::DevBuf t_uvw, t_freq, t_vis;
   cip::TileWork twork;
@@ -326,11 +328,15 @@ cip_status run_gridder(cip_ctx* ctx, int slot, cudaStream_t stream, const GridGe
                        int win_last, void* grid, int plane_base, int nslots);
 cip_status run_fft(cip_ctx* ctx, void* grid, int nu, int nv, int batch, int fp64, int keep_v = 0);
 cip_status fft_rows(cip_ctx* ctx, void* data, int n, int batch, int fp64);  // data == nullptr: plan only
-// FFT + w-screen of the resident planes [plane_base, plane_base + nslots) into the image.  Default: per plane,
-// 1-D transforms along v, transpose of the retained columns, 1-D transforms along u, w-screen from the
+// FFT + w-screen of the resident planes [plane_base, plane_base + nslots) into the image.  Default: the own pruned
+// transform with the fused w-screen (pfft.cu) where the row fits shared memory.  Else, and with CIP_FFT=cufft: per
+// plane, cuFFT 1-D transforms along v, transpose of the retained columns, 1-D transforms along u, w-screen from the
 // transposed plane (see image.cu); CIP_FFT_2D=1: cuFFT's 2-D plan on every plane, then one w-screen pass.
 cip_status run_fft_screen(cip_ctx* ctx, const cip_plan& p, void* grid, int plane_base, int nslots, void* image,
                           double* ms_fft, double* ms_wscreen);
+cip_status pfft_prepare(cip_ctx* ctx, const cip_plan& p, bool* ok);  // tables and work area; *ok: the plan is supported
+cip_status run_pfft_screen(cip_ctx* ctx, const cip_plan& p, void* grid, int plane_base, int nslots, void* image);
+void pfft_release(cip_ctx* ctx);
 cip_status run_wscreen(cip_ctx* ctx, const cip_plan& p, const void* grid, int plane_base, int nslots, void* image);
 cip_status run_correct(cip_ctx* ctx, const cip_plan& p, void* image, int row_begin, int row_end, double scale);
 

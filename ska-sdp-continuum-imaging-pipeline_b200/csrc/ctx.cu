@@ -343,6 +343,7 @@ extern "C" cip_status cip_ctx_destroy(cip_ctx* ctx) {
   if (ctx->stream) cudaStreamSynchronize(ctx->stream);
   if (ctx->grid_stream) cudaStreamSynchronize(ctx->grid_stream);
   for (auto& kv : ctx->fft_plans) cufftDestroy(kv.second.handle);
+  cip::pfft_release(ctx);
   DevBuf* bufs[] = {&ctx->in_uvw, &ctx->in_freq, &ctx->in_vis, &ctx->in_wgt, &ctx->in_mask, &ctx->in_rows, &ctx->out_img,
                     &ctx->scan_out, &ctx->grid, &ctx->image, &ctx->tables, &ctx->fft_t, &ctx->t_uvw, &ctx->t_freq, &ctx->t_vis,
                     &ctx->call_flags};

@@ -207,6 +207,9 @@ cip_status run_fft_screen(cip_ctx* ctx, const cip_plan& pl, void* grid, int plan
                           double* ms_fft, double* ms_wscreen) {
   NvtxRange nvtx("cip:fft+wscreen");
   (void)ms_wscreen;
+  bool own = false;
+  if (!getenv("CIP_FFT_2D")) CIP_TRY(pfft_prepare(ctx, pl, &own));  // the own pruned transform with the fused w-screen (pfft.cu)
+  if (own) return grid ? run_pfft_screen(ctx, pl, grid, plane_base, nslots, image) : CIP_OK;
   if (grid == nullptr) {  // plans only
     if (getenv("CIP_FFT_2D")) return run_fft(ctx, nullptr, pl.nu, pl.nv, 0, pl.accumulate_fp64, pl.npix_y);
     // plans, their work areas and the transposed plane exist before the plane stack is sized from what is free

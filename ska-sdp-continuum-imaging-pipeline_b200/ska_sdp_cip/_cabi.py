@@ -97,6 +97,7 @@ def lib():
                                                    C.POINTER(Report)]
             L.cip_bin_inspect.argtypes = [C.c_void_p, C.POINTER(InvertArgs), C.POINTER(Plan), C.POINTER(C.c_int64),
                                           C.POINTER(C.c_int64), C.POINTER(C.c_int), C.c_void_p, C.c_void_p]
+            L.cip_plane_fft_crop.argtypes = [C.c_void_p, C.c_void_p, C.c_int, C.c_int, C.c_int, C.c_int, C.c_int, C.c_void_p]
             L.cip_correct_image.argtypes = [C.c_void_p, C.POINTER(Plan), C.c_void_p, C.c_int, C.c_int, C.c_double]
             L.cip_invert.argtypes = [C.c_void_p, C.POINTER(InvertArgs), C.c_void_p, C.POINTER(ScanResult),
                                      C.POINTER(Plan), C.POINTER(Report)]
@@ -117,7 +118,7 @@ def lib():
 
 EXPORTS = ["cip_last_error", "cip_version", "cip_ctx_create", "cip_ctx_destroy", "cip_ctx_stream",
            "cip_ctx_synchronize", "cip_ctx_launches", "cip_ctx_device", "cip_current_device", "cip_plan_make", "cip_kernel_table", "cip_kernel_ft", "cip_scan", "cip_w_histogram",
-           "cip_grid_accumulate", "cip_grid_accumulate_many", "cip_bin_inspect", "cip_correct_image", "cip_invert", "cip_stokes_i", "cip_stokes_i_async", "cip_tile_bin",
+           "cip_grid_accumulate", "cip_grid_accumulate_many", "cip_bin_inspect", "cip_plane_fft_crop", "cip_correct_image", "cip_invert", "cip_stokes_i", "cip_stokes_i_async", "cip_tile_bin",
            "cip_tile_fetch", "cip_tile_gather", "cip_tile_free"]
 
 
@@ -212,6 +213,20 @@ def bin_inspect(ctx: "Context", args: InvertArgs, plan: Plan):
         check(lib().cip_bin_inspect(ctx.handle, C.byref(args), C.byref(plan), C.byref(nj), C.byref(ng), C.byref(rb),
                                     jobs.ctypes.data, recs.ctypes.data))
     return jobs, recs
+
+
+def plane_fft_crop(ctx: "Context", plane, nx: int, ny: int):
+    """Retained nx x ny cells of the unnormalised e^{+i} 2-D transform of a CUDA complex64 / complex128 plane
+    (torch tensor, shape (nu, nv)), in image order -- see cip_plane_fft_crop."""
+    import torch
+    assert plane.is_cuda and plane.is_contiguous() and plane.dtype in (torch.complex64, torch.complex128)
+    nu, nv = plane.shape
+    out = torch.empty((nx, ny), dtype=plane.dtype, device=plane.device)
+    torch.cuda.current_stream(plane.device).synchronize()
+    with ctx.lock:
+        check(lib().cip_plane_fft_crop(ctx.handle, plane.data_ptr(), nu, nv, nx, ny, int(plane.dtype == torch.complex128),
+                                       out.data_ptr()))
+    return out
 
 
 def kernel_ft(plan: Plan, xi) -> np.ndarray:

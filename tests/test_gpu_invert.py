@@ -320,13 +320,13 @@ def _with_env(name, value, fn):
 
 
 @pytest.mark.parametrize("env", [("CIP_GRID_TC", "1"), ("CIP_GRID_MMA", "0"), ("CIP_DEVICE_CHUNKS", "3"), ("CIP_FFT_2D", "1"),
-                                 ("CIP_BIN_TABLE_ENTRIES", "1")])
+                                 ("CIP_FFT", "cufft"), ("CIP_BIN_TABLE_ENTRIES", "1")])
 def test_kernel_variants_agree(wg, small, wide, env):
     """The alternatives kept behind environment switches compute the same sums in another order: the tcgen05
     gridder (accumulators in tensor memory, whose float32 accumulation truncates: looser agreement), FFMA2 rank-1
     updates instead of 3xTF32 mma.sync tiles, device inputs cut into chunks that are binned and gridded on two
-    streams, cuFFT's 2-D plan and one w-screen pass instead of the per-plane transposed transform, one binning
-    pass per window (what a key table too large for one pass falls back to)."""
+    streams, cuFFT's 2-D plan and one w-screen pass / cuFFT 1-D transforms around a transposed crop instead of the own
+    pruned transform with the fused w-screen, one binning pass per window (what a key table too large for one pass falls back to)."""
     name, value = env
     prob, ref = wide if name == "CIP_BIN_TABLE_ENTRIES" else small
     base, info = invert(wg, prob)
