@@ -177,7 +177,8 @@ cip_status cip_bin_inspect(cip_ctx* ctx, const cip_invert_args* args, const cip_
  * e^{+i} 2-D transform of one nu x nv plane (complex64, or complex128 if fp64) that the image keeps,
  *   out[i][j] = sum_{u,v} plane[u][v] exp(+2 pi i (u fu / nu + v fv / nv)),  fu = (i - nx/2) mod nu, fv = (j - ny/2) mod nv,
  * computed by the pruned transform of csrc/pfft.cu (what ducc0 does inside ms2dirty between gridding and the
- * w-screen; reference call site src/ska_sdp_cip/invert.py:170-183).  plane and out are device pointers. */
+ * w-screen; reference call site src/ska_sdp_cip/invert.py:170-183).  plane and out are device pointers; the plane is
+ * overwritten (it holds the row transforms afterwards). */
 cip_status cip_plane_fft_crop(cip_ctx* ctx, const void* plane, int nu, int nv, int nx, int ny, int fp64, void* out);
 
 /* The same for several device-resident shards (memspace 1; e.g. the chunks of the reference's partition that one

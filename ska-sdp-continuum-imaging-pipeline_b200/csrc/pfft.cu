@@ -144,6 +144,7 @@ constexpr int kMaxStages = 16;
 struct Stages {
   int n = 0, count = 0;
   int radix[kMaxStages] = {};
+  int toff[kMaxStages] = {};  // float32 passes: where the twiddle table of the stage starts (pfft_f32.cuh)
 };
 
 // One stage: n points per sequence, span L, radix R; table tw of exp(2 pi i t / N) with w_n = tw[tstep].
@@ -266,6 +267,12 @@ struct ScreenArgs {
   const uint32_t* skip;  // != 0 on the device: a binning pass of this call overflowed, the image must stay untouched
 };
 
+}  // namespace
+}  // namespace cip
+#include "pfft_f32.cuh"  // the float32 passes, on packed pairs
+namespace cip {
+namespace {
+
 // For column block blockIdx.x and q = blockIdx.y: X[q + n1 s'] = sum_r Z[r][q] w_n2^{s' r}; the retained frequencies
 // (image rows) go through the w-screen into the image (SCREEN) or are written as they are (tests).
 template <typename T, bool SCREEN>
@@ -351,6 +358,47 @@ std::vector<int> make_perm(const Stages& st) {  // position of frequency f after
   return perm;
 }
 
+// float32 stage tables: for every stage with sub = L / R > 1 the factors w_L^{qk}, q = 1 .. R - 1, k < sub.
+// soa: cos block then sin block of floats (row pass, read as packed pairs over k); else float2 (cos, sin).
+// Returns the table; sets st->toff (in floats resp. float2).
+std::vector<float> make_stage_tables(Stages* st, bool soa) {
+  std::vector<float> tab;
+  int L = st->n;
+  for (int i = 0; i < st->count; ++i) {
+    const int R = st->radix[i], sub = L / R;
+    st->toff[i] = (int)(soa ? tab.size() : tab.size() / 2);
+    if (sub > 1) {
+      const size_t cnt = (size_t)(R - 1) * sub, at = tab.size();
+      tab.resize(at + 2 * cnt);
+      for (int q = 1; q < R; ++q)
+        for (int k = 0; k < sub; ++k) {
+          const double ang = 2.0 * M_PI * (double)(((long long)q * k) % L) / (double)L;
+          const size_t e = (size_t)(q - 1) * sub + k;
+          if (soa) {
+            tab[at + e] = (float)cos(ang);
+            tab[at + cnt + e] = (float)sin(ang);
+          } else {
+            tab[at + 2 * e] = (float)cos(ang);
+            tab[at + 2 * e + 1] = (float)sin(ang);
+          }
+        }
+    }
+    L /= R;
+  }
+  return tab;
+}
+
+// the packed row pass needs an even number of butterflies per block in every stage but the last
+bool rows_pairable(const Stages& st) {
+  int L = st.n;
+  for (int i = 0; i < st.count; ++i) {
+    const int sub = L / st.radix[i];
+    if (sub > 1 && sub % 2) return false;
+    L /= st.radix[i];
+  }
+  return st.count > 0;
+}
+
 template <typename T>
 void fill_twiddles(std::vector<unsigned char>& buf, size_t off, int n) {
   cx<T>* t = reinterpret_cast<cx<T>*>(buf.data() + off);
@@ -379,9 +427,11 @@ struct PfftPlan {
   DevBuf buf;
   Stages sa, s1, s2;
   int n1 = 0, n2 = 0;
-  size_t off_twv = 0, off_twu = 0, off_pa = 0, off_p1 = 0, off_p2 = 0;
+  size_t off_twv = 0, off_twu = 0, off_pa = 0, off_p1 = 0, off_p2 = 0, off_ta = 0, off_t1 = 0, off_t2 = 0, off_fb = 0, off_bf = 0;
+  int wf = 1;
   size_t smem_a = 0;
-  bool ok = false;
+  bool ok = false;       // the column passes are available (float32: cuFFT can do the row pass)
+  bool ok_rows = false;  // the own row pass too
 };
 
 void pfft_release(cip_ctx* ctx) {
@@ -392,10 +442,18 @@ void pfft_release(cip_ctx* ctx) {
   ctx->pfft_plans.clear();
 }
 
-static int split_columns(int nu) {  // n2: the divisor of nu closest to 64 from below (>= 8), so that n1 = nu / n2 stays small
-  int best = 1;
-  for (int d = 1; d <= 128 && d <= nu; ++d)
-    if (nu % d == 0) best = d;
+static int split_columns(int nu) {  // n2: the divisor (<= 128) of nu that needs the fewest stages for n1 = nu / n2 and n2 together
+  int best = 1, best_cost = 1 << 30;
+  for (int d = 2; d <= 128 && d <= nu; ++d) {
+    if (nu % d) continue;
+    const Stages a = make_stages(d), b = make_stages(nu / d);
+    if (a.count < 0 || b.count < 0) continue;
+    const int cost = (a.count + b.count) * 4 + (d < 32 ? 3 : 0) + (nu / d > 512 ? 3 : 0);
+    if (cost <= best_cost) {
+      best_cost = cost;
+      best = d;
+    }
+  }
   return best;
 }
 
@@ -413,10 +471,37 @@ static cip_status get_pfft(cip_ctx* ctx, int nu, int nv, int fp64, PfftPlan** ou
   p->sa = make_stages(nv);
   p->s1 = make_stages(p->n1);
   p->s2 = make_stages(p->n2);
-  p->smem_a = padded_len((size_t)nv) * csize;
-  const size_t smem_b = (size_t)std::max(p->n1, p->n2) * 16 * csize;
-  p->ok = p->sa.count > 0 && p->s1.count >= 0 && p->s2.count >= 0 && p->smem_a <= ctx->smem_optin && smem_b <= ctx->smem_optin &&
-          p->n1 >= 1 && p->n2 >= 2 && (int64_t)nu * nv < ((int64_t)1 << 40);
+  p->smem_a = fp64 ? padded_len((size_t)nv) * csize : (size_t)nv * csize;
+  std::vector<float> ta, t1, t2;
+  std::vector<int> fblock, bf_of_f;
+  if (!fp64 && p->sa.count > 0 && p->s1.count >= 0 && p->s2.count >= 0) {
+    ta = make_stage_tables(&p->sa, true);
+    t1 = make_stage_tables(&p->s1, false);
+    t2 = make_stage_tables(&p->s2, false);
+    // row pass: the last stage's butterfly per frequency, and the frequency contribution of the blocks of the stage
+    // before it (pfft_f32.cuh, rows_stage / rows_final)
+    const int m = p->sa.count;
+    Stages head = p->sa;  // stages 1 .. m - 1 on n / R_m points
+    head.count = m - 1;
+    head.n = nv / p->sa.radix[m - 1];
+    bf_of_f = make_perm(head);
+    Stages head2 = head;  // stages 1 .. m - 2 on R_1 .. R_{m-2} points
+    if (m >= 2) {
+      head2.count = m - 2;
+      head2.n = head.n / p->sa.radix[m - 2];
+    } else {
+      head2.count = 0;
+      head2.n = 1;
+    }
+    const std::vector<int> pos = make_perm(head2);
+    fblock.assign(head2.n, 0);
+    for (int f = 0; f < head2.n; ++f) fblock[pos[f]] = f;
+    p->wf = head2.n;
+  }
+  const size_t smem_b = (size_t)std::max(p->n1, p->n2) * 16 * csize * 2;  // double-buffered tiles (float32)
+  p->ok = p->sa.count > 0 && p->s1.count >= 0 && p->s2.count >= 0 && smem_b <= ctx->smem_optin && p->n1 >= 1 && p->n2 >= 2 &&
+          (int64_t)nu * nv < ((int64_t)1 << 40);
+  p->ok_rows = p->ok && p->smem_a <= ctx->smem_optin && (fp64 || rows_pairable(p->sa));
   if (p->ok) {
     auto al = [](size_t x) { return (x + 255) & ~(size_t)255; };
     p->off_twv = 0;
@@ -424,7 +509,12 @@ static cip_status get_pfft(cip_ctx* ctx, int nu, int nv, int fp64, PfftPlan** ou
     p->off_pa = al(p->off_twu + csize * nu);
     p->off_p1 = al(p->off_pa + sizeof(int) * nv);
     p->off_p2 = al(p->off_p1 + sizeof(int) * p->n1);
-    const size_t total = al(p->off_p2 + sizeof(int) * p->n2);
+    p->off_ta = al(p->off_p2 + sizeof(int) * p->n2);
+    p->off_t1 = al(p->off_ta + sizeof(float) * ta.size());
+    p->off_t2 = al(p->off_t1 + sizeof(float) * t1.size());
+    p->off_fb = al(p->off_t2 + sizeof(float) * t2.size());
+    p->off_bf = al(p->off_fb + sizeof(int) * fblock.size());
+    const size_t total = al(p->off_bf + sizeof(int) * bf_of_f.size());
     std::vector<unsigned char> host(total, 0);
     if (fp64) {
       fill_twiddles<double>(host, p->off_twv, nv);
@@ -437,6 +527,11 @@ static cip_status get_pfft(cip_ctx* ctx, int nu, int nv, int fp64, PfftPlan** ou
     memcpy(host.data() + p->off_pa, pa.data(), sizeof(int) * pa.size());
     memcpy(host.data() + p->off_p1, p1.data(), sizeof(int) * p1.size());
     memcpy(host.data() + p->off_p2, p2.data(), sizeof(int) * p2.size());
+    if (!ta.empty()) memcpy(host.data() + p->off_ta, ta.data(), sizeof(float) * ta.size());
+    if (!t1.empty()) memcpy(host.data() + p->off_t1, t1.data(), sizeof(float) * t1.size());
+    if (!t2.empty()) memcpy(host.data() + p->off_t2, t2.data(), sizeof(float) * t2.size());
+    if (!fblock.empty()) memcpy(host.data() + p->off_fb, fblock.data(), sizeof(int) * fblock.size());
+    if (!bf_of_f.empty()) memcpy(host.data() + p->off_bf, bf_of_f.data(), sizeof(int) * bf_of_f.size());
     CIP_TRY(p->buf.ensure(total));
     CIP_CHECK_CUDA(cudaMemcpyAsync(p->buf.p, host.data(), total, cudaMemcpyHostToDevice, ctx->stream));
     CIP_CHECK_CUDA(cudaStreamSynchronize(ctx->stream));  // `host` goes out of scope
@@ -446,11 +541,26 @@ static cip_status get_pfft(cip_ctx* ctx, int nu, int nv, int fp64, PfftPlan** ou
   return CIP_OK;
 }
 
-static int pfft_pitch(int ny) { return (ny + 15) & ~15; }
+static int pfft_pitch(int ny) { return (ny + 63) & ~63; }  // columns of the work area: whole tiles of up to 32 pairs
+// pairs per tile row of a column pass over n points: the widest tile whose two buffers stay within 48 KB
+static int cols_pairs(int n) { return 2 * (size_t)n * 32 * 16 <= 48 * 1024 ? 32 : (2 * (size_t)n * 16 * 16 <= 48 * 1024 ? 16 : 8); }
+// CIP_FFT=own: the own row pass too; default: cuFFT for the contiguous row pass, own column passes
+static bool pfft_hybrid() {
+  const char* e = getenv("CIP_FFT");
+  return !(e && strcmp(e, "own") == 0);
+}
 
 bool pfft_enabled() {
   const char* e = getenv("CIP_FFT");
   return !(e && strcmp(e, "cufft") == 0);
+}
+
+// 0: not available; 1: own row pass; 2: cuFFT row pass + own column passes (float32 only)
+static int pfft_variant(const PfftPlan* p, int fp64, int ny) {
+  if (!p->ok) return 0;
+  if (fp64) return p->ok_rows ? 1 : 0;
+  if (pfft_hybrid() && ny % 4 == 0) return 2;
+  return p->ok_rows ? 1 : (ny % 4 == 0 ? 2 : 0);
 }
 
 // Whether the own transform handles this plan (else the cuFFT path of image.cu / fft.cu runs); creates the tables.
@@ -459,8 +569,12 @@ cip_status pfft_prepare(cip_ctx* ctx, const cip_plan& pl, bool* ok) {
   if (!pfft_enabled()) return CIP_OK;
   PfftPlan* p;
   CIP_TRY(get_pfft(ctx, pl.nu, pl.nv, pl.accumulate_fp64, &p));
-  if (!p->ok) return CIP_OK;
+  const int variant = pfft_variant(p, pl.accumulate_fp64, pl.npix_y);
+  if (!variant) return CIP_OK;
+  // float64: only on request (CIP_FFT=own) -- its passes are the unpacked first version, not tuned
+  if (pl.accumulate_fp64 && pfft_hybrid()) return CIP_OK;
   CIP_TRY(ctx->fft_t.ensure((size_t)(pl.accumulate_fp64 ? 16 : 8) * pl.nu * pfft_pitch(pl.npix_y)));
+  if (variant == 2) CIP_TRY(fft_rows(ctx, nullptr, pl.nv, pl.nu, 0));  // the plan and its work area
   *ok = true;
   return CIP_OK;
 }
@@ -470,31 +584,79 @@ static cip_status pfft_plane(cip_ctx* ctx, PfftPlan* p, const void* plane, int n
   using C = cx<T>;
   const int pitch = pfft_pitch(ny);
   C* g = ctx->fft_t.as<C>();
-  const C* twv = reinterpret_cast<const C*>(static_cast<char*>(p->buf.p) + p->off_twv);
-  const C* twu = reinterpret_cast<const C*>(static_cast<char*>(p->buf.p) + p->off_twu);
-  const int* pa = reinterpret_cast<const int*>(static_cast<char*>(p->buf.p) + p->off_pa);
-  const int* p1 = reinterpret_cast<const int*>(static_cast<char*>(p->buf.p) + p->off_p1);
-  const int* p2 = reinterpret_cast<const int*>(static_cast<char*>(p->buf.p) + p->off_p2);
+  char* tb = static_cast<char*>(p->buf.p);
+  const C* twv = reinterpret_cast<const C*>(tb + p->off_twv);
+  const C* twu = reinterpret_cast<const C*>(tb + p->off_twu);
+  const int* pa = reinterpret_cast<const int*>(tb + p->off_pa);
+  const int* p1 = reinterpret_cast<const int*>(tb + p->off_p1);
+  const int* p2 = reinterpret_cast<const int*>(tb + p->off_p2);
   cudaStream_t st = ctx->stream;
-  {
-    // rows of up to 56 KB: four CTAs of 256 threads per SM; longer ones: one or two CTAs of 512
-    const bool small = p->smem_a <= 56 * 1024;
-    auto kern = small ? rows_kernel<T, 256> : rows_kernel<T, 512>;
-    CIP_CHECK_CUDA(cudaFuncSetAttribute(kern, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)p->smem_a));
-    kern<<<nu, small ? 256 : 512, p->smem_a, st>>>(static_cast<const C*>(plane), g, p->sa, twv, pa, nv, ny, pitch);
-  }
   const int ncb = pitch / 16;
-  {
-    auto kern = cols1_kernel<T>;
-    const size_t smem = (size_t)p->n1 * 16 * sizeof(C);
-    CIP_CHECK_CUDA(cudaFuncSetAttribute(kern, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem));
-    kern<<<dim3(ncb, p->n2), 128, smem, st>>>(g, p->s1, twu, p1, p->n2, ny, pitch);
-  }
-  {
-    auto kern = cols2_kernel<T, SCREEN>;
-    const size_t smem = (size_t)p->n2 * 16 * sizeof(C);
-    CIP_CHECK_CUDA(cudaFuncSetAttribute(kern, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem));
-    kern<<<dim3(ncb, p->n1), 128, smem, st>>>(g, p->s2, twu, p2, p->n1, pitch, sa, out);
+  const size_t smem1 = (size_t)p->n1 * 16 * sizeof(C), smem2 = (size_t)p->n2 * 16 * sizeof(C);
+  // rows of up to 56 KB: several CTAs of 256 threads per SM; longer ones: one or two CTAs of 512
+  const bool small = p->smem_a <= 56 * 1024;
+  if constexpr (sizeof(T) == 4) {
+    const float* ta = reinterpret_cast<const float*>(tb + p->off_ta);
+    const float2* t1 = reinterpret_cast<const float2*>(tb + p->off_t1);
+    const float2* t2 = reinterpret_cast<const float2*>(tb + p->off_t2);
+    // G as granules of two columns (pfft_f32.cuh); the column passes are persistent CTAs with double-buffered tiles
+    const int gpitch = pitch / 2;
+    float4* g4 = reinterpret_cast<float4*>(g);
+    const bool hybrid = pfft_variant(p, 0, ny) == 2;
+    if (hybrid) {
+      // pass A by cuFFT: contiguous 1-D transforms along v, in place (its single-pass kernel runs near the HBM rate;
+      // the own row pass of rows_kernel_p does not); pass B1 then reads the retained columns of the plane
+      CIP_TRY(fft_rows(ctx, const_cast<void*>(plane), nv, nu, 0));
+    } else {
+      const RowsAux aux{ta, reinterpret_cast<const int*>(tb + p->off_fb), reinterpret_cast<const int*>(tb + p->off_bf), p->wf};
+      auto ka = small ? rows_kernel_p<256> : rows_kernel_p<512>;
+      CIP_CHECK_CUDA(cudaFuncSetAttribute(ka, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)p->smem_a));
+      ka<<<nu, small ? 256 : 512, p->smem_a, st>>>(static_cast<const float2*>(plane), reinterpret_cast<float*>(g), p->sa, aux, nv, ny, gpitch);
+    }
+    const Cols1Src src{static_cast<const float2*>(plane), nv, ny};
+    auto launch1 = [&](auto kern, int P) -> cip_status {
+      const size_t smem = 2 * (size_t)p->n1 * P * sizeof(float4);
+      const int ncb = gpitch / P;
+      CIP_CHECK_CUDA(cudaFuncSetAttribute(kern, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem));
+      int per_sm = 1;
+      CIP_CHECK_CUDA(cudaOccupancyMaxActiveBlocksPerMultiprocessor(&per_sm, kern, 128, smem));
+      kern<<<std::min(ncb * p->n2, ctx->sm_count * std::max(per_sm, 1)), 128, smem, st>>>(g4, src, p->s1, t1, p1, twu, p->n2, ncb, gpitch);
+      return CIP_OK;
+    };
+    auto launch2 = [&](auto kern, int P) -> cip_status {
+      const size_t smem = 2 * (size_t)p->n2 * P * sizeof(float4);
+      const int ncb = gpitch / P;
+      CIP_CHECK_CUDA(cudaFuncSetAttribute(kern, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem));
+      int per_sm = 1;
+      CIP_CHECK_CUDA(cudaOccupancyMaxActiveBlocksPerMultiprocessor(&per_sm, kern, 128, smem));
+      kern<<<std::min(ncb * p->n1, ctx->sm_count * std::max(per_sm, 1)), 128, smem, st>>>(g4, p->s2, t2, p2, p->n1, ncb, gpitch, sa, out);
+      return CIP_OK;
+    };
+    const int P1 = cols_pairs(p->n1), P2 = cols_pairs(p->n2);
+    if (hybrid) {
+      if (P1 == 32) CIP_TRY(launch1(cols1_kernel_p<32, true>, 32));
+      else if (P1 == 16) CIP_TRY(launch1(cols1_kernel_p<16, true>, 16));
+      else CIP_TRY(launch1(cols1_kernel_p<8, true>, 8));
+    } else {
+      if (P1 == 32) CIP_TRY(launch1(cols1_kernel_p<32, false>, 32));
+      else if (P1 == 16) CIP_TRY(launch1(cols1_kernel_p<16, false>, 16));
+      else CIP_TRY(launch1(cols1_kernel_p<8, false>, 8));
+    }
+    if (P2 == 32) CIP_TRY(launch2(cols2_kernel_p<32, SCREEN>, 32));
+    else if (P2 == 16) CIP_TRY(launch2(cols2_kernel_p<16, SCREEN>, 16));
+    else CIP_TRY(launch2(cols2_kernel_p<8, SCREEN>, 8));
+    (void)pa;
+    (void)ncb;
+  } else {
+    auto ka = small ? rows_kernel<T, 256> : rows_kernel<T, 512>;
+    CIP_CHECK_CUDA(cudaFuncSetAttribute(ka, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)p->smem_a));
+    ka<<<nu, small ? 256 : 512, p->smem_a, st>>>(static_cast<const C*>(plane), g, p->sa, twv, pa, nv, ny, pitch);
+    auto k1 = cols1_kernel<T>;
+    CIP_CHECK_CUDA(cudaFuncSetAttribute(k1, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem1));
+    k1<<<dim3(ncb, p->n2), 128, smem1, st>>>(g, p->s1, twu, p1, p->n2, ny, pitch);
+    auto k2 = cols2_kernel<T, SCREEN>;
+    CIP_CHECK_CUDA(cudaFuncSetAttribute(k2, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem2));
+    k2<<<dim3(ncb, p->n1), 128, smem2, st>>>(g, p->s2, twu, p2, p->n1, pitch, sa, out);
   }
   ctx->launches += 3;
   CIP_CHECK_CUDA(cudaGetLastError());
@@ -505,7 +667,7 @@ static cip_status pfft_plane(cip_ctx* ctx, PfftPlan* p, const void* plane, int n
 cip_status run_pfft_screen(cip_ctx* ctx, const cip_plan& pl, void* grid, int plane_base, int nslots, void* image) {
   PfftPlan* p;
   CIP_TRY(get_pfft(ctx, pl.nu, pl.nv, pl.accumulate_fp64, &p));
-  CIP_REQUIRE(p->ok, "own transform not available for %d x %d", pl.nu, pl.nv);
+  CIP_REQUIRE(pfft_variant(p, pl.accumulate_fp64, pl.npix_y), "own transform not available for %d x %d", pl.nu, pl.nv);
   const size_t csize = pl.accumulate_fp64 ? 16 : 8;
   CIP_TRY(ctx->fft_t.ensure(csize * pl.nu * pfft_pitch(pl.npix_y)));
   for (int s = 0; s < nslots; ++s) {
@@ -532,7 +694,7 @@ extern "C" cip_status cip_plane_fft_crop(cip_ctx* ctx, const void* plane, int nu
   CIP_ENTER_DEVICE(ctx);
   PfftPlan* p;
   CIP_TRY(get_pfft(ctx, nu, nv, fp64, &p));
-  CIP_REQUIRE(p->ok, "own transform not available for %d x %d (fp64 = %d)", nu, nv, fp64);
+  CIP_REQUIRE(pfft_variant(p, fp64, ny), "own transform not available for %d x %d (fp64 = %d)", nu, nv, fp64);
   CIP_TRY(ctx->fft_t.ensure((size_t)(fp64 ? 16 : 8) * nu * pfft_pitch(ny)));
   ScreenArgs sa{nx, ny, nu, nv, 0.0, 0.0, 0.0, 0.0, 0, nullptr};
   if (fp64) CIP_TRY((pfft_plane<double, false>(ctx, p, plane, nu, nv, ny, sa, out)));

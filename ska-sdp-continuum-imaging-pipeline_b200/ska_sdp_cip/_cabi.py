@@ -215,12 +215,15 @@ def bin_inspect(ctx: "Context", args: InvertArgs, plan: Plan):
     return jobs, recs
 
 
-def plane_fft_crop(ctx: "Context", plane, nx: int, ny: int):
+def plane_fft_crop(ctx: "Context", plane, nx: int, ny: int, overwrite: bool = False):
     """Retained nx x ny cells of the unnormalised e^{+i} 2-D transform of a CUDA complex64 / complex128 plane
-    (torch tensor, shape (nu, nv)), in image order -- see cip_plane_fft_crop."""
+    (torch tensor, shape (nu, nv)), in image order -- see cip_plane_fft_crop.  The library works in place on the
+    plane; unless ``overwrite`` a copy is transformed."""
     import torch
     assert plane.is_cuda and plane.is_contiguous() and plane.dtype in (torch.complex64, torch.complex128)
     nu, nv = plane.shape
+    if not overwrite:
+        plane = plane.clone()
     out = torch.empty((nx, ny), dtype=plane.dtype, device=plane.device)
     torch.cuda.current_stream(plane.device).synchronize()
     with ctx.lock:

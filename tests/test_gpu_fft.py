@@ -1,5 +1,5 @@
-"""Stage G3 on its own: the pruned 2-D transform of csrc/pfft.cu (row pass, two column passes, crop in image
-order) against numpy's FFT on the same plane.  Unnormalised, exp(+i) sign -- what cuFFT's CUFFT_INVERSE gives and
+"""Stage G3 on its own: the pruned 2-D transform of csrc/pfft.cu (row pass -- cuFFT's or, CIP_FFT=own, the own one --
+two own column passes, crop in image order) against numpy's FFT on the same plane.  Unnormalised, exp(+i) sign -- what cuFFT's CUFFT_INVERSE gives and
 what the w-stacking algorithm of SURVEY.md appendix A needs.  Tolerances: float32 transforms of n points carry a
 relative rms error of a few 1e-7 (checked at 2e-6 of the output rms), float64 ones 1e-15 (checked at 1e-13)."""
 import numpy as np
@@ -31,10 +31,22 @@ SIZES = [(16, 16, 16, 16), (32, 64, 16, 32), (96, 128, 64, 80), (98, 150, 50, 74
          (686, 2 * 3 * 5 * 7 * 4, 300, 422), (1280, 2560, 1280, 2560)]
 
 
+@pytest.fixture(params=["default", "own"])
+def row_pass(request):
+    """default: cuFFT does the contiguous row pass (float32, image width a multiple of 4); own: rows_kernel_p."""
+    import os
+    if request.param == "own":
+        os.environ["CIP_FFT"] = "own"
+    yield request.param
+    os.environ.pop("CIP_FFT", None)
+
+
 @pytest.mark.parametrize("nu,nv,nx,ny", SIZES)
 @pytest.mark.parametrize("dtype,tol", [(np.complex64, 2e-6), (np.complex128, 1e-13)])
-def test_pruned_transform_matches_numpy(cabi, nu, nv, nx, ny, dtype, tol):
+def test_pruned_transform_matches_numpy(cabi, row_pass, nu, nv, nx, ny, dtype, tol):
     import torch
+    if dtype == np.complex128 and row_pass == "default":
+        pytest.skip("float64 planes always take the own row pass")
     rng = np.random.default_rng(nu * 131 + nv)
     plane = (rng.standard_normal((nu, nv)) + 1j * rng.standard_normal((nu, nv))).astype(dtype)
     ctx = cabi.Context.get(-1)
@@ -45,7 +57,7 @@ def test_pruned_transform_matches_numpy(cabi, nu, nv, nx, ny, dtype, tol):
     assert err <= tol, err
 
 
-def test_single_tone_lands_on_its_pixel(cabi):
+def test_single_tone_lands_on_its_pixel(cabi, row_pass):
     """A plane that is one complex exponential transforms to a single retained cell (indexing and sign)."""
     import torch
     nu, nv, nx, ny = 768, 640, 512, 320
@@ -61,7 +73,7 @@ def test_single_tone_lands_on_its_pixel(cabi):
     assert np.abs(out).max() <= 2e-4 * nu * nv
 
 
-def test_headline_plane_size(cabi):
+def test_headline_plane_size(cabi, row_pass):
     """The 6144^2 plane / 4096^2 image of BASELINE configs[1] (float32)."""
     import torch
     nu = nv = 6144
