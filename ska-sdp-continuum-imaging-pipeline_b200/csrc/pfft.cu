@@ -4,24 +4,27 @@
 // The image keeps nx x ny of the nu x nv cells of a transformed plane, so the transform is pruned and never
 // materialised:
 //
-//   pass A  (rows_kernel)   one CTA per grid row: the whole row of nv samples in shared memory, transformed along v,
-//                           only the ny retained columns written, in image order, to G[nu][pitch]
-//   pass B1 (cols1_kernel)  the transform along u as a four-step transform nu = n1 n2 on blocks of 16 neighbouring
-//                           columns (one 128-byte line per row): for every residue r, the n1-point transform over the
-//                           rows r + n2 k, times the step twiddle, in place
-//   pass B2 (cols2_kernel)  for every q, the n2-point transform over the n2 contiguous rows n2 q ..., whose outputs are
-//                           the frequencies q + n1 s; the retained ones are multiplied with the w-screen of the plane
-//                           and their real part is added to the image -- the transformed plane is never written
+//   pass A   the transform along v of every grid row.  Default (float32, image width a multiple of 4): cuFFT's
+//            contiguous 1-D transform in place -- its single-pass register-resident kernel runs at 4.4 TB/s on 6144-point
+//            rows, the own row pass below reaches half of that.  CIP_FFT=own / float64: rows_kernel(_p), one CTA per row,
+//            the whole row in shared memory, only the ny retained columns written, in image order, to the work area G.
+//   pass B1  (cols1_kernel) the transform along u as a four-step transform nu = n1 n2 on blocks of 16 to 64 neighbouring
+//            retained columns: for every residue r the n1-point transform over the rows r + n2 k, times the step
+//            twiddle; reads the plane (default) or G, writes G.
+//   pass B2  (cols2_kernel) for every q the n2-point transform over the n2 contiguous rows n2 q ..., whose outputs are
+//            the frequencies q + n1 s; the retained ones are multiplied with the w-screen of the plane and their real
+//            part is added to the image -- the transformed plane is never written.
 //
-// Per 6144^2 plane and a 4096^2 image that is 302 + 201 (A), 201 + 201 (B1), 201 + 2 x 67 (B2) = 1.24 GB against
-// 1.68 GB for cuFFT rows / transpose-crop / cuFFT rows / w-screen, in three launches; at 24576^2 cuFFT needs two
-// passes per dimension where pass A needs one.
+// Per 6144^2 plane and a 4096^2 image: 604 MB (cuFFT rows) + 201 + 201 (B1) + 201 + 2 x 67 (B2) = 1.34 GB in three
+// launches against 1.68 GB in four for cuFFT rows / transpose-crop / cuFFT rows / w-screen; measured 0.38 against
+// 0.43 ms per plane (configs[1]), 7.0 against 8.9 ms at 24576^2 (configs[3]).
 //
-// All three passes use the same in-place mixed-radix decimation-in-frequency transform in shared memory (radices
-// 16, 8, 4, 2, 3, 5, 7: every size good_size() produces): stage of span L and radix R:
+// The own passes use an in-place mixed-radix decimation-in-frequency transform in shared memory (radices 16, 8, 4, 2, 3,
+// 5, 7: every size good_size() produces): stage of span L and radix R:
 //     y_q[k] = (sum_r x[k + r L/R] w_R^{qr}) w_L^{qk}   stored at q L/R + k,   w_m = exp(+2 pi i / m)
-// after which position sum_s d_s n / (R_1 .. R_s) holds frequency d_1 + R_1 d_2 + R_1 R_2 d_3 + ... (a table).  Twiddles
-// come from one table of exp(2 pi i t / n) per dimension (w_L^k is looked up, its powers are multiplied up).
+// after which position sum_s d_s n / (R_1 .. R_s) holds frequency d_1 + R_1 d_2 + R_1 R_2 d_3 + ... (a table).  The
+// float32 passes (pfft_f32.cuh) work on packed pairs with per-stage twiddle tables; the float64 passes below are the
+// plain first version (one table of exp(2 pi i t / n) per dimension, powers multiplied up).
 #include <cmath>
 #include <cstdlib>
 #include <cstring>
