@@ -150,6 +150,18 @@ cip_status cip_scan(cip_ctx* ctx, const cip_invert_args* args, cip_scan_result* 
 cip_status cip_w_histogram(cip_ctx* ctx, const cip_invert_args* args, double wmin, double wmax, int nbins,
                            int64_t* counts_out);
 
+/* The same histogram for callers that cannot allocate device memory (code under CUDA graph capture, tight serving
+ * loops, harnesses that forbid cudaMalloc).  No counterpart in the reference.
+ * Device inputs only (args->memspace = 1, else CIP_EINVAL); counts_out is host memory, int64[nbins], counts
+ * ADDED.  The kernel's per-bin counters live in a static device array of CIP_W_HISTOGRAM_STATIC_MAX_BINS x 8 bytes
+ * (32 KB held by every GPU that loads the library, until exit): nbins beyond that is rejected with CIP_EINVAL.  The call
+ * makes no cudaMalloc / cudaFree and calls no allocating library routine (the first call on a device resolves the
+ * array's address).  All calls on a device share the array -- each call clears the bins it uses, and calls that overlap
+ * on the GPU (two contexts / streams of the same device at once) race. */
+#define CIP_W_HISTOGRAM_STATIC_MAX_BINS 4096
+cip_status cip_w_histogram_static(cip_ctx* ctx, const cip_invert_args* args, double wmin, double wmax, int nbins,
+                                  int64_t* counts_out);
+
 /* G1 binning + G2 gridding + G3 FFT + G4 w-screen: ADD the uncorrected dirty image of the
  * samples in args to `image` (device memory, (npix_x,npix_y) float32, or float64 when
  * plan->accumulate_fp64).  Linear in the samples, so shards may be reduced before

@@ -7,6 +7,7 @@
 #include <algorithm>
 #include <cstdlib>
 #include <cstring>
+#include <mutex>
 #include <vector>
 
 #include "geom.cuh"
@@ -186,6 +187,53 @@ cip_status run_w_histogram(cip_ctx* ctx, const DevInputs& in, double wmin, doubl
   return CIP_OK;
 }
 
+// ---- the |w| histogram without any allocation (cip_w_histogram_static) ----------------------------------------
+// Scratch of the histogram kernel: the per-bin counters, here in a file-scope array instead of a context buffer.  Every
+// GPU that loads the library holds these 32 KB until exit; all calls on a device share them.
+static_assert(kMaxWBins == CIP_W_HISTOGRAM_STATIC_MAX_BINS, "cip.h states the limit");
+static __device__ __align__(256) unsigned long long g_whist_scratch[kMaxWBins];
+
+// Device address of the array on the current device.  In host code `g_whist_scratch` is only a stand-in for the
+// symbol, not a device address: it is resolved once per device, with that device current.
+static cip_status whist_scratch_ptr(int device, unsigned long long** out) {
+  constexpr int kMaxDevices = 64;
+  static unsigned long long* ptrs[kMaxDevices] = {};
+  static std::mutex mu;
+  CIP_REQUIRE(device >= 0 && device < kMaxDevices, "device index %d out of range", device);
+  std::lock_guard<std::mutex> lock(mu);
+  if (!ptrs[device]) {
+    unsigned long long* p = nullptr;
+    CIP_CHECK_CUDA(cudaGetSymbolAddress(reinterpret_cast<void**>(&p), g_whist_scratch));
+    ptrs[device] = p;
+  }
+  *out = ptrs[device];
+  return CIP_OK;
+}
+
+cip_status run_w_histogram_static(cip_ctx* ctx, const DevInputs& in, double wmin, double wmax, int nbins, int64_t* counts_out) {
+  CIP_REQUIRE(nbins >= 1, "nbins must be positive");
+  CIP_REQUIRE(nbins <= kMaxWBins, "nbins = %d exceeds the %d bins of the static scratch array of cip_w_histogram_static", nbins,
+              kMaxWBins);
+  CIP_REQUIRE(wmax >= wmin, "bad |w| range");
+  unsigned long long* d = nullptr;
+  CIP_TRY(whist_scratch_ptr(ctx->device, &d));
+  cudaStream_t st = ctx->stream;
+  // the array keeps the counts of the previous call: clear the bins this call uses
+  CIP_CHECK_CUDA(cudaMemsetAsync(d, 0, sizeof(unsigned long long) * nbins, st));
+  if (in.nrow * in.nchan > 0) {
+    const double scale = wmax > wmin ? nbins / (wmax - wmin) : 0.0;
+    const int blocks = (int)std::min<int64_t>((in.nrow * 32 + 255) / 256, (int64_t)ctx->sm_count * 8);
+    whist_kernel<<<blocks, 256, 0, st>>>(in, wmin, scale, nbins, d);
+    ctx->launches++;
+    CIP_CHECK_CUDA(cudaGetLastError());
+  }
+  unsigned long long h[kMaxWBins];  // 32 KB of stack: no host allocation either
+  CIP_CHECK_CUDA(cudaMemcpyAsync(h, d, sizeof(unsigned long long) * nbins, cudaMemcpyDeviceToHost, st));
+  CIP_CHECK_CUDA(cudaStreamSynchronize(st));
+  for (int b = 0; b < nbins; ++b) counts_out[b] += (int64_t)h[b];
+  return CIP_OK;
+}
+
 cip_status run_scan(cip_ctx* ctx, const DevInputs& in, int do_wstacking, cip_scan_result* out) {
   NvtxRange nvtx("cip:scan");
   CIP_TRY(ctx->scan_out.ensure(sizeof(ScanOut)));
@@ -229,3 +277,17 @@ cip_status run_scan(cip_ctx* ctx, const DevInputs& in, int do_wstacking, cip_sca
 }
 
 }  // namespace cip
+
+// No counterpart in the reference: added for callers that cannot call
+// cudaMalloc (see include/cip.h).
+extern "C" cip_status cip_w_histogram_static(cip_ctx* ctx, const cip_invert_args* args, double wmin, double wmax, int nbins,
+                                             int64_t* counts_out) {
+  using namespace cip;
+  CIP_REQUIRE(ctx && counts_out, "NULL argument");
+  CIP_TRY(validate_args(args));
+  CIP_REQUIRE(args->memspace == 1, "cip_w_histogram_static takes device inputs only (memspace 1): staging host arrays allocates");
+  CIP_ENTER_DEVICE(ctx);
+  DevInputs in;
+  CIP_TRY(stage_inputs(ctx, args, &in, nullptr, false, nullptr));  // device inputs: pointers are taken as they are
+  return run_w_histogram_static(ctx, in, wmin, wmax, nbins, counts_out);
+}

@@ -93,6 +93,7 @@ def lib():
             L.cip_grid_accumulate.argtypes = [C.c_void_p, C.POINTER(InvertArgs), C.POINTER(Plan), C.c_void_p,
                                               C.POINTER(Report)]
             L.cip_w_histogram.argtypes = [C.c_void_p, C.POINTER(InvertArgs), C.c_double, C.c_double, C.c_int, C.c_void_p]
+            L.cip_w_histogram_static.argtypes = L.cip_w_histogram.argtypes
             L.cip_grid_accumulate_many.argtypes = [C.c_void_p, C.POINTER(InvertArgs), C.c_int, C.POINTER(Plan), C.c_void_p,
                                                    C.POINTER(Report)]
             L.cip_bin_inspect.argtypes = [C.c_void_p, C.POINTER(InvertArgs), C.POINTER(Plan), C.POINTER(C.c_int64),
@@ -117,7 +118,7 @@ def lib():
 
 
 EXPORTS = ["cip_last_error", "cip_version", "cip_ctx_create", "cip_ctx_destroy", "cip_ctx_stream",
-           "cip_ctx_synchronize", "cip_ctx_launches", "cip_ctx_device", "cip_current_device", "cip_plan_make", "cip_kernel_table", "cip_kernel_ft", "cip_scan", "cip_w_histogram",
+           "cip_ctx_synchronize", "cip_ctx_launches", "cip_ctx_device", "cip_current_device", "cip_plan_make", "cip_kernel_table", "cip_kernel_ft", "cip_scan", "cip_w_histogram", "cip_w_histogram_static",
            "cip_grid_accumulate", "cip_grid_accumulate_many", "cip_bin_inspect", "cip_plane_fft_crop", "cip_correct_image", "cip_invert", "cip_stokes_i", "cip_stokes_i_async", "cip_tile_bin",
            "cip_tile_fetch", "cip_tile_gather", "cip_tile_free"]
 
