@@ -413,7 +413,7 @@ def run_b200(args):
         "ms_bin": nvis * (12 + 16) + 2 * nrow_ * 24,                          # samples read once, 16-byte records written
         "ms_zero": npl_ * nu_ * nv_ * 8,
         "ms_grid": int(alg_bytes),
-        "ms_fft": npl_ * (2 * nu_ * nv_ * 8 + 4 * N * nu_ * 8 + N * N * 16),  # v pass, transpose-crop, u pass, w-screen
+        "ms_fft": npl_ * (2 * nu_ * nv_ * 8 + 3 * N * nu_ * 8 + 2 * N * N * 4),  # v pass in place, pruned u passes, w-screen
         "ms_correct": 2 * N * N * 4,
     }
     roofline_stages = {k: {"ms": stage[k], "algorithmic_bytes": int(b),
