@@ -37,12 +37,11 @@ __global__ void finv_kernel(const double* __restrict__ freq, int64_t nchan, doub
 }
 
 // ---- pass 1: histogram of the keys ------------------------------------------------------------------------
-__global__ void __launch_bounds__(256) hist_kernel(DevInputs in, GridGeom g, const double* __restrict__ finv,
+__global__ void __launch_bounds__(256) hist_kernel(DevInputs in, GridGeom g, BinConsts kc, const double* __restrict__ finv,
                                                    uint32_t* __restrict__ table) {
   const int lane = threadIdx.x & 31;
   const int64_t row = ((int64_t)blockIdx.x * blockDim.x + threadIdx.x) >> 5;
   if (row >= in.nrow) return;
-  const BinConsts kc = bin_consts(g);
   const RowGeom rg = row_geom(g, in.uvw[3 * row], in.uvw[3 * row + 1], in.uvw[3 * row + 2]);
   const RowSpan sp = row_span(in, row);
   for (int c0 = sp.c_begin & ~31; c0 < sp.c_end; c0 += 32) {
@@ -287,14 +286,13 @@ __global__ void __launch_bounds__(256) items_kernel(Job* __restrict__ jobs, cons
 // ---- pass 3: records --------------------------------------------------------------------------------------
 // One warp per row, lanes stride the channels.  Reads are row-contiguous; a segment's records are contiguous.
 template <typename R, bool PACK, bool WIDE>
-__global__ void __launch_bounds__(256, 6) records_kernel(DevInputs in, GridGeom g, const double* __restrict__ finv,
+__global__ void __launch_bounds__(256, 6) records_kernel(DevInputs in, GridGeom g, BinConsts kc, const double* __restrict__ finv,
                                                          uint32_t* __restrict__ table, const BinHeader* __restrict__ hdr,
                                                          Rec<R>* __restrict__ recs) {
   if (hdr->overflow) return;
   const int lane = threadIdx.x & 31;
   const int64_t row = ((int64_t)blockIdx.x * blockDim.x + threadIdx.x) >> 5;
   if (row >= in.nrow) return;
-  const BinConsts kc = bin_consts(g);
   const RowGeom rg = row_geom(g, in.uvw[3 * row], in.uvw[3 * row + 1], in.uvw[3 * row + 2]);
   const RowSpan sp = row_span(in, row);
   for (int c0 = sp.c_begin & ~31; c0 < sp.c_end; c0 += 32) {
@@ -341,7 +339,7 @@ __global__ void __launch_bounds__(256, 6) records_kernel(DevInputs in, GridGeom 
       if (s.flip) im = -im;
       if (g.do_wstacking && g.nshift != 0.0) {  // V' = V exp(+2 pi i w s); phase reduced in float64
         double ph = s.w * g.nshift;
-        ph -= rint(ph);
+        ph -= rint_magic(ph);
         R sn, cs;
         if constexpr (sizeof(R) == 4) sincospif(2.0f * (float)ph, &sn, &cs);
         else sincospi(2.0 * ph, &sn, &cs);
@@ -439,7 +437,8 @@ cip_status run_binning(cip_ctx* ctx, int slot, const DevInputs& in, const GridGe
   }
   finv_kernel<<<nblk(nchan, 256), 256, 0, st>>>(in.freq, nchan, finv);
   const int rblocks = nblk(nrow * 32, 256);
-  hist_kernel<<<rblocks, 256, 0, st>>>(in, g, finv, table);
+  const BinConsts kc = bin_consts(g);
+  hist_kernel<<<rblocks, 256, 0, st>>>(in, g, kc, finv, table);
   scan_reduce_kernel<<<(unsigned)ntiles, kScanThreads, 0, st>>>(table, n, w.tile_sums.as<uint2>());
   scan_tiles_kernel<<<1, 1024, 0, st>>>(w.tile_sums.as<uint2>(), ntiles, hdr, (uint32_t)std::min<int64_t>(w.cap_groups, 0xffffffffll),
                                         (uint32_t)std::min<int64_t>(w.cap_jobs, 0xffffffffll), ctx->call_flags.as<uint32_t>(),
@@ -448,15 +447,15 @@ cip_status run_binning(cip_ctx* ctx, int slot, const DevInputs& in, const GridGe
   if (pack) {
     scan_apply_kernel<16><<<(unsigned)ntiles, kScanThreads, 0, st>>>(table, n, w.tile_sums.as<uint2>(), hdr, g, epw, w.jobs.as<Job>(),
                                                                      w.recs.as<unsigned char>(), wjs);
-    if (in.wide) records_kernel<float, true, true><<<rblocks, 256, 0, st>>>(in, g, finv, table, hdr, w.recs.as<Rec<float>>());
-    else records_kernel<float, true, false><<<rblocks, 256, 0, st>>>(in, g, finv, table, hdr, w.recs.as<Rec<float>>());
+    if (in.wide) records_kernel<float, true, true><<<rblocks, 256, 0, st>>>(in, g, kc, finv, table, hdr, w.recs.as<Rec<float>>());
+    else records_kernel<float, true, false><<<rblocks, 256, 0, st>>>(in, g, kc, finv, table, hdr, w.recs.as<Rec<float>>());
   } else {
     scan_apply_kernel<32><<<(unsigned)ntiles, kScanThreads, 0, st>>>(table, n, w.tile_sums.as<uint2>(), hdr, g, epw, w.jobs.as<Job>(),
                                                                      w.recs.as<unsigned char>(), wjs);
-    if (fp64 && in.wide) records_kernel<double, false, true><<<rblocks, 256, 0, st>>>(in, g, finv, table, hdr, w.recs.as<Rec<double>>());
-    else if (fp64) records_kernel<double, false, false><<<rblocks, 256, 0, st>>>(in, g, finv, table, hdr, w.recs.as<Rec<double>>());
-    else if (in.wide) records_kernel<float, false, true><<<rblocks, 256, 0, st>>>(in, g, finv, table, hdr, w.recs.as<Rec<float>>());
-    else records_kernel<float, false, false><<<rblocks, 256, 0, st>>>(in, g, finv, table, hdr, w.recs.as<Rec<float>>());
+    if (fp64 && in.wide) records_kernel<double, false, true><<<rblocks, 256, 0, st>>>(in, g, kc, finv, table, hdr, w.recs.as<Rec<double>>());
+    else if (fp64) records_kernel<double, false, false><<<rblocks, 256, 0, st>>>(in, g, kc, finv, table, hdr, w.recs.as<Rec<double>>());
+    else if (in.wide) records_kernel<float, false, true><<<rblocks, 256, 0, st>>>(in, g, kc, finv, table, hdr, w.recs.as<Rec<float>>());
+    else records_kernel<float, false, false><<<rblocks, 256, 0, st>>>(in, g, kc, finv, table, hdr, w.recs.as<Rec<float>>());
   }
   ctx->launches += 6;
   if (want_items) {

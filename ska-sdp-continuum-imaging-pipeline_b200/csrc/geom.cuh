@@ -22,7 +22,9 @@ struct BinConsts {
   int snap, pmax;
   bool fast;                        // W <= kFastSupport: windows and register-window lattice in use
 };
-__device__ __forceinline__ BinConsts bin_consts(const GridGeom& g) {
+// Computed once on the host and passed to the kernels by value: evaluated per thread it cost more instructions (a 64-bit
+// division among them) than the two loop iterations a 64-channel row needs.
+__host__ __device__ __forceinline__ BinConsts bin_consts(const GridGeom& g) {
   BinConsts k;
   k.nu_d = (double)g.nu;
   k.nv_d = (double)g.nv;
@@ -59,37 +61,50 @@ __device__ __forceinline__ RowGeom row_geom(const GridGeom& g, double um, double
 // ducc0.wgridder.ms2dirty implements (reference call site src/ska_sdp_cip/invert.py:170-183).
 // All coordinate arithmetic is float64: grid indices reach 65536 and need ~1e-6 cell accuracy.
 // finv = frequency / c (tabulated once per call).  FRAC = false skips the fractional offsets (key passes).
+// Rounding without the conversion unit: FRND.F64 / F2I.F64 issue at a quarter of the FP64 add rate and the binning passes
+// are bound by instruction issue.  x + 1.5 * 2^52 rounds x to the nearest integer (ties to even, exact for |x| < 2^51)
+// and leaves it, as a two's-complement int, in the low word of the sum.
+constexpr double kRoundMagic = 6755399441055744.0;
+__device__ __forceinline__ double rint_magic(double x) { return (x + kRoundMagic) - kRoundMagic; }
+// ceil(x) as int (|x| < 2^31) and, in *frac, ceil(x) - x (one rounding, as the direct difference has)
+__device__ __forceinline__ int ceil_magic(double x, double* frac) {
+  const double t = x + kRoundMagic, r = t - kRoundMagic;  // r = rint(x)
+  const bool up = r < x;
+  *frac = (r - x) + (up ? 1.0 : 0.0);  // r - x is exact
+  return __double2loint(t) + (up ? 1 : 0);
+}
+
 template <bool FRAC>
 __device__ __forceinline__ SampleGeom sample_geom(const GridGeom& g, const BinConsts& k, const RowGeom& r, double finv) {
   SampleGeom s;
   s.flip = r.flip;
   double xu = r.upx * finv;
-  xu -= rint(xu);
+  xu -= rint_magic(xu);
   double xv = r.vpy * finv;
-  xv -= rint(xv);
+  xv -= rint_magic(xv);
   const double us = fma(xu, k.nu_d, k.off_u), vs = fma(xv, k.nv_d, k.off_v);
-  const double ci = ceil(us), cj = ceil(vs);
-  s.i0 = (int)ci;
-  s.j0 = (int)cj;
+  double du, dv;
+  s.i0 = ceil_magic(us, &du);
+  s.j0 = ceil_magic(vs, &dv);
   s.w = r.wabs * finv;
   if (FRAC) {
-    s.dfu = ci - us;
-    s.dfv = cj - vs;
+    s.dfu = du;
+    s.dfv = dv;
     s.fu = (float)s.dfu;
     s.fv = (float)s.dfv;
   }
   if (g.do_wstacking) {
     const double ps = fma(s.w, k.w_scale, k.w_off);
-    double cp = ceil(ps);
-    int p0 = (int)cp;
+    double dp;
+    int p0 = ceil_magic(ps, &dp);
     // samples outside the scanned w range are inactive (zero weight); keep their window legal
     if (p0 < 0 || p0 > k.pmax) {
       p0 = p0 < 0 ? 0 : k.pmax;
-      cp = (double)p0;
+      dp = (double)p0 - ps;
     }
     s.p0 = p0;
     if (FRAC) {
-      s.dfw = fmin(fmax(cp - ps, 0.0), 1.0);
+      s.dfw = fmin(fmax(dp, 0.0), 1.0);
       s.fw = (float)s.dfw;
     }
   } else {
@@ -185,8 +200,8 @@ __device__ __forceinline__ double es_kernel(double x, double beta_w) {
   return t >= 0.0 ? exp(beta_w * (sqrt(t) - 1.0)) : 0.0;
 }
 
-__device__ __forceinline__ uint64_t to_fix18(double f) {
-  const uint32_t q = (uint32_t)(f * kFix18 + 0.5);
+__device__ __forceinline__ uint64_t to_fix18(double f) {  // f in [0, 1]: round(f 2^18), without the conversion unit
+  const uint32_t q = (uint32_t)__double2loint(fma(f, kFix18, kRoundMagic));
   return q > 262143u ? 262143u : q;
 }
 __device__ __forceinline__ uint32_t to_fix32(double f) {
