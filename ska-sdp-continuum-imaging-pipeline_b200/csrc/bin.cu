@@ -338,11 +338,13 @@ __global__ void __launch_bounds__(256, 6) records_kernel(DevInputs in, GridGeom 
       im = (R)((P)v.y * (P)wgt);
       if (s.flip) im = -im;
       if (g.do_wstacking && g.nshift != 0.0) {  // V' = V exp(+2 pi i w s); phase reduced in float64
-        double ph = s.w * g.nshift;
-        ph -= rint_magic(ph);
+        const double ph = s.w * g.nshift;
         R sn, cs;
-        if constexpr (sizeof(R) == 4) sincospif(2.0f * (float)ph, &sn, &cs);
-        else sincospi(2.0 * ph, &sn, &cs);
+        if constexpr (sizeof(R) == 4) {
+          sincos_turns(ph, &sn, &cs);
+        } else {
+          sincospi(2.0 * (ph - rint_magic(ph)), &sn, &cs);
+        }
         const R t = re * cs - im * sn;
         im = re * sn + im * cs;
         re = t;
