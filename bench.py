@@ -425,9 +425,20 @@ def run_b200(args):
     rate_dev = nvis * args.steps / ms_dev / 1e3 if world == 1 else None       # Mvis/s of one GPU's share
     invert_roofline_mvis = nvis / (b_alg / (peak * 1e9)) / 1e6
     sm_hz = 1e6 * float((clocks or {}).get("sm_mhz") or 1965.0)
+    # operand form of the tensor path (grid.cu: two-term bfloat16 where the plan's kernel error is >= 5e-6, else 3xTF32)
+    import ctypes as _C
+    from ska_sdp_cip import _cabi
+    _beta, _err = _C.c_double(), _C.c_double()
+    _cabi.lib().cip_kernel_table(float(plan["sigma"]), int(plan["support"]), _C.byref(_beta), _C.byref(_err))
+    mma_mode = int(os.environ.get("CIP_GRID_MMA", "2" if _err.value >= 5e-6 else "1"))
+    n_mma = {1: 24.0, 2: 16.0}.get(mma_mode)      # mma.sync per group of 8 visibilities (8 tiles x 3 or 2 products)
+    k_mma = {1: 8, 2: 16}.get(mma_mode)
     grid_compute = {
-        "tflops_3xtf32": nvis * 3 * 2 * 1024 / (stage["ms_grid"] * 1e-3) / 1e12,       # 8 x 8 x 8 window x (re, im), three split products
-        "tensor_pipe_frac": nvis * 24.0 / (4 * 148 * sm_hz * stage["ms_grid"] * 1e-3),  # 24 mma.sync cycles per visibility and SMSP
+        "operands": {0: "FFMA2 rank-1 updates", 1: "3xTF32 (m16n8k8)", 2: "two-term bfloat16 (m16n8k16)"}.get(mma_mode),
+        # 8 x 8 x 8 window x (re, im) per visibility: tensor-core flops actually issued for it
+        "tensor_tflops": (nvis / 8 * n_mma * 2 * 16 * 8 * k_mma / (stage["ms_grid"] * 1e-3) / 1e12) if n_mma else None,
+        # 8 cycles per mma.sync and sub-partition (tools/experiments/mma_rate.cu, both shapes)
+        "tensor_pipe_frac": (nvis / 8 * n_mma * 8.0 / (4 * 148 * sm_hz * stage["ms_grid"] * 1e-3)) if n_mma else None,
     }
     # ---- CPU baseline on a bounded sample -----------------------------------------------------
     cpu = None
@@ -457,7 +468,7 @@ def run_b200(args):
                              ("ms_h2d", "ms_scan", "ms_bin", "ms_grid", "ms_fft", "ms_d2h", "ms_total")}
                 if host_reports else None},
         "gpu_launches": int(launches),
-        "roofline": {"bound": "hbm", "kernel": "grid_warp_kernel<1, true, 1>", "achieved": achieved, "peak": peak,
+        "roofline": {"bound": "hbm", "kernel": "grid_warp_kernel<%d>" % mma_mode, "achieved": achieved, "peak": peak,
                      "unit": "GB/s", "frac": achieved / peak, "traffic": ncu_traffic(), "peak_source": peak_kind,
                      "ms_per_launch": ms_grid, "algorithmic_bytes": int(alg_bytes), "compute": grid_compute,
                      "invert": {"B_alg_bytes": int(b_alg), "roofline_mvis_per_gpu": invert_roofline_mvis,

@@ -209,6 +209,7 @@ struct GridGeom {
   int win_begin, win_end; // windows binned by the current pass (keys of other windows are skipped)
   int do_wstacking;
   float beta_w;           // beta * W
+  int bf16_operands;      // float32 tensor path: the kernel's own error (>= 5e-6) allows two-term bfloat16 operands
   double beta_wd;         // the same in float64 (float64 path)
 };
 

@@ -493,6 +493,25 @@ __device__ __forceinline__ void mma_tf32_first(float (&d)[4], const uint32_t (&a
                : "=f"(d[0]), "=f"(d[1]), "=f"(d[2]), "=f"(d[3])
                : "r"(a[0]), "r"(a[1]), "r"(a[2]), "r"(a[3]), "r"(b0), "r"(b1), "f"(0.0f));
 }
+// Two-term bfloat16 split (MMA = 2): x = hi + lo, both rounded to nearest, |x - hi - lo| <= 2^-18 |x|.  One m16n8k16 holds both terms of the 8 visibilities of a group
+// along k -- slots 2t, 2t+1 = hi terms of the visibilities t and t + 4, slots 2t+8, 2t+9 = their lo terms -- so
+// (A_hi + A_lo) B_hi is ONE instruction (b0 = b1) and (A_hi + A_lo) B_lo a second: 16 instead of 24 tensor
+// instructions per group at the same issue rate (tools/experiments/mma_rate.cu).
+__device__ __forceinline__ void mma_bf16(float (&d)[4], const uint32_t (&a)[4], uint32_t b) {
+  asm("mma.sync.aligned.m16n8k16.row.col.f32.bf16.bf16.f32 {%0,%1,%2,%3}, {%4,%5,%6,%7}, {%8,%8}, {%0,%1,%2,%3};"
+      : "+f"(d[0]), "+f"(d[1]), "+f"(d[2]), "+f"(d[3])
+      : "r"(a[0]), "r"(a[1]), "r"(a[2]), "r"(a[3]), "r"(b));
+}
+__device__ __forceinline__ void mma_bf16_first(float (&d)[4], const uint32_t (&a)[4], uint32_t b) {
+  asm("mma.sync.aligned.m16n8k16.row.col.f32.bf16.bf16.f32 {%0,%1,%2,%3}, {%4,%5,%6,%7}, {%8,%8}, {%9,%9,%9,%9};"
+      : "=f"(d[0]), "=f"(d[1]), "=f"(d[2]), "=f"(d[3])
+      : "r"(a[0]), "r"(a[1]), "r"(a[2]), "r"(a[3]), "r"(b), "f"(0.0f));
+}
+__device__ __forceinline__ uint32_t bf16_rn_pair(float lo, float hi) {
+  uint32_t d;
+  asm("cvt.rn.bf16x2.f32 %0, %1, %2;" : "=r"(d) : "f"(hi), "f"(lo));
+  return d;
+}
 template <int OFF>
 __device__ __forceinline__ float2 lds_f2(uint32_t addr) {
   float2 v;
@@ -502,6 +521,12 @@ __device__ __forceinline__ float2 lds_f2(uint32_t addr) {
 __device__ __forceinline__ float lds_f32(uint32_t addr) {
   float v;
   asm volatile("ld.shared.f32 %0, [%1];" : "=f"(v) : "r"(addr));
+  return v;
+}
+template <int OFF>
+__device__ __forceinline__ float lds_f32o(uint32_t addr) {
+  float v;
+  asm volatile("ld.shared.f32 %0, [%1+%2];" : "=f"(v) : "r"(addr), "n"(OFF));
   return v;
 }
 
@@ -548,8 +573,12 @@ struct WarpAcc {
   // visibility pq, kuoff = byte offset of ku[a] in it.  The products are born in the registers the A fragments
   // need (aligned quads), so nothing is moved.
   // (v = 2m, 2m+1) of the visibilities pq (pp) and pq + 4 (qq) as packed float32 pairs
-  __device__ __forceinline__ static void load_product_pairs(uint32_t pam, uint32_t kuoff, u64 (&pp)[4], u64 (&qq)[4]) {
-    const u64 kup = dup2(lds_f32(pam + kuoff)), kuq = dup2(lds_f32(pam + kuoff + 4 * kKRow));
+  // Addresses of a group (tensor path): pA = factor row of visibility pq, pK = pA + the byte offset of ku[a] in it --
+  // the even-plane column n = a of the B row sits at the same offset of ITS row, i.e. at pK + kBStage -- and pB1 =
+  // column n = a of the odd-plane block.  Three registers, advanced per group; every load is [register + immediate].
+  static constexpr int kBStage = kBatch * kKRow;  // B stage behind the factor stage
+  __device__ __forceinline__ static void load_product_pairs(uint32_t pam, uint32_t pK, u64 (&pp)[4], u64 (&qq)[4]) {
+    const u64 kup = dup2(lds_f32o<0>(pK)), kuq = dup2(lds_f32o<4 * kKRow>(pK));
     const float4 p0 = lds_f4<16>(pam), p1 = lds_f4<32>(pam);
     const float4 q0 = lds_f4<4 * kKRow + 16>(pam), q1 = lds_f4<4 * kKRow + 32>(pam);
     pp[0] = fmul2(kup, pack2(p0.x, p0.y)); pp[1] = fmul2(kup, pack2(p0.z, p0.w));
@@ -559,14 +588,14 @@ struct WarpAcc {
   }
   // Products, operand split and the float32 addition of the tiles work on packed pairs (FMUL2 / FADD2): the pairs
   // (v = 2 mt, 2 mt + 1) and (re, im) are exactly the register pairs of the fragments.
-  __device__ __forceinline__ void update_mma(uint32_t pam, uint32_t kuoff, uint32_t pbm0, uint32_t pbm1) {
+  __device__ __forceinline__ void update_mma(uint32_t pam, uint32_t pK, uint32_t pbm1) {
     u64 pp[4], qq[4];
-    load_product_pairs(pam, kuoff, pp, qq);
+    load_product_pairs(pam, pK, pp, qq);
     uint32_t bh[2][2], bl[2][2];
-    tf32_split(lds_f32(pbm0), bh[0][0], bl[0][0]);
-    tf32_split(lds_f32(pbm0 + 4 * kBRow), bh[0][1], bl[0][1]);
-    tf32_split(lds_f32(pbm1), bh[1][0], bl[1][0]);
-    tf32_split(lds_f32(pbm1 + 4 * kBRow), bh[1][1], bl[1][1]);
+    tf32_split(lds_f32o<kBStage>(pK), bh[0][0], bl[0][0]);
+    tf32_split(lds_f32o<kBStage + 4 * kBRow>(pK), bh[0][1], bl[0][1]);
+    tf32_split(lds_f32o<0>(pbm1), bh[1][0], bl[1][0]);
+    tf32_split(lds_f32o<4 * kBRow>(pbm1), bh[1][1], bl[1][1]);
     // two row tiles at a time: four independent accumulation chains (a dependent mma.sync issued after only
     // one other instruction of the tensor pipe waits for its accumulator)
 #pragma unroll
@@ -591,6 +620,53 @@ struct WarpAcc {
             if (term == 0) mma_tf32_first(d[m][nt], al[m], bh[nt][0], bh[nt][1]);
             else if (term == 1) mma_tf32(d[m][nt], ah[m], bl[nt][0], bl[nt][1]);
             else mma_tf32(d[m][nt], ah[m], bh[nt][0], bh[nt][1]);
+          }
+#pragma unroll
+      for (int m = 0; m < 2; ++m)
+#pragma unroll
+        for (int nt = 0; nt < 2; ++nt) {
+          c[2 * (mp + m)][nt] = fadd2(c[2 * (mp + m)][nt], pack2(d[m][nt][0], d[m][nt][1]));
+          c[2 * (mp + m) + 1][nt] = fadd2(c[2 * (mp + m) + 1][nt], pack2(d[m][nt][2], d[m][nt][3]));
+        }
+    }
+  }
+  // The same update with two-term bfloat16 operands (see mma_bf16): 16 tensor instructions per group.
+  // x = (x0, x1), y = (y0, y1): h0 = (x0, y0), h1 = (x1, y1) as bf16 pairs rounded to nearest, l0 / l1 the bf16 pairs
+  // of their residuals (a truncated hi term -- one PRMT, a mask for the residual -- measured 0.1 ms faster and twice
+  // the error: 5.5e-6 against 2.8e-6 relative rms, tests/accuracy_modes.py).
+  __device__ __forceinline__ static void bf16_split(u64 x, u64 y, uint32_t& h0, uint32_t& h1, uint32_t& l0, uint32_t& l1) {
+    uint32_t x0, x1, y0, y1;
+    unpack2u(x, x0, x1);
+    unpack2u(y, y0, y1);
+    h0 = bf16_rn_pair(__uint_as_float(x0), __uint_as_float(y0));
+    h1 = bf16_rn_pair(__uint_as_float(x1), __uint_as_float(y1));
+    const u64 lp = fsub2(x, pack2(__uint_as_float(h0 << 16), __uint_as_float(h1 << 16)));
+    const u64 lq = fsub2(y, pack2(__uint_as_float(h0 & 0xffff0000u), __uint_as_float(h1 & 0xffff0000u)));
+    const float2 rp = unpack2(lp), rq = unpack2(lq);
+    l0 = bf16_rn_pair(rp.x, rq.x);
+    l1 = bf16_rn_pair(rp.y, rq.y);
+  }
+  __device__ __forceinline__ void update_mma_bf16(uint32_t pam, uint32_t pK, uint32_t pbm1) {
+    u64 pp[4], qq[4];
+    load_product_pairs(pam, pK, pp, qq);
+    uint32_t bh[2], bl[2];
+    // B: (even block of visibility pq, odd block of pq) and the same of visibility pq + 4
+    bf16_split(pack2(lds_f32o<kBStage>(pK), lds_f32o<0>(pbm1)),
+                   pack2(lds_f32o<kBStage + 4 * kBRow>(pK), lds_f32o<4 * kBRow>(pbm1)), bh[0], bh[1], bl[0], bl[1]);
+#pragma unroll
+    for (int mp = 0; mp < 4; mp += 2) {
+      uint32_t af[2][4];
+#pragma unroll
+      for (int m = 0; m < 2; ++m) bf16_split(pp[mp + m], qq[mp + m], af[m][0], af[m][1], af[m][2], af[m][3]);
+      float d[2][2][4];
+#pragma unroll
+      for (int term = 0; term < 2; ++term)
+#pragma unroll
+        for (int m = 0; m < 2; ++m)
+#pragma unroll
+          for (int nt = 0; nt < 2; ++nt) {
+            if (term == 0) mma_bf16_first(d[m][nt], af[m], bl[nt]);
+            else mma_bf16(d[m][nt], af[m], bh[nt]);
           }
 #pragma unroll
       for (int m = 0; m < 2; ++m)
@@ -726,7 +802,7 @@ __device__ __forceinline__ void grid_warp_item(const Item& item, const RecP* __r
   const uint32_t pb0 = sB + (pq < 2 ? pq * 8 : 48 + pq * 8), pb10 = sB + 16 + pq * 8;
   // tensor path: rows of visibilities pq and pq + 4 of a group, column n = a of the B blocks
   const uint32_t pam0 = sA + pq * kKRow;
-  const uint32_t pbm00 = sB + pq * kBRow + 4 * (a < 4 ? a : 12 + a), pbm10 = sB + pq * kBRow + 4 * (4 + a);
+  const uint32_t pbm10 = sB + pq * kBRow + 4 * (4 + a);  // (the even block's column sits at pam0 + kuoff + kBStage)
   WarpAcc acc;
   acc.clear();
   WarpCells cells;
@@ -785,27 +861,59 @@ __device__ __forceinline__ void grid_warp_item(const Item& item, const RecP* __r
     }
     __syncwarp();
     // ---------------- consume: lane = (a, bh, ph) ----------------
-    {
-      WarpOps x;
-      if (!MMA) x = warp_load<0, false>(pa0, 0u, pb0, pb10);
+    if constexpr (MMA != 0) {
+      // Tensor path.  Every key is padded to whole k-groups (bin.cu), so a window moves at a group start: fold there
+      // and keep the group on the tensor cores.  The three group addresses live in registers the compiler may not
+      // re-derive (it used to rebuild them from the thread index for every group: 20 of ~110 instructions).
+      uint32_t pA = pam0, pK = pam0 + kuoff, pB1 = pbm10;
 #pragma unroll 1
       for (int k0 = 0; k0 < kBatch; k0 += 8) {
-        const uint32_t pa = pa0 + k0 * ROW, pkv = pkv0 + k0 * ROW, pb = pb0 + k0 * kBRow, pb1 = pb10 + k0 * kBRow;
+        asm volatile("" : "+r"(pA), "+r"(pK), "+r"(pB1));
+        const uint32_t m8 = (moved >> k0) & 0xffu;
+        if (m8 & 1u) {
+          acc.fold(sink, cells.i, cells.wj, pq);
+          cells.set(lds_u32(sOrg + 4 * k0), a);
+        }
+        if ((m8 & ~1u) == 0) {
+          if (MMA >= 2) acc.update_mma_bf16(pA, pK, pB1);
+          else acc.update_mma(pA, pK, pB1);
+        } else {
+          // a window moves inside the group (records that do not come from bin.cu's padded keys): rank-1 updates
+          const uint32_t pa = pa0 + k0 * ROW, pkv = pkv0 + k0 * ROW, pb = pb0 + k0 * kBRow, pb1 = pb10 + k0 * kBRow;
+          WarpOps x = warp_load<0, FACT>(pa, pkv, pb, pb1);
+#pragma unroll 1
+          for (int u = 0; u < 8; ++u) {
+            const WarpOps nxt = warp_load<1, FACT>(pa + u * ROW, pkv + u * ROW, pb + u * kBRow, pb1 + u * kBRow);
+            if (u && ((m8 >> u) & 1u)) {
+              acc.fold(sink, cells.i, cells.wj, pq);
+              cells.set(lds_u32(sOrg + 4 * (k0 + u)), a);
+            }
+            acc.update(x);
+            x = nxt;
+          }
+        }
+        pA += 8 * kKRow;
+        pK += 8 * kKRow;
+        pB1 += 8 * kBRow;
+      }
+    } else {
+      WarpOps x = warp_load<0, false>(pa0, 0u, pb0, pb10);
+#pragma unroll 1
+      for (int k0 = 0; k0 < kBatch; k0 += 8) {
+        const uint32_t pa = pa0 + k0 * ROW, pb = pb0 + k0 * kBRow, pb1 = pb10 + k0 * kBRow;
         const uint32_t porg = sOrg + 4 * k0;
         const uint32_t m8 = (moved >> k0) & 0xffu;
         // most groups stay inside one register window: branch-free fast path.  The operands of visibility
         // k0 + 8 are prefetched at the end of a group; past the last group that reads the rows after the
         // stage (still inside the CTA's shared memory: kSlack), which are discarded.
         if (m8 == 0) {
-          if (MMA) acc.update_mma(pam0 + k0 * kKRow, kuoff, pbm00 + k0 * kBRow, pbm10 + k0 * kBRow);
-          else warp_consume8<false>(pa, pb, pb1, porg, m8, x, acc, sink, cells, a, pq);
+          warp_consume8<false>(pa, pb, pb1, porg, m8, x, acc, sink, cells, a, pq);
         } else {
-          if (MMA) x = warp_load<0, FACT>(pa, pkv, pb, pb1);
-          // a window moves inside this group (rare): rolled loop, so that the fold is not inlined eight times
+          // a window moves inside this group: rolled loop, so that the fold is not inlined eight times
           // (the unrolled variant doubled the code size and a third of the stalls were instruction fetches)
 #pragma unroll 1
           for (int u = 0; u < 8; ++u) {
-            const WarpOps nxt = warp_load<1, FACT>(pa + u * ROW, pkv + u * ROW, pb + u * kBRow, pb1 + u * kBRow);
+            const WarpOps nxt = warp_load<1, false>(pa + u * ROW, 0u, pb + u * kBRow, pb1 + u * kBRow);
             if ((m8 >> u) & 1u) {
               acc.fold(sink, cells.i, cells.wj, pq);
               cells.set(lds_u32(porg + 4 * u), a);
@@ -832,8 +940,11 @@ struct ItemList {
   int win_first, win_last;
 };
 
+// Resident one-warp CTAs per SM the register allocation aims at: 24 (80 registers) for the tensor paths, measured
+// against 20 / 28 / 32 (3xTF32 7.56 / 7.33 / 7.47 ms, bf16 7.05 / 6.92 ms at 20 / 24 on configs[1]); 20 for FFMA2.
+constexpr int warp_minb(int mma) { return mma ? 24 : 20; }
 template <int MMA>
-__global__ void __launch_bounds__(32, 20) grid_warp_kernel(ItemList il, const RecP* __restrict__ recs, GridGeom g,
+__global__ void __launch_bounds__(32, warp_minb(MMA)) grid_warp_kernel(ItemList il, const RecP* __restrict__ recs, GridGeom g,
                                                             float* __restrict__ grid, int plane_base, int nslots) {
   if (il.hdr->overflow) return;
   const uint32_t n = il.counters[0], njobs = il.hdr->njobs;
@@ -929,7 +1040,7 @@ cip_status launch_warp(cip_ctx* ctx, cudaStream_t stream, const ItemList& jl, co
   constexpr int smem = warp_smem_bytes(MMA != 0);
   CIP_CHECK_CUDA(cudaFuncSetAttribute(kern, cudaFuncAttributeMaxDynamicSharedMemorySize, smem));
   CIP_CHECK_CUDA(cudaFuncSetAttribute(kern, cudaFuncAttributePreferredSharedMemoryCarveout, (int)cudaSharedmemCarveoutMaxShared));
-  kern<<<ctx->sm_count * 20, 32, smem, stream>>>(jl, recs, g, grid, plane_base, nslots);
+  kern<<<ctx->sm_count * warp_minb(MMA), 32, smem, stream>>>(jl, recs, g, grid, plane_base, nslots);
   return CIP_OK;
 }
 
@@ -950,9 +1061,14 @@ cip_status launch(cip_ctx* ctx, int slot, cudaStream_t stream, const GridGeom& g
       uint32_t* counters = w.items.as<uint32_t>() + w.cap_jobs;
       CIP_CHECK_CUDA(cudaMemsetAsync(counters + 1, 0, sizeof(uint32_t), stream));  // the same items may be gridded again (plane blocks)
       const ItemList il{w.jobs.as<Job>(), w.items.as<uint32_t>(), counters, w.hdr.as<BinHeader>(), win_first, win_last};
-      const int mma = getenv("CIP_GRID_MMA") ? atoi(getenv("CIP_GRID_MMA")) : 1;
-      if (mma == 0) CIP_TRY((launch_warp<0>(ctx, stream, il, reinterpret_cast<const RecP*>(recs), g, static_cast<float*>(grid), plane_base, nslots)));
-      else CIP_TRY((launch_warp<1>(ctx, stream, il, reinterpret_cast<const RecP*>(recs), g, static_cast<float*>(grid), plane_base, nslots)));
+      // Operand form of the tensor path: two-term bfloat16 (2.8e-6 relative rms arithmetic error) where the plan's
+      // kernel is coarser than that anyway, 3xTF32 (the float32 floor, 2e-6 against the FFMA2 form's 1.9e-6) otherwise.
+      const int mma = getenv("CIP_GRID_MMA") ? atoi(getenv("CIP_GRID_MMA")) : (g.bf16_operands ? 2 : 1);
+      const RecP* rp = reinterpret_cast<const RecP*>(recs);
+      float* gp = static_cast<float*>(grid);
+      if (mma == 0) CIP_TRY((launch_warp<0>(ctx, stream, il, rp, g, gp, plane_base, nslots)));
+      else if (mma == 2) CIP_TRY((launch_warp<2>(ctx, stream, il, rp, g, gp, plane_base, nslots)));
+      else CIP_TRY((launch_warp<1>(ctx, stream, il, rp, g, gp, plane_base, nslots)));
     } else {
       // float64: producer / consumer warp pair ("residue owner")
       constexpr size_t smem = grid_smem_bytes<R>();

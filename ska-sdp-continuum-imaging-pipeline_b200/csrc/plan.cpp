@@ -120,6 +120,8 @@ GridGeom make_geom(const cip_plan& p) {
   g.nplanes = p.nplanes;
   g.do_wstacking = p.do_wstacking;
   g.beta_w = (float)(p.beta * p.support);
+  KernelEntry ke;
+  g.bf16_operands = kernel_lookup(p.sigma, p.support, &ke) && ke.err >= 5e-6;
   g.beta_wd = p.beta * p.support;
   if (p.support <= kFastSupport) {
     g.win_step = kWin - p.support + 1;

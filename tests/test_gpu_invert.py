@@ -319,12 +319,13 @@ def _with_env(name, value, fn):
         os.environ.pop(name)
 
 
-@pytest.mark.parametrize("env", [("CIP_GRID_TC", "1"), ("CIP_GRID_MMA", "0"), ("CIP_DEVICE_CHUNKS", "3"), ("CIP_FFT_2D", "1"),
+@pytest.mark.parametrize("env", [("CIP_GRID_TC", "1"), ("CIP_GRID_MMA", "0"), ("CIP_GRID_MMA", "1"), ("CIP_DEVICE_CHUNKS", "3"), ("CIP_FFT_2D", "1"),
                                  ("CIP_FFT", "cufft"), ("CIP_BIN_TABLE_ENTRIES", "1")])
 def test_kernel_variants_agree(wg, small, wide, env):
     """The alternatives kept behind environment switches compute the same sums in another order: the tcgen05
     gridder (accumulators in tensor memory, whose float32 accumulation truncates: looser agreement), FFMA2 rank-1
-    updates instead of 3xTF32 mma.sync tiles, device inputs cut into chunks that are binned and gridded on two
+    updates and 3xTF32 mma.sync tiles instead of the two-term bfloat16 tiles this plan's kernel error allows (operands
+    held to 2^-18: 2.8e-6 relative rms, profiles/r2z_accuracy_modes.txt), device inputs cut into chunks that are binned and gridded on two
     streams, cuFFT's 2-D plan and one w-screen pass / cuFFT 1-D transforms around a transposed crop instead of the own
     pruned transform with the fused w-screen, one binning pass per window (what a key table too large for one pass falls back to)."""
     name, value = env
@@ -341,7 +342,7 @@ def test_kernel_variants_agree(wg, small, wide, env):
         alt, ainfo = _with_env(name, value, lambda: invert(wg, prob))
         if name == "CIP_BIN_TABLE_ENTRIES":
             assert ainfo["report"]["nblocks"] > info["report"]["nblocks"] >= 1
-    assert dft.rel_rms(alt, base) <= (6e-5 if name == "CIP_GRID_TC" else 2e-6)
+    assert dft.rel_rms(alt, base) <= {"CIP_GRID_TC": 6e-5, "CIP_GRID_MMA": 8e-6}.get(name, 2e-6)
     assert dft.rel_rms(alt, ref) <= TOL_FP32
 
 
