@@ -141,14 +141,21 @@ __global__ void __launch_bounds__(256) correct_kernel(CorrectParams p, const dou
   __shared__ double ck[64];
   for (int q = threadIdx.x; q < p.ncheb; q += blockDim.x) ck[q] = tables[p.nx + p.ny + q];
   __syncthreads();
+  // the factor is even in m: one thread serves the columns j and ny - j (bit-identical to one thread per pixel)
   const int j = blockIdx.x * blockDim.x + threadIdx.x;
   const int i = p.row_begin + blockIdx.y;
-  if (j >= p.ny || i >= p.row_end) return;
+  if (j > p.ny / 2 || i >= p.row_end) return;
   const double* cu = tables;
   const double* cv = tables + p.nx;
   const double l = (i - p.nx / 2) * p.px, m = (j - p.ny / 2) * p.py, e = l * l + m * m;
   const size_t k = (size_t)i * p.ny + j;
-  if (e >= 1.0) { image[k] = 0; return; }
+  const bool twin = j > 0 && 2 * j < p.ny;
+  const size_t k2 = (size_t)i * p.ny + (p.ny - j);
+  if (e >= 1.0) {
+    image[k] = 0;
+    if (twin) image[k2] = 0;
+    return;
+  }
   double fac = cu[i] * cv[j];
   if (p.do_wstacking) {
     const double nm1 = -e / (sqrt(1.0 - e) + 1.0);
@@ -163,7 +170,9 @@ __global__ void __launch_bounds__(256) correct_kernel(CorrectParams p, const dou
     const double cw = fma(t, b1, ck[0] - b2);
     fac *= cw * (nm1 + 1.0);
   }
-  image[k] = (R)((double)image[k] * (p.scale / fac));
+  const double f = p.scale / fac;
+  image[k] = (R)((double)image[k] * f);
+  if (twin) image[k2] = (R)((double)image[k2] * f);
 }
 
 }  // namespace
@@ -289,7 +298,7 @@ cip_status run_correct(cip_ctx* ctx, const cip_plan& pl, void* image, int row_be
   }
   CorrectParams p{nx, ny, pl.pixsize_x, pl.pixsize_y, pl.dw, pl.nshift, scale, 1.0 / (ximax * ximax),
                   ctx->tables_ncheb, pl.do_wstacking, row_begin, row_end};
-  dim3 grd((ny + 255) / 256, row_end - row_begin);
+  dim3 grd((ny / 2 + 1 + 255) / 256, row_end - row_begin);
   if (pl.accumulate_fp64)
     correct_kernel<double><<<grd, 256, 0, ctx->stream>>>(p, ctx->tables.as<double>(), static_cast<double*>(image));
   else
