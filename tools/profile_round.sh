@@ -18,8 +18,13 @@ CMD="python bench.py --steps 1 --warmup 1 --no-cpu --no-parity"
 if $CMD > $OUT/plain.log 2>&1; then
   # launches of the last timed step and the e2e step included; warm-up launches skipped by name filter + count
   ncu --metrics gpu__time_duration.sum --clock-control none -k "$KERNELS" -c 400 --csv --log-file $OUT/${TAG}_launches.csv $CMD > $OUT/ncu1.log 2>&1
-  # one launch of each kernel of one step: skip the first step (warm-up, buffers grow there)
-  ncu --set full --clock-control none --import-source on -k "$KERNELS" -s 34 -c 34 -o $OUT/${TAG}_full $CMD > $OUT/ncu2.log 2>&1
+  # one launch of each kernel of one step (the first step is the warm-up, buffers grow there); the report of ~40
+  # kernels exceeds what gpurun brings back, so it is summarised on the box (tools/ncu_kernels.py) and dropped
+  ncu --set full --clock-control none -k "$KERNELS" -s 36 -c 40 -o $OUT/${TAG}_full $CMD > $OUT/ncu2.log 2>&1
+  python tools/ncu_kernels.py $OUT/${TAG}_full.ncu-rep --traffic $OUT/grid_kernel_traffic.json grid_warp_kernel > $OUT/${TAG}_kernels_ncu_summary.txt 2>&1
+  rm -f $OUT/${TAG}_full.ncu-rep
+  # the gridding kernel alone, with source-level sampling
+  ncu --set full --clock-control none --import-source on -k regex:grid_warp_kernel -s 1 -c 1 -o $OUT/${TAG}_grid $CMD > $OUT/ncu3.log 2>&1
   echo "ncu done"
 else
   echo "plain run failed; not profiled"
