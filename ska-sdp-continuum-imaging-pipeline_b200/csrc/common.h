@@ -241,7 +241,9 @@ struct cip_ctx {
   // binning workspaces: two sets, so that chunk c+1 is binned (context stream) while chunk c is gridded
   // (grid stream)
   cip::BinWork work[2];
-  cip::DevBuf call_flags;         // u32[4]: [0] sticky overflow of the binning passes of the current call
+  cip::DevBuf call_flags;         // u32[4]: [0] sticky overflow of the binning passes of the current call; bytes 32..47: u extent
+  int rows_kept_blocks = 0;       // > 0: only the first and the last rows_kept_blocks row blocks of every resident plane hold
+                                  // data (the others were not cleared and must not be read); 0: all rows
   void* flags_host = nullptr;     // mapped pinned mirror of call_flags and the last BinHeader (read after the sync)
   void* flags_host_dev = nullptr;
   cudaStream_t grid_stream = nullptr;
@@ -336,6 +338,11 @@ cip_status fft_rows(cip_ctx* ctx, void* data, int n, int batch, int fp64);  // d
 cip_status run_fft_screen(cip_ctx* ctx, const cip_plan& p, void* grid, int plane_base, int nslots, void* image,
                           double* ms_fft, double* ms_wscreen);
 cip_status pfft_prepare(cip_ctx* ctx, const cip_plan& p, bool* ok);  // tables and work area; *ok: the plan is supported
+// Row blocks (pfft.cu): a plane of 1 GB and more counts as kRowBlocks blocks of rows, and the blocks the visibilities
+// cannot reach (|u| beyond their extent: rows that were never written) are neither cleared, nor transformed along v,
+// nor read.  pfft_row_blocks: rows per block if this plan's transform can skip blocks, else 0.
+constexpr int kRowBlocks = 32;
+int pfft_row_blocks(cip_ctx* ctx, const cip_plan& p);
 cip_status run_pfft_screen(cip_ctx* ctx, const cip_plan& p, void* grid, int plane_base, int nslots, void* image);
 void pfft_release(cip_ctx* ctx);
 cip_status run_wscreen(cip_ctx* ctx, const cip_plan& p, const void* grid, int plane_base, int nslots, void* image);

@@ -77,6 +77,51 @@ extern "C" cip_status cip_w_histogram(cip_ctx* ctx, const cip_invert_args* args,
   return CIP_OK;
 }
 
+// Largest |u| (metres) over the rows and largest frequency, as the bit patterns of non-negative doubles (they order like
+// unsigned integers): what bounds the plane rows the visibilities can reach.
+__global__ void __launch_bounds__(256) uext_kernel(const double* __restrict__ uvw, int64_t nrow, const double* __restrict__ freq,
+                                                   int64_t nchan, unsigned long long* __restrict__ out) {
+  const int64_t t0 = (int64_t)blockIdx.x * blockDim.x + threadIdx.x, stride = (int64_t)gridDim.x * blockDim.x;
+  double um = 0.0, fm = 0.0;
+  for (int64_t r = t0; r < nrow; r += stride) um = fmax(um, fabs(uvw[3 * r]));
+  for (int64_t c = t0; c < nchan; c += stride) fm = fmax(fm, fabs(freq[c]));
+#pragma unroll
+  for (int o = 16; o; o >>= 1) {
+    um = fmax(um, __shfl_xor_sync(0xffffffffu, um, o));
+    fm = fmax(fm, __shfl_xor_sync(0xffffffffu, fm, o));
+  }
+  if ((threadIdx.x & 31) == 0) {
+    if (um > 0.0) atomicMax(out, (unsigned long long)__double_as_longlong(um));
+    if (fm > 0.0) atomicMax(out + 1, (unsigned long long)__double_as_longlong(fm));
+  }
+}
+
+// How many row blocks at either end of a plane (FFT order: u = 0 is row 0) the shards' visibilities can reach: a sample
+// at u wavelengths touches the rows within W / 2 + 1 of u px nu.  0: no block can be skipped (or the transform does
+// not work block-wise).  One small kernel and one 16-byte read-back per call.
+static cip_status reachable_row_blocks(cip_ctx* ctx, const DevInputs* ins, int nshards, const cip_plan& plan, int* kept) {
+  *kept = 0;
+  const int bs = pfft_row_blocks(ctx, plan);
+  if (bs == 0) return CIP_OK;
+  unsigned long long* d = reinterpret_cast<unsigned long long*>(static_cast<char*>(ctx->call_flags.p) + 32);
+  CIP_CHECK_CUDA(cudaMemsetAsync(d, 0, 16, ctx->stream));
+  for (int k = 0; k < nshards; ++k) {
+    if (ins[k].nrow == 0) continue;
+    const int blocks = (int)std::min<int64_t>((ins[k].nrow + 255) / 256, 4 * ctx->sm_count);
+    uext_kernel<<<blocks, 256, 0, ctx->stream>>>(ins[k].uvw, ins[k].nrow, ins[k].freq, ins[k].nchan, d);
+    ctx->launches++;
+  }
+  CIP_CHECK_CUDA(cudaGetLastError());
+  double ext[2];
+  CIP_TRY(fetch_small(ctx, d, 16, ext));
+  const double cells = ext[0] * ext[1] / kSpeedOfLight * plan.pixsize_x * plan.nu;  // |u| in cells, at most
+  if (!(cells < 0.5 * plan.nu)) return CIP_OK;                                       // wraps around (or NaN): every row
+  const int rows = (int)std::ceil(cells) + plan.support / 2 + 12;  // support, the 8-cell register window, slack
+  const int kb = rows / bs + 1;
+  if (2 * kb < kRowBlocks) *kept = kb;
+  return CIP_OK;
+}
+
 // Rows [r0, r1) of the staged inputs as inputs of their own.
 static DevInputs row_slice(const DevInputs& in, int64_t r0, int64_t r1) {
   DevInputs c = in;
@@ -150,6 +195,14 @@ static cip_status grid_accumulate_attempt(cip_ctx* ctx, const DevInputs* ins, co
     // the overlap when a report is requested.
     const bool dev_timing = rep && !tm.host;
     cudaStream_t gs = ctx->grid_stream;
+    // Large planes: the row blocks no visibility reaches are neither cleared, nor transformed along v, nor read
+    int kept_blocks = 0;
+    CIP_TRY(reachable_row_blocks(ctx, ins, nshards, *plan, &kept_blocks));
+    struct KeptGuard {
+      cip_ctx* c;
+      ~KeptGuard() { c->rows_kept_blocks = 0; }
+    } kept_guard{ctx};
+    ctx->rows_kept_blocks = kept_blocks;
     // The plane stack is cleared on the grid stream (ordered behind everything already on the context stream):
     // the first gridding pass needs it, the first binning pass does not, and the two have different limits (HBM
     // writes against issue slots), so they run side by side.
@@ -157,7 +210,16 @@ static cip_status grid_accumulate_attempt(cip_ctx* ctx, const DevInputs* ins, co
     CIP_CHECK_CUDA(cudaStreamWaitEvent(gs, ctx->zero_ev, 0));
     if (dev_timing) CIP_CHECK_CUDA(cudaEventRecord(ctx->ev[14], gs));
     const double tz0 = now_ms();
-    CIP_CHECK_CUDA(cudaMemsetAsync(ctx->grid.p, 0, plane_bytes * plan->nplanes, gs));
+    if (kept_blocks > 0) {
+      // the last kept rows of plane p and the first kept rows of plane p + 1 are one contiguous range
+      const size_t edge = plane_bytes / kRowBlocks * kept_blocks;
+      char* base = static_cast<char*>(ctx->grid.p);
+      CIP_CHECK_CUDA(cudaMemsetAsync(base, 0, edge, gs));
+      for (int p = 1; p < plan->nplanes; ++p) CIP_CHECK_CUDA(cudaMemsetAsync(base + plane_bytes * p - edge, 0, 2 * edge, gs));
+      CIP_CHECK_CUDA(cudaMemsetAsync(base + plane_bytes * plan->nplanes - edge, 0, edge, gs));
+    } else {
+      CIP_CHECK_CUDA(cudaMemsetAsync(ctx->grid.p, 0, plane_bytes * plan->nplanes, gs));
+    }
     if (dev_timing) CIP_CHECK_CUDA(cudaEventRecord(ctx->ev[15], gs));
     if (rep && !dev_timing) {
       CIP_CHECK_CUDA(cudaEventRecord(ctx->sync_ev, gs));

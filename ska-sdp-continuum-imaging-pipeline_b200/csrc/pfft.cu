@@ -566,6 +566,15 @@ static int pfft_variant(const PfftPlan* p, int fp64, int ny) {
   return p->ok_rows ? 1 : (ny % 4 == 0 ? 2 : 0);
 }
 
+int pfft_row_blocks(cip_ctx* ctx, const cip_plan& pl) {
+  if (!pfft_enabled() || pl.accumulate_fp64 || getenv("CIP_FFT_2D") || pl.nu % kRowBlocks) return 0;
+  const char* e = getenv("CIP_ROW_BLOCKS");  // 0: never, 1: always (tests on small planes)
+  if (e ? atoi(e) == 0 : (size_t)pl.nu * pl.nv * 8 < ((size_t)1 << 30)) return 0;
+  PfftPlan* p;
+  if (get_pfft(ctx, pl.nu, pl.nv, 0, &p) != CIP_OK || pfft_variant(p, 0, pl.npix_y) != 2) return 0;
+  return pl.nu / kRowBlocks;
+}
+
 // Whether the own transform handles this plan (else the cuFFT path of image.cu / fft.cu runs); creates the tables.
 cip_status pfft_prepare(cip_ctx* ctx, const cip_plan& pl, bool* ok) {
   *ok = false;
@@ -582,8 +591,11 @@ cip_status pfft_prepare(cip_ctx* ctx, const cip_plan& pl, bool* ok) {
   return CIP_OK;
 }
 
+// row_block > 0 and kept > 0: only the first and the last `kept` blocks of row_block rows hold data (the rows between
+// them were never written or cleared: pass A skips them, pass B1 takes them as zeros).
 template <typename T, bool SCREEN>
-static cip_status pfft_plane(cip_ctx* ctx, PfftPlan* p, const void* plane, int nu, int nv, int ny, const ScreenArgs& sa, void* out) {
+static cip_status pfft_plane(cip_ctx* ctx, PfftPlan* p, const void* plane, int nu, int nv, int ny, const ScreenArgs& sa, void* out,
+                             int row_block = 0, int kept = 0) {
   using C = cx<T>;
   const int pitch = pfft_pitch(ny);
   C* g = ctx->fft_t.as<C>();
@@ -609,14 +621,25 @@ static cip_status pfft_plane(cip_ctx* ctx, PfftPlan* p, const void* plane, int n
     if (hybrid) {
       // pass A by cuFFT: contiguous 1-D transforms along v, in place (its single-pass kernel runs near the HBM rate;
       // the own row pass of rows_kernel_p does not); pass B1 then reads the retained columns of the plane
-      CIP_TRY(fft_rows(ctx, const_cast<void*>(plane), nv, nu, 0));
+      if (row_block > 0 && kept > 0) {
+        // two transforms of kept * row_block rows each, one plan per distinct count (block-wise execution of one small
+        // plan costs more than it saves: 4.34 ms for 32 blocks of a 24576^2 plane against 3.58 ms in one piece,
+        // tools/experiments/fft_blocks.cu)
+        const int rows = kept * row_block;
+        float2* f = static_cast<float2*>(const_cast<void*>(plane));
+        CIP_TRY(fft_rows(ctx, f, nv, rows, 0));
+        CIP_TRY(fft_rows(ctx, f + (size_t)(nu - rows) * nv, nv, rows, 0));
+      } else {
+        CIP_TRY(fft_rows(ctx, const_cast<void*>(plane), nv, nu, 0));
+      }
     } else {
       const RowsAux aux{ta, reinterpret_cast<const int*>(tb + p->off_fb), reinterpret_cast<const int*>(tb + p->off_bf), p->wf};
       auto ka = small ? rows_kernel_p<256> : rows_kernel_p<512>;
       CIP_CHECK_CUDA(cudaFuncSetAttribute(ka, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)p->smem_a));
       ka<<<nu, small ? 256 : 512, p->smem_a, st>>>(static_cast<const float2*>(plane), reinterpret_cast<float*>(g), p->sa, aux, nv, ny, gpitch);
     }
-    const Cols1Src src{static_cast<const float2*>(plane), nv, ny};
+    const bool pruned = hybrid && row_block > 0 && kept > 0;
+    const Cols1Src src{static_cast<const float2*>(plane), nv, ny, pruned ? kept * row_block : nu, pruned ? nu - kept * row_block : nu};
     auto launch1 = [&](auto kern, int P) -> cip_status {
       const size_t smem = 2 * (size_t)p->n1 * P * sizeof(float4);
       const int ncb = gpitch / P;
@@ -673,6 +696,8 @@ cip_status run_pfft_screen(cip_ctx* ctx, const cip_plan& pl, void* grid, int pla
   CIP_REQUIRE(pfft_variant(p, pl.accumulate_fp64, pl.npix_y), "own transform not available for %d x %d", pl.nu, pl.nv);
   const size_t csize = pl.accumulate_fp64 ? 16 : 8;
   CIP_TRY(ctx->fft_t.ensure(csize * pl.nu * pfft_pitch(pl.npix_y)));
+  const int row_block = pfft_row_blocks(ctx, pl);
+  CIP_REQUIRE(row_block > 0 || ctx->rows_kept_blocks == 0, "row blocks were skipped for a transform that reads every row");
   for (int s = 0; s < nslots; ++s) {
     const int plane = plane_base + s;
     if (plane >= pl.nplanes) break;
@@ -680,7 +705,7 @@ cip_status run_pfft_screen(cip_ctx* ctx, const cip_plan& pl, void* grid, int pla
                   pl.do_wstacking, ctx->call_flags.as<uint32_t>()};
     const char* f = static_cast<const char*>(grid) + csize * (size_t)s * pl.nu * pl.nv;
     if (pl.accumulate_fp64) CIP_TRY((pfft_plane<double, true>(ctx, p, f, pl.nu, pl.nv, pl.npix_y, sa, image)));
-    else CIP_TRY((pfft_plane<float, true>(ctx, p, f, pl.nu, pl.nv, pl.npix_y, sa, image)));
+    else CIP_TRY((pfft_plane<float, true>(ctx, p, f, pl.nu, pl.nv, pl.npix_y, sa, image, row_block, ctx->rows_kept_blocks)));
   }
   return CIP_OK;
 }

@@ -226,6 +226,7 @@ __device__ __forceinline__ void cols_prefetch(float4* sm, const float4* __restri
 struct Cols1Src {
   const float2* plane;  // AOS only
   int nv, ny;
+  int keep_lo, keep_hi;  // AOS only: rows [keep_lo, keep_hi) of the plane are known to be zero and are not read
 };
 
 // Pass B1, persistent: tile = (column block cb, residue r); see pfft.cu.
@@ -247,7 +248,11 @@ __global__ void __launch_bounds__(128, 4) cols1_kernel_p(float4* __restrict__ g,
       const float2* from = src.plane + (size_t)r * src.nv + c;
       const size_t step = (size_t)n2 * src.nv;
       if (jp < src.ny) {
-        for (int k = threadIdx.x / P; k < n1; k += blockDim.x / P) cp_async16(sm + k * P + p, from + (size_t)k * step);
+        for (int k = threadIdx.x / P; k < n1; k += blockDim.x / P) {
+          const int row = r + k * n2;
+          if (row < src.keep_lo || row >= src.keep_hi) cp_async16(sm + k * P + p, from + (size_t)k * step);
+          else sm[k * P + p] = make_float4(0.f, 0.f, 0.f, 0.f);
+        }
       } else {
         for (int k = threadIdx.x / P; k < n1; k += blockDim.x / P) sm[k * P + p] = make_float4(0.f, 0.f, 0.f, 0.f);
       }

@@ -346,6 +346,27 @@ def test_kernel_variants_agree(wg, small, wide, env):
     assert dft.rel_rms(alt, ref) <= TOL_FP32
 
 
+def test_unreached_row_blocks_are_skipped(wg):
+    """Planes of 1 GB and more count as 32 row blocks, and the blocks beyond the visibilities' |u| extent are neither
+    cleared nor transformed along v nor read (CIP_ROW_BLOCKS=1 forces that on a small plane).  The skipped rows hold
+    whatever the previous call left there -- here a problem that reaches every row -- and must not be read."""
+    everywhere = random_problem(nrow=3000, nchan=8, nx=256, fov_scale=1.2, seed=5)
+    centred = random_problem(nrow=3000, nchan=8, nx=256, fov_scale=0.4, seed=6)  # |u| px <= 0.16
+    uvw, freq, vis, wgt, nx, px = centred
+    ref = dft.dft_dirty(uvw, freq, vis, wgt, nx, nx, px, px)
+    base, binfo = _with_env("CIP_ROW_BLOCKS", "0", lambda: invert(wg, centred))
+    _with_env("CIP_ROW_BLOCKS", "1", lambda: invert(wg, everywhere))
+    alt, ainfo = _with_env("CIP_ROW_BLOCKS", "1", lambda: invert(wg, centred))
+    assert ainfo["plan"]["nu"] % 32 == 0 and ainfo["plan"] == binfo["plan"]
+    # two transforms along v per plane (the first and the last rows) instead of one, and the extent kernel
+    assert ainfo["report"]["launches"] - binfo["report"]["launches"] == ainfo["plan"]["nplanes"] + 1, "no row block was skipped"
+    assert dft.rel_rms(alt, base) <= 2e-6
+    assert dft.rel_rms(alt, ref) <= TOL_FP32
+    full, finfo = _with_env("CIP_ROW_BLOCKS", "1", lambda: invert(wg, everywhere))
+    uvw, freq, vis, wgt, nx, px = everywhere
+    assert dft.rel_rms(full, dft.dft_dirty(uvw, freq, vis, wgt, nx, nx, px, px)) <= TOL_FP32
+
+
 def test_invalid_arguments_raise(wg, small):
     (uvw, freq, vis, wgt, nx, px), _ = small
     with pytest.raises(ValueError):
