@@ -267,9 +267,16 @@ def run_b200(args):
         shard = StokesIGridderInput(d_freq, None, d_uvw, d_vis, d_wgt)
         reps = []
         acc = accumulate_shards_by_w if args.sharding == "w" else accumulate_shards
+        t_a = time.perf_counter()
         img, plan, sumw = acc([shard], N, px, epsilon=cfg.epsilon, reports=reps)
-        reports.extend(reps)
+        torch.cuda.synchronize()
+        t_b = time.perf_counter()  # this rank's partial image is complete: what follows includes the wait for the slowest rank
         img = reduce_and_correct(img, plan, sumw, normalise=False)
+        torch.cuda.synchronize()
+        if reps:
+            reps[-1]["ms_accumulate_host"] = 1e3 * (t_b - t_a)
+            reps[-1]["ms_reduce_host"] = 1e3 * (time.perf_counter() - t_b)
+        reports.extend(reps)
         return img, plan.as_dict()
 
     def barrier():
@@ -386,6 +393,20 @@ def run_b200(args):
     del h_vis, h_wgt, n_vis_np, n_wgt_np
     d2h = int(N * N * 4)
 
+    # every rank's share of a sharded step: accumulate (its own work) against reduce (collectives + waiting for the
+    # slowest rank), and its planes / stage times -- what shows an unbalanced sharding
+    per_rank = None
+    if world > 1:
+        mine = {"rank": rank,
+                "ms_accumulate": float(np.sum([r.get("ms_accumulate_host", 0.0) for r in timed_reports]) / args.steps),
+                "ms_reduce": float(np.sum([r.get("ms_reduce_host", 0.0) for r in timed_reports]) / args.steps),
+                "nplanes": [r["nplanes"] for r in timed_reports if "nplanes" in r][:1],
+                **{k: float(np.sum([r[k] for r in timed_reports]) / args.steps) for k in ("ms_bin", "ms_grid", "ms_fft", "ms_zero")},
+                "phases_ms": {k: float(np.sum([r["phases_ms"].get(k, 0.0) for r in timed_reports if "phases_ms" in r]) / args.steps)
+                              for k in sorted({k for r in timed_reports for k in r.get("phases_ms", {})})}}
+        gathered = [None] * world
+        dist.all_gather_object(gathered, mine)
+        per_rank = gathered
     if rank != 0:
         if world > 1:
             dist.destroy_process_group()
@@ -405,6 +426,8 @@ def run_b200(args):
         stage["w_sharding_phases_ms"] = {k: float(np.sum([r["phases_ms"].get(k, 0.0) for r in timed_reports
                                                            if "phases_ms" in r]) / args.steps) for k in phase_keys}
         stage["nplanes_of_rank0"] = [r["nplanes"] for r in timed_reports if "nplanes" in r][:4]
+    if per_rank is not None:
+        stage["per_rank"] = per_rank
     # ---- per-stage rooflines and the whole-invert fraction of SURVEY.md 8(d) --------------------------------
     nrow_, nchan_ = uvw.shape[0], freq.shape[0]
     nu_, nv_, npl_, sg_ = plan["nu"], plan["nv"], plan["nplanes"], plan["sigma"]

@@ -336,16 +336,19 @@ def image_to_host(image) -> NDArray:
 W_HIST_BINS = 4096
 
 
-def w_slab_edges(counts, wmin: float, wmax: float, nslabs: int, *, plane_cost: float = 0.0, dw: float = 0.0
-                 ) -> list[float]:
+def w_slab_edges(counts, wmin: float, wmax: float, nslabs: int, *, plane_cost: float = 0.0, dw: float = 0.0,
+                 bin_factor=None) -> list[float]:
     """Cut the |w| axis into ``nslabs`` slabs of (nearly) equal COST from a histogram of ``len(counts)`` equal bins
     over [wmin, wmax]: a bin costs its samples plus ``plane_cost`` sample-equivalents per w plane it spans (bin
     width / dw) -- with plane_cost = 0 the slabs hold equal numbers of samples, with a large one equal numbers of
     planes (what matters when the per-plane FFTs dominate).  Returns nslabs + 1 edges, the first 0 and the last
-    +inf, so that every sample falls into exactly one slab [edges[s], edges[s + 1])."""
+    +inf, so that every sample falls into exactly one slab [edges[s], edges[s + 1]).  ``bin_factor`` (one number per
+    bin) scales the cost of the bins: what ``rebalanced_bin_factor`` has learnt from measured times."""
     cost = np.asarray(counts, dtype=np.float64).copy()
     if plane_cost > 0 and dw > 0 and wmax > wmin:
         cost += plane_cost * (wmax - wmin) / len(cost) / dw
+    if bin_factor is not None:
+        cost *= np.asarray(bin_factor, dtype=np.float64)
     cum = np.concatenate([[0.0], np.cumsum(cost)])
     total = cum[-1]
     edges = [0.0]
@@ -356,6 +359,30 @@ def w_slab_edges(counts, wmin: float, wmax: float, nslabs: int, *, plane_cost: f
         edges.append(max(wmin + (wmax - wmin) * b / len(cost), edges[-1]))
     edges.append(float("inf"))
     return edges
+
+
+def rebalanced_bin_factor(bin_factor, edges, wmin: float, wmax: float, times, *, gain: float = 1.3,
+                          done_within: float = 0.03):
+    """One step of measured load balancing of the |w| slabs: ``times[s]`` is what slab s (cut at ``edges``) took on its
+    rank; the cost of every histogram bin inside slab s is scaled by (times[s] / mean(times)) ** gain, so that the
+    next cut gives slow slabs less and fast slabs more.  Every slab carries a fixed part (W - 1 extra planes), so its
+    time answers less than proportionally to its content; the gain above 1 makes up for that without overshooting
+    while that fixed part is at least a quarter of a slab's time.  Returns the new factors (the old ones when the
+    slowest slab is within ``done_within`` of the mean).  Pure function of its arguments: every rank computes the
+    same result from the gathered times."""
+    f = np.asarray(bin_factor, dtype=np.float64).copy()
+    t = np.asarray(times, dtype=np.float64)
+    if len(t) < 2 or not np.all(t > 0) or t.max() <= (1.0 + done_within) * t.mean():
+        return f
+    nb = len(f)
+    centres = wmin + (wmax - wmin) * (np.arange(nb) + 0.5) / nb
+    slab = np.clip(np.searchsorted(np.asarray(edges[1:-1], dtype=np.float64), centres, side="right"), 0, len(t) - 1)
+    f *= (t / t.mean())[slab] ** gain
+    return f / f.mean()
+
+
+# problem signature -> bin factors learnt over the calls so far (an imaging run inverts the same uvw many times)
+_SLAB_BALANCE: dict = {}
 
 
 # sample-equivalents of one w plane per grid cell (FFT + w-screen ~ 12 ps per cell, binning + gridding ~ 65 ps per
@@ -505,13 +532,19 @@ def accumulate_shards_by_w(shards: Sequence[StokesIGridderInput], num_pixels: in
         t = torch.from_numpy(counts).to(dev)
         torch.distributed.all_reduce(t, group=group)
         counts = t.cpu().numpy()
-    edges = w_slab_edges(counts, wmin, wmax, nslabs, plane_cost=PLANE_COST_PER_CELL * common.nu * common.nv, dw=common.dw)
+    # the slabs are cut by modelled cost, corrected by what the ranks measured on earlier calls of the same problem
+    balance_key = (world, num_pixels, float(pixel_size_lm), float(epsilon), bool(accumulate_fp64), int(nactive),
+                   float(wmin), float(wmax))
+    bin_factor = _SLAB_BALANCE.get(balance_key) if world > 1 and not os.environ.get("CIP_NO_SLAB_REBALANCE") else None
+    edges = w_slab_edges(counts, wmin, wmax, nslabs, plane_cost=PLANE_COST_PER_CELL * common.nu * common.nv, dw=common.dw,
+                         bin_factor=bin_factor)
     mark("ms_histogram")
     mine = shards
     if world > 1:
         mine = _exchange_rows_by_slab(shards, edges, group=group, device=dev)
         mark("ms_exchange")
     plan = common
+    t_own = time.perf_counter()  # the device is idle here (mark synchronises)
     for s in ([rank] if world > 1 else range(nslabs)):
         slab = (edges[s], min(edges[s + 1], 1e300))
         smin, smax, sact, _ssum, skeep = scan_all(mine, slab)
@@ -524,6 +557,14 @@ def accumulate_shards_by_w(shards: Sequence[StokesIGridderInput], num_pixels: in
         for rep in _grid_shards(ctx, [a for a, _sh, _w in skeep], plan, image, reports is not None):
             reports.append(dict(rep, nplanes=plan.nplanes, slab=s))
         mark("ms_grid_call")
+    if world > 1 and not os.environ.get("CIP_NO_SLAB_REBALANCE"):
+        # every rank's time for its slab -> the bin factors of the next call (one small all-gather)
+        mine = torch.tensor([time.perf_counter() - t_own], dtype=torch.float64, device=dev)
+        every = torch.empty(world, dtype=torch.float64, device=dev)
+        torch.distributed.all_gather_into_tensor(every, mine, group=group)
+        _SLAB_BALANCE[balance_key] = rebalanced_bin_factor(np.ones(W_HIST_BINS) if bin_factor is None else bin_factor,
+                                                           edges, wmin, wmax, every.cpu().numpy())
+        mark("ms_balance")
     if reports:
         reports[-1]["phases_ms"] = phases
     return image, plan, sumw
