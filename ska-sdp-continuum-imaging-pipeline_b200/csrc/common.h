@@ -338,7 +338,7 @@ cip_status fft_rows(cip_ctx* ctx, void* data, int n, int batch, int fp64);  // d
 cip_status run_fft_screen(cip_ctx* ctx, const cip_plan& p, void* grid, int plane_base, int nslots, void* image,
                           double* ms_fft, double* ms_wscreen);
 cip_status pfft_prepare(cip_ctx* ctx, const cip_plan& p, bool* ok);  // tables and work area; *ok: the plan is supported
-// Row blocks (pfft.cu): a plane of 1 GB and more counts as kRowBlocks blocks of rows, and the blocks the visibilities
+// Row blocks (pfft.cu): a plane of 128 MB and more counts as kRowBlocks blocks of rows, and the blocks the visibilities
 // cannot reach (|u| beyond their extent: rows that were never written) are neither cleared, nor transformed along v,
 // nor read.  pfft_row_blocks: rows per block if this plan's transform can skip blocks, else 0.
 constexpr int kRowBlocks = 32;

@@ -569,7 +569,7 @@ static int pfft_variant(const PfftPlan* p, int fp64, int ny) {
 int pfft_row_blocks(cip_ctx* ctx, const cip_plan& pl) {
   if (!pfft_enabled() || pl.accumulate_fp64 || getenv("CIP_FFT_2D") || pl.nu % kRowBlocks) return 0;
   const char* e = getenv("CIP_ROW_BLOCKS");  // 0: never, 1: always (tests on small planes)
-  if (e ? atoi(e) == 0 : (size_t)pl.nu * pl.nv * 8 < ((size_t)1 << 30)) return 0;
+  if (e ? atoi(e) == 0 : (size_t)pl.nu * pl.nv * 8 < ((size_t)128 << 20)) return 0;  // below 128 MB the extent read-back costs what it saves
   PfftPlan* p;
   if (get_pfft(ctx, pl.nu, pl.nv, 0, &p) != CIP_OK || pfft_variant(p, 0, pl.npix_y) != 2) return 0;
   return pl.nu / kRowBlocks;

@@ -347,7 +347,7 @@ def test_kernel_variants_agree(wg, small, wide, env):
 
 
 def test_unreached_row_blocks_are_skipped(wg):
-    """Planes of 1 GB and more count as 32 row blocks, and the blocks beyond the visibilities' |u| extent are neither
+    """Planes of 128 MB and more count as 32 row blocks, and the blocks beyond the visibilities' |u| extent are neither
     cleared nor transformed along v nor read (CIP_ROW_BLOCKS=1 forces that on a small plane).  The skipped rows hold
     whatever the previous call left there -- here a problem that reaches every row -- and must not be read."""
     everywhere = random_problem(nrow=3000, nchan=8, nx=256, fov_scale=1.2, seed=5)
