@@ -7,7 +7,7 @@ set -u
 TAG=${1:-rX}
 OUT=gpurun_out
 mkdir -p $OUT
-KERNELS='regex:^(cols[12]_kernel|correct_kernel|finv_kernel|grid_|hist_kernel|items_kernel|records_kernel|rows_kernel|scan_|whist|wscreen|transpose_crop|vector_fft|regular_fft)'
+KERNELS='regex:^(cols[12]_kernel|correct_kernel|finv_kernel|grid_|hist_kernel|uext_kernel|items_kernel|records_kernel|rows_kernel|scan_|whist|wscreen|transpose_crop|vector_fft|regular_fft)'
 (time timeout 900 python -m pytest tests -m gpu -x -q) > $OUT/${TAG}_pytest_gpu.log 2>&1
 echo "pytest rc=$?"
 timeout 400 python bench.py > $OUT/${TAG}_bench.json 2> $OUT/${TAG}_bench.err
