@@ -562,6 +562,8 @@ def accumulate_shards_by_w(shards: Sequence[StokesIGridderInput], num_pixels: in
         mine = torch.tensor([time.perf_counter() - t_own], dtype=torch.float64, device=dev)
         every = torch.empty(world, dtype=torch.float64, device=dev)
         torch.distributed.all_gather_into_tensor(every, mine, group=group)
+        if len(_SLAB_BALANCE) >= 64 and balance_key not in _SLAB_BALANCE:
+            _SLAB_BALANCE.clear()  # a long-running process that meets many different problems: start over
         _SLAB_BALANCE[balance_key] = rebalanced_bin_factor(np.ones(W_HIST_BINS) if bin_factor is None else bin_factor,
                                                            edges, wmin, wmax, every.cpu().numpy())
         mark("ms_balance")
