@@ -440,7 +440,11 @@ cip_status run_binning(cip_ctx* ctx, int slot, const DevInputs& in, const GridGe
   finv_kernel<<<nblk(nchan, 256), 256, 0, st>>>(in.freq, nchan, finv);
   const int rblocks = nblk(nrow * 32, 256);
   const BinConsts kc = bin_consts(g);
-  hist_kernel<<<rblocks, 256, 0, st>>>(in, g, kc, finv, table);
+  // One window and no |w| slab: every sample's key has window 0 whatever its plane, so the key pass skips the
+  // w coordinate (the record pass computes it for the records; both passes agree on the keys).
+  GridGeom gk = g;
+  if (g.nwin == 1 && !(in.w_hi > 0.0)) gk.do_wstacking = 0;
+  hist_kernel<<<rblocks, 256, 0, st>>>(in, gk, kc, finv, table);
   scan_reduce_kernel<<<(unsigned)ntiles, kScanThreads, 0, st>>>(table, n, w.tile_sums.as<uint2>());
   scan_tiles_kernel<<<1, 1024, 0, st>>>(w.tile_sums.as<uint2>(), ntiles, hdr, (uint32_t)std::min<int64_t>(w.cap_groups, 0xffffffffll),
                                         (uint32_t)std::min<int64_t>(w.cap_jobs, 0xffffffffll), ctx->call_flags.as<uint32_t>(),
