@@ -85,7 +85,7 @@ class ClockSampler:
     def start(self):
         try:
             self.p = subprocess.Popen(["nvidia-smi", "-i", str(self.index), f"--query-gpu={self.Q}",
-                                       "--format=csv,noheader,nounits", "-lms", "100"], stdout=self.f,
+                                       "--format=csv,noheader,nounits", "-lms", "25"], stdout=self.f,
                                       stderr=subprocess.DEVNULL)
         except OSError:
             self.p = None
@@ -241,6 +241,11 @@ def run_b200(args):
     if world > 1:
         os.environ.setdefault("NCCL_DEBUG_FILE", "/dev/stderr")  # keep stdout to the one JSON line
         dist.init_process_group("nccl", device_id=dev)
+    # nvidia-smi needs a second or two before its loop delivers samples: start it before the inputs are synthesised, so
+    # that it is sampling by the time the (short) timed region begins
+    sampler = ClockSampler(local)
+    if rank == 0:
+        sampler.start()
     cfg, px, wname, uvw, freq, desc = workload(args, world, rank)
     N = cfg.num_pixels
     d_vis, d_wgt = S.make_vis_torch(cfg, uvw, freq, px, dev, seed=1234 + rank)
@@ -307,9 +312,6 @@ def run_b200(args):
             ms = float(t.item())
         return ms
 
-    sampler = ClockSampler(local)
-    if rank == 0:
-        sampler.start()  # nvidia-smi takes a moment to start: launch it before the warm-up
     for _ in range(args.warmup):
         step_device()
     reports.clear()
