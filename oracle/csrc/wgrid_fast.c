@@ -4,8 +4,10 @@
  * call site src/ska_sdp_cip/invert.py:170-183; ducc0 itself is not installable here), organised for speed on many
  * cores rather than for checking:
  *   - records are binned by uv tile with a two-pass parallel counting sort (per-thread counts, no serial scatter);
- *   - a record's 3 W kernel taps are evaluated ONCE, in float32, and applied to all its W planes -- the planes of
- *     a block are resident together -- instead of re-evaluating them for every plane it touches;
+ *   - a record's 3 W kernel taps are evaluated ONCE, in float32 and eight at a time (a vectorised polynomial
+ *     exponential instead of libm calls), and applied to all its W planes -- the planes of a block are resident
+ *     together -- instead of re-evaluating them for every plane it touches; a row of the support is updated as 16
+ *     consecutive floats (two 8-wide fused multiply-adds);
  *   - tiles of 32 x 32 cells are processed in four colour phases so that concurrent threads never share a cell;
  *   - the w correction comes from a table in (n - 1) with linear interpolation instead of a quadrature per pixel.
  * wgrid.c stays the float64 checker; tests/test_oracle.py compares both with the DFT.  PARITY UNPINNED against ducc0.
@@ -116,14 +118,127 @@ static inline float es_f(float x, float bW)
   return t > 0.0f ? expf(bW * (sqrtf(t) - 1.0f)) : 0.0f;
 }
 
+/* The W taps of one axis, eight at a time so that the compiler vectorises the loop: exp(y), y in [-beta W, 0], as
+   2^round(z) * e^{(z - round(z)) ln 2} with a degree-6 Taylor polynomial on |.| <= ln(2)/2 (relative error 1.2e-7)
+   instead of a libm call per tap -- the taps were 2/3 of the gridding time. */
+static inline void es_taps8(float f, float tw, float bW, int W, float* restrict out)
+{
+#pragma omp simd
+  for (int a = 0; a < 8; ++a) {
+    const float x = (f + (float)a) * tw - 1.0f;
+    const float t = 1.0f - x * x;
+    const float tt = t > 0.0f ? t : 0.0f;
+    const float z = bW * (sqrtf(tt) - 1.0f) * 1.4426950408889634f;
+    const float zi = rintf(z), r = (z - zi) * 0.6931471805599453f;
+    float p = 1.3888889e-3f;
+    p = p * r + 8.3333333e-3f;
+    p = p * r + 4.1666667e-2f;
+    p = p * r + 1.6666667e-1f;
+    p = p * r + 0.5f;
+    p = p * r + 1.0f;
+    p = p * r + 1.0f;
+    union { float f; int32_t i; } u;
+    u.f = p;
+    u.i += (int32_t)zi << 23;
+    out[a] = (a < W && t > 0.0f) ? u.f : 0.0f;
+  }
+}
+
+#define FLB (FTS + 8) /* edge of a tile's private buffer: origins span FTS cells, supports reach 8 further */
+
+/* One record into `dst`, a stack of planes with `rowlen` cells per row and `plane` floats per plane, whose cell
+   (row i, column j) for this record's first support cell is (ib, jb); no wrap-around inside the support.  W <= 8:
+   one row of the support = 16 consecutive floats (re, im of 8 cells; the taps beyond W are zero), two 8-wide fused
+   multiply-adds per row. */
+static inline void fast_add8(const fast_rec* R, const float* ku, const float* kv2, const float* kw, int W, int c_lo, int c_hi,
+                             float* dst, int64_t plane, int64_t rowlen, int first_plane, int ib, int jb, int nu_wrap)
+{
+  for (int c = c_lo; c < c_hi; ++c) {
+    float* pl = dst + (int64_t)(R->p0 + c - first_plane) * plane;
+    const float vr = R->vr * kw[c], vi = R->vi * kw[c];
+    for (int a = 0; a < W; ++a) {
+      int i = ib + a; if (nu_wrap && i >= nu_wrap) i -= nu_wrap;
+      const float tr = vr * ku[a], ti = vi * ku[a];
+      float* restrict d = pl + 2 * ((int64_t)i * rowlen + jb);
+#pragma omp simd
+      for (int m = 0; m < 16; ++m) d[m] += kv2[m] * ((m & 1) ? ti : tr);
+    }
+  }
+}
+
 /* Planes [p_lo, p_hi) of the stack are resident in grid (p_hi - p_lo, nu, nv, 2) float32: every record adds its
-   W x W x (planes inside the block) contributions with taps evaluated once. */
+   W x W x (planes inside the block) contributions with taps evaluated once.  Tiles are processed in colour phases,
+   one thread per tile; the few tiles that hold a large share of the records (the core of an SKA layout lands in the
+   four tiles around the uv origin: a quarter of all records) are first handled by ALL threads, each with a private
+   copy of the tile that is summed into the grid afterwards -- without that the densest tile of each colour is the
+   critical path. */
 void oracle_fast_grid(const oracle_plan* P, const fast_rec* recs, const int64_t* offsets, int ntu, int ntv,
                       int p_lo, int p_hi, float* grid)
 {
   const int W = P->W, nu = P->nu, nv = P->nv;
   const float bW = (float)(P->beta * W), tw = 2.0f / (float)W;
   const int64_t plane = (int64_t)nu * nv * 2;
+  const int narrow = W <= 8;  /* the vectorised forms below hold 8 taps per axis */
+  const int npl = p_hi - p_lo;
+  const int64_t ntile = (int64_t)ntu * ntv;
+  int nth = 1;
+#ifdef _OPENMP
+  nth = omp_get_max_threads();
+#endif
+  int64_t dense = offsets[ntile] / (8 * (int64_t)nth);
+  if (dense < 4096) dense = 4096;
+  unsigned char* is_dense = (unsigned char*)calloc((size_t)ntile, 1);
+  if (narrow && nth > 1) {
+    const int64_t pplane = (int64_t)FLB * FLB * 2, pstride = pplane * npl;
+    float* priv = NULL;
+    for (int64_t t = 0; t < ntile; ++t) {
+      const int64_t n = offsets[t + 1] - offsets[t];
+      const int tu = (int)(t / ntv), tv = (int)(t % ntv);
+      if (n <= dense || tu >= ntu - 2 || tv >= ntv - 2) continue;
+      is_dense[t] = 1;
+      if (!priv) priv = (float*)malloc(sizeof(float) * (size_t)pstride * nth);
+      const int oi = tu * FTS - 16, oj = tv * FTS - 16;  /* first origin of the tile */
+#pragma omp parallel
+      {
+        int q = 0, nq = 1;
+#ifdef _OPENMP
+        q = omp_get_thread_num(); nq = omp_get_num_threads();
+#endif
+        float* mine = priv + (int64_t)q * pstride;
+        memset(mine, 0, sizeof(float) * (size_t)pstride);
+        for (int64_t k = offsets[t] + n * q / nq; k < offsets[t] + n * (q + 1) / nq; ++k) {
+          const fast_rec* R = &recs[k];
+          int c_lo = p_lo - R->p0, c_hi = p_hi - R->p0;
+          if (c_lo < 0) c_lo = 0;
+          if (c_hi > W) c_hi = W;
+          if (c_lo >= c_hi) continue;
+          float ku[8], kv[8], kw[8], kv2[16];
+          es_taps8(R->fu, tw, bW, W, ku);
+          es_taps8(R->fv, tw, bW, W, kv);
+          es_taps8(R->fw, tw, bW, W, kw);
+          for (int b = 0; b < 8; ++b) kv2[2 * b] = kv2[2 * b + 1] = kv[b];
+          fast_add8(R, ku, kv2, kw, W, c_lo, c_hi, mine, pplane, FLB, p_lo, R->i0 - oi, R->j0 - oj, 0);
+        }
+#pragma omp barrier
+#pragma omp for collapse(2) schedule(static)
+        for (int pc = 0; pc < npl; ++pc)
+          for (int li = 0; li < FLB; ++li) {
+            const int gi = ((oi + li + nu / 2) % nu + nu) % nu;
+            for (int lj = 0; lj < FLB; ++lj) {
+              float sr = 0.0f, si = 0.0f;
+              const int64_t o = (int64_t)pc * pplane + 2 * ((int64_t)li * FLB + lj);
+              for (int w = 0; w < nq; ++w) { sr += priv[(int64_t)w * pstride + o]; si += priv[(int64_t)w * pstride + o + 1]; }
+              if (sr != 0.0f || si != 0.0f) {
+                const int gj = ((oj + lj + nv / 2) % nv + nv) % nv;
+                float* d = grid + (int64_t)pc * plane + 2 * ((int64_t)gi * nv + gj);
+                d[0] += sr; d[1] += si;
+              }
+            }
+          }
+      }
+    }
+    free(priv);
+  }
   for (int colour = 0; colour < 5; ++colour) {
 #pragma omp parallel for schedule(dynamic, 1) collapse(2) if (colour < 4)
     for (int tu = (colour < 4 ? (colour >> 1) : 0); tu < ntu; tu += (colour < 4 ? 2 : 1))
@@ -131,6 +246,7 @@ void oracle_fast_grid(const oracle_plan* P, const fast_rec* recs, const int64_t*
         int seam = (tu >= ntu - 2) || (tv >= ntv - 2);
         if ((colour < 4) == seam) continue;
         int64_t t = (int64_t)tu * ntv + tv;
+        if (is_dense[t]) continue;
         for (int64_t k = offsets[t]; k < offsets[t + 1]; ++k) {
           const fast_rec* R = &recs[k];
           int c_lo = p_lo - R->p0, c_hi = p_hi - R->p0;
@@ -138,13 +254,27 @@ void oracle_fast_grid(const oracle_plan* P, const fast_rec* recs, const int64_t*
           if (c_hi > W) c_hi = W;
           if (c_lo >= c_hi) continue;
           float ku[16], kv[16], kw[16];
-          for (int a = 0; a < W; ++a) {
-            ku[a] = es_f((R->fu + a) * tw - 1.0f, bW);
-            kv[a] = es_f((R->fv + a) * tw - 1.0f, bW);
-            kw[a] = es_f((R->fw + a) * tw - 1.0f, bW);
+          if (narrow) {
+            es_taps8(R->fu, tw, bW, W, ku);
+            es_taps8(R->fv, tw, bW, W, kv);
+            es_taps8(R->fw, tw, bW, W, kw);
+          } else {
+            for (int a = 0; a < W; ++a) {
+              ku[a] = es_f((R->fu + a) * tw - 1.0f, bW);
+              kv[a] = es_f((R->fv + a) * tw - 1.0f, bW);
+              kw[a] = es_f((R->fw + a) * tw - 1.0f, bW);
+            }
           }
           int ib = ((R->i0 + nu / 2) % nu + nu) % nu, jb = ((R->j0 + nv / 2) % nv + nv) % nv;
           const int wrap_j = jb + W > nv;
+          if (narrow && jb + 8 <= nv) {
+            /* (the cells the zero taps beyond W "touch" lie inside this tile's halo, which no other thread works on in
+               this colour phase) */
+            float kv2[16];
+            for (int b = 0; b < 8; ++b) kv2[2 * b] = kv2[2 * b + 1] = kv[b];
+            fast_add8(R, ku, kv2, kw, W, c_lo, c_hi, grid, plane, nv, p_lo, ib, jb, nu);
+            continue;
+          }
           for (int c = c_lo; c < c_hi; ++c) {
             float* pl = grid + (int64_t)(R->p0 + c - p_lo) * plane;
             const float vr = R->vr * kw[c], vi = R->vi * kw[c];
@@ -166,6 +296,7 @@ void oracle_fast_grid(const oracle_plan* P, const fast_rec* recs, const int64_t*
         }
       }
   }
+  free(is_dense);
 }
 
 /* img += Re( F[(i-nx/2) mod nu, (j-ny/2) mod nv] exp(-2 pi i w_p (n-1+s)) ), float32 transform, float64 image */

@@ -145,3 +145,10 @@ def test_fast_cpu_baseline_reproduces_the_dft():
     blocks = wstack.ms2dirty_fast(uvw, freq, vis, wgt, nx, nx, px, px, 1e-4, max_stack_bytes=3 * 8 * 288 * 288)
     assert dft.rel_rms(fast, ref) < 1e-4 and dft.rel_rms(blocks, ref) < 1e-4
     assert dft.rel_rms(fast, wstack.ms2dirty(uvw, freq, vis, wgt, nx, nx, px, px, 1e-4)) < 5e-6
+    # all records in the tiles around the uv origin: the path on which every thread works on a private copy of a dense tile
+    uvw, freq, vis, wgt, nx, _ = random_problem(nrow=4000, nchan=16, nx=128, seed=3, uvscale=3.0, wscale=1.0)
+    px = 2e-4
+    ref = dft.dft_dirty(uvw, freq, vis, wgt, nx, nx, px, px)
+    fast = wstack.ms2dirty_fast(uvw, freq, vis, wgt, nx, nx, px, px, 1e-4)
+    assert dft.rel_rms(fast, ref) < 1e-4
+    assert dft.rel_rms(fast, wstack.ms2dirty(uvw, freq, vis, wgt, nx, nx, px, px, 1e-4)) < 3e-5  # float32 sums of 64,000 records
