@@ -21,7 +21,10 @@
 #endif
 
 #define C_LIGHT 299792458.0
-#define FTS 32 /* tile edge in cells, >= W - 1 */
+#define FTS 32 /* tile edge in cells, >= 8 (a support of W <= 8 cells plus the halo of the colour scheme); 16 measured
+                  no faster */
+#define FTH (FTS / 2)
+int oracle_fast_tile_edge(void) { return FTS; }
 
 typedef struct {
   int nx, ny, nu, nv, W, nplanes;
@@ -83,7 +86,7 @@ int64_t oracle_fast_bin(const oracle_plan* P, const double* uvw, int64_t nrow, c
         int64_t k = r * nchan + c;
         fast_rec R;
         if (!fast_make_rec(P, uvw + 3 * r, finv[c], vis[2 * k], vis[2 * k + 1], wgt ? wgt[k] : 1.0f, &R)) continue;
-        my[(int64_t)((R.i0 + 16) / FTS) * ntv + (R.j0 + 16) / FTS]++;
+        my[(int64_t)((R.i0 + FTH) / FTS) * ntv + (R.j0 + FTH) / FTS]++;
       }
 #pragma omp barrier
 #pragma omp single
@@ -104,7 +107,7 @@ int64_t oracle_fast_bin(const oracle_plan* P, const double* uvw, int64_t nrow, c
         int64_t k = r * nchan + c;
         fast_rec R;
         if (!fast_make_rec(P, uvw + 3 * r, finv[c], vis[2 * k], vis[2 * k + 1], wgt ? wgt[k] : 1.0f, &R)) continue;
-        recs[my[(int64_t)((R.i0 + 16) / FTS) * ntv + (R.j0 + 16) / FTS]++] = R;
+        recs[my[(int64_t)((R.i0 + FTH) / FTS) * ntv + (R.j0 + FTH) / FTS]++] = R;
       }
   }
   int64_t total = offsets[ntile];
@@ -185,7 +188,8 @@ void oracle_fast_grid(const oracle_plan* P, const fast_rec* recs, const int64_t*
 #ifdef _OPENMP
   nth = omp_get_max_threads();
 #endif
-  int64_t dense = offsets[ntile] / (8 * (int64_t)nth);
+  /* a tile left to one thread must not be a noticeable share of a colour phase: 1/64 of a thread's fair share at most */
+  int64_t dense = offsets[ntile] / (64 * (int64_t)nth);
   if (dense < 4096) dense = 4096;
   unsigned char* is_dense = (unsigned char*)calloc((size_t)ntile, 1);
   if (narrow && nth > 1) {
@@ -197,7 +201,7 @@ void oracle_fast_grid(const oracle_plan* P, const fast_rec* recs, const int64_t*
       if (n <= dense || tu >= ntu - 2 || tv >= ntv - 2) continue;
       is_dense[t] = 1;
       if (!priv) priv = (float*)malloc(sizeof(float) * (size_t)pstride * nth);
-      const int oi = tu * FTS - 16, oj = tv * FTS - 16;  /* first origin of the tile */
+      const int oi = tu * FTS - FTH, oj = tv * FTS - FTH;  /* first origin of the tile */
 #pragma omp parallel
       {
         int q = 0, nq = 1;

@@ -160,7 +160,8 @@ def ms2dirty_fast(uvw, freq, vis, wgt, nx, ny, px, py, epsilon=1e-4, *, sigma=No
         return img
     pl = make_plan(nx, ny, px, py, epsilon, wmin, wmax, nact, fp64=False, sigma=sigma, W=W)
     cp = _cplan(pl)
-    ntu, ntv = (pl.nu + 32) // 32 + 1, (pl.nv + 32) // 32 + 1
+    ts = L.oracle_fast_tile_edge()
+    ntu, ntv = (pl.nu + ts) // ts + 1, (pl.nv + ts) // ts + 1  # the last two tile rows / columns are the wrap-around seam
     recs = np.empty(nrow * nchan, dtype=np.dtype(_FastRec))
     offsets = np.zeros(ntu * ntv + 1, dtype=np.int64)
     L.oracle_fast_bin(C.byref(cp), _p(uvw), C.c_int64(nrow), _p(freq), C.c_int64(nchan), _p(vis),
